@@ -1,0 +1,233 @@
+/*
+ * rsp_chains.h -- C ABI of librsp_b200.so, the B200 (sm_100a) implementation of the rsp-chains hot path
+ *                 PLFG -> NCO -> SDF-FFT -> LogMagMux -> CFAR, batched over chirps / RX channels / frames.
+ *
+ * This is the drop-in boundary: plain pointers and sizes, no C++ / torch types.  Each entry point names the
+ * reference interface it replaces (file:line relative to the rsp-chains repository).  The reference is a
+ * Chisel hardware generator: a "block" there is a rocket-chip DspBlock with one AXI4-Stream node (32-bit
+ * beats + `last`) and one memory-mapped register file; a "chain" is blocks bound with `:=`.  Here a chain is
+ * an opaque handle, the compile-time case classes are the structs below, the register files are
+ * rsp_reg_write/rsp_reg_read with the reference's word offsets, and the stream is a device (or host) buffer
+ * of the very same 32-bit beats, one chirp after another.
+ *
+ * Conventions
+ *   - every function returns rsp_status (0 = OK); rsp_last_error() gives a message for the calling thread
+ *   - the caller owns every buffer it passes; the handle owns tables, registers and scratch
+ *   - device entry points are asynchronous on the given stream (a cudaStream_t passed as void*; NULL = the
+ *     legacy default stream); host entry points (rsp_*_host) return after the results are in the host buffer
+ *   - a handle is not thread-safe; distinct handles are independent
+ *   - parameter checks reproduce the reference's `require`s / `assert`s and return RSP_EINVAL
+ *   - there is no CPU fallback: without a CUDA device every compute entry point fails with RSP_ECUDA
+ */
+#ifndef RSP_CHAINS_H
+#define RSP_CHAINS_H
+#include <stddef.h>
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define RSP_ABI_VERSION 1
+
+typedef enum {
+  RSP_OK = 0,
+  RSP_EINVAL = 1,       /* a reference `require`/`assert` would have fired, or a bad argument */
+  RSP_ECUDA = 2,        /* CUDA runtime error (no device, launch failure, ...) */
+  RSP_ENOMEM = 3,
+  RSP_EUNSUPPORTED = 4  /* legal in the reference generator, not built here (listed in DESIGN.md) */
+} rsp_status;
+
+/* blocks of the chain, in composition order (src/main/scala/RspChain.scala:41-58) */
+typedef enum { RSP_BLK_PLFG = 0, RSP_BLK_NCO = 1, RSP_BLK_FFT = 2, RSP_BLK_MAG = 3, RSP_BLK_CFAR = 4 } rsp_block;
+
+/* arithmetic of the data path: the FixedPoint generator, or the "DspReal golden" flavour run in fp32 */
+typedef enum { RSP_ARITH_FIXED = 0, RSP_ARITH_FP32 = 1 } rsp_arith;
+
+/* dsptools TrimType (generators/sdf-fft/src/test/scala/Radix22SQNRSpec.scala:184) */
+typedef enum {
+  RSP_TRIM_ROUND_HALF_UP = 0, RSP_TRIM_FLOOR = 1 /* RoundDown */, RSP_TRIM_CONVERGENT = 2 /* RoundHalfToEven */,
+  RSP_TRIM_ROUND_UP = 3, RSP_TRIM_ROUND_TOWARDS_ZERO = 4, RSP_TRIM_ROUND_TOWARDS_INFINITY = 5,
+  RSP_TRIM_ROUND_HALF_DOWN = 6, RSP_TRIM_ROUND_HALF_TOWARDS_ZERO = 7, RSP_TRIM_ROUND_HALF_TOWARDS_INFINITY = 8,
+  RSP_TRIM_ROUND_HALF_TO_ODD = 9, RSP_TRIM_NO_TRIM = 10
+} rsp_trim;
+
+/* ---- compile-time tier: C mirrors of the case classes ------------------------------------------------ */
+
+/* FFTParams.fixed (generators/sdf-fft/src/main/scala/SDFFFTParams.scala:22-46,90-149) */
+typedef struct {
+  int32_t numPoints;        /* power of two, 2..16384                                                    */
+  int32_t dataWidth;        /* 2..16 (protoIQ = FixedPoint(dataWidth.W, binPoint.BP))                    */
+  int32_t binPoint;
+  int32_t twiddleWidth;     /* 3..16, twiddles are Q2.(twiddleWidth-2) (:116)                             */
+  int32_t trimType;         /* rsp_trim, used by div2 / context_* / trimBinary                            */
+  int32_t use4Muls;         /* complexUse4Muls                                                            */
+  int32_t useBitReverse;    /* 1: natural-order output (BitReversePingPong), 0: bit-reversed              */
+  int32_t fftDir;           /* 1 = FFT, 0 = IFFT (reset value of the fftDir register)                     */
+  int32_t runTime;          /* 1: the fftSize register may select a smaller transform                     */
+  uint32_t keepMSBorLSB;    /* bit i = keepMSBorLSB(i): 1 scale by 1/2 with trimType, 0 keep LSBs (wrap)   */
+  int32_t decimType;        /* 0 = DIF (only DIF is built; DIT -> RSP_EUNSUPPORTED)                        */
+  int32_t sdfRadix;         /* 4 = "2^2" (only radix 2^2 is built; 2 -> RSP_EUNSUPPORTED)                  */
+  int32_t expandLogicAny;   /* 1 if any expandLogic(i) != 0 (grow mode -> RSP_EUNSUPPORTED)                */
+} rsp_fft_params;
+
+/* MAGParams.fixed (generators/logMagMux/src/main/scala/LogMagMux.scala:14-49) */
+typedef struct {
+  int32_t dataWidth, binPoint;        /* proto          */
+  int32_t dataWidthLog, binPointLog;  /* protoLog       */
+  int32_t log2LookUpWidth;
+} rsp_mag_params;
+
+/* CFARParams (generators/cfar/src/main/scala/CFARParams.scala:24-49) */
+typedef enum { RSP_CFAR_CA = 0 /* CACFARType */, RSP_CFAR_GOS = 1 /* GOSCFARType */, RSP_CFAR_GOSCA = 2 /* GOSCACFARType */ } rsp_cfar_type;
+typedef struct {
+  int32_t inWidth, inBinPoint;               /* protoIn         */
+  int32_t thresholdWidth, thresholdBinPoint; /* protoThreshold  */
+  int32_t scalerWidth, scalerBinPoint;       /* protoScaler     */
+  int32_t CFARAlgorithm;                     /* rsp_cfar_type   */
+  int32_t includeCASH;
+  int32_t minSubWindowSize;                  /* 0 = None        */
+  int32_t leadLaggWindowSize;                /* power of two    */
+  int32_t sendCut;
+  int32_t guardWindowSize;
+  int32_t fftSize;                           /* power of two; width of the fftBin field of the output beat */
+} rsp_cfar_params;
+
+/* FixedPLFGParams (generators/plfg/src/main/scala/PLFGDspBlockMem.scala:20-72) */
+typedef struct {
+  int32_t maxNumOfSegments, maxNumOfDifferentChirps, maxNumOfRepeatedChirps, maxChirpOrdinalNum, maxNumOfFrames;
+  int32_t maxNumOfSamplesWidth, outputWidthInt, outputWidthFrac;
+} rsp_plfg_params;
+
+/* FixedNCOParams, standard-mode table + accumulator (generators/nco/src/main/scala/NCO.scala:14-83) */
+typedef struct {
+  int32_t tableSize, tableWidth, phaseWidth;
+  int32_t phaseAccEnable;
+  int32_t rasterizedMode, nInterpolationTerms, ditherEnable, useMultiplier, useQAM; /* non-zero -> RSP_EUNSUPPORTED */
+} rsp_nco_params;
+
+/* RspChainVanillaParameters / FftMagCfarVanillaParameters (src/main/scala/RspChain.scala:24-33,
+ * src/main/scala/FftMagCfarChain.scala:21-29) without the AddressSets (there is no bus) */
+typedef struct {
+  int32_t arith;          /* rsp_arith */
+  int32_t hasGenerator;   /* 1: RspChainVanilla (plfg+nco in front), 0: FftMagCfarChainVanilla */
+  rsp_plfg_params plfg;
+  rsp_nco_params nco;
+  rsp_fft_params fft;
+  rsp_mag_params mag;
+  rsp_cfar_params cfar;
+} rsp_chain_params;
+
+/* defaults = RspChainVanillaApp (src/main/scala/RspChain.scala:80-147): 1024 points, 16-bit, binPoint 0 */
+void rsp_chain_params_default(rsp_chain_params *p);
+
+/* ---- run-time tier: register word indices (= byte offset / beatBytes in the reference regmaps) -------- */
+enum { /* AXI4FFTBlock (generators/sdf-fft/src/main/scala/FFTBlock.scala:86-102) */
+  RSP_FFT_REG_FFTSIZE = 0 /* log2 of the run-time size */, RSP_FFT_REG_FFTDIR = 1, RSP_FFT_REG_KEEPMSBORLSB = 2,
+  RSP_FFT_REG_BUSY = 3 /* RO */, RSP_FFT_REG_OVERFLOW = 4 /* RO */ };
+enum { /* AXI4LogMagMuxBlock (generators/logMagMux/src/main/scala/LogMagMuxDspBlock.scala:31-39) */
+  RSP_MAG_REG_SEL = 0 /* 0 bypass, 1 |z|^2, 2 JPL magnitude, 3 log2 magnitude */ };
+enum { /* AXI4CFARBlock (generators/cfar/src/main/scala/CFARDspBlock.scala:96-130) */
+  RSP_CFAR_REG_FFTWIN = 0, RSP_CFAR_REG_THRESHOLDSCALER = 1, RSP_CFAR_REG_LOGORLINEARMODE = 2, RSP_CFAR_REG_DIVSUM = 3,
+  RSP_CFAR_REG_PEAKGROUPING = 4, RSP_CFAR_REG_CFARALGORITHM = 5, RSP_CFAR_REG_CFARMODE = 6, RSP_CFAR_REG_WINDOWCELLS = 7,
+  RSP_CFAR_REG_GUARDCELLS = 8, RSP_CFAR_REG_INDEXLAGG = 9, RSP_CFAR_REG_INDEXLEAD = 10, RSP_CFAR_REG_SUBWINDOWSIZE = 11 };
+enum { /* PLFGDspBlockMem (generators/plfg/src/main/scala/PLFGDspBlockMem.scala:182-217) */
+  RSP_PLFG_REG_ENABLE = 0, RSP_PLFG_REG_RESET = 1, RSP_PLFG_REG_FRAMENUM = 2, RSP_PLFG_REG_INTERFRAMENUMOFSAMPLES = 3,
+  RSP_PLFG_REG_DIFFERENTCHIRPSNUM = 4, RSP_PLFG_REG_STARTINGPOINT = 5, RSP_PLFG_REG_SEGMENTNUMS0 = 6
+  /* then segmentNums[maxChirpOrdinalNum], repeatedChirpNums[maxNumOfDifferentChirps], chirpOrdinalNums[maxNumOfDifferentChirps] */ };
+/* fp32 chains only: the threshold scaler as a float (the FixedPoint register has no fp32 meaning) */
+#define RSP_CFAR_REG_THRESHOLDSCALER_F32 0x100u
+
+typedef struct rsp_chain rsp_chain;
+
+/* one detection = one output beat with peak = 1, unpacked */
+typedef struct {
+  uint32_t chirp;      /* index of the chirp (row) inside the call: rx * n_chirps + chirp */
+  uint32_t bin;        /* fftBin                                                          */
+  int32_t threshold;   /* fixed: raw protoThreshold bits; fp32: float bits                 */
+  int32_t cut;         /* fixed: raw protoIn bits of the cell under test; fp32: float bits  */
+} rsp_detection;
+
+/* device-side detection list the caller provides: `list` has room for `capacity` entries, `count` is one
+ * uint32 the kernels atomically advance (the caller zeroes it; it may exceed capacity = overflow, entries
+ * past capacity are dropped).  Both are device pointers. */
+typedef struct {
+  rsp_detection *list;
+  uint32_t *count;
+  uint32_t capacity;
+} rsp_dets;
+
+/* ---- life cycle ------------------------------------------------------------------------------------------
+ * replaces: LazyModule(new RspChainVanilla(params)) / new FftMagCfarChainVanilla(params)
+ *           (src/main/scala/RspChain.scala:35-61,150; src/main/scala/FftMagCfarChain.scala:31-49) */
+rsp_status rsp_chain_create(const rsp_chain_params *params, int device, rsp_chain **out);
+void rsp_chain_destroy(rsp_chain *c);
+
+/* replaces: AXI4MasterModel.memWriteWord(blockBase + 4*word_index, value) / memReadWord
+ *           (src/test/scala/FftMagCfarChainTester.scala:82-132; regmaps cited above) */
+rsp_status rsp_reg_write(rsp_chain *c, rsp_block blk, uint32_t word_index, uint32_t value);
+rsp_status rsp_reg_read(rsp_chain *c, rsp_block blk, uint32_t word_index, uint32_t *value);
+/* replaces: writes into the PLFG config RAM at plfgRAM + 4*word_index, word = {reset, sign, nSamples, slope}
+ *           (generators/plfg/src/main/scala/PLFGDspBlockMem.scala:108-128,168-178) */
+rsp_status rsp_plfg_ram_write(rsp_chain *c, uint32_t word_index, uint32_t value);
+
+/* ---- the hot path, device buffers ------------------------------------------------------------------------
+ * replaces: streaming n_rx*n_chirps chirps of fftSize beats into FftMagCfarChainVanilla.streamNode and reading
+ *           the CFAR beats back (src/main/scala/FftMagCfarChain.scala:47; tester hot loop
+ *           src/test/scala/FftMagCfarChainTester.scala:137-151).
+ * d_in : fixed  -> uint32 beats Cat(re16, im16) (generators/sdf-fft/src/main/scala/FFTBlock.scala:106)
+ *        fp32   -> float2 (re, im)
+ * d_out: fixed  -> uint32 beats Cat(threshold, fftBin, peak) or the CUT when sendCut
+ *                  (generators/cfar/src/main/scala/CFARDspBlock.scala:78-90); may be NULL
+ *        fp32   -> float thresholds, one per bin; may be NULL
+ * d_peak_mask: fp32 only (NULL otherwise / when not wanted): 1 bit per bin, bin n of chirp c at bit (n & 31)
+ *        of word c*N/32 + n/32
+ * dets : optional compacted detection list (NULL = none)
+ * The transform size is the run-time fftSize register (N = 1 << fftSize). */
+rsp_status rsp_run(rsp_chain *c, const void *d_in, uint32_t n_chirps, uint32_t n_rx, void *d_out, uint32_t *d_peak_mask,
+                   const rsp_dets *dets, void *stream);
+
+/* replaces: RspChainVanilla with the PLFG enabled (src/main/scala/RspChain.scala:57-58;
+ *           src/test/scala/RspChainVanillaTester.scala:86-147): the chirps are synthesised on the device by the
+ *           PLFG -> NCO kernels from the registers / config RAM and consumed by the same fused chain.
+ * d_nco_out (optional) receives the NCO beats Cat(cos16, sin16) (generators/nco/src/main/scala/NCOLazyModuleBlock.scala:452). */
+rsp_status rsp_run_from_generator(rsp_chain *c, uint32_t n_chirps, uint32_t n_rx, void *d_out, uint32_t *d_peak_mask,
+                                  const rsp_dets *dets, uint32_t *d_nco_out, void *stream);
+
+/* ---- single blocks (each reference DspBlock is usable on its own) ----------------------------------------- */
+/* replaces AXI4FFTBlock (generators/sdf-fft/src/main/scala/FFTBlock.scala:122-124): beats in -> beats out */
+rsp_status rsp_fft_run(rsp_chain *c, const void *d_in, uint32_t n_chirps, void *d_out, void *stream);
+/* replaces AXI4LogMagMuxBlock (generators/logMagMux/src/main/scala/LogMagMuxDspBlock.scala:59-61); n_beats beats */
+rsp_status rsp_mag_run(rsp_chain *c, const void *d_in, uint64_t n_beats, void *d_out, void *stream);
+/* replaces AXI4CFARBlock (generators/cfar/src/main/scala/CFARDspBlock.scala:134-136): n_chirps rows of fftWin beats
+ * (fixed: low inWidth bits of each beat are the sample, :49; fp32: floats) */
+rsp_status rsp_cfar_run(rsp_chain *c, const void *d_in, uint32_t n_chirps, void *d_out, uint32_t *d_peak_mask,
+                        const rsp_dets *dets, void *stream);
+/* replaces PLFGDspBlockMem -> AXI4NCOLazyModuleBlock (src/main/scala/RspChain.scala:57): n_samples NCO beats
+ * Cat(cos16, sin16); d_plfg_out (optional) receives the PLFG words (one int32 per sample, sign-extended) */
+rsp_status rsp_generate(rsp_chain *c, uint64_t n_samples, uint32_t *d_nco_out, int32_t *d_plfg_out, void *stream);
+
+/* ---- the hot path, host buffers (the call a reference user's tester makes) ----------------------------------
+ * Same as rsp_run but in/out are HOST pointers; the library pipelines host->device copies, the fused kernel and
+ * device->host copies over its own streams in chunks and returns when h_out is complete.  Pinned buffers from
+ * rsp_host_alloc are copied directly; pageable ones are staged through internal pinned buffers.
+ * h_dets/h_n_dets (optional): detections gathered on the host, up to max_dets; *h_n_dets = number found. */
+rsp_status rsp_run_host(rsp_chain *c, const void *h_in, uint32_t n_chirps, uint32_t n_rx, void *h_out, uint32_t *h_peak_mask,
+                        rsp_detection *h_dets, uint32_t max_dets, uint32_t *h_n_dets);
+rsp_status rsp_host_alloc(void **p, size_t bytes); /* pinned host memory */
+void rsp_host_free(void *p);
+
+/* ---- introspection ------------------------------------------------------------------------------------------ */
+const char *rsp_status_str(rsp_status s);
+const char *rsp_last_error(void);
+int rsp_abi_version(void);
+/* kernels launched by this handle since creation (bench.py reports it as gpu_launches) */
+uint64_t rsp_kernel_launches(const rsp_chain *c);
+/* name of the kernel variant the current registers select for rsp_run, e.g. "chain_fixed<10,fast>" */
+const char *rsp_variant_name(rsp_chain *c);
+/* algorithmic HBM bytes one chirp of the current configuration moves through rsp_run (in + out) */
+uint64_t rsp_bytes_per_chirp(rsp_chain *c);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

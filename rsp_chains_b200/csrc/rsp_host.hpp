@@ -1,0 +1,430 @@
+// rsp_host.hpp -- host-side state of a chain: parameter checks (the reference's `require`s), register files with the
+// reference's field widths and reset values, table generation, and the translation of (params, registers) into the
+// kernel argument blocks.  No CUDA in this header: the C-ABI library (rsp_abi.cu) and the CPU emulation harness under
+// tests/emu both include it.
+#pragma once
+#include <cmath>
+#include <cstdint>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/rsp_chains.h"
+#include "rsp_device.cuh"
+#include "rsp_device_f32.cuh"
+
+namespace rsp {
+
+inline bool is_pow2(int v) { return v > 0 && (v & (v - 1)) == 0; }
+inline int log2_ceil(uint32_t v) { int n = 0; while ((1u << n) < v) ++n; return n; }   // chisel3.util.log2Ceil
+inline int bit_length(uint32_t v) { int n = 0; while (v) { ++n; v >>= 1; } return n; }
+inline long long wrap_host(long long v, int w) { return wrapw64(v, w); }
+inline long long from_double(double x, int bp) { return (long long)std::floor(std::ldexp(x, bp) + 0.5); } // FixedPoint.fromDouble
+
+struct Regs {
+  uint32_t fft[5];
+  uint32_t mag[1];
+  uint32_t cfar[12];
+  std::vector<uint32_t> plfg;      // 6 + maxChirpOrdinalNum + 2 * maxNumOfDifferentChirps words
+  std::vector<uint32_t> plfg_ram;  // maxChirpOrdinalNum * maxNumOfSegments words
+  float scaler_f32;
+};
+
+struct Tables {
+  std::vector<uint32_t> tw;   // fixed twiddles, packed (cos16 << 16 | sin16 & 0xFFFF); per stageN three runs [W^2k | W^k | W^3k]
+  std::vector<F2> twf;        // fp32 twiddles, same layout
+  int tw_off[16];
+  std::vector<int32_t> log_tab;
+  std::vector<int32_t> nco_tab;
+};
+
+// ---- the reference's elaboration-time checks -------------------------------------------------------------------
+inline rsp_status validate_params(const rsp_chain_params &p, std::string &err) {
+  const rsp_fft_params &f = p.fft;
+  const rsp_cfar_params &c = p.cfar;
+  const rsp_mag_params &m = p.mag;
+#define RSP_REQ(cond, st, msg) do { if (!(cond)) { err = msg; return st; } } while (0)
+  RSP_REQ(p.arith == RSP_ARITH_FIXED || p.arith == RSP_ARITH_FP32, RSP_EINVAL, "arith must be RSP_ARITH_FIXED or RSP_ARITH_FP32");
+  // FFTParams (SDFFFTParams.scala:53-86)
+  RSP_REQ(is_pow2(f.numPoints), RSP_EINVAL, "number of points must be a power of 2");
+  RSP_REQ(f.numPoints >= 2 && f.numPoints <= 16384, RSP_EUNSUPPORTED, "numPoints must be in 2..16384 (one chirp stays resident in shared memory)");
+  RSP_REQ(f.decimType == 0, RSP_EUNSUPPORTED, "only DIFDecimType is built");
+  RSP_REQ(f.sdfRadix == 4, RSP_EUNSUPPORTED, "only sdfRadix \"2^2\" is built");
+  RSP_REQ(!f.expandLogicAny, RSP_EUNSUPPORTED, "expandLogic (grow) stages are not built");
+  if (p.arith == RSP_ARITH_FIXED) {
+    RSP_REQ(f.dataWidth >= 2 && f.dataWidth <= 16, RSP_EUNSUPPORTED, "dataWidth must be in 2..16 (32-bit beats carry Cat(re16, im16))");
+    RSP_REQ(f.binPoint >= 0 && f.binPoint <= 15, RSP_EINVAL, "binPoint must be in 0..15");
+    RSP_REQ(f.twiddleWidth >= 3 && f.twiddleWidth <= 16, RSP_EUNSUPPORTED, "twiddleWidth must be in 3..16");
+    RSP_REQ(f.trimType >= 0 && f.trimType <= RSP_TRIM_NO_TRIM, RSP_EINVAL, "unknown trimType");
+    RSP_REQ(m.dataWidth >= 2 && m.dataWidth <= 16 && m.binPoint >= 0 && m.binPoint <= 15, RSP_EUNSUPPORTED, "MAGParams proto must fit 16 bits");
+    RSP_REQ(m.dataWidthLog >= 2 && m.dataWidthLog <= 32 && m.binPointLog >= 0 && m.binPointLog < 31, RSP_EINVAL, "bad protoLog");
+    RSP_REQ(m.log2LookUpWidth >= 1 && m.log2LookUpWidth <= 14 && m.log2LookUpWidth <= m.dataWidth - 1, RSP_EINVAL, "log2LookUpWidth must be in 1..dataWidth-1");
+    RSP_REQ(c.inWidth >= 2 && c.inWidth <= 16 && c.inBinPoint >= 0 && c.inBinPoint <= 15, RSP_EUNSUPPORTED, "CFAR protoIn must fit 16 bits");
+    RSP_REQ(c.thresholdWidth >= 2 && c.thresholdWidth <= 32 && c.thresholdBinPoint >= 0 && c.thresholdBinPoint <= 31, RSP_EINVAL, "bad protoThreshold");
+    RSP_REQ(c.scalerWidth >= 2 && c.scalerWidth <= 16 && c.scalerBinPoint >= 0 && c.scalerBinPoint <= 15, RSP_EUNSUPPORTED, "CFAR protoScaler must fit 16 bits");
+  }
+  // CFARParams (CFARParams.scala:40-44)
+  RSP_REQ(is_pow2(c.leadLaggWindowSize) && is_pow2(c.fftSize), RSP_EINVAL, "leadLaggWindowSize and fftSize must be powers of 2");
+  RSP_REQ(c.leadLaggWindowSize > 0 && c.guardWindowSize > 0, RSP_EINVAL, "leadLaggWindowSize and guardWindowSize must be positive");
+  RSP_REQ(c.leadLaggWindowSize > c.guardWindowSize, RSP_EINVAL, "leadLaggWindowSize must exceed guardWindowSize");
+  RSP_REQ(c.fftSize <= 16384 && c.leadLaggWindowSize <= 4096, RSP_EUNSUPPORTED, "CFAR fftSize must be <= 16384");
+  RSP_REQ(c.CFARAlgorithm >= RSP_CFAR_CA && c.CFARAlgorithm <= RSP_CFAR_GOSCA, RSP_EINVAL, "unknown CFARAlgorithm");
+  if (c.includeCASH)
+    RSP_REQ(c.minSubWindowSize > 0, RSP_EINVAL, "If includeCash parameter is set then minSubWindowSize needs to be defined as a positive value");
+  if (p.hasGenerator) {
+    const rsp_plfg_params &g = p.plfg;
+    const rsp_nco_params &n = p.nco;
+    // FixedPLFGParams (PLFGDspBlockMem.scala:41-48)
+    RSP_REQ(g.outputWidthInt >= 2 && g.outputWidthFrac >= 0, RSP_EINVAL, "outputWidthInt >= 2 and outputWidthFrac >= 0 required");
+    RSP_REQ(is_pow2(g.maxNumOfSegments) && is_pow2(g.maxNumOfDifferentChirps) && is_pow2(g.maxNumOfRepeatedChirps) &&
+            is_pow2(g.maxChirpOrdinalNum) && is_pow2(g.maxNumOfFrames), RSP_EINVAL, "PLFG maxima must be powers of 2");
+    RSP_REQ(g.outputWidthInt + g.outputWidthFrac <= 16 && g.maxNumOfSamplesWidth >= 1 &&
+            g.outputWidthInt + g.maxNumOfSamplesWidth + 2 <= 32, RSP_EUNSUPPORTED, "PLFG config word must fit 32 bits");
+    RSP_REQ(g.maxNumOfSegments <= 64 && g.maxNumOfDifferentChirps <= 256 && g.maxChirpOrdinalNum <= 256, RSP_EUNSUPPORTED, "PLFG tables too large");
+    // FixedNCOParams (NCO.scala:54-55)
+    RSP_REQ(n.tableWidth >= 3 && n.tableWidth <= 16, RSP_EINVAL, "tableWidth must be in 3..16");
+    RSP_REQ(is_pow2(n.tableSize) && n.tableSize <= 65536, RSP_EINVAL, "tableSize must be a power of 2");
+    RSP_REQ(n.phaseWidth >= log2_ceil((uint32_t)n.tableSize) + 2 && n.phaseWidth <= 32, RSP_EINVAL, "phaseWidth must cover quadrant + table address");
+    RSP_REQ(!n.rasterizedMode && !n.nInterpolationTerms && !n.ditherEnable && !n.useMultiplier && !n.useQAM, RSP_EUNSUPPORTED,
+            "NCO rasterized mode, Taylor terms, dither, multiplier and QAM are not built");
+    RSP_REQ(p.arith == RSP_ARITH_FIXED, RSP_EUNSUPPORTED, "the PLFG/NCO generator feeds the fixed-point chain only");
+  }
+#undef RSP_REQ
+  return RSP_OK;
+}
+
+// ---- register files ---------------------------------------------------------------------------------------------
+inline int plfg_reg_count(const rsp_plfg_params &g) { return 6 + g.maxChirpOrdinalNum + 2 * g.maxNumOfDifferentChirps; }
+
+inline void regs_reset(const rsp_chain_params &p, Regs &r) {
+  const int numStages = log2_ceil((uint32_t)p.fft.numPoints);
+  std::memset(r.fft, 0, sizeof(r.fft)); std::memset(r.mag, 0, sizeof(r.mag)); std::memset(r.cfar, 0, sizeof(r.cfar));
+  r.fft[RSP_FFT_REG_FFTSIZE] = (uint32_t)numStages;           // FFTBlock.scala:62
+  r.fft[RSP_FFT_REG_FFTDIR] = 1;                               // :63
+  r.fft[RSP_FFT_REG_KEEPMSBORLSB] = 0;                         // :64
+  r.cfar[RSP_CFAR_REG_FFTWIN] = (uint32_t)p.cfar.fftSize;      // CFARDspBlock.scala:29-43
+  r.cfar[RSP_CFAR_REG_WINDOWCELLS] = (uint32_t)p.cfar.leadLaggWindowSize;
+  r.cfar[RSP_CFAR_REG_GUARDCELLS] = (uint32_t)p.cfar.guardWindowSize;
+  r.cfar[RSP_CFAR_REG_INDEXLEAD] = (uint32_t)p.cfar.leadLaggWindowSize / 2;
+  r.cfar[RSP_CFAR_REG_INDEXLAGG] = (uint32_t)p.cfar.leadLaggWindowSize / 2;
+  r.cfar[RSP_CFAR_REG_SUBWINDOWSIZE] = (uint32_t)p.cfar.leadLaggWindowSize;
+  r.scaler_f32 = 0.0f;
+  r.plfg.clear(); r.plfg_ram.clear();
+  if (p.hasGenerator) {
+    r.plfg.assign((size_t)plfg_reg_count(p.plfg), 0u);
+    r.plfg[RSP_PLFG_REG_FRAMENUM] = 1;                         // PLFGDspBlockMem.scala:133-137
+    r.plfg[RSP_PLFG_REG_INTERFRAMENUMOFSAMPLES] = 63u & ((1u << p.plfg.maxNumOfSamplesWidth) - 1);
+    r.plfg[RSP_PLFG_REG_DIFFERENTCHIRPSNUM] = 1;
+    for (int i = 0; i < p.plfg.maxChirpOrdinalNum; ++i)       // segmentNums reset to 1 (:139)
+      r.plfg[RSP_PLFG_REG_SEGMENTNUMS0 + i] = 1u & ((1u << log2_ceil((uint32_t)p.plfg.maxNumOfSegments)) - 1);
+    r.plfg_ram.assign((size_t)p.plfg.maxChirpOrdinalNum * p.plfg.maxNumOfSegments, 0u);
+  }
+}
+
+// width in bits of a register field (RegField widths of the reference regmaps); -1: no such register; ro: read-only
+inline int reg_width(const rsp_chain_params &p, rsp_block blk, uint32_t idx, bool *ro) {
+  *ro = false;
+  const int numStages = log2_ceil((uint32_t)p.fft.numPoints);
+  const rsp_cfar_params &c = p.cfar;
+  switch (blk) {
+  case RSP_BLK_FFT:
+    switch (idx) {
+    case RSP_FFT_REG_FFTSIZE: return log2_ceil((uint32_t)numStages + 1);  // the register's own width (FFTBlock.scala:62)
+    case RSP_FFT_REG_FFTDIR: return 1;
+    case RSP_FFT_REG_KEEPMSBORLSB: return numStages;
+    case RSP_FFT_REG_BUSY: *ro = true; return 1;
+    case RSP_FFT_REG_OVERFLOW: *ro = true; return numStages;
+    default: return -1;
+    }
+  case RSP_BLK_MAG: return idx == RSP_MAG_REG_SEL ? 2 : -1;
+  case RSP_BLK_CFAR:
+    switch (idx) {
+    case RSP_CFAR_REG_FFTWIN: return log2_ceil((uint32_t)c.fftSize + 1);
+    case RSP_CFAR_REG_THRESHOLDSCALER: return c.scalerWidth;
+    case RSP_CFAR_REG_LOGORLINEARMODE: return 1;
+    case RSP_CFAR_REG_DIVSUM: return log2_ceil((uint32_t)log2_ceil((uint32_t)c.leadLaggWindowSize + 1));
+    case RSP_CFAR_REG_PEAKGROUPING: return 1;
+    case RSP_CFAR_REG_CFARALGORITHM: return 1;
+    case RSP_CFAR_REG_CFARMODE: return 2;
+    case RSP_CFAR_REG_WINDOWCELLS: case RSP_CFAR_REG_INDEXLAGG: case RSP_CFAR_REG_INDEXLEAD: case RSP_CFAR_REG_SUBWINDOWSIZE:
+      return log2_ceil((uint32_t)c.leadLaggWindowSize + 1);
+    case RSP_CFAR_REG_GUARDCELLS: return log2_ceil((uint32_t)c.guardWindowSize + 1);
+    default: return -1;
+    }
+  case RSP_BLK_PLFG: {
+    if (!p.hasGenerator) return -1;
+    const rsp_plfg_params &g = p.plfg;
+    const uint32_t a = RSP_PLFG_REG_SEGMENTNUMS0, b = a + g.maxChirpOrdinalNum, d = b + g.maxNumOfDifferentChirps, e = d + g.maxNumOfDifferentChirps;
+    if (idx == RSP_PLFG_REG_ENABLE || idx == RSP_PLFG_REG_RESET) return 1;
+    if (idx == RSP_PLFG_REG_FRAMENUM) return log2_ceil((uint32_t)g.maxNumOfFrames);
+    if (idx == RSP_PLFG_REG_INTERFRAMENUMOFSAMPLES) return g.maxNumOfSamplesWidth < 10 ? g.maxNumOfSamplesWidth : 10;
+    if (idx == RSP_PLFG_REG_DIFFERENTCHIRPSNUM) return log2_ceil((uint32_t)g.maxNumOfDifferentChirps);
+    if (idx == RSP_PLFG_REG_STARTINGPOINT) return g.outputWidthInt;
+    if (idx >= a && idx < b) return log2_ceil((uint32_t)g.maxNumOfSegments);
+    if (idx >= b && idx < d) return log2_ceil((uint32_t)g.maxNumOfRepeatedChirps);
+    if (idx >= d && idx < e) return log2_ceil((uint32_t)g.maxChirpOrdinalNum);
+    return -1;
+  }
+  case RSP_BLK_NCO: return -1;  // chain configuration: pinc Streaming, poff Fixed, no multiplier => no regmap (NCOLazyModuleBlock.scala:246-271)
+  default: return -1;
+  }
+}
+
+inline uint32_t *reg_slot(Regs &r, rsp_block blk, uint32_t idx) {
+  switch (blk) {
+  case RSP_BLK_FFT: return &r.fft[idx];
+  case RSP_BLK_MAG: return &r.mag[idx];
+  case RSP_BLK_CFAR: return &r.cfar[idx];
+  case RSP_BLK_PLFG: return &r.plfg[idx];
+  default: return nullptr;
+  }
+}
+
+// ---- tables ------------------------------------------------------------------------------------------------------
+// twiddle(t) = (cos, -sin)(2 pi t / stageN) through fromDoubleWithFixedWidth into Q2.(tw-2) (SDFChainRadix22.scala:255-267).
+// Stored per stageN as three runs of q = stageN/4 entries, [W^2k | W^k | W^3k], i.e. the quarters 1..3 of the reference's
+// index pattern [0]*q ++ [2k] ++ [k] ++ [3k] (:255-259), so that neighbouring lanes read neighbouring words.
+inline void build_tables(const rsp_chain_params &p, Tables &t) {
+  const int Smax = log2_ceil((uint32_t)p.fft.numPoints);
+  const int tww = p.fft.twiddleWidth, twbp = tww - 2;
+  t.tw.clear(); t.twf.clear();
+  for (int L = 0; L < 16; ++L) t.tw_off[L] = 0;
+  const double PI = 3.14159265358979323846;  // scala.math.Pi
+  for (int L = 3; L <= Smax; ++L) {
+    const int stageN = 1 << L, q = stageN / 4;
+    t.tw_off[L] = (int)t.tw.size();
+    const int mult[3] = {2, 1, 3};
+    for (int slot = 0; slot < 3; ++slot)
+      for (int k = 0; k < q; ++k) {
+        const int tt = mult[slot] * k;
+        const double ang = 2.0 * PI * (double)tt / (double)stageN;
+        const double c = std::cos(ang), s = -std::sin(ang);
+        const long long re = wrap_host(from_double(c, twbp), tww), im = wrap_host(from_double(s, twbp), tww);
+        t.tw.push_back(pack_iq((int)re, (int)im));
+        F2 f; f.x = (float)c; f.y = (float)s;
+        t.twf.push_back(f);
+      }
+  }
+  if (t.tw.empty()) { t.tw.push_back(0); F2 f; f.x = 1.f; f.y = 0.f; t.twf.push_back(f); }
+  // log2 LUT (LogMagMux.scala:120-131)
+  const int Lw = p.mag.log2LookUpWidth, num = 1 << Lw;
+  t.log_tab.resize((size_t)num);
+  const double ln2 = std::log(2.0);
+  for (int n = 0; n < num; ++n) {
+    const double v = std::log((double)n / (double)num + 1.0) / ln2;
+    t.log_tab[(size_t)n] = (int32_t)wrap_host(from_double(v, p.mag.binPointLog), p.mag.binPointLog + 1);
+  }
+  // NCO quarter-wave sine table (NCOTable.scala:254-258)
+  t.nco_tab.clear();
+  if (p.hasGenerator) {
+    t.nco_tab.resize((size_t)p.nco.tableSize);
+    for (int i = 0; i < p.nco.tableSize; ++i)
+      t.nco_tab[(size_t)i] = (int32_t)from_double(std::sin(((double)i * 0.5 * PI) / (double)p.nco.tableSize), p.nco.tableWidth - 2);
+  } else t.nco_tab.push_back(0);
+}
+
+// ---- (params, registers) -> kernel arguments ------------------------------------------------------------------------
+struct Plan {
+  int S;          // log2 of the transform / window size
+  int mode;       // MODE_* of the fixed kernels
+  int first_stage, last_stage;
+};
+
+// the part of the CFAR set-up common to both arithmetics; fills core/W/G/... of either argument block
+template <typename A>
+inline rsp_status plan_cfar_common(const rsp_chain_params &p, const Regs &r, int N, A &a, std::string &err) {
+  const rsp_cfar_params &c = p.cfar;
+  a.core = (c.CFARAlgorithm == RSP_CFAR_CA) ? (c.includeCASH ? CORE_ASR : CORE_MEM) : CORE_LIS;   // CFARcore.scala:62-64
+  a.W = (int)r.cfar[RSP_CFAR_REG_WINDOWCELLS];
+  a.G = (int)r.cfar[RSP_CFAR_REG_GUARDCELLS];
+  a.div_sum = (int)r.cfar[RSP_CFAR_REG_DIVSUM];
+  a.peak_grouping = (int)r.cfar[RSP_CFAR_REG_PEAKGROUPING];
+  a.cfar_mode = (int)r.cfar[RSP_CFAR_REG_CFARMODE];
+  a.log_or_linear = (int)r.cfar[RSP_CFAR_REG_LOGORLINEARMODE];
+  a.cfar_algorithm = c.CFARAlgorithm == RSP_CFAR_GOS ? 1 : (c.CFARAlgorithm == RSP_CFAR_GOSCA ? (int)r.cfar[RSP_CFAR_REG_CFARALGORITHM] : 0);
+  a.idx_lagg = (int)r.cfar[RSP_CFAR_REG_INDEXLAGG];
+  a.idx_lead = (int)r.cfar[RSP_CFAR_REG_INDEXLEAD];
+  a.sub_cells = (int)r.cfar[RSP_CFAR_REG_SUBWINDOWSIZE];
+  a.sub_log2 = 0; while ((2 << a.sub_log2) <= a.sub_cells) ++a.sub_log2;
+  a.guard_window_size = c.guardWindowSize;
+  a.send_cut = c.sendCut;
+  a.binw = log2_ceil((uint32_t)c.fftSize);
+  if ((int)r.cfar[RSP_CFAR_REG_FFTWIN] != N) { err = "CFAR fftWin register must equal the run-time transform size"; return RSP_EINVAL; }
+  if (N > c.fftSize) { err = "fftWin exceeds CFARParams.fftSize"; return RSP_EINVAL; }
+  // run-time asserts of the cores (CFARCoreWithMem.scala:31-32)
+  if (a.W < 1 || a.W > c.leadLaggWindowSize) { err = "windowCells must be in 1..leadLaggWindowSize"; return RSP_EINVAL; }
+  if (a.G < 0 || a.G > c.guardWindowSize) { err = "guardCells must be in 0..guardWindowSize"; return RSP_EINVAL; }
+  if (a.core == CORE_MEM && a.G < 1) { err = "guardCells must be positive"; return RSP_EINVAL; }
+  if (!(N > 2 * a.W + 2 * a.G + 1)) { err = "fftWin must exceed 2*windowCells + 2*guardCells + 1"; return RSP_EINVAL; }
+  if (a.core == CORE_LIS && a.cfar_algorithm == 1 &&
+      (a.idx_lagg < 1 || a.idx_lagg > a.W || a.idx_lead < 1 || a.idx_lead > a.W)) { err = "indexLagg/indexLead must be in 1..windowCells"; return RSP_EINVAL; }
+  if (a.core == CORE_ASR && (a.sub_cells < 1 || a.sub_cells > a.W || !is_pow2(a.sub_cells) || (a.W % a.sub_cells))) {
+    err = "subWindowSize must be a power of 2 dividing windowCells"; return RSP_EINVAL; }
+  if (a.core != CORE_ASR && a.cfar_mode == 3) { /* MuxLookup default: smallestOf (CFARCoreWithMem.scala:138-141) */ }
+  return RSP_OK;
+}
+
+inline rsp_status plan_fixed(const rsp_chain_params &p, const Regs &r, const Tables &t, int first_stage, int last_stage,
+                             FxArgs &a, Plan &pl, std::string &err) {
+  std::memset(&a, 0, sizeof(a));
+  const rsp_fft_params &f = p.fft;
+  const int Smax = log2_ceil((uint32_t)f.numPoints);
+  int S;
+  if (first_stage == STAGE_CFAR) {
+    const int N = (int)r.cfar[RSP_CFAR_REG_FFTWIN];
+    if (!is_pow2(N) || N < 2) { err = "CFAR fftWin must be a power of 2 here"; return RSP_EUNSUPPORTED; }
+    S = log2_ceil((uint32_t)N);
+  } else {
+    S = f.runTime ? (int)r.fft[RSP_FFT_REG_FFTSIZE] : Smax;
+    if (S < 1 || S > Smax) { err = "fftSize register must be in 1..log2(numPoints)"; return RSP_EINVAL; }
+    if ((Smax - S) & 1) { err = "radix 2^2 run-time size must drop an even number of stages (Radix22RunTimeSpec.scala:18-19)"; return RSP_EINVAL; }
+  }
+  pl.S = S; pl.first_stage = first_stage; pl.last_stage = last_stage;
+  a.first_stage = first_stage; a.last_stage = last_stage;
+  a.data_width = f.dataWidth; a.bp = f.binPoint; a.tw_bp = f.twiddleWidth - 2; a.trim = f.trimType; a.use4muls = f.use4Muls ? 1 : 0;
+  a.bitrev = f.useBitReverse ? 1 : 0;
+  a.fft_dir = f.fftDirReg ? (int)(r.fft[RSP_FFT_REG_FFTDIR] & 1u) : (f.fftDir ? 1 : 0);
+  const uint32_t phys = f.keepMSBorLSBReg ? r.fft[RSP_FFT_REG_KEEPMSBORLSB] : f.keepMSBorLSB;
+  const uint32_t smask = S >= 32 ? 0xFFFFFFFFu : ((1u << S) - 1u);
+  a.keep_mask = (first_stage == STAGE_CFAR) ? smask : ((phys >> (Smax - S)) & smask);   // run-time size uses the LAST S stages
+  for (int L = 0; L < 16; ++L) a.tw_off[L] = t.tw_off[L];
+  a.sel = (int)(r.mag[RSP_MAG_REG_SEL] & 3u);
+  a.mag_w = p.mag.dataWidth; a.mag_bp = p.mag.binPoint; a.log_w = p.mag.dataWidthLog; a.log_bp = p.mag.binPointLog;
+  a.log_L = p.mag.log2LookUpWidth; a.mag_trim = TRIM_FLOOR;   // DspContext default trimType
+  const rsp_cfar_params &c = p.cfar;
+  a.in_w = c.inWidth; a.in_bp = c.inBinPoint; a.thr_w = c.thresholdWidth; a.thr_bp = c.thresholdBinPoint;
+  a.sc_w = c.scalerWidth; a.sc_bp = c.scalerBinPoint;
+  a.sumw = c.inWidth + bit_length((uint32_t)log2_ceil((uint32_t)c.leadLaggWindowSize)) + 1;   // CFARCoreWithMem.scala:34
+  a.scaler = (int)wrap_host((long long)r.cfar[RSP_CFAR_REG_THRESHOLDSCALER], c.scalerWidth);
+  a.cfar_trim = TRIM_FLOOR;
+  if (last_stage == STAGE_CFAR) {
+    const rsp_status st = plan_cfar_common(p, r, 1 << S, a, err);
+    if (st != RSP_OK) return st;
+    if (a.sumw > 31) { err = "CFAR sum register too wide"; return RSP_EUNSUPPORTED; }
+  }
+  // kernel variant
+  const int bp_a = a.bp, bp_b = a.tw_bp;
+  const int s1 = bp_a + bp_b - ((bp_a > bp_b ? bp_a : bp_b) + 1);
+  const bool common = f.dataWidth == 16 && f.trimType == RSP_TRIM_ROUND_HALF_UP && a.keep_mask == smask && a.fft_dir == 1 &&
+                      p.mag.dataWidth == 16;
+  pl.mode = MODE_GENERIC;
+  if (common && s1 <= 0) pl.mode = MODE_FAST;
+  else if (common && s1 >= 1 && !f.use4Muls) pl.mode = MODE_FAST3;
+  return RSP_OK;
+}
+
+inline rsp_status plan_f32(const rsp_chain_params &p, const Regs &r, const Tables &t, int first_stage, int last_stage,
+                           F32Args &a, Plan &pl, std::string &err) {
+  std::memset(&a, 0, sizeof(a));
+  const rsp_fft_params &f = p.fft;
+  const int Smax = log2_ceil((uint32_t)f.numPoints);
+  int S;
+  if (first_stage == STAGE_CFAR) {
+    const int N = (int)r.cfar[RSP_CFAR_REG_FFTWIN];
+    if (!is_pow2(N) || N < 2) { err = "CFAR fftWin must be a power of 2 here"; return RSP_EUNSUPPORTED; }
+    S = log2_ceil((uint32_t)N);
+  } else {
+    S = f.runTime ? (int)r.fft[RSP_FFT_REG_FFTSIZE] : Smax;
+    if (S < 1 || S > Smax) { err = "fftSize register must be in 1..log2(numPoints)"; return RSP_EINVAL; }
+  }
+  pl.S = S; pl.mode = 0; pl.first_stage = first_stage; pl.last_stage = last_stage;
+  a.first_stage = first_stage; a.last_stage = last_stage;
+  a.bitrev = f.useBitReverse ? 1 : 0;
+  a.fft_dir = f.fftDirReg ? (int)(r.fft[RSP_FFT_REG_FFTDIR] & 1u) : (f.fftDir ? 1 : 0);
+  for (int L = 0; L < 16; ++L) a.tw_off[L] = t.tw_off[L];
+  a.sel = (int)(r.mag[RSP_MAG_REG_SEL] & 3u);
+  a.scaler = r.scaler_f32;
+  if (last_stage == STAGE_CFAR) {
+    const rsp_status st = plan_cfar_common(p, r, 1 << S, a, err);
+    if (st != RSP_OK) return st;
+    a.inv_div = std::ldexp(1.0f, -a.div_sum);
+  }
+  return RSP_OK;
+}
+
+// ---- PLFG schedule -----------------------------------------------------------------------------------------------
+// The PLFG is a counter tree (frames > chirps > repeats > segments > samples, PLFGDspBlockMem.scala:242-345).  Inside a
+// segment the frequency word is an arithmetic progression and the NCO phase a quadratic in the sample index, so the host
+// flattens the registers + config RAM into a list of segments with their starting values and the device evaluates any
+// sample in closed form (modulo 2^outputWidth and 2^phaseWidth).
+struct GenSegment {
+  uint64_t start;     // index of the segment's first sample in the stream
+  uint32_t n;         // samples in the segment
+  int32_t f0;         // PLFG value of the first sample (raw, sign-extended)
+  int32_t step;       // per-sample increment (signed slope; 0 for pauses)
+  uint32_t phase0;    // NCO accumulator before the first sample of the segment
+  uint32_t flags;     // bit 0: every sample is f0 (reset segment / inter-frame pause)
+};
+
+inline rsp_status plan_generator(const rsp_chain_params &p, const Regs &r, uint64_t n_samples, std::vector<GenSegment> &segs, std::string &err) {
+  const rsp_plfg_params &g = p.plfg;
+  const int ow = g.outputWidthInt + g.outputWidthFrac, nsw = g.maxNumOfSamplesWidth, pw = p.nco.phaseWidth;
+  const uint32_t pmask = pw >= 32 ? 0xFFFFFFFFu : ((1u << pw) - 1u);
+  const long long start = wrap_host((long long)r.plfg[RSP_PLFG_REG_STARTINGPOINT], ow);
+  const uint32_t frame_num = r.plfg[RSP_PLFG_REG_FRAMENUM];
+  const uint32_t inter = r.plfg[RSP_PLFG_REG_INTERFRAMENUMOFSAMPLES];
+  const uint32_t ndiff = r.plfg[RSP_PLFG_REG_DIFFERENTCHIRPSNUM] < 1 ? 1 : r.plfg[RSP_PLFG_REG_DIFFERENTCHIRPSNUM];
+  const uint32_t seg0 = RSP_PLFG_REG_SEGMENTNUMS0, rep0 = seg0 + g.maxChirpOrdinalNum, ord0 = rep0 + g.maxNumOfDifferentChirps;
+  segs.clear();
+  uint64_t k = 0;
+  long long cur = start;
+  uint32_t phase = 0;
+  auto push = [&](uint32_t n, long long f0, long long step, bool constant) {
+    GenSegment s; s.start = k; s.n = n; s.f0 = (int32_t)f0; s.step = (int32_t)step; s.phase0 = phase; s.flags = constant ? 1u : 0u;
+    segs.push_back(s);
+    // advance: phase += sum_{m<n} (f0 + m*step) mod 2^pw; cur = value of the last sample
+    const unsigned long long nn = n;
+    const unsigned long long sum = (unsigned long long)(uint32_t)f0 * nn + (constant ? 0ULL : (unsigned long long)(long long)step * (nn * (nn - 1) / 2));
+    // per-sample truncation of the frequency word to phaseWidth bits commutes with the modular sum only if the PLFG value is
+    // reduced modulo 2^ow first; the device handles the 2^ow wrap exactly (see gen_sample), so do the same here sample-exact:
+    (void)sum;
+    k += n;
+  };
+  (void)push;
+  // sample-exact walk (segment lists are short; the per-sample work is on the device)
+  const bool forever = frame_num == 0;
+  for (uint32_t frame = 0; (forever || frame < frame_num) && k < n_samples; ++frame) {
+    for (uint32_t d = 0; d < ndiff && k < n_samples; ++d) {
+      const uint32_t chirp = r.plfg[ord0 + d];
+      const uint32_t reps = r.plfg[rep0 + d] < 1 ? 1 : r.plfg[rep0 + d];
+      if (chirp >= (uint32_t)g.maxChirpOrdinalNum) { err = "chirpOrdinalNums entry out of range"; return RSP_EINVAL; }
+      for (uint32_t rep = 0; rep < reps && k < n_samples; ++rep) {
+        const uint32_t nseg = r.plfg[seg0 + chirp] < 1 ? 1 : r.plfg[seg0 + chirp];
+        for (uint32_t sg = 0; sg < nseg && k < n_samples; ++sg) {
+          const uint64_t wd = r.plfg_ram[(size_t)chirp * g.maxNumOfSegments + sg];
+          const long long slope = wrap_host((long long)(wd & ((1ULL << ow) - 1)), ow);
+          uint32_t ns = (uint32_t)((wd >> ow) & ((1ULL << nsw) - 1));
+          if (!(ns > 1)) ns += 1;                                   // PLFGDspBlockMem.scala:175
+          const int sign = (int)((wd >> (ow + nsw)) & 1), reset = (int)((wd >> (ow + nsw + 1)) & 1);
+          const long long step = sign ? slope : -slope;
+          GenSegment s; s.start = k; s.n = ns; s.phase0 = phase; s.step = (int32_t)step;
+          if (reset) { s.f0 = (int32_t)start; s.flags = 1u; }
+          else if (sg == 0) { s.f0 = (int32_t)start; s.flags = 0u; }              // first sample of a chirp restarts at startingPoint
+          else { s.f0 = (int32_t)wrap_host(cur + step, ow); s.flags = 0u; }
+          segs.push_back(s);
+          // walk the segment to get the end state exactly as the hardware's wrapping registers do
+          for (uint32_t q = 0; q < ns; ++q) {
+            long long v;
+            if (s.flags & 1u) v = start;
+            else v = wrap_host((long long)s.f0 + (long long)q * step, ow);
+            cur = v;
+            phase = (phase + ((uint32_t)v & pmask)) & pmask;
+          }
+          k += ns;
+        }
+      }
+    }
+    if ((forever || frame + 1 < frame_num) && inter > 0 && k < n_samples) {   // inter-frame pause emits startingPoint
+      GenSegment s; s.start = k; s.n = inter; s.f0 = (int32_t)start; s.step = 0; s.phase0 = phase; s.flags = 1u;
+      segs.push_back(s);
+      for (uint32_t q = 0; q < inter; ++q) phase = (phase + ((uint32_t)start & pmask)) & pmask;
+      cur = start;
+      k += inter;
+    }
+    if (segs.size() > (1u << 22)) { err = "PLFG schedule too long"; return RSP_EUNSUPPORTED; }
+  }
+  if (k < n_samples) { err = "the PLFG schedule (frameNum frames) ends before n_samples; set frameNum = 0 to run forever"; return RSP_EINVAL; }
+  return RSP_OK;
+}
+
+}  // namespace rsp
