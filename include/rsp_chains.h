@@ -68,6 +68,8 @@ typedef struct {
   int32_t decimType;        /* 0 = DIF (only DIF is built; DIT -> RSP_EUNSUPPORTED)                        */
   int32_t sdfRadix;         /* 4 = "2^2" (only radix 2^2 is built; 2 -> RSP_EUNSUPPORTED)                  */
   int32_t expandLogicAny;   /* 1 if any expandLogic(i) != 0 (grow mode -> RSP_EUNSUPPORTED)                */
+  int32_t keepMSBorLSBReg;  /* 1: the keepMSBorLSBReg register overrides keepMSBorLSB (FFTBlock.scala:92-93)   */
+  int32_t fftDirReg;        /* 1: the fftDir register overrides fftDir (FFTBlock.scala:90-91)                 */
 } rsp_fft_params;
 
 /* MAGParams.fixed (generators/logMagMux/src/main/scala/LogMagMux.scala:14-49) */

@@ -1,0 +1,575 @@
+// rsp_abi.cu -- the C ABI of librsp_b200.so (include/rsp_chains.h): handle, register files, kernel dispatch and the
+// host-buffer pipeline.  CUDA only: without a device every compute entry point fails with RSP_ECUDA.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <cstdio>
+#include <cstdlib>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "../../include/rsp_chains.h"
+#include "rsp_host.hpp"
+#include "rsp_launch.hpp"
+#include "rsp_fast.cuh"
+
+using namespace rsp;
+
+static thread_local std::string g_last_error;
+static rsp_status fail(rsp_status st, const std::string &msg) { g_last_error = msg; return st; }
+#define CUDA_TRY(expr)                                                                                       \
+  do {                                                                                                       \
+    cudaError_t e__ = (expr);                                                                                \
+    if (e__ != cudaSuccess) return fail(RSP_ECUDA, std::string(#expr) + ": " + cudaGetErrorString(e__));     \
+  } while (0)
+
+static const int N_PIPE = 3;   // chunks in flight in rsp_run_host
+
+struct rsp_chain {
+  rsp_chain_params p;
+  Regs r;
+  Tables t;
+  int device = 0, sm_count = 0;
+  uint32_t *d_tw = nullptr;
+  F2 *d_twf = nullptr;
+  int32_t *d_log_tab = nullptr, *d_nco_tab = nullptr;
+  GenSegment *d_segs = nullptr;
+  size_t segs_cap = 0;
+  uint32_t *d_gen_scratch = nullptr;   // NCO beats between generator and chain when the caller does not want them
+  size_t gen_scratch_cap = 0;
+  bool gen_dirty = true;               // PLFG registers / RAM changed since the segment list was uploaded
+  GenPlan gen_plan;
+  uint64_t launches = 0;
+  std::string variant;
+  // host pipeline
+  cudaStream_t pipe_stream[N_PIPE] = {nullptr, nullptr, nullptr};
+  void *pipe_in[N_PIPE] = {nullptr, nullptr, nullptr}, *pipe_out[N_PIPE] = {nullptr, nullptr, nullptr};
+  uint32_t *pipe_mask[N_PIPE] = {nullptr, nullptr, nullptr};
+  void *stage_in[N_PIPE] = {nullptr, nullptr, nullptr}, *stage_out[N_PIPE] = {nullptr, nullptr, nullptr};   // pinned staging for pageable callers
+  size_t pipe_rows_cap = 0, pipe_row_in = 0, pipe_row_out = 0, pipe_row_mask = 0;
+  rsp_detection *d_det_list = nullptr;
+  uint32_t *d_det_count = nullptr;
+  uint32_t det_cap = 0;
+};
+
+// ---------------------------------------------------------------------------------------------------------------------
+// small kernels that live in this translation unit
+namespace rsp {
+// LogMagMux alone: one beat per thread, grid-stride (AXI4LogMagMuxBlock)
+__global__ void __launch_bounds__(256) mag_fixed_kernel(const FxArgs a, unsigned long long n_beats) {
+  const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
+  for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < n_beats; i += stride) {
+    const uint32_t wd = ldg(&a.in[i]);
+    const int re = wrapw((int)(wd >> 16), a.mag_w), im = wrapw((int)(wd & 0xFFFFu), a.mag_w);
+    int ore;
+    const int v = mag_one(a, re, im, &ore);
+    a.out[i] = pack_iq(ore, v);
+  }
+}
+
+__global__ void __launch_bounds__(256) mag_f32_kernel(const F32Args a, unsigned long long n_beats) {
+  const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
+  for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < n_beats; i += stride) {
+    const F2 v = a.in[i];
+    a.out[i] = mag_f32(a.sel, v.x, v.y);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// PLFG -> NCO: one sample per thread-iteration, evaluated in closed form from the flattened segment list
+__global__ void __launch_bounds__(256) generator_kernel(const GenArgs g, unsigned long long n_samples, uint32_t *nco_out, int32_t *plfg_out) {
+  const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
+  for (unsigned long long k = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; k < n_samples; k += stride) {
+    int v;
+    const uint32_t beat = gen_sample(g, k, &v);
+    if (nco_out) nco_out[k] = beat;
+    if (plfg_out) plfg_out[k] = v;
+  }
+}
+
+}  // namespace rsp
+
+// ---------------------------------------------------------------------------------------------------------------------
+// launch helpers
+static rsp_status launch_fixed(rsp_chain *c, const Plan &pl, const FxArgs &a, cudaStream_t st) {
+  if (a.n_rows == 0) return RSP_OK;
+  const LaunchCtx ctx = {c->device, c->sm_count};
+  const char *err = "";
+  const rsp_status s = fast_chain_supported(pl, a) ? launch_fast_chain(pl, ctx, a, st, &err)
+                                                   : launch_fixed_inst(pl.mode, pl.S, ctx, a, st, &err);
+  if (s != RSP_OK) return fail(s, err);
+  ++c->launches;
+  return RSP_OK;
+}
+
+static rsp_status launch_f32(rsp_chain *c, const Plan &pl, const F32Args &a, cudaStream_t st) {
+  if (a.n_rows == 0) return RSP_OK;
+  const LaunchCtx ctx = {c->device, c->sm_count};
+  const char *err = "";
+  const rsp_status s = launch_f32_inst(pl.S, ctx, a, st, &err);
+  if (s != RSP_OK) return fail(s, err);
+  ++c->launches;
+  return RSP_OK;
+}
+
+static unsigned ew_grid(const rsp_chain *c, unsigned long long n) {
+  const unsigned long long want = (n + 255) / 256;
+  return (unsigned)std::max<unsigned long long>(1, std::min<unsigned long long>(want, (unsigned long long)c->sm_count * 16));
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// life cycle
+extern "C" void rsp_chain_params_default(rsp_chain_params *p) {
+  if (!p) return;
+  std::memset(p, 0, sizeof(*p));
+  p->arith = RSP_ARITH_FIXED;
+  p->hasGenerator = 1;
+  // RspChainVanillaApp (src/main/scala/RspChain.scala:83-147)
+  p->plfg = {4, 8, 8, 4, 4, 8, 16, 0};
+  p->nco.tableSize = 128; p->nco.tableWidth = 16; p->nco.phaseWidth = 9; p->nco.phaseAccEnable = 1;
+  rsp_fft_params &f = p->fft;
+  f.numPoints = 1024; f.dataWidth = 16; f.binPoint = 0; f.twiddleWidth = 16; f.trimType = RSP_TRIM_ROUND_HALF_UP; f.use4Muls = 0;
+  f.useBitReverse = 1; f.fftDir = 1; f.runTime = 1; f.keepMSBorLSB = 0x3FF; f.decimType = 0; f.sdfRadix = 4; f.expandLogicAny = 0;
+  f.keepMSBorLSBReg = 0; f.fftDirReg = 0;
+  p->mag = {16, 0, 16, 9, 9};
+  rsp_cfar_params &c = p->cfar;
+  c.inWidth = 16; c.inBinPoint = 0; c.thresholdWidth = 16; c.thresholdBinPoint = 0; c.scalerWidth = 16; c.scalerBinPoint = 0;
+  c.CFARAlgorithm = RSP_CFAR_CA; c.includeCASH = 0; c.minSubWindowSize = 0; c.leadLaggWindowSize = 64; c.sendCut = 0;
+  c.guardWindowSize = 4; c.fftSize = 1024;
+}
+
+static void free_pipe(rsp_chain *c) {
+  for (int i = 0; i < N_PIPE; ++i) {
+    if (c->pipe_in[i]) cudaFree(c->pipe_in[i]);
+    if (c->pipe_out[i]) cudaFree(c->pipe_out[i]);
+    if (c->pipe_mask[i]) cudaFree(c->pipe_mask[i]);
+    if (c->stage_in[i]) cudaFreeHost(c->stage_in[i]);
+    if (c->stage_out[i]) cudaFreeHost(c->stage_out[i]);
+    c->pipe_in[i] = c->pipe_out[i] = nullptr; c->pipe_mask[i] = nullptr; c->stage_in[i] = c->stage_out[i] = nullptr;
+  }
+  c->pipe_rows_cap = 0;
+}
+
+extern "C" void rsp_chain_destroy(rsp_chain *c) {
+  if (!c) return;
+  cudaSetDevice(c->device);
+  free_pipe(c);
+  for (int i = 0; i < N_PIPE; ++i) if (c->pipe_stream[i]) cudaStreamDestroy(c->pipe_stream[i]);
+  cudaFree(c->d_tw); cudaFree(c->d_twf); cudaFree(c->d_log_tab); cudaFree(c->d_nco_tab); cudaFree(c->d_segs);
+  cudaFree(c->d_gen_scratch); cudaFree(c->d_det_list); cudaFree(c->d_det_count);
+  delete c;
+}
+
+template <typename T>
+static rsp_status upload(const std::vector<T> &v, T **d) {
+  CUDA_TRY(cudaMalloc((void **)d, std::max<size_t>(1, v.size()) * sizeof(T)));
+  if (!v.empty()) CUDA_TRY(cudaMemcpy(*d, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice));
+  return RSP_OK;
+}
+
+extern "C" rsp_status rsp_chain_create(const rsp_chain_params *params, int device, rsp_chain **out) {
+  if (!params || !out) return fail(RSP_EINVAL, "null argument");
+  *out = nullptr;
+  std::string err;
+  const rsp_status vs = validate_params(*params, err);
+  if (vs != RSP_OK) return fail(vs, err);
+  int n_dev = 0;
+  if (cudaGetDeviceCount(&n_dev) != cudaSuccess || n_dev < 1)
+    return fail(RSP_ECUDA, "no CUDA device: librsp_b200 has no CPU path");
+  if (device < 0 || device >= n_dev) return fail(RSP_EINVAL, "device index out of range");
+  CUDA_TRY(cudaSetDevice(device));
+  rsp_chain *c = new (std::nothrow) rsp_chain();
+  if (!c) return fail(RSP_ENOMEM, "out of host memory");
+  c->p = *params;
+  c->device = device;
+  cudaDeviceProp prop;
+  if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) { delete c; return fail(RSP_ECUDA, "cudaGetDeviceProperties failed"); }
+  c->sm_count = prop.multiProcessorCount;
+  regs_reset(c->p, c->r);
+  build_tables(c->p, c->t);
+  rsp_status s = upload(c->t.tw, &c->d_tw);
+  if (s == RSP_OK) s = upload(c->t.twf, &c->d_twf);
+  if (s == RSP_OK) s = upload(c->t.log_tab, &c->d_log_tab);
+  if (s == RSP_OK) s = upload(c->t.nco_tab, &c->d_nco_tab);
+  if (s != RSP_OK) { rsp_chain_destroy(c); return s; }
+  *out = c;
+  return RSP_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// registers
+extern "C" rsp_status rsp_reg_write(rsp_chain *c, rsp_block blk, uint32_t idx, uint32_t value) {
+  if (!c) return fail(RSP_EINVAL, "null handle");
+  bool ro = false;
+  const int w = reg_width(c->p, blk, idx, &ro);
+  if (blk == RSP_BLK_CFAR && idx == RSP_CFAR_REG_THRESHOLDSCALER_F32) {
+    std::memcpy(&c->r.scaler_f32, &value, 4);
+    return RSP_OK;
+  }
+  if (w < 0) return fail(RSP_EINVAL, "no such register");
+  if (ro) return RSP_OK;   // writes to read-only fields are ignored by the regmap
+  uint32_t *slot = reg_slot(c->r, blk, idx);
+  if (!slot) return fail(RSP_EINVAL, "no such register");
+  *slot = w >= 32 ? value : (value & ((1u << w) - 1u));   // RegField(width): upper bits are dropped
+  if (blk == RSP_BLK_PLFG) c->gen_dirty = true;
+  return RSP_OK;
+}
+
+extern "C" rsp_status rsp_reg_read(rsp_chain *c, rsp_block blk, uint32_t idx, uint32_t *value) {
+  if (!c || !value) return fail(RSP_EINVAL, "null argument");
+  if (blk == RSP_BLK_CFAR && idx == RSP_CFAR_REG_THRESHOLDSCALER_F32) { std::memcpy(value, &c->r.scaler_f32, 4); return RSP_OK; }
+  bool ro = false;
+  if (reg_width(c->p, blk, idx, &ro) < 0) return fail(RSP_EINVAL, "no such register");
+  uint32_t *slot = reg_slot(c->r, blk, idx);
+  if (!slot) return fail(RSP_EINVAL, "no such register");
+  *value = *slot;   // busy / overflow read 0: calls are synchronous with respect to the registers, overflow flags are not built
+  return RSP_OK;
+}
+
+extern "C" rsp_status rsp_plfg_ram_write(rsp_chain *c, uint32_t idx, uint32_t value) {
+  if (!c) return fail(RSP_EINVAL, "null handle");
+  if (!c->p.hasGenerator) return fail(RSP_EINVAL, "this chain has no PLFG");
+  if (idx >= c->r.plfg_ram.size()) return fail(RSP_EINVAL, "PLFG RAM index out of range");
+  const int bits = c->p.plfg.outputWidthInt + c->p.plfg.maxNumOfSamplesWidth + 2;   // protoRAM width (PLFGDspBlockMem.scala:108-117)
+  c->r.plfg_ram[idx] = bits >= 32 ? value : (value & ((1u << bits) - 1u));
+  c->gen_dirty = true;
+  return RSP_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// planning glue
+static void bind_fixed(rsp_chain *c, FxArgs &a) { a.tw = c->d_tw; a.log_tab = c->d_log_tab; }
+static void bind_f32(rsp_chain *c, F32Args &a) { a.tw = c->d_twf; }
+static void bind_dets(const rsp_dets *d, Detection **list, uint32_t **count, uint32_t *cap) {
+  if (d && d->list && d->count) { *list = reinterpret_cast<Detection *>(d->list); *count = d->count; *cap = d->capacity; }
+  else { *list = nullptr; *count = nullptr; *cap = 0; }
+}
+
+static rsp_status run_stages(rsp_chain *c, int first, int last, const void *d_in, uint32_t n_rows, void *d_out, uint32_t *d_peak_mask,
+                             const rsp_dets *dets, cudaStream_t st, uint32_t row_base = 0) {
+  std::string err;
+  Plan pl;
+  if (c->p.arith == RSP_ARITH_FIXED) {
+    FxArgs a;
+    const rsp_status s = plan_fixed(c->p, c->r, c->t, first, last, a, pl, err);
+    if (s != RSP_OK) return fail(s, err);
+    bind_fixed(c, a);
+    a.in = static_cast<const uint32_t *>(d_in); a.out = static_cast<uint32_t *>(d_out); a.n_rows = n_rows; a.row_base = row_base;
+    bind_dets(dets, &a.det_list, &a.det_count, &a.det_cap);
+    if (!a.out && !(last == STAGE_CFAR && a.det_list)) return fail(RSP_EINVAL, "no output requested");
+    return launch_fixed(c, pl, a, st);
+  }
+  F32Args a;
+  const rsp_status s = plan_f32(c->p, c->r, c->t, first, last, a, pl, err);
+  if (s != RSP_OK) return fail(s, err);
+  bind_f32(c, a);
+  if (first == STAGE_CFAR) a.in_mag = static_cast<const float *>(d_in); else a.in = static_cast<const F2 *>(d_in);
+  if (last == STAGE_FFT) a.out_c = static_cast<F2 *>(d_out); else a.out = static_cast<float *>(d_out);
+  a.peak_mask = d_peak_mask; a.n_rows = n_rows; a.row_base = row_base;
+  bind_dets(dets, &a.det_list, &a.det_count, &a.det_cap);
+  if (!d_out && !(last == STAGE_CFAR && (a.det_list || a.peak_mask))) return fail(RSP_EINVAL, "no output requested");
+  return launch_f32(c, pl, a, st);
+}
+
+static rsp_status rows_of(uint32_t n_chirps, uint32_t n_rx, uint32_t *rows) {
+  const unsigned long long r = (unsigned long long)n_chirps * (unsigned long long)n_rx;
+  if (r > 0x7FFFFFFFull) return fail(RSP_EINVAL, "n_chirps * n_rx too large");
+  *rows = (uint32_t)r;
+  return RSP_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// device entry points
+extern "C" rsp_status rsp_run(rsp_chain *c, const void *d_in, uint32_t n_chirps, uint32_t n_rx, void *d_out, uint32_t *d_peak_mask,
+                              const rsp_dets *dets, void *stream) {
+  if (!c || !d_in) return fail(RSP_EINVAL, "null argument");
+  uint32_t rows;
+  rsp_status s = rows_of(n_chirps, n_rx, &rows);
+  if (s != RSP_OK) return s;
+  CUDA_TRY(cudaSetDevice(c->device));
+  return run_stages(c, STAGE_FFT, STAGE_CFAR, d_in, rows, d_out, d_peak_mask, dets, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" rsp_status rsp_fft_run(rsp_chain *c, const void *d_in, uint32_t n_chirps, void *d_out, void *stream) {
+  if (!c || !d_in || !d_out) return fail(RSP_EINVAL, "null argument");
+  CUDA_TRY(cudaSetDevice(c->device));
+  return run_stages(c, STAGE_FFT, STAGE_FFT, d_in, n_chirps, d_out, nullptr, nullptr, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" rsp_status rsp_cfar_run(rsp_chain *c, const void *d_in, uint32_t n_chirps, void *d_out, uint32_t *d_peak_mask,
+                                   const rsp_dets *dets, void *stream) {
+  if (!c || !d_in) return fail(RSP_EINVAL, "null argument");
+  CUDA_TRY(cudaSetDevice(c->device));
+  return run_stages(c, STAGE_CFAR, STAGE_CFAR, d_in, n_chirps, d_out, d_peak_mask, dets, static_cast<cudaStream_t>(stream));
+}
+
+extern "C" rsp_status rsp_mag_run(rsp_chain *c, const void *d_in, uint64_t n_beats, void *d_out, void *stream) {
+  if (!c || !d_in || !d_out) return fail(RSP_EINVAL, "null argument");
+  CUDA_TRY(cudaSetDevice(c->device));
+  if (n_beats == 0) return RSP_OK;
+  std::string err;
+  Plan pl;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (c->p.arith == RSP_ARITH_FIXED) {
+    FxArgs a;
+    const rsp_status s = plan_fixed(c->p, c->r, c->t, STAGE_MAG, STAGE_MAG, a, pl, err);
+    if (s != RSP_OK) return fail(s, err);
+    bind_fixed(c, a);
+    a.in = static_cast<const uint32_t *>(d_in); a.out = static_cast<uint32_t *>(d_out);
+    mag_fixed_kernel<<<ew_grid(c, n_beats), 256, 0, st>>>(a, n_beats);
+  } else {
+    F32Args a;
+    const rsp_status s = plan_f32(c->p, c->r, c->t, STAGE_MAG, STAGE_MAG, a, pl, err);
+    if (s != RSP_OK) return fail(s, err);
+    a.in = static_cast<const F2 *>(d_in); a.out = static_cast<float *>(d_out);
+    mag_f32_kernel<<<ew_grid(c, n_beats), 256, 0, st>>>(a, n_beats);
+  }
+  CUDA_TRY(cudaGetLastError());
+  ++c->launches;
+  return RSP_OK;
+}
+
+static rsp_status prepare_generator(rsp_chain *c, uint64_t n_samples, GenArgs &g, cudaStream_t st) {
+  if (!c->p.hasGenerator) return fail(RSP_EINVAL, "this chain has no PLFG/NCO (hasGenerator = 0)");
+  if (!(c->r.plfg[RSP_PLFG_REG_ENABLE] & 1u)) return fail(RSP_EINVAL, "the PLFG enable register is 0");
+  if (c->gen_dirty) {
+    std::string err;
+    const rsp_status s = plan_generator(c->p, c->r, c->gen_plan, err);
+    if (s != RSP_OK) return fail(s, err);
+    const size_t n = c->gen_plan.segs.size();
+    if (n > c->segs_cap) {
+      // the previous list may still be read by a kernel in flight on another stream: drain before freeing
+      CUDA_TRY(cudaDeviceSynchronize());
+      cudaFree(c->d_segs); c->d_segs = nullptr; c->segs_cap = 0;
+      CUDA_TRY(cudaMalloc((void **)&c->d_segs, n * sizeof(GenSegment)));
+      c->segs_cap = n;
+    }
+    CUDA_TRY(cudaMemcpyAsync(c->d_segs, c->gen_plan.segs.data(), n * sizeof(GenSegment), cudaMemcpyHostToDevice, st));
+    CUDA_TRY(cudaStreamSynchronize(st));   // the host vector may be rebuilt by the next register write
+    c->gen_dirty = false;
+  }
+  if (n_samples > c->gen_plan.total)
+    return fail(RSP_EINVAL, "the PLFG schedule (frameNum frames) ends before the requested samples; frameNum = 0 runs forever");
+  g.segs = c->d_segs; g.n_segs = (uint32_t)c->gen_plan.segs.size();
+  g.period_len = c->gen_plan.period_len; g.period_phase = c->gen_plan.period_phase;
+  g.nco_tab = c->d_nco_tab;
+  g.table_size = c->p.nco.tableSize; g.addr_bits = log2_ceil((uint32_t)c->p.nco.tableSize);
+  g.table_width = c->p.nco.tableWidth; g.phase_width = c->p.nco.phaseWidth;
+  g.out_width = c->p.plfg.outputWidthInt + c->p.plfg.outputWidthFrac;
+  g.phase_acc_enable = c->p.nco.phaseAccEnable ? 1 : 0;
+  g.poff = 0;   // poffType Fixed: no phase-offset port (NCOLazyModuleBlock.scala:246-271)
+  return RSP_OK;
+}
+
+extern "C" rsp_status rsp_generate(rsp_chain *c, uint64_t n_samples, uint32_t *d_nco_out, int32_t *d_plfg_out, void *stream) {
+  if (!c || (!d_nco_out && !d_plfg_out)) return fail(RSP_EINVAL, "null argument");
+  CUDA_TRY(cudaSetDevice(c->device));
+  if (n_samples == 0) return RSP_OK;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  GenArgs g;
+  const rsp_status s = prepare_generator(c, n_samples, g, st);
+  if (s != RSP_OK) return s;
+  generator_kernel<<<ew_grid(c, n_samples), 256, 0, st>>>(g, n_samples, d_nco_out, d_plfg_out);
+  CUDA_TRY(cudaGetLastError());
+  ++c->launches;
+  return RSP_OK;
+}
+
+extern "C" rsp_status rsp_run_from_generator(rsp_chain *c, uint32_t n_chirps, uint32_t n_rx, void *d_out, uint32_t *d_peak_mask,
+                                             const rsp_dets *dets, uint32_t *d_nco_out, void *stream) {
+  if (!c) return fail(RSP_EINVAL, "null handle");
+  if (c->p.arith != RSP_ARITH_FIXED) return fail(RSP_EUNSUPPORTED, "the PLFG/NCO generator feeds the fixed-point chain only");
+  uint32_t rows;
+  rsp_status s = rows_of(n_chirps, n_rx, &rows);
+  if (s != RSP_OK) return s;
+  CUDA_TRY(cudaSetDevice(c->device));
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  const int S = c->p.fft.runTime ? (int)c->r.fft[RSP_FFT_REG_FFTSIZE] : log2_ceil((uint32_t)c->p.fft.numPoints);
+  const uint64_t n_samples = (uint64_t)rows << S;
+  uint32_t *beats = d_nco_out;
+  if (!beats) {
+    if (n_samples > c->gen_scratch_cap) {
+      CUDA_TRY(cudaDeviceSynchronize());
+      cudaFree(c->d_gen_scratch); c->d_gen_scratch = nullptr; c->gen_scratch_cap = 0;
+      CUDA_TRY(cudaMalloc((void **)&c->d_gen_scratch, n_samples * sizeof(uint32_t)));
+      c->gen_scratch_cap = n_samples;
+    }
+    beats = c->d_gen_scratch;
+  }
+  s = rsp_generate(c, n_samples, beats, nullptr, stream);
+  if (s != RSP_OK) return s;
+  return run_stages(c, STAGE_FFT, STAGE_CFAR, beats, rows, d_out, d_peak_mask, dets, st);
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// host-buffer pipeline
+extern "C" rsp_status rsp_host_alloc(void **p, size_t bytes) {
+  if (!p) return fail(RSP_EINVAL, "null argument");
+  CUDA_TRY(cudaHostAlloc(p, std::max<size_t>(bytes, 1), cudaHostAllocDefault));
+  return RSP_OK;
+}
+extern "C" void rsp_host_free(void *p) { if (p) cudaFreeHost(p); }
+
+static bool is_pinned(const void *p) {
+  cudaPointerAttributes at;
+  if (cudaPointerGetAttributes(&at, p) != cudaSuccess) { cudaGetLastError(); return false; }
+  return at.type == cudaMemoryTypeHost;
+}
+
+static rsp_status ensure_pipe(rsp_chain *c, size_t rows_per_chunk, size_t row_in, size_t row_out, size_t row_mask, bool need_stage_in, bool need_stage_out) {
+  for (int i = 0; i < N_PIPE; ++i)
+    if (!c->pipe_stream[i]) CUDA_TRY(cudaStreamCreateWithFlags(&c->pipe_stream[i], cudaStreamNonBlocking));
+  const bool fits = c->pipe_rows_cap >= rows_per_chunk && c->pipe_row_in >= row_in && c->pipe_row_out >= row_out && c->pipe_row_mask >= row_mask;
+  if (!fits) {
+    CUDA_TRY(cudaDeviceSynchronize());
+    free_pipe(c);
+    for (int i = 0; i < N_PIPE; ++i) {
+      CUDA_TRY(cudaMalloc(&c->pipe_in[i], rows_per_chunk * row_in));
+      CUDA_TRY(cudaMalloc(&c->pipe_out[i], std::max<size_t>(1, rows_per_chunk * row_out)));
+      CUDA_TRY(cudaMalloc((void **)&c->pipe_mask[i], std::max<size_t>(1, rows_per_chunk * row_mask)));
+    }
+    c->pipe_rows_cap = rows_per_chunk; c->pipe_row_in = row_in; c->pipe_row_out = row_out; c->pipe_row_mask = row_mask;
+  }
+  for (int i = 0; i < N_PIPE; ++i) {
+    if (need_stage_in && !c->stage_in[i]) CUDA_TRY(cudaHostAlloc(&c->stage_in[i], c->pipe_rows_cap * c->pipe_row_in, cudaHostAllocDefault));
+    if (need_stage_out && !c->stage_out[i]) CUDA_TRY(cudaHostAlloc(&c->stage_out[i], std::max<size_t>(1, c->pipe_rows_cap * std::max(c->pipe_row_out, c->pipe_row_mask)), cudaHostAllocDefault));
+  }
+  return RSP_OK;
+}
+
+extern "C" rsp_status rsp_run_host(rsp_chain *c, const void *h_in, uint32_t n_chirps, uint32_t n_rx, void *h_out, uint32_t *h_peak_mask,
+                                   rsp_detection *h_dets, uint32_t max_dets, uint32_t *h_n_dets) {
+  if (!c || !h_in) return fail(RSP_EINVAL, "null argument");
+  uint32_t rows;
+  rsp_status s = rows_of(n_chirps, n_rx, &rows);
+  if (s != RSP_OK) return s;
+  CUDA_TRY(cudaSetDevice(c->device));
+  const bool fixed = c->p.arith == RSP_ARITH_FIXED;
+  const int S = c->p.fft.runTime ? (int)c->r.fft[RSP_FFT_REG_FFTSIZE] : log2_ceil((uint32_t)c->p.fft.numPoints);
+  if (S < 1 || S > 14) return fail(RSP_EINVAL, "fftSize register out of range");
+  const size_t N = (size_t)1 << S;
+  const size_t row_in = N * (fixed ? 4 : 8), row_out = h_out ? N * 4 : 0;
+  const size_t row_mask = (!fixed && h_peak_mask) ? ((N + 31) / 32) * 4 : 0;
+  // chunks of ~8 MiB of input keep three copies/kernels in flight without holding much HBM
+  size_t rows_per_chunk = std::max<size_t>(1, ((size_t)8 << 20) / row_in);
+  rows_per_chunk = std::min<size_t>(rows_per_chunk, std::max<uint32_t>(rows, 1));
+  const bool in_pinned = is_pinned(h_in), out_pinned = !h_out || is_pinned(h_out);
+  const bool mask_pinned = !row_mask || is_pinned(h_peak_mask);
+  s = ensure_pipe(c, rows_per_chunk, row_in, row_out, row_mask, !in_pinned, !(out_pinned && mask_pinned));
+  if (s != RSP_OK) return s;
+  rows_per_chunk = c->pipe_rows_cap >= rows_per_chunk ? rows_per_chunk : c->pipe_rows_cap;
+  rsp_dets dets = {nullptr, nullptr, 0};
+  if (h_dets && max_dets) {
+    if (c->det_cap < max_dets) {
+      CUDA_TRY(cudaDeviceSynchronize());
+      cudaFree(c->d_det_list); c->d_det_list = nullptr; c->det_cap = 0;
+      CUDA_TRY(cudaMalloc((void **)&c->d_det_list, (size_t)max_dets * sizeof(rsp_detection)));
+      c->det_cap = max_dets;
+    }
+    if (!c->d_det_count) CUDA_TRY(cudaMalloc((void **)&c->d_det_count, sizeof(uint32_t)));
+    CUDA_TRY(cudaMemsetAsync(c->d_det_count, 0, sizeof(uint32_t), c->pipe_stream[0]));
+    CUDA_TRY(cudaStreamSynchronize(c->pipe_stream[0]));
+    dets.list = c->d_det_list; dets.count = c->d_det_count; dets.capacity = max_dets;
+  }
+  if (!h_out && !dets.list && !row_mask) return fail(RSP_EINVAL, "no output requested");
+  const unsigned char *src = static_cast<const unsigned char *>(h_in);
+  unsigned char *dst = static_cast<unsigned char *>(h_out);
+  unsigned char *mdst = reinterpret_cast<unsigned char *>(h_peak_mask);
+  struct Pending { size_t row0 = 0, n = 0; bool live = false; } pend[N_PIPE];
+  auto drain = [&](int slot) -> rsp_status {   // wait for the slot's chunk and unstage it
+    if (!pend[slot].live) return RSP_OK;
+    CUDA_TRY(cudaStreamSynchronize(c->pipe_stream[slot]));
+    if (!out_pinned && dst) std::memcpy(dst + pend[slot].row0 * row_out, c->stage_out[slot], pend[slot].n * row_out);
+    if (!mask_pinned && row_mask) std::memcpy(mdst + pend[slot].row0 * row_mask, c->stage_out[slot], pend[slot].n * row_mask);
+    pend[slot].live = false;
+    return RSP_OK;
+  };
+  size_t chunk = 0;
+  for (size_t row0 = 0; row0 < rows; row0 += rows_per_chunk, ++chunk) {
+    const int slot = (int)(chunk % N_PIPE);
+    const size_t n = std::min<size_t>(rows_per_chunk, rows - row0);
+    s = drain(slot);
+    if (s != RSP_OK) return s;
+    cudaStream_t st = c->pipe_stream[slot];
+    const void *hsrc = src + row0 * row_in;
+    if (!in_pinned) { std::memcpy(c->stage_in[slot], hsrc, n * row_in); hsrc = c->stage_in[slot]; }
+    CUDA_TRY(cudaMemcpyAsync(c->pipe_in[slot], hsrc, n * row_in, cudaMemcpyHostToDevice, st));
+    // detections carry the row index inside the call: the chunk's first row is passed as row_base
+    s = run_stages(c, STAGE_FFT, STAGE_CFAR, c->pipe_in[slot], (uint32_t)n, row_out ? c->pipe_out[slot] : nullptr,
+                   row_mask ? c->pipe_mask[slot] : nullptr, dets.list ? &dets : nullptr, st, (uint32_t)row0);
+    if (s != RSP_OK) return s;
+    if (row_out) {
+      void *hdst = out_pinned ? (void *)(dst + row0 * row_out) : c->stage_out[slot];
+      CUDA_TRY(cudaMemcpyAsync(hdst, c->pipe_out[slot], n * row_out, cudaMemcpyDeviceToHost, st));
+    }
+    if (row_mask) {
+      if (!mask_pinned && !out_pinned && row_out) {   // one staging buffer: finish the threshold copy first
+        CUDA_TRY(cudaStreamSynchronize(st));
+        std::memcpy(dst + row0 * row_out, c->stage_out[slot], n * row_out);
+      }
+      void *hdst = mask_pinned ? (void *)(mdst + row0 * row_mask) : c->stage_out[slot];
+      CUDA_TRY(cudaMemcpyAsync(hdst, c->pipe_mask[slot], n * row_mask, cudaMemcpyDeviceToHost, st));
+      if (!mask_pinned && !out_pinned && row_out) {
+        CUDA_TRY(cudaStreamSynchronize(st));
+        std::memcpy(mdst + row0 * row_mask, c->stage_out[slot], n * row_mask);
+        continue;   // already unstaged
+      }
+    }
+    pend[slot].row0 = row0; pend[slot].n = n; pend[slot].live = true;
+  }
+  for (int i = 0; i < N_PIPE; ++i) { s = drain(i); if (s != RSP_OK) return s; }
+  for (int i = 0; i < N_PIPE; ++i) CUDA_TRY(cudaStreamSynchronize(c->pipe_stream[i]));
+  if (dets.list) {
+    uint32_t cnt = 0;
+    CUDA_TRY(cudaMemcpy(&cnt, c->d_det_count, sizeof(uint32_t), cudaMemcpyDeviceToHost));
+    const uint32_t ncopy = std::min(cnt, max_dets);
+    if (ncopy) CUDA_TRY(cudaMemcpy(h_dets, c->d_det_list, (size_t)ncopy * sizeof(rsp_detection), cudaMemcpyDeviceToHost));
+    if (h_n_dets) *h_n_dets = cnt;
+  } else if (h_n_dets) *h_n_dets = 0;
+  return RSP_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// introspection
+extern "C" const char *rsp_status_str(rsp_status s) {
+  switch (s) {
+  case RSP_OK: return "RSP_OK";
+  case RSP_EINVAL: return "RSP_EINVAL";
+  case RSP_ECUDA: return "RSP_ECUDA";
+  case RSP_ENOMEM: return "RSP_ENOMEM";
+  case RSP_EUNSUPPORTED: return "RSP_EUNSUPPORTED";
+  default: return "RSP_?";
+  }
+}
+extern "C" const char *rsp_last_error(void) { return g_last_error.c_str(); }
+extern "C" int rsp_abi_version(void) { return RSP_ABI_VERSION; }
+extern "C" uint64_t rsp_kernel_launches(const rsp_chain *c) { return c ? c->launches : 0; }
+
+extern "C" const char *rsp_variant_name(rsp_chain *c) {
+  if (!c) return "";
+  std::string err;
+  Plan pl;
+  char buf[96];
+  if (c->p.arith == RSP_ARITH_FIXED) {
+    FxArgs a;
+    if (plan_fixed(c->p, c->r, c->t, STAGE_FFT, STAGE_CFAR, a, pl, err) != RSP_OK) { c->variant = "invalid: " + err; return c->variant.c_str(); }
+    const char *m = pl.mode == MODE_FAST ? "fast" : (pl.mode == MODE_FAST3 ? "fast3" : "generic");
+    if (fast_chain_supported(pl, a)) std::snprintf(buf, sizeof(buf), "chain_fixed_fast<%d>", pl.S);
+    else std::snprintf(buf, sizeof(buf), "chain_fixed<%d,%s>", pl.S, m);
+  } else {
+    F32Args a;
+    if (plan_f32(c->p, c->r, c->t, STAGE_FFT, STAGE_CFAR, a, pl, err) != RSP_OK) { c->variant = "invalid: " + err; return c->variant.c_str(); }
+    std::snprintf(buf, sizeof(buf), "chain_f32<%d>", pl.S);
+  }
+  c->variant = buf;
+  return c->variant.c_str();
+}
+
+extern "C" uint64_t rsp_bytes_per_chirp(rsp_chain *c) {
+  if (!c) return 0;
+  const int S = c->p.fft.runTime ? (int)c->r.fft[RSP_FFT_REG_FFTSIZE] : log2_ceil((uint32_t)c->p.fft.numPoints);
+  const uint64_t N = 1ull << S;
+  if (c->p.arith == RSP_ARITH_FIXED) return N * 8;        // Cat(re16, im16) in, Cat(threshold, bin, peak) out
+  return N * 8 + N * 4 + ((N + 31) / 32) * 4;             // float2 in, float threshold + 1 bit out
+}

@@ -41,6 +41,7 @@ struct FxArgs {
   const uint32_t *in;
   uint32_t *out;
   uint32_t n_rows;          // chirps in this launch
+  uint32_t row_base;        // index of row 0 inside the caller's batch (reported in detections)
   int first_stage, last_stage;
   // FFT
   int data_width, bp, tw_bp, trim, use4muls, bitrev, fft_dir;
@@ -448,7 +449,7 @@ RSP_HD void cfar_bin(const FxArgs &a, uint32_t row, int n, const uint32_t *bufM,
 #else
     const uint32_t slot = (*a.det_count)++;
 #endif
-    if (slot < a.det_cap) { Detection d; d.chirp = row; d.bin = (uint32_t)n; d.threshold = thr_out; d.cut = cut; a.det_list[slot] = d; }
+    if (slot < a.det_cap) { Detection d; d.chirp = a.row_base + row; d.bin = (uint32_t)n; d.threshold = thr_out; d.cut = cut; a.det_list[slot] = d; }
   }
 }
 

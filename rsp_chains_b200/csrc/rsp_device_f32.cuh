@@ -18,7 +18,7 @@ struct F32Args {
   float *out;            // thresholds (CFAR), magnitudes (MAG)
   F2 *out_c;             // FFT-only output
   uint32_t *peak_mask;   // 1 bit per bin, ceil(N/32) words per chirp (nullable)
-  uint32_t n_rows;
+  uint32_t n_rows, row_base;
   int first_stage, last_stage;
   int bitrev, fft_dir;
   const F2 *tw;
@@ -239,7 +239,7 @@ RSP_HD uint32_t cfar_thread_f32(const F32Args &a, uint32_t row, int tl, const fl
 #else
         const uint32_t slot = (*a.det_count)++;
 #endif
-        if (slot < a.det_cap) { Detection d; d.chirp = row; d.bin = (uint32_t)n; d.threshold = f32_bits(thr); d.cut = f32_bits(cut); a.det_list[slot] = d; }
+        if (slot < a.det_cap) { Detection d; d.chirp = a.row_base + row; d.bin = (uint32_t)n; d.threshold = f32_bits(thr); d.cut = f32_bits(cut); a.det_list[slot] = d; }
       }
     }
   }

@@ -1,0 +1,12 @@
+// rsp_fast.cuh -- specialised kernels for the chain configurations the benchmarks run (selected by fast_chain_supported).
+#pragma once
+#include <cuda_runtime.h>
+
+#include "../../include/rsp_chains.h"
+#include "rsp_host.hpp"
+#include "rsp_launch.hpp"
+
+namespace rsp {
+bool fast_chain_supported(const Plan &pl, const FxArgs &a);
+rsp_status launch_fast_chain(const Plan &pl, const LaunchCtx &ctx, const FxArgs &a, cudaStream_t st, const char **err);
+}  // namespace rsp

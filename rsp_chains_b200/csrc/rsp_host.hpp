@@ -12,6 +12,7 @@
 #include "../../include/rsp_chains.h"
 #include "rsp_device.cuh"
 #include "rsp_device_f32.cuh"
+#include "rsp_device_gen.cuh"
 
 namespace rsp {
 
@@ -345,85 +346,72 @@ inline rsp_status plan_f32(const rsp_chain_params &p, const Regs &r, const Table
 // ---- PLFG schedule -----------------------------------------------------------------------------------------------
 // The PLFG is a counter tree (frames > chirps > repeats > segments > samples, PLFGDspBlockMem.scala:242-345).  Inside a
 // segment the frequency word is an arithmetic progression and the NCO phase a quadratic in the sample index, so the host
-// flattens the registers + config RAM into a list of segments with their starting values and the device evaluates any
-// sample in closed form (modulo 2^outputWidth and 2^phaseWidth).
-struct GenSegment {
-  uint64_t start;     // index of the segment's first sample in the stream
-  uint32_t n;         // samples in the segment
-  int32_t f0;         // PLFG value of the first sample (raw, sign-extended)
-  int32_t step;       // per-sample increment (signed slope; 0 for pauses)
-  uint32_t phase0;    // NCO accumulator before the first sample of the segment
-  uint32_t flags;     // bit 0: every sample is f0 (reset segment / inter-frame pause)
+// flattens the registers + config RAM into the segments of ONE period (a frame plus the inter-frame pause) with the
+// accumulator value in front of each, and the device evaluates any sample in closed form (modulo 2^outputWidth and
+// 2^phaseWidth); later periods only shift the accumulator by a constant.
+struct GenPlan {
+  std::vector<GenSegment> segs;
+  uint64_t period_len = 0;     // samples of one frame + pause
+  uint64_t frame_len = 0;      // samples of one frame without the pause
+  uint32_t period_phase = 0;   // accumulator advance over one period (mod 2^phaseWidth)
+  uint64_t total = 0;          // samples the PLFG produces before it stops (~0 = forever)
 };
 
-inline rsp_status plan_generator(const rsp_chain_params &p, const Regs &r, uint64_t n_samples, std::vector<GenSegment> &segs, std::string &err) {
+inline rsp_status plan_generator(const rsp_chain_params &p, const Regs &r, GenPlan &gp, std::string &err) {
   const rsp_plfg_params &g = p.plfg;
   const int ow = g.outputWidthInt + g.outputWidthFrac, nsw = g.maxNumOfSamplesWidth, pw = p.nco.phaseWidth;
+  if (pw > ow) { err = "phaseWidth > PLFG output width is not built (closed-form accumulator needs phaseWidth <= outputWidth)"; return RSP_EUNSUPPORTED; }
   const uint32_t pmask = pw >= 32 ? 0xFFFFFFFFu : ((1u << pw) - 1u);
   const long long start = wrap_host((long long)r.plfg[RSP_PLFG_REG_STARTINGPOINT], ow);
   const uint32_t frame_num = r.plfg[RSP_PLFG_REG_FRAMENUM];
   const uint32_t inter = r.plfg[RSP_PLFG_REG_INTERFRAMENUMOFSAMPLES];
   const uint32_t ndiff = r.plfg[RSP_PLFG_REG_DIFFERENTCHIRPSNUM] < 1 ? 1 : r.plfg[RSP_PLFG_REG_DIFFERENTCHIRPSNUM];
   const uint32_t seg0 = RSP_PLFG_REG_SEGMENTNUMS0, rep0 = seg0 + g.maxChirpOrdinalNum, ord0 = rep0 + g.maxNumOfDifferentChirps;
-  segs.clear();
+  if (ndiff > (uint32_t)g.maxNumOfDifferentChirps) { err = "differentChirpsNum exceeds maxNumOfDifferentChirps"; return RSP_EINVAL; }
+  gp.segs.clear();
   uint64_t k = 0;
   long long cur = start;
   uint32_t phase = 0;
-  auto push = [&](uint32_t n, long long f0, long long step, bool constant) {
-    GenSegment s; s.start = k; s.n = n; s.f0 = (int32_t)f0; s.step = (int32_t)step; s.phase0 = phase; s.flags = constant ? 1u : 0u;
-    segs.push_back(s);
-    // advance: phase += sum_{m<n} (f0 + m*step) mod 2^pw; cur = value of the last sample
-    const unsigned long long nn = n;
-    const unsigned long long sum = (unsigned long long)(uint32_t)f0 * nn + (constant ? 0ULL : (unsigned long long)(long long)step * (nn * (nn - 1) / 2));
-    // per-sample truncation of the frequency word to phaseWidth bits commutes with the modular sum only if the PLFG value is
-    // reduced modulo 2^ow first; the device handles the 2^ow wrap exactly (see gen_sample), so do the same here sample-exact:
-    (void)sum;
-    k += n;
-  };
-  (void)push;
-  // sample-exact walk (segment lists are short; the per-sample work is on the device)
-  const bool forever = frame_num == 0;
-  for (uint32_t frame = 0; (forever || frame < frame_num) && k < n_samples; ++frame) {
-    for (uint32_t d = 0; d < ndiff && k < n_samples; ++d) {
-      const uint32_t chirp = r.plfg[ord0 + d];
-      const uint32_t reps = r.plfg[rep0 + d] < 1 ? 1 : r.plfg[rep0 + d];
-      if (chirp >= (uint32_t)g.maxChirpOrdinalNum) { err = "chirpOrdinalNums entry out of range"; return RSP_EINVAL; }
-      for (uint32_t rep = 0; rep < reps && k < n_samples; ++rep) {
-        const uint32_t nseg = r.plfg[seg0 + chirp] < 1 ? 1 : r.plfg[seg0 + chirp];
-        for (uint32_t sg = 0; sg < nseg && k < n_samples; ++sg) {
-          const uint64_t wd = r.plfg_ram[(size_t)chirp * g.maxNumOfSegments + sg];
-          const long long slope = wrap_host((long long)(wd & ((1ULL << ow) - 1)), ow);
-          uint32_t ns = (uint32_t)((wd >> ow) & ((1ULL << nsw) - 1));
-          if (!(ns > 1)) ns += 1;                                   // PLFGDspBlockMem.scala:175
-          const int sign = (int)((wd >> (ow + nsw)) & 1), reset = (int)((wd >> (ow + nsw + 1)) & 1);
-          const long long step = sign ? slope : -slope;
-          GenSegment s; s.start = k; s.n = ns; s.phase0 = phase; s.step = (int32_t)step;
-          if (reset) { s.f0 = (int32_t)start; s.flags = 1u; }
-          else if (sg == 0) { s.f0 = (int32_t)start; s.flags = 0u; }              // first sample of a chirp restarts at startingPoint
-          else { s.f0 = (int32_t)wrap_host(cur + step, ow); s.flags = 0u; }
-          segs.push_back(s);
-          // walk the segment to get the end state exactly as the hardware's wrapping registers do
-          for (uint32_t q = 0; q < ns; ++q) {
-            long long v;
-            if (s.flags & 1u) v = start;
-            else v = wrap_host((long long)s.f0 + (long long)q * step, ow);
-            cur = v;
-            phase = (phase + ((uint32_t)v & pmask)) & pmask;
-          }
-          k += ns;
+  for (uint32_t d = 0; d < ndiff; ++d) {
+    const uint32_t chirp = r.plfg[ord0 + d];
+    const uint32_t reps = r.plfg[rep0 + d] < 1 ? 1 : r.plfg[rep0 + d];   // (cnt + 1) >= n ends the repeat loop (:259)
+    if (chirp >= (uint32_t)g.maxChirpOrdinalNum) { err = "chirpOrdinalNums entry out of range"; return RSP_EINVAL; }
+    for (uint32_t rep = 0; rep < reps; ++rep) {
+      const uint32_t nseg = r.plfg[seg0 + chirp] < 1 ? 1 : r.plfg[seg0 + chirp];
+      if (nseg > (uint32_t)g.maxNumOfSegments) { err = "segmentNums entry exceeds maxNumOfSegments"; return RSP_EINVAL; }
+      for (uint32_t sg = 0; sg < nseg; ++sg) {
+        const uint64_t wd = r.plfg_ram[(size_t)chirp * g.maxNumOfSegments + sg];
+        const long long slope = wrap_host((long long)(wd & ((1ULL << ow) - 1)), ow);
+        uint32_t ns = (uint32_t)((wd >> ow) & ((1ULL << nsw) - 1));
+        if (!(ns > 1)) ns += 1;                                   // PLFGDspBlockMem.scala:175
+        const int sign = (int)((wd >> (ow + nsw)) & 1), reset = (int)((wd >> (ow + nsw + 1)) & 1);
+        const long long step = sign ? slope : -slope;
+        GenSegment s; s.pad_ = 0; s.start = k; s.n = ns; s.phase0 = phase; s.step = (int32_t)step;
+        if (reset) { s.f0 = (int32_t)start; s.flags = 1u; }
+        else if (sg == 0) { s.f0 = (int32_t)start; s.flags = 0u; }              // first sample of a chirp restarts at startingPoint
+        else { s.f0 = (int32_t)wrap_host(cur + step, ow); s.flags = 0u; }
+        gp.segs.push_back(s);
+        // walk the segment to get the end state exactly as the hardware's wrapping registers do
+        for (uint32_t q = 0; q < ns; ++q) {
+          const long long v = (s.flags & 1u) ? start : wrap_host((long long)s.f0 + (long long)q * step, ow);
+          cur = v;
+          phase = (phase + ((uint32_t)v & pmask)) & pmask;
         }
+        k += ns;
       }
     }
-    if ((forever || frame + 1 < frame_num) && inter > 0 && k < n_samples) {   // inter-frame pause emits startingPoint
-      GenSegment s; s.start = k; s.n = inter; s.f0 = (int32_t)start; s.step = 0; s.phase0 = phase; s.flags = 1u;
-      segs.push_back(s);
-      for (uint32_t q = 0; q < inter; ++q) phase = (phase + ((uint32_t)start & pmask)) & pmask;
-      cur = start;
-      k += inter;
-    }
-    if (segs.size() > (1u << 22)) { err = "PLFG schedule too long"; return RSP_EUNSUPPORTED; }
   }
-  if (k < n_samples) { err = "the PLFG schedule (frameNum frames) ends before n_samples; set frameNum = 0 to run forever"; return RSP_EINVAL; }
+  gp.frame_len = k;
+  if (inter > 0) {   // inter-frame pause emits startingPoint (plfg_script.py:50-53)
+    GenSegment s; s.pad_ = 0; s.start = k; s.n = inter; s.f0 = (int32_t)start; s.step = 0; s.phase0 = phase; s.flags = 1u;
+    gp.segs.push_back(s);
+    for (uint32_t q = 0; q < inter; ++q) phase = (phase + ((uint32_t)start & pmask)) & pmask;
+    k += inter;
+  }
+  gp.period_len = k;
+  gp.period_phase = phase;
+  // frameNum frames with a pause between them, none after the last; 0 = forever
+  gp.total = frame_num == 0 ? ~0ULL : (uint64_t)frame_num * gp.period_len - (uint64_t)inter;
   return RSP_OK;
 }
 

@@ -1,0 +1,174 @@
+"""Parity of the CUDA path (through the C ABI) against the CPU oracle, fixed-point chain.  Bit-exact."""
+import numpy as np
+import pytest
+
+import rsp_chains_b200 as R
+from rsp_chains_b200 import synth
+from rsp_chains_b200.params import (CACFARType, CFARParams, FFTParams, FftMagCfarVanillaParameters, FixedPoint,
+                                    GOSCACFARType, GOSCFARType, MAGParams)
+from tests.util import configure, decode_cfar_words, from_dev_u32, oracle_cfgs, to_dev
+
+pytestmark = pytest.mark.gpu
+
+
+def chain_params(n=1024, bp=0, trim="RoundHalfUp", cfar_type=CACFARType, cash=False, W=64, G=4, **fft_kw):
+    return FftMagCfarVanillaParameters(
+        fftParams=FFTParams.fixed(dataWidth=16, twiddleWidth=16, numPoints=n, useBitReverse=True, runTime=True, binPoint=bp,
+                                  trimType=trim, **fft_kw),
+        magParams=MAGParams.fixed(dataWidth=16, binPoint=bp, dataWidthLog=16, binPointLog=9, log2LookUpWidth=9),
+        cfarParams=CFARParams(protoIn=FixedPoint(16, bp), protoThreshold=FixedPoint(16, bp), protoScaler=FixedPoint(16, bp),
+                              leadLaggWindowSize=W, guardWindowSize=G, fftSize=n, includeCASH=cash,
+                              minSubWindowSize=4 if cash else None, CFARAlgorithm=cfar_type))
+
+
+def run_and_compare(cuda, oracle, params, log_n, sel, regs, beats):
+    n = 1 << log_n
+    rows = beats.shape[0]
+    with R.FftMagCfarChainVanilla(params) as ch:
+        configure(ch, log_n, sel, regs)
+        d_in = to_dev(cuda, beats)
+        d_out = cuda.empty((rows, n), dtype=cuda.int32, device="cuda")
+        ch.run(d_in, rows, 1, out=d_out)
+        cuda.cuda.synchronize()
+        got = from_dev_u32(d_out)
+        variant = ch.variant
+    fft, mag, cfar = oracle_cfgs(oracle, params, log_n, sel, regs)
+    want = oracle.chain_fixed_words(fft, mag, cfar, beats, n_threads=oracle.max_threads())
+    bad = np.argwhere(got != want)
+    assert bad.size == 0, f"{variant}: {bad.shape[0]} beats differ, first at {bad[0]}: got {got[tuple(bad[0])]:#x} want {want[tuple(bad[0])]:#x}"
+    return got
+
+
+def test_c2_frame_ca(cuda, oracle):
+    """BASELINE config 1: one frame 256 x 1024, fixed bp 0, JPL, CA-CFAR guard 4 ref 16"""
+    p = chain_params(1024, 0)
+    regs = dict(fftWin=1024, thresholdScaler=4, logOrLinearMode=1, divSum=4, peakGrouping=0, cfarMode=0, windowCells=16, guardCells=4)
+    beats = synth.chirps_fixed(256, 1024)
+    got = run_and_compare(cuda, oracle, p, 10, 2, regs, beats)
+    thr, bins, peak = decode_cfar_words(got, 1024)
+    assert (bins == np.arange(1024)[None, :]).all()
+    # the two synthetic targets of row 0 are detected
+    assert peak[0, 128] == 1 and peak[0, 256] == 1
+
+
+@pytest.mark.parametrize("log_n", [1, 2, 3, 4, 5, 6, 7, 8, 9, 10, 11, 12, 13, 14])
+def test_chain_all_sizes_random(cuda, oracle, log_n):
+    """every transform size, full-range random beats (all overflow corners), CA/GO/SO"""
+    n = 1 << log_n
+    W = max(1, min(16, n // 8))
+    G = 1
+    if not (n > 2 * W + 2 * G + 1):
+        pytest.skip("CFAR window does not fit this size")
+    p = chain_params(n, 0, W=max(2, W), G=max(1, G))
+    beats = synth.random_beats(37 if log_n < 13 else 5, n, seed=log_n)
+    for mode in (0, 1, 2):
+        regs = dict(fftWin=n, thresholdScaler=3, logOrLinearMode=1, divSum=max(0, W.bit_length() - 1), peakGrouping=mode & 1,
+                    cfarMode=mode, windowCells=W, guardCells=G)
+        run_and_compare(cuda, oracle, p, log_n, 2, regs, beats)
+
+
+@pytest.mark.parametrize("bp,trim,use4", [(12, "RoundHalfUp", False), (14, "RoundHalfUp", False), (12, "Convergent", False),
+                                           (12, "RoundHalfUp", True), (0, "Convergent", False), (12, "RoundDown", False)])
+def test_chain_binpoints_and_trims(cuda, oracle, bp, trim, use4):
+    p = chain_params(1024, bp, trim, use4Muls=use4)
+    regs = dict(fftWin=1024, thresholdScaler=int(3.5 * (1 << bp)), logOrLinearMode=1, divSum=5, cfarMode=1, windowCells=32, guardCells=4)
+    beats = np.concatenate([synth.chirps_fixed(24, 1024, seed=5), synth.random_beats(8, 1024, seed=6)])
+    for sel in (1, 2, 3):
+        run_and_compare(cuda, oracle, p, 10, sel, regs, beats)
+
+
+def test_runtime_size_smaller_than_numpoints(cuda, oracle):
+    p = chain_params(1024, 0)
+    for log_n in (6, 8):
+        n = 1 << log_n
+        regs = dict(fftWin=n, thresholdScaler=3, logOrLinearMode=1, divSum=2, cfarMode=0, windowCells=4, guardCells=2)
+        run_and_compare(cuda, oracle, p, log_n, 2, regs, synth.random_beats(19, n, seed=log_n, full_range=False))
+    with R.FftMagCfarChainVanilla(p) as ch:
+        ch.memWriteWord(p.fftAddress.base, 9)   # odd number of dropped stages: not a radix-2^2 size
+        ch.memWriteWord(p.cfarAddress.base, 512)
+        d = cuda.zeros((1, 512), dtype=cuda.int32, device="cuda")
+        with pytest.raises(R.RspError):
+            ch.run(d, 1, 1, out=d.clone())
+
+
+def test_log_mode_and_threshold_field(cuda, oracle):
+    p = chain_params(256, 0, W=16, G=2)
+    regs = dict(fftWin=256, thresholdScaler=40, logOrLinearMode=0, divSum=4, cfarMode=0, windowCells=16, guardCells=2)
+    run_and_compare(cuda, oracle, p, 8, 3, regs, synth.chirps_fixed(33, 256, seed=9))
+
+
+@pytest.mark.parametrize("ctype,cash", [(GOSCFARType, False), (GOSCACFARType, False), (CACFARType, True)])
+def test_cfar_cores(cuda, oracle, ctype, cash):
+    """Lis core (GOS, both algorithms of GOSCA) and ASR core (CASH) behind the same chain"""
+    p = chain_params(512, 0, cfar_type=ctype, cash=cash, W=32, G=4)
+    beats = synth.chirps_fixed(21, 512, seed=3)
+    for mode in (0, 1, 2, 3):
+        for alg in ((0, 1) if ctype == GOSCACFARType else (0,)):
+            regs = dict(fftWin=512, thresholdScaler=3, logOrLinearMode=1, divSum=4, peakGrouping=1, cfarAlgorithm=alg, cfarMode=mode,
+                        windowCells=16, guardCells=3, indexLagg=12, indexLead=5, subWindowSize=4)
+            run_and_compare(cuda, oracle, p, 9, 2, regs, beats)
+
+
+def test_os_cfar_c4(cuda, oracle):
+    """BASELINE config 3 reading (A): GOS, 64 cells per side, k = 48, 4096-point profiles"""
+    p = chain_params(4096, 0, cfar_type=GOSCFARType, W=64, G=4)
+    regs = dict(fftWin=4096, thresholdScaler=2, logOrLinearMode=1, peakGrouping=0, cfarMode=0, windowCells=64, guardCells=4,
+                indexLagg=48, indexLead=48)
+    run_and_compare(cuda, oracle, p, 12, 2, regs, synth.chirps_fixed(16, 4096, seed=4))
+
+
+def test_blocks_alone(cuda, oracle):
+    """AXI4FFTBlock, AXI4LogMagMuxBlock, AXI4CFARBlock used on their own equal the oracle's stages"""
+    p = chain_params(1024, 12)
+    regs = dict(fftWin=1024, thresholdScaler=int(3.5 * 4096), logOrLinearMode=1, divSum=5, cfarMode=0, windowCells=32, guardCells=4)
+    beats = synth.chirps_fixed(16, 1024, seed=8)
+    fft, mag, cfar = oracle_cfgs(oracle, p, 10, 2, regs)
+    want_out, want_fft, want_mag = oracle.chain_fixed_words(fft, mag, cfar, beats, want_stages=True)
+    with R.FftMagCfarChainVanilla(p) as ch:
+        configure(ch, 10, 2, regs)
+        d_in = to_dev(cuda, beats)
+        d_f = cuda.empty_like(d_in); d_m = cuda.empty_like(d_in); d_c = cuda.empty_like(d_in)
+        ch.fft(d_in, 16, d_f)
+        ch.mag(d_f, 16 * 1024, d_m)
+        ch.cfar(d_m, 16, out=d_c)
+        cuda.cuda.synchronize()
+        assert (from_dev_u32(d_f) == want_fft).all()
+        assert (from_dev_u32(d_m) == want_mag).all()
+        assert (from_dev_u32(d_c) == want_out).all()
+        assert ch.kernel_launches == 3
+
+
+def test_run_host_and_detections(cuda, oracle):
+    p = chain_params(1024, 0)
+    regs = dict(fftWin=1024, thresholdScaler=4, logOrLinearMode=1, divSum=4, cfarMode=0, windowCells=16, guardCells=4)
+    rows = 4500   # several pipeline chunks with a ragged tail
+    beats = np.tile(synth.chirps_fixed(250, 1024, seed=2), (18, 1))[:rows]
+    fft, mag, cfar = oracle_cfgs(oracle, p, 10, 2, regs)
+    want = oracle.chain_fixed_words(fft, mag, cfar, beats[:250], n_threads=oracle.max_threads())
+    with R.FftMagCfarChainVanilla(p) as ch:
+        configure(ch, 10, 2, regs)
+        out, _, dets, n_dets = ch.run_host(beats, rows, 1, max_dets=1 << 20)
+    assert (out[:250] == want).all()
+    assert (out[250 * 17:] == want[:rows - 250 * 17]).all()
+    _, bins, peak = decode_cfar_words(out, 1024)
+    assert n_dets == int(peak.sum()) == dets.shape[0]
+    got = set(map(tuple, dets[:, :2].tolist()))
+    exp = set(map(tuple, np.argwhere(peak == 1).tolist()))
+    assert got == exp
+
+
+def test_invalid_parameters_raise(cuda):
+    p = chain_params(1024, 0)
+    p.cfarParams.guardWindowSize = 0   # CFARParams.scala:41
+    with pytest.raises(R.RspError) as e:
+        R.FftMagCfarChainVanilla(p)
+    assert e.value.status == R._abi.RSP_EINVAL
+    p = chain_params(1024, 0)
+    with R.FftMagCfarChainVanilla(p) as ch:
+        ch.memWriteWord(p.cfarAddress.base, 1024)
+        ch.memWriteWord(p.cfarAddress.base + 7 * 4, 64)
+        ch.memWriteWord(p.cfarAddress.base + 8 * 4, 4)
+        ch.memWriteWord(p.fftAddress.base, 6)   # fftWin (1024) != transform size (64)
+        d = cuda.zeros((1, 64), dtype=cuda.int32, device="cuda")
+        with pytest.raises(R.RspError):
+            ch.run(d, 1, 1, out=d.clone())
