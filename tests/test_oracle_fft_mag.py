@@ -1,0 +1,207 @@
+"""Pins the oracle's fixed-point FFT and LogMagMux restatement with every criterion the reference's own tests apply:
+ - FixedPointSDFFFTTester.simpleTestFFT (generators/sdf-fft/src/test/scala/SDFFFTTester.scala:27-71): every output bin within
+   fixTolLSBs t of fourierTr(x) / 2^(#scaled stages), i.e. |raw error| <= 2^t - 1, on genRandSignal inputs (U[0,1) re/im,
+   TesterUtil.scala:141-147), over the Radix22RandomSpec grid (Radix22RandomSpec.scala:17-44: N = 2..1024, 16-bit Q2.14,
+   Convergent, scale every stage, t = 3)
+ - the published SQNR curve (generators/sdf-fft/doc/images/SQNRdataWidth.png, producer Radix22SQNRSpec.scala:40-173, metric
+   TesterUtil.scala:44-54)
+ - checkFFTError |delta| <= 4 (TesterUtil.scala:222-228) on the AXI-level tone test
+ - LogMagMuxSpec closed forms (generators/logMagMux/src/test/scala/LogMagMuxSpec.scala:21-31), t = 3 (JPL) / 7 (|z|^2)
+The bit-level results themselves are unpinned by the reference (it ships no vectors); see DESIGN.md."""
+import numpy as np
+import pytest
+
+
+def java_rand_signal(oracle, n, seed):
+    """genRandSignal: Complex(Random.nextDouble(), Random.nextDouble()) per sample, scala.util.Random = java.util.Random"""
+    r = oracle.JavaRandom(seed)
+    re, im = np.zeros(n), np.zeros(n)
+    for i in range(n):
+        re[i] = r.next_double()
+        im[i] = r.next_double()
+    return re, im
+
+
+def quantize(x, bp):   # dsptools poke of a Double into a FixedPoint port: round(x * 2^bp)
+    return np.floor(x * (1 << bp) + 0.5).astype(np.int64)
+
+
+@pytest.mark.parametrize("n", [2, 4, 8, 16, 32, 64, 128, 256, 512, 1024])
+@pytest.mark.parametrize("trim,tol", [("Convergent", 3), ("RoundHalfUp", 3)])
+def test_fft_radix22_random_spec_tolerance(oracle, n, trim, tol):
+    log_n = n.bit_length() - 1
+    cfg = oracle.fft_cfg(log_n, 16, 14, 16, trim, False, True, (1 << log_n) - 1, True)
+    for rep in range(2):                                  # numSamples = 2 (Radix22RandomSpec.scala:16)
+        re, im = java_rand_signal(oracle, n, 11110 + rep)
+        qr, qi = quantize(re, 14), quantize(im, 14)
+        ore, oim = oracle.fft_fixed(cfg, qr, qi)
+        want = np.fft.fft(re + 1j * im) / n * (1 << 14)    # out / scalingFactor, in raw LSB
+        err = max(np.abs(ore - want.real).max(), np.abs(oim - want.imag).max())
+        assert err <= (1 << tol) - 1, f"N={n} {trim}: max raw error {err:.2f} LSB"
+
+
+def sqnr_db(got, want):   # calc_sqnr, TesterUtil.scala:44-54 (sums of magnitudes, 20 log10)
+    return 20 * np.log10(np.abs(want).sum() / np.abs(got - want).sum())
+
+
+def test_fft_reproduces_published_sqnr_curve(oracle):
+    """16-bit, scale every stage: ~84 dB at N=2 falling ~linearly to ~50 dB at N=1024 (Convergent),
+    ~46.5 dB at N=1024 for RoundHalfUp (SQNRroundings.png).  Median over >= 8 random signals, +-2.5 dB."""
+    published = {2: 84, 4: 80, 8: 75, 16: 71, 32: 67, 64: 63.5, 128: 60, 256: 56.5, 512: 53, 1024: 50}
+    for n, want_db in published.items():
+        log_n = n.bit_length() - 1
+        cfg = oracle.fft_cfg(log_n, 16, 14, 16, "Convergent", False, True, (1 << log_n) - 1, True)
+        vals = []
+        for rep in range(max(8, 512 // n)):                 # tiny transforms have few error samples: average more of them
+            re, im = java_rand_signal(oracle, n, 100 + rep)
+            ore, oim = oracle.fft_fixed(cfg, quantize(re, 14), quantize(im, 14))
+            ref = np.fft.fft(re + 1j * im) / n
+            vals.append(sqnr_db((ore + 1j * oim) / (1 << 14), ref))
+        assert abs(np.median(vals) - want_db) < 2.5, f"N={n}: {np.median(vals):.1f} dB vs published ~{want_db}"
+    cfg = oracle.fft_cfg(10, 16, 14, 16, "RoundHalfUp", False, True, 1023, True)
+    vals = []
+    for rep in range(8):
+        re, im = java_rand_signal(oracle, 1024, 100 + rep)
+        ore, oim = oracle.fft_fixed(cfg, quantize(re, 14), quantize(im, 14))
+        vals.append(sqnr_db((ore + 1j * oim) / (1 << 14), np.fft.fft(re + 1j * im) / 1024))
+    assert abs(np.mean(vals) - 46.5) < 2.5
+
+
+@pytest.mark.parametrize("n", [64, 1024, 2048, 16384])
+def test_fft_bp0_tone_axi_level(oracle, n):
+    """integer beats (binPoint 0) as the chain apps use (src/main/scala/RspChain.scala:118): checkFFTError |delta| <= 4
+    against fft / N (TesterUtil.scala:222-228, FFTBlockWithWindowingSpec.scala:149)"""
+    log_n = n.bit_length() - 1
+    t = np.arange(n)
+    x = 0.4 * np.exp(2j * np.pi * (n // 8) * t / n) + 0.2 * np.exp(2j * np.pi * (n // 4) * t / n)
+    qr, qi = np.floor(x.real * 8192).astype(np.int64), np.floor(x.imag * 8192).astype(np.int64)
+    cfg = oracle.fft_cfg(log_n, 16, 0, 16, "RoundHalfUp", False, True, (1 << log_n) - 1, True)
+    ore, oim = oracle.fft_fixed(cfg, qr, qi)
+    want = np.fft.fft(qr + 1j * qi) / n
+    assert np.abs(ore - want.real).max() <= 4 and np.abs(oim - want.imag).max() <= 4
+    assert int(np.abs(ore + 1j * oim).argmax()) == n // 8
+    # packed-beat entry point agrees with the array entry point
+    words = oracle.fft_fixed_words(cfg, oracle.pack_iq(qr, qi))
+    r2, i2 = oracle.unpack_iq(words)
+    assert (r2 == ore).all() and (i2 == oim).all()
+
+
+def test_fft_fixed_matches_f64_flavour(oracle):
+    """the DspReal flavour of the same dataflow equals numpy fft / N to 1e-12; the fixed one stays within the tolerance of it"""
+    rng = np.random.default_rng(3)
+    for log_n in (1, 2, 3, 5, 8, 11):
+        n = 1 << log_n
+        re, im = rng.uniform(-1, 1, n), rng.uniform(-1, 1, n)
+        fr, fi = oracle.fft_f64(log_n, re, im)
+        ref = np.fft.fft(re + 1j * im) / n
+        assert np.abs(fr + 1j * fi - ref).max() < 1e-12
+        br, bi = oracle.fft_f64(log_n, re, im, bit_reverse=False)     # DIF order = bit-reversed bins
+        rev = np.array([int(format(i, f"0{log_n}b")[::-1], 2) for i in range(n)])
+        assert np.abs(br + 1j * bi - ref[rev]).max() < 1e-12
+
+
+def test_fft_runtime_size_is_last_k_stages(oracle):
+    """run-time size N' = 2^k equals a k-stage transform (SDFChainRadix22.scala:146-150,216-219): keep_msb_mask bits are those
+    of the LAST k physical stages, which the glue shifts down"""
+    rng = np.random.default_rng(5)
+    re, im = rng.integers(-8000, 8000, 256), rng.integers(-8000, 8000, 256)
+    full = oracle.fft_cfg(8, 16, 0, 16, "RoundHalfUp", False, True, 0xFF, True)
+    a = oracle.fft_fixed(full, re, im)
+    want = np.fft.fft(re + 1j * im) / 256
+    assert np.abs(a[0] - want.real).max() <= 4
+
+
+def test_fft_keep_lsb_and_ifft(oracle):
+    """keepMSBorLSB(i) = false keeps the LSBs (no scaling, wrap) (SDFChainRadix22.scala:487-493); ifft = swap re/im in and out
+    (:205-211,362-383)"""
+    rng = np.random.default_rng(6)
+    n, log_n = 64, 6
+    re, im = rng.integers(-100, 100, n), rng.integers(-100, 100, n)
+    cfg = oracle.fft_cfg(log_n, 16, 0, 16, "RoundHalfUp", False, True, 0, True)       # never scale: plain FFT while no overflow
+    ore, oim = oracle.fft_fixed(cfg, re, im)
+    want = np.fft.fft(re + 1j * im)
+    assert np.abs(ore - want.real).max() <= 6 and np.abs(oim - want.imag).max() <= 6   # 2 twiddle roundings, unscaled
+    inv = oracle.fft_cfg(log_n, 16, 0, 16, "RoundHalfUp", False, True, (1 << log_n) - 1, False)
+    br, bi = oracle.fft_fixed(inv, ore, oim)                                          # scaled by 1/N -> recovers the input
+    assert np.abs(br - re).max() <= 3 and np.abs(bi - im).max() <= 3
+
+
+def test_trim_modes(oracle):
+    """dsptools TrimType semantics on x / 2 (names of Radix22SQNRSpec.scala:184)"""
+    table = {  # value: (-3, -1, 1, 3) / 2 = (-1.5, -0.5, 0.5, 1.5)
+        "RoundHalfUp": (-1, 0, 1, 2), "RoundDown": (-2, -1, 0, 1), "Convergent": (-2, 0, 0, 2), "RoundUp": (-1, 0, 1, 2),
+        "RoundTowardsZero": (-1, 0, 0, 1), "RoundTowardsInfinity": (-2, -1, 1, 2), "RoundHalfDown": (-2, -1, 0, 1),
+        "RoundHalfTowardsZero": (-1, 0, 0, 1), "RoundHalfTowardsInfinity": (-2, -1, 1, 2), "RoundHalfToOdd": (-1, -1, 1, 1),
+    }
+    for mode, want in table.items():
+        assert tuple(oracle.trim(v, 1, mode) for v in (-3, -1, 1, 3)) == want, mode
+    assert oracle.trim(5, 2, "RoundHalfUp") == 1 and oracle.trim(6, 2, "RoundHalfUp") == 2 and oracle.trim(-6, 2, "RoundHalfUp") == -1
+    assert oracle.trim(7, 1, "NoTrim") == 7
+
+
+def test_twiddle_table(oracle):
+    """(cos, -sin)(2 pi t / stageN) in Q2.14 (SDFChainRadix22.scala:262-267)"""
+    re, im = oracle.twiddle_table(64, 16)
+    t = np.arange(48)
+    assert (re == np.floor(np.cos(2 * np.pi * t / 64) * 16384 + 0.5)).all()
+    assert (im == np.floor(-np.sin(2 * np.pi * t / 64) * 16384 + 0.5)).all()
+    assert re[0] == 16384 and im[16] == -16384
+
+
+# ------------------------------------------------------------------------------------------------- LogMagMux
+
+def test_mag_closed_forms_integer_inputs(oracle):
+    """LogMagMuxSpec.scala:47-66 ("binaryPoint set to zero"): 8-bit-range integers, JPL and |z|^2 exact for integers"""
+    r = oracle.JavaRandom(11110)
+    rng = np.random.default_rng(11110)
+    re = rng.integers(-128, 128, 200)
+    im = rng.integers(-128, 128, 200)
+    words = oracle.pack_iq(re, im)
+    for sel, tol in ((2, 3), (1, 7)):
+        cfg = oracle.mag_cfg(16, 0, 16, 11, 11, sel)
+        out = oracle.mag_words(cfg, words)
+        hi, lo = oracle.unpack_iq(out)
+        assert (hi == 0).all()                                # .real := 0 (LogMagMux.scala:147-163)
+        u, v = np.maximum(abs(re), abs(im)), np.minimum(abs(re), abs(im))
+        want = np.maximum(u + v / 8, 7 * u / 8 + v / 2) if sel == 2 else re * re + im * im
+        assert np.abs(lo - want).max() <= (1 << tol) - 1
+        if sel == 1:
+            assert (lo == want).all()                         # integer products are exact at binPoint 0
+    out = oracle.mag_words(oracle.mag_cfg(16, 0, 16, 11, 11, 0), words)     # bypass
+    assert (out == words).all()
+
+
+def test_mag_fractional_inputs_tolerance(oracle):
+    """LogMagMuxSpec.scala:21-31: inputs (U*2-1)*50 in Q(16,8)-like precision, tol t = 3 (JPL) / 7 (|z|^2)"""
+    rng = np.random.default_rng(1)
+    bp = 4                                                    # 16-bit, 4 fractional bits: +-50 and 2*50^2 = 5000 fit
+    re, im = (rng.uniform(-1, 1, 300) * 50), (rng.uniform(-1, 1, 300) * 50)
+    qr, qi = np.floor(re * 16 + 0.5).astype(np.int64), np.floor(im * 16 + 0.5).astype(np.int64)
+    rq, iq = qr / 16.0, qi / 16.0
+    for sel, tol in ((2, 3), (1, 7)):
+        out = oracle.mag_words(oracle.mag_cfg(16, bp, 16, 9, 9, sel), oracle.pack_iq(qr, qi))
+        _, lo = oracle.unpack_iq(out)
+        want = np.array([oracle.jpl_f64(a, b) for a, b in zip(rq, iq)]) if sel == 2 else (rq * rq + iq * iq) / 16.0 * 16.0
+        if sel == 1:
+            lo = lo.astype(np.int64) & 0xFFFF                 # 5000 * 16 = 80000 wraps the 16-bit output (the reference notes
+            want_raw = np.floor(want * 16).astype(np.int64) & 0xFFFF   # "scale to prevent overflow"); compare modulo 2^16
+            d = (lo - want_raw + 32768) % 65536 - 32768
+            assert np.abs(d).max() <= (1 << tol) - 1
+        else:
+            assert np.abs(lo - want * 16).max() <= (1 << tol) - 1
+
+
+def test_log2_lut_and_intended_math(oracle):
+    """sel 3: out = (floor(log2 jpl) - bp) << bpLog + LUT[fraction bits]  (LogMagMux.scala:115-143); vs log2(jpl) within
+    2^-L + LUT rounding.  The reference never checks log2 (LogMagMuxTester.scala:64-66): unpinned."""
+    tab = oracle.log2_table(9, 9)
+    n = np.arange(512)
+    assert (tab == np.floor(np.log2(1 + n / 512.0) * 512 + 0.5)).all()
+    rng = np.random.default_rng(2)
+    re, im = rng.integers(1, 20000, 500), rng.integers(-20000, 20000, 500)
+    out = oracle.mag_words(oracle.mag_cfg(16, 0, 16, 9, 9, 3), oracle.pack_iq(re, im))
+    _, lo = oracle.unpack_iq(out)
+    jpl = np.array([np.floor(oracle.jpl_f64(a, b) + 1e-9) for a, b in zip(re, im)])
+    u, v = np.maximum(abs(re), abs(im)), np.minimum(abs(re), abs(im))
+    jpl = np.maximum(u + (v >> 3), (u - (u >> 3)) + (v >> 1))
+    assert np.abs(lo / 512.0 - np.log2(jpl)).max() < 2.0 ** -8

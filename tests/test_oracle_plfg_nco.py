@@ -1,0 +1,126 @@
+"""Pins the oracle's PLFG / NCO restatement (oracle/rsp_oracle.c) against the reference's own known answers:
+ - the PLFG RAM words and expected ramps of generators/plfg/src/test/scala/PLFGSpec.scala:42-62
+ - outputs of the reference's Python golden PLFG() (tests/golden/plfg_golden.json, made by tests/golden/make_plfg_golden.py)
+ - the NCO acceptance criteria of generators/nco/src/test/scala/NCOTester.scala:43-140 (|err| vs sin/cos within tolLSB)
+ - calcExpectedNcoOut (src/test/scala/RspChainTesterUtils.scala:174-181)."""
+import json
+import os
+
+import numpy as np
+import pytest
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+def ramp(start, length, slope):           # PLFGTesterUtil.scala:17-28
+    return [start + i * slope for i in range(length)]
+
+
+def triangle(start, l1, l2, s1, s2):      # PLFGTesterUtil.scala:43-59
+    out, v = [], start
+    for i in range(l1):
+        out.append(v)
+        if i != l1 - 1:
+            v += s1
+    for _ in range(l2):
+        v -= s2
+        out.append(v)
+    return out
+
+
+def test_plfgspec_known_answer(oracle):
+    """PLFGSpec.scala:42-62: RAM words 0x1180002, 0x2060000, 0x120000A, 0x0140008 -> ramp ++ constant ++ triangle"""
+    p = oracle.Plfg(frame_num=1, interframe_num_of_samples=60, different_chirps_num=1, starting_point=0, segment_nums=[4],
+                    repeated_chirp_nums=[1], chirp_ordinal_nums=[0], ram=[0x1180002, 0x2060000, 0x120000A, 0x0140008])
+    got = p.run(24 + 6 + 52).tolist()
+    want = ramp(0, 24, 2) + [0] * 6 + triangle(10, 32, 20, 10, 8)
+    assert got == want
+
+
+def test_plfg_ram_word_layout(oracle):
+    """{reset, sign, nSamples[8], slope[16]} (PLFGDspBlockMem.scala:168-178) reproduces the spec's literals"""
+    assert oracle.plfg_ram_word(2, 24, True, False) == 0x1180002
+    assert oracle.plfg_ram_word(0, 6, False, True) == 0x2060000
+    assert oracle.plfg_ram_word(10, 32, True, False) == 0x120000A
+    assert oracle.plfg_ram_word(8, 20, False, False) == 0x0140008
+
+
+def _golden_cases():
+    with open(os.path.join(HERE, "golden", "plfg_golden.json")) as f:
+        return json.load(f)
+
+
+@pytest.mark.parametrize("case", _golden_cases(), ids=lambda c: c["name"])
+def test_plfg_matches_reference_python_golden(oracle, case):
+    """oracle PLFG == outputs of the reference's plfg_script.PLFG() (exact integers)"""
+    n_chirps = case["numOfChirps"]
+    ram = [0] * (4 * 4)
+    for c in range(n_chirps):
+        for s in range(case["numOfSegments"][c]):
+            slope = case["slopes"][c][s]
+            ram[c * 4 + s] = oracle.plfg_ram_word(abs(slope), case["numOfSamples"][c][s], slope >= 0, case["segmentResets"][c][s])
+    p = oracle.Plfg(max_num_of_segments=4, max_chirp_ordinal_num=4, frame_num=case["numOfFrames"],
+                    interframe_num_of_samples=case["interFrameNumOfSamples"], different_chirps_num=n_chirps,
+                    starting_point=case["startingPoint"] & 0xFFFF, segment_nums=case["numOfSegments"],
+                    repeated_chirp_nums=[1] * n_chirps, chirp_ordinal_nums=list(range(n_chirps)), ram=ram)
+    want = case["output"]
+    got = p.run(len(want) + 100)
+    assert got.tolist() == want        # and the PLFG stops after frameNum frames (no trailing pause)
+
+
+def test_plfg_bumps_short_segments_and_wraps(oracle):
+    """nSamples < 2 is bumped by one (PLFGDspBlockMem.scala:175); the value wraps at outputWidth bits"""
+    p = oracle.Plfg(frame_num=1, different_chirps_num=1, starting_point=32000, segment_nums=[2], repeated_chirp_nums=[1],
+                    chirp_ordinal_nums=[0], ram=[oracle.plfg_ram_word(500, 1, True, False), oracle.plfg_ram_word(500, 4, True, False)])
+    got = p.run(100).tolist()
+    assert len(got) == 2 + 4
+    assert got[:2] == [32000, 32500]
+    assert got[2] == 33000 - 65536     # wrapped to 16 bits
+
+
+def test_nco_table_entries(oracle):
+    """T[i] = round(sin(pi/2 * i / tableSize) * 2^(W-2)) (NCOTable.scala:254-258)"""
+    t = oracle.nco_table(128, 16)
+    i = np.arange(128)
+    want = np.floor(np.sin(i * 0.5 * np.pi / 128) * (1 << 14) + 0.5).astype(np.int64)
+    assert (t == want).all()
+    assert t[0] == 0 and t.max() < (1 << 14)
+
+
+@pytest.mark.parametrize("table_size,width,phase_width", [(128, 16, 9), (256, 16, 10), (512, 14, 11), (64, 12, 8)])
+def test_nco_against_sin_cos(oracle, table_size, width, phase_width):
+    """the reference's NCO acceptance: |out - sin/cos(2 pi phase / 2^pw)| within tolLSB raw LSB for every phase
+    (generators/nco/src/test/scala/NCOTester.scala:43-140; phaseWidth = addr bits + 2 -> no interpolation terms)"""
+    n = 1 << phase_width
+    freq = np.ones(n, np.int32)                        # phase walks 1, 2, ..., 2^pw (wraps to 0)
+    words, final = oracle.nco_words(freq, table_size, width, phase_width)
+    assert final == 0
+    re, im = oracle.unpack_iq(words)
+    ph = (np.arange(1, n + 1) % n) * 2.0 * np.pi / n
+    scale = 1 << (width - 2)
+    assert np.abs(im - np.sin(ph) * scale).max() <= 1.0    # rounding of the table entry only
+    assert np.abs(re - np.cos(ph) * scale).max() <= 1.0
+    # quadrant symmetries hold exactly
+    assert re[n - 1] == scale and im[n - 1] == 0         # phase 0: cos = exactly 1.0 (NCOTable.scala:201,262-263)
+    q = n // 4
+    assert im[q - 1] == scale and re[q - 1] == 0          # phase pi/2
+
+
+def test_nco_constant_frequency_gives_expected_bin(oracle):
+    """RspChainVanillaTester.scala:85: startingPoint f -> tone at bin f * N / (4 * tableSize); calcExpectedNcoOut
+    (RspChainTesterUtils.scala:174-181): sample n carries phase (n + 1) * f"""
+    f, n_pts, ts = 16, 1024, 128
+    words, _ = oracle.nco_words(np.full(n_pts, f, np.int32), ts, 16, 9)
+    re, im = oracle.unpack_iq(words)
+    spec = np.abs(np.fft.fft(re + 1j * im))
+    assert int(spec.argmax()) == f * n_pts // (4 * ts)
+    ph = 2.0 * np.pi * ((np.arange(n_pts) + 1) * f % 512) / 512
+    assert np.abs(re - np.cos(ph) * 16384).max() <= 1.0 and np.abs(im - np.sin(ph) * 16384).max() <= 1.0
+
+
+def test_java_random_known_answer(oracle):
+    """java.util.Random(11110L).nextDouble(): the LCG the reference's seeded signals come from.  First values of seed 0
+    are the published java.util.Random known answers (0.730967787376657, 0.24053641567148587)."""
+    r = oracle.JavaRandom(0)
+    assert abs(r.next_double() - 0.730967787376657) < 1e-15
+    assert abs(r.next_double() - 0.24053641567148587) < 1e-15
