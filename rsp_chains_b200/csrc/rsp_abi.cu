@@ -32,6 +32,7 @@ struct rsp_chain {
   Tables t;
   int device = 0, sm_count = 0;
   uint32_t *d_tw = nullptr;
+  int32_t *d_tw2 = nullptr;
   F2 *d_twf = nullptr;
   int32_t *d_log_tab = nullptr, *d_nco_tab = nullptr;
   GenSegment *d_segs = nullptr;
@@ -96,7 +97,7 @@ static rsp_status launch_fixed(rsp_chain *c, const Plan &pl, const FxArgs &a, cu
   if (a.n_rows == 0) return RSP_OK;
   const LaunchCtx ctx = {c->device, c->sm_count};
   const char *err = "";
-  const rsp_status s = fast_chain_supported(pl, a) ? launch_fast_chain(pl, ctx, a, st, &err)
+  const rsp_status s = (a.out && fast_chain_supported(pl, a)) ? launch_fast_chain(pl, ctx, a, st, &err)
                                                    : launch_fixed_inst(pl.mode, pl.S, ctx, a, st, &err);
   if (s != RSP_OK) return fail(s, err);
   ++c->launches;
@@ -156,7 +157,7 @@ extern "C" void rsp_chain_destroy(rsp_chain *c) {
   cudaSetDevice(c->device);
   free_pipe(c);
   for (int i = 0; i < N_PIPE; ++i) if (c->pipe_stream[i]) cudaStreamDestroy(c->pipe_stream[i]);
-  cudaFree(c->d_tw); cudaFree(c->d_twf); cudaFree(c->d_log_tab); cudaFree(c->d_nco_tab); cudaFree(c->d_segs);
+  cudaFree(c->d_tw); cudaFree(c->d_tw2); cudaFree(c->d_twf); cudaFree(c->d_log_tab); cudaFree(c->d_nco_tab); cudaFree(c->d_segs);
   cudaFree(c->d_gen_scratch); cudaFree(c->d_det_list); cudaFree(c->d_det_count);
   delete c;
 }
@@ -189,6 +190,7 @@ extern "C" rsp_status rsp_chain_create(const rsp_chain_params *params, int devic
   regs_reset(c->p, c->r);
   build_tables(c->p, c->t);
   rsp_status s = upload(c->t.tw, &c->d_tw);
+  if (s == RSP_OK) s = upload(c->t.tw2, &c->d_tw2);
   if (s == RSP_OK) s = upload(c->t.twf, &c->d_twf);
   if (s == RSP_OK) s = upload(c->t.log_tab, &c->d_log_tab);
   if (s == RSP_OK) s = upload(c->t.nco_tab, &c->d_nco_tab);
@@ -239,7 +241,7 @@ extern "C" rsp_status rsp_plfg_ram_write(rsp_chain *c, uint32_t idx, uint32_t va
 
 // ---------------------------------------------------------------------------------------------------------------------
 // planning glue
-static void bind_fixed(rsp_chain *c, FxArgs &a) { a.tw = c->d_tw; a.log_tab = c->d_log_tab; }
+static void bind_fixed(rsp_chain *c, FxArgs &a) { a.tw = c->d_tw; a.tw2 = c->d_tw2; a.log_tab = c->d_log_tab; }
 static void bind_f32(rsp_chain *c, F32Args &a) { a.tw = c->d_twf; }
 static void bind_dets(const rsp_dets *d, Detection **list, uint32_t **count, uint32_t *cap) {
   if (d && d->list && d->count) { *list = reinterpret_cast<Detection *>(d->list); *count = d->count; *cap = d->capacity; }

@@ -1,10 +1,361 @@
-// rsp_fast.cu -- specialised kernels for the chain configurations the benchmarks run.
+// rsp_fast.cu -- the specialised fused chain kernel for the configuration the reference's chain apps run and the benchmarks
+// time: 16-bit data and twiddles, binPoint 0, RoundHalfUp, scale at every stage, forward transform, natural-order output
+// (src/main/scala/RspChain.scala:107-121), JPL magnitude (sel = 2, src/test/scala/FftMagCfarChainTester.scala:84), CFARCoreWithMem
+// in CA / GO / SO mode with a linear or log threshold (generators/cfar/src/main/scala/CFARCoreWithMem.scala:102-189).
+// Anything else runs on the generic kernels of rsp_kernels.cuh; results are identical where both apply (tests/test_gpu_chain.py).
+//
+// Why a second kernel: the chain is integer-issue bound, not HBM bound (DESIGN.md "kernel"), so what counts is instructions per
+// sample.  Everything a register can hold at compile time is folded:
+//  * butterfly (generators/sdf-fft/src/main/scala/SDFFFTUtil.scala:51-61 + div2, SDFChainRadix22.scala:459-464):
+//      s = (a + c + 1) >> 1 exactly, and the scaled difference is d = wrap16(s - c) because (a - c + 1) >> 1 == ((a + c + 1) >> 1) - c
+//  * twiddle product (SDFChainRadix22.scala:298-308): the table holds (cos, sin) << 2, so
+//      (ar * cos4 - ai * sin4 + 2^15) >> 16   (32-bit wrap-around arithmetic)
+//    is exactly wrap16((ar*cos - ai*sin + 2^13) >> 14): rounding, trimBinary and the 16-bit store in one shift
+//  * the rows of a CTA stay in shared memory from their first global load to their last global store; the bit reversal is the
+//    scatter of the magnitudes; the CFAR window sums are differences of one prefix-sum array
+//  * global loads and stores are warp-contiguous 128-byte lines.
+#include <algorithm>
+
 #include "rsp_fast.cuh"
 
 namespace rsp {
-bool fast_chain_supported(const Plan &, const FxArgs &) { return false; }
-rsp_status launch_fast_chain(const Plan &, const LaunchCtx &, const FxArgs &, cudaStream_t, const char **err) {
-  *err = "no fast variant for this configuration";
-  return RSP_EUNSUPPORTED;
+
+// ---------------------------------------------------------------------------------------------------------------------
+struct FastArgs {
+  const uint32_t *in;
+  uint32_t *out;
+  uint32_t n_rows, row_base;
+  const int2 *tw;        // (cos << 2, sin << 2) with sin = -sin(2 pi t / stageN), per stageN three runs [W^2k | W^k | W^3k]
+  int tw_off[16];
+  int W, G, div_sum, scaler;
+  uint32_t thr_mask;     // (1 << thresholdWidth) - 1
+  int out_shift;         // log2(fftSize) + 1: position of the threshold field in the output beat
+  int thr_sext;          // 32 - thresholdWidth: sign extension of the threshold reported in a detection
+  Detection *det_list;
+  uint32_t *det_count;
+  uint32_t det_cap;
+};
+
+template <int S> struct FGeo {
+  static constexpr int N = 1 << S;
+  static constexpr int PTS = 16;
+  static constexpr int TPC = N / PTS;                        // threads per chirp
+  static constexpr int CPC = TPC >= 256 ? 1 : 256 / TPC;     // chirps per CTA
+  static constexpr int THREADS = TPC * CPC;
+  static constexpr int XB = N + 4 * (N >> 6);                // words of the exchange buffer: index f(p) = p + 4 * (p >> 6)
+  static constexpr int XM = N / 2;                           // words of the magnitude array (int16 per bin)
+  static constexpr int ROW = XB + XM;                        // words per chirp
+  static constexpr int NW = TPC / 32;                        // warps per chirp
+};
+
+__device__ __forceinline__ int fidx(int p) { return p + ((p >> 6) << 2); }
+// Sign extensions and shifts go through inline PTX on purpose: when the compiler can prove a value fits 16 bits it rewrites the
+// rounded average (a + c + 1) >> 1 into the overflow-free (a | c) - ((a ^ c) >> 1) form and narrows the arithmetic, which
+// costs about twice the instructions of the plain 32-bit IADD3 + SHF.
+__device__ __forceinline__ int sext16(int v) { int r; asm("prmt.b32 %0, %1, 0, 0x9910;" : "=r"(r) : "r"(v)); return r; }
+__device__ __forceinline__ int hi16s(uint32_t v) { int r; asm("prmt.b32 %0, %1, 0, 0xbb32;" : "=r"(r) : "r"(v)); return r; }
+__device__ __forceinline__ int sar(int v, int n) { int r; asm("shr.s32 %0, %1, %2;" : "=r"(r) : "r"(v), "r"(n)); return r; }
+__device__ __forceinline__ uint32_t pack2(int re, int im) { return __byte_perm((uint32_t)im, (uint32_t)re, 0x5410); }
+
+// scaled butterfly, RoundHalfUp; WRAP = false when the result is packed to 16 bits right away
+template <bool WRAP>
+__device__ __forceinline__ void fbf(int &ar, int &ai, int &cr, int &ci) {
+  const int sr = sar(ar + cr + 1, 1), si = sar(ai + ci + 1, 1);
+  const int dr = sr - cr, di = si - ci;
+  ar = sr; ai = si;
+  cr = WRAP ? sext16(dr) : dr;
+  ci = WRAP ? sext16(di) : di;
 }
+
+// x <- x * W, W = (cos, sin) as stored (already << 2); result rounded half up at bit 14 and wrapped to 16 bits
+__device__ __forceinline__ void fcmul(int &xr, int &xi, const int2 w) {
+  const int r = xr * w.x - xi * w.y + 0x8000;
+  const int i = xr * w.y + xi * w.x + 0x8000;
+  xr = sar(r, 16); xi = sar(i, 16);
+}
+
+// JPL magnitude approximation (generators/logMagMux/src/main/scala/LogMagMux.scala:92-110), stored to 16 bits by the caller
+__device__ __forceinline__ int fjpl(int re, int im) {
+  const int ar = abs(re), ai = abs(im);
+  const int u = max(ar, ai), v = min(ar, ai);
+  return max(u + (v >> 3), (u - (u >> 3)) + (v >> 1));
+}
+
+// One pass = m radix-2 stages in registers on 2^m points Dl apart (same decomposition as rsp_device.cuh, fx_pass_*).
+// Thread tl of the chirp works on the groups vt = g * TPC + tl, so a warp touches consecutive words in every pass.
+template <int S, int K>
+__device__ __forceinline__ void fast_pass(const FastArgs &a, int tl, const uint32_t *__restrict__ gin, uint32_t *xb, uint32_t *xm) {
+  using Gm = FGeo<S>;
+  constexpr int m = fx_pass_size(S, K), i0 = fx_pass_start(S, K), LDl = S - i0 - m, Dl = 1 << LDl;
+  constexpr int PTS = Gm::PTS, G = PTS >> m, R = 1 << m, TPC = Gm::TPC;
+  constexpr bool first = (K == 0), last = (K == fx_n_passes(S) - 1);
+  static_assert((i0 & 1) == 0, "passes start on even stages");
+  int mags[last ? PTS : 1];
+#pragma unroll
+  for (int g = 0; g < G; ++g) {
+    const int vt = g * TPC + tl;
+    const int low = vt & (Dl - 1), high = vt >> LDl;
+    const int base = (high << (m + LDl)) | low;
+    int re[R], im[R];
+    if (last && m == 2) {   // 4 consecutive points: one 128-bit load
+      const uint4 v = *reinterpret_cast<const uint4 *>(&xb[fidx(base)]);
+      const uint32_t wd[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+      for (int rr = 0; rr < R; ++rr) { re[rr] = hi16s(wd[rr & 3]); im[rr] = sext16((int)wd[rr & 3]); }
+    } else {
+#pragma unroll
+      for (int rr = 0; rr < R; ++rr) {
+        const int p = base + rr * Dl;
+        const uint32_t wd = first ? __ldg(&gin[p]) : xb[fidx(p)];
+        re[rr] = hi16s(wd); im[rr] = sext16((int)wd);
+      }
+    }
+#pragma unroll
+    for (int s = 0; s < m; ++s) {
+      const int i = i0 + s;
+      const int dist = 1 << (m - 1 - s);
+      // the differences of the last stage of an inner pass need no wrap when they are packed to 16 bits right away (even
+      // stage: at most the -j swap follows); after an odd stage they feed the twiddle product and must be wrapped first
+      const bool wrap = last || (s != m - 1) || (i & 1);
+#pragma unroll
+      for (int rr = 0; rr < R; ++rr)
+        if (!(rr & dist)) {
+          if (wrap) fbf<true>(re[rr], im[rr], re[rr + dist], im[rr + dist]);
+          else fbf<false>(re[rr], im[rr], re[rr + dist], im[rr + dist]);
+        }
+      if (i == S - 1) continue;
+      if ((i & 1) == 0) {   // x (-j) on the last quarter of each 4D block (SDFChainRadix22.scala:319-337)
+#pragma unroll
+        for (int rr = 0; rr < R; ++rr)
+          if ((rr & dist) && (rr & (dist >> 1))) { const int t = re[rr]; re[rr] = im[rr]; im[rr] = wrap ? sext16(-t) : -t; }
+      } else {
+        const int L = S - i + 1;
+        const int q = 1 << (L - 2);
+        const int2 *tab = a.tw + a.tw_off[L];
+#pragma unroll
+        for (int rr = 0; rr < R; ++rr) {
+          const int quarter = ((rr >> (m - 1 - s)) & 1) + 2 * ((rr >> (m - s)) & 1);
+          if (quarter) {
+            const int k = (rr & (dist - 1)) * Dl + low;
+            const int slot = quarter == 1 ? 0 : (quarter == 2 ? 1 : 2);
+            fcmul(re[rr], im[rr], __ldg(&tab[slot * q + k]));
+          }
+        }
+      }
+    }
+    if (!last) {
+#pragma unroll
+      for (int rr = 0; rr < R; ++rr) xb[fidx(base + rr * Dl)] = pack2(re[rr], im[rr]);
+    } else {
+#pragma unroll
+      for (int rr = 0; rr < R; ++rr) mags[g * R + rr] = fjpl(re[rr], im[rr]);
+    }
+  }
+  if (last) {
+    // bin of point p = (vt << m) + rr is bitrev_S(p) = rev_m(rr) << (S - m) | rev_{S-4}(tl) << (4 - m) | rev_{4-m}(g):
+    // for a fixed rr the G groups of the thread are G consecutive bins -> one G * 16-bit store per rr
+    const uint32_t rtl = (__brev((uint32_t)tl) >> (32 - (S - 4))) << (4 - m);
+    uint16_t *xm16 = reinterpret_cast<uint16_t *>(xm);
+#pragma unroll
+    for (int rr = 0; rr < R; ++rr) {
+      const uint32_t rrr = (__brev((uint32_t)rr) >> (32 - m)) << (S - m);   // compile-time
+      const uint32_t bin0 = rrr | rtl;
+      if (G == 4) {   // groups in bin order: rev2(g) = 0,1,2,3 <- g = 0,2,1,3
+        uint2 v;
+        v.x = __byte_perm((uint32_t)mags[0 * R + rr], (uint32_t)mags[2 * R + rr], 0x5410);
+        v.y = __byte_perm((uint32_t)mags[1 * R + rr], (uint32_t)mags[3 * R + rr], 0x5410);
+        *reinterpret_cast<uint2 *>(&xm16[bin0]) = v;
+      } else if (G == 2) {
+        *reinterpret_cast<uint32_t *>(&xm16[bin0]) = __byte_perm((uint32_t)mags[0 * R + rr], (uint32_t)mags[1 * R + rr], 0x5410);
+      } else {
+        xm16[bin0] = (uint16_t)mags[rr];
+      }
+    }
+  }
+}
+
+template <int S, int K>
+__device__ __forceinline__ void fast_passes(const FastArgs &a, bool active, int tl, const uint32_t *gin, uint32_t *xb, uint32_t *xm) {
+  if (active) fast_pass<S, K>(a, tl, gin, xb, xm);
+  __syncthreads();
+  if constexpr (K + 1 < fx_n_passes(S)) fast_passes<S, K + 1>(a, active, tl, gin, xb, xm);
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// CFAR (CFARCoreWithMem.scala:102-189).  P[n] = sum of x[0..n-1] lives in the exchange buffer (dead after the last FFT pass);
+// lagging sum of bin n = P[n+G+W+1] - P[n+G+1], leading sum = P[n-G] - P[n-G-W].
+
+// exclusive prefix of `total` over the TPC threads of one chirp: warp shuffles, then one shared-memory hop across the warps
+template <int S>
+__device__ __forceinline__ int chirp_scan_exclusive(int total, int c, int tl, int *wsum) {
+  constexpr int NW = FGeo<S>::NW;
+  const int lane = tl & 31;
+  int incl = total;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const int v = __shfl_up_sync(0xffffffffu, incl, d);
+    if (lane >= d) incl += v;
+  }
+  int offset = 0;
+  if (NW > 1) {
+    const int w = tl >> 5;
+    if (lane == 31) wsum[c * NW + w] = incl;
+    __syncthreads();
+#pragma unroll
+    for (int h = 0; h < NW - 1; ++h) offset += (h < w) ? wsum[c * NW + h] : 0;
+  }
+  return offset + incl - total;
+}
+
+// threshold, peak and output beat of bin n = tl + j * TPC.  EDGE: the bin may miss one of its windows (one-sided threshold,
+// CFARCoreWithMem.scala:154-171); indices are clamped so no load leaves the chirp's arrays.
+template <int S, int CMODE, bool LINEAR, bool EDGE>
+__device__ __forceinline__ void fast_cfar_bin(const FastArgs &a, uint32_t row, int n, const int *P, const short *X, uint32_t *gout) {
+  constexpr int N = 1 << S;
+  const int W = a.W, G = a.G;
+  int L, R;
+  bool lagg_full = true, lead_full = true;
+  if (EDGE) {
+    lagg_full = (n + G + W <= N - 1); lead_full = (n - G - W >= 0);
+    const int hi = min(n + G + W + 1, N), lo = max(n - G - W, 0);
+    L = (P[hi] - P[hi - W]) >> a.div_sum;
+    R = (P[lo + W] - P[lo]) >> a.div_sum;
+  } else {
+    L = (P[n + G + W + 1] - P[n + G + 1]) >> a.div_sum;
+    R = (P[n - G] - P[n - G - W]) >> a.div_sum;
+  }
+  int t = CMODE == 0 ? ((R + L) >> 1) : (CMODE == 1 ? max(L, R) : min(L, R));
+  if (EDGE) t = lead_full ? (lagg_full ? t : R) : L;
+  const int thr = LINEAR ? t * a.scaler : t + a.scaler;
+  const int cut = X[n];
+  const bool pk = cut > thr;
+  gout[n] = (((uint32_t)thr & a.thr_mask) << a.out_shift) | ((uint32_t)n << 1) | (pk ? 1u : 0u);
+  if (pk && a.det_list) {
+    const uint32_t slot = atomicAdd(a.det_count, 1u);
+    if (slot < a.det_cap) { Detection d; d.chirp = a.row_base + row; d.bin = (uint32_t)n; d.threshold = (int)((uint32_t)thr << a.thr_sext) >> a.thr_sext; d.cut = cut; a.det_list[slot] = d; }
+  }
+}
+
+// EJ = number of leading / trailing iterations j whose bins may miss a window (ceil((W + G) / TPC), checked by the host)
+template <int S, int CMODE, bool LINEAR, int EJ>
+__global__ void __launch_bounds__(FGeo<S>::THREADS) chain_fixed_fast_kernel(const FastArgs a) {
+  using Gm = FGeo<S>;
+  constexpr int N = Gm::N, TPC = Gm::TPC, CPC = Gm::CPC, PTS = Gm::PTS;
+  extern __shared__ __align__(16) uint32_t smem[];
+  __shared__ int wsum[CPC * Gm::NW];
+  const int c = threadIdx.x / TPC, tl = threadIdx.x % TPC;
+  uint32_t *xb = smem + (size_t)c * Gm::ROW, *xm = xb + Gm::XB;
+  int *P = reinterpret_cast<int *>(xb);
+  const short *X = reinterpret_cast<const short *>(xm);
+  for (uint32_t row0 = blockIdx.x * CPC; row0 < a.n_rows; row0 += gridDim.x * CPC) {
+    const uint32_t row = row0 + c;
+    const bool active = row < a.n_rows;
+    fast_passes<S, 0>(a, active, tl, a.in + (size_t)row * N, xb, xm);
+    // prefix sums of the thread's 16 consecutive magnitudes
+    int x[PTS];
+    {
+      const uint4 v0 = *reinterpret_cast<const uint4 *>(&xm[tl * 8]), v1 = *reinterpret_cast<const uint4 *>(&xm[tl * 8 + 4]);
+      const uint32_t wd[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
+#pragma unroll
+      for (int k = 0; k < 8; ++k) { x[2 * k] = sext16((int)wd[k]); x[2 * k + 1] = hi16s(wd[k]); }
+    }
+    int total = 0;
+#pragma unroll
+    for (int k = 0; k < PTS; ++k) total += x[k];
+    int acc = chirp_scan_exclusive<S>(total, c, tl, wsum);
+    {
+      int pv[PTS];
+#pragma unroll
+      for (int k = 0; k < PTS; ++k) { pv[k] = acc; acc += x[k]; }
+#pragma unroll
+      for (int k = 0; k < PTS; k += 4) *reinterpret_cast<int4 *>(&P[tl * PTS + k]) = make_int4(pv[k], pv[k + 1], pv[k + 2], pv[k + 3]);
+      if (tl == TPC - 1) P[N] = acc;
+    }
+    __syncthreads();
+    if (active) {
+      uint32_t *gout = a.out + (size_t)row * N;
+#pragma unroll
+      for (int j = 0; j < PTS; ++j) {
+        const int n = tl + j * TPC;
+        if (j < EJ || j >= PTS - EJ) fast_cfar_bin<S, CMODE, LINEAR, true>(a, row, n, P, X, gout);
+        else fast_cfar_bin<S, CMODE, LINEAR, false>(a, row, n, P, X, gout);
+      }
+    }
+    __syncthreads();
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// host side
+static int fast_edge_iters(int S, int W, int G) { const int tpc = (1 << S) / 16; return (W + G + tpc - 1) / tpc; }
+
+bool fast_chain_supported(const Plan &pl, const FxArgs &a) {
+  if (pl.mode != MODE_FAST || pl.first_stage != STAGE_FFT || pl.last_stage != STAGE_CFAR) return false;
+  if (pl.S < RSP_FAST_SMIN || pl.S > RSP_FAST_SMAX) return false;
+  if (a.bp != 0 || a.tw_bp != 14 || !a.bitrev || a.sel != 2 || a.mag_w != 16 || a.mag_bp != 0) return false;
+  if (a.core != CORE_MEM || a.in_w != 16 || a.in_bp != 0 || a.sc_bp != 0 || a.thr_bp != 0 || a.send_cut || a.peak_grouping) return false;
+  if (a.thr_w < 1 || a.thr_w > 32 || a.G < 1 || a.W < 1 || a.div_sum < 0 || a.div_sum > 30) return false;
+  const int ej = fast_edge_iters(pl.S, a.W, a.G);
+  if (ej > (pl.S == 10 ? 2 : 1)) return false;
+  // the window sums must fit the reference's sum register (no wrap to reproduce) and the scaled threshold must fit 32 bits
+  const long long smax = (long long)a.W * 32768;
+  if (smax > (1LL << (a.sumw - 1))) return false;
+  const long long tmax = (smax >> a.div_sum) + 1, sc = a.scaler < 0 ? -(long long)a.scaler : a.scaler;
+  if (a.log_or_linear ? (tmax * sc >= (1LL << 31)) : (tmax + sc >= (1LL << 31))) return false;
+  return true;
+}
+
+template <int S, int CMODE, bool LINEAR, int EJ>
+static rsp_status launch_fast_inst(const LaunchCtx &c, const FastArgs &fa, cudaStream_t st, const char **err) {
+  using Gm = FGeo<S>;
+  static int occ_dev[64] = {0};
+  int &occ = occ_dev[c.device & 63];
+  const size_t smem = (size_t)Gm::CPC * Gm::ROW * sizeof(uint32_t);
+  auto kernel = chain_fixed_fast_kernel<S, CMODE, LINEAR, EJ>;
+  if (!occ) { const rsp_status s = launch_cfg(kernel, smem, Gm::THREADS, &occ, err); if (s != RSP_OK) return s; }
+  const unsigned groups = (fa.n_rows + Gm::CPC - 1) / Gm::CPC;
+  const unsigned grid = std::max(1u, std::min(groups, (unsigned)(c.sm_count * occ)));
+  kernel<<<grid, Gm::THREADS, smem, st>>>(fa);
+  if (cudaGetLastError() != cudaSuccess) { *err = "chain_fixed_fast_kernel launch failed"; return RSP_ECUDA; }
+  return RSP_OK;
+}
+
+template <int S, int EJ>
+static rsp_status launch_fast_modes(int cmode, bool linear, const LaunchCtx &c, const FastArgs &fa, cudaStream_t st, const char **err) {
+  if (linear) switch (cmode) {
+    case 0: return launch_fast_inst<S, 0, true, EJ>(c, fa, st, err);
+    case 1: return launch_fast_inst<S, 1, true, EJ>(c, fa, st, err);
+    default: return launch_fast_inst<S, 2, true, EJ>(c, fa, st, err);
+  }
+  switch (cmode) {
+    case 0: return launch_fast_inst<S, 0, false, EJ>(c, fa, st, err);
+    case 1: return launch_fast_inst<S, 1, false, EJ>(c, fa, st, err);
+    default: return launch_fast_inst<S, 2, false, EJ>(c, fa, st, err);
+  }
+}
+
+rsp_status launch_fast_chain(const Plan &pl, const LaunchCtx &ctx, const FxArgs &a, cudaStream_t st, const char **err) {
+  FastArgs fa;
+  fa.in = a.in; fa.out = a.out; fa.n_rows = a.n_rows; fa.row_base = a.row_base;
+  fa.tw = reinterpret_cast<const int2 *>(a.tw2);
+  for (int L = 0; L < 16; ++L) fa.tw_off[L] = a.tw_off[L];
+  fa.W = a.W; fa.G = a.G; fa.div_sum = a.div_sum; fa.scaler = a.scaler;
+  fa.thr_mask = a.thr_w >= 32 ? 0xFFFFFFFFu : ((1u << a.thr_w) - 1u);
+  fa.out_shift = a.binw + 1; fa.thr_sext = 32 - a.thr_w;
+  fa.det_list = a.det_list; fa.det_count = a.det_count; fa.det_cap = a.det_cap;
+  const int cmode = a.cfar_mode == 0 ? 0 : (a.cfar_mode == 1 ? 1 : 2);   // MuxLookup default: smallestOf (CFARCoreWithMem.scala:138-141)
+  const bool linear = a.log_or_linear != 0;
+  const int ej = fast_edge_iters(pl.S, a.W, a.G);
+  switch (pl.S) {
+  case 10: return ej == 2 ? launch_fast_modes<10, 2>(cmode, linear, ctx, fa, st, err) : launch_fast_modes<10, 1>(cmode, linear, ctx, fa, st, err);
+#if RSP_FAST_SMAX > 10
+  case 11: return launch_fast_modes<11, 1>(cmode, linear, ctx, fa, st, err);
+  case 12: return launch_fast_modes<12, 1>(cmode, linear, ctx, fa, st, err);
+  case 13: return launch_fast_modes<13, 1>(cmode, linear, ctx, fa, st, err);
+  case 14: return launch_fast_modes<14, 1>(cmode, linear, ctx, fa, st, err);
+#endif
+  default: *err = "no fast variant for this size"; return RSP_EUNSUPPORTED;
+  }
+}
+
 }  // namespace rsp

@@ -6,6 +6,13 @@
 #include "rsp_host.hpp"
 #include "rsp_launch.hpp"
 
+#ifndef RSP_FAST_SMIN
+#define RSP_FAST_SMIN 10
+#endif
+#ifndef RSP_FAST_SMAX
+#define RSP_FAST_SMAX 10
+#endif
+
 namespace rsp {
 bool fast_chain_supported(const Plan &pl, const FxArgs &a);
 rsp_status launch_fast_chain(const Plan &pl, const LaunchCtx &ctx, const FxArgs &a, cudaStream_t st, const char **err);

@@ -34,6 +34,8 @@ struct Regs {
 struct Tables {
   std::vector<uint32_t> tw;   // fixed twiddles, packed (cos16 << 16 | sin16 & 0xFFFF); per stageN three runs [W^2k | W^k | W^3k]
   std::vector<F2> twf;        // fp32 twiddles, same layout
+  std::vector<int32_t> tw2;   // fixed twiddles again as int32 pairs (cos << s, sin << s), s = 16 - (twiddleWidth - 2): the fast
+                              // kernels' product then carries its rounded, wrapped result in bits 16..31 (rsp_fast.cu)
   int tw_off[16];
   std::vector<int32_t> log_tab;
   std::vector<int32_t> nco_tab;
@@ -188,7 +190,8 @@ inline uint32_t *reg_slot(Regs &r, rsp_block blk, uint32_t idx) {
 inline void build_tables(const rsp_chain_params &p, Tables &t) {
   const int Smax = log2_ceil((uint32_t)p.fft.numPoints);
   const int tww = p.fft.twiddleWidth, twbp = tww - 2;
-  t.tw.clear(); t.twf.clear();
+  t.tw.clear(); t.twf.clear(); t.tw2.clear();
+  const int pre = 16 - twbp > 0 ? 16 - twbp : 0;
   for (int L = 0; L < 16; ++L) t.tw_off[L] = 0;
   const double PI = 3.14159265358979323846;  // scala.math.Pi
   for (int L = 3; L <= Smax; ++L) {
@@ -202,11 +205,12 @@ inline void build_tables(const rsp_chain_params &p, Tables &t) {
         const double c = std::cos(ang), s = -std::sin(ang);
         const long long re = wrap_host(from_double(c, twbp), tww), im = wrap_host(from_double(s, twbp), tww);
         t.tw.push_back(pack_iq((int)re, (int)im));
+        t.tw2.push_back((int32_t)(re * (1LL << pre))); t.tw2.push_back((int32_t)(im * (1LL << pre)));
         F2 f; f.x = (float)c; f.y = (float)s;
         t.twf.push_back(f);
       }
   }
-  if (t.tw.empty()) { t.tw.push_back(0); F2 f; f.x = 1.f; f.y = 0.f; t.twf.push_back(f); }
+  if (t.tw.empty()) { t.tw.push_back(0); t.tw2.push_back(0); t.tw2.push_back(0); F2 f; f.x = 1.f; f.y = 0.f; t.twf.push_back(f); }
   // log2 LUT (LogMagMux.scala:120-131)
   const int Lw = p.mag.log2LookUpWidth, num = 1 << Lw;
   t.log_tab.resize((size_t)num);
