@@ -48,7 +48,7 @@ struct FxArgs {
   uint32_t keep_mask;       // bit i: stage i of THIS transform scales (1) or keeps LSBs (0)
   const uint32_t *tw;       // packed (cos16 << 16 | sin16) twiddles, per stageN three runs [W^2k | W^k | W^3k]
   int tw_off[16];           // word offset of the table of stageN = 1 << L
-  const int32_t *tw2;       // same entries as (cos << s, sin << s) int32 pairs, s = 16 - tw_bp (fast kernels, rsp_fast.cu)
+  const int32_t *tw2;       // same entries as int32 quads (c, s, -c, -s) << (16 - tw_bp) (fast kernels, rsp_fast.cu)
   // LogMagMux
   int sel, mag_w, mag_bp, log_w, log_bp, log_L, mag_trim;
   const int32_t *log_tab;

@@ -7,7 +7,8 @@
 // Why a second kernel: the chain is integer-issue bound, not HBM bound (DESIGN.md "kernel"), so what counts is instructions per
 // sample.  Everything a register can hold at compile time is folded:
 //  * butterfly (generators/sdf-fft/src/main/scala/SDFFFTUtil.scala:51-61 + div2, SDFChainRadix22.scala:459-464):
-//      s = (a + c + 1) >> 1 exactly, and the scaled difference is d = wrap16(s - c) because (a - c + 1) >> 1 == ((a + c + 1) >> 1) - c
+//      -s = (-a - c) >> 1 exactly, and the scaled difference is d = wrap16(s - c) because (a - c + 1) >> 1 == ((a + c + 1) >> 1) - c;
+//      values are held with compile-time signs so that every add is a single IMAD on the otherwise idle FMA pipe
 //  * twiddle product (SDFChainRadix22.scala:298-308): the table holds (cos, sin) << 2, so
 //      (ar * cos4 - ai * sin4 + 2^15) >> 16   (32-bit wrap-around arithmetic)
 //    is exactly wrap16((ar*cos - ai*sin + 2^13) >> 14): rounding, trimBinary and the 16-bit store in one shift
@@ -25,9 +26,10 @@ struct FastArgs {
   const uint32_t *in;
   uint32_t *out;
   uint32_t n_rows, row_base;
-  const int2 *tw;        // (cos << 2, sin << 2) with sin = -sin(2 pi t / stageN), per stageN three runs [W^2k | W^k | W^3k]
+  const int4 *tw;        // (c, s, -c, -s) with c = cos << 2, s = -sin(2 pi t / stageN) << 2; per stageN three runs [W^2k | W^k | W^3k]
   int tw_off[16];
   int W, G, div_sum, scaler;
+  int one, m1;           // +1 and -1 as run-time values: multipliers of the IMADs that do the adds on the FMA pipe (see fadd)
   uint32_t thr_mask;     // (1 << thresholdWidth) - 1
   int out_shift;         // log2(fftSize) + 1: position of the threshold field in the output beat
   int thr_sext;          // 32 - thresholdWidth: sign extension of the threshold reported in a detection
@@ -40,7 +42,10 @@ template <int S> struct FGeo {
   static constexpr int N = 1 << S;
   static constexpr int PTS = 16;
   static constexpr int TPC = N / PTS;                        // threads per chirp
-  static constexpr int CPC = TPC >= 256 ? 1 : 256 / TPC;     // chirps per CTA
+#ifndef RSP_FAST_CTA
+#define RSP_FAST_CTA 256
+#endif
+  static constexpr int CPC = TPC >= RSP_FAST_CTA ? 1 : RSP_FAST_CTA / TPC;     // chirps per CTA
   static constexpr int THREADS = TPC * CPC;
   static constexpr int XB = N + 4 * (N >> 6);                // words of the exchange buffer: index f(p) = p + 4 * (p >> 6)
   static constexpr int XM = N / 2;                           // words of the magnitude array (int16 per bin)
@@ -57,20 +62,37 @@ __device__ __forceinline__ int hi16s(uint32_t v) { int r; asm("prmt.b32 %0, %1, 
 __device__ __forceinline__ int sar(int v, int n) { int r; asm("shr.s32 %0, %1, %2;" : "=r"(r) : "r"(v), "r"(n)); return r; }
 __device__ __forceinline__ uint32_t pack2(int re, int im) { return __byte_perm((uint32_t)im, (uint32_t)re, 0x5410); }
 
-// scaled butterfly, RoundHalfUp; WRAP = false when the result is packed to 16 bits right away
-template <bool WRAP>
-__device__ __forceinline__ void fbf(int &ar, int &ai, int &cr, int &ci) {
-  const int sr = sar(ar + cr + 1, 1), si = sar(ai + ci + 1, 1);
-  const int dr = sr - cr, di = si - ci;
-  ar = sr; ai = si;
-  cr = WRAP ? sext16(dr) : dr;
-  ci = WRAP ? sext16(di) : di;
+// sa * A + sc * C with compile-time signs, as ONE IMAD (FMA pipe).  The multiplier is a run-time +-1 so that ptxas keeps the
+// IMAD instead of strength-reducing it to an IADD3: the ALU pipe (PRMT, SHF, compares) is the bound of this kernel and the
+// FMA pipe is half empty, so every add that can move over does.  ptxas folds the neg into the IMAD's addend modifier.
+__device__ __forceinline__ int fadd(int sa, int A, int sc, int C, int one, int m1) {
+  int r;
+  const int mul = sa > 0 ? one : m1;
+  if (sc > 0) asm("mad.lo.s32 %0, %1, %2, %3;" : "=r"(r) : "r"(A), "r"(mul), "r"(C));
+  else asm("{.reg .s32 t; neg.s32 t, %3; mad.lo.s32 %0, %1, %2, t;}" : "=r"(r) : "r"(A), "r"(mul), "r"(C));
+  return r;
 }
 
-// x <- x * W, W = (cos, sin) as stored (already << 2); result rounded half up at bit 14 and wrapped to 16 bits
-__device__ __forceinline__ void fcmul(int &xr, int &xi, const int2 w) {
-  const int r = xr * w.x - xi * w.y + 0x8000;
-  const int i = xr * w.y + xi * w.x + 0x8000;
+// Scaled butterfly, RoundHalfUp (generators/sdf-fft/src/main/scala/SDFFFTUtil.scala:51-61, SDFChainRadix22.scala:459-464), on
+// values held with compile-time signs: A = sa * a, C = sc * c.
+//   -s = (-a - c) >> 1           floor of the negated sum = minus the half-up rounded average: the +1 needs no third addend
+//    d = wrap16(s - c)           because (a - c + 1) >> 1 == ((a + c + 1) >> 1) - c
+// The sum position then holds -s (sign -1) and the difference position d (sign +1).  NEGD: hold wrap16(-d) instead, which is
+// what the x(-j) rotation wants in its imaginary part (wrap16(-wrap16(d)) == wrap16(-d): d never is -32768 unwrapped).
+// WRAP = false only where |d| is all that is used afterwards (last stage before the magnitude).
+__device__ __forceinline__ void fbf1(int sa, int &A, int sc, int &C, bool negd, bool wrap, int one, int m1) {
+  const int sn = sar(fadd(-sa, A, -sc, C, one, m1), 1);
+  const int d = negd ? fadd(1, sn, sc, C, one, m1) : fadd(-1, sn, -sc, C, one, m1);
+  A = sn;
+  C = wrap ? sext16(d) : d;
+}
+
+// x <- x * W for a point held with sign sg (both components), W = (c, s, -c, -s) as stored (<< 2): the result (sign +1) is
+// rounded half up at bit 14 and wrapped to 16 bits by taking bits 16..31 of the 32-bit wrap-around sum
+__device__ __forceinline__ void fcmul(int sg, int &xr, int &xi, const int4 w) {
+  const int c = sg > 0 ? w.x : w.z, s = sg > 0 ? w.y : w.w, ns = sg > 0 ? w.w : w.y;
+  const int r = xr * c + xi * ns + 0x8000;
+  const int i = xr * s + xi * c + 0x8000;
   xr = sar(r, 16); xi = sar(i, 16);
 }
 
@@ -110,38 +132,44 @@ __device__ __forceinline__ void fast_pass(const FastArgs &a, int tl, const uint3
         re[rr] = hi16s(wd); im[rr] = sext16((int)wd);
       }
     }
+    int sg[R];   // sign each point is held with (compile-time after unrolling): value = sg * register
+#pragma unroll
+    for (int rr = 0; rr < R; ++rr) sg[rr] = 1;
 #pragma unroll
     for (int s = 0; s < m; ++s) {
       const int i = i0 + s;
       const int dist = 1 << (m - 1 - s);
-      // the differences of the last stage of an inner pass need no wrap when they are packed to 16 bits right away (even
-      // stage: at most the -j swap follows); after an odd stage they feed the twiddle product and must be wrapped first
-      const bool wrap = last || (s != m - 1) || (i & 1);
+      const bool rot = (i != S - 1) && ((i & 1) == 0);   // x(-j) on the last quarter of each 4D block follows (SDFChainRadix22.scala:319-337)
+      const bool wrap = !(last && s == m - 1);            // the magnitude only takes |d| (|wrap16(32768)| == 32768)
 #pragma unroll
       for (int rr = 0; rr < R; ++rr)
         if (!(rr & dist)) {
-          if (wrap) fbf<true>(re[rr], im[rr], re[rr + dist], im[rr + dist]);
-          else fbf<false>(re[rr], im[rr], re[rr + dist], im[rr + dist]);
+          const int rc = rr + dist;
+          const bool mj = rot && (rc & (dist >> 1));      // the difference point is rotated: (re, im) <- (im, -re)
+          fbf1(sg[rr], re[rr], sg[rc], re[rc], mj, wrap, a.one, a.m1);
+          fbf1(sg[rr], im[rr], sg[rc], im[rc], false, wrap, a.one, a.m1);
+          if (mj) { const int t = re[rc]; re[rc] = im[rc]; im[rc] = t; }
+          sg[rr] = -1; sg[rc] = 1;
         }
-      if (i == S - 1) continue;
-      if ((i & 1) == 0) {   // x (-j) on the last quarter of each 4D block (SDFChainRadix22.scala:319-337)
+      if (i == S - 1 || rot) continue;
+      const int L = S - i + 1;
+      const int q = 1 << (L - 2);
+      const int4 *tab = a.tw + a.tw_off[L];
 #pragma unroll
-        for (int rr = 0; rr < R; ++rr)
-          if ((rr & dist) && (rr & (dist >> 1))) { const int t = re[rr]; re[rr] = im[rr]; im[rr] = wrap ? sext16(-t) : -t; }
-      } else {
-        const int L = S - i + 1;
-        const int q = 1 << (L - 2);
-        const int2 *tab = a.tw + a.tw_off[L];
-#pragma unroll
-        for (int rr = 0; rr < R; ++rr) {
-          const int quarter = ((rr >> (m - 1 - s)) & 1) + 2 * ((rr >> (m - s)) & 1);
-          if (quarter) {
-            const int k = (rr & (dist - 1)) * Dl + low;
-            const int slot = quarter == 1 ? 0 : (quarter == 2 ? 1 : 2);
-            fcmul(re[rr], im[rr], __ldg(&tab[slot * q + k]));
-          }
+      for (int rr = 0; rr < R; ++rr) {
+        const int quarter = ((rr >> (m - 1 - s)) & 1) + 2 * ((rr >> (m - s)) & 1);
+        if (quarter) {
+          const int k = (rr & (dist - 1)) * Dl + low;
+          const int slot = quarter == 1 ? 0 : (quarter == 2 ? 1 : 2);
+          fcmul(sg[rr], re[rr], im[rr], __ldg(&tab[slot * q + k]));
+          sg[rr] = 1;
         }
       }
+    }
+    if (!last) {   // the exchange buffer holds true values: un-negate what is still held negated
+#pragma unroll
+      for (int rr = 0; rr < R; ++rr)
+        if (sg[rr] < 0) { re[rr] = fadd(-1, re[rr], 1, 0, a.one, a.m1); im[rr] = fadd(-1, im[rr], 1, 0, a.one, a.m1); }
     }
     if (!last) {
 #pragma unroll
@@ -337,9 +365,9 @@ static rsp_status launch_fast_modes(int cmode, bool linear, const LaunchCtx &c, 
 rsp_status launch_fast_chain(const Plan &pl, const LaunchCtx &ctx, const FxArgs &a, cudaStream_t st, const char **err) {
   FastArgs fa;
   fa.in = a.in; fa.out = a.out; fa.n_rows = a.n_rows; fa.row_base = a.row_base;
-  fa.tw = reinterpret_cast<const int2 *>(a.tw2);
+  fa.tw = reinterpret_cast<const int4 *>(a.tw2);
   for (int L = 0; L < 16; ++L) fa.tw_off[L] = a.tw_off[L];
-  fa.W = a.W; fa.G = a.G; fa.div_sum = a.div_sum; fa.scaler = a.scaler;
+  fa.W = a.W; fa.G = a.G; fa.div_sum = a.div_sum; fa.scaler = a.scaler; fa.one = 1; fa.m1 = -1;
   fa.thr_mask = a.thr_w >= 32 ? 0xFFFFFFFFu : ((1u << a.thr_w) - 1u);
   fa.out_shift = a.binw + 1; fa.thr_sext = 32 - a.thr_w;
   fa.det_list = a.det_list; fa.det_count = a.det_count; fa.det_cap = a.det_cap;

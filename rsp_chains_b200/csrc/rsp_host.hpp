@@ -34,8 +34,8 @@ struct Regs {
 struct Tables {
   std::vector<uint32_t> tw;   // fixed twiddles, packed (cos16 << 16 | sin16 & 0xFFFF); per stageN three runs [W^2k | W^k | W^3k]
   std::vector<F2> twf;        // fp32 twiddles, same layout
-  std::vector<int32_t> tw2;   // fixed twiddles again as int32 pairs (cos << s, sin << s), s = 16 - (twiddleWidth - 2): the fast
-                              // kernels' product then carries its rounded, wrapped result in bits 16..31 (rsp_fast.cu)
+  std::vector<int32_t> tw2;   // fixed twiddles again as int32 quads (c, s, -c, -s) << (16 - (twiddleWidth - 2)): the fast kernels'
+                              // product then carries its rounded, wrapped result in bits 16..31 (rsp_fast.cu)
   int tw_off[16];
   std::vector<int32_t> log_tab;
   std::vector<int32_t> nco_tab;
@@ -205,12 +205,13 @@ inline void build_tables(const rsp_chain_params &p, Tables &t) {
         const double c = std::cos(ang), s = -std::sin(ang);
         const long long re = wrap_host(from_double(c, twbp), tww), im = wrap_host(from_double(s, twbp), tww);
         t.tw.push_back(pack_iq((int)re, (int)im));
-        t.tw2.push_back((int32_t)(re * (1LL << pre))); t.tw2.push_back((int32_t)(im * (1LL << pre)));
+        const int32_t c4 = (int32_t)(re * (1LL << pre)), s4 = (int32_t)(im * (1LL << pre));
+        t.tw2.push_back(c4); t.tw2.push_back(s4); t.tw2.push_back(-c4); t.tw2.push_back(-s4);
         F2 f; f.x = (float)c; f.y = (float)s;
         t.twf.push_back(f);
       }
   }
-  if (t.tw.empty()) { t.tw.push_back(0); t.tw2.push_back(0); t.tw2.push_back(0); F2 f; f.x = 1.f; f.y = 0.f; t.twf.push_back(f); }
+  if (t.tw.empty()) { t.tw.push_back(0); for (int z = 0; z < 4; ++z) t.tw2.push_back(0); F2 f; f.x = 1.f; f.y = 0.f; t.twf.push_back(f); }
   // log2 LUT (LogMagMux.scala:120-131)
   const int Lw = p.mag.log2LookUpWidth, num = 1 << Lw;
   t.log_tab.resize((size_t)num);

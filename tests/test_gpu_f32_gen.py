@@ -1,0 +1,158 @@
+"""GPU parity, part 2 (through the C ABI): the fp32 flavour of the chain against the fp64 oracle (tolerance 1e-4 relative,
+identical detections -- north_star), and the PLFG -> NCO generator kernels against the integer oracle (bit-exact)."""
+import numpy as np
+import pytest
+
+import rsp_chains_b200 as R
+from rsp_chains_b200 import synth
+from rsp_chains_b200.params import (CACFARType, CFARParams, FFTParams, FftMagCfarVanillaParameters, FixedPoint, GOSCFARType,
+                                    MAGParams)
+from tests.util import configure, decode_cfar_words, from_dev_u32, oracle_cfgs, to_dev
+
+pytestmark = pytest.mark.gpu
+
+REL_TOL = 1e-4   # north_star: fp32 results within 1e-4 relative error of an fp64 reference
+
+
+def f32_params(n, W, G, cfar_type=CACFARType):
+    return FftMagCfarVanillaParameters(
+        fftParams=FFTParams.DSPReal(numPoints=n, useBitReverse=True, runTime=True),
+        magParams=MAGParams.fixed(),
+        cfarParams=CFARParams(leadLaggWindowSize=W, guardWindowSize=G, fftSize=n, CFARAlgorithm=cfar_type, sendCut=False))
+
+
+def f64_chain(oracle, x, log_n, sel, regs, scaler, W, G):
+    """the DspReal dataflow in fp64: FFT/N (natural order), magnitude, CFARCoreWithMem edge policy"""
+    n = 1 << log_n
+    thr = np.zeros((x.shape[0], n)); peak = np.zeros((x.shape[0], n), np.uint8); mag = np.zeros((x.shape[0], n))
+    cfg = oracle.cfar_cfg(n, W, G, 0, core=oracle.CORE_MEM, cfar_mode=regs["cfarMode"], div_sum=regs["divSum"],
+                          log_or_linear=regs["logOrLinearMode"], peak_grouping=regs.get("peakGrouping", 0))
+    for r in range(x.shape[0]):
+        fr, fi = oracle.fft_f64(log_n, x[r].real, x[r].imag)
+        if sel == 2:
+            m = np.array([oracle.jpl_f64(a, b) for a, b in zip(fr, fi)])
+        elif sel == 1:
+            m = fr * fr + fi * fi
+        else:
+            m = np.log2(np.array([oracle.jpl_f64(a, b) for a, b in zip(fr, fi)]))
+        mag[r] = m
+        thr[r], peak[r] = oracle.cfar_f64(cfg, scaler, m)
+    return mag, thr, peak
+
+
+def unpack_mask(mask, n):
+    bits = np.unpackbits(mask.view(np.uint8), bitorder="little").reshape(mask.shape[0], -1)
+    return bits[:, :n]
+
+
+@pytest.mark.parametrize("mode", [1, 2, 0])
+def test_c3_fp32_chain_go_so(cuda, oracle, mode):
+    """BASELINE config 2 (reduced row count for the fp64 oracle): 4 RX x chirps x 2048-point fp32 chain, GO / SO / CA CFAR"""
+    n, log_n, W, G, n_rx, n_chirps = 2048, 11, 32, 4, 4, 6
+    rows = n_rx * n_chirps
+    phases = np.repeat(np.arange(n_rx) * np.pi / 8, n_chirps)
+    xc = synth.chirps_complex(rows, n, seed=3, rx_phase=phases)
+    x32 = np.stack([xc.real, xc.imag], axis=-1).astype(np.float32)
+    xq = x32[..., 0].astype(np.float64) + 1j * x32[..., 1].astype(np.float64)      # what the kernel actually sees
+    regs = dict(fftWin=n, logOrLinearMode=1, divSum=5, peakGrouping=0, cfarMode=mode, windowCells=W, guardCells=G)
+    scaler = 3.5
+    with R.FftMagCfarChainVanilla(f32_params(n, W, G)) as ch:
+        configure(ch, log_n, 2, regs)
+        ch.set_threshold_scaler_f32(scaler)
+        d_in = cuda.from_numpy(x32).cuda()
+        d_thr = cuda.empty((rows, n), dtype=cuda.float32, device="cuda")
+        d_mask = cuda.zeros((rows, n // 32), dtype=cuda.int32, device="cuda")
+        ch.run(d_in, n_chirps, n_rx, out=d_thr, peak_mask=d_mask)
+        cuda.cuda.synchronize()
+        thr = d_thr.cpu().numpy()
+        pk = unpack_mask(d_mask.cpu().numpy().view(np.uint32), n)
+        assert ch.variant.startswith("chain_f32")
+    mag, want_thr, want_pk = f64_chain(oracle, xq, log_n, 2, regs, scaler, W, G)
+    scale = np.abs(want_thr).max()
+    rel = np.abs(thr - want_thr) / np.maximum(np.abs(want_thr), 1e-3 * scale)
+    assert rel.max() < REL_TOL, f"max relative threshold error {rel.max():.3e}"
+    # identical detections, except cells whose margin |cut - thr| is itself inside the fp32 tolerance (none in this data)
+    margin = np.abs(mag - want_thr) / np.maximum(np.abs(want_thr), 1e-30)
+    decided = margin > 10 * REL_TOL
+    assert (pk[decided] == want_pk[decided]).all()
+    assert (pk == want_pk).all()
+    assert want_pk.sum() >= 2 * rows      # both targets of every row
+
+
+def test_fp32_blocks_and_sizes(cuda, oracle):
+    """fft alone (FFT(x)/N, natural order) for several sizes, magnitude modes, log threshold"""
+    rng = np.random.default_rng(1)
+    for log_n in (3, 6, 10, 13):
+        n = 1 << log_n
+        W = max(2, min(16, n // 8)); G = 1
+        x = (rng.uniform(-1, 1, (5, n)) + 1j * rng.uniform(-1, 1, (5, n)))
+        x32 = np.stack([x.real, x.imag], axis=-1).astype(np.float32)
+        with R.FftMagCfarChainVanilla(f32_params(n, W, G)) as ch:
+            configure(ch, log_n, 2, dict(fftWin=n, logOrLinearMode=0, divSum=int(np.log2(W)), cfarMode=0, windowCells=W, guardCells=G))
+            d_in = cuda.from_numpy(x32).cuda()
+            d_out = cuda.empty((5, n, 2), dtype=cuda.float32, device="cuda")
+            ch.fft(d_in, 5, d_out)
+            cuda.cuda.synchronize()
+            got = d_out.cpu().numpy()
+        xq = x32[..., 0].astype(np.float64) + 1j * x32[..., 1].astype(np.float64)
+        want = np.fft.fft(xq, axis=1) / n
+        err = np.abs(got[..., 0] + 1j * got[..., 1] - want).max() / np.abs(want).max()
+        assert err < REL_TOL, f"N={n}: {err:.2e}"
+
+
+# ---------------------------------------------------------------------------------------------------- PLFG -> NCO
+
+def write_plfg(ch, p, oracle, starting_point, segs, n_rep=1, frame_num=1, inter=10):
+    """program the PLFG through the register bus as the reference tester does (RspChainVanillaTester.scala:86-130)"""
+    bb = p.beatBytes
+    for i, (slope, ns, up, rst) in enumerate(segs):
+        ch.memWriteWord(p.plfgRAM.base + i * bb, oracle.plfg_ram_word(slope, ns, up, rst))
+    seg0 = 6
+    rep0 = seg0 + p.plfgParams.maxChirpOrdinalNum
+    ord0 = rep0 + p.plfgParams.maxNumOfDifferentChirps
+    ch.memWriteWord(p.plfgAddress.base + 2 * bb, frame_num)
+    ch.memWriteWord(p.plfgAddress.base + 3 * bb, inter)
+    ch.memWriteWord(p.plfgAddress.base + 4 * bb, 1)
+    ch.memWriteWord(p.plfgAddress.base + 5 * bb, starting_point)
+    ch.memWriteWord(p.plfgAddress.base + seg0 * bb, len(segs))
+    ch.memWriteWord(p.plfgAddress.base + rep0 * bb, n_rep)
+    ch.memWriteWord(p.plfgAddress.base + ord0 * bb, 0)
+    ch.memWriteWord(p.plfgAddress.base + 1 * bb, 0)
+    ch.memWriteWord(p.plfgAddress.base + 0 * bb, 1)   # enable
+
+
+def test_generator_matches_oracle_and_c1_chain(cuda, oracle):
+    """BASELINE config 0, reference-faithful reading: PLFG (1 segment, slope 0, startingPoint 16) -> NCO (table 128, 16 bit,
+    phase 9) -> 1024-point fixed FFT -> JPL -> CA-CFAR: tone at bin 16 * 1024 / (4 * 128) = 32
+    (src/test/scala/RspChainVanillaTester.scala:85-94).  Then a triangle chirp (up / down segments) for the closed-form phase."""
+    p = R.rsp_chain_vanilla_app_params()
+    regs = dict(fftWin=1024, thresholdScaler=4, logOrLinearMode=1, divSum=5, peakGrouping=0, cfarMode=0, windowCells=32, guardCells=4)
+    for name, start, segs, n_rep in (("tone", 16, [(0, 255, True, False)] * 4 + [], 1),
+                                     ("triangle", 3, [(1, 200, True, False), (2, 180, False, False), (0, 100, False, True), (3, 32, True, False)], 2)):
+        segs = segs[:4]
+        n_per_chirp = sum(s[1] for s in segs)
+        with R.RspChainVanilla(p) as ch:
+            configure(ch, 10, 2, regs)
+            write_plfg(ch, p, oracle, start, segs, n_rep=n_rep, frame_num=0, inter=7)
+            n_samples = 4 * 1024
+            d_nco = cuda.zeros(n_samples, dtype=cuda.int32, device="cuda")
+            d_plfg = cuda.zeros(n_samples, dtype=cuda.int32, device="cuda")
+            ch.generate(n_samples, d_nco, d_plfg)
+            d_out = cuda.zeros((4, 1024), dtype=cuda.int32, device="cuda")
+            ch.run_from_generator(4, 1, out=d_out)
+            cuda.cuda.synchronize()
+            got_nco, got_plfg, got_out = from_dev_u32(d_nco), d_plfg.cpu().numpy(), from_dev_u32(d_out)
+        ram = [oracle.plfg_ram_word(*s) for s in segs]
+        op = oracle.Plfg(frame_num=0, interframe_num_of_samples=7, different_chirps_num=1, starting_point=start,
+                         segment_nums=[len(segs)], repeated_chirp_nums=[n_rep], chirp_ordinal_nums=[0], ram=ram)
+        want_plfg = op.run(n_samples)
+        assert (got_plfg == want_plfg).all(), name
+        want_nco, _ = oracle.nco_words(want_plfg, 128, 16, 9)
+        assert (got_nco == want_nco).all(), name
+        fft, mag, cfar = oracle_cfgs(oracle, p, 10, 2, regs)
+        want_out = oracle.chain_fixed_words(fft, mag, cfar, want_nco.reshape(4, 1024))
+        assert (got_out == want_out).all(), name
+        if name == "tone":
+            _, bins, peak = decode_cfar_words(got_out, 1024)
+            assert n_per_chirp == 4 * 255
+            assert peak[0, 32] == 1     # (quantisation-noise bins next to an all-zero window may flag too: threshold 0)
