@@ -43,7 +43,7 @@ template <int S> struct FGeo {
   static constexpr int PTS = 16;
   static constexpr int TPC = N / PTS;                        // threads per chirp
 #ifndef RSP_FAST_CTA
-#define RSP_FAST_CTA 256
+#define RSP_FAST_CTA 128
 #endif
   static constexpr int CPC = TPC >= RSP_FAST_CTA ? 1 : RSP_FAST_CTA / TPC;     // chirps per CTA
   static constexpr int THREADS = TPC * CPC;
