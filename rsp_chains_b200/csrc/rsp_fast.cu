@@ -31,7 +31,7 @@ struct FastArgs {
   int W, G, div_sum, scaler;
   int one, m1;           // +1 and -1 as run-time values: multipliers of the IMADs that do the adds on the FMA pipe (see fadd)
   uint32_t thr_mask;     // (1 << thresholdWidth) - 1
-  int out_shift;         // log2(fftSize) + 1: position of the threshold field in the output beat
+  int out_mul;           // 1 << (log2(fftSize) + 1): position of the threshold field in the output beat
   int thr_sext;          // 32 - thresholdWidth: sign extension of the threshold reported in a detection
   Detection *det_list;
   uint32_t *det_count;
@@ -67,6 +67,7 @@ __device__ __forceinline__ uint32_t pack2(int re, int im) { return __byte_perm((
 // FMA pipe is half empty, so every add that can move over does.  ptxas folds the neg into the IMAD's addend modifier.
 __device__ __forceinline__ int fadd(int sa, int A, int sc, int C, int one, int m1) {
   int r;
+
   const int mul = sa > 0 ? one : m1;
   if (sc > 0) asm("mad.lo.s32 %0, %1, %2, %3;" : "=r"(r) : "r"(A), "r"(mul), "r"(C));
   else asm("{.reg .s32 t; neg.s32 t, %3; mad.lo.s32 %0, %1, %2, t;}" : "=r"(r) : "r"(A), "r"(mul), "r"(C));
@@ -106,7 +107,7 @@ __device__ __forceinline__ int fjpl(int re, int im) {
 // One pass = m radix-2 stages in registers on 2^m points Dl apart (same decomposition as rsp_device.cuh, fx_pass_*).
 // Thread tl of the chirp works on the groups vt = g * TPC + tl, so a warp touches consecutive words in every pass.
 template <int S, int K>
-__device__ __forceinline__ void fast_pass(const FastArgs &a, int tl, const uint32_t *__restrict__ gin, uint32_t *xb, uint32_t *xm) {
+__device__ __forceinline__ void fast_pass(const FastArgs &a, int tl, const uint32_t (&pre)[16], uint32_t *xb, uint32_t *xm) {
   using Gm = FGeo<S>;
   constexpr int m = fx_pass_size(S, K), i0 = fx_pass_start(S, K), LDl = S - i0 - m, Dl = 1 << LDl;
   constexpr int PTS = Gm::PTS, G = PTS >> m, R = 1 << m, TPC = Gm::TPC;
@@ -128,7 +129,7 @@ __device__ __forceinline__ void fast_pass(const FastArgs &a, int tl, const uint3
 #pragma unroll
       for (int rr = 0; rr < R; ++rr) {
         const int p = base + rr * Dl;
-        const uint32_t wd = first ? __ldg(&gin[p]) : xb[fidx(p)];
+        const uint32_t wd = first ? pre[rr] : xb[fidx(p)];   // first pass: m = 4, one group, p = tl + rr * TPC
         re[rr] = hi16s(wd); im[rr] = sext16((int)wd);
       }
     }
@@ -202,11 +203,16 @@ __device__ __forceinline__ void fast_pass(const FastArgs &a, int tl, const uint3
   }
 }
 
+// Barrier between the phases of a row.  The chirps of a CTA share nothing, so a named barrier per chirp (bar.sync c + 1, TPC)
+// would do -- measured on B200 it is 7% SLOWER than the plain CTA barrier (204 vs 219 Gsamples/s), so the CTA barrier stays.
+template <int S> __device__ __forceinline__ void chirp_sync(int) { __syncthreads(); }
+
 template <int S, int K>
-__device__ __forceinline__ void fast_passes(const FastArgs &a, bool active, int tl, const uint32_t *gin, uint32_t *xb, uint32_t *xm) {
-  if (active) fast_pass<S, K>(a, tl, gin, xb, xm);
-  __syncthreads();
-  if constexpr (K + 1 < fx_n_passes(S)) fast_passes<S, K + 1>(a, active, tl, gin, xb, xm);
+__device__ __forceinline__ void fast_passes(const FastArgs &a, int c, int tl, const uint32_t (&pre)[16], uint32_t *xb, uint32_t *xm) {
+  static_assert(K != 0 || fx_pass_size(S, 0) == 4, "the first pass takes the 16 prefetched beats of the thread");
+  fast_pass<S, K>(a, tl, pre, xb, xm);
+  chirp_sync<S>(c);
+  if constexpr (K + 1 < fx_n_passes(S)) fast_passes<S, K + 1>(a, c, tl, pre, xb, xm);
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
@@ -228,45 +234,70 @@ __device__ __forceinline__ int chirp_scan_exclusive(int total, int c, int tl, in
   if (NW > 1) {
     const int w = tl >> 5;
     if (lane == 31) wsum[c * NW + w] = incl;
-    __syncthreads();
+    chirp_sync<S>(c);
 #pragma unroll
     for (int h = 0; h < NW - 1; ++h) offset += (h < w) ? wsum[c * NW + h] : 0;
   }
   return offset + incl - total;
 }
 
-// threshold, peak and output beat of bin n = tl + j * TPC.  EDGE: the bin may miss one of its windows (one-sided threshold,
-// CFARCoreWithMem.scala:154-171); indices are clamped so no load leaves the chirp's arrays.
+// Threshold, peak and output beat of bin n = tl + j * TPC; returns the peak bit.  pA..pD point at P[tl + offset] for the four
+// window borders, so every load is [register + immediate].  EDGE: the bin may miss one of its windows (one-sided threshold,
+// CFARCoreWithMem.scala:154-171); the indices are clamped so that no load leaves the chirp's arrays.
 template <int S, int CMODE, bool LINEAR, bool EDGE>
-__device__ __forceinline__ void fast_cfar_bin(const FastArgs &a, uint32_t row, int n, const int *P, const short *X, uint32_t *gout) {
-  constexpr int N = 1 << S;
-  const int W = a.W, G = a.G;
+__device__ __forceinline__ int fast_cfar_bin(const FastArgs &a, int j, int tl, int n2, const int *P, const int *pA, const int *pB,
+                                             const int *pC, const int *pD, const short *X, uint32_t *gout) {
+  constexpr int N = 1 << S, TPC = FGeo<S>::TPC;
+  const int n = tl + j * TPC;
   int L, R;
   bool lagg_full = true, lead_full = true;
   if (EDGE) {
+    const int W = a.W, G = a.G;
     lagg_full = (n + G + W <= N - 1); lead_full = (n - G - W >= 0);
     const int hi = min(n + G + W + 1, N), lo = max(n - G - W, 0);
-    L = (P[hi] - P[hi - W]) >> a.div_sum;
-    R = (P[lo + W] - P[lo]) >> a.div_sum;
+    L = fadd(1, P[hi], -1, P[hi - W], a.one, a.m1);
+    R = fadd(1, P[lo + W], -1, P[lo], a.one, a.m1);
   } else {
-    L = (P[n + G + W + 1] - P[n + G + 1]) >> a.div_sum;
-    R = (P[n - G] - P[n - G - W]) >> a.div_sum;
+    L = fadd(1, pA[j * TPC], -1, pB[j * TPC], a.one, a.m1);
+    R = fadd(1, pC[j * TPC], -1, pD[j * TPC], a.one, a.m1);
   }
-  int t = CMODE == 0 ? ((R + L) >> 1) : (CMODE == 1 ? max(L, R) : min(L, R));
+  L = sar(L, a.div_sum); R = sar(R, a.div_sum);
+  int t = CMODE == 0 ? sar(fadd(1, R, 1, L, a.one, a.m1), 1) : (CMODE == 1 ? max(L, R) : min(L, R));
   if (EDGE) t = lead_full ? (lagg_full ? t : R) : L;
-  const int thr = LINEAR ? t * a.scaler : t + a.scaler;
+  const int thr = LINEAR ? t * a.scaler : fadd(1, t, 1, a.scaler, a.one, a.m1);
   const int cut = X[n];
-  const bool pk = cut > thr;
-  gout[n] = (((uint32_t)thr & a.thr_mask) << a.out_shift) | ((uint32_t)n << 1) | (pk ? 1u : 0u);
-  if (pk && a.det_list) {
+  // peak = cut > thr as the sign bit of thr - cut (|thr| < 2^31 - 2^16 is checked by the host)
+  const int pk = (int)((uint32_t)fadd(1, thr, -1, cut, a.one, a.m1) >> 31);
+  const int w0 = (int)(((uint32_t)thr & a.thr_mask) * (uint32_t)a.out_mul + (uint32_t)n2);   // threshold field | bin field (n << 1)
+  gout[n] = (uint32_t)fadd(1, pk, 1, w0, a.one, a.m1);
+  return pk;
+}
+
+// detections of one thread: bit (15 - j) of `mask` = peak of bin tl + j * TPC.  Rare path, recomputes from shared memory.
+struct FastDetArgs { int W, G, div_sum, scaler, thr_sext; uint32_t chirp, det_cap; Detection *det_list; uint32_t *det_count; };
+template <int S, int CMODE, bool LINEAR>
+__device__ __noinline__ void fast_detections(const FastDetArgs a, int tl, uint32_t mask, const int *P, const short *X) {
+  constexpr int N = 1 << S, TPC = FGeo<S>::TPC;
+  for (int j = 0; j < 16; ++j) {
+    if (!((mask >> (15 - j)) & 1u)) continue;
+    const int n = tl + j * TPC, W = a.W, G = a.G;
+    const bool lagg_full = (n + G + W <= N - 1), lead_full = (n - G - W >= 0);
+    const int hi = min(n + G + W + 1, N), lo = max(n - G - W, 0);
+    const int L = (P[hi] - P[hi - W]) >> a.div_sum, R = (P[lo + W] - P[lo]) >> a.div_sum;
+    int t = CMODE == 0 ? ((R + L) >> 1) : (CMODE == 1 ? max(L, R) : min(L, R));
+    t = lead_full ? (lagg_full ? t : R) : L;
+    const int thr = LINEAR ? t * a.scaler : t + a.scaler;
     const uint32_t slot = atomicAdd(a.det_count, 1u);
-    if (slot < a.det_cap) { Detection d; d.chirp = a.row_base + row; d.bin = (uint32_t)n; d.threshold = (int)((uint32_t)thr << a.thr_sext) >> a.thr_sext; d.cut = cut; a.det_list[slot] = d; }
+    if (slot < a.det_cap) {
+      Detection d; d.chirp = a.chirp; d.bin = (uint32_t)n; d.threshold = (int)((uint32_t)thr << a.thr_sext) >> a.thr_sext; d.cut = X[n];
+      a.det_list[slot] = d;
+    }
   }
 }
 
 // EJ = number of leading / trailing iterations j whose bins may miss a window (ceil((W + G) / TPC), checked by the host)
 template <int S, int CMODE, bool LINEAR, int EJ>
-__global__ void __launch_bounds__(FGeo<S>::THREADS) chain_fixed_fast_kernel(const FastArgs a) {
+__global__ void __launch_bounds__(FGeo<S>::THREADS, 1024 / FGeo<S>::THREADS) chain_fixed_fast_kernel(const FastArgs a) {
   using Gm = FGeo<S>;
   constexpr int N = Gm::N, TPC = Gm::TPC, CPC = Gm::CPC, PTS = Gm::PTS;
   extern __shared__ __align__(16) uint32_t smem[];
@@ -275,10 +306,20 @@ __global__ void __launch_bounds__(FGeo<S>::THREADS) chain_fixed_fast_kernel(cons
   uint32_t *xb = smem + (size_t)c * Gm::ROW, *xm = xb + Gm::XB;
   int *P = reinterpret_cast<int *>(xb);
   const short *X = reinterpret_cast<const short *>(xm);
-  for (uint32_t row0 = blockIdx.x * CPC; row0 < a.n_rows; row0 += gridDim.x * CPC) {
-    const uint32_t row = row0 + c;
-    const bool active = row < a.n_rows;
-    fast_passes<S, 0>(a, active, tl, a.in + (size_t)row * N, xb, xm);
+  const int *pA = P + tl + a.G + a.W + 1, *pB = P + tl + a.G + 1, *pC = P + tl - a.G, *pD = P + tl - a.G - a.W;
+  const uint32_t stride = gridDim.x * CPC;
+  // the loop bound is the same for every thread of the CTA (the barriers are CTA-wide); a chirp slot past the last row
+  // recomputes the last row -- it stores the same beats again and reports no detections
+  for (uint32_t row0 = blockIdx.x * CPC; row0 < a.n_rows; row0 += stride) {
+    const bool active = row0 + c < a.n_rows;
+    const uint32_t row = active ? row0 + c : a.n_rows - 1;
+    uint32_t pre[PTS];   // the thread's 16 beats of the row: p = tl + rr * TPC, warp-contiguous 128-byte lines
+    {
+      const uint32_t *gin = a.in + (size_t)row * N + tl;
+#pragma unroll
+      for (int rr = 0; rr < PTS; ++rr) pre[rr] = __ldg(&gin[rr * TPC]);
+    }
+    fast_passes<S, 0>(a, c, tl, pre, xb, xm);
     // prefix sums of the thread's 16 consecutive magnitudes
     int x[PTS];
     {
@@ -299,17 +340,23 @@ __global__ void __launch_bounds__(FGeo<S>::THREADS) chain_fixed_fast_kernel(cons
       for (int k = 0; k < PTS; k += 4) *reinterpret_cast<int4 *>(&P[tl * PTS + k]) = make_int4(pv[k], pv[k + 1], pv[k + 2], pv[k + 3]);
       if (tl == TPC - 1) P[N] = acc;
     }
-    __syncthreads();
-    if (active) {
-      uint32_t *gout = a.out + (size_t)row * N;
+    chirp_sync<S>(c);
+    uint32_t *gout = a.out + (size_t)row * N;
+    int mask = 0;
+    int n2 = tl << 1;
 #pragma unroll
-      for (int j = 0; j < PTS; ++j) {
-        const int n = tl + j * TPC;
-        if (j < EJ || j >= PTS - EJ) fast_cfar_bin<S, CMODE, LINEAR, true>(a, row, n, P, X, gout);
-        else fast_cfar_bin<S, CMODE, LINEAR, false>(a, row, n, P, X, gout);
-      }
+    for (int j = 0; j < PTS; ++j) {
+      int pk;
+      if (j < EJ || j >= PTS - EJ) pk = fast_cfar_bin<S, CMODE, LINEAR, true>(a, j, tl, n2, P, pA, pB, pC, pD, X, gout);
+      else pk = fast_cfar_bin<S, CMODE, LINEAR, false>(a, j, tl, n2, P, pA, pB, pC, pD, X, gout);
+      mask = mask * 2 + pk;
+      n2 += 2 * TPC;
     }
-    __syncthreads();
+    if (mask != 0 && a.det_list != nullptr && active) {
+      const FastDetArgs da = {a.W, a.G, a.div_sum, a.scaler, a.thr_sext, a.row_base + row, a.det_cap, a.det_list, a.det_count};
+      fast_detections<S, CMODE, LINEAR>(da, tl, (uint32_t)mask, P, X);
+    }
+    chirp_sync<S>(c);
   }
 }
 
@@ -329,7 +376,9 @@ bool fast_chain_supported(const Plan &pl, const FxArgs &a) {
   const long long smax = (long long)a.W * 32768;
   if (smax > (1LL << (a.sumw - 1))) return false;
   const long long tmax = (smax >> a.div_sum) + 1, sc = a.scaler < 0 ? -(long long)a.scaler : a.scaler;
-  if (a.log_or_linear ? (tmax * sc >= (1LL << 31)) : (tmax + sc >= (1LL << 31))) return false;
+  const long long lim = (1LL << 31) - (1LL << 16);   // the peak is the sign bit of thr - cut
+  if (a.log_or_linear ? (tmax * sc >= lim) : (tmax + sc >= lim)) return false;
+  if (a.binw + 1 > 31) return false;
   return true;
 }
 
@@ -369,7 +418,7 @@ rsp_status launch_fast_chain(const Plan &pl, const LaunchCtx &ctx, const FxArgs 
   for (int L = 0; L < 16; ++L) fa.tw_off[L] = a.tw_off[L];
   fa.W = a.W; fa.G = a.G; fa.div_sum = a.div_sum; fa.scaler = a.scaler; fa.one = 1; fa.m1 = -1;
   fa.thr_mask = a.thr_w >= 32 ? 0xFFFFFFFFu : ((1u << a.thr_w) - 1u);
-  fa.out_shift = a.binw + 1; fa.thr_sext = 32 - a.thr_w;
+  fa.out_mul = (int)(1u << (a.binw + 1)); fa.thr_sext = 32 - a.thr_w;
   fa.det_list = a.det_list; fa.det_count = a.det_count; fa.det_cap = a.det_cap;
   const int cmode = a.cfar_mode == 0 ? 0 : (a.cfar_mode == 1 ? 1 : 2);   // MuxLookup default: smallestOf (CFARCoreWithMem.scala:138-141)
   const bool linear = a.log_or_linear != 0;
