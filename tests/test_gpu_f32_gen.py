@@ -127,9 +127,9 @@ def test_generator_matches_oracle_and_c1_chain(cuda, oracle):
     (src/test/scala/RspChainVanillaTester.scala:85-94).  Then a triangle chirp (up / down segments) for the closed-form phase."""
     p = R.rsp_chain_vanilla_app_params()
     regs = dict(fftWin=1024, thresholdScaler=4, logOrLinearMode=1, divSum=5, peakGrouping=0, cfarMode=0, windowCells=32, guardCells=4)
-    for name, start, segs, n_rep in (("tone", 16, [(0, 255, True, False)] * 4 + [], 1),
-                                     ("triangle", 3, [(1, 200, True, False), (2, 180, False, False), (0, 100, False, True), (3, 32, True, False)], 2)):
-        segs = segs[:4]
+    # segmentNums is log2Ceil(maxNumOfSegments) = 2 bits wide (PLFGDspBlockMem.scala:49,161): at most 3 segments per chirp here
+    for name, start, segs, n_rep in (("tone", 16, [(0, 255, True, False)] * 3, 1),
+                                     ("triangle", 3, [(1, 200, True, False), (2, 180, False, False), (0, 100, False, True)], 2)):
         n_per_chirp = sum(s[1] for s in segs)
         with R.RspChainVanilla(p) as ch:
             configure(ch, 10, 2, regs)
@@ -154,5 +154,5 @@ def test_generator_matches_oracle_and_c1_chain(cuda, oracle):
         assert (got_out == want_out).all(), name
         if name == "tone":
             _, bins, peak = decode_cfar_words(got_out, 1024)
-            assert n_per_chirp == 4 * 255
+            assert n_per_chirp == 3 * 255
             assert peak[0, 32] == 1     # (quantisation-noise bins next to an all-zero window may flag too: threshold 0)
