@@ -48,6 +48,23 @@ def chain_params():
     return p
 
 
+def ncu_traffic():
+    """DRAM bytes per launch of the chain kernel from the committed `ncu --set full` capture (profiles/), or None"""
+    import glob
+    best = None
+    for f in sorted(glob.glob(os.path.join(ROOT, "profiles", "*ncu_full_chain_fixed_fast*.txt"))):
+        rd = wr = None
+        for line in open(f):
+            c = line.rstrip("\n").split("\t")
+            if len(c) == 3 and c[0] == "dram__bytes_read.sum" and c[1] == "Mbyte":
+                rd = float(c[2])
+            if len(c) == 3 and c[0] == "dram__bytes_write.sum" and c[1] == "Mbyte":
+                wr = float(c[2])
+        if rd is not None and wr is not None:
+            best = ((rd + wr) * 1e6, os.path.basename(f))
+    return best
+
+
 def measured_peak():
     try:
         with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
@@ -266,7 +283,8 @@ def main():
                        "l2_policy": "inputs+outputs (512 MiB per step) exceed the 126 MB L2", "parallelism": f"frames sharded over {world} GPU(s), no data-path collective",
                        "detections_gathered_one_frame": n_gathered, "host_path_equals_device_path": host_equal},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                         "traffic": None, "peak_source": peak_src, "kernel_ms_avg": avg_ms, "kernel_ms_median": med_ms,
+                         "traffic": (ncu_traffic() or (None, None))[0], "traffic_source": (ncu_traffic() or (None, None))[1],
+                         "algorithmic_bytes_per_launch": samples_per_step * BYTES_PER_SAMPLE, "peak_source": peak_src, "kernel_ms_avg": avg_ms, "kernel_ms_median": med_ms,
                          "bytes_per_sample": BYTES_PER_SAMPLE},
             "e2e": {"value": e2e_value, "unit": "Msamples/s", "h2d_bytes_per_step": rows * N_POINTS * 4, "d2h_bytes_per_step": rows * N_POINTS * 4,
                     "steps": args.e2e_steps, "api": "rsp_run_host (pinned host buffers, 3-deep chunk pipeline)"},

@@ -10,7 +10,7 @@
 #define RSP_FAST_SMIN 10
 #endif
 #ifndef RSP_FAST_SMAX
-#define RSP_FAST_SMAX 10
+#define RSP_FAST_SMAX 14
 #endif
 
 namespace rsp {

@@ -172,3 +172,77 @@ def test_invalid_parameters_raise(cuda):
         d = cuda.zeros((1, 64), dtype=cuda.int32, device="cuda")
         with pytest.raises(R.RspError):
             ch.run(d, 1, 1, out=d.clone())
+
+
+# ------------------------------------------------------------------------------------------- the specialised fast kernel
+def _fast_params(n, W, G, thr_w=16):
+    p = chain_params(n, 0, W=W, G=G)
+    p.cfarParams.protoThreshold = FixedPoint(thr_w, 0)
+    return p
+
+
+@pytest.mark.parametrize("log_n,W,G", [(10, 16, 4), (10, 64, 4), (10, 32, 8), (11, 32, 4), (12, 64, 4), (13, 16, 2), (14, 64, 8)])
+def test_fast_kernel_variants(cuda, oracle, log_n, W, G):
+    """chain_fixed_fast<S>: CA/GO/SO x linear/log, ragged row counts (two chirps per CTA), edge iterations (W + G > 64 at
+    N = 1024), threshold fields of other widths, full-range random rows next to realistic chirps"""
+    n = 1 << log_n
+    rows = 37 if log_n <= 12 else 9
+    beats = np.concatenate([synth.chirps_fixed(rows - 5, n, seed=log_n), synth.random_beats(5, n, seed=100 + log_n)])
+    for mode, lin, thr_w, scaler in ((0, 1, 16, 4), (1, 1, 16, 3), (2, 0, 16, 700), (0, 1, 12, 5), (2, 1, 20, -3), (3, 1, 16, 2)):
+        p = _fast_params(n, W, G, thr_w)
+        regs = dict(fftWin=n, thresholdScaler=scaler & 0xFFFF, logOrLinearMode=lin, divSum=int(np.log2(W)), peakGrouping=0, cfarMode=mode,
+                    windowCells=W, guardCells=G)
+        with R.FftMagCfarChainVanilla(p) as ch:
+            configure(ch, log_n, 2, regs)
+            assert ch.variant == f"chain_fixed_fast<{log_n}>", ch.variant
+        run_and_compare(cuda, oracle, p, log_n, 2, regs, beats)
+
+
+def test_fast_kernel_detection_list(cuda, oracle):
+    """the out-of-line detection path of the fast kernel reports exactly the beats with peak = 1 (chirp, bin, threshold, cut)"""
+    p = _fast_params(1024, 16, 4)
+    regs = dict(fftWin=1024, thresholdScaler=4, logOrLinearMode=1, divSum=4, peakGrouping=0, cfarMode=0, windowCells=16, guardCells=4)
+    rows = 301
+    beats = synth.chirps_fixed(rows, 1024, seed=21)
+    fft, mag, cfar = oracle_cfgs(oracle, p, 10, 2, regs)
+    want, _, want_mag = oracle.chain_fixed_words(fft, mag, cfar, beats, n_threads=oracle.max_threads(), want_stages=True)
+    with R.FftMagCfarChainVanilla(p) as ch:
+        configure(ch, 10, 2, regs)
+        d_in = to_dev(cuda, beats)
+        d_out = cuda.empty((rows, 1024), dtype=cuda.int32, device="cuda")
+        det_list = cuda.zeros((1 << 16, 4), dtype=cuda.int32, device="cuda")
+        det_count = cuda.zeros(1, dtype=cuda.int32, device="cuda")
+        ch.run(d_in, rows, 1, out=d_out, det_list=det_list, det_count=det_count)
+        cuda.cuda.synchronize()
+        got = from_dev_u32(d_out)
+        k = int(det_count.item())
+        dets = det_list[:k].cpu().numpy()
+    assert (got == want).all()
+    thr, bins, peak = decode_cfar_words(want, 1024)
+    exp = {(r, b): (int(thr[r, b]), int(np.int16(want_mag[r, b] & 0xFFFF))) for r, b in np.argwhere(peak == 1)}
+    assert k == len(exp)
+    assert {(int(d[0]), int(d[1])): (int(d[2]) & 0xFFFF, int(d[3])) for d in dets} == exp
+
+
+def test_c5_full_size_rows_are_independent(cuda, oracle):
+    """BASELINE config 4 at full size: 8 RX x 4096 chirps x 16384 points (2^29 samples, 2 GiB in + 2 GiB out).  The oracle
+    checks 8 distinct rows; the size-independent property is that a row's result depends on that row alone: every replica of
+    the 8-row block must equal the first, wherever it sits in the batch."""
+    n, log_n, W, G = 16384, 14, 64, 8
+    p = _fast_params(n, W, G)
+    regs = dict(fftWin=n, thresholdScaler=4, logOrLinearMode=1, divSum=6, peakGrouping=0, cfarMode=0, windowCells=W, guardCells=G)
+    base = np.concatenate([synth.chirps_fixed(7, n, seed=77), synth.random_beats(1, n, seed=78)])
+    n_rx, n_chirps = 8, 4096
+    rows = n_rx * n_chirps
+    fft, mag, cfar = oracle_cfgs(oracle, p, log_n, 2, regs)
+    want = oracle.chain_fixed_words(fft, mag, cfar, base, n_threads=oracle.max_threads())
+    with R.FftMagCfarChainVanilla(p) as ch:
+        configure(ch, log_n, 2, regs)
+        d_in = to_dev(cuda, base).repeat(rows // 8, 1).contiguous()
+        d_out = cuda.empty_like(d_in)
+        ch.run(d_in, n_chirps, n_rx, out=d_out)
+        cuda.cuda.synchronize()
+        assert ch.variant == "chain_fixed_fast<14>"
+        first = d_out[:8]
+        assert (from_dev_u32(first) == want).all()
+        assert bool((d_out.view(rows // 8, 8, n) == first.unsqueeze(0)).all().item())
