@@ -28,7 +28,9 @@ struct FastArgs {
   uint32_t n_rows, row_base;
   const int4 *tw;        // (c, s, -c, -s) with c = cos << 2, s = -sin(2 pi t / stageN) << 2; per stageN three runs [W^2k | W^k | W^3k]
   int tw_off[16];
-  int W, G, div_sum, scaler;
+  int W, G, div_sum, scaler;   // div_sum here = (32 - sumw) + divSum: shift applied to the pre-scaled window sums (see wmul)
+  int wmul;              // 1 << (32 - sumw): the prefix sums are kept times wmul, so that differences wrap exactly like the
+                         // reference's sumw-bit sum registers (CFARCoreWithMem.scala:34,108,123) in plain 32-bit arithmetic
   int one, m1;           // +1 and -1 as run-time values: multipliers of the IMADs that do the adds on the FMA pipe (see fadd)
   uint32_t thr_mask;     // (1 << thresholdWidth) - 1
   int out_mul;           // 1 << (log2(fftSize) + 1): position of the threshold field in the output beat
@@ -274,7 +276,7 @@ __device__ __forceinline__ int fast_cfar_bin(const FastArgs &a, int j, int tl, i
 }
 
 // detections of one thread: bit (15 - j) of `mask` = peak of bin tl + j * TPC.  Rare path, recomputes from shared memory.
-struct FastDetArgs { int W, G, div_sum, scaler, thr_sext; uint32_t chirp, det_cap; Detection *det_list; uint32_t *det_count; };
+struct FastDetArgs { int W, G, div_sum, scaler, thr_sext;   /* div_sum as in FastArgs */ uint32_t chirp, det_cap; Detection *det_list; uint32_t *det_count; };
 template <int S, int CMODE, bool LINEAR>
 __device__ __noinline__ void fast_detections(const FastDetArgs a, int tl, uint32_t mask, const int *P, const short *X) {
   constexpr int N = 1 << S, TPC = FGeo<S>::TPC;
@@ -283,7 +285,7 @@ __device__ __noinline__ void fast_detections(const FastDetArgs a, int tl, uint32
     const int n = tl + j * TPC, W = a.W, G = a.G;
     const bool lagg_full = (n + G + W <= N - 1), lead_full = (n - G - W >= 0);
     const int hi = min(n + G + W + 1, N), lo = max(n - G - W, 0);
-    const int L = (P[hi] - P[hi - W]) >> a.div_sum, R = (P[lo + W] - P[lo]) >> a.div_sum;
+    const int L = (int)((uint32_t)P[hi] - (uint32_t)P[hi - W]) >> a.div_sum, R = (int)((uint32_t)P[lo + W] - (uint32_t)P[lo]) >> a.div_sum;
     int t = CMODE == 0 ? ((R + L) >> 1) : (CMODE == 1 ? max(L, R) : min(L, R));
     t = lead_full ? (lagg_full ? t : R) : L;
     const int thr = LINEAR ? t * a.scaler : t + a.scaler;
@@ -330,12 +332,12 @@ __global__ void __launch_bounds__(FGeo<S>::THREADS, 1024 / FGeo<S>::THREADS) cha
     }
     int total = 0;
 #pragma unroll
-    for (int k = 0; k < PTS; ++k) total += x[k];
+    for (int k = 0; k < PTS; ++k) total = (int)((uint32_t)x[k] * (uint32_t)a.wmul + (uint32_t)total);   // mod 2^32 on purpose
     int acc = chirp_scan_exclusive<S>(total, c, tl, wsum);
     {
       int pv[PTS];
 #pragma unroll
-      for (int k = 0; k < PTS; ++k) { pv[k] = acc; acc += x[k]; }
+      for (int k = 0; k < PTS; ++k) { pv[k] = acc; acc = (int)((uint32_t)x[k] * (uint32_t)a.wmul + (uint32_t)acc); }
 #pragma unroll
       for (int k = 0; k < PTS; k += 4) *reinterpret_cast<int4 *>(&P[tl * PTS + k]) = make_int4(pv[k], pv[k + 1], pv[k + 2], pv[k + 3]);
       if (tl == TPC - 1) P[N] = acc;
@@ -372,9 +374,9 @@ bool fast_chain_supported(const Plan &pl, const FxArgs &a) {
   if (a.thr_w < 1 || a.thr_w > 32 || a.G < 1 || a.W < 1 || a.div_sum < 0 || a.div_sum > 30) return false;
   const int ej = fast_edge_iters(pl.S, a.W, a.G);
   if (ej > (pl.S == 10 ? 2 : 1)) return false;
-  // the window sums must fit the reference's sum register (no wrap to reproduce) and the scaled threshold must fit 32 bits
-  const long long smax = (long long)a.W * 32768;
-  if (smax > (1LL << (a.sumw - 1))) return false;
+  // the scaled threshold must fit 32 bits (the window sums wrap at sumw bits like the reference's registers, see FastArgs::wmul)
+  if (a.sumw < 2 || a.sumw > 31) return false;
+  const long long smax = std::min<long long>((long long)a.W * 32768, 1LL << (a.sumw - 1));
   const long long tmax = (smax >> a.div_sum) + 1, sc = a.scaler < 0 ? -(long long)a.scaler : a.scaler;
   const long long lim = (1LL << 31) - (1LL << 16);   // the peak is the sign bit of thr - cut
   if (a.log_or_linear ? (tmax * sc >= lim) : (tmax + sc >= lim)) return false;
@@ -416,7 +418,8 @@ rsp_status launch_fast_chain(const Plan &pl, const LaunchCtx &ctx, const FxArgs 
   fa.in = a.in; fa.out = a.out; fa.n_rows = a.n_rows; fa.row_base = a.row_base;
   fa.tw = reinterpret_cast<const int4 *>(a.tw2);
   for (int L = 0; L < 16; ++L) fa.tw_off[L] = a.tw_off[L];
-  fa.W = a.W; fa.G = a.G; fa.div_sum = a.div_sum; fa.scaler = a.scaler; fa.one = 1; fa.m1 = -1;
+  fa.W = a.W; fa.G = a.G; fa.scaler = a.scaler; fa.one = 1; fa.m1 = -1;
+  fa.wmul = (int)(1u << (32 - a.sumw)); fa.div_sum = std::min(31, 32 - a.sumw + a.div_sum);
   fa.thr_mask = a.thr_w >= 32 ? 0xFFFFFFFFu : ((1u << a.thr_w) - 1u);
   fa.out_mul = (int)(1u << (a.binw + 1)); fa.thr_sext = 32 - a.thr_w;
   fa.det_list = a.det_list; fa.det_count = a.det_count; fa.det_cap = a.det_cap;
