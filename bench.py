@@ -110,6 +110,14 @@ class ClockSampler:
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons), "samples": len(sm)}
 
 
+def host_threads():
+    """all host threads this process may use (torchrun exports OMP_NUM_THREADS=1, which is not what the CPU arm wants)"""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except Exception:
+        return max(1, os.cpu_count() or 1)
+
+
 def oracle_setup():
     from oracle import oracle as O
     from oracle.glue import oracle_cfgs
@@ -121,7 +129,7 @@ def oracle_setup():
 def time_oracle(beats, target_s=12.0):
     """all host threads, bounded sample sized to ~target_s of CPU work"""
     O, fft, mag, cfar = oracle_setup()
-    threads = O.max_threads()
+    threads = host_threads()
     probe = beats[:256]
     t0 = time.perf_counter(); O.chain_fixed_words(fft, mag, cfar, probe, n_threads=threads); dt = time.perf_counter() - t0
     rate = probe.size / max(dt, 1e-9)
@@ -147,7 +155,7 @@ def run_reference(args):
     if rank != 0:
         return
     O, fft, mag, cfar = oracle_setup()
-    threads = O.max_threads()
+    threads = host_threads()
     base = host_frames()
     # each step: a bounded sample of the workload (~1.5 s of CPU work)
     t0 = time.perf_counter(); O.chain_fixed_words(fft, mag, cfar, base[:256], n_threads=threads); dt = time.perf_counter() - t0
