@@ -34,6 +34,7 @@ struct rsp_chain {
   uint32_t *d_tw = nullptr;
   int32_t *d_tw2 = nullptr;
   F2 *d_twf = nullptr;
+  float *d_twf4 = nullptr;
   int32_t *d_log_tab = nullptr, *d_nco_tab = nullptr;
   GenSegment *d_segs = nullptr;
   size_t segs_cap = 0;
@@ -108,7 +109,8 @@ static rsp_status launch_f32(rsp_chain *c, const Plan &pl, const F32Args &a, cud
   if (a.n_rows == 0) return RSP_OK;
   const LaunchCtx ctx = {c->device, c->sm_count};
   const char *err = "";
-  const rsp_status s = launch_f32_inst(pl.S, ctx, a, st, &err);
+  const rsp_status s = fast_f32_chain_supported(pl, a) ? launch_fast_f32_chain(pl, ctx, a, reinterpret_cast<const float4 *>(c->d_twf4), st, &err)
+                                                       : launch_f32_inst(pl.S, ctx, a, st, &err);
   if (s != RSP_OK) return fail(s, err);
   ++c->launches;
   return RSP_OK;
@@ -157,7 +159,7 @@ extern "C" void rsp_chain_destroy(rsp_chain *c) {
   cudaSetDevice(c->device);
   free_pipe(c);
   for (int i = 0; i < N_PIPE; ++i) if (c->pipe_stream[i]) cudaStreamDestroy(c->pipe_stream[i]);
-  cudaFree(c->d_tw); cudaFree(c->d_tw2); cudaFree(c->d_twf); cudaFree(c->d_log_tab); cudaFree(c->d_nco_tab); cudaFree(c->d_segs);
+  cudaFree(c->d_tw); cudaFree(c->d_tw2); cudaFree(c->d_twf); cudaFree(c->d_twf4); cudaFree(c->d_log_tab); cudaFree(c->d_nco_tab); cudaFree(c->d_segs);
   cudaFree(c->d_gen_scratch); cudaFree(c->d_det_list); cudaFree(c->d_det_count);
   delete c;
 }
@@ -192,6 +194,7 @@ extern "C" rsp_status rsp_chain_create(const rsp_chain_params *params, int devic
   rsp_status s = upload(c->t.tw, &c->d_tw);
   if (s == RSP_OK) s = upload(c->t.tw2, &c->d_tw2);
   if (s == RSP_OK) s = upload(c->t.twf, &c->d_twf);
+  if (s == RSP_OK) s = upload(c->t.twf4, &c->d_twf4);
   if (s == RSP_OK) s = upload(c->t.log_tab, &c->d_log_tab);
   if (s == RSP_OK) s = upload(c->t.nco_tab, &c->d_nco_tab);
   if (s != RSP_OK) { rsp_chain_destroy(c); return s; }
@@ -562,7 +565,9 @@ extern "C" const char *rsp_variant_name(rsp_chain *c) {
   } else {
     F32Args a;
     if (plan_f32(c->p, c->r, c->t, STAGE_FFT, STAGE_CFAR, a, pl, err) != RSP_OK) { c->variant = "invalid: " + err; return c->variant.c_str(); }
-    std::snprintf(buf, sizeof(buf), "chain_f32<%d>", pl.S);
+    a.out = reinterpret_cast<float *>(c);   // any non-null output: the name is that of the full chain with thresholds requested
+    if (fast_f32_chain_supported(pl, a)) std::snprintf(buf, sizeof(buf), "chain_f32_fast<%d>", pl.S);
+    else std::snprintf(buf, sizeof(buf), "chain_f32<%d>", pl.S);
   }
   c->variant = buf;
   return c->variant.c_str();

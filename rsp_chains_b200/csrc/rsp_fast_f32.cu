@@ -1,0 +1,393 @@
+// rsp_fast_f32.cu -- the specialised fused chain kernel of the fp32 flavour (the generator elaborated with DspReal,
+// generators/sdf-fft/src/main/scala/SDFFFTParams.scala:151-206, run in single precision): forward radix-2^2 DIF transform
+// (SDFChainRadix22.scala:224-352) with natural-order output scaled by 1/N, JPL magnitude (LogMagMux.scala:92-110),
+// CFARCoreWithMem in CA / GO / SO mode with a linear or log threshold (CFARCoreWithMem.scala:102-189); threshold per bin +
+// 1 peak bit per bin out.  Anything else runs on chain_f32_kernel (rsp_kernels.cuh); both are held to the same tolerance
+// against the fp64 oracle (tests/test_gpu_f32_gen.py).
+//
+// This flavour is the one that can reach the HBM roofline (12.125 B and ~55 instructions per sample), so the kernel is
+// written for issue slots and shared-memory wavefronts:
+//  * a point (re, im) lives in one 64-bit register pair and the butterflies are Blackwell's packed fp32 instructions
+//    (FADD2 / FMUL2 / FFMA2, PTX add/mul/fma.f32x2): one instruction per complex add, two per complex twiddle product
+//    ((c, s) * re then (-s, c) * im + acc, the table holds (c, s, -s, c))
+//  * the x(-j) rotation is never executed: the butterfly that consumes a rotated point is written out on the swapped lanes
+//  * three (four) register passes of up to 4 radix-2 stages; between passes the points cross shared memory once, at
+//    index p + 2 (p >> 4) + 4 (p >> 6), which makes every 64-bit and 128-bit access pattern of every pass conflict-free
+//  * the bit reversal is the scatter of the magnitudes; the CFAR window sums are differences of one prefix-sum array that
+//    reuses the exchange buffer; bins are taken interleaved so that loads have immediate offsets and stores are coalesced
+//  * the peak bits of 32 consecutive bins are one warp ballot.
+#include <algorithm>
+
+#include "rsp_fast.cuh"
+
+namespace rsp {
+
+typedef unsigned long long u64;
+
+struct FastF32Args {
+  const u64 *in;           // (re, im) float pairs
+  float *out;              // thresholds (nullable)
+  uint32_t *peak_mask;     // N/32 words per row (nullable)
+  uint32_t n_rows, row_base;
+  const float4 *tw;        // (c, s, -s, c), c + j s = exp(-2 pi j t / stageN); per stageN three runs [W^2k | W^k | W^3k]
+  int tw_off[16];
+  int W, G;
+  float k_both, k_one;     // linear: threshold = comb(L, R) * k_both, one-sided L * k_one; log: comb * k_both + scaler
+  float scaler, inv_n;
+  Detection *det_list;
+  uint32_t *det_count;
+  uint32_t det_cap;
+};
+
+template <int S> struct FGeoF {
+  static constexpr int N = 1 << S;
+  static constexpr int PTS = 16;
+  static constexpr int TPC = N / PTS;                         // threads per chirp
+  static constexpr int CPC = TPC >= 128 ? 1 : 128 / TPC;      // chirps per CTA
+  static constexpr int THREADS = TPC * CPC;
+  static constexpr int XB = N + (N >> 3) + (N >> 4) + 8;      // u64 elements of the exchange buffer, index xidx(p)
+  static constexpr int MG = N + (N >> 3) + 8;                 // floats of the magnitude array, index midx(n)
+  static constexpr size_t ROW_BYTES = (size_t)XB * 8 + (size_t)MG * 4;
+  static constexpr int NW = TPC / 32;                         // warps per chirp
+  static constexpr int MASKW = N / 32;
+  static constexpr int JSTEP = TPC + (TPC >> 3);              // midx(n + TPC) - midx(n)
+};
+
+__device__ __forceinline__ int xidx(int p) { return p + ((p >> 4) << 1) + ((p >> 6) << 2); }
+__device__ __forceinline__ int midx(int n) { return n + ((n >> 5) << 2); }
+
+__device__ __forceinline__ u64 pk2(float lo, float hi) { u64 r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi)); return r; }
+__device__ __forceinline__ void upk2(u64 v, float &lo, float &hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
+__device__ __forceinline__ u64 add2(u64 a, u64 b) { u64 r; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ u64 sub2(u64 a, u64 b) { u64 r; asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ u64 mul2(u64 a, u64 b) { u64 r; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
+__device__ __forceinline__ u64 fma2(u64 a, u64 b, u64 c) { u64 r; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c)); return r; }
+
+// a <- a + c, c <- a - c
+__device__ __forceinline__ void bf_plain(u64 &a, u64 &c) { const u64 s = add2(a, c), d = sub2(a, c); a = s; c = d; }
+// the same with c standing for -j c = (c.im, -c.re) (SDFChainRadix22.scala:319-337: the rotation after an even stage)
+__device__ __forceinline__ void bf_rot(u64 &a, u64 &c) {
+  float ar, ai, cr, ci;
+  upk2(a, ar, ai); upk2(c, cr, ci);
+  a = pk2(ar + ci, ai - cr);
+  c = pk2(ar - ci, ai + cr);
+}
+// x <- x * (c + j s), w = (c, s, -s, c)
+__device__ __forceinline__ u64 cmul(u64 x, const float4 w) {
+  float xr, xi;
+  upk2(x, xr, xi);
+  return fma2(pk2(xi, xi), pk2(w.z, w.w), mul2(pk2(xr, xr), pk2(w.x, w.y)));
+}
+// JPL magnitude approximation (LogMagMux.scala:92-110) of two points at once, times `sc` (a power of two: the 1/N of the
+// scale-every-stage transform): max(u + v/8, 7u/8 + v/2) with u = max(|re|, |im|), v = min(|re|, |im|)
+__device__ __forceinline__ void jpl2_scaled(u64 z0, u64 z1, float sc, float &m0, float &m1) {
+  float r0, i0, r1, i1;
+  upk2(z0, r0, i0); upk2(z1, r1, i1);
+  const u64 u = pk2(fmaxf(fabsf(r0), fabsf(i0)), fmaxf(fabsf(r1), fabsf(i1)));
+  const u64 v = pk2(fminf(fabsf(r0), fabsf(i0)), fminf(fabsf(r1), fabsf(i1)));
+  const u64 x = fma2(v, pk2(0.125f, 0.125f), u);
+  const u64 y = fma2(v, pk2(0.5f, 0.5f), mul2(u, pk2(0.875f, 0.875f)));
+  float x0, x1, y0, y1;
+  upk2(x, x0, x1); upk2(y, y0, y1);
+  const u64 mm = mul2(pk2(fmaxf(x0, y0), fmaxf(x1, y1)), pk2(sc, sc));
+  upk2(mm, m0, m1);
+}
+
+constexpr int xoff_c(int p) { return p + ((p >> 4) << 1) + ((p >> 6) << 2); }   // xidx of a compile-time offset
+constexpr int moff_c(int n) { return n + ((n >> 5) << 2); }
+
+// One pass = m radix-2 stages in registers on 2^m points Dl apart (the decomposition of rsp_device.cuh, fx_pass_*).
+// Thread tl of the chirp works on the groups vt = g * TPC + tl, so a warp touches consecutive points in every pass.
+// Every shared-memory address is one run-time base plus a compile-time offset: xidx(base + g * TPC * R + rr * Dl) =
+// xidx(base) + xidx(g * TPC * R + rr * Dl) for all the shapes used here (checked exhaustively, tests/test_abi_host.py).
+template <int S, int K>
+__device__ __forceinline__ void f32_pass(const FastF32Args &a, int tl, const u64 (&pre)[16], u64 *xb, float *mg) {
+  using Gm = FGeoF<S>;
+  constexpr int m = fx_pass_size(S, K), i0 = fx_pass_start(S, K), LDl = S - i0 - m, Dl = 1 << LDl;
+  constexpr int PTS = Gm::PTS, G = PTS >> m, R = 1 << m, TPC = Gm::TPC;
+  constexpr bool first = (K == 0), last = (K == fx_n_passes(S) - 1);
+  static_assert((i0 & 1) == 0, "passes start on even stages");
+  static_assert(!last || Dl == 1, "the last pass works on neighbouring points");
+  float mags[last ? PTS : 1];
+  const int low = tl & (Dl - 1);
+  const int base0 = ((tl >> LDl) << (m + LDl)) | low;        // group g starts at base0 + g * TPC * R
+  u64 *xp = xb + xidx(base0);
+#pragma unroll
+  for (int g = 0; g < G; ++g) {
+    u64 z[R];
+    if (first) {
+#pragma unroll
+      for (int rr = 0; rr < R; ++rr) z[rr] = pre[rr];        // m = 4, one group, p = tl + rr * TPC
+    } else if (last) {                                        // 2^m neighbouring points: 128-bit loads
+#pragma unroll
+      for (int rr = 0; rr < R; rr += 2) {
+        const ulonglong2 v = *reinterpret_cast<const ulonglong2 *>(&xp[xoff_c(g * TPC * R + rr)]);
+        z[rr] = v.x; z[rr + 1] = v.y;
+      }
+    } else {
+#pragma unroll
+      for (int rr = 0; rr < R; ++rr) z[rr] = xp[xoff_c(g * TPC * R + rr * Dl)];
+    }
+#pragma unroll
+    for (int s = 0; s < m; ++s) {
+      const int i = i0 + s;
+      const int dist = 1 << (m - 1 - s);
+#pragma unroll
+      for (int rr = 0; rr < R; ++rr)
+        if (!(rr & dist)) {
+          // odd stage: the partner was the difference output of the previous stage's butterfly (bit 2 dist of rr) and sits
+          // in the last quarter of its 4 dist block -> it carries the pending x(-j)
+          const bool rot = (i & 1) && (rr & (dist << 1));
+          if (rot) bf_rot(z[rr], z[rr + dist]); else bf_plain(z[rr], z[rr + dist]);
+        }
+      if (i == S - 1 || (i & 1) == 0) continue;
+      const int L = S - i + 1;
+      const int q = 1 << (L - 2);
+      const float4 *tab = a.tw + a.tw_off[L] + low;
+#pragma unroll
+      for (int rr = 0; rr < R; ++rr) {
+        const int quarter = ((rr >> (m - 1 - s)) & 1) + 2 * ((rr >> (m - s)) & 1);
+        if (quarter) {
+          const int k = (rr & (dist - 1)) * Dl;
+          const int slot = quarter == 1 ? 0 : (quarter == 2 ? 1 : 2);
+          z[rr] = cmul(z[rr], __ldg(&tab[slot * q + k]));
+        }
+      }
+    }
+    if (!last) {
+#pragma unroll
+      for (int rr = 0; rr < R; ++rr) xp[xoff_c(g * TPC * R + rr * Dl)] = z[rr];
+    } else {
+#pragma unroll
+      for (int rr = 0; rr < R; rr += 2) jpl2_scaled(z[rr], z[rr + 1], a.inv_n, mags[g * R + rr], mags[g * R + rr + 1]);
+    }
+  }
+  if (last) {
+    // bin of point p = (vt << m) + rr is bitrev_S(p) = rev_m(rr) << (S - m) | rev_{S-4}(tl) << (4 - m) | rev_{4-m}(g):
+    // for a fixed rr the G groups of the thread are G neighbouring bins -> one G-float store per rr
+    const uint32_t rtl = (__brev((uint32_t)tl) >> (32 - (S - 4))) << (4 - m);
+    float *mp = mg + midx((int)rtl);
+#pragma unroll
+    for (int rr = 0; rr < R; ++rr) {
+      constexpr int SH = S - m;
+      const int rrr = (int)((__brev((uint32_t)rr) >> (32 - m)) << SH);   // compile-time, a multiple of 32
+      float *dst = mp + rrr + ((rrr >> 5) << 2);
+      if (G == 4) *reinterpret_cast<float4 *>(dst) = make_float4(mags[0 * R + rr], mags[2 * R + rr], mags[1 * R + rr], mags[3 * R + rr]);
+      else if (G == 2) *reinterpret_cast<float2 *>(dst) = make_float2(mags[0 * R + rr], mags[1 * R + rr]);
+      else *dst = mags[rr];
+    }
+  }
+}
+
+template <int S, int K>
+__device__ __forceinline__ void f32_passes(const FastF32Args &a, int tl, const u64 (&pre)[16], u64 *xb, float *mg) {
+  static_assert(K != 0 || fx_pass_size(S, 0) == 4, "the first pass takes the 16 prefetched points of the thread");
+  f32_pass<S, K>(a, tl, pre, xb, mg);
+  __syncthreads();
+  if constexpr (K + 1 < fx_n_passes(S)) f32_passes<S, K + 1>(a, tl, pre, xb, mg);
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// CFAR (CFARCoreWithMem.scala:102-189).  P[n] = sum of x[0..n-1] lives in the exchange buffer (dead after the last FFT pass);
+// lagging sum of bin n = P[n+G+W+1] - P[n+G+1], leading sum = P[n-G] - P[n-G-W].
+
+// exclusive prefix of `total` over the TPC threads of one chirp: warp scan, then a warp scan of the warp totals
+template <int S>
+__device__ __forceinline__ float chirp_scan_exclusive_f32(float total, int c, int tl, float *wsum) {
+  constexpr int NW = FGeoF<S>::NW;
+  const int lane = tl & 31;
+  float incl = total;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) {
+    const float v = __shfl_up_sync(0xffffffffu, incl, d);
+    if (lane >= d) incl += v;
+  }
+  const int w = tl >> 5;
+  if (lane == 31) wsum[c * NW + w] = incl;
+  __syncthreads();
+  float wv = lane < NW ? wsum[c * NW + lane] : 0.f;
+#pragma unroll
+  for (int d = 1; d < NW; d <<= 1) {
+    const float v = __shfl_up_sync(0xffffffffu, wv, d);
+    if (lane >= d) wv += v;
+  }
+  const float upto = __shfl_sync(0xffffffffu, wv, w > 0 ? w - 1 : 0);   // inclusive sum of the warps before this one
+  return (w > 0 ? upto : 0.f) + (incl - total);
+}
+
+// threshold from the two window sums, explicit roundings so that the detection path reproduces the hot loop bit for bit
+template <int CMODE, bool LINEAR, typename A>
+__device__ __forceinline__ float f32_threshold(const A &a, float L, float R, bool lagg_full, bool lead_full) {
+  float comb = CMODE == 0 ? __fadd_rn(L, R) : (CMODE == 1 ? fmaxf(L, R) : fminf(L, R));
+  float k = a.k_both;
+  if (!(lagg_full && lead_full)) { comb = lead_full ? R : (lagg_full ? L : 0.f); k = a.k_one; }
+  return LINEAR ? __fmul_rn(comb, k) : __fmaf_rn(comb, k, a.scaler);
+}
+
+// detections of one thread: bit j of `mask` = peak of bin tl + j * TPC.  Rare path, recomputes from shared memory.
+struct FastF32DetArgs { int W, G; float k_both, k_one, scaler; uint32_t chirp, mask, det_cap; Detection *det_list; uint32_t *det_count; };
+template <int S, int CMODE, bool LINEAR>
+__device__ __noinline__ void f32_detections(const FastF32DetArgs a, int tl, const float *P, const float *X) {
+  constexpr int N = 1 << S, TPC = FGeoF<S>::TPC;
+  for (int j = 0; j < 16; ++j) {
+    if (!((a.mask >> j) & 1u)) continue;
+    const int n = tl + j * TPC, W = a.W, G = a.G;
+    const bool lagg_full = (n + G + W <= N - 1), lead_full = (n - G - W >= 0);
+    const int hi = min(n + G + W + 1, N), lo = max(n - G - W, 0);
+    const float L = __fsub_rn(P[midx(hi)], P[midx(hi - W)]), R = __fsub_rn(P[midx(lo + W)], P[midx(lo)]);
+    const float thr = f32_threshold<CMODE, LINEAR>(a, L, R, lagg_full, lead_full);
+    const uint32_t slot = atomicAdd(a.det_count, 1u);
+    if (slot < a.det_cap) {
+      Detection d; d.chirp = a.chirp; d.bin = (uint32_t)n; d.threshold = __float_as_int(thr); d.cut = __float_as_int(X[midx(n)]);
+      a.det_list[slot] = d;
+    }
+  }
+}
+
+// EJ = number of leading / trailing iterations j whose bins may miss a window (ceil((W + G) / TPC), checked by the host)
+template <int S, int CMODE, bool LINEAR, int EJ>
+__global__ void __launch_bounds__(FGeoF<S>::THREADS, (1024 / FGeoF<S>::THREADS) > 7 ? 7 : (1024 / FGeoF<S>::THREADS))
+chain_f32_fast_kernel(const FastF32Args a) {
+  using Gm = FGeoF<S>;
+  constexpr int N = Gm::N, TPC = Gm::TPC, CPC = Gm::CPC, PTS = Gm::PTS, JSTEP = Gm::JSTEP;
+  extern __shared__ __align__(16) unsigned char smem_raw[];
+  __shared__ float wsum[CPC * Gm::NW];
+  const int c = threadIdx.x / TPC, tl = threadIdx.x % TPC;
+  u64 *xb = reinterpret_cast<u64 *>(smem_raw + (size_t)c * Gm::ROW_BYTES);
+  float *mg = reinterpret_cast<float *>(xb + Gm::XB);
+  float *P = reinterpret_cast<float *>(xb);
+  const float *pA = P + midx(tl + a.G + a.W + 1), *pB = P + midx(tl + a.G + 1);
+  // the leading borders of the first iterations are negative: only dereferenced from j >= EJ on, where the index is >= 0
+  const int iC = tl - a.G + EJ * TPC, iD = tl - a.G - a.W + EJ * TPC;
+  const float *pC = P + midx(iC) - EJ * JSTEP, *pD = P + midx(iD) - EJ * JSTEP;
+  const float *pX = mg + midx(tl);
+  const float *pX16 = mg + midx(tl * PTS);   // the thread's 16 neighbouring bins: midx(16 tl + k) = midx(16 tl) + k
+  float *pP16 = P + midx(tl * PTS);
+  const uint32_t stride = gridDim.x * CPC;
+  for (uint32_t row0 = blockIdx.x * CPC; row0 < a.n_rows; row0 += stride) {
+    const bool active = row0 + c < a.n_rows;
+    const uint32_t row = active ? row0 + c : a.n_rows - 1;
+    u64 pre[PTS];   // the thread's 16 points of the row: p = tl + rr * TPC, warp-contiguous 256-byte runs
+    {
+      const u64 *gin = a.in + (size_t)row * N + tl;
+#pragma unroll
+      for (int rr = 0; rr < PTS; ++rr) pre[rr] = __ldg(&gin[rr * TPC]);
+    }
+    f32_passes<S, 0>(a, tl, pre, xb, mg);
+    // prefix sums of the thread's 16 neighbouring magnitudes
+    float x[PTS];
+#pragma unroll
+    for (int k = 0; k < PTS; k += 4) {
+      const float4 v = *reinterpret_cast<const float4 *>(&pX16[k]);
+      x[k] = v.x; x[k + 1] = v.y; x[k + 2] = v.z; x[k + 3] = v.w;
+    }
+    float total = 0.f;
+#pragma unroll
+    for (int k = 0; k < PTS; ++k) total += x[k];
+    float acc = chirp_scan_exclusive_f32<S>(total, c, tl, wsum);
+    {
+      float pv[PTS];
+#pragma unroll
+      for (int k = 0; k < PTS; ++k) { pv[k] = acc; acc += x[k]; }
+#pragma unroll
+      for (int k = 0; k < PTS; k += 4) *reinterpret_cast<float4 *>(&pP16[k]) = make_float4(pv[k], pv[k + 1], pv[k + 2], pv[k + 3]);
+      if (tl == TPC - 1) P[midx(N)] = acc;
+    }
+    __syncthreads();
+    float *gout = a.out ? a.out + (size_t)row * N + tl : nullptr;
+    uint32_t *gmask = a.peak_mask ? a.peak_mask + (size_t)row * Gm::MASKW + (tl >> 5) : nullptr;
+    uint32_t mask = 0;
+#pragma unroll
+    for (int j = 0; j < PTS; ++j) {
+      float L, R;
+      bool lagg_full = true, lead_full = true;
+      if (j < EJ || j >= PTS - EJ) {
+        const int n = tl + j * TPC, W = a.W, G = a.G;
+        lagg_full = (n + G + W <= N - 1); lead_full = (n - G - W >= 0);
+        const int hi = min(n + G + W + 1, N), lo = max(n - G - W, 0);
+        L = __fsub_rn(P[midx(hi)], P[midx(hi - W)]); R = __fsub_rn(P[midx(lo + W)], P[midx(lo)]);
+      } else {
+        L = __fsub_rn(pA[j * JSTEP], pB[j * JSTEP]); R = __fsub_rn(pC[j * JSTEP], pD[j * JSTEP]);
+      }
+      const float thr = f32_threshold<CMODE, LINEAR>(a, L, R, lagg_full, lead_full);
+      const bool pk = pX[j * JSTEP] > thr;
+      if (gout) gout[j * TPC] = thr;
+      const uint32_t word = __ballot_sync(0xffffffffu, pk);
+      if (gmask && (tl & 31) == 0) gmask[j * (TPC / 32)] = word;
+      mask |= (pk ? 1u : 0u) << j;
+    }
+    if (mask != 0 && a.det_list != nullptr && active) {
+      const FastF32DetArgs da = {a.W, a.G, a.k_both, a.k_one, a.scaler, a.row_base + row, mask, a.det_cap, a.det_list, a.det_count};
+      f32_detections<S, CMODE, LINEAR>(da, tl, P, mg);
+    }
+    __syncthreads();
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// host side
+static int f32_edge_iters(int S, int W, int G) { const int tpc = (1 << S) / 16; return (W + G + tpc - 1) / tpc; }
+
+bool fast_f32_chain_supported(const Plan &pl, const F32Args &a) {
+  if (pl.first_stage != STAGE_FFT || pl.last_stage != STAGE_CFAR) return false;
+  if (pl.S < RSP_FAST_SMIN || pl.S > RSP_FAST_SMAX) return false;
+  if (!a.bitrev || a.fft_dir != 1 || a.sel != 2) return false;
+  if (a.core != CORE_MEM || a.send_cut || a.peak_grouping) return false;
+  if (a.G < 1 || a.W < 1 || a.div_sum < 0 || a.div_sum > 30) return false;
+  if (f32_edge_iters(pl.S, a.W, a.G) > (pl.S == 10 ? 2 : 1)) return false;
+  return a.out != nullptr || a.peak_mask != nullptr || a.det_list != nullptr;
+}
+
+template <int S, int CMODE, bool LINEAR, int EJ>
+static rsp_status launch_f32_fast_inst(const LaunchCtx &c, const FastF32Args &fa, cudaStream_t st, const char **err) {
+  using Gm = FGeoF<S>;
+  static int occ_dev[64] = {0};
+  int &occ = occ_dev[c.device & 63];
+  const size_t smem = (size_t)Gm::CPC * Gm::ROW_BYTES;
+  auto kernel = chain_f32_fast_kernel<S, CMODE, LINEAR, EJ>;
+  if (!occ) { const rsp_status s = launch_cfg(kernel, smem, Gm::THREADS, &occ, err); if (s != RSP_OK) return s; }
+  const unsigned groups = (fa.n_rows + Gm::CPC - 1) / Gm::CPC;
+  const unsigned grid = std::max(1u, std::min(groups, (unsigned)(c.sm_count * occ)));
+  kernel<<<grid, Gm::THREADS, smem, st>>>(fa);
+  if (cudaGetLastError() != cudaSuccess) { *err = "chain_f32_fast_kernel launch failed"; return RSP_ECUDA; }
+  return RSP_OK;
+}
+
+template <int S, int EJ>
+static rsp_status launch_f32_fast_modes(int cmode, bool linear, const LaunchCtx &c, const FastF32Args &fa, cudaStream_t st, const char **err) {
+  if (linear) switch (cmode) {
+    case 0: return launch_f32_fast_inst<S, 0, true, EJ>(c, fa, st, err);
+    case 1: return launch_f32_fast_inst<S, 1, true, EJ>(c, fa, st, err);
+    default: return launch_f32_fast_inst<S, 2, true, EJ>(c, fa, st, err);
+  }
+  switch (cmode) {
+    case 0: return launch_f32_fast_inst<S, 0, false, EJ>(c, fa, st, err);
+    case 1: return launch_f32_fast_inst<S, 1, false, EJ>(c, fa, st, err);
+    default: return launch_f32_fast_inst<S, 2, false, EJ>(c, fa, st, err);
+  }
+}
+
+rsp_status launch_fast_f32_chain(const Plan &pl, const LaunchCtx &ctx, const F32Args &a, const float4 *tw4, cudaStream_t st, const char **err) {
+  FastF32Args fa;
+  fa.in = reinterpret_cast<const u64 *>(a.in); fa.out = a.out; fa.peak_mask = a.peak_mask; fa.n_rows = a.n_rows; fa.row_base = a.row_base;
+  fa.tw = tw4;
+  for (int L = 0; L < 16; ++L) fa.tw_off[L] = a.tw_off[L];
+  fa.W = a.W; fa.G = a.G; fa.scaler = a.scaler; fa.inv_n = 1.0f / (float)(1 << pl.S);
+  const int cmode = a.cfar_mode == 0 ? 0 : (a.cfar_mode == 1 ? 1 : 2);   // MuxLookup default: smallestOf (CFARCoreWithMem.scala:138-141)
+  const bool linear = a.log_or_linear != 0;
+  const float both = cmode == 0 ? 0.5f * a.inv_div : a.inv_div;            // CA: (L + R) / 2 (CFARCoreWithMem.scala:135-137)
+  fa.k_both = linear ? both * a.scaler : both;
+  fa.k_one = linear ? a.inv_div * a.scaler : a.inv_div;
+  fa.det_list = a.det_list; fa.det_count = a.det_count; fa.det_cap = a.det_cap;
+  const int ej = f32_edge_iters(pl.S, a.W, a.G);
+  switch (pl.S) {
+  case 10: return ej == 2 ? launch_f32_fast_modes<10, 2>(cmode, linear, ctx, fa, st, err) : launch_f32_fast_modes<10, 1>(cmode, linear, ctx, fa, st, err);
+  case 11: return launch_f32_fast_modes<11, 1>(cmode, linear, ctx, fa, st, err);
+  case 12: return launch_f32_fast_modes<12, 1>(cmode, linear, ctx, fa, st, err);
+  case 13: return launch_f32_fast_modes<13, 1>(cmode, linear, ctx, fa, st, err);
+  case 14: return launch_f32_fast_modes<14, 1>(cmode, linear, ctx, fa, st, err);
+  default: *err = "no fast fp32 variant for this size"; return RSP_EUNSUPPORTED;
+  }
+}
+
+}  // namespace rsp

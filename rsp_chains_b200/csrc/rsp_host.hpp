@@ -34,6 +34,7 @@ struct Regs {
 struct Tables {
   std::vector<uint32_t> tw;   // fixed twiddles, packed (cos16 << 16 | sin16 & 0xFFFF); per stageN three runs [W^2k | W^k | W^3k]
   std::vector<F2> twf;        // fp32 twiddles, same layout
+  std::vector<float> twf4;    // fp32 twiddles again as (c, s, -s, c) quads: the two operands of the packed complex product (rsp_fast_f32.cu)
   std::vector<int32_t> tw2;   // fixed twiddles again as int32 quads (c, s, -c, -s) << (16 - (twiddleWidth - 2)): the fast kernels'
                               // product then carries its rounded, wrapped result in bits 16..31 (rsp_fast.cu)
   int tw_off[16];
@@ -190,7 +191,7 @@ inline uint32_t *reg_slot(Regs &r, rsp_block blk, uint32_t idx) {
 inline void build_tables(const rsp_chain_params &p, Tables &t) {
   const int Smax = log2_ceil((uint32_t)p.fft.numPoints);
   const int tww = p.fft.twiddleWidth, twbp = tww - 2;
-  t.tw.clear(); t.twf.clear(); t.tw2.clear();
+  t.tw.clear(); t.twf.clear(); t.tw2.clear(); t.twf4.clear();
   const int pre = 16 - twbp > 0 ? 16 - twbp : 0;
   for (int L = 0; L < 16; ++L) t.tw_off[L] = 0;
   const double PI = 3.14159265358979323846;  // scala.math.Pi
@@ -209,9 +210,11 @@ inline void build_tables(const rsp_chain_params &p, Tables &t) {
         t.tw2.push_back(c4); t.tw2.push_back(s4); t.tw2.push_back(-c4); t.tw2.push_back(-s4);
         F2 f; f.x = (float)c; f.y = (float)s;
         t.twf.push_back(f);
+        t.twf4.push_back(f.x); t.twf4.push_back(f.y); t.twf4.push_back(-f.y); t.twf4.push_back(f.x);
       }
   }
-  if (t.tw.empty()) { t.tw.push_back(0); for (int z = 0; z < 4; ++z) t.tw2.push_back(0); F2 f; f.x = 1.f; f.y = 0.f; t.twf.push_back(f); }
+  if (t.tw.empty()) { t.tw.push_back(0); for (int z = 0; z < 4; ++z) t.tw2.push_back(0); F2 f; f.x = 1.f; f.y = 0.f; t.twf.push_back(f);
+                      t.twf4.push_back(1.f); t.twf4.push_back(0.f); t.twf4.push_back(0.f); t.twf4.push_back(1.f); }
   // log2 LUT (LogMagMux.scala:120-131)
   const int Lw = p.mag.log2LookUpWidth, num = 1 << Lw;
   t.log_tab.resize((size_t)num);
