@@ -78,6 +78,12 @@ __device__ __forceinline__ u64 cmul(u64 x, const float4 w) {
   upk2(x, xr, xi);
   return fma2(pk2(xi, xi), pk2(w.z, w.w), mul2(pk2(xr, xr), pk2(w.x, w.y)));
 }
+// x <- x * w with w given as its two operand pairs A = (c, s), B = (-s, c)
+__device__ __forceinline__ u64 cmul2(u64 x, u64 A, u64 B) {
+  float xr, xi;
+  upk2(x, xr, xi);
+  return fma2(pk2(xi, xi), B, mul2(pk2(xr, xr), A));
+}
 // JPL magnitude approximation (LogMagMux.scala:92-110) of two points at once, times `sc` (a power of two: the 1/N of the
 // scale-every-stage transform): max(u + v/8, 7u/8 + v/2) with u = max(|re|, |im|), v = min(|re|, |im|)
 __device__ __forceinline__ void jpl2_scaled(u64 z0, u64 z1, float sc, float &m0, float &m1) {
@@ -143,14 +149,22 @@ __device__ __forceinline__ void f32_pass(const FastF32Args &a, int tl, const u64
       if (i == S - 1 || (i & 1) == 0) continue;
       const int L = S - i + 1;
       const int q = 1 << (L - 2);
-      const float4 *tab = a.tw + a.tw_off[L] + low;
+      // one table read per distinct k: W^k with both operand pairs A = (c, s), B = (-s, c); W^2k = W^k W^k and
+      // W^3k = W^2k W^k follow by the same packed product (B' = j W' = (j W) W), which saves two thirds of the loads
+      const float4 *tab = a.tw + a.tw_off[L] + q + low;       // the W^k run
 #pragma unroll
-      for (int rr = 0; rr < R; ++rr) {
-        const int quarter = ((rr >> (m - 1 - s)) & 1) + 2 * ((rr >> (m - s)) & 1);
-        if (quarter) {
-          const int k = (rr & (dist - 1)) * Dl;
-          const int slot = quarter == 1 ? 0 : (quarter == 2 ? 1 : 2);
-          z[rr] = cmul(z[rr], __ldg(&tab[slot * q + k]));
+      for (int kk = 0; kk < dist; ++kk) {
+        const float4 w1 = __ldg(&tab[kk * Dl]);
+        const u64 A1 = pk2(w1.x, w1.y), B1 = pk2(w1.z, w1.w);
+        const u64 A2 = cmul2(A1, A1, B1), B2 = cmul2(B1, A1, B1);
+        const u64 A3 = cmul2(A2, A1, B1), B3 = cmul2(B2, A1, B1);
+#pragma unroll
+        for (int rr = 0; rr < R; ++rr) {
+          if ((rr & (dist - 1)) != kk) continue;
+          const int quarter = ((rr >> (m - 1 - s)) & 1) + 2 * ((rr >> (m - s)) & 1);
+          if (quarter == 1) z[rr] = cmul2(z[rr], A2, B2);
+          else if (quarter == 2) z[rr] = cmul2(z[rr], A1, B1);
+          else if (quarter == 3) z[rr] = cmul2(z[rr], A3, B3);
         }
       }
     }
@@ -188,32 +202,7 @@ __device__ __forceinline__ void f32_passes(const FastF32Args &a, int tl, const u
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
-// CFAR (CFARCoreWithMem.scala:102-189).  P[n] = sum of x[0..n-1] lives in the exchange buffer (dead after the last FFT pass);
-// lagging sum of bin n = P[n+G+W+1] - P[n+G+1], leading sum = P[n-G] - P[n-G-W].
-
-// exclusive prefix of `total` over the TPC threads of one chirp: warp scan, then a warp scan of the warp totals
-template <int S>
-__device__ __forceinline__ float chirp_scan_exclusive_f32(float total, int c, int tl, float *wsum) {
-  constexpr int NW = FGeoF<S>::NW;
-  const int lane = tl & 31;
-  float incl = total;
-#pragma unroll
-  for (int d = 1; d < 32; d <<= 1) {
-    const float v = __shfl_up_sync(0xffffffffu, incl, d);
-    if (lane >= d) incl += v;
-  }
-  const int w = tl >> 5;
-  if (lane == 31) wsum[c * NW + w] = incl;
-  __syncthreads();
-  float wv = lane < NW ? wsum[c * NW + lane] : 0.f;
-#pragma unroll
-  for (int d = 1; d < NW; d <<= 1) {
-    const float v = __shfl_up_sync(0xffffffffu, wv, d);
-    if (lane >= d) wv += v;
-  }
-  const float upto = __shfl_sync(0xffffffffu, wv, w > 0 ? w - 1 : 0);   // inclusive sum of the warps before this one
-  return (w > 0 ? upto : 0.f) + (incl - total);
-}
+// CFAR (CFARCoreWithMem.scala:102-189): lagging window of bin n = [n+G+1, n+G+W], leading window = [n-G-W, n-G-1].
 
 // threshold from the two window sums, explicit roundings so that the detection path reproduces the hot loop bit for bit
 template <int CMODE, bool LINEAR, typename A>
@@ -227,14 +216,14 @@ __device__ __forceinline__ float f32_threshold(const A &a, float L, float R, boo
 // detections of one thread: bit j of `mask` = peak of bin tl + j * TPC.  Rare path, recomputes from shared memory.
 struct FastF32DetArgs { int W, G; float k_both, k_one, scaler; uint32_t chirp, mask, det_cap; Detection *det_list; uint32_t *det_count; };
 template <int S, int CMODE, bool LINEAR>
-__device__ __noinline__ void f32_detections(const FastF32DetArgs a, int tl, const float *P, const float *X) {
+__device__ __noinline__ void f32_detections(const FastF32DetArgs a, int tl, const float *QP, const float *AS, const float *X) {
   constexpr int N = 1 << S, TPC = FGeoF<S>::TPC;
   for (int j = 0; j < 16; ++j) {
     if (!((a.mask >> j) & 1u)) continue;
     const int n = tl + j * TPC, W = a.W, G = a.G;
     const bool lagg_full = (n + G + W <= N - 1), lead_full = (n - G - W >= 0);
     const int hi = min(n + G + W + 1, N), lo = max(n - G - W, 0);
-    const float L = __fsub_rn(P[midx(hi)], P[midx(hi - W)]), R = __fsub_rn(P[midx(lo + W)], P[midx(lo)]);
+    const float L = __fadd_rn(AS[hi - W], QP[hi]), R = __fadd_rn(AS[lo], QP[lo + W]);
     const float thr = f32_threshold<CMODE, LINEAR>(a, L, R, lagg_full, lead_full);
     const uint32_t slot = atomicAdd(a.det_count, 1u);
     if (slot < a.det_cap) {
@@ -251,18 +240,19 @@ chain_f32_fast_kernel(const FastF32Args a) {
   using Gm = FGeoF<S>;
   constexpr int N = Gm::N, TPC = Gm::TPC, CPC = Gm::CPC, PTS = Gm::PTS, JSTEP = Gm::JSTEP;
   extern __shared__ __align__(16) unsigned char smem_raw[];
-  __shared__ float wsum[CPC * Gm::NW];
   const int c = threadIdx.x / TPC, tl = threadIdx.x % TPC;
   u64 *xb = reinterpret_cast<u64 *>(smem_raw + (size_t)c * Gm::ROW_BYTES);
   float *mg = reinterpret_cast<float *>(xb + Gm::XB);
-  float *P = reinterpret_cast<float *>(xb);
-  const float *pA = P + midx(tl + a.G + a.W + 1), *pB = P + midx(tl + a.G + 1);
+  // QP, AS and the block totals (+ 8 zeros for the blocks past the end of the row) reuse the exchange buffer, dead after the last FFT pass
+  float *QP = reinterpret_cast<float *>(xb), *AS = QP + N + 16, *tsum = AS + N;
+  static_assert((size_t)(2 * N + 16 + TPC + 8) * 4 <= (size_t)Gm::XB * 8, "the CFAR arrays fit the exchange buffer");
   // the leading borders of the first iterations are negative: only dereferenced from j >= EJ on, where the index is >= 0
-  const int iC = tl - a.G + EJ * TPC, iD = tl - a.G - a.W + EJ * TPC;
-  const float *pC = P + midx(iC) - EJ * JSTEP, *pD = P + midx(iD) - EJ * JSTEP;
+  const float *pA = AS + (tl + a.G + 1), *pB = QP + (tl + a.G + a.W + 1), *pC = AS + (tl - a.G - a.W), *pD = QP + (tl - a.G);
+  const int nblk = a.W >> 4;
   const float *pX = mg + midx(tl);
   const float *pX16 = mg + midx(tl * PTS);   // the thread's 16 neighbouring bins: midx(16 tl + k) = midx(16 tl) + k
-  float *pP16 = P + midx(tl * PTS);
+  float *pP16 = QP + tl * PTS, *pS16 = AS + tl * PTS;
+  const int prot = (tl >> 1) & 3;
   const uint32_t stride = gridDim.x * CPC;
   for (uint32_t row0 = blockIdx.x * CPC; row0 < a.n_rows; row0 += stride) {
     const bool active = row0 + c < a.n_rows;
@@ -274,24 +264,55 @@ chain_f32_fast_kernel(const FastF32Args a) {
       for (int rr = 0; rr < PTS; ++rr) pre[rr] = __ldg(&gin[rr * TPC]);
     }
     f32_passes<S, 0>(a, tl, pre, xb, mg);
-    // prefix sums of the thread's 16 neighbouring magnitudes
+    // window sums without a row-wide prefix (which would lose the noise floor behind a strong target in fp32): bins are
+    // cut into the threads' blocks of 16; QP[n] = sum of the block of n before n, AS[n] = sum of the block of n from n on
+    // plus the W/16 - 1 blocks that follow.  A window [a, a + W) with W a multiple of 16 is AS[a] + QP[a + W]: additions
+    // of non-negative terms only, every partial sum no larger than the window's own.
     float x[PTS];
 #pragma unroll
     for (int k = 0; k < PTS; k += 4) {
       const float4 v = *reinterpret_cast<const float4 *>(&pX16[k]);
       x[k] = v.x; x[k + 1] = v.y; x[k + 2] = v.z; x[k + 3] = v.w;
     }
-    float total = 0.f;
+    float sv[PTS];
+    sv[PTS - 1] = x[PTS - 1];
 #pragma unroll
-    for (int k = 0; k < PTS; ++k) total += x[k];
-    float acc = chirp_scan_exclusive_f32<S>(total, c, tl, wsum);
+    for (int k = PTS - 2; k >= 0; --k) sv[k] = sv[k + 1] + x[k];
+    tsum[tl] = sv[0];
+    if (tl < 8) tsum[TPC + tl] = 0.f;
+    __syncthreads();
+    float follow = 0.f;
+    for (int i = 1; i < nblk; ++i) follow += tsum[tl + i];
     {
       float pv[PTS];
+      pv[0] = 0.f;
 #pragma unroll
-      for (int k = 0; k < PTS; ++k) { pv[k] = acc; acc += x[k]; }
+      for (int k = 1; k < PTS; ++k) pv[k] = pv[k - 1] + x[k - 1];
 #pragma unroll
-      for (int k = 0; k < PTS; k += 4) *reinterpret_cast<float4 *>(&pP16[k]) = make_float4(pv[k], pv[k + 1], pv[k + 2], pv[k + 3]);
-      if (tl == TPC - 1) P[midx(N)] = acc;
+      for (int k = 0; k < PTS; ++k) sv[k] += follow;
+      // The thread's 16 values are 64 bytes: lanes 64 bytes apart would hit two 16-byte bank groups only, so lane l stores
+      // its four quads in the order rotated by (l >> 1) & 3, which spreads the 8 lanes of a quarter warp over all 8 groups.
+      const bool r1 = (tl >> 1) & 1, r2 = (tl >> 2) & 1;
+#pragma unroll
+      for (int arr = 0; arr < 2; ++arr) {
+        const float *src = arr ? sv : pv;
+        float *dst = arr ? pS16 : pP16;
+        float4 f4[4], g4[4];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) f4[k] = make_float4(src[4 * k], src[4 * k + 1], src[4 * k + 2], src[4 * k + 3]);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const float4 p = f4[k], n = f4[(k + 1) & 3];
+          g4[k] = make_float4(r1 ? n.x : p.x, r1 ? n.y : p.y, r1 ? n.z : p.z, r1 ? n.w : p.w);
+        }
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          const float4 p = g4[k], n = g4[(k + 2) & 3];
+          const float4 v = make_float4(r2 ? n.x : p.x, r2 ? n.y : p.y, r2 ? n.z : p.z, r2 ? n.w : p.w);
+          *reinterpret_cast<float4 *>(&dst[((k + prot) & 3) * 4]) = v;
+        }
+      }
+      if (tl == 0) QP[N] = 0.f;
     }
     __syncthreads();
     float *gout = a.out ? a.out + (size_t)row * N + tl : nullptr;
@@ -305,9 +326,9 @@ chain_f32_fast_kernel(const FastF32Args a) {
         const int n = tl + j * TPC, W = a.W, G = a.G;
         lagg_full = (n + G + W <= N - 1); lead_full = (n - G - W >= 0);
         const int hi = min(n + G + W + 1, N), lo = max(n - G - W, 0);
-        L = __fsub_rn(P[midx(hi)], P[midx(hi - W)]); R = __fsub_rn(P[midx(lo + W)], P[midx(lo)]);
+        L = __fadd_rn(AS[hi - W], QP[hi]); R = __fadd_rn(AS[lo], QP[lo + W]);
       } else {
-        L = __fsub_rn(pA[j * JSTEP], pB[j * JSTEP]); R = __fsub_rn(pC[j * JSTEP], pD[j * JSTEP]);
+        L = __fadd_rn(pA[j * TPC], pB[j * TPC]); R = __fadd_rn(pC[j * TPC], pD[j * TPC]);
       }
       const float thr = f32_threshold<CMODE, LINEAR>(a, L, R, lagg_full, lead_full);
       const bool pk = pX[j * JSTEP] > thr;
@@ -318,7 +339,7 @@ chain_f32_fast_kernel(const FastF32Args a) {
     }
     if (mask != 0 && a.det_list != nullptr && active) {
       const FastF32DetArgs da = {a.W, a.G, a.k_both, a.k_one, a.scaler, a.row_base + row, mask, a.det_cap, a.det_list, a.det_count};
-      f32_detections<S, CMODE, LINEAR>(da, tl, P, mg);
+      f32_detections<S, CMODE, LINEAR>(da, tl, QP, AS, mg);
     }
     __syncthreads();
   }
@@ -334,6 +355,7 @@ bool fast_f32_chain_supported(const Plan &pl, const F32Args &a) {
   if (!a.bitrev || a.fft_dir != 1 || a.sel != 2) return false;
   if (a.core != CORE_MEM || a.send_cut || a.peak_grouping) return false;
   if (a.G < 1 || a.W < 1 || a.div_sum < 0 || a.div_sum > 30) return false;
+  if ((a.W & 15) || a.W > 128) return false;   // the block-of-16 window sums (see the kernel)
   if (f32_edge_iters(pl.S, a.W, a.G) > (pl.S == 10 ? 2 : 1)) return false;
   return a.out != nullptr || a.peak_mask != nullptr || a.det_list != nullptr;
 }

@@ -1,0 +1,22 @@
+#!/usr/bin/env python
+"""One configuration of scripts/bench_configs.py by key, for profiling: python scripts/bench_one.py c3|c5f|c2|c4os|c5 [steps]"""
+import sys, os
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT); sys.path.insert(0, os.path.join(ROOT, "scripts"))
+import bench_configs as B
+from rsp_chains_b200.params import GOSCFARType
+import torch
+key = sys.argv[1] if len(sys.argv) > 1 else "c3"
+torch.cuda.set_device(0)
+ca = lambda n, W, G, ds, mode=0: dict(fftWin=n, thresholdScaler=4, logOrLinearMode=1, divSum=ds, peakGrouping=0, cfarMode=mode, windowCells=W, guardCells=G)
+if key == "c3":
+    B.run_case("C3 x 16 frames fp32 GO", B.f32_params(2048, 32, 4), 11, ca(2048, 32, 4, 5, 1), 32768, 4, fp32=True, bytes_per_sample=12.125)
+elif key == "c5f":
+    B.run_case("C5 shape fp32 CA, 1/4 frame", B.f32_params(16384, 64, 8), 14, ca(16384, 64, 8, 6), 8192, 8, fp32=True, bytes_per_sample=12.125)
+elif key == "c2":
+    B.run_case("C2 x 256 frames", B.fixed_params(1024, 64, 4), 10, ca(1024, 16, 4, 4), 65536, 1)
+elif key == "c5":
+    B.run_case("C5 fixed one frame", B.fixed_params(16384, 64, 8), 14, ca(16384, 64, 8, 6), 32768, 8)
+elif key == "c4os":
+    os_regs = dict(fftWin=4096, thresholdScaler=2, logOrLinearMode=1, peakGrouping=0, cfarMode=0, windowCells=64, guardCells=4, indexLagg=48, indexLead=48)
+    B.run_case("C4 GOS", B.fixed_params(4096, 64, 4, GOSCFARType), 12, os_regs, 1024, 1)
