@@ -363,13 +363,156 @@ __global__ void __launch_bounds__(FGeo<S>::THREADS, 1024 / FGeo<S>::THREADS) cha
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
+// GOS / OS-CFAR (CFARCoreWithLis.scala:13-245 with cfarAlgorithm = 1): each side's reference cells are kept sorted by the
+// reference's LinearSorter and the threshold is built from the indexLagg-th / indexLead-th largest cell (:136-150); the
+// threshold is 0 unless both windows are full (:172-173).  Both sides are the same function of the window start,
+//   K_k[s] = k-th largest of x[s .. s+W-1],   lagging value of bin n = K[n+G+1], leading value = K[n-G-W],
+// so one array per distinct k serves the whole row.  It is computed by rank counting, one thread per group of 8 neighbouring
+// cells: cell i is the k-th largest of window s iff exactly k-1 cells of the window beat it (ties go to the lower index).
+// Sliding the window from s to s-1 adds x[s-1] and drops x[s+W-1], so the rank of every cell that stays moves by two
+// comparisons; the 8 cells of a thread look at the same window in the same step and share its two loads.  About 6 W
+// instructions per cell instead of 16 W for the bitwise search of the generic kernel, and no shared-memory traffic to speak of.
+struct GosArgs { int cmode, linear, kl1, kr1; };   // kl1 = indexLagg - 1, kr1 = indexLead - 1
+
+template <int S> struct GGeo {
+  static constexpr int N = 1 << S;
+  static constexpr int WM = 128;                                           // margin on both sides of the row (>= windowCells)
+  static constexpr int XBG = (N + 2 * WM) + ((N + 2 * WM) >> 4) + 8;       // words: FFT exchange buffer, then the padded cell array
+  static constexpr int ROW = XBG + FGeo<S>::XM + N;                        // + int16 magnitudes + two int16 K arrays
+  static_assert(XBG >= FGeo<S>::XB, "the exchange buffer fits");
+};
+
+// offset of cell (16 tl + o) in the padded array, relative to the thread's base X32 + 17 tl (one pad word per 16 cells:
+// lanes 16 cells apart are 17 words apart, conflict-free)
+__device__ __forceinline__ int gpad(int o) { return (o + 128) + ((o + 128) >> 4); }
+
+template <bool TWO>
+__device__ __forceinline__ void gos_step(int (&r)[8], const int (&xp)[8], int e_lo, int e_hi, int vL, int vR, int kl, int kr,
+                                         short *KL, short *KR, int aidx) {
+#pragma unroll
+  for (int e = 0; e < 8; ++e) {
+    if (e < e_lo || e > e_hi) continue;
+    if (r[e] == kl) KL[aidx] = (short)xp[e];
+    if (TWO && r[e] == kr) KR[aidx] = (short)xp[e];
+    r[e] += (vL >= xp[e] ? 1 : 0) - (vR > xp[e] ? 1 : 0);
+  }
+}
+
+// K arrays of the 8 cells i0 .. i0+7 (i0 = 16 tl + o0) over all the windows that hold them
+template <int S, bool TWO>
+__device__ __forceinline__ void gos_group(const int *xt, int tl, int o0, int W, int kl1, int kr1, short *KL, short *KR) {
+  constexpr int N = 1 << S;
+  int xp[8], r[8];
+#pragma unroll
+  for (int e = 0; e < 8; ++e) { xp[e] = xt[gpad(o0 + e)]; r[e] = 0; }
+  // cells after i_e inside its first window [i_e, i_e + W - 1] that beat it
+#pragma unroll
+  for (int d = 1; d < 8; ++d) {
+    const int v = xt[gpad(o0 + d)];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) if (e < d) r[e] += v > xp[e] ? 1 : 0;
+  }
+  for (int d = 8; d < W; ++d) {
+    const int v = xt[gpad(o0 + d)];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) r[e] += v > xp[e] ? 1 : 0;
+  }
+#pragma unroll
+  for (int q = 0; q < 7; ++q) {
+    const int v = xt[gpad(o0 + W + q)];
+#pragma unroll
+    for (int e = 0; e < 8; ++e) if (e > q) r[e] += v > xp[e] ? 1 : 0;
+  }
+  // diagonal s: window start 16 tl + o0 - s; cell e is at step t = s + e of its own W windows
+  const int a0 = 16 * tl + o0;
+  auto diag = [&](int s, int e_lo, int e_hi) {
+    const int oa = o0 - s, aidx = a0 - s;
+    const int vL = xt[gpad(oa - 1)], vR = xt[gpad(oa + W - 1)];
+    const bool valid = (unsigned)aidx <= (unsigned)(N - W);
+    gos_step<TWO>(r, xp, e_lo, e_hi, vL, vR, valid ? kl1 : -1, valid ? kr1 : -1, KL, KR, valid ? aidx : 0);
+  };
+#pragma unroll
+  for (int s = -7; s < 0; ++s) diag(s, -s, 7);
+  for (int s = 0; s <= W - 8; ++s) diag(s, 0, 7);
+#pragma unroll
+  for (int q = 1; q < 8; ++q) diag(W - 8 + q, 0, 7 - q);
+}
+
+template <int S>
+__global__ void __launch_bounds__(FGeo<S>::THREADS, 1024 / FGeo<S>::THREADS) chain_fixed_fast_gos_kernel(const FastArgs a, const GosArgs ga) {
+  using Gm = FGeo<S>;
+  using Gg = GGeo<S>;
+  constexpr int N = Gm::N, TPC = Gm::TPC, CPC = Gm::CPC, PTS = Gm::PTS;
+  extern __shared__ __align__(16) uint32_t smem[];
+  const int c = threadIdx.x / TPC, tl = threadIdx.x % TPC;
+  uint32_t *xb = smem + (size_t)c * Gg::ROW, *xm = xb + Gg::XBG;
+  const short *X = reinterpret_cast<const short *>(xm);
+  short *KL = reinterpret_cast<short *>(xm + Gm::XM), *KR = ga.kl1 == ga.kr1 ? KL : KL + N;
+  int *xt = reinterpret_cast<int *>(xb) + 17 * tl;
+  const uint32_t stride = gridDim.x * CPC;
+  for (uint32_t row0 = blockIdx.x * CPC; row0 < a.n_rows; row0 += stride) {
+    const bool active = row0 + c < a.n_rows;
+    const uint32_t row = active ? row0 + c : a.n_rows - 1;
+    uint32_t pre[PTS];
+    {
+      const uint32_t *gin = a.in + (size_t)row * N + tl;
+#pragma unroll
+      for (int rr = 0; rr < PTS; ++rr) pre[rr] = __ldg(&gin[rr * TPC]);
+    }
+    fast_passes<S, 0>(a, c, tl, pre, xb, xm);
+    {   // the thread's 16 cells as 32-bit words in the padded array (the exchange buffer is dead)
+      const uint4 v0 = *reinterpret_cast<const uint4 *>(&xm[tl * 8]), v1 = *reinterpret_cast<const uint4 *>(&xm[tl * 8 + 4]);
+      const uint32_t wd[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
+#pragma unroll
+      for (int k = 0; k < 8; ++k) { xt[gpad(2 * k)] = sext16((int)wd[k]); xt[gpad(2 * k + 1)] = hi16s(wd[k]); }
+    }
+    chirp_sync<S>(c);
+    for (int h = 0; h < 2; ++h) {
+      if (ga.kl1 == ga.kr1) gos_group<S, false>(xt, tl, 8 * h, a.W, ga.kl1, ga.kr1, KL, KR);
+      else gos_group<S, true>(xt, tl, 8 * h, a.W, ga.kl1, ga.kr1, KL, KR);
+    }
+    chirp_sync<S>(c);
+    uint32_t *gout = a.out + (size_t)row * N;
+#pragma unroll 4
+    for (int j = 0; j < PTS; ++j) {
+      const int n = tl + j * TPC, W = a.W, G = a.G;
+      const bool both = (n + G + W <= N - 1) && (n - G - W >= 0);
+      const int L = KL[min(n + G + 1, N - W)], R = KR[max(n - G - W, 0)];
+      int t = ga.cmode == 0 ? ((R + L) >> 1) : (ga.cmode == 1 ? max(L, R) : min(L, R));
+      t = both ? t : 0;                                                  // CFARCoreWithLis.scala:172-173
+      const int thr = ga.linear ? t * a.scaler : t + a.scaler;
+      const int cut = X[n];
+      const int pk = cut > thr ? 1 : 0;
+      gout[n] = ((uint32_t)thr & a.thr_mask) * (uint32_t)a.out_mul + (uint32_t)(n << 1) + (uint32_t)pk;
+      if (pk && a.det_list != nullptr && active) {
+        const uint32_t slot = atomicAdd(a.det_count, 1u);
+        if (slot < a.det_cap) {
+          Detection d; d.chirp = a.row_base + row; d.bin = (uint32_t)n; d.threshold = (int)((uint32_t)thr << a.thr_sext) >> a.thr_sext; d.cut = cut;
+          a.det_list[slot] = d;
+        }
+      }
+    }
+    chirp_sync<S>(c);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
 // host side
 static int fast_edge_iters(int S, int W, int G) { const int tpc = (1 << S) / 16; return (W + G + tpc - 1) / tpc; }
+
+static bool fast_gos_supported(const FxArgs &a) {
+  if (a.core != CORE_LIS || a.cfar_algorithm != 1) return false;
+  if (a.in_w != 16 || a.in_bp != 0 || a.sc_bp != 0 || a.thr_bp != 0 || a.send_cut || a.peak_grouping) return false;
+  if (a.thr_w < 1 || a.thr_w > 32 || a.G < 0 || a.W < 8 || a.W > 128 || (a.W & 7)) return false;
+  if (a.idx_lagg < 1 || a.idx_lagg > a.W || a.idx_lead < 1 || a.idx_lead > a.W) return false;
+  return a.binw + 1 <= 31;
+}
 
 bool fast_chain_supported(const Plan &pl, const FxArgs &a) {
   if (pl.mode != MODE_FAST || pl.first_stage != STAGE_FFT || pl.last_stage != STAGE_CFAR) return false;
   if (pl.S < RSP_FAST_SMIN || pl.S > RSP_FAST_SMAX) return false;
   if (a.bp != 0 || a.tw_bp != 14 || !a.bitrev || a.sel != 2 || a.mag_w != 16 || a.mag_bp != 0) return false;
+  if (a.core == CORE_LIS) return fast_gos_supported(a);
   if (a.core != CORE_MEM || a.in_w != 16 || a.in_bp != 0 || a.sc_bp != 0 || a.thr_bp != 0 || a.send_cut || a.peak_grouping) return false;
   if (a.thr_w < 1 || a.thr_w > 32 || a.G < 1 || a.W < 1 || a.div_sum < 0 || a.div_sum > 30) return false;
   const int ej = fast_edge_iters(pl.S, a.W, a.G);
@@ -413,6 +556,21 @@ static rsp_status launch_fast_modes(int cmode, bool linear, const LaunchCtx &c, 
   }
 }
 
+template <int S>
+static rsp_status launch_fast_gos(const LaunchCtx &c, const FastArgs &fa, const GosArgs &ga, cudaStream_t st, const char **err) {
+  using Gm = FGeo<S>;
+  static int occ_dev[64] = {0};
+  int &occ = occ_dev[c.device & 63];
+  const size_t smem = (size_t)Gm::CPC * GGeo<S>::ROW * sizeof(uint32_t);
+  auto kernel = chain_fixed_fast_gos_kernel<S>;
+  if (!occ) { const rsp_status s = launch_cfg(kernel, smem, Gm::THREADS, &occ, err); if (s != RSP_OK) return s; }
+  const unsigned groups = (fa.n_rows + Gm::CPC - 1) / Gm::CPC;
+  const unsigned grid = std::max(1u, std::min(groups, (unsigned)(c.sm_count * occ)));
+  kernel<<<grid, Gm::THREADS, smem, st>>>(fa, ga);
+  if (cudaGetLastError() != cudaSuccess) { *err = "chain_fixed_fast_gos_kernel launch failed"; return RSP_ECUDA; }
+  return RSP_OK;
+}
+
 rsp_status launch_fast_chain(const Plan &pl, const LaunchCtx &ctx, const FxArgs &a, cudaStream_t st, const char **err) {
   FastArgs fa;
   fa.in = a.in; fa.out = a.out; fa.n_rows = a.n_rows; fa.row_base = a.row_base;
@@ -425,6 +583,17 @@ rsp_status launch_fast_chain(const Plan &pl, const LaunchCtx &ctx, const FxArgs 
   fa.det_list = a.det_list; fa.det_count = a.det_count; fa.det_cap = a.det_cap;
   const int cmode = a.cfar_mode == 0 ? 0 : (a.cfar_mode == 1 ? 1 : 2);   // MuxLookup default: smallestOf (CFARCoreWithMem.scala:138-141)
   const bool linear = a.log_or_linear != 0;
+  if (a.core == CORE_LIS) {
+    const GosArgs ga = {cmode, linear ? 1 : 0, a.idx_lagg - 1, a.idx_lead - 1};
+    switch (pl.S) {
+    case 10: return launch_fast_gos<10>(ctx, fa, ga, st, err);
+    case 11: return launch_fast_gos<11>(ctx, fa, ga, st, err);
+    case 12: return launch_fast_gos<12>(ctx, fa, ga, st, err);
+    case 13: return launch_fast_gos<13>(ctx, fa, ga, st, err);
+    case 14: return launch_fast_gos<14>(ctx, fa, ga, st, err);
+    default: *err = "no fast variant for this size"; return RSP_EUNSUPPORTED;
+    }
+  }
   const int ej = fast_edge_iters(pl.S, a.W, a.G);
   switch (pl.S) {
   case 10: return ej == 2 ? launch_fast_modes<10, 2>(cmode, linear, ctx, fa, st, err) : launch_fast_modes<10, 1>(cmode, linear, ctx, fa, st, err);

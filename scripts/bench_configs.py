@@ -93,6 +93,7 @@ def main():
     run_case("C3 shape in fixed point, GO", fixed_params(2048, 32, 4), 11, ca(2048, 32, 4, 5, 1), 32768, 4, peak=peak)
     os_regs = dict(fftWin=4096, thresholdScaler=2, logOrLinearMode=1, peakGrouping=0, cfarMode=0, windowCells=64, guardCells=4, indexLagg=48, indexLead=48)
     run_case("C4 1024 x 4096 fixed GOS (64 cells per side, k=48)", fixed_params(4096, 64, 4, GOSCFARType), 12, os_regs, 1024, 1, peak=peak)
+    run_case("C4 x 16: 16384 x 4096 fixed GOS (64 cells per side, k=48)", fixed_params(4096, 64, 4, GOSCFARType), 12, os_regs, 1024 if quick else 16384, 1, peak=peak)
     run_case("C4 shape with CA-CFAR (W64 G4)", fixed_params(4096, 64, 4), 12, ca(4096, 64, 4, 6), 1024 if quick else 16384, 1, peak=peak)
     run_case("C5 8 RX x 4096 x 16384 fixed CA (W64 G8), one frame", fixed_params(16384, 64, 8), 14, ca(16384, 64, 8, 6),
              4096 if quick else 32768, 8, peak=peak)

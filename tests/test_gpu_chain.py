@@ -246,3 +246,22 @@ def test_c5_full_size_rows_are_independent(cuda, oracle):
         first = d_out[:8]
         assert (from_dev_u32(first) == want).all()
         assert bool((d_out.view(rows // 8, 8, n) == first.unsqueeze(0)).all().item())
+
+
+@pytest.mark.parametrize("log_n,W,G,kl,kr", [(10, 16, 2, 12, 12), (10, 64, 4, 48, 48), (11, 32, 0, 24, 7), (12, 64, 4, 48, 20), (13, 8, 1, 1, 8),
+                                              (14, 128, 8, 96, 96)])
+def test_fast_gos_kernel_variants(cuda, oracle, log_n, W, G, kl, kr):
+    """chain_fixed_fast_gos<S> (rank-counting OS-CFAR): CA/GO/SO combination of the two order statistics, linear and log threshold,
+    equal and different indexLagg / indexLead, ragged row counts, full-range random rows (ties, negative magnitudes)"""
+    n = 1 << log_n
+    rows = 19 if log_n <= 12 else 5
+    beats = np.concatenate([synth.chirps_fixed(rows - 3, n, seed=log_n), synth.random_beats(3, n, seed=200 + log_n)])
+    beats[-1, n // 2:] = beats[-1, 7]          # long runs of equal cells
+    p = chain_params(n, 0, cfar_type=GOSCFARType, W=max(W, 16), G=max(G, 1))
+    for mode, lin, scaler in ((0, 1, 2), (1, 1, 3), (2, 0, 500), (3, 1, -2)):
+        regs = dict(fftWin=n, thresholdScaler=scaler & 0xFFFF, logOrLinearMode=lin, peakGrouping=0, cfarMode=mode, windowCells=W, guardCells=G,
+                    indexLagg=kl, indexLead=kr)
+        with R.FftMagCfarChainVanilla(p) as ch:
+            configure(ch, log_n, 2, regs)
+            assert ch.variant == f"chain_fixed_fast_gos<{log_n}>", ch.variant
+        run_and_compare(cuda, oracle, p, log_n, 2, regs, beats)
