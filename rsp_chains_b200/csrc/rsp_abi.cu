@@ -24,7 +24,16 @@ static rsp_status fail(rsp_status st, const std::string &msg) { g_last_error = m
     if (e__ != cudaSuccess) return fail(RSP_ECUDA, std::string(#expr) + ": " + cudaGetErrorString(e__));     \
   } while (0)
 
-static const int N_PIPE = 3;   // chunks in flight in rsp_run_host
+static const int N_PIPE = 6;   // most chunks in flight in rsp_run_host (pipe_depth() of them are used)
+// tuning knobs of the host pipeline (defaults measured on B200 / PCIe Gen5, scripts/e2e_sweep.py)
+static int env_int(const char *name, int dflt, int lo, int hi) {
+  const char *v = std::getenv(name);
+  if (!v || !*v) return dflt;
+  const long x = std::strtol(v, nullptr, 10);
+  return x < lo ? lo : (x > hi ? hi : (int)x);
+}
+static int pipe_depth() { static const int d = env_int("RSP_PIPE_DEPTH", 3, 1, N_PIPE); return d; }
+static size_t pipe_chunk_bytes() { static const int m = env_int("RSP_PIPE_CHUNK_MIB", 16, 1, 1024); return (size_t)m << 20; }
 
 struct rsp_chain {
   rsp_chain_params p;
@@ -45,10 +54,10 @@ struct rsp_chain {
   uint64_t launches = 0;
   std::string variant;
   // host pipeline
-  cudaStream_t pipe_stream[N_PIPE] = {nullptr, nullptr, nullptr};
-  void *pipe_in[N_PIPE] = {nullptr, nullptr, nullptr}, *pipe_out[N_PIPE] = {nullptr, nullptr, nullptr};
-  uint32_t *pipe_mask[N_PIPE] = {nullptr, nullptr, nullptr};
-  void *stage_in[N_PIPE] = {nullptr, nullptr, nullptr}, *stage_out[N_PIPE] = {nullptr, nullptr, nullptr};   // pinned staging for pageable callers
+  cudaStream_t pipe_stream[N_PIPE] = {};
+  void *pipe_in[N_PIPE] = {}, *pipe_out[N_PIPE] = {};
+  uint32_t *pipe_mask[N_PIPE] = {};
+  void *stage_in[N_PIPE] = {}, *stage_out[N_PIPE] = {};   // pinned staging for pageable callers
   size_t pipe_rows_cap = 0, pipe_row_in = 0, pipe_row_out = 0, pipe_row_mask = 0;
   rsp_detection *d_det_list = nullptr;
   uint32_t *d_det_count = nullptr;
@@ -423,20 +432,20 @@ static bool is_pinned(const void *p) {
 }
 
 static rsp_status ensure_pipe(rsp_chain *c, size_t rows_per_chunk, size_t row_in, size_t row_out, size_t row_mask, bool need_stage_in, bool need_stage_out) {
-  for (int i = 0; i < N_PIPE; ++i)
+  for (int i = 0; i < pipe_depth(); ++i)
     if (!c->pipe_stream[i]) CUDA_TRY(cudaStreamCreateWithFlags(&c->pipe_stream[i], cudaStreamNonBlocking));
   const bool fits = c->pipe_rows_cap >= rows_per_chunk && c->pipe_row_in >= row_in && c->pipe_row_out >= row_out && c->pipe_row_mask >= row_mask;
   if (!fits) {
     CUDA_TRY(cudaDeviceSynchronize());
     free_pipe(c);
-    for (int i = 0; i < N_PIPE; ++i) {
+    for (int i = 0; i < pipe_depth(); ++i) {
       CUDA_TRY(cudaMalloc(&c->pipe_in[i], rows_per_chunk * row_in));
       CUDA_TRY(cudaMalloc(&c->pipe_out[i], std::max<size_t>(1, rows_per_chunk * row_out)));
       CUDA_TRY(cudaMalloc((void **)&c->pipe_mask[i], std::max<size_t>(1, rows_per_chunk * row_mask)));
     }
     c->pipe_rows_cap = rows_per_chunk; c->pipe_row_in = row_in; c->pipe_row_out = row_out; c->pipe_row_mask = row_mask;
   }
-  for (int i = 0; i < N_PIPE; ++i) {
+  for (int i = 0; i < pipe_depth(); ++i) {
     if (need_stage_in && !c->stage_in[i]) CUDA_TRY(cudaHostAlloc(&c->stage_in[i], c->pipe_rows_cap * c->pipe_row_in, cudaHostAllocDefault));
     if (need_stage_out && !c->stage_out[i]) CUDA_TRY(cudaHostAlloc(&c->stage_out[i], std::max<size_t>(1, c->pipe_rows_cap * std::max(c->pipe_row_out, c->pipe_row_mask)), cudaHostAllocDefault));
   }
@@ -456,8 +465,8 @@ extern "C" rsp_status rsp_run_host(rsp_chain *c, const void *h_in, uint32_t n_ch
   const size_t N = (size_t)1 << S;
   const size_t row_in = N * (fixed ? 4 : 8), row_out = h_out ? N * 4 : 0;
   const size_t row_mask = (!fixed && h_peak_mask) ? ((N + 31) / 32) * 4 : 0;
-  // chunks of ~8 MiB of input keep three copies/kernels in flight without holding much HBM
-  size_t rows_per_chunk = std::max<size_t>(1, ((size_t)8 << 20) / row_in);
+  // chunks of ~16 MiB of input (42.7 GB/s each way on PCIe Gen5 against 39.9 at 8 MiB; both directions at once peak at 49.8) keep three copies/kernels in flight
+  size_t rows_per_chunk = std::max<size_t>(1, pipe_chunk_bytes() / row_in);
   rows_per_chunk = std::min<size_t>(rows_per_chunk, std::max<uint32_t>(rows, 1));
   const bool in_pinned = is_pinned(h_in), out_pinned = !h_out || is_pinned(h_out);
   const bool mask_pinned = !row_mask || is_pinned(h_peak_mask);
@@ -481,6 +490,7 @@ extern "C" rsp_status rsp_run_host(rsp_chain *c, const void *h_in, uint32_t n_ch
   const unsigned char *src = static_cast<const unsigned char *>(h_in);
   unsigned char *dst = static_cast<unsigned char *>(h_out);
   unsigned char *mdst = reinterpret_cast<unsigned char *>(h_peak_mask);
+  const int depth = pipe_depth();
   struct Pending { size_t row0 = 0, n = 0; bool live = false; } pend[N_PIPE];
   auto drain = [&](int slot) -> rsp_status {   // wait for the slot's chunk and unstage it
     if (!pend[slot].live) return RSP_OK;
@@ -492,7 +502,7 @@ extern "C" rsp_status rsp_run_host(rsp_chain *c, const void *h_in, uint32_t n_ch
   };
   size_t chunk = 0;
   for (size_t row0 = 0; row0 < rows; row0 += rows_per_chunk, ++chunk) {
-    const int slot = (int)(chunk % N_PIPE);
+    const int slot = (int)(chunk % (size_t)depth);
     const size_t n = std::min<size_t>(rows_per_chunk, rows - row0);
     s = drain(slot);
     if (s != RSP_OK) return s;
@@ -523,8 +533,8 @@ extern "C" rsp_status rsp_run_host(rsp_chain *c, const void *h_in, uint32_t n_ch
     }
     pend[slot].row0 = row0; pend[slot].n = n; pend[slot].live = true;
   }
-  for (int i = 0; i < N_PIPE; ++i) { s = drain(i); if (s != RSP_OK) return s; }
-  for (int i = 0; i < N_PIPE; ++i) CUDA_TRY(cudaStreamSynchronize(c->pipe_stream[i]));
+  for (int i = 0; i < depth; ++i) { s = drain(i); if (s != RSP_OK) return s; }
+  for (int i = 0; i < depth; ++i) CUDA_TRY(cudaStreamSynchronize(c->pipe_stream[i]));
   if (dets.list) {
     uint32_t cnt = 0;
     CUDA_TRY(cudaMemcpy(&cnt, c->d_det_count, sizeof(uint32_t), cudaMemcpyDeviceToHost));
