@@ -12,7 +12,7 @@
 //    ((c, s) * re then (-s, c) * im + acc, the table holds (c, s, -s, c))
 //  * the x(-j) rotation is never executed: the butterfly that consumes a rotated point is written out on the swapped lanes
 //  * three (four) register passes of up to 4 radix-2 stages; between passes the points cross shared memory once, at
-//    index p + 2 (p >> 4) + 4 (p >> 6), which makes every 64-bit and 128-bit access pattern of every pass conflict-free
+//    index p + 2 (p >> 4) + 4 (p >> 6), which makes the 64-bit and 128-bit access patterns of the passes conflict-free
 //  * the bit reversal is the scatter of the magnitudes; the CFAR window sums are differences of one prefix-sum array that
 //    reuses the exchange buffer; bins are taken interleaved so that loads have immediate offsets and stores are coalesced
 //  * the peak bits of 32 consecutive bins are one warp ballot.
@@ -53,16 +53,33 @@ template <int S> struct FGeoF {
   static constexpr int JSTEP = TPC + (TPC >> 3);              // midx(n + TPC) - midx(n)
 };
 
-__device__ __forceinline__ int xidx(int p) { return p + ((p >> 4) << 1) + ((p >> 6) << 2); }
+// exchange-buffer index of point p: one 16-byte pad per 16 points, and (except at N = 4096, whose last pass reads 16 neighbouring
+// points per thread and is conflict-free without it) one 32-byte pad per 64 (tests/test_kernel_layout.py models every pass)
+template <int S> __host__ __device__ constexpr int xidx(int p) { return p + ((p >> 4) << 1) + (S == 12 ? 0 : ((p >> 6) << 2)); }
 __device__ __forceinline__ int midx(int n) { return n + ((n >> 5) << 2); }
 
 __device__ __forceinline__ u64 pk2(float lo, float hi) { u64 r; asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi)); return r; }
 __device__ __forceinline__ void upk2(u64 v, float &lo, float &hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
+// Packed or scalar arithmetic: measured on B200 (scripts/ubench/fp2.cu, profiles/r01_f_ubench_fp2.txt) FADD2/FFMA2 issue at
+// 1.1 warp-instructions/clk/SM against 2.7 for FADD/FFMA, i.e. a packed instruction saves an issue slot but costs ~25% more
+// FMA-pipe time than the two scalar ones.  RSP_F32_PACKED selects which of the two this kernel is built from.
+#ifndef RSP_F32_PACKED
+#define RSP_F32_PACKED 1
+#endif
+#if RSP_F32_PACKED
 __device__ __forceinline__ u64 add2(u64 a, u64 b) { u64 r; asm("add.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
 __device__ __forceinline__ u64 sub2(u64 a, u64 b) { u64 r; asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
 __device__ __forceinline__ u64 mul2(u64 a, u64 b) { u64 r; asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b)); return r; }
 __device__ __forceinline__ u64 fma2(u64 a, u64 b, u64 c) { u64 r; asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c)); return r; }
-
+#else
+__device__ __forceinline__ u64 add2(u64 a, u64 b) { float a0, a1, b0, b1; upk2(a, a0, a1); upk2(b, b0, b1); return pk2(a0 + b0, a1 + b1); }
+__device__ __forceinline__ u64 sub2(u64 a, u64 b) { float a0, a1, b0, b1; upk2(a, a0, a1); upk2(b, b0, b1); return pk2(a0 - b0, a1 - b1); }
+__device__ __forceinline__ u64 mul2(u64 a, u64 b) { float a0, a1, b0, b1; upk2(a, a0, a1); upk2(b, b0, b1); return pk2(a0 * b0, a1 * b1); }
+__device__ __forceinline__ u64 fma2(u64 a, u64 b, u64 c) {
+  float a0, a1, b0, b1, c0, c1; upk2(a, a0, a1); upk2(b, b0, b1); upk2(c, c0, c1);
+  return pk2(fmaf(a0, b0, c0), fmaf(a1, b1, c1));
+}
+#endif
 // a <- a + c, c <- a - c
 __device__ __forceinline__ void bf_plain(u64 &a, u64 &c) { const u64 s = add2(a, c), d = sub2(a, c); a = s; c = d; }
 // the same with c standing for -j c = (c.im, -c.re) (SDFChainRadix22.scala:319-337: the rotation after an even stage)
@@ -99,13 +116,11 @@ __device__ __forceinline__ void jpl2_scaled(u64 z0, u64 z1, float sc, float &m0,
   upk2(mm, m0, m1);
 }
 
-constexpr int xoff_c(int p) { return p + ((p >> 4) << 1) + ((p >> 6) << 2); }   // xidx of a compile-time offset
-constexpr int moff_c(int n) { return n + ((n >> 5) << 2); }
 
 // One pass = m radix-2 stages in registers on 2^m points Dl apart (the decomposition of rsp_device.cuh, fx_pass_*).
 // Thread tl of the chirp works on the groups vt = g * TPC + tl, so a warp touches consecutive points in every pass.
 // Every shared-memory address is one run-time base plus a compile-time offset: xidx(base + g * TPC * R + rr * Dl) =
-// xidx(base) + xidx(g * TPC * R + rr * Dl) for all the shapes used here (checked exhaustively, tests/test_abi_host.py).
+// xidx(base) + xidx(g * TPC * R + rr * Dl) for all the shapes used here (checked exhaustively, tests/test_kernel_layout.py).
 template <int S, int K>
 __device__ __forceinline__ void f32_pass(const FastF32Args &a, int tl, const u64 (&pre)[16], u64 *xb, float *mg) {
   using Gm = FGeoF<S>;
@@ -117,7 +132,7 @@ __device__ __forceinline__ void f32_pass(const FastF32Args &a, int tl, const u64
   float mags[last ? PTS : 1];
   const int low = tl & (Dl - 1);
   const int base0 = ((tl >> LDl) << (m + LDl)) | low;        // group g starts at base0 + g * TPC * R
-  u64 *xp = xb + xidx(base0);
+  u64 *xp = xb + xidx<S>(base0);
 #pragma unroll
   for (int g = 0; g < G; ++g) {
     u64 z[R];
@@ -127,12 +142,12 @@ __device__ __forceinline__ void f32_pass(const FastF32Args &a, int tl, const u64
     } else if (last) {                                        // 2^m neighbouring points: 128-bit loads
 #pragma unroll
       for (int rr = 0; rr < R; rr += 2) {
-        const ulonglong2 v = *reinterpret_cast<const ulonglong2 *>(&xp[xoff_c(g * TPC * R + rr)]);
+        const ulonglong2 v = *reinterpret_cast<const ulonglong2 *>(&xp[xidx<S>(g * TPC * R + rr)]);
         z[rr] = v.x; z[rr + 1] = v.y;
       }
     } else {
 #pragma unroll
-      for (int rr = 0; rr < R; ++rr) z[rr] = xp[xoff_c(g * TPC * R + rr * Dl)];
+      for (int rr = 0; rr < R; ++rr) z[rr] = xp[xidx<S>(g * TPC * R + rr * Dl)];
     }
 #pragma unroll
     for (int s = 0; s < m; ++s) {
@@ -170,7 +185,7 @@ __device__ __forceinline__ void f32_pass(const FastF32Args &a, int tl, const u64
     }
     if (!last) {
 #pragma unroll
-      for (int rr = 0; rr < R; ++rr) xp[xoff_c(g * TPC * R + rr * Dl)] = z[rr];
+      for (int rr = 0; rr < R; ++rr) xp[xidx<S>(g * TPC * R + rr * Dl)] = z[rr];
     } else {
 #pragma unroll
       for (int rr = 0; rr < R; rr += 2) jpl2_scaled(z[rr], z[rr + 1], a.inv_n, mags[g * R + rr], mags[g * R + rr + 1]);

@@ -100,6 +100,50 @@ def test_fp32_blocks_and_sizes(cuda, oracle):
         assert err < REL_TOL, f"N={n}: {err:.2e}"
 
 
+@pytest.mark.parametrize("log_n,W,G", [(10, 16, 2), (10, 64, 8), (11, 32, 4), (12, 64, 4), (13, 16, 1), (14, 64, 8)])
+def test_fast_f32_kernel_variants(cuda, oracle, log_n, W, G):
+    """chain_f32_fast<S>: every size it is built for, CA / GO / SO x linear / log threshold, ragged row counts (two chirps per CTA at
+    N = 1024, edge iterations with W + G > 64), rows 60 dB apart in level, thresholds + peak mask + detection list"""
+    n = 1 << log_n
+    rows = 5 if log_n <= 12 else 3
+    xc = synth.chirps_complex(rows, n, seed=10 + log_n)
+    xc[1, :] *= 1e-3                                   # a weak row
+    xc[2, :] *= 1.9                                    # close to full scale
+    x32 = np.stack([xc.real, xc.imag], axis=-1).astype(np.float32)
+    xq = x32[..., 0].astype(np.float64) + 1j * x32[..., 1].astype(np.float64)
+    for mode, lin, scaler in ((0, 1, 3.5), (1, 1, 2.5), (2, 1, 4.0), (0, 0, 1e-4), (2, 0, 0.0)):
+        regs = dict(fftWin=n, logOrLinearMode=lin, divSum=int(np.log2(W)), peakGrouping=0, cfarMode=mode, windowCells=W, guardCells=G)
+        with R.FftMagCfarChainVanilla(f32_params(n, max(W, 16), max(G, 1))) as ch:
+            configure(ch, log_n, 2, regs)
+            ch.set_threshold_scaler_f32(scaler)
+            assert ch.variant == f"chain_f32_fast<{log_n}>", ch.variant
+            d_in = cuda.from_numpy(x32).cuda()
+            d_thr = cuda.empty((rows, n), dtype=cuda.float32, device="cuda")
+            d_mask = cuda.zeros((rows, n // 32), dtype=cuda.int32, device="cuda")
+            det_list = cuda.zeros((rows * n, 4), dtype=cuda.int32, device="cuda")
+            det_count = cuda.zeros(1, dtype=cuda.int32, device="cuda")
+            ch.run(d_in, rows, 1, out=d_thr, peak_mask=d_mask, det_list=det_list, det_count=det_count)
+            cuda.cuda.synchronize()
+            thr = d_thr.cpu().numpy()
+            pk = unpack_mask(d_mask.cpu().numpy().view(np.uint32), n)
+            k = int(det_count.item())
+            dets = det_list[:k].cpu().numpy()
+        mag, want_thr, want_pk = f64_chain(oracle, xq, log_n, 2, regs, scaler, W, G)
+        scale = np.abs(want_thr).max(axis=1, keepdims=True)
+        rel = np.abs(thr - want_thr) / np.maximum(np.abs(want_thr), 1e-6 * scale)
+        assert rel.max() < REL_TOL, f"mode {mode} lin {lin}: max relative threshold error {rel.max():.3e}"
+        margin = np.abs(mag - want_thr) / np.maximum(np.abs(want_thr), 1e-30)
+        decided = margin > 10 * REL_TOL
+        assert (pk[decided] == want_pk[decided]).all(), f"mode {mode} lin {lin}"
+        # the detection list is the peak mask, with the threshold and the cell under test as float bits
+        assert k == int(pk.sum())
+        got = set(map(tuple, dets[:, :2].tolist()))
+        assert got == set(map(tuple, np.argwhere(pk == 1).tolist()))
+        if k:
+            r0, b0 = dets[0, 0], dets[0, 1]
+            assert dets[0, 2:].view(np.float32)[0] == thr[r0, b0]
+
+
 # ---------------------------------------------------------------------------------------------------- PLFG -> NCO
 
 def write_plfg(ch, p, oracle, starting_point, segs, n_rep=1, frame_num=1, inter=10):
