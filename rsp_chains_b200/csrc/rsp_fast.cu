@@ -386,15 +386,25 @@ template <int S> struct GGeo {
 // lanes 16 cells apart are 17 words apart, conflict-free)
 __device__ __forceinline__ int gpad(int o) { return (o + 128) + ((o + 128) >> 4); }
 
+// The compiler turns `r += a >= b` into add + conditional move and merges the conditional stores into select chains (9
+// instructions per cell and step); written as predicated PTX it is compare + predicated add / store (6 per cell and step).
+__device__ __forceinline__ void inc_if_ge(int &r, int a, int b) { asm("{.reg .pred p; setp.ge.s32 p, %1, %2; @p add.s32 %0, %0, 1;}" : "+r"(r) : "r"(a), "r"(b)); }
+__device__ __forceinline__ void inc_if_gt(int &r, int a, int b) { asm("{.reg .pred p; setp.gt.s32 p, %1, %2; @p add.s32 %0, %0, 1;}" : "+r"(r) : "r"(a), "r"(b)); }
+__device__ __forceinline__ void dec_if_gt(int &r, int a, int b) { asm("{.reg .pred p; setp.gt.s32 p, %1, %2; @p add.s32 %0, %0, -1;}" : "+r"(r) : "r"(a), "r"(b)); }
+__device__ __forceinline__ void sts16_if_eq(int r, int k, uint32_t saddr, int v) {
+  asm volatile("{.reg .pred p; setp.eq.s32 p, %0, %1; @p st.shared.u16 [%2], %3;}" :: "r"(r), "r"(k), "r"(saddr), "h"((short)v) : "memory");
+}
+
 template <bool TWO>
 __device__ __forceinline__ void gos_step(int (&r)[8], const int (&xp)[8], int e_lo, int e_hi, int vL, int vR, int kl, int kr,
-                                         short *KL, short *KR, int aidx) {
+                                         uint32_t kl_addr, uint32_t kr_addr) {
 #pragma unroll
   for (int e = 0; e < 8; ++e) {
     if (e < e_lo || e > e_hi) continue;
-    if (r[e] == kl) KL[aidx] = (short)xp[e];
-    if (TWO && r[e] == kr) KR[aidx] = (short)xp[e];
-    r[e] += (vL >= xp[e] ? 1 : 0) - (vR > xp[e] ? 1 : 0);
+    sts16_if_eq(r[e], kl, kl_addr, xp[e]);
+    if (TWO) sts16_if_eq(r[e], kr, kr_addr, xp[e]);
+    inc_if_ge(r[e], vL, xp[e]);
+    dec_if_gt(r[e], vR, xp[e]);
   }
 }
 
@@ -410,26 +420,28 @@ __device__ __forceinline__ void gos_group(const int *xt, int tl, int o0, int W, 
   for (int d = 1; d < 8; ++d) {
     const int v = xt[gpad(o0 + d)];
 #pragma unroll
-    for (int e = 0; e < 8; ++e) if (e < d) r[e] += v > xp[e] ? 1 : 0;
+    for (int e = 0; e < 8; ++e) if (e < d) inc_if_gt(r[e], v, xp[e]);
   }
   for (int d = 8; d < W; ++d) {
     const int v = xt[gpad(o0 + d)];
 #pragma unroll
-    for (int e = 0; e < 8; ++e) r[e] += v > xp[e] ? 1 : 0;
+    for (int e = 0; e < 8; ++e) inc_if_gt(r[e], v, xp[e]);
   }
 #pragma unroll
   for (int q = 0; q < 7; ++q) {
     const int v = xt[gpad(o0 + W + q)];
 #pragma unroll
-    for (int e = 0; e < 8; ++e) if (e > q) r[e] += v > xp[e] ? 1 : 0;
+    for (int e = 0; e < 8; ++e) if (e > q) inc_if_gt(r[e], v, xp[e]);
   }
   // diagonal s: window start 16 tl + o0 - s; cell e is at step t = s + e of its own W windows
   const int a0 = 16 * tl + o0;
+  const uint32_t kl_base = (uint32_t)__cvta_generic_to_shared(KL), kr_base = (uint32_t)__cvta_generic_to_shared(KR);
   auto diag = [&](int s, int e_lo, int e_hi) {
     const int oa = o0 - s, aidx = a0 - s;
     const int vL = xt[gpad(oa - 1)], vR = xt[gpad(oa + W - 1)];
     const bool valid = (unsigned)aidx <= (unsigned)(N - W);
-    gos_step<TWO>(r, xp, e_lo, e_hi, vL, vR, valid ? kl1 : -1, valid ? kr1 : -1, KL, KR, valid ? aidx : 0);
+    gos_step<TWO>(r, xp, e_lo, e_hi, vL, vR, valid ? kl1 : -1, valid ? kr1 : -1, kl_base + 2u * (uint32_t)(valid ? aidx : 0),
+                  kr_base + 2u * (uint32_t)(valid ? aidx : 0));
   };
 #pragma unroll
   for (int s = -7; s < 0; ++s) diag(s, -s, 7);
