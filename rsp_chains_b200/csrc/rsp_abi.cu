@@ -33,6 +33,7 @@ static int env_int(const char *name, int dflt, int lo, int hi) {
   return x < lo ? lo : (x > hi ? hi : (int)x);
 }
 static int pipe_depth() { static const int d = env_int("RSP_PIPE_DEPTH", 3, 1, N_PIPE); return d; }
+static bool pipe_ramp() { static const int r = env_int("RSP_PIPE_RAMP", 1, 0, 1); return r != 0; }
 static size_t pipe_chunk_bytes() { static const int m = env_int("RSP_PIPE_CHUNK_MIB", 16, 1, 1024); return (size_t)m << 20; }
 
 struct rsp_chain {
@@ -501,9 +502,19 @@ extern "C" rsp_status rsp_run_host(rsp_chain *c, const void *h_in, uint32_t n_ch
     return RSP_OK;
   };
   size_t chunk = 0;
-  for (size_t row0 = 0; row0 < rows; row0 += rows_per_chunk, ++chunk) {
+  // Chunk schedule: the first chunks ramp up (1/8, 1/4, 1/2 of a chunk) and the last ones ramp down the same way, so that the
+  // time in which only one of the two PCIe directions is busy (first H2D, last D2H) is that of a small chunk, not a full one.
+  const size_t ramp_min = std::max<size_t>(1, rows_per_chunk / 8);
+  const bool ramp = pipe_ramp() && rows > 2 * rows_per_chunk;
+  size_t n = 0;
+  for (size_t row0 = 0; row0 < rows; row0 += n, ++chunk) {
     const int slot = (int)(chunk % (size_t)depth);
-    const size_t n = std::min<size_t>(rows_per_chunk, rows - row0);
+    const size_t remaining = rows - row0;
+    n = std::min<size_t>(rows_per_chunk, remaining);
+    if (ramp) {
+      if (chunk < 3) n = std::min(n, std::max(ramp_min, rows_per_chunk >> (3 - chunk)));
+      if (remaining <= 2 * rows_per_chunk && remaining > ramp_min) n = std::min(n, std::max(ramp_min, remaining / 2));
+    }
     s = drain(slot);
     if (s != RSP_OK) return s;
     cudaStream_t st = c->pipe_stream[slot];
