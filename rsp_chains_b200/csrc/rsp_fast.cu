@@ -108,7 +108,9 @@ __device__ __forceinline__ int fjpl(int re, int im) {
 
 // One pass = m radix-2 stages in registers on 2^m points Dl apart (same decomposition as rsp_device.cuh, fx_pass_*).
 // Thread tl of the chirp works on the groups vt = g * TPC + tl, so a warp touches consecutive words in every pass.
-template <int S, int K>
+// WRAP = false: the row was found "quiet" (see quiet_beats): no value of the transform can reach +-32768, so the 16-bit wrap
+// of the butterfly differences is the identity and its PRMT is left out (13% of the ALU-pipe instructions of the kernel).
+template <int S, int K, bool WRAP>
 __device__ __forceinline__ void fast_pass(const FastArgs &a, int tl, const uint32_t (&pre)[16], uint32_t *xb, uint32_t *xm) {
   using Gm = FGeo<S>;
   constexpr int m = fx_pass_size(S, K), i0 = fx_pass_start(S, K), LDl = S - i0 - m, Dl = 1 << LDl;
@@ -143,7 +145,7 @@ __device__ __forceinline__ void fast_pass(const FastArgs &a, int tl, const uint3
       const int i = i0 + s;
       const int dist = 1 << (m - 1 - s);
       const bool rot = (i != S - 1) && ((i & 1) == 0);   // x(-j) on the last quarter of each 4D block follows (SDFChainRadix22.scala:319-337)
-      const bool wrap = !(last && s == m - 1);            // the magnitude only takes |d| (|wrap16(32768)| == 32768)
+      const bool wrap = WRAP && !(last && s == m - 1);    // the magnitude only takes |d| (|wrap16(32768)| == 32768)
 #pragma unroll
       for (int rr = 0; rr < R; ++rr)
         if (!(rr & dist)) {
@@ -209,12 +211,42 @@ __device__ __forceinline__ void fast_pass(const FastArgs &a, int tl, const uint3
 // would do -- measured on B200 it is 7% SLOWER than the plain CTA barrier (204 vs 219 Gsamples/s), so the CTA barrier stays.
 template <int S> __device__ __forceinline__ void chirp_sync(int) { __syncthreads(); }
 
+// A row is "quiet" when every input component is within +-QUIET_MAX.  Then |x| <= 32739 for every complex input, a scaled
+// butterfly raises the largest modulus by at most sqrt(2)/2 (the two roundings), a twiddle product by at most
+// 32767 * 2^-14 * sqrt(2)/2 + sqrt(2)/2 (twiddle quantisation + rounding), the x(-j) keeps it: after S <= 14 stages and
+// 6 products no modulus, hence no component, exceeds 32739 + 14 * 0.71 + 6 * 2.2 < 32767, and nothing ever wraps.
+// Rows that are not quiet (full-scale inputs, the -32768 corners) take the passes with the wraps; both give the same bits.
+#define RSP_QUIET_MAX 23150
+__device__ __forceinline__ bool quiet_beats(const uint32_t (&pre)[16]) {
+  uint32_t mx = pre[0], mn = pre[0];
+#pragma unroll
+  for (int k = 1; k < 15; k += 2) { mx = __vimax3_s16x2(mx, pre[k], pre[k + 1]); mn = __vimin3_s16x2(mn, pre[k], pre[k + 1]); }
+  mx = __vmaxs2(mx, pre[15]); mn = __vmins2(mn, pre[15]);
+  const uint32_t lim = (uint32_t)RSP_QUIET_MAX * 0x10001u, nlim = (uint32_t)(0x10000 - RSP_QUIET_MAX) * 0x10001u;
+  return __vmins2(mx, lim) == mx && __vmaxs2(mn, nlim) == mn;
+}
+
+// The first pass works on the thread's own 16 beats, so each warp decides for itself; the later passes mix the whole chirp and
+// decide by the chirp's flag, which every warp of the chirp has or-ed into before the barrier that ends the first pass.
 template <int S, int K>
-__device__ __forceinline__ void fast_passes(const FastArgs &a, int c, int tl, const uint32_t (&pre)[16], uint32_t *xb, uint32_t *xm) {
-  static_assert(K != 0 || fx_pass_size(S, 0) == 4, "the first pass takes the 16 prefetched beats of the thread");
-  fast_pass<S, K>(a, tl, pre, xb, xm);
+__device__ __forceinline__ void fast_passes_from(const FastArgs &a, int c, int tl, bool quiet, const uint32_t (&pre)[16], uint32_t *xb, uint32_t *xm) {
+  if (quiet) fast_pass<S, K, false>(a, tl, pre, xb, xm); else fast_pass<S, K, true>(a, tl, pre, xb, xm);
   chirp_sync<S>(c);
-  if constexpr (K + 1 < fx_n_passes(S)) fast_passes<S, K + 1>(a, c, tl, pre, xb, xm);
+  if constexpr (K + 1 < fx_n_passes(S)) fast_passes_from<S, K + 1>(a, c, tl, quiet, pre, xb, xm);
+}
+
+template <int S, int K>
+__device__ __forceinline__ void fast_passes(const FastArgs &a, int c, int tl, const uint32_t (&pre)[16], uint32_t *xb, uint32_t *xm, int *loud) {
+  static_assert(K == 0 && fx_pass_size(S, 0) == 4, "the first pass takes the 16 prefetched beats of the thread");
+  const bool warp_quiet = __all_sync(0xffffffffu, quiet_beats(pre));
+  if (!warp_quiet && (tl & 31) == 0) loud[c] = 1;
+  if (warp_quiet) fast_pass<S, 0, false>(a, tl, pre, xb, xm); else fast_pass<S, 0, true>(a, tl, pre, xb, xm);
+  chirp_sync<S>(c);
+  if constexpr (fx_n_passes(S) > 1) {
+    const bool quiet = loud[c] == 0;
+    fast_passes_from<S, 1>(a, c, tl, quiet, pre, xb, xm);     // ends with a barrier: every thread has read the flag
+    if (tl == 0) loud[c] = 0;                                 // next written before the first barrier of the next row
+  }
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
@@ -304,6 +336,9 @@ __global__ void __launch_bounds__(FGeo<S>::THREADS, 1024 / FGeo<S>::THREADS) cha
   constexpr int N = Gm::N, TPC = Gm::TPC, CPC = Gm::CPC, PTS = Gm::PTS;
   extern __shared__ __align__(16) uint32_t smem[];
   __shared__ int wsum[CPC * Gm::NW];
+  __shared__ int loud[CPC];   // per chirp: some warp saw a beat that is not quiet (fast_passes)
+  if (threadIdx.x < CPC) loud[threadIdx.x] = 0;
+  __syncthreads();
   const int c = threadIdx.x / TPC, tl = threadIdx.x % TPC;
   uint32_t *xb = smem + (size_t)c * Gm::ROW, *xm = xb + Gm::XB;
   int *P = reinterpret_cast<int *>(xb);
@@ -321,7 +356,7 @@ __global__ void __launch_bounds__(FGeo<S>::THREADS, 1024 / FGeo<S>::THREADS) cha
 #pragma unroll
       for (int rr = 0; rr < PTS; ++rr) pre[rr] = __ldg(&gin[rr * TPC]);
     }
-    fast_passes<S, 0>(a, c, tl, pre, xb, xm);
+    fast_passes<S, 0>(a, c, tl, pre, xb, xm, loud);
     // prefix sums of the thread's 16 consecutive magnitudes
     int x[PTS];
     {
@@ -456,6 +491,9 @@ __global__ void __launch_bounds__(FGeo<S>::THREADS, 1024 / FGeo<S>::THREADS) cha
   using Gg = GGeo<S>;
   constexpr int N = Gm::N, TPC = Gm::TPC, CPC = Gm::CPC, PTS = Gm::PTS;
   extern __shared__ __align__(16) uint32_t smem[];
+  __shared__ int loud[CPC];
+  if (threadIdx.x < CPC) loud[threadIdx.x] = 0;
+  __syncthreads();
   const int c = threadIdx.x / TPC, tl = threadIdx.x % TPC;
   uint32_t *xb = smem + (size_t)c * Gg::ROW, *xm = xb + Gg::XBG;
   const short *X = reinterpret_cast<const short *>(xm);
@@ -471,7 +509,7 @@ __global__ void __launch_bounds__(FGeo<S>::THREADS, 1024 / FGeo<S>::THREADS) cha
 #pragma unroll
       for (int rr = 0; rr < PTS; ++rr) pre[rr] = __ldg(&gin[rr * TPC]);
     }
-    fast_passes<S, 0>(a, c, tl, pre, xb, xm);
+    fast_passes<S, 0>(a, c, tl, pre, xb, xm, loud);
     {   // the thread's 16 cells as 32-bit words in the padded array (the exchange buffer is dead)
       const uint4 v0 = *reinterpret_cast<const uint4 *>(&xm[tl * 8]), v1 = *reinterpret_cast<const uint4 *>(&xm[tl * 8 + 4]);
       const uint32_t wd[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};

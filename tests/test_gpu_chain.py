@@ -265,3 +265,32 @@ def test_fast_gos_kernel_variants(cuda, oracle, log_n, W, G, kl, kr):
             configure(ch, log_n, 2, regs)
             assert ch.variant == f"chain_fixed_fast_gos<{log_n}>", ch.variant
         run_and_compare(cuda, oracle, p, log_n, 2, regs, beats)
+
+
+@pytest.mark.parametrize("log_n", [10, 12])
+def test_fast_kernel_quiet_and_loud_rows(cuda, oracle, log_n):
+    """the fast kernel leaves the 16-bit wraps of the butterflies out for rows whose beats are all within +-23150 (they cannot wrap)
+    and keeps them for the others, warp by warp in the first pass and chirp by chirp afterwards: rows at the limit, one beat over it,
+    full-scale square waves (the -32768 / +32767 corners that do wrap), and a loud beat seen by only one warp of the chirp"""
+    n = 1 << log_n
+    rng = np.random.default_rng(log_n)
+    rows = []
+    for amp in (23150, 23151, 32767):
+        re = rng.integers(-amp, amp + 1, n); im = rng.integers(-amp, amp + 1, n)
+        re[::7] = amp; im[::5] = -amp
+        rows.append((re, im))
+    sq = np.where((np.arange(n) // 3) % 2 == 0, 32767, -32768)
+    rows.append((sq, -sq - 1))
+    rows.append((np.full(n, -32768), np.full(n, -32768)))
+    for pos in (0, n // 2 + 5, n - 1):          # quiet noise with a single loud beat
+        re = rng.integers(-2000, 2001, n); im = rng.integers(-2000, 2001, n)
+        re[pos] = -32768
+        rows.append((re, im))
+    beats = np.stack([((r.astype(np.int64) & 0xFFFF) << 16 | (i.astype(np.int64) & 0xFFFF)).astype(np.uint32) for r, i in rows])
+    beats = np.concatenate([beats, synth.chirps_fixed(3, n, seed=77)])
+    p = _fast_params(n, 16, 4)
+    regs = dict(fftWin=n, thresholdScaler=3, logOrLinearMode=1, divSum=4, peakGrouping=0, cfarMode=0, windowCells=16, guardCells=4)
+    with R.FftMagCfarChainVanilla(p) as ch:
+        configure(ch, log_n, 2, regs)
+        assert ch.variant == f"chain_fixed_fast<{log_n}>"
+    run_and_compare(cuda, oracle, p, log_n, 2, regs, beats)
