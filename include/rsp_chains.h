@@ -70,7 +70,15 @@ typedef struct {
   int32_t expandLogicAny;   /* 1 if any expandLogic(i) != 0 (grow mode -> RSP_EUNSUPPORTED)                */
   int32_t keepMSBorLSBReg;  /* 1: the keepMSBorLSBReg register overrides keepMSBorLSB (FFTBlock.scala:92-93)   */
   int32_t fftDirReg;        /* 1: the fftDir register overrides fftDir (FFTBlock.scala:90-91)                 */
+  /* windowFunc (generators/sdf-fft/src/main/scala/WindowFunc.scala:10-38): the coefficient ROM of numPoints entries of type
+   * protoWin = FixedPoint(windowWidth, windowWidth - 2) (SDFFFTParams.scala:118; doubles in the fp32 flavour), multiplied into
+   * the forward transform's input, `in * window(cntWin)` truncated on assignment (SDFFFT.scala:53-66,233-234).                */
+  int32_t windowFunc;       /* rsp_window; RSP_WINDOW_NONE = no multiply                                    */
+  int32_t windowWidth;      /* WindowFunctionType.dataWidth, 3..16                                           */
+  double windowA0, windowA1, windowA2;   /* Hamming: alpha, beta; Blackman: a0, a1, a2 (WindowFunc.scala:13-28)      */
 } rsp_fft_params;
+typedef enum { RSP_WINDOW_NONE = 0, RSP_WINDOW_HAMMING = 1, RSP_WINDOW_HANNING = 2, RSP_WINDOW_BLACKMAN = 3, RSP_WINDOW_TRIANGULAR = 4,
+               RSP_WINDOW_USER = 5 } rsp_window;
 
 /* MAGParams.fixed (generators/logMagMux/src/main/scala/LogMagMux.scala:14-49) */
 typedef struct {
@@ -171,6 +179,10 @@ rsp_status rsp_reg_read(rsp_chain *c, rsp_block blk, uint32_t word_index, uint32
 /* replaces: writes into the PLFG config RAM at plfgRAM + 4*word_index, word = {reset, sign, nSamples, slope}
  *           (generators/plfg/src/main/scala/PLFGDspBlockMem.scala:108-128,168-178) */
 rsp_status rsp_plfg_ram_write(rsp_chain *c, uint32_t word_index, uint32_t value);
+/* WindowFunctionTypes.User(dataWidth, dv) (WindowFunc.scala:30-33): the numPoints doubles of a user-specified window; the chain
+ * must have been created with windowFunc = RSP_WINDOW_USER (until this call its window is all ones).  n must equal numPoints
+ * (SDFFFT.scala:59: "Length of specified window function is not the same as fft size").  Synchronises the device.            */
+rsp_status rsp_fft_window_user(rsp_chain *c, const double *coeffs, uint32_t n);
 
 /* ---- the hot path, device buffers ------------------------------------------------------------------------
  * replaces: streaming n_rx*n_chirps chirps of fftSize beats into FftMagCfarChainVanilla.streamNode and reading

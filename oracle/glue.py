@@ -32,3 +32,13 @@ def oracle_cfgs(O, params, log_n, sel, cfar_regs: dict):
                       div_sum=r["divSum"], peak_grouping=r["peakGrouping"], cfar_algorithm=alg, cfar_mode=r["cfarMode"],
                       index_lagg=r["indexLagg"], index_lead=r["indexLead"], sub_cells=r["subWindowSize"])
     return fft, mag, cfar
+
+
+def apply_window(O, params, beats):
+    """the window multiply in front of the forward transform (identity for WindowFunctionTypes.None / the IFFT)"""
+    f = params.fftParams
+    w = f.windowFunc
+    if w is None or w.kind == 0 or not f.fftDir:
+        return beats
+    raw = O.window_raw(O.window_coeffs(w.kind, f.numPoints, w.a0, w.a1, w.a2, w.dv), w.dataWidth)
+    return O.apply_window_words(beats, raw, w.dataWidth, f.dataWidth)

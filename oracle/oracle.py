@@ -407,3 +407,52 @@ def unpack_iq(words):
 
 def trim(v, shift, mode):
     return int(lib().rspo_trim(C.c_int64(int(v)), shift, TRIM[mode] if isinstance(mode, str) else mode))
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# window functions (generators/sdf-fft/src/main/scala/WindowFunc.scala:41-65, SDFFFT.scala:53-66,233-234).  numpy restatement:
+# integer arithmetic on the beats, so it stays exact.
+WINDOW_NONE, WINDOW_HAMMING, WINDOW_HANNING, WINDOW_BLACKMAN, WINDOW_TRIANGULAR, WINDOW_USER = range(6)
+
+
+def window_coeffs(kind, length, a0=0.0, a1=0.0, a2=0.0, dv=None):
+    """the doubles of the window ROM: SDFFFT.scala:53-62 always calls the generators with their default isPeriodic = true"""
+    if kind == WINDOW_NONE:
+        return np.ones(length)
+    if kind == WINDOW_USER:
+        assert len(dv) == length, "Length of specified window function is not the same as fft size"
+        return np.asarray(dv, dtype=np.float64)
+    if length == 1:
+        return np.ones(1)
+    count = np.arange(length + 1, dtype=np.float64)
+    if kind == WINDOW_HAMMING:          # hammingWindow(length, alpha, beta) (:43-47)
+        w = a0 - a1 * np.cos(2 * np.pi * count / length)
+    elif kind == WINDOW_HANNING:        # hanningWindow (:61-65)
+        w = 0.5 * (1 - np.cos(2 * np.pi * count / length))
+    elif kind == WINDOW_BLACKMAN:       # blackmanWindow (:55-59); its periodic branch has no .take(length): length + 1 values, the ROM is indexed 0..length-1
+        w = a0 - a1 * np.cos(2 * np.pi * count / length) + a2 * np.cos(4 * np.pi * count / length)
+    elif kind == WINDOW_TRIANGULAR:     # triangularWindow (:49-53)
+        w = 1 - np.abs((count - length / 2.0) / (length / 2.0))
+    else:
+        raise ValueError(kind)
+    return w[:length]
+
+
+def window_raw(coeffs, width=16):
+    """fromDoubleWithFixedWidth(t, FixedPoint(width, width - 2)): round half up, then the width-bit two's complement value"""
+    raw = np.floor(np.ldexp(np.asarray(coeffs, dtype=np.float64), width - 2) + 0.5).astype(np.int64)
+    return ((raw + (1 << (width - 1))) & ((1 << width) - 1)) - (1 << (width - 1))
+
+
+def apply_window_words(beats, raw, width=16, data_width=16):
+    """`in * window(cntWin)` on Cat(re16, im16) beats [rows, n]: full-precision product, the assignment to protoIQ floors away the
+    width - 2 fractional bits and drops the MSBs (SDFFFT.scala:233-234); cntWin runs 0..n-1 over the first n ROM entries"""
+    b = np.asarray(beats, dtype=np.uint32)
+    n = b.shape[-1]
+    w = np.asarray(raw, dtype=np.int64)[:n]
+    half, mask = 1 << (data_width - 1), (1 << data_width) - 1
+    def sx(v):
+        return ((v.astype(np.int64) + half) & mask) - half
+    re = sx((b >> 16) & mask); im = sx(b & mask)
+    re = sx((re * w) >> (width - 2)); im = sx((im * w) >> (width - 2))
+    return (((re & 0xFFFF) << 16) | (im & 0xFFFF)).astype(np.uint32)

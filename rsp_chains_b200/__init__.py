@@ -6,7 +6,7 @@ from ._abi import RspError
 from .chain import (FftMagCfarChainVanilla, RspChainVanilla, gather_detections, host_alloc, host_free, shard_rows)
 from .params import (AddressSet, CACFARType, CFARParams, Convergent, DIFDecimType, DITDecimType, FFTParams,
                      FftMagCfarVanillaParameters, FixedNCOParams, FixedPLFGParams, FixedPoint, GOSCACFARType, GOSCFARType,
-                     MAGParams, RoundDown, RoundHalfUp, RspChainVanillaParameters, fft_mag_cfar_chain_vanilla_app_params,
+                     MAGParams, RoundDown, RoundHalfUp, RspChainVanillaParameters, WindowFunctionType, WindowFunctionTypes, fft_mag_cfar_chain_vanilla_app_params,
                      log2Up, rsp_chain_vanilla_app_params)
 
 __all__ = [n for n in dir() if not n.startswith("_")]

@@ -44,6 +44,14 @@ class _Chain:
         self._c_params = c_params
         _abi.check(self._lib.rsp_chain_create(C.byref(c_params), self.device, C.byref(self._h)))
 
+    def _load_user_window(self, fft_params):
+        """WindowFunctionTypes.User: the coefficients are part of the case class, the C ABI takes them right after creation"""
+        w = fft_params.windowFunc
+        if w is not None and w.kind == 5:
+            assert len(w.dv) == fft_params.numPoints, "Length of specified window function is not the same as fft size"
+            arr = (C.c_double * len(w.dv))(*w.dv)
+            _abi.check(self._lib.rsp_fft_window_user(self._h, arr, len(w.dv)))
+
     # ---- life cycle
     def close(self):
         if getattr(self, "_h", None) and self._h.value:
@@ -231,6 +239,7 @@ class FftMagCfarChainVanilla(_Chain):
         self.params = params
         amap = [(params.fftAddress, _abi.BLK_FFT), (params.magAddress, _abi.BLK_MAG), (params.cfarAddress, _abi.BLK_CFAR)]
         super().__init__(_c_params(params.fftParams, params.magParams, params.cfarParams), amap, params.beatBytes, device)
+        self._load_user_window(params.fftParams)
 
 
 class RspChainVanilla(_Chain):
@@ -242,6 +251,7 @@ class RspChainVanilla(_Chain):
                 (params.fftAddress, _abi.BLK_FFT), (params.magAddress, _abi.BLK_MAG), (params.cfarAddress, _abi.BLK_CFAR)]
         super().__init__(_c_params(params.fftParams, params.magParams, params.cfarParams, params.plfgParams, params.ncoParams),
                          amap, params.beatBytes, device)
+        self._load_user_window(params.fftParams)
 
     def generate(self, n_samples: int, nco_out=None, plfg_out=None, stream=None):
         """PLFGDspBlockMem -> AXI4NCOLazyModuleBlock alone (rsp_generate)"""

@@ -45,7 +45,8 @@ struct rsp_chain {
   int32_t *d_tw2 = nullptr;
   F2 *d_twf = nullptr;
   float *d_twf4 = nullptr;
-  int32_t *d_log_tab = nullptr, *d_nco_tab = nullptr;
+  int32_t *d_log_tab = nullptr, *d_nco_tab = nullptr, *d_win = nullptr;
+  float *d_winf = nullptr;
   GenSegment *d_segs = nullptr;
   size_t segs_cap = 0;
   uint32_t *d_gen_scratch = nullptr;   // NCO beats between generator and chain when the caller does not want them
@@ -144,7 +145,7 @@ extern "C" void rsp_chain_params_default(rsp_chain_params *p) {
   rsp_fft_params &f = p->fft;
   f.numPoints = 1024; f.dataWidth = 16; f.binPoint = 0; f.twiddleWidth = 16; f.trimType = RSP_TRIM_ROUND_HALF_UP; f.use4Muls = 0;
   f.useBitReverse = 1; f.fftDir = 1; f.runTime = 1; f.keepMSBorLSB = 0x3FF; f.decimType = 0; f.sdfRadix = 4; f.expandLogicAny = 0;
-  f.keepMSBorLSBReg = 0; f.fftDirReg = 0;
+  f.keepMSBorLSBReg = 0; f.fftDirReg = 0; f.windowFunc = RSP_WINDOW_NONE; f.windowWidth = 16;
   p->mag = {16, 0, 16, 9, 9};
   rsp_cfar_params &c = p->cfar;
   c.inWidth = 16; c.inBinPoint = 0; c.thresholdWidth = 16; c.thresholdBinPoint = 0; c.scalerWidth = 16; c.scalerBinPoint = 0;
@@ -169,7 +170,7 @@ extern "C" void rsp_chain_destroy(rsp_chain *c) {
   cudaSetDevice(c->device);
   free_pipe(c);
   for (int i = 0; i < N_PIPE; ++i) if (c->pipe_stream[i]) cudaStreamDestroy(c->pipe_stream[i]);
-  cudaFree(c->d_tw); cudaFree(c->d_tw2); cudaFree(c->d_twf); cudaFree(c->d_twf4); cudaFree(c->d_log_tab); cudaFree(c->d_nco_tab); cudaFree(c->d_segs);
+  cudaFree(c->d_tw); cudaFree(c->d_tw2); cudaFree(c->d_twf); cudaFree(c->d_twf4); cudaFree(c->d_win); cudaFree(c->d_winf); cudaFree(c->d_log_tab); cudaFree(c->d_nco_tab); cudaFree(c->d_segs);
   cudaFree(c->d_gen_scratch); cudaFree(c->d_det_list); cudaFree(c->d_det_count);
   delete c;
 }
@@ -201,10 +202,13 @@ extern "C" rsp_status rsp_chain_create(const rsp_chain_params *params, int devic
   c->sm_count = prop.multiProcessorCount;
   regs_reset(c->p, c->r);
   build_tables(c->p, c->t);
+  build_window(c->p, c->t);
   rsp_status s = upload(c->t.tw, &c->d_tw);
   if (s == RSP_OK) s = upload(c->t.tw2, &c->d_tw2);
   if (s == RSP_OK) s = upload(c->t.twf, &c->d_twf);
   if (s == RSP_OK) s = upload(c->t.twf4, &c->d_twf4);
+  if (s == RSP_OK) s = upload(c->t.win, &c->d_win);
+  if (s == RSP_OK) s = upload(c->t.winf, &c->d_winf);
   if (s == RSP_OK) s = upload(c->t.log_tab, &c->d_log_tab);
   if (s == RSP_OK) s = upload(c->t.nco_tab, &c->d_nco_tab);
   if (s != RSP_OK) { rsp_chain_destroy(c); return s; }
@@ -252,10 +256,23 @@ extern "C" rsp_status rsp_plfg_ram_write(rsp_chain *c, uint32_t idx, uint32_t va
   return RSP_OK;
 }
 
+extern "C" rsp_status rsp_fft_window_user(rsp_chain *c, const double *coeffs, uint32_t n) {
+  if (!c || !coeffs) return fail(RSP_EINVAL, "null argument");
+  if (c->p.fft.windowFunc != RSP_WINDOW_USER) return fail(RSP_EINVAL, "the chain was not created with windowFunc = RSP_WINDOW_USER");
+  if (n != (uint32_t)c->p.fft.numPoints) return fail(RSP_EINVAL, "Length of specified window function is not the same as fft size");
+  CUDA_TRY(cudaSetDevice(c->device));
+  CUDA_TRY(cudaDeviceSynchronize());   // a kernel in flight may still read the old ROM
+  c->t.win_user.assign(coeffs, coeffs + n);
+  build_window(c->p, c->t);
+  CUDA_TRY(cudaMemcpy(c->d_win, c->t.win.data(), c->t.win.size() * sizeof(int32_t), cudaMemcpyHostToDevice));
+  CUDA_TRY(cudaMemcpy(c->d_winf, c->t.winf.data(), c->t.winf.size() * sizeof(float), cudaMemcpyHostToDevice));
+  return RSP_OK;
+}
+
 // ---------------------------------------------------------------------------------------------------------------------
 // planning glue
-static void bind_fixed(rsp_chain *c, FxArgs &a) { a.tw = c->d_tw; a.tw2 = c->d_tw2; a.log_tab = c->d_log_tab; }
-static void bind_f32(rsp_chain *c, F32Args &a) { a.tw = c->d_twf; }
+static void bind_fixed(rsp_chain *c, FxArgs &a) { a.tw = c->d_tw; a.tw2 = c->d_tw2; a.log_tab = c->d_log_tab; a.win = c->d_win; }
+static void bind_f32(rsp_chain *c, F32Args &a) { a.tw = c->d_twf; a.win = c->d_winf; }
 static void bind_dets(const rsp_dets *d, Detection **list, uint32_t **count, uint32_t *cap) {
   if (d && d->list && d->count) { *list = reinterpret_cast<Detection *>(d->list); *count = d->count; *cap = d->capacity; }
   else { *list = nullptr; *count = nullptr; *cap = 0; }

@@ -49,6 +49,8 @@ struct FxArgs {
   const uint32_t *tw;       // packed (cos16 << 16 | sin16) twiddles, per stageN three runs [W^2k | W^k | W^3k]
   int tw_off[16];           // word offset of the table of stageN = 1 << L
   const int32_t *tw2;       // same entries as int32 quads (c, s, -c, -s) << (16 - tw_bp) (fast kernels, rsp_fast.cu)
+  const int32_t *win;       // window ROM (protoWin raw values), read when win_on
+  int win_on, win_shift;    // win_shift = binary point of protoWin = windowWidth - 2
   // LogMagMux
   int sel, mag_w, mag_bp, log_w, log_bp, log_L, mag_trim;
   const int32_t *log_tab;
@@ -271,7 +273,13 @@ RSP_HD void fft_pass(const FxArgs &a, int tl, const uint32_t *gin, uint32_t *buf
       const uint32_t wd = first ? ldg(&gin[p]) : bufA[pad(p)];
       if (MODE != MODE_GENERIC) { re[rr] = hi16(wd); im[rr] = lo16(wd); }
       else {
-        const int r0 = wrapw((int)(wd >> 16), a.data_width), i0v = wrapw((int)(wd & 0xFFFFu), a.data_width);
+        int r0 = wrapw((int)(wd >> 16), a.data_width), i0v = wrapw((int)(wd & 0xFFFFu), a.data_width);
+        if (first && a.win_on) {
+          // in * window(cntWin): full-precision product, then the assignment to protoIQ drops win_shift fractional bits
+          // (floor) and the MSBs beyond dataWidth (SDFFFT.scala:233-234)
+          const int w = ldg(&a.win[p]);
+          r0 = wrapw((r0 * w) >> a.win_shift, a.data_width); i0v = wrapw((i0v * w) >> a.win_shift, a.data_width);
+        }
         // ifft swaps real and imaginary on the way in (SDFChainRadix22.scala:205-211)
         const bool sw = first && !a.fft_dir;
         re[rr] = sw ? i0v : r0; im[rr] = sw ? r0 : i0v;

@@ -23,6 +23,8 @@ struct F32Args {
   int bitrev, fft_dir;
   const F2 *tw;
   int tw_off[16];
+  const float *win;      // window coefficients, read when win_on
+  int win_on;
   int sel;
   // CFAR
   int core, guard_window_size, binw, send_cut;
@@ -71,7 +73,11 @@ RSP_HD void fft_pass_f32(const F32Args &a, int tl, const F2 *gin, F2 *bufA, floa
     for (int rr = 0; rr < R; ++rr) {
       const int p = base + rr * Dl;
       F2 v;
-      if (first) { v = gin[p]; if (!a.fft_dir) { const float t = v.x; v.x = v.y; v.y = t; } }
+      if (first) {
+        v = gin[p];
+        if (!a.fft_dir) { const float t = v.x; v.x = v.y; v.y = t; }
+        else if (a.win_on) { const float w = a.win[p]; v.x *= w; v.y *= w; }   // SDFFFT.scala:233-234
+      }
       else v = bufA[padf(p)];
       re[rr] = v.x; im[rr] = v.y;
     }

@@ -40,6 +40,9 @@ struct Tables {
   int tw_off[16];
   std::vector<int32_t> log_tab;
   std::vector<int32_t> nco_tab;
+  std::vector<int32_t> win;   // window ROM, protoWin raw values (empty: WindowFunctionTypes.None)
+  std::vector<float> winf;    // the same coefficients as floats (fp32 flavour: protoWin = DspReal)
+  std::vector<double> win_user;   // WindowFunctionTypes.User coefficients (rsp_fft_window_user)
 };
 
 // ---- the reference's elaboration-time checks -------------------------------------------------------------------
@@ -55,6 +58,8 @@ inline rsp_status validate_params(const rsp_chain_params &p, std::string &err) {
   RSP_REQ(f.decimType == 0, RSP_EUNSUPPORTED, "only DIFDecimType is built");
   RSP_REQ(f.sdfRadix == 4, RSP_EUNSUPPORTED, "only sdfRadix \"2^2\" is built");
   RSP_REQ(!f.expandLogicAny, RSP_EUNSUPPORTED, "expandLogic (grow) stages are not built");
+  RSP_REQ(f.windowFunc >= RSP_WINDOW_NONE && f.windowFunc <= RSP_WINDOW_USER, RSP_EINVAL, "unknown windowFunc");
+  RSP_REQ(f.windowFunc == RSP_WINDOW_NONE || (f.windowWidth >= 3 && f.windowWidth <= 16), RSP_EUNSUPPORTED, "window dataWidth must be in 3..16");
   if (p.arith == RSP_ARITH_FIXED) {
     RSP_REQ(f.dataWidth >= 2 && f.dataWidth <= 16, RSP_EUNSUPPORTED, "dataWidth must be in 2..16 (32-bit beats carry Cat(re16, im16))");
     RSP_REQ(f.binPoint >= 0 && f.binPoint <= 15, RSP_EINVAL, "binPoint must be in 0..15");
@@ -232,6 +237,29 @@ inline void build_tables(const rsp_chain_params &p, Tables &t) {
   } else t.nco_tab.push_back(0);
 }
 
+// window ROM (SDFFFT.scala:53-66): the periodic forms of WindowFunc.scala:41-65 evaluated in double, then
+// fromDoubleWithFixedWidth into protoWin = FixedPoint(w, w - 2) (SDFFFTParams.scala:118)
+inline void build_window(const rsp_chain_params &p, Tables &t) {
+  const rsp_fft_params &f = p.fft;
+  t.win.clear(); t.winf.clear();
+  if (f.windowFunc == RSP_WINDOW_NONE) return;
+  const int n = f.numPoints, wbp = f.windowWidth - 2;
+  const double PI = 3.14159265358979323846;
+  for (int k = 0; k < n; ++k) {
+    double v = 1.0;
+    const double x = (double)k / (double)n;
+    if (n > 1) switch (f.windowFunc) {
+      case RSP_WINDOW_HAMMING: v = f.windowA0 - f.windowA1 * std::cos(2 * PI * x); break;
+      case RSP_WINDOW_HANNING: v = 0.5 * (1 - std::cos(2 * PI * x)); break;
+      case RSP_WINDOW_BLACKMAN: v = f.windowA0 - f.windowA1 * std::cos(2 * PI * x) + f.windowA2 * std::cos(4 * PI * x); break;
+      case RSP_WINDOW_TRIANGULAR: v = 1 - std::fabs(((double)k - n / 2.0) / (n / 2.0)); break;
+      default: v = (size_t)k < t.win_user.size() ? t.win_user[(size_t)k] : 1.0; break;
+    }
+    t.win.push_back((int32_t)wrap_host(from_double(v, wbp), f.windowWidth));
+    t.winf.push_back((float)v);
+  }
+}
+
 // ---- (params, registers) -> kernel arguments ------------------------------------------------------------------------
 struct Plan {
   int S;          // log2 of the transform / window size
@@ -297,6 +325,9 @@ inline rsp_status plan_fixed(const rsp_chain_params &p, const Regs &r, const Tab
   const uint32_t smask = S >= 32 ? 0xFFFFFFFFu : ((1u << S) - 1u);
   a.keep_mask = (first_stage == STAGE_CFAR) ? smask : ((phys >> (Smax - S)) & smask);   // run-time size uses the LAST S stages
   for (int L = 0; L < 16; ++L) a.tw_off[L] = t.tw_off[L];
+  // windowing happens on the forward transform only (SDFFFT.scala:229-245: `when (fftDir)`); win itself is bound by the caller
+  a.win_on = (first_stage == STAGE_FFT && f.windowFunc != RSP_WINDOW_NONE && a.fft_dir == 1) ? 1 : 0;
+  a.win_shift = f.windowWidth - 2;
   a.sel = (int)(r.mag[RSP_MAG_REG_SEL] & 3u);
   a.mag_w = p.mag.dataWidth; a.mag_bp = p.mag.binPoint; a.log_w = p.mag.dataWidthLog; a.log_bp = p.mag.binPointLog;
   a.log_L = p.mag.log2LookUpWidth; a.mag_trim = TRIM_FLOOR;   // DspContext default trimType
@@ -317,6 +348,7 @@ inline rsp_status plan_fixed(const rsp_chain_params &p, const Regs &r, const Tab
   const bool common = f.dataWidth == 16 && f.trimType == RSP_TRIM_ROUND_HALF_UP && a.keep_mask == smask && a.fft_dir == 1 &&
                       p.mag.dataWidth == 16;
   pl.mode = MODE_GENERIC;
+  if (a.win_on) return RSP_OK;   // the window multiply lives in the generic kernels
   if (common && s1 <= 0) pl.mode = MODE_FAST;
   else if (common && s1 >= 1 && !f.use4Muls) pl.mode = MODE_FAST3;
   return RSP_OK;
@@ -341,6 +373,7 @@ inline rsp_status plan_f32(const rsp_chain_params &p, const Regs &r, const Table
   a.bitrev = f.useBitReverse ? 1 : 0;
   a.fft_dir = f.fftDirReg ? (int)(r.fft[RSP_FFT_REG_FFTDIR] & 1u) : (f.fftDir ? 1 : 0);
   for (int L = 0; L < 16; ++L) a.tw_off[L] = t.tw_off[L];
+  a.win_on = (first_stage == STAGE_FFT && f.windowFunc != RSP_WINDOW_NONE && a.fft_dir == 1) ? 1 : 0;
   a.sel = (int)(r.mag[RSP_MAG_REG_SEL] & 3u);
   a.scaler = r.scaler_f32;
   if (last_stage == STAGE_CFAR) {

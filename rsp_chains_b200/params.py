@@ -48,6 +48,48 @@ class FixedPoint:
 
 
 @dataclass
+class WindowFunctionType:
+    """generators/sdf-fft/src/main/scala/WindowFunc.scala:10-38 (`isPeriodic` is carried but, as in the reference's SDFFFT.scala:53-62,
+    the ROM is always built from the periodic form)"""
+    kind: int = 0
+    dataWidth: int = 16
+    a0: float = 0.0
+    a1: float = 0.0
+    a2: float = 0.0
+    isPeriodic: bool = True
+    dv: Optional[List[float]] = None
+
+    def to_c(self):
+        return (self.kind, self.dataWidth, float(self.a0), float(self.a1), float(self.a2))
+
+
+class WindowFunctionTypes:
+    @staticmethod
+    def Hamming(dataWidth_tmp=16, alpha=0.54, beta=0.46, isPeriodic=True):
+        return WindowFunctionType(1, dataWidth_tmp, alpha, beta, 0.0, isPeriodic)
+
+    @staticmethod
+    def Hanning(dataWidth_tmp=16, isPeriodic=True):
+        return WindowFunctionType(2, dataWidth_tmp, 0.0, 0.0, 0.0, isPeriodic)
+
+    @staticmethod
+    def Blackman(dataWidth_tmp=16, a0=0.42, a1=0.5, a2=0.08, isPeriodic=True):
+        return WindowFunctionType(3, dataWidth_tmp, a0, a1, a2, isPeriodic)
+
+    @staticmethod
+    def Triangular(dataWidth_tmp=16, isPeriodic=True):
+        return WindowFunctionType(4, dataWidth_tmp, 0.0, 0.0, 0.0, isPeriodic)
+
+    @staticmethod
+    def User(dataWidth_tmp=16, dv=()):
+        return WindowFunctionType(5, dataWidth_tmp, dv=list(dv))
+
+    @staticmethod
+    def NoWindow(dataWidth_tmp=16):
+        return WindowFunctionType(0, dataWidth_tmp)
+
+
+@dataclass
 class FFTParams:
     numPoints: int = 2
     dataWidth: int = 16
@@ -70,7 +112,7 @@ class FFTParams:
     use4Muls: bool = False
     useBitReverse: bool = False
     minSRAMdepth: int = 0
-    windowFunc: Optional[str] = None
+    windowFunc: Optional["WindowFunctionType"] = None    # None = WindowFunctionTypes.None()
     arith: str = "fixed"       # "fixed" (FFTParams.fixed) or "fp32" (FFTParams.DSPReal run in single precision)
 
     @staticmethod
@@ -103,7 +145,8 @@ class FFTParams:
             self.numPoints, self.dataWidth, self.binPoint, self.twiddleWidth, _abi.TRIM[self.trimType],
             int(self.use4Muls), int(self.useBitReverse), int(self.fftDir), int(self.runTime), mask,
             0 if self.decimType == DIFDecimType else 1, 4 if self.sdfRadix == "2^2" else 2,
-            int(any(e != 0 for e in self.expandLogic)), int(self.keepMSBorLSBReg), int(self.fftDirReg))
+            int(any(e != 0 for e in self.expandLogic)), int(self.keepMSBorLSBReg), int(self.fftDirReg),
+            *(self.windowFunc.to_c() if self.windowFunc is not None else (0, 16, 0.0, 0.0, 0.0)))
 
 
 @dataclass

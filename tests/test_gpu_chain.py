@@ -294,3 +294,51 @@ def test_fast_kernel_quiet_and_loud_rows(cuda, oracle, log_n):
         configure(ch, log_n, 2, regs)
         assert ch.variant == f"chain_fixed_fast<{log_n}>"
     run_and_compare(cuda, oracle, p, log_n, 2, regs, beats)
+
+
+def test_window_functions(cuda, oracle):
+    """FFTParams.windowFunc (WindowFunc.scala, SDFFFT.scala:53-66,233-234): every window type in front of the forward transform, a
+    narrower coefficient type, a run-time size below numPoints (first n ROM entries), no window on the IFFT; whole chain and FFT alone"""
+    from oracle.glue import apply_window
+    from rsp_chains_b200 import WindowFunctionTypes as WT
+    n = 1024
+    rng = np.random.default_rng(5)
+    user = WT.User(14, dv=list(rng.uniform(-1.5, 1.9, n)))
+    beats = np.concatenate([synth.chirps_fixed(6, n, seed=21), synth.random_beats(3, n, seed=22)])
+    regs = dict(fftWin=n, thresholdScaler=3, logOrLinearMode=1, divSum=4, peakGrouping=0, cfarMode=0, windowCells=16, guardCells=4)
+    for win in (WT.Hanning(), WT.Hamming(16, 0.54, 0.46), WT.Blackman(12), WT.Triangular(10), user):
+        p = chain_params(n, 0, W=16, G=4)
+        p.fftParams.windowFunc = win
+        with R.FftMagCfarChainVanilla(p) as ch:
+            configure(ch, 10, 2, regs)
+            assert ch.variant == "chain_fixed<10,generic>", ch.variant
+        # the product applies the window itself: compare it on the raw beats with the oracle on the windowed beats
+        with R.FftMagCfarChainVanilla(p) as ch:
+            configure(ch, 10, 2, regs)
+            d_out = cuda.empty((beats.shape[0], n), dtype=cuda.int32, device="cuda")
+            ch.run(to_dev(cuda, beats), beats.shape[0], 1, out=d_out)
+            d_fft = cuda.empty((beats.shape[0], n), dtype=cuda.int32, device="cuda")
+            ch.fft(to_dev(cuda, beats), beats.shape[0], d_fft)
+            cuda.cuda.synchronize()
+            got, got_fft = from_dev_u32(d_out), from_dev_u32(d_fft)
+        fft, mag, cfar = oracle_cfgs(oracle, p, 10, 2, regs)
+        want, want_fft, _ = oracle.chain_fixed_words(fft, mag, cfar, apply_window(oracle, p, beats), want_stages=True)
+        assert (got_fft == want_fft).all(), win
+        assert (got == want).all(), win
+    # run-time size 256 of a 1024-point generator: cntWin addresses the first 256 coefficients
+    p = chain_params(n, 0, W=16, G=4)
+    p.fftParams.windowFunc = WT.Hanning()
+    regs8 = dict(regs, fftWin=256)
+    with R.FftMagCfarChainVanilla(p) as ch:
+        configure(ch, 8, 2, regs8)
+        d_out = cuda.empty((beats.shape[0], 256), dtype=cuda.int32, device="cuda")
+        ch.run(to_dev(cuda, np.ascontiguousarray(beats[:, :256])), beats.shape[0], 1, out=d_out)
+        cuda.cuda.synchronize()
+        got = from_dev_u32(d_out)
+    fft, mag, cfar = oracle_cfgs(oracle, p, 8, 2, regs8)
+    want = oracle.chain_fixed_words(fft, mag, cfar, apply_window(oracle, p, np.ascontiguousarray(beats[:, :256])))
+    assert (got == want).all()
+    # IFFT: no window (SDFFFT.scala:236-245)
+    p = chain_params(n, 0, W=16, G=4, fftDir=False)
+    p.fftParams.windowFunc = WT.Hanning()
+    run_and_compare(cuda, oracle, p, 10, 2, regs, beats)

@@ -144,6 +144,35 @@ def test_fast_f32_kernel_variants(cuda, oracle, log_n, W, G):
             assert dets[0, 2:].view(np.float32)[0] == thr[r0, b0]
 
 
+def test_fp32_window_functions(cuda, oracle):
+    """windowFunc in the fp32 flavour (protoWin = DspReal, SDFFFTParams.scala:177): x * window(n) in front of the forward transform"""
+    from rsp_chains_b200 import WindowFunctionTypes as WT
+    n, log_n, W, G, rows = 2048, 11, 32, 4, 4
+    xc = synth.chirps_complex(rows, n, seed=31)
+    x32 = np.stack([xc.real, xc.imag], axis=-1).astype(np.float32)
+    regs = dict(fftWin=n, logOrLinearMode=1, divSum=5, peakGrouping=0, cfarMode=0, windowCells=W, guardCells=G)
+    for win in (WT.Hanning(), WT.Blackman()):
+        p = f32_params(n, W, G)
+        p.fftParams.windowFunc = win
+        w = oracle.window_coeffs(win.kind, n, win.a0, win.a1, win.a2)
+        xq = (x32[..., 0].astype(np.float64) + 1j * x32[..., 1].astype(np.float64)) * w.astype(np.float32).astype(np.float64)[None, :]
+        with R.FftMagCfarChainVanilla(p) as ch:
+            configure(ch, log_n, 2, regs)
+            ch.set_threshold_scaler_f32(3.0)
+            assert ch.variant == f"chain_f32<{log_n}>", ch.variant
+            d_thr = cuda.empty((rows, n), dtype=cuda.float32, device="cuda")
+            d_mask = cuda.zeros((rows, n // 32), dtype=cuda.int32, device="cuda")
+            ch.run(cuda.from_numpy(x32).cuda(), rows, 1, out=d_thr, peak_mask=d_mask)
+            cuda.cuda.synchronize()
+            thr = d_thr.cpu().numpy()
+            pk = unpack_mask(d_mask.cpu().numpy().view(np.uint32), n)
+        mag, want_thr, want_pk = f64_chain(oracle, xq, log_n, 2, regs, 3.0, W, G)
+        rel = np.abs(thr - want_thr) / np.maximum(np.abs(want_thr), 1e-3 * np.abs(want_thr).max())
+        assert rel.max() < REL_TOL, f"{win.kind}: {rel.max():.3e}"
+        decided = np.abs(mag - want_thr) / np.maximum(np.abs(want_thr), 1e-30) > 10 * REL_TOL
+        assert (pk[decided] == want_pk[decided]).all()
+
+
 # ---------------------------------------------------------------------------------------------------- PLFG -> NCO
 
 def write_plfg(ch, p, oracle, starting_point, segs, n_rep=1, frame_num=1, inter=10):

@@ -205,3 +205,31 @@ def test_log2_lut_and_intended_math(oracle):
     u, v = np.maximum(abs(re), abs(im)), np.minimum(abs(re), abs(im))
     jpl = np.maximum(u + (v >> 3), (u - (u >> 3)) + (v >> 1))
     assert np.abs(lo / 512.0 - np.log2(jpl)).max() < 2.0 ** -8
+
+
+def test_window_rom_and_multiply():
+    """window ROM (WindowFunc.scala:41-65 periodic forms, protoWin = FixedPoint(w, w - 2), SDFFFTParams.scala:118) and the
+    truncating multiply of SDFFFT.scala:233-234"""
+    from oracle import oracle as O
+    n = 256
+    han = O.window_coeffs(O.WINDOW_HANNING, n)
+    ham = O.window_coeffs(O.WINDOW_HAMMING, n, 0.54, 0.46)
+    bla = O.window_coeffs(O.WINDOW_BLACKMAN, n, 0.42, 0.5, 0.08)
+    tri = O.window_coeffs(O.WINDOW_TRIANGULAR, n)
+    for w in (han, ham, bla, tri):
+        assert w.shape == (n,) and np.allclose(w[1:], w[1:][::-1]) and abs(w[n // 2] - 1.0) < 1e-12     # periodic: w[k] = w[n - k]
+    assert han[0] == 0.0 and abs(ham[0] - 0.08) < 1e-12 and abs(bla[0]) < 1e-12 and tri[0] == 0.0 and tri[n // 4] == 0.5
+    assert O.window_coeffs(O.WINDOW_HANNING, 1)[0] == 1.0
+    raw = O.window_raw(han, 16)
+    assert raw[n // 2] == 1 << 14 and raw[0] == 0 and raw.max() == 1 << 14 and (raw == np.floor(han * 2 ** 14 + 0.5)).all()
+    assert O.window_raw([1.0, -1.0, 1.99], 12).tolist() == [1 << 10, -(1 << 10), 2038]
+    # all ones (WindowFunctionTypes.None) is the identity, also on the -32768 corner
+    rng = np.random.default_rng(0)
+    beats = rng.integers(0, 1 << 32, (3, n), dtype=np.uint64).astype(np.uint32)
+    beats[0, 0] = 0x80008000
+    assert (O.apply_window_words(beats, O.window_raw(np.ones(n), 16)) == beats).all()
+    # floor, not round: -1 * 0.5 -> -1 (arithmetic shift), 1 * 0.5 -> 0
+    b = np.array([[(0xFFFF << 16) | 0x0001]], dtype=np.uint32)
+    assert O.apply_window_words(b, O.window_raw([0.5], 16))[0, 0] == 0xFFFF0000
+    # run-time size below numPoints: the first n ROM entries
+    assert (O.apply_window_words(beats[:, :64], raw) == O.apply_window_words(np.pad(beats[:, :64], ((0, 0), (0, n - 64))), raw)[:, :64]).all()
