@@ -45,7 +45,7 @@ struct rsp_chain {
   int32_t *d_tw2 = nullptr;
   F2 *d_twf = nullptr;
   float *d_twf4 = nullptr;
-  int32_t *d_log_tab = nullptr, *d_nco_tab = nullptr, *d_win = nullptr;
+  int32_t *d_log_tab = nullptr, *d_nco_tab = nullptr, *d_win = nullptr, *d_win4 = nullptr;
   float *d_winf = nullptr;
   GenSegment *d_segs = nullptr;
   size_t segs_cap = 0;
@@ -170,7 +170,7 @@ extern "C" void rsp_chain_destroy(rsp_chain *c) {
   cudaSetDevice(c->device);
   free_pipe(c);
   for (int i = 0; i < N_PIPE; ++i) if (c->pipe_stream[i]) cudaStreamDestroy(c->pipe_stream[i]);
-  cudaFree(c->d_tw); cudaFree(c->d_tw2); cudaFree(c->d_twf); cudaFree(c->d_twf4); cudaFree(c->d_win); cudaFree(c->d_winf); cudaFree(c->d_log_tab); cudaFree(c->d_nco_tab); cudaFree(c->d_segs);
+  cudaFree(c->d_tw); cudaFree(c->d_tw2); cudaFree(c->d_twf); cudaFree(c->d_twf4); cudaFree(c->d_win); cudaFree(c->d_win4); cudaFree(c->d_winf); cudaFree(c->d_log_tab); cudaFree(c->d_nco_tab); cudaFree(c->d_segs);
   cudaFree(c->d_gen_scratch); cudaFree(c->d_det_list); cudaFree(c->d_det_count);
   delete c;
 }
@@ -208,6 +208,7 @@ extern "C" rsp_status rsp_chain_create(const rsp_chain_params *params, int devic
   if (s == RSP_OK) s = upload(c->t.twf, &c->d_twf);
   if (s == RSP_OK) s = upload(c->t.twf4, &c->d_twf4);
   if (s == RSP_OK) s = upload(c->t.win, &c->d_win);
+  if (s == RSP_OK) s = upload(c->t.win4, &c->d_win4);
   if (s == RSP_OK) s = upload(c->t.winf, &c->d_winf);
   if (s == RSP_OK) s = upload(c->t.log_tab, &c->d_log_tab);
   if (s == RSP_OK) s = upload(c->t.nco_tab, &c->d_nco_tab);
@@ -265,13 +266,14 @@ extern "C" rsp_status rsp_fft_window_user(rsp_chain *c, const double *coeffs, ui
   c->t.win_user.assign(coeffs, coeffs + n);
   build_window(c->p, c->t);
   CUDA_TRY(cudaMemcpy(c->d_win, c->t.win.data(), c->t.win.size() * sizeof(int32_t), cudaMemcpyHostToDevice));
+  CUDA_TRY(cudaMemcpy(c->d_win4, c->t.win4.data(), c->t.win4.size() * sizeof(int32_t), cudaMemcpyHostToDevice));
   CUDA_TRY(cudaMemcpy(c->d_winf, c->t.winf.data(), c->t.winf.size() * sizeof(float), cudaMemcpyHostToDevice));
   return RSP_OK;
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
 // planning glue
-static void bind_fixed(rsp_chain *c, FxArgs &a) { a.tw = c->d_tw; a.tw2 = c->d_tw2; a.log_tab = c->d_log_tab; a.win = c->d_win; }
+static void bind_fixed(rsp_chain *c, FxArgs &a) { a.tw = c->d_tw; a.tw2 = c->d_tw2; a.log_tab = c->d_log_tab; a.win = c->d_win; a.win4 = c->d_win4; }
 static void bind_f32(rsp_chain *c, F32Args &a) { a.tw = c->d_twf; a.win = c->d_winf; }
 static void bind_dets(const rsp_dets *d, Detection **list, uint32_t **count, uint32_t *cap) {
   if (d && d->list && d->count) { *list = reinterpret_cast<Detection *>(d->list); *count = d->count; *cap = d->capacity; }

@@ -50,6 +50,7 @@ struct FxArgs {
   int tw_off[16];           // word offset of the table of stageN = 1 << L
   const int32_t *tw2;       // same entries as int32 quads (c, s, -c, -s) << (16 - tw_bp) (fast kernels, rsp_fast.cu)
   const int32_t *win;       // window ROM (protoWin raw values), read when win_on
+  const int32_t *win4;      // the same << (16 - win_shift): bits 16..31 of beat * win4 are the windowed beat (fast kernels)
   int win_on, win_shift;    // win_shift = binary point of protoWin = windowWidth - 2
   // LogMagMux
   int sel, mag_w, mag_bp, log_w, log_bp, log_L, mag_trim;
@@ -271,8 +272,13 @@ RSP_HD void fft_pass(const FxArgs &a, int tl, const uint32_t *gin, uint32_t *buf
     for (int rr = 0; rr < R; ++rr) {
       const int p = base + rr * Dl;
       const uint32_t wd = first ? ldg(&gin[p]) : bufA[pad(p)];
-      if (MODE != MODE_GENERIC) { re[rr] = hi16(wd); im[rr] = lo16(wd); }
-      else {
+      if (MODE != MODE_GENERIC) {   // dataWidth 16, forward
+        re[rr] = hi16(wd); im[rr] = lo16(wd);
+        if (first && a.win_on) {
+          const int w = ldg(&a.win[p]);
+          re[rr] = wrap16((re[rr] * w) >> a.win_shift); im[rr] = wrap16((im[rr] * w) >> a.win_shift);
+        }
+      } else {
         int r0 = wrapw((int)(wd >> 16), a.data_width), i0v = wrapw((int)(wd & 0xFFFFu), a.data_width);
         if (first && a.win_on) {
           // in * window(cntWin): full-precision product, then the assignment to protoIQ drops win_shift fractional bits

@@ -26,6 +26,7 @@ struct FastArgs {
   const uint32_t *in;
   uint32_t *out;
   uint32_t n_rows, row_base;
+  const int32_t *win4;   // window ROM << (16 - binary point) or null (FFTParams.windowFunc, SDFFFT.scala:53-66,233-234)
   const int4 *tw;        // (c, s, -c, -s) with c = cos << 2, s = -sin(2 pi t / stageN) << 2; per stageN three runs [W^2k | W^k | W^3k]
   int tw_off[16];
   int W, G, div_sum, scaler;   // div_sum here = (32 - sumw) + divSum: shift applied to the pre-scaled window sums (see wmul)
@@ -207,6 +208,25 @@ __device__ __forceinline__ void fast_pass(const FastArgs &a, int tl, const uint3
   }
 }
 
+// The thread's 16 beats of a row, p = tl + rr * TPC (warp-contiguous 128-byte lines), times the window when there is one:
+// bits 16..31 of beat * (window << (16 - bp)) are wrap16(floor(beat * window >> bp)), the truncating assignment of
+// SDFFFT.scala:233-234; the windowed beats are packed again so that everything behind (the quiet test too) sees plain beats.
+template <int S>
+__device__ __forceinline__ void load_beats(const FastArgs &a, uint32_t row, int tl, uint32_t (&pre)[16]) {
+  constexpr int N = 1 << S, TPC = FGeo<S>::TPC;
+  const uint32_t *gin = a.in + (size_t)row * N + tl;
+#pragma unroll
+  for (int rr = 0; rr < 16; ++rr) pre[rr] = __ldg(&gin[rr * TPC]);
+  if (a.win4 != nullptr) {
+    const int32_t *gw = a.win4 + tl;
+#pragma unroll
+    for (int rr = 0; rr < 16; ++rr) {
+      const int w = __ldg(&gw[rr * TPC]);
+      pre[rr] = __byte_perm((uint32_t)(sext16((int)pre[rr]) * w), (uint32_t)(hi16s(pre[rr]) * w), 0x7632);
+    }
+  }
+}
+
 // Barrier between the phases of a row.  The chirps of a CTA share nothing, so a named barrier per chirp (bar.sync c + 1, TPC)
 // would do -- measured on B200 it is 7% SLOWER than the plain CTA barrier (204 vs 219 Gsamples/s), so the CTA barrier stays.
 template <int S> __device__ __forceinline__ void chirp_sync(int) { __syncthreads(); }
@@ -350,12 +370,8 @@ __global__ void __launch_bounds__(FGeo<S>::THREADS, 1024 / FGeo<S>::THREADS) cha
   for (uint32_t row0 = blockIdx.x * CPC; row0 < a.n_rows; row0 += stride) {
     const bool active = row0 + c < a.n_rows;
     const uint32_t row = active ? row0 + c : a.n_rows - 1;
-    uint32_t pre[PTS];   // the thread's 16 beats of the row: p = tl + rr * TPC, warp-contiguous 128-byte lines
-    {
-      const uint32_t *gin = a.in + (size_t)row * N + tl;
-#pragma unroll
-      for (int rr = 0; rr < PTS; ++rr) pre[rr] = __ldg(&gin[rr * TPC]);
-    }
+    uint32_t pre[PTS];
+    load_beats<S>(a, row, tl, pre);
     fast_passes<S, 0>(a, c, tl, pre, xb, xm, loud);
     // prefix sums of the thread's 16 consecutive magnitudes
     int x[PTS];
@@ -504,11 +520,7 @@ __global__ void __launch_bounds__(FGeo<S>::THREADS, 1024 / FGeo<S>::THREADS) cha
     const bool active = row0 + c < a.n_rows;
     const uint32_t row = active ? row0 + c : a.n_rows - 1;
     uint32_t pre[PTS];
-    {
-      const uint32_t *gin = a.in + (size_t)row * N + tl;
-#pragma unroll
-      for (int rr = 0; rr < PTS; ++rr) pre[rr] = __ldg(&gin[rr * TPC]);
-    }
+    load_beats<S>(a, row, tl, pre);
     fast_passes<S, 0>(a, c, tl, pre, xb, xm, loud);
     {   // the thread's 16 cells as 32-bit words in the padded array (the exchange buffer is dead)
       const uint4 v0 = *reinterpret_cast<const uint4 *>(&xm[tl * 8]), v1 = *reinterpret_cast<const uint4 *>(&xm[tl * 8 + 4]);
@@ -625,6 +637,7 @@ rsp_status launch_fast_chain(const Plan &pl, const LaunchCtx &ctx, const FxArgs 
   FastArgs fa;
   fa.in = a.in; fa.out = a.out; fa.n_rows = a.n_rows; fa.row_base = a.row_base;
   fa.tw = reinterpret_cast<const int4 *>(a.tw2);
+  fa.win4 = a.win_on ? a.win4 : nullptr;
   for (int L = 0; L < 16; ++L) fa.tw_off[L] = a.tw_off[L];
   fa.W = a.W; fa.G = a.G; fa.scaler = a.scaler; fa.one = 1; fa.m1 = -1;
   fa.wmul = (int)(1u << (32 - a.sumw)); fa.div_sum = std::min(31, 32 - a.sumw + a.div_sum);

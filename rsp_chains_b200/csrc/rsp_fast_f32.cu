@@ -29,6 +29,7 @@ struct FastF32Args {
   float *out;              // thresholds (nullable)
   uint32_t *peak_mask;     // N/32 words per row (nullable)
   uint32_t n_rows, row_base;
+  const float *win;        // window coefficients or null (FFTParams.windowFunc, SDFFFT.scala:53-66,233-234)
   const float4 *tw;        // (c, s, -s, c), c + j s = exp(-2 pi j t / stageN); per stageN three runs [W^2k | W^k | W^3k]
   int tw_off[16];
   int W, G;
@@ -277,6 +278,11 @@ chain_f32_fast_kernel(const FastF32Args a) {
       const u64 *gin = a.in + (size_t)row * N + tl;
 #pragma unroll
       for (int rr = 0; rr < PTS; ++rr) pre[rr] = __ldg(&gin[rr * TPC]);
+      if (a.win != nullptr) {
+        const float *gw = a.win + tl;
+#pragma unroll
+        for (int rr = 0; rr < PTS; ++rr) { const float w = __ldg(&gw[rr * TPC]); pre[rr] = mul2(pre[rr], pk2(w, w)); }
+      }
     }
     f32_passes<S, 0>(a, tl, pre, xb, mg);
     // window sums without a row-wide prefix (which would lose the noise floor behind a strong target in fp32): bins are
@@ -367,7 +373,7 @@ static int f32_edge_iters(int S, int W, int G) { const int tpc = (1 << S) / 16; 
 bool fast_f32_chain_supported(const Plan &pl, const F32Args &a) {
   if (pl.first_stage != STAGE_FFT || pl.last_stage != STAGE_CFAR) return false;
   if (pl.S < RSP_FAST_SMIN || pl.S > RSP_FAST_SMAX) return false;
-  if (!a.bitrev || a.fft_dir != 1 || a.sel != 2 || a.win_on) return false;
+  if (!a.bitrev || a.fft_dir != 1 || a.sel != 2) return false;
   if (a.core != CORE_MEM || a.send_cut || a.peak_grouping) return false;
   if (a.G < 1 || a.W < 1 || a.div_sum < 0 || a.div_sum > 30) return false;
   if ((a.W & 15) || a.W > 128) return false;   // the block-of-16 window sums (see the kernel)
@@ -407,7 +413,7 @@ static rsp_status launch_f32_fast_modes(int cmode, bool linear, const LaunchCtx 
 rsp_status launch_fast_f32_chain(const Plan &pl, const LaunchCtx &ctx, const F32Args &a, const float4 *tw4, cudaStream_t st, const char **err) {
   FastF32Args fa;
   fa.in = reinterpret_cast<const u64 *>(a.in); fa.out = a.out; fa.peak_mask = a.peak_mask; fa.n_rows = a.n_rows; fa.row_base = a.row_base;
-  fa.tw = tw4;
+  fa.tw = tw4; fa.win = a.win_on ? a.win : nullptr;
   for (int L = 0; L < 16; ++L) fa.tw_off[L] = a.tw_off[L];
   fa.W = a.W; fa.G = a.G; fa.scaler = a.scaler; fa.inv_n = 1.0f / (float)(1 << pl.S);
   const int cmode = a.cfar_mode == 0 ? 0 : (a.cfar_mode == 1 ? 1 : 2);   // MuxLookup default: smallestOf (CFARCoreWithMem.scala:138-141)

@@ -41,6 +41,7 @@ struct Tables {
   std::vector<int32_t> log_tab;
   std::vector<int32_t> nco_tab;
   std::vector<int32_t> win;   // window ROM, protoWin raw values (empty: WindowFunctionTypes.None)
+  std::vector<int32_t> win4;  // win << (16 - (windowWidth - 2)) for the fast fixed kernels
   std::vector<float> winf;    // the same coefficients as floats (fp32 flavour: protoWin = DspReal)
   std::vector<double> win_user;   // WindowFunctionTypes.User coefficients (rsp_fft_window_user)
 };
@@ -241,7 +242,7 @@ inline void build_tables(const rsp_chain_params &p, Tables &t) {
 // fromDoubleWithFixedWidth into protoWin = FixedPoint(w, w - 2) (SDFFFTParams.scala:118)
 inline void build_window(const rsp_chain_params &p, Tables &t) {
   const rsp_fft_params &f = p.fft;
-  t.win.clear(); t.winf.clear();
+  t.win.clear(); t.winf.clear(); t.win4.clear();
   if (f.windowFunc == RSP_WINDOW_NONE) return;
   const int n = f.numPoints, wbp = f.windowWidth - 2;
   const double PI = 3.14159265358979323846;
@@ -256,6 +257,7 @@ inline void build_window(const rsp_chain_params &p, Tables &t) {
       default: v = (size_t)k < t.win_user.size() ? t.win_user[(size_t)k] : 1.0; break;
     }
     t.win.push_back((int32_t)wrap_host(from_double(v, wbp), f.windowWidth));
+    t.win4.push_back((int32_t)(t.win.back() * (1 << (16 - wbp))));
     t.winf.push_back((float)v);
   }
 }
@@ -348,7 +350,6 @@ inline rsp_status plan_fixed(const rsp_chain_params &p, const Regs &r, const Tab
   const bool common = f.dataWidth == 16 && f.trimType == RSP_TRIM_ROUND_HALF_UP && a.keep_mask == smask && a.fft_dir == 1 &&
                       p.mag.dataWidth == 16;
   pl.mode = MODE_GENERIC;
-  if (a.win_on) return RSP_OK;   // the window multiply lives in the generic kernels
   if (common && s1 <= 0) pl.mode = MODE_FAST;
   else if (common && s1 >= 1 && !f.use4Muls) pl.mode = MODE_FAST3;
   return RSP_OK;

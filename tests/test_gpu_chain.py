@@ -311,7 +311,7 @@ def test_window_functions(cuda, oracle):
         p.fftParams.windowFunc = win
         with R.FftMagCfarChainVanilla(p) as ch:
             configure(ch, 10, 2, regs)
-            assert ch.variant == "chain_fixed<10,generic>", ch.variant
+            assert ch.variant == "chain_fixed_fast<10>", ch.variant
         # the product applies the window itself: compare it on the raw beats with the oracle on the windowed beats
         with R.FftMagCfarChainVanilla(p) as ch:
             configure(ch, 10, 2, regs)
@@ -338,6 +338,21 @@ def test_window_functions(cuda, oracle):
     fft, mag, cfar = oracle_cfgs(oracle, p, 8, 2, regs8)
     want = oracle.chain_fixed_words(fft, mag, cfar, apply_window(oracle, p, np.ascontiguousarray(beats[:, :256])))
     assert (got == want).all()
+    # the generic kernels (binPoint 12 takes the 3-multiplier variant, Convergent the fully generic one) and N = 4096 in the fast one
+    for bp, trim, log_n in ((12, "RoundHalfUp", 10), (0, "Convergent", 9), (0, "RoundHalfUp", 12)):
+        nn = 1 << log_n
+        p = chain_params(nn, bp, trim=trim, W=16, G=4)
+        p.fftParams.windowFunc = WT.Hamming()
+        regs_n = dict(regs, fftWin=nn, thresholdScaler=3 << bp)
+        b = np.concatenate([synth.chirps_fixed(4, nn, seed=23), synth.random_beats(2, nn, seed=24)])
+        with R.FftMagCfarChainVanilla(p) as ch:
+            configure(ch, log_n, 2, regs_n)
+            d_out = cuda.empty((b.shape[0], nn), dtype=cuda.int32, device="cuda")
+            ch.run(to_dev(cuda, b), b.shape[0], 1, out=d_out)
+            cuda.cuda.synchronize()
+            got = from_dev_u32(d_out)
+        fft, mag, cfar = oracle_cfgs(oracle, p, log_n, 2, regs_n)
+        assert (got == oracle.chain_fixed_words(fft, mag, cfar, apply_window(oracle, p, b))).all(), (bp, trim, log_n)
     # IFFT: no window (SDFFFT.scala:236-245)
     p = chain_params(n, 0, W=16, G=4, fftDir=False)
     p.fftParams.windowFunc = WT.Hanning()

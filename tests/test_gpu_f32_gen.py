@@ -159,7 +159,7 @@ def test_fp32_window_functions(cuda, oracle):
         with R.FftMagCfarChainVanilla(p) as ch:
             configure(ch, log_n, 2, regs)
             ch.set_threshold_scaler_f32(3.0)
-            assert ch.variant == f"chain_f32<{log_n}>", ch.variant
+            assert ch.variant == f"chain_f32_fast<{log_n}>", ch.variant
             d_thr = cuda.empty((rows, n), dtype=cuda.float32, device="cuda")
             d_mask = cuda.zeros((rows, n // 32), dtype=cuda.int32, device="cuda")
             ch.run(cuda.from_numpy(x32).cuda(), rows, 1, out=d_thr, peak_mask=d_mask)
