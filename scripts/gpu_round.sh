@@ -1,12 +1,15 @@
 #!/bin/bash
-# one GPU visit: parity tests, smoke, bench, ncu launch list + full capture.  Outputs -> gpurun_out/
+# one GPU visit: parity tests, smoke, bench, reference arm, all-config sweep, per-config CPU baseline, ncu launch list + full capture.  Outputs -> gpurun_out/
 mkdir -p gpurun_out
 nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,memory.total --format=csv > gpurun_out/smi.txt 2>&1
-timeout 900 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?" | tee -a gpurun_out/pytest_gpu.log
+timeout 1200 python -m pytest tests -m gpu -x -q > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?" | tee -a gpurun_out/pytest_gpu.log
 timeout 300 python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/smoke.log 2>&1; echo "smoke rc=$?" | tee -a gpurun_out/smoke.log
 timeout 600 python bench.py > gpurun_out/bench.json 2> gpurun_out/bench.err; echo "bench rc=$?"
 cat gpurun_out/bench.json
 timeout 300 python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/bench_ref.json 2> gpurun_out/bench_ref.err; echo "ref rc=$?"
+timeout 900 python scripts/bench_configs.py > gpurun_out/configs.jsonl 2> gpurun_out/configs.err; echo "configs rc=$?"
+timeout 300 python scripts/cpu_configs.py > gpurun_out/cpu_configs.jsonl 2> gpurun_out/cpu_configs.err; echo "cpu configs rc=$?"
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/launches.csv python bench.py --steps 2 --warmup 3 --e2e-steps 1 --no-cpu-baseline > gpurun_out/ncu_list.log 2>&1; echo "ncu list rc=$?"
 timeout 900 ncu --set full --clock-control none --import-source on -k regex:chain_ -s 3 -c 1 -f -o gpurun_out/chain_full python bench.py --steps 2 --warmup 3 --e2e-steps 1 --no-cpu-baseline > gpurun_out/ncu_full.log 2>&1; echo "ncu full rc=$?"
-tail -n 5 gpurun_out/pytest_gpu.log gpurun_out/smoke.log
+ncu -i gpurun_out/chain_full.ncu-rep --page raw --csv > gpurun_out/chain_full_raw.csv 2>/dev/null
+tail -n 4 gpurun_out/pytest_gpu.log gpurun_out/smoke.log; cat gpurun_out/configs.jsonl gpurun_out/cpu_configs.jsonl
