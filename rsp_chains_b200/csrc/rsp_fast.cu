@@ -429,13 +429,14 @@ template <int S> struct GGeo {
   static constexpr int N = 1 << S;
   static constexpr int WM = 128;                                           // margin on both sides of the row (>= windowCells)
   static constexpr int XBG = (N + 2 * WM) + ((N + 2 * WM) >> 4) + 8;       // words: FFT exchange buffer, then the padded cell array
-  static constexpr int ROW = XBG + FGeo<S>::XM + N;                        // + int16 magnitudes + two int16 K arrays
+  static constexpr int KM = 128;                                           // int16 slots in front of each K array (window starts < 0)
+  static constexpr int ROW = XBG + FGeo<S>::XM + N + KM;                   // + int16 magnitudes + two int16 K arrays with their margins
   static_assert(XBG >= FGeo<S>::XB, "the exchange buffer fits");
 };
 
 // offset of cell (16 tl + o) in the padded array, relative to the thread's base X32 + 17 tl (one pad word per 16 cells:
 // lanes 16 cells apart are 17 words apart, conflict-free)
-__device__ __forceinline__ int gpad(int o) { return (o + 128) + ((o + 128) >> 4); }
+__host__ __device__ constexpr int gpad(int o) { return (o + 128) + ((o + 128) >> 4); }
 
 // The compiler turns `r += a >= b` into add + conditional move and merges the conditional stores into select chains (9
 // instructions per cell and step); written as predicated PTX it is compare + predicated add / store (6 per cell and step).
@@ -447,13 +448,13 @@ __device__ __forceinline__ void sts16_if_eq(int r, int k, uint32_t saddr, int v)
 }
 
 template <bool TWO>
-__device__ __forceinline__ void gos_step(int (&r)[8], const int (&xp)[8], int e_lo, int e_hi, int vL, int vR, int kl, int kr,
+__device__ __forceinline__ void gos_step(int (&r)[8], const int (&xp)[8], int i0, int e_lo, int e_hi, int vL, int vR, int kl, int kr,
                                          uint32_t kl_addr, uint32_t kr_addr) {
 #pragma unroll
   for (int e = 0; e < 8; ++e) {
     if (e < e_lo || e > e_hi) continue;
-    sts16_if_eq(r[e], kl, kl_addr, xp[e]);
-    if (TWO) sts16_if_eq(r[e], kr, kr_addr, xp[e]);
+    sts16_if_eq(r[e], kl, kl_addr, i0 + e);
+    if (TWO) sts16_if_eq(r[e], kr, kr_addr, i0 + e);
     inc_if_ge(r[e], vL, xp[e]);
     dec_if_gt(r[e], vR, xp[e]);
   }
@@ -491,7 +492,7 @@ __device__ __forceinline__ void gos_group(const int *xt, int tl, int o0, int W, 
     const int oa = o0 - s, aidx = a0 - s;
     const int vL = xt[gpad(oa - 1)], vR = xt[gpad(oa + W - 1)];
     const bool valid = (unsigned)aidx <= (unsigned)(N - W);
-    gos_step<TWO>(r, xp, e_lo, e_hi, vL, vR, valid ? kl1 : -1, valid ? kr1 : -1, kl_base + 2u * (uint32_t)(valid ? aidx : 0),
+    gos_step<TWO>(r, xp, a0, e_lo, e_hi, vL, vR, valid ? kl1 : -1, valid ? kr1 : -1, kl_base + 2u * (uint32_t)(valid ? aidx : 0),
                   kr_base + 2u * (uint32_t)(valid ? aidx : 0));
   };
 #pragma unroll
@@ -499,6 +500,113 @@ __device__ __forceinline__ void gos_group(const int *xt, int tl, int o0, int W, 
   for (int s = 0; s <= W - 8; ++s) diag(s, 0, 7);
 #pragma unroll
   for (int q = 1; q < 8; ++q) diag(W - 8 + q, 0, 7 - q);
+}
+
+// Packed form of the same rank counting, for rows whose cells all lie in 0 .. 32766 (every row that is not close to full scale;
+// the others take gos_group above).  Two neighbouring cells share a register, the cells negated, and
+//   [v > x]  = max(min(v - x, 1), 0)      [v >= x] = max(min(v + 1 - x, 1), 0)
+// are ONE VIADDMNMX.S16x2.RELU for both cells (no 16-bit overflow: v + 1 <= 32767, -x >= -32766); its third operand masks the
+// cells that have not started / are done (0x0001, 0x10000).  A half-register holds 8 * rank + e (e = 0 .. 7, the cell's place
+// in the group), the update 8 * ([vL >= x] - [vR > x]) is two IMADs with a run-time +-8 (FMA pipe, as in the butterflies).
+// "Some cell of mine has rank k" is then a minimum: min over the pairs of (half - 8 k) mod 2^16 is below 8 iff there is one,
+// and it is its e -- four VIADDMNMX.U16x2 (add + min in one), one more min across the halves, one LOP3 with predicate output
+// and ONE guarded 16-bit store of the cell's index per step (a predicated-off STS still costs its LSU slot on B200, measured
+// in scripts/ubench/pipes.cu: eight of them per step were the bound of an earlier version).  Windows that start in front of
+// the row land in the margin of the K arrays instead of being tested for.  Per step and 8 cells: 16 ALU-pipe + 11 FMA-pipe
+// instructions + 2 LDS + 1 STS, against 42 + 16 + 8 for the scalar form.
+__device__ __forceinline__ uint32_t gos_dup(int v, uint32_t add) { return (uint32_t)v * 0x10001u + add; }
+__device__ __forceinline__ void gos_acc(uint32_t &r, uint32_t d, int mul) { asm("mad.lo.s32 %0, %1, %2, %0;" : "+r"(r) : "r"(d), "r"(mul)); }
+// if ((key & 0xfff8) == 0) K[slot] = i0 + key   (low half of key: 8 * (rank - k) + e of the best cell)
+__device__ __forceinline__ void gos_store_if_match(uint32_t key, uint32_t saddr, int i0, int one) {
+  uint32_t idx = (uint32_t)i0;
+  gos_acc(idx, key, one);
+  asm volatile("{.reg .pred p, q; .reg .b32 d; setp.ne.u32 q, %0, %0; lop3.or.b32 d|p, %0, 0xfff8, 0, 0xc0, q; @!p st.shared.u16 [%1], %2;}"
+               :: "r"(key), "r"(saddr), "h"((short)idx) : "memory");
+}
+
+// 8 consecutive steps.  MODE 0: all 8 cells take part; 1: start-up, step u has the cells e >= 7 - u (u = 0 .. 6); 2: run-out,
+// step u has the cells e <= 7 - u.  pl / pr point at the word of step 0's entering / leaving cell, later steps go down by one
+// (the 8 cells of a chunk sit in one aligned group of 8, so there is no pad word between them); ka: K slot of step 0.
+template <bool TWO, int MODE>
+__device__ __forceinline__ void gos_chunk(uint32_t (&r)[4], const uint32_t (&nx)[4], const int *pl, const int *pr, uint32_t nkl, uint32_t nkr,
+                                          uint32_t kal, uint32_t kar, int i0, int one, int p8, int m8) {
+#pragma unroll
+  for (int u = 0; u < (MODE == 1 ? 7 : 8); ++u) {
+    const uint32_t vl1 = gos_dup(pl[-u], 0x10001u), vr = gos_dup(pr[-u], 0u);
+    uint32_t ml = 0xFFFFFFFFu, mr = 0xFFFFFFFFu;
+#pragma unroll
+    for (int p = 0; p < 4; ++p) {
+      const bool lo = MODE == 0 || (MODE == 1 ? 2 * p >= 7 - u : 2 * p <= 7 - u);
+      const bool hi = MODE == 0 || (MODE == 1 ? 2 * p + 1 >= 7 - u : 2 * p + 1 <= 7 - u);
+      if (!lo && !hi) continue;
+      const uint32_t live = r[p] | (lo ? 0u : 0xFFFFu) | (hi ? 0u : 0xFFFF0000u);   // a cell outside its windows never matches
+      ml = __viaddmin_u16x2(live, (lo ? nkl & 0xFFFFu : 0u) | (hi ? nkl & 0xFFFF0000u : 0u), ml);
+      if (TWO) mr = __viaddmin_u16x2(live, (lo ? nkr & 0xFFFFu : 0u) | (hi ? nkr & 0xFFFF0000u : 0u), mr);
+      const uint32_t ones = (lo ? 1u : 0u) | (hi ? 0x10000u : 0u);
+      gos_acc(r[p], __viaddmin_s16x2_relu(vl1, nx[p], ones), p8);
+      gos_acc(r[p], __viaddmin_s16x2_relu(vr, nx[p], ones), m8);
+    }
+    gos_store_if_match(__vminu2(ml, ml >> 16), kal - 2u * u, i0, one);
+    if (TWO) gos_store_if_match(__vminu2(mr, mr >> 16), kar - 2u * u, i0, one);
+  }
+}
+
+template <int S, bool TWO, int O0>
+__device__ __forceinline__ void gos_group_packed(const int *xt, int tl, int W, int kl1, int kr1, short *KL, short *KR, int one, int m1) {
+  constexpr int B0 = gpad(O0);
+  const int p8 = one * 8, m8 = m1 * 8;
+  uint32_t nx[4], r[4];
+#pragma unroll
+  for (int p = 0; p < 4; ++p) {
+    nx[p] = __byte_perm((uint32_t)(-xt[B0 + 2 * p]), (uint32_t)(-xt[B0 + 2 * p + 1]), 0x5410);
+    r[p] = (uint32_t)(2 * p) | ((uint32_t)(2 * p + 1) << 16);
+  }
+  // cells after i_e inside its first window [i_e, i_e + W - 1] that beat it
+#pragma unroll
+  for (int d = 1; d < 8; ++d) {
+    const uint32_t v = gos_dup(xt[B0 + d], 0u);
+#pragma unroll
+    for (int p = 0; p < 4; ++p) {
+      const uint32_t ones = (2 * p < d ? 1u : 0u) | (2 * p + 1 < d ? 0x10000u : 0u);
+      if (ones) gos_acc(r[p], __viaddmin_s16x2_relu(v, nx[p], ones), p8);
+    }
+  }
+  for (int j = 1; j < (W >> 3); ++j) {
+    const int idx = O0 + 128 + 8 * j;
+    const int *pv = xt + idx + (idx >> 4);
+#pragma unroll
+    for (int u = 0; u < 8; ++u) {
+      const uint32_t v = gos_dup(pv[u], 0u);
+#pragma unroll
+      for (int p = 0; p < 4; ++p) gos_acc(r[p], __viaddmin_s16x2_relu(v, nx[p], 0x10001u), p8);
+    }
+  }
+  {
+    const int *pv = xt + gpad(O0 + W);
+#pragma unroll
+    for (int q = 0; q < 7; ++q) {
+      const uint32_t v = gos_dup(pv[q], 0u);
+#pragma unroll
+      for (int p = 0; p < 4; ++p) {
+        const uint32_t ones = (2 * p > q ? 1u : 0u) | (2 * p + 1 > q ? 0x10000u : 0u);
+        if (ones) gos_acc(r[p], __viaddmin_s16x2_relu(v, nx[p], ones), p8);
+      }
+    }
+  }
+  // step s looks at the window that starts at a0 - s: s = -7 .. -1 start-up, 0 .. W - 9 all cells, W - 8 .. W - 1 run-out
+  const int a0 = 16 * tl + O0;
+  const uint32_t nkl = ((uint32_t)(-8 * kl1) & 0xFFFFu) * 0x10001u, nkr = ((uint32_t)(-8 * kr1) & 0xFFFFu) * 0x10001u;   // -8 k in both halves
+  const uint32_t kl0 = (uint32_t)__cvta_generic_to_shared(KL) + 2u * (uint32_t)a0, kr0 = (uint32_t)__cvta_generic_to_shared(KR) + 2u * (uint32_t)a0;
+  gos_chunk<TWO, 1>(r, nx, xt + B0 + 6, xt + gpad(O0 + W) + 6, nkl, nkr, kl0 + 14u, kr0 + 14u, a0, one, p8, m8);
+  for (int j = 0; j < (W >> 3) - 1; ++j) {
+    const int il = O0 + 128 - 8 - 8 * j, ir = il + W;
+    gos_chunk<TWO, 0>(r, nx, xt + il + (il >> 4) + 7, xt + ir + (ir >> 4) + 7, nkl, nkr, kl0 - 16u * (uint32_t)j, kr0 - 16u * (uint32_t)j, a0, one, p8, m8);
+  }
+  {
+    const int il = O0 + 128 - W;
+    const uint32_t ko = 2u * (uint32_t)(W - 8);
+    gos_chunk<TWO, 2>(r, nx, xt + il + (il >> 4) + 7, xt + B0 + 7, nkl, nkr, kl0 - ko, kr0 - ko, a0, one, p8, m8);
+  }
 }
 
 template <int S>
@@ -513,7 +621,7 @@ __global__ void __launch_bounds__(FGeo<S>::THREADS, 1024 / FGeo<S>::THREADS) cha
   const int c = threadIdx.x / TPC, tl = threadIdx.x % TPC;
   uint32_t *xb = smem + (size_t)c * Gg::ROW, *xm = xb + Gg::XBG;
   const short *X = reinterpret_cast<const short *>(xm);
-  short *KL = reinterpret_cast<short *>(xm + Gm::XM), *KR = ga.kl1 == ga.kr1 ? KL : KL + N;
+  short *KL = reinterpret_cast<short *>(xm + Gm::XM) + Gg::KM, *KR = ga.kl1 == ga.kr1 ? KL : KL + N + Gg::KM;
   int *xt = reinterpret_cast<int *>(xb) + 17 * tl;
   const uint32_t stride = gridDim.x * CPC;
   for (uint32_t row0 = blockIdx.x * CPC; row0 < a.n_rows; row0 += stride) {
@@ -522,16 +630,26 @@ __global__ void __launch_bounds__(FGeo<S>::THREADS, 1024 / FGeo<S>::THREADS) cha
     uint32_t pre[PTS];
     load_beats<S>(a, row, tl, pre);
     fast_passes<S, 0>(a, c, tl, pre, xb, xm, loud);
+    uint32_t wide = 0;
     {   // the thread's 16 cells as 32-bit words in the padded array (the exchange buffer is dead)
       const uint4 v0 = *reinterpret_cast<const uint4 *>(&xm[tl * 8]), v1 = *reinterpret_cast<const uint4 *>(&xm[tl * 8 + 4]);
       const uint32_t wd[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
 #pragma unroll
       for (int k = 0; k < 8; ++k) { xt[gpad(2 * k)] = sext16((int)wd[k]); xt[gpad(2 * k + 1)] = hi16s(wd[k]); }
+#pragma unroll
+      for (int k = 0; k < 8; ++k) wide |= (wd[k] + 0x00010001u) | wd[k];   // bit 15 of a half: the cell is negative or 32767
     }
-    chirp_sync<S>(c);
-    for (int h = 0; h < 2; ++h) {
-      if (ga.kl1 == ga.kr1) gos_group<S, false>(xt, tl, 8 * h, a.W, ga.kl1, ga.kr1, KL, KR);
-      else gos_group<S, true>(xt, tl, 8 * h, a.W, ga.kl1, ga.kr1, KL, KR);
+    if (__syncthreads_or((int)(wide & 0x80008000u))) {   // some cell of the CTA's rows is outside 0 .. 32766: scalar ranks
+      for (int h = 0; h < 2; ++h) {
+        if (ga.kl1 == ga.kr1) gos_group<S, false>(xt, tl, 8 * h, a.W, ga.kl1, ga.kr1, KL, KR);
+        else gos_group<S, true>(xt, tl, 8 * h, a.W, ga.kl1, ga.kr1, KL, KR);
+      }
+    } else if (ga.kl1 == ga.kr1) {
+      gos_group_packed<S, false, 0>(xt, tl, a.W, ga.kl1, ga.kr1, KL, KR, a.one, a.m1);
+      gos_group_packed<S, false, 8>(xt, tl, a.W, ga.kl1, ga.kr1, KL, KR, a.one, a.m1);
+    } else {
+      gos_group_packed<S, true, 0>(xt, tl, a.W, ga.kl1, ga.kr1, KL, KR, a.one, a.m1);
+      gos_group_packed<S, true, 8>(xt, tl, a.W, ga.kl1, ga.kr1, KL, KR, a.one, a.m1);
     }
     chirp_sync<S>(c);
     uint32_t *gout = a.out + (size_t)row * N;
@@ -539,7 +657,7 @@ __global__ void __launch_bounds__(FGeo<S>::THREADS, 1024 / FGeo<S>::THREADS) cha
     for (int j = 0; j < PTS; ++j) {
       const int n = tl + j * TPC, W = a.W, G = a.G;
       const bool both = (n + G + W <= N - 1) && (n - G - W >= 0);
-      const int L = KL[min(n + G + 1, N - W)], R = KR[max(n - G - W, 0)];
+      const int L = X[KL[min(n + G + 1, N - W)]], R = X[KR[max(n - G - W, 0)]];   // the K arrays hold the cell's index
       int t = ga.cmode == 0 ? ((R + L) >> 1) : (ga.cmode == 1 ? max(L, R) : min(L, R));
       t = both ? t : 0;                                                  // CFARCoreWithLis.scala:172-173
       const int thr = ga.linear ? t * a.scaler : t + a.scaler;

@@ -20,6 +20,9 @@ elif key == "c5":
 elif key == "c4os":
     os_regs = dict(fftWin=4096, thresholdScaler=2, logOrLinearMode=1, peakGrouping=0, cfarMode=0, windowCells=64, guardCells=4, indexLagg=48, indexLead=48)
     B.run_case("C4 GOS", B.fixed_params(4096, 64, 4, GOSCFARType), 12, os_regs, 1024, 1)
+elif key == "c4os16":
+    os_regs = dict(fftWin=4096, thresholdScaler=2, logOrLinearMode=1, peakGrouping=0, cfarMode=0, windowCells=64, guardCells=4, indexLagg=48, indexLead=48)
+    B.run_case("C4 x 16 GOS", B.fixed_params(4096, 64, 4, GOSCFARType), 12, os_regs, 16384, 1)
 elif key.startswith("fx"):      # fxS: fixed CA chain at N = 2^S, 512 MiB footprint
     S = int(key[2:]); n = 1 << S
     B.run_case(f"fixed CA N={n}", B.fixed_params(n, 64, 8), S, ca(n, 64, 8, 6), (1 << 26) // n, 1)

@@ -31,6 +31,14 @@ __global__ void __launch_bounds__(512) k(int *out, int seed, int mul, int sh) {
 #define LDS16_(i) asm volatile("ld.shared.s16 %0, [%1+" #i "*128];" : "=r"(v[i]) : "r"(sa));
 #define STS_(i) asm volatile("st.shared.b32 [%1+" #i "*128], %0;" :: "r"(v[i]), "r"(sa));
 #define STS16_(i) asm volatile("st.shared.b16 [%1+" #i "*128], %0;" :: "h"((short)v[i]), "r"(sa));
+#define VAMR_(i) v[i] = __viaddmin_s16x2_relu((unsigned)v[i], (unsigned)w[i], 0x00010001u);
+#define VMX2_(i) v[i] = __vmaxs2((unsigned)v[i], (unsigned)w[i]);
+#define LOPP_(i) asm volatile("{.reg .pred p, q; .reg .b32 d; setp.ne.u32 q, %0, %0; lop3.or.b32 d|p, %0, %1, 0xffff, 0x28, q; @!p st.shared.u16 [%2+" #i "*128], %3;}" :: "r"(v[i]), "r"(w[i]), "r"(sa), "h"((short)mul) : "memory");
+    if (KIND == 19) { REP8(VAMR_) }
+    if (KIND == 20) { REP8(VMX2_) }
+    if (KIND == 21) { REP8(VAMR_) REP8(IMAD_) }
+    if (KIND == 22) { REP8(LOPP_) REP8(IMAD_) }                                   // test + (almost never taken) predicated store, + mad
+    if (KIND == 23) { REP8(LOPP_) REP8(VAMR_) REP8(IMAD_) REP8(VAMR_) REP8(IMAD_) } // the packed OS-CFAR step: 2 alu + 2 alu... per pair
     if (KIND == 0) { REP8(IADD3_) }
     if (KIND == 1) { REP8(IMAD_) }
     if (KIND == 2) { REP8(IMADHI_) }
@@ -96,5 +104,10 @@ int main() {
   run<14>("st.shared.b16", 8, d, s, clk);
   run<15>("lds + add + mad + shr + mad (1:2:2)", 40, d, s, clk);
   run<18>("lds sts + 3 alu + 3 fma (2:3:3)", 64, d, s, clk);
+  run<19>("viaddmin.s16x2.relu (VIADDMNMX.S16x2.RELU)", 8, d, s, clk);
+  run<20>("vimax.s16x2 (VIMNMX.S16x2)", 8, d, s, clk);
+  run<21>("viaddmin.s16x2.relu + mad.lo 1:1", 16, d, s, clk);
+  run<22>("lop3 -> pred + @p sts.u16, + mad.lo", 24, d, s, clk);
+  run<23>("lop3/sts + 2 x (viaddmnmx + mad)", 48, d, s, clk);
   return 0;
 }

@@ -249,7 +249,7 @@ def test_c5_full_size_rows_are_independent(cuda, oracle):
 
 
 @pytest.mark.parametrize("log_n,W,G,kl,kr", [(10, 16, 2, 12, 12), (10, 64, 4, 48, 48), (11, 32, 0, 24, 7), (12, 64, 4, 48, 20), (13, 8, 1, 1, 8),
-                                              (14, 128, 8, 96, 96)])
+                                              (14, 128, 8, 96, 96), (11, 24, 2, 20, 20), (12, 40, 3, 1, 40), (10, 72, 1, 72, 1)])
 def test_fast_gos_kernel_variants(cuda, oracle, log_n, W, G, kl, kr):
     """chain_fixed_fast_gos<S> (rank-counting OS-CFAR): CA/GO/SO combination of the two order statistics, linear and log threshold,
     equal and different indexLagg / indexLead, ragged row counts, full-range random rows (ties, negative magnitudes)"""
@@ -257,7 +257,12 @@ def test_fast_gos_kernel_variants(cuda, oracle, log_n, W, G, kl, kr):
     rows = 19 if log_n <= 12 else 5
     beats = np.concatenate([synth.chirps_fixed(rows - 3, n, seed=log_n), synth.random_beats(3, n, seed=200 + log_n)])
     beats[-1, n // 2:] = beats[-1, 7]          # long runs of equal cells
-    p = chain_params(n, 0, cfar_type=GOSCFARType, W=max(W, 16), G=max(G, 1))
+    # the packed rank counting takes rows whose cells all lie in 0 .. 32766, the scalar one the others: a row at each side of the limit
+    # (DC rows: bin 0 = the beat itself, JPL magnitude 32766 / 32767 / wrapped negative), and a loud row next to a quiet one
+    def const_row(re, im): return np.full(n, ((re & 0xFFFF) << 16) | (im & 0xFFFF), dtype=np.uint32)
+    beats = np.concatenate([beats, np.stack([const_row(32766, 0), const_row(32767, 0), const_row(32767, 32767), const_row(0, -32768)]),
+                            synth.chirps_fixed(2, n, seed=300 + log_n)])
+    p = chain_params(n, 0, cfar_type=GOSCFARType, W=max(1 << (W - 1).bit_length(), 16), G=max(G, 1))
     for mode, lin, scaler in ((0, 1, 2), (1, 1, 3), (2, 0, 500), (3, 1, -2)):
         regs = dict(fftWin=n, thresholdScaler=scaler & 0xFFFF, logOrLinearMode=lin, peakGrouping=0, cfarMode=mode, windowCells=W, guardCells=G,
                     indexLagg=kl, indexLead=kr)
