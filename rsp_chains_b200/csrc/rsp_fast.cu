@@ -41,6 +41,22 @@ struct FastArgs {
   uint32_t det_cap;
 };
 
+// Exchange-buffer index of point p.  The pads are chosen per size by the shared-memory model in tests/test_kernel_layout.py so
+// that every pass of the size's decomposition (strided 32-bit stores / loads, 128-bit loads of 4 consecutive points in the
+// last pass) is free of bank conflicts (N = 8192: 1.17 wavefronts per access, the best an additive pad reaches).  All pads are
+// multiples of 4 words from bit 5 up, so groups of 4 points stay contiguous and 16-byte aligned, and the index is additive over
+// the disjoint bit fields it is used with (thread base | point in the group | group).
+template <int S> __host__ __device__ constexpr int fidx(int p) {
+  return S == 11 ? p + ((p >> 5) << 2) + ((p >> 8) << 3)
+       : S == 12 ? p + ((p >> 5) << 2) + ((p >> 7) << 3)
+       : S == 13 ? p + ((p >> 5) << 3)
+                 : p + ((p >> 6) << 2);
+}
+// Index (in 16-bit units) of bin n in the magnitude array: 8 bins of padding per 64 (and per 1024 at N = 16384) spread the
+// bit-reversed scatter of the last pass over the banks (N = 16384: 24 instead of 144 wavefronts per warp and row) and keep a
+// thread's 16 consecutive bins contiguous and 16-byte aligned; additive over tl + j * TPC.
+template <int S> __host__ __device__ constexpr int mhx(int n) { return n + ((n >> 6) << 3) + (S == 14 ? ((n >> 10) << 3) : 0); }
+
 template <int S> struct FGeo {
   static constexpr int N = 1 << S;
   static constexpr int PTS = 16;
@@ -50,13 +66,12 @@ template <int S> struct FGeo {
 #endif
   static constexpr int CPC = TPC >= RSP_FAST_CTA ? 1 : RSP_FAST_CTA / TPC;     // chirps per CTA
   static constexpr int THREADS = TPC * CPC;
-  static constexpr int XB = N + 4 * (N >> 6);                // words of the exchange buffer: index f(p) = p + 4 * (p >> 6)
-  static constexpr int XM = N / 2;                           // words of the magnitude array (int16 per bin)
+  static constexpr int XB = (fidx<S>(N - 1) + 4) & ~3;        // words of the exchange buffer (also holds the N + 1 prefix sums)
+  static constexpr int XM = (mhx<S>(N - 1) / 2 + 4) & ~3;     // words of the magnitude array (int16 per bin, padded)
   static constexpr int ROW = XB + XM;                        // words per chirp
   static constexpr int NW = TPC / 32;                        // warps per chirp
 };
 
-__device__ __forceinline__ int fidx(int p) { return p + ((p >> 6) << 2); }
 // Sign extensions and shifts go through inline PTX on purpose: when the compiler can prove a value fits 16 bits it rewrites the
 // rounded average (a + c + 1) >> 1 into the overflow-free (a | c) - ((a ^ c) >> 1) form and narrows the arithmetic, which
 // costs about twice the instructions of the plain 32-bit IADD3 + SHF.
@@ -119,22 +134,27 @@ __device__ __forceinline__ void fast_pass(const FastArgs &a, int tl, const uint3
   constexpr bool first = (K == 0), last = (K == fx_n_passes(S) - 1);
   static_assert((i0 & 1) == 0, "passes start on even stages");
   int mags[last ? PTS : 1];
+  // exchange-buffer address of point (g, rr) = xf[fidx(g * TPC * R) + fidx(rr * Dl)]: one run-time base per pass, the rest
+  // folds into the instruction's immediate (fidx is additive over these disjoint bit fields)
+  const int low0 = tl & (Dl - 1);
+  uint32_t *xf = xb + fidx<S>(((tl >> LDl) << (m + LDl)) | low0);
 #pragma unroll
   for (int g = 0; g < G; ++g) {
-    const int vt = g * TPC + tl;
-    const int low = vt & (Dl - 1), high = vt >> LDl;
-    const int base = (high << (m + LDl)) | low;
+    const int low = low0;   // (g * TPC + tl) & (Dl - 1): Dl divides TPC
+    const int go = fidx<S>(g * TPC * R);
     int re[R], im[R];
-    if (last && m == 2) {   // 4 consecutive points: one 128-bit load
-      const uint4 v = *reinterpret_cast<const uint4 *>(&xb[fidx(base)]);
-      const uint32_t wd[4] = {v.x, v.y, v.z, v.w};
+    if (last && !first) {   // R consecutive points: 128-bit loads
 #pragma unroll
-      for (int rr = 0; rr < R; ++rr) { re[rr] = hi16s(wd[rr & 3]); im[rr] = sext16((int)wd[rr & 3]); }
+      for (int q = 0; q < R / 4; ++q) {
+        const uint4 v = *reinterpret_cast<const uint4 *>(&xf[go + fidx<S>(4 * q)]);
+        const uint32_t wd[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (int k = 0; k < 4; ++k) { re[4 * q + k] = hi16s(wd[k]); im[4 * q + k] = sext16((int)wd[k]); }
+      }
     } else {
 #pragma unroll
       for (int rr = 0; rr < R; ++rr) {
-        const int p = base + rr * Dl;
-        const uint32_t wd = first ? pre[rr] : xb[fidx(p)];   // first pass: m = 4, one group, p = tl + rr * TPC
+        const uint32_t wd = first ? pre[rr] : xf[go + fidx<S>(rr * Dl)];   // first pass: m = 4, one group, p = tl + rr * TPC
         re[rr] = hi16s(wd); im[rr] = sext16((int)wd);
       }
     }
@@ -179,7 +199,7 @@ __device__ __forceinline__ void fast_pass(const FastArgs &a, int tl, const uint3
     }
     if (!last) {
 #pragma unroll
-      for (int rr = 0; rr < R; ++rr) xb[fidx(base + rr * Dl)] = pack2(re[rr], im[rr]);
+      for (int rr = 0; rr < R; ++rr) xf[go + fidx<S>(rr * Dl)] = pack2(re[rr], im[rr]);
     } else {
 #pragma unroll
       for (int rr = 0; rr < R; ++rr) mags[g * R + rr] = fjpl(re[rr], im[rr]);
@@ -189,11 +209,11 @@ __device__ __forceinline__ void fast_pass(const FastArgs &a, int tl, const uint3
     // bin of point p = (vt << m) + rr is bitrev_S(p) = rev_m(rr) << (S - m) | rev_{S-4}(tl) << (4 - m) | rev_{4-m}(g):
     // for a fixed rr the G groups of the thread are G consecutive bins -> one G * 16-bit store per rr
     const uint32_t rtl = (__brev((uint32_t)tl) >> (32 - (S - 4))) << (4 - m);
-    uint16_t *xm16 = reinterpret_cast<uint16_t *>(xm);
+    uint16_t *xm16 = reinterpret_cast<uint16_t *>(xm) + mhx<S>((int)rtl);
 #pragma unroll
     for (int rr = 0; rr < R; ++rr) {
       const uint32_t rrr = (__brev((uint32_t)rr) >> (32 - m)) << (S - m);   // compile-time
-      const uint32_t bin0 = rrr | rtl;
+      const int bin0 = mhx<S>((int)rrr);                                     // mhx is additive over rrr | rtl
       if (G == 4) {   // groups in bin order: rev2(g) = 0,1,2,3 <- g = 0,2,1,3
         uint2 v;
         v.x = __byte_perm((uint32_t)mags[0 * R + rr], (uint32_t)mags[2 * R + rr], 0x5410);
@@ -319,7 +339,7 @@ __device__ __forceinline__ int fast_cfar_bin(const FastArgs &a, int j, int tl, i
   int t = CMODE == 0 ? sar(fadd(1, R, 1, L, a.one, a.m1), 1) : (CMODE == 1 ? max(L, R) : min(L, R));
   if (EDGE) t = lead_full ? (lagg_full ? t : R) : L;
   const int thr = LINEAR ? t * a.scaler : fadd(1, t, 1, a.scaler, a.one, a.m1);
-  const int cut = X[n];
+  const int cut = X[mhx<S>(j * TPC)];   // X points at the thread's first bin (mhx is additive over tl + j * TPC)
   // peak = cut > thr as the sign bit of thr - cut (|thr| < 2^31 - 2^16 is checked by the host)
   const int pk = (int)((uint32_t)fadd(1, thr, -1, cut, a.one, a.m1) >> 31);
   const int w0 = (int)(((uint32_t)thr & a.thr_mask) * (uint32_t)a.out_mul + (uint32_t)n2);   // threshold field | bin field (n << 1)
@@ -343,7 +363,7 @@ __device__ __noinline__ void fast_detections(const FastDetArgs a, int tl, uint32
     const int thr = LINEAR ? t * a.scaler : t + a.scaler;
     const uint32_t slot = atomicAdd(a.det_count, 1u);
     if (slot < a.det_cap) {
-      Detection d; d.chirp = a.chirp; d.bin = (uint32_t)n; d.threshold = (int)((uint32_t)thr << a.thr_sext) >> a.thr_sext; d.cut = X[n];
+      Detection d; d.chirp = a.chirp; d.bin = (uint32_t)n; d.threshold = (int)((uint32_t)thr << a.thr_sext) >> a.thr_sext; d.cut = X[mhx<S>(n)];
       a.det_list[slot] = d;
     }
   }
@@ -362,7 +382,7 @@ __global__ void __launch_bounds__(FGeo<S>::THREADS, 1024 / FGeo<S>::THREADS) cha
   const int c = threadIdx.x / TPC, tl = threadIdx.x % TPC;
   uint32_t *xb = smem + (size_t)c * Gm::ROW, *xm = xb + Gm::XB;
   int *P = reinterpret_cast<int *>(xb);
-  const short *X = reinterpret_cast<const short *>(xm);
+  const short *X = reinterpret_cast<const short *>(xm), *Xt = X + mhx<S>(tl);
   const int *pA = P + tl + a.G + a.W + 1, *pB = P + tl + a.G + 1, *pC = P + tl - a.G, *pD = P + tl - a.G - a.W;
   const uint32_t stride = gridDim.x * CPC;
   // the loop bound is the same for every thread of the CTA (the barriers are CTA-wide); a chirp slot past the last row
@@ -376,7 +396,8 @@ __global__ void __launch_bounds__(FGeo<S>::THREADS, 1024 / FGeo<S>::THREADS) cha
     // prefix sums of the thread's 16 consecutive magnitudes
     int x[PTS];
     {
-      const uint4 v0 = *reinterpret_cast<const uint4 *>(&xm[tl * 8]), v1 = *reinterpret_cast<const uint4 *>(&xm[tl * 8 + 4]);
+      const uint32_t *xq = xm + mhx<S>(16 * tl) / 2;   // the thread's 16 consecutive bins
+      const uint4 v0 = *reinterpret_cast<const uint4 *>(xq), v1 = *reinterpret_cast<const uint4 *>(xq + 4);
       const uint32_t wd[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
 #pragma unroll
       for (int k = 0; k < 8; ++k) { x[2 * k] = sext16((int)wd[k]); x[2 * k + 1] = hi16s(wd[k]); }
@@ -400,8 +421,8 @@ __global__ void __launch_bounds__(FGeo<S>::THREADS, 1024 / FGeo<S>::THREADS) cha
 #pragma unroll
     for (int j = 0; j < PTS; ++j) {
       int pk;
-      if (j < EJ || j >= PTS - EJ) pk = fast_cfar_bin<S, CMODE, LINEAR, true>(a, j, tl, n2, P, pA, pB, pC, pD, X, gout);
-      else pk = fast_cfar_bin<S, CMODE, LINEAR, false>(a, j, tl, n2, P, pA, pB, pC, pD, X, gout);
+      if (j < EJ || j >= PTS - EJ) pk = fast_cfar_bin<S, CMODE, LINEAR, true>(a, j, tl, n2, P, pA, pB, pC, pD, Xt, gout);
+      else pk = fast_cfar_bin<S, CMODE, LINEAR, false>(a, j, tl, n2, P, pA, pB, pC, pD, Xt, gout);
       mask = mask * 2 + pk;
       n2 += 2 * TPC;
     }
@@ -428,10 +449,10 @@ struct GosArgs { int cmode, linear, kl1, kr1; };   // kl1 = indexLagg - 1, kr1 =
 template <int S> struct GGeo {
   static constexpr int N = 1 << S;
   static constexpr int WM = 128;                                           // margin on both sides of the row (>= windowCells)
-  static constexpr int XBG = (N + 2 * WM) + ((N + 2 * WM) >> 4) + 8;       // words: FFT exchange buffer, then the padded cell array
+  static constexpr int XCELLS = (N + 2 * WM) + ((N + 2 * WM) >> 4) + 8;    // words of the padded cell array ...
+  static constexpr int XBG = XCELLS > FGeo<S>::XB ? XCELLS : FGeo<S>::XB;  // ... which takes the place of the FFT exchange buffer
   static constexpr int KM = 128;                                           // int16 slots in front of each K array (window starts < 0)
   static constexpr int ROW = XBG + FGeo<S>::XM + N + KM;                   // + int16 magnitudes + two int16 K arrays with their margins
-  static_assert(XBG >= FGeo<S>::XB, "the exchange buffer fits");
 };
 
 // offset of cell (16 tl + o) in the padded array, relative to the thread's base X32 + 17 tl (one pad word per 16 cells:
@@ -632,7 +653,8 @@ __global__ void __launch_bounds__(FGeo<S>::THREADS, 1024 / FGeo<S>::THREADS) cha
     fast_passes<S, 0>(a, c, tl, pre, xb, xm, loud);
     uint32_t wide = 0;
     {   // the thread's 16 cells as 32-bit words in the padded array (the exchange buffer is dead)
-      const uint4 v0 = *reinterpret_cast<const uint4 *>(&xm[tl * 8]), v1 = *reinterpret_cast<const uint4 *>(&xm[tl * 8 + 4]);
+      const uint32_t *xq = xm + mhx<S>(16 * tl) / 2;   // the thread's 16 consecutive bins
+      const uint4 v0 = *reinterpret_cast<const uint4 *>(xq), v1 = *reinterpret_cast<const uint4 *>(xq + 4);
       const uint32_t wd[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
 #pragma unroll
       for (int k = 0; k < 8; ++k) { xt[gpad(2 * k)] = sext16((int)wd[k]); xt[gpad(2 * k + 1)] = hi16s(wd[k]); }
@@ -657,11 +679,11 @@ __global__ void __launch_bounds__(FGeo<S>::THREADS, 1024 / FGeo<S>::THREADS) cha
     for (int j = 0; j < PTS; ++j) {
       const int n = tl + j * TPC, W = a.W, G = a.G;
       const bool both = (n + G + W <= N - 1) && (n - G - W >= 0);
-      const int L = X[KL[min(n + G + 1, N - W)]], R = X[KR[max(n - G - W, 0)]];   // the K arrays hold the cell's index
+      const int L = X[mhx<S>(KL[min(n + G + 1, N - W)])], R = X[mhx<S>(KR[max(n - G - W, 0)])];   // the K arrays hold the cell's index
       int t = ga.cmode == 0 ? ((R + L) >> 1) : (ga.cmode == 1 ? max(L, R) : min(L, R));
       t = both ? t : 0;                                                  // CFARCoreWithLis.scala:172-173
       const int thr = ga.linear ? t * a.scaler : t + a.scaler;
-      const int cut = X[n];
+      const int cut = X[mhx<S>(n)];
       const int pk = cut > thr ? 1 : 0;
       gout[n] = ((uint32_t)thr & a.thr_mask) * (uint32_t)a.out_mul + (uint32_t)(n << 1) + (uint32_t)pk;
       if (pk && a.det_list != nullptr && active) {
