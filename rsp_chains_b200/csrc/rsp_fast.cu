@@ -27,12 +27,13 @@ struct FastArgs {
   uint32_t *out;
   uint32_t n_rows, row_base;
   const int32_t *win4;   // window ROM << (16 - binary point) or null (FFTParams.windowFunc, SDFFFT.scala:53-66,233-234)
-  const int4 *tw;        // (c, s, -c, -s) with c = cos << 2, s = -sin(2 pi t / stageN) << 2; per stageN three runs [W^2k | W^k | W^3k]
+  const int2 *tw;        // (c, s) with c = cos << 2, s = -sin(2 pi t / stageN) << 2; per stageN three runs [W^2k | W^k | W^3k]
   int tw_off[16];
   int W, G, div_sum, scaler;   // div_sum here = (32 - sumw) + divSum: shift applied to the pre-scaled window sums (see wmul)
   int wmul;              // 1 << (32 - sumw): the prefix sums are kept times wmul, so that differences wrap exactly like the
                          // reference's sumw-bit sum registers (CFARCoreWithMem.scala:34,108,123) in plain 32-bit arithmetic
   int one, m1;           // +1 and -1 as run-time values: multipliers of the IMADs that do the adds on the FMA pipe (see fadd)
+  int rnd[4];            // 0x8000, -0x8000, 0x7FFF, -0x7FFF: rounding addends of the twiddle products (see fcmul)
   uint32_t thr_mask;     // (1 << thresholdWidth) - 1
   int out_mul;           // 1 << (log2(fftSize) + 1): position of the threshold field in the output beat
   int thr_sext;          // 32 - thresholdWidth: sign extension of the threshold reported in a detection
@@ -106,12 +107,33 @@ __device__ __forceinline__ void fbf1(int sa, int &A, int sc, int &C, bool negd, 
   C = wrap ? sext16(d) : d;
 }
 
-// x <- x * W for a point held with sign sg (both components), W = (c, s, -c, -s) as stored (<< 2): the result (sign +1) is
-// rounded half up at bit 14 and wrapped to 16 bits by taking bits 16..31 of the 32-bit wrap-around sum
-__device__ __forceinline__ void fcmul(int sg, int &xr, int &xi, const int4 w) {
-  const int c = sg > 0 ? w.x : w.z, s = sg > 0 ? w.y : w.w, ns = sg > 0 ? w.w : w.y;
-  const int r = xr * c + xi * ns + 0x8000;
-  const int i = xr * s + xi * c + 0x8000;
+// x <- x * W for a point held with sign sg (both components), W = (c, s) as stored (<< 2): 8 bytes per twiddle -- the twiddle
+// loads are a third (N = 1024) to a half (N = 16384) of the L1 traffic of the kernel.  The product is rounded half up at bit 14
+// and wrapped to 16 bits by taking bits 16..31 of the 32-bit wrap-around sum; the subtractions are IMADs with a negated addend.
+//   sg > 0:              re = (xr c - (xi s - R)) >> 16,  im = (xr s + (xi c + R)) >> 16,  R = 0x8000
+//   sg < 0, TRUE_OUT:    re = (xi s - (xr c - R)) >> 16,  im = (-(xr s + (xi c - R))) >> 16   (one more IMAD for the negation)
+//   sg < 0, !TRUE_OUT:   the result stays negated, -floor((P + R) / 2^16) = floor((-P + R - 1) / 2^16): the sg > 0 formulas
+//                        with R - 1.  Only where nothing can wrap (quiet rows: -(-32768) has no 16-bit form) and the sign
+//                        can be carried on (not at the end of a pass: the exchange buffer holds true values).
+__device__ __forceinline__ int imad(int x, int y, int z) { int r; asm("mad.lo.s32 %0, %1, %2, %3;" : "=r"(r) : "r"(x), "r"(y), "r"(z)); return r; }
+__device__ __forceinline__ int imad_sub(int x, int y, int z) {   // x * y - z
+  int r; asm("{.reg .s32 t; neg.s32 t, %3; mad.lo.s32 %0, %1, %2, t;}" : "=r"(r) : "r"(x), "r"(y), "r"(z)); return r;
+}
+// rnd = {0x8000, -0x8000, 0x7FFF, -0x7FFF} come from the kernel arguments so that they are constant-bank operands of the IMADs
+// (written as literals the compiler splits them off into VIADDs on the ALU pipe, the pipe that bounds the kernel)
+template <bool TRUE_OUT>
+__device__ __forceinline__ void fcmul(int &sg, int &xr, int &xi, const int2 w, int m1, const int (&rnd)[4]) {
+  const int c = w.x, s = w.y;
+  int r, i;
+  if (sg > 0 || !TRUE_OUT) {
+    const int t = imad(xi, s, sg > 0 ? rnd[1] : rnd[3]), u = imad(xi, c, sg > 0 ? rnd[0] : rnd[2]);
+    r = imad_sub(xr, c, t); i = imad(xr, s, u);
+  } else {
+    const int t = imad(xr, c, rnd[1]), u = imad(xi, c, rnd[1]);
+    r = imad_sub(xi, s, t);
+    i = imad(imad(xr, s, u), m1, 0);
+    sg = 1;
+  }
   xr = sar(r, 16); xi = sar(i, 16);
 }
 
@@ -180,15 +202,15 @@ __device__ __forceinline__ void fast_pass(const FastArgs &a, int tl, const uint3
       if (i == S - 1 || rot) continue;
       const int L = S - i + 1;
       const int q = 1 << (L - 2);
-      const int4 *tab = a.tw + a.tw_off[L];
+      const int2 *tab = a.tw + a.tw_off[L];
 #pragma unroll
       for (int rr = 0; rr < R; ++rr) {
         const int quarter = ((rr >> (m - 1 - s)) & 1) + 2 * ((rr >> (m - s)) & 1);
         if (quarter) {
           const int k = (rr & (dist - 1)) * Dl + low;
           const int slot = quarter == 1 ? 0 : (quarter == 2 ? 1 : 2);
-          fcmul(sg[rr], re[rr], im[rr], __ldg(&tab[slot * q + k]));
-          sg[rr] = 1;
+          if (WRAP || (s == m - 1 && !last)) fcmul<true>(sg[rr], re[rr], im[rr], __ldg(&tab[slot * q + k]), a.m1, a.rnd);
+          else fcmul<false>(sg[rr], re[rr], im[rr], __ldg(&tab[slot * q + k]), a.m1, a.rnd);
         }
       }
     }
@@ -776,10 +798,10 @@ static rsp_status launch_fast_gos(const LaunchCtx &c, const FastArgs &fa, const 
 rsp_status launch_fast_chain(const Plan &pl, const LaunchCtx &ctx, const FxArgs &a, cudaStream_t st, const char **err) {
   FastArgs fa;
   fa.in = a.in; fa.out = a.out; fa.n_rows = a.n_rows; fa.row_base = a.row_base;
-  fa.tw = reinterpret_cast<const int4 *>(a.tw2);
+  fa.tw = reinterpret_cast<const int2 *>(a.tw2);
   fa.win4 = a.win_on ? a.win4 : nullptr;
   for (int L = 0; L < 16; ++L) fa.tw_off[L] = a.tw_off[L];
-  fa.W = a.W; fa.G = a.G; fa.scaler = a.scaler; fa.one = 1; fa.m1 = -1;
+  fa.W = a.W; fa.G = a.G; fa.scaler = a.scaler; fa.one = 1; fa.m1 = -1; fa.rnd[0] = 0x8000; fa.rnd[1] = -0x8000; fa.rnd[2] = 0x7FFF; fa.rnd[3] = -0x7FFF;
   fa.wmul = (int)(1u << (32 - a.sumw)); fa.div_sum = std::min(31, 32 - a.sumw + a.div_sum);
   fa.thr_mask = a.thr_w >= 32 ? 0xFFFFFFFFu : ((1u << a.thr_w) - 1u);
   fa.out_mul = (int)(1u << (a.binw + 1)); fa.thr_sext = 32 - a.thr_w;

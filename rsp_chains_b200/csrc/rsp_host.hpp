@@ -35,7 +35,7 @@ struct Tables {
   std::vector<uint32_t> tw;   // fixed twiddles, packed (cos16 << 16 | sin16 & 0xFFFF); per stageN three runs [W^2k | W^k | W^3k]
   std::vector<F2> twf;        // fp32 twiddles, same layout
   std::vector<float> twf4;    // fp32 twiddles again as (c, s, -s, c) quads: the two operands of the packed complex product (rsp_fast_f32.cu)
-  std::vector<int32_t> tw2;   // fixed twiddles again as int32 quads (c, s, -c, -s) << (16 - (twiddleWidth - 2)): the fast kernels'
+  std::vector<int32_t> tw2;   // fixed twiddles again as int32 pairs (c, s) << (16 - (twiddleWidth - 2)): the fast kernels'
                               // product then carries its rounded, wrapped result in bits 16..31 (rsp_fast.cu)
   int tw_off[16];
   std::vector<int32_t> log_tab;
@@ -213,13 +213,13 @@ inline void build_tables(const rsp_chain_params &p, Tables &t) {
         const long long re = wrap_host(from_double(c, twbp), tww), im = wrap_host(from_double(s, twbp), tww);
         t.tw.push_back(pack_iq((int)re, (int)im));
         const int32_t c4 = (int32_t)(re * (1LL << pre)), s4 = (int32_t)(im * (1LL << pre));
-        t.tw2.push_back(c4); t.tw2.push_back(s4); t.tw2.push_back(-c4); t.tw2.push_back(-s4);
+        t.tw2.push_back(c4); t.tw2.push_back(s4);
         F2 f; f.x = (float)c; f.y = (float)s;
         t.twf.push_back(f);
         t.twf4.push_back(f.x); t.twf4.push_back(f.y); t.twf4.push_back(-f.y); t.twf4.push_back(f.x);
       }
   }
-  if (t.tw.empty()) { t.tw.push_back(0); for (int z = 0; z < 4; ++z) t.tw2.push_back(0); F2 f; f.x = 1.f; f.y = 0.f; t.twf.push_back(f);
+  if (t.tw.empty()) { t.tw.push_back(0); for (int z = 0; z < 2; ++z) t.tw2.push_back(0); F2 f; f.x = 1.f; f.y = 0.f; t.twf.push_back(f);
                       t.twf4.push_back(1.f); t.twf4.push_back(0.f); t.twf4.push_back(0.f); t.twf4.push_back(1.f); }
   // log2 LUT (LogMagMux.scala:120-131)
   const int Lw = p.mag.log2LookUpWidth, num = 1 << Lw;
