@@ -2,7 +2,7 @@
 used by tests/, __graft_entry__.smoke() and bench.py's CPU legs only)."""
 from __future__ import annotations
 
-from rsp_chains_b200.params import CACFARType, GOSCFARType, log2Up
+from rsp_chains_b200.params import CACFARType, DITDecimType, GOSCFARType, log2Up
 
 
 def oracle_cfgs(O, params, log_n, sel, cfar_regs: dict):
@@ -11,8 +11,11 @@ def oracle_cfgs(O, params, log_n, sel, cfar_regs: dict):
     mask = 0
     for i, k in enumerate(f.keepMSBorLSB):
         mask |= (1 if k else 0) << i
-    mask = (mask >> (smax - log_n)) & ((1 << log_n) - 1)
-    fft = O.fft_cfg(log_n, f.dataWidth, f.binPoint, f.twiddleWidth, f.trimType, f.use4Muls, f.useBitReverse, mask, f.fftDir)
+    dit = f.decimType == DITDecimType
+    # a run-time size of k stages is the LAST k stages in DIF, the FIRST k in DIT (SDFChainRadix2.scala:127-134,196-203)
+    mask = (mask if dit else (mask >> (smax - log_n))) & ((1 << log_n) - 1)
+    fft = O.fft_cfg(log_n, f.dataWidth, f.binPoint, f.twiddleWidth, f.trimType, f.use4Muls, f.useBitReverse, mask, f.fftDir,
+                    f.sdfRadix, dit)
     mag = O.mag_cfg(m.dataWidth, m.binPoint, m.dataWidthLog, m.binPointLog, m.log2LookUpWidth, sel)
     if c.CFARAlgorithm == CACFARType:
         core = O.CORE_ASR if c.includeCASH else O.CORE_MEM

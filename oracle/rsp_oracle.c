@@ -155,8 +155,29 @@ static inline int tw_index(int n, int q) {
 /* twiddle tables of every multiplier stage of an S-stage transform (odd stage index i < S-1) */
 typedef struct { int32_t *re[32]; int32_t *im[32]; } fft_tabs;
 static void fft_tabs_free(fft_tabs *t) { for (int i = 0; i < 32; ++i) { free(t->re[i]); free(t->im[i]); t->re[i] = t->im[i] = NULL; } }
-static int fft_tabs_build(fft_tabs *t, int S, int tw) {
+/* radix-2 stage ROM: twiddles_rom(k) = (cos, -sin)(2*Pi*k / (2*delay)), k < delay (SDFChainRadix2.scala:300-306) */
+void rspo_twiddle_table_radix2(int delay, int tw_width, int32_t *re, int32_t *im) {
+  const int bp = tw_width - 2;
+  for (int k = 0; k < delay; ++k) {
+    const double ang = 2.0 * M_PI * (double)k / (double)(2 * delay);
+    re[k] = (int32_t)rspo_wrap(from_double(cos(ang), bp), tw_width);
+    im[k] = (int32_t)rspo_wrap(from_double(-sin(ang), bp), tw_width);
+  }
+}
+
+static int fft_tabs_build(fft_tabs *t, const rspo_fft_cfg *cfg) {
+  const int S = cfg->log_n, tw = cfg->twiddle_width;
   memset(t, 0, sizeof(*t));
+  if (cfg->sdf_radix == 2) { /* one ROM per stage, slot = log2(delay) */
+    for (int d = 0; d < S; ++d) {
+      const int delay = 1 << d;
+      t->re[d] = (int32_t *)malloc(sizeof(int32_t) * (size_t)delay);
+      t->im[d] = (int32_t *)malloc(sizeof(int32_t) * (size_t)delay);
+      if (!t->re[d] || !t->im[d]) { fft_tabs_free(t); return -2; }
+      rspo_twiddle_table_radix2(delay, tw, t->re[d], t->im[d]);
+    }
+    return 0;
+  }
   for (int i = 1; i < S - 1; i += 2) {
     const int stage_n = 4 << (S - 1 - i); /* 2 << (numStages - index) (SDFChainRadix22.scala:228) */
     t->re[i] = (int32_t *)malloc(sizeof(int32_t) * (size_t)stage_n);
@@ -167,11 +188,69 @@ static int fft_tabs_build(fft_tabs *t, int S, int tw) {
   return 0;
 }
 
+/* radix-2 SDF chain, DIF or DIT (SDFChainRadix2.scala:18-440).
+ * Stage with delay D: Butterfly + div2 / keep-LSB exactly as the radix-2^2 stage (:398-440).  The twiddle multiplier sits
+ * behind the butterfly on the difference output in DIF (`cntr < delay && cntr =/= 0`, :343-357: index k = 1..D-1 of the
+ * second half) and in front of the butterfly on the second-half input in DIT (`cntr > delay`, :321-339).  The product is
+ * taken with trimType = NoTrim / overflowType = Grow, i.e. exactly, and trimmed ONCE by trimBinary(bpos) under
+ * params.trimType (:350-351), then assigned to protoIQ (MSBs dropped).  k = 0 bypasses the multiplier.
+ * DIF: delays N/2 .. 1, natural-order input, bit-reversed output; DIT: delays 1 .. N/2, bit-reversed input, natural
+ * output (:26, SDFFFT.scala:217-270: with useBitReverse the ping-pong buffer sits behind DIF / in front of DIT).
+ * A run-time size of k stages is the last k stages in DIF and the first k in DIT (:127-134,196-203); the caller's
+ * keep_msb_mask is already aligned to the stages of THIS transform. */
+static int fft_fixed_core_radix2(const rspo_fft_cfg *cfg, const fft_tabs *tabs, int64_t *xr, int64_t *xi,
+                                 const int32_t *in_re, const int32_t *in_im, int32_t *out_re, int32_t *out_im) {
+  const int S = cfg->log_n, N = 1 << S;
+  const int w = cfg->data_width, tbp = cfg->twiddle_width - 2, trim = cfg->trim_type;
+  const int dit = cfg->decim_dit;
+  for (int p = 0; p < N; ++p) {
+    const int src = (dit && cfg->bit_reverse) ? (int)bitrev((uint32_t)p, S) : p;
+    xr[p] = rspo_wrap(cfg->fft_dir ? in_re[src] : in_im[src], w); /* ifft: swap on the way in (:214-220) */
+    xi[p] = rspo_wrap(cfg->fft_dir ? in_im[src] : in_re[src], w);
+  }
+  for (int i = 0; i < S; ++i) {
+    const int dl = dit ? i : S - 1 - i, D = 1 << dl;
+    const int scale = (cfg->keep_msb_mask >> i) & 1;
+    const int32_t *tr = tabs->re[dl], *ti = tabs->im[dl];
+    for (int b = 0; b < N; b += 2 * D)
+      for (int k = 0; k < D; ++k) {
+        const int p0 = b + k, p1 = b + k + D;
+        if (dit && k) {
+          const int64_t ar = xr[p1], ai = xi[p1];
+          xr[p1] = rspo_wrap(rspo_trim(ar * tr[k] - ai * ti[k], tbp, trim), w);
+          xi[p1] = rspo_wrap(rspo_trim(ar * ti[k] + ai * tr[k], tbp, trim), w);
+        }
+        const int64_t sr = xr[p0] + xr[p1], si = xi[p0] + xi[p1];
+        const int64_t dr = xr[p0] - xr[p1], di = xi[p0] - xi[p1];
+        if (scale) {
+          xr[p0] = rspo_wrap(rspo_trim(sr, 1, trim), w); xi[p0] = rspo_wrap(rspo_trim(si, 1, trim), w);
+          xr[p1] = rspo_wrap(rspo_trim(dr, 1, trim), w); xi[p1] = rspo_wrap(rspo_trim(di, 1, trim), w);
+        } else {
+          xr[p0] = rspo_wrap(sr, w); xi[p0] = rspo_wrap(si, w);
+          xr[p1] = rspo_wrap(dr, w); xi[p1] = rspo_wrap(di, w);
+        }
+        if (!dit && k) {
+          const int64_t ar = xr[p1], ai = xi[p1];
+          xr[p1] = rspo_wrap(rspo_trim(ar * tr[k] - ai * ti[k], tbp, trim), w);
+          xi[p1] = rspo_wrap(rspo_trim(ar * ti[k] + ai * tr[k], tbp, trim), w);
+        }
+      }
+  }
+  for (int n = 0; n < N; ++n) {
+    const int p = (!dit && cfg->bit_reverse) ? (int)bitrev((uint32_t)n, S) : n;
+    out_re[n] = (int32_t)(cfg->fft_dir ? xr[p] : xi[p]); /* ifft: swap on the way out, scalar 1.0 (:280,289-300) */
+    out_im[n] = (int32_t)(cfg->fft_dir ? xi[p] : xr[p]);
+  }
+  return 0;
+}
+
 static int fft_fixed_core(const rspo_fft_cfg *cfg, const fft_tabs *tabs, int64_t *xr, int64_t *xi,
                           const int32_t *in_re, const int32_t *in_im, int32_t *out_re, int32_t *out_im) {
   const int S = cfg->log_n;
   const int N = 1 << S;
   const int w = cfg->data_width, bp = cfg->bin_point, tw = cfg->twiddle_width, trim = cfg->trim_type;
+  if (cfg->sdf_radix == 2) return fft_fixed_core_radix2(cfg, tabs, xr, xi, in_re, in_im, out_re, out_im);
+  if (cfg->decim_dit) return -1; /* radix-2^2 DIT is not restated */
   for (int p = 0; p < N; ++p) {
     /* ifft swaps real and imaginary on the way in (SDFChainRadix22.scala:205-211) */
     xr[p] = rspo_wrap(cfg->fft_dir ? in_re[p] : in_im[p], w);
@@ -230,7 +309,7 @@ int rspo_fft_fixed(const rspo_fft_cfg *cfg, const int32_t *in_re, const int32_t 
   if (S < 1 || S > 24 || cfg->data_width < 2 || cfg->data_width > 32) return -1;
   const int N = 1 << S;
   fft_tabs tabs;
-  if (fft_tabs_build(&tabs, S, cfg->twiddle_width)) return -2;
+  if (fft_tabs_build(&tabs, cfg)) return -2;
   int64_t *xr = (int64_t *)malloc(sizeof(int64_t) * 2 * (size_t)N);
   if (!xr) { fft_tabs_free(&tabs); return -2; }
   const int rc = fft_fixed_core(cfg, &tabs, xr, xr + N, in_re, in_im, out_re, out_im);
@@ -308,7 +387,7 @@ static int fft_fixed_words_tabs(const rspo_fft_cfg *cfg, const fft_tabs *tabs, c
 int rspo_fft_fixed_words(const rspo_fft_cfg *cfg, const uint32_t *in, uint32_t *out, int n_chirps) {
   if (cfg->data_width > 16 || cfg->log_n < 1 || cfg->log_n > 24) return -1;
   fft_tabs tabs;
-  if (fft_tabs_build(&tabs, cfg->log_n, cfg->twiddle_width)) return -2;
+  if (fft_tabs_build(&tabs, cfg)) return -2;
   const int rc = fft_fixed_words_tabs(cfg, &tabs, in, out, n_chirps);
   fft_tabs_free(&tabs);
   return rc;
@@ -781,7 +860,7 @@ int rspo_chain_fixed_words(const rspo_chain_cfg *cfg, const uint32_t *in, uint32
   (void)n_threads;
   if (cfg->fft.data_width > 16 || cfg->fft.log_n < 1 || cfg->fft.log_n > 24) return -1;
   fft_tabs tabs;
-  if (fft_tabs_build(&tabs, cfg->fft.log_n, cfg->fft.twiddle_width)) return -2;
+  if (fft_tabs_build(&tabs, &cfg->fft)) return -2;
 #ifdef _OPENMP
 #pragma omp parallel num_threads(n_threads > 0 ? n_threads : 1)
 #endif

@@ -51,6 +51,8 @@ typedef struct {
   int32_t bit_reverse;    /* useBitReverse: 1 -> natural-order output                         */
   uint32_t keep_msb_mask; /* bit i = keepMSBorLSB(i) for stage i of THIS transform (1 = scale, 0 = keep LSB / wrap) */
   int32_t fft_dir;        /* 1 = FFT, 0 = IFFT (SDFChainRadix22.scala:205-211,362-383)        */
+  int32_t sdf_radix;      /* 2 = sdfRadix "2" (SDFChainRadix2.scala); 0 or 4 = "2^2"          */
+  int32_t decim_dit;      /* 1 = DITDecimType (radix 2 only), 0 = DIFDecimType                */
 } rspo_fft_cfg;
 
 /* MAGParams (generators/logMagMux/src/main/scala/LogMagMux.scala:14-49) + run-time sel */
@@ -96,6 +98,8 @@ int64_t rspo_wrap(int64_t v, int width);
 /* twiddles of one multiplier stage: entries t in [0, 3*stage_n/4), (cos, -sin)(2 pi t / stage_n) in Q2.(tw-2)
  * (SDFChainRadix22.scala:255-267) */
 void rspo_twiddle_table(int stage_n, int tw_width, int32_t *re, int32_t *im);
+/* radix-2 stage ROM of `delay` entries (SDFChainRadix2.scala:300-306) */
+void rspo_twiddle_table_radix2(int delay, int tw_width, int32_t *re, int32_t *im);
 /* sine quarter table (NCOTable.scala:254-258) */
 void rspo_nco_table(int table_size, int table_width, int32_t *tab);
 /* log2 LUT (LogMagMux.scala:120-131) */

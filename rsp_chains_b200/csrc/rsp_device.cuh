@@ -32,7 +32,9 @@ enum { STAGE_FFT = 0, STAGE_MAG = 1, STAGE_CFAR = 2 };
 // kernel variants of the fixed-point chain
 enum { MODE_GENERIC = 0,   // every parameter read at run time
        MODE_FAST = 1,      // 16-bit data, RoundHalfUp, scale every stage, forward, product trimmed once (binPoint <= 1)
-       MODE_FAST3 = 2 };   // as FAST but 3-multiplier product with per-product trim (binPoint >= 2, use4Muls = false)
+       MODE_FAST3 = 2,     // as FAST but 3-multiplier product with per-product trim (binPoint >= 2, use4Muls = false)
+       MODE_RADIX2 = 3 };  // sdfRadix "2" (SDFChainRadix2.scala), DIF or DIT; every parameter read at run time like GENERIC
+constexpr bool mode_is_generic(int m) { return m == MODE_GENERIC || m == MODE_RADIX2; }
 
 struct Detection { uint32_t chirp, bin; int32_t threshold, cut; };
 
@@ -44,7 +46,8 @@ struct FxArgs {
   uint32_t row_base;        // index of row 0 inside the caller's batch (reported in detections)
   int first_stage, last_stage;
   // FFT
-  int data_width, bp, tw_bp, trim, use4muls, bitrev, fft_dir;
+  int data_width, bp, tw_bp, trim, use4muls, bitrev, fft_dir;   // bitrev: the result is stored at the bit-reversed index
+  int radix2, dit, load_rev;   // sdfRadix "2" (SDFChainRadix2.scala), DITDecimType, beats arrive in bit-reversed order (DIT without useBitReverse)
   uint32_t keep_mask;       // bit i: stage i of THIS transform scales (1) or keeps LSBs (0)
   const uint32_t *tw;       // packed (cos16 << 16 | sin16) twiddles, per stageN three runs [W^2k | W^k | W^3k]
   int tw_off[16];           // word offset of the table of stageN = 1 << L
@@ -145,7 +148,7 @@ template <int S> struct Geo {
 // ------------------------------------------------------------------------------------------------ FFT arithmetic
 template <int MODE> RSP_HD void butterfly(const FxArgs &a, int scale, int &ar, int &ai, int &cr, int &ci) {
   const int sr = ar + cr, si = ai + ci, dr = ar - cr, di = ai - ci;
-  if (MODE != MODE_GENERIC) {
+  if (!mode_is_generic(MODE)) {
     // RoundHalfUp div2: (v + 1) >> 1.  The sum cannot leave 16 bits; the difference can (+32768) and wraps.
     ar = (sr + 1) >> 1; ai = (si + 1) >> 1;
     cr = wrap16((dr + 1) >> 1); ci = wrap16((di + 1) >> 1);
@@ -164,7 +167,7 @@ template <int MODE> RSP_HD void butterfly(const FxArgs &a, int scale, int &ar, i
 template <int MODE> RSP_HD void mul_mj(const FxArgs &a, int &re, int &im) {
   const int r = re;
   re = im;
-  im = (MODE != MODE_GENERIC) ? wrap16(-r) : wrapw(-r, a.data_width);
+  im = (!mode_is_generic(MODE)) ? wrap16(-r) : wrapw(-r, a.data_width);
 }
 
 // DspComplex context_* then trimBinary(bpos) then `:=` into protoIQ
@@ -209,6 +212,15 @@ template <int MODE> RSP_HD void cmul(const FxArgs &a, int &xr, int &xi, uint32_t
     xr = wrapw(re, a.data_width);
     xi = wrapw(im, a.data_width);
   }
+}
+
+// radix-2 chain: the product is exact (trimType = NoTrim, overflowType = Grow) and trimmed once by trimBinary(bpos) under
+// params.trimType, then assigned to protoIQ (SDFChainRadix2.scala:327-330,349-352)
+RSP_HD void cmul_r2(const FxArgs &a, int &xr, int &xi, uint32_t tw) {
+  const int br = hi16(tw), bi = lo16(tw);
+  const int ar = xr, ai = xi;
+  xr = wrapw(trim_rt<int>(ar * br - ai * bi, a.tw_bp, a.trim), a.data_width);
+  xi = wrapw(trim_rt<int>(ar * bi + ai * br, a.tw_bp, a.trim), a.data_width);
 }
 
 // ------------------------------------------------------------------------------------------------ LogMagMux
@@ -271,8 +283,9 @@ RSP_HD void fft_pass(const FxArgs &a, int tl, const uint32_t *gin, uint32_t *buf
 #pragma unroll
     for (int rr = 0; rr < R; ++rr) {
       const int p = base + rr * Dl;
-      const uint32_t wd = first ? ldg(&gin[p]) : bufA[pad(p)];
-      if (MODE != MODE_GENERIC) {   // dataWidth 16, forward
+      const int gp = (mode_is_generic(MODE) && first && a.load_rev) ? (int)bitrev_n((uint32_t)p, S) : p;
+      const uint32_t wd = first ? ldg(&gin[gp]) : bufA[pad(p)];
+      if (!mode_is_generic(MODE)) {   // dataWidth 16, forward
         re[rr] = hi16(wd); im[rr] = lo16(wd);
         if (first && a.win_on) {
           const int w = ldg(&a.win[p]);
@@ -295,7 +308,36 @@ RSP_HD void fft_pass(const FxArgs &a, int tl, const uint32_t *gin, uint32_t *buf
     for (int s = 0; s < m; ++s) {
       const int i = i0 + s;
       const int dist = 1 << (m - 1 - s);
-      const int scale = (MODE != MODE_GENERIC) ? 1 : (int)((a.keep_mask >> i) & 1u);
+      const int scale = (!mode_is_generic(MODE)) ? 1 : (int)((a.keep_mask >> i) & 1u);
+      if (MODE == MODE_RADIX2) {
+        // Radix-2 SDF chain.  DIF: the stage of delay D = Dl * dist multiplies the difference outputs k = 1..D-1 of every block by
+        // W_2D^k behind the butterfly (SDFChainRadix2.scala:343-357).  DIT is run in its natural-in / bit-reversed-out form, the
+        // same index space as DIF (point q here is point bitrev(q) of the reference's stream): stage i pairs points 2^(S-1-i)
+        // apart and multiplies the second one by W_2^(i+1)^k IN FRONT of the butterfly (:321-339), k = bitrev_i(block number).
+        // Both ROMs are run 0 ([W^2k], k < stageN/4) of the table of stageN = 4 * delay.
+        const uint32_t *tab = a.tw + a.tw_off[a.dit ? i + 2 : S - i + 1];
+        if (a.dit && i > 0) {
+#pragma unroll
+          for (int rr = 0; rr < R; ++rr)
+            if (rr & dist) {
+              const int blk = (high << s) | (rr >> (m - s));
+              const int k = (int)bitrev_n((uint32_t)blk, i);
+              if (k) cmul_r2(a, re[rr], im[rr], ldg(&tab[k]));
+            }
+        }
+#pragma unroll
+        for (int rr = 0; rr < R; ++rr)
+          if (!(rr & dist)) butterfly<MODE>(a, scale, re[rr], im[rr], re[rr + dist], im[rr + dist]);
+        if (!a.dit && i != S - 1) {
+#pragma unroll
+          for (int rr = 0; rr < R; ++rr)
+            if (rr & dist) {
+              const int k = (rr & (dist - 1)) * Dl + low;
+              if (k) cmul_r2(a, re[rr], im[rr], ldg(&tab[k]));
+            }
+        }
+        continue;
+      }
 #pragma unroll
       for (int rr = 0; rr < R; ++rr)
         if (!(rr & dist)) butterfly<MODE>(a, scale, re[rr], im[rr], re[rr + dist], im[rr + dist]);
@@ -325,11 +367,11 @@ RSP_HD void fft_pass(const FxArgs &a, int tl, const uint32_t *gin, uint32_t *buf
       if (!last) { bufA[pad(p)] = pack_iq(re[rr], im[rr]); continue; }
       const int bin = a.bitrev ? (int)bitrev_n((uint32_t)p, S) : p;
       int orr = re[rr], oi = im[rr];
-      if (MODE == MODE_GENERIC && !a.fft_dir) { const int t = orr; orr = oi; oi = t; }
+      if (mode_is_generic(MODE) && !a.fft_dir) { const int t = orr; orr = oi; oi = t; }
       uint32_t wd = pack_iq(orr, oi);
       if (a.last_stage != STAGE_FFT) {
         int mr, mi, ore;
-        if (MODE != MODE_GENERIC) { mr = orr; mi = oi; }
+        if (!mode_is_generic(MODE)) { mr = orr; mi = oi; }
         else { mr = wrapw((int)(wd >> 16), a.mag_w); mi = wrapw((int)(wd & 0xFFFFu), a.mag_w); }
         const int v = mag_one(a, mr, mi, &ore);
         wd = pack_iq(ore, v);

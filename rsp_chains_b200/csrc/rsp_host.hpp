@@ -56,8 +56,10 @@ inline rsp_status validate_params(const rsp_chain_params &p, std::string &err) {
   // FFTParams (SDFFFTParams.scala:53-86)
   RSP_REQ(is_pow2(f.numPoints), RSP_EINVAL, "number of points must be a power of 2");
   RSP_REQ(f.numPoints >= 2 && f.numPoints <= 16384, RSP_EUNSUPPORTED, "numPoints must be in 2..16384 (one chirp stays resident in shared memory)");
-  RSP_REQ(f.decimType == 0, RSP_EUNSUPPORTED, "only DIFDecimType is built");
-  RSP_REQ(f.sdfRadix == 4, RSP_EUNSUPPORTED, "only sdfRadix \"2^2\" is built");
+  RSP_REQ(f.sdfRadix == 2 || f.sdfRadix == 4, RSP_EINVAL, "Radix must be 2 or 2^2");   // SDFFFTParams.scala:61-64
+  RSP_REQ(f.decimType == 0 || f.decimType == 1, RSP_EINVAL, "decimType must be DIF or DIT");
+  RSP_REQ(f.decimType == 0 || (f.sdfRadix == 2 && p.arith == RSP_ARITH_FIXED), RSP_EUNSUPPORTED,
+          "DITDecimType is built for the fixed-point radix-2 chain only");
   RSP_REQ(!f.expandLogicAny, RSP_EUNSUPPORTED, "expandLogic (grow) stages are not built");
   RSP_REQ(f.windowFunc >= RSP_WINDOW_NONE && f.windowFunc <= RSP_WINDOW_USER, RSP_EINVAL, "unknown windowFunc");
   RSP_REQ(f.windowFunc == RSP_WINDOW_NONE || (f.windowWidth >= 3 && f.windowWidth <= 16), RSP_EUNSUPPORTED, "window dataWidth must be in 3..16");
@@ -201,7 +203,10 @@ inline void build_tables(const rsp_chain_params &p, Tables &t) {
   const int pre = 16 - twbp > 0 ? 16 - twbp : 0;
   for (int L = 0; L < 16; ++L) t.tw_off[L] = 0;
   const double PI = 3.14159265358979323846;  // scala.math.Pi
-  for (int L = 3; L <= Smax; ++L) {
+  // the radix-2 chain reads run 0 of the table of stageN = 4 * delay as its stage ROM, W_(2 delay)^k = W_stageN^2k bit for bit
+  // (SDFChainRadix2.scala:300-306): its first stage needs one table more
+  const int Lmax = p.fft.sdfRadix == 2 ? (Smax + 1 < 15 ? Smax + 1 : 15) : Smax;
+  for (int L = 3; L <= Lmax; ++L) {
     const int stageN = 1 << L, q = stageN / 4;
     t.tw_off[L] = (int)t.tw.size();
     const int mult[3] = {2, 1, 3};
@@ -316,16 +321,22 @@ inline rsp_status plan_fixed(const rsp_chain_params &p, const Regs &r, const Tab
   } else {
     S = f.runTime ? (int)r.fft[RSP_FFT_REG_FFTSIZE] : Smax;
     if (S < 1 || S > Smax) { err = "fftSize register must be in 1..log2(numPoints)"; return RSP_EINVAL; }
-    if ((Smax - S) & 1) { err = "radix 2^2 run-time size must drop an even number of stages (Radix22RunTimeSpec.scala:18-19)"; return RSP_EINVAL; }
+    if (f.sdfRadix == 4 && ((Smax - S) & 1)) { err = "radix 2^2 run-time size must drop an even number of stages (Radix22RunTimeSpec.scala:18-19)"; return RSP_EINVAL; }
   }
   pl.S = S; pl.first_stage = first_stage; pl.last_stage = last_stage;
   a.first_stage = first_stage; a.last_stage = last_stage;
   a.data_width = f.dataWidth; a.bp = f.binPoint; a.tw_bp = f.twiddleWidth - 2; a.trim = f.trimType; a.use4muls = f.use4Muls ? 1 : 0;
-  a.bitrev = f.useBitReverse ? 1 : 0;
+  a.radix2 = f.sdfRadix == 2 ? 1 : 0;
+  a.dit = (a.radix2 && f.decimType == 1) ? 1 : 0;
+  // DIT runs natural-in / bit-reversed-out like DIF (rsp_device.cuh): its result always lands at the bit-reversed index, and
+  // without useBitReverse the caller's beats are in bit-reversed order (SDFFFT.scala:217-270)
+  a.bitrev = (f.useBitReverse || a.dit) ? 1 : 0;
+  a.load_rev = (a.dit && !f.useBitReverse) ? 1 : 0;
   a.fft_dir = f.fftDirReg ? (int)(r.fft[RSP_FFT_REG_FFTDIR] & 1u) : (f.fftDir ? 1 : 0);
   const uint32_t phys = f.keepMSBorLSBReg ? r.fft[RSP_FFT_REG_KEEPMSBORLSB] : f.keepMSBorLSB;
   const uint32_t smask = S >= 32 ? 0xFFFFFFFFu : ((1u << S) - 1u);
-  a.keep_mask = (first_stage == STAGE_CFAR) ? smask : ((phys >> (Smax - S)) & smask);   // run-time size uses the LAST S stages
+  // a run-time size uses the LAST S stages in DIF and the FIRST S in DIT (SDFChainRadix2.scala:127-134,196-203)
+  a.keep_mask = (first_stage == STAGE_CFAR) ? smask : (((a.dit ? phys : (phys >> (Smax - S)))) & smask);
   for (int L = 0; L < 16; ++L) a.tw_off[L] = t.tw_off[L];
   // windowing happens on the forward transform only (SDFFFT.scala:229-245: `when (fftDir)`); win itself is bound by the caller
   a.win_on = (first_stage == STAGE_FFT && f.windowFunc != RSP_WINDOW_NONE && a.fft_dir == 1) ? 1 : 0;
@@ -350,6 +361,7 @@ inline rsp_status plan_fixed(const rsp_chain_params &p, const Regs &r, const Tab
   const bool common = f.dataWidth == 16 && f.trimType == RSP_TRIM_ROUND_HALF_UP && a.keep_mask == smask && a.fft_dir == 1 &&
                       p.mag.dataWidth == 16;
   pl.mode = MODE_GENERIC;
+  if (a.radix2) { pl.mode = MODE_RADIX2; return RSP_OK; }   // run-time-parameter kernel with the radix-2 stage structure
   if (common && s1 <= 0) pl.mode = MODE_FAST;
   else if (common && s1 >= 1 && !f.use4Muls) pl.mode = MODE_FAST3;
   return RSP_OK;

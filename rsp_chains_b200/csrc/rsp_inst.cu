@@ -1,17 +1,17 @@
 // rsp_inst.cu -- instantiates one slice of the templated chain kernels.  Compiled once per RSP_UNIT (see Makefile):
-//   0/1 generic fixed, 2/3 fast fixed, 4/5 fast3 fixed (low / high transform sizes); 6/7 fp32 (low / high).
+//   0/1 generic fixed, 2/3 fast fixed, 4/5 fast3 fixed, 8/9 radix-2 fixed (low / high transform sizes); 6/7 fp32 (low / high).
 #include <algorithm>
 
 #include "rsp_kernels.cuh"
 #include "rsp_launch.hpp"
 
 #ifndef RSP_UNIT
-#error "compile with -DRSP_UNIT=0..7"
+#error "compile with -DRSP_UNIT=0..9"
 #endif
 
 namespace rsp {
 
-#if RSP_UNIT < 6
+#if RSP_UNIT < 6 || RSP_UNIT >= 8
 template <int S, int MODE>
 static rsp_status launch_fixed_sm(const LaunchCtx &c, const FxArgs &a, cudaStream_t st, const char **err) {
   using G = Geo<S>;
@@ -31,6 +31,8 @@ static rsp_status launch_fixed_sm(const LaunchCtx &c, const FxArgs &a, cudaStrea
 #define RSP_MODE_OF_UNIT MODE_GENERIC
 #elif RSP_UNIT / 2 == 1
 #define RSP_MODE_OF_UNIT MODE_FAST
+#elif RSP_UNIT / 2 == 4
+#define RSP_MODE_OF_UNIT MODE_RADIX2
 #else
 #define RSP_MODE_OF_UNIT MODE_FAST3
 #endif

@@ -362,3 +362,63 @@ def test_window_functions(cuda, oracle):
     p = chain_params(n, 0, W=16, G=4, fftDir=False)
     p.fftParams.windowFunc = WT.Hanning()
     run_and_compare(cuda, oracle, p, 10, 2, regs, beats)
+
+
+# ------------------------------------------------------------------------------------------------ radix-2 chain (SDFChainRadix2.scala)
+@pytest.mark.parametrize("dit", [False, True])
+@pytest.mark.parametrize("log_n", [1, 2, 3, 4, 5, 7, 8, 10, 11, 13, 14])
+def test_radix2_chain_all_sizes(cuda, oracle, log_n, dit):
+    """sdfRadix = "2", DIF and DIT, full-range random beats, every pass geometry of the row-resident kernel; FFT block alone for
+    the sizes too small for a CFAR window"""
+    n = 1 << log_n
+    dec = R.DITDecimType if dit else R.DIFDecimType
+    beats = synth.random_beats(23 if log_n < 13 else 4, n, seed=100 + log_n)
+    W, G = max(2, min(16, n // 8)), 1
+    p = chain_params(n, 0, W=W, G=G, sdfRadix="2", decimType=dec)
+    if n > 2 * W + 2 * G + 1:
+        regs = dict(fftWin=n, thresholdScaler=3, logOrLinearMode=1, divSum=max(0, W.bit_length() - 1), peakGrouping=0, cfarMode=dit,
+                    windowCells=W, guardCells=G)
+        run_and_compare(cuda, oracle, p, log_n, 2, regs, beats)
+    fft, _, _ = oracle_cfgs(oracle, p, log_n, 2, {})
+    with R.FftMagCfarChainVanilla(p) as ch:
+        ch.memWriteWord(p.fftAddress.base, log_n)
+        d_in = to_dev(cuda, beats)
+        d_f = cuda.empty_like(d_in)
+        ch.fft(d_in, beats.shape[0], d_f)
+        cuda.cuda.synchronize()
+        if n > 2 * W + 2 * G + 1:
+            assert ("radix2-dit" if dit else "radix2-dif") in ch.variant
+        assert (from_dev_u32(d_f) == oracle.fft_fixed_words(fft, beats)).all()
+
+
+@pytest.mark.parametrize("dit", [False, True])
+@pytest.mark.parametrize("bp,trim,use4,bitrev,fwd,keep", [
+    (14, "Convergent", False, True, True, None), (12, "RoundDown", True, False, True, None), (0, "RoundHalfUp", False, False, False, None),
+    (12, "RoundHalfToOdd", False, True, True, 0b1011011101), (9, "RoundTowardsZero", False, True, False, 0b0000011111)])
+def test_radix2_fft_block_variants(cuda, oracle, dit, bp, trim, use4, bitrev, fwd, keep):
+    """radix-2 FFT block alone: binary points, trim types, bit-reversed input (DIT) / output (DIF) without the ping-pong buffer,
+    IFFT, keep-LSB stages, run-time sizes (DIF: last k stages, DIT: first k; any k, SDFChainRadix2.scala:127-134)"""
+    n, smax = 1024, 10
+    kw = dict(sdfRadix="2", decimType=R.DITDecimType if dit else R.DIFDecimType, use4Muls=use4, fftDir=fwd)
+    if keep is not None:
+        kw["keepMSBorLSB"] = [bool((keep >> i) & 1) for i in range(smax)]
+    p = chain_params(n, bp, trim, **kw)
+    p.fftParams.useBitReverse = bitrev
+    for log_n in (10, 9, 6, 1):
+        beats = synth.random_beats(9, 1 << log_n, seed=log_n + 7 * bp, full_range=keep is None)
+        fft, _, _ = oracle_cfgs(oracle, p, log_n, 2, {})
+        with R.FftMagCfarChainVanilla(p) as ch:
+            ch.memWriteWord(p.fftAddress.base, log_n)
+            d_in = to_dev(cuda, beats)
+            d_f = cuda.empty_like(d_in)
+            ch.fft(d_in, beats.shape[0], d_f)
+            cuda.cuda.synchronize()
+            got = from_dev_u32(d_f)
+        want = oracle.fft_fixed_words(fft, beats)
+        assert (got == want).all(), f"log_n={log_n}: {(got != want).sum()} beats differ"
+
+
+def test_radix22_dit_is_unsupported(cuda):
+    p = chain_params(256, 0, W=16, G=2, decimType=R.DITDecimType)
+    with pytest.raises(R.RspError):
+        R.FftMagCfarChainVanilla(p)

@@ -126,6 +126,82 @@ def test_fft_keep_lsb_and_ifft(oracle):
     assert np.abs(br - re).max() <= 3 and np.abs(bi - im).max() <= 3
 
 
+# ------------------------------------------------------------------------------------------------ radix-2 chain (SDFChainRadix2.scala)
+def real_tone(n, f1r):   # Radix2Spec.getRealTone (Radix2Spec.scala:18-21), f2r = 0
+    i = np.arange(n)
+    return np.sin(2 * np.pi * f1r * i) + np.sin(2 * np.pi * 0.0 * i)
+
+
+@pytest.mark.parametrize("dit", [False, True])
+@pytest.mark.parametrize("n", [4, 8, 16, 32, 64, 128, 256, 512])
+def test_fft_radix2_spec_tolerance(oracle, n, dit):
+    """Radix2Spec.scala:27-52: radix 2, DIF and DIT, Convergent, scale every stage, real tone at 1/N, testFFT(3, ...) with the
+    default FFTParams.fixed widths (16-bit Q2.14, SDFFFTParams.scala:92-96): |raw error| <= 2^3 - 1 vs fft(x) / N;
+    the 4-multiplier variant (:55-70) gives the same bits because the product is taken with NoTrim"""
+    log_n = n.bit_length() - 1
+    x = real_tone(n, 1.0 / n)
+    want = np.fft.fft(x) / n * (1 << 14)
+    outs = []
+    for use4 in (False, True):
+        cfg = oracle.fft_cfg(log_n, 16, 14, 16, "Convergent", use4, True, (1 << log_n) - 1, True, "2", dit)
+        ore, oim = oracle.fft_fixed(cfg, quantize(x, 14), np.zeros(n, np.int64))
+        err = max(np.abs(ore - want.real).max(), np.abs(oim - want.imag).max())
+        assert err <= 7, f"N={n} dit={dit}: max raw error {err:.2f} LSB"
+        outs.append((ore, oim))
+    assert (outs[0][0] == outs[1][0]).all() and (outs[0][1] == outs[1][1]).all()
+
+
+@pytest.mark.parametrize("n", [2, 4, 8, 16, 32, 64, 128, 256, 512, 1024])
+def test_fft_radix2_random_spec_tolerance(oracle, n):
+    """Radix2RandomSpec.scala:14-40: genRandSignal, 16-bit Q2.14, Convergent, radix 2, simpleTestFFT(3, ...)"""
+    log_n = n.bit_length() - 1
+    for dit in (False, True):
+        cfg = oracle.fft_cfg(log_n, 16, 14, 16, "Convergent", False, True, (1 << log_n) - 1, True, "2", dit)
+        for rep in range(2):
+            re, im = java_rand_signal(oracle, n, 11110 + rep)
+            ore, oim = oracle.fft_fixed(cfg, quantize(re, 14), quantize(im, 14))
+            want = np.fft.fft(re + 1j * im) / n * (1 << 14)
+            err = max(np.abs(ore - want.real).max(), np.abs(oim - want.imag).max())
+            assert err <= 7, f"N={n} dit={dit}: max raw error {err:.2f} LSB"
+
+
+def test_fft_radix2_orders_runtime_size_and_ifft(oracle):
+    """without useBitReverse DIF leaves its bins bit-reversed and DIT expects bit-reversed input (SDFFFT.scala:217-270,
+    SDFFFTTester.scala:127-129); a run-time size of k stages is a k-stage transform; ifft(fft(x)) recovers x"""
+    rng = np.random.default_rng(8)
+    n, log_n = 128, 7
+    re, im = rng.integers(-9000, 9000, n), rng.integers(-9000, 9000, n)
+    rev = np.array([int(format(i, f"0{log_n}b")[::-1], 2) for i in range(n)])
+    mask = (1 << log_n) - 1
+    for dit in (False, True):
+        nat = oracle.fft_fixed(oracle.fft_cfg(log_n, 16, 0, 16, "RoundHalfUp", False, True, mask, True, "2", dit), re, im)
+        raw_cfg = oracle.fft_cfg(log_n, 16, 0, 16, "RoundHalfUp", False, False, mask, True, "2", dit)
+        if dit:
+            raw = oracle.fft_fixed(raw_cfg, re[rev], im[rev])          # bit-reversed in, natural out
+            assert (raw[0] == nat[0]).all() and (raw[1] == nat[1]).all()
+        else:
+            raw = oracle.fft_fixed(raw_cfg, re, im)                    # natural in, bit-reversed out
+            assert (raw[0] == nat[0][rev]).all() and (raw[1] == nat[1][rev]).all()
+        want = np.fft.fft(re + 1j * im) / n
+        assert max(np.abs(nat[0] - want.real).max(), np.abs(nat[1] - want.imag).max()) <= 4
+        sre, sim = re // 100, im // 100                                # small enough for a transform that never scales
+        fwd = oracle.fft_fixed(oracle.fft_cfg(log_n, 16, 0, 16, "RoundHalfUp", False, True, 0, True, "2", dit), sre, sim)
+        inv = oracle.fft_cfg(log_n, 16, 0, 16, "RoundHalfUp", False, True, mask, False, "2", dit)   # scaled inverse: 1/N
+        br, bi = oracle.fft_fixed(inv, fwd[0], fwd[1])
+        assert max(np.abs(br - sre).max(), np.abs(bi - sim).max()) <= 3
+
+
+def test_radix2_rom_is_run_0_of_the_radix22_table(oracle):
+    """W_(2 delay)^k (SDFChainRadix2.scala:300-306) equals W_(4 delay)^(2k) (SDFChainRadix22.scala:262-267) bit for bit: the CUDA
+    library reads the radix-2 stage ROMs out of its radix-2^2 tables (rsp_host.hpp build_tables)"""
+    for tw in (16, 12, 9):
+        for d in range(1, 15):
+            delay = 1 << d
+            r2 = oracle.twiddle_table_radix2(delay, tw)
+            r4 = oracle.twiddle_table(4 * delay, tw)
+            assert (r2[0] == r4[0][0:2 * delay:2]).all() and (r2[1] == r4[1][0:2 * delay:2]).all()
+
+
 def test_trim_modes(oracle):
     """dsptools TrimType semantics on x / 2 (names of Radix22SQNRSpec.scala:184)"""
     table = {  # value: (-3, -1, 1, 3) / 2 = (-1.5, -0.5, 0.5, 1.5)
