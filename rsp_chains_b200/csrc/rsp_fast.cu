@@ -16,6 +16,8 @@
 //    scatter of the magnitudes; the CFAR window sums are differences of one prefix-sum array
 //  * global loads and stores are warp-contiguous 128-byte lines.
 #include <algorithm>
+#include <cstdint>
+#include <cstdlib>
 
 #include "rsp_fast.cuh"
 
@@ -40,6 +42,8 @@ struct FastArgs {
   Detection *det_list;
   uint32_t *det_count;
   uint32_t det_cap;
+  int stage;             // 1: the next row's beats are fetched with cp.async into a staging area behind the CTA's rows while this
+                         // row's CFAR phase runs (chain_fixed_fast_kernel); needs 16-byte aligned rows and N more words per chirp
 };
 
 // Exchange-buffer index of point p.  The pads are chosen per size by the shared-memory model in tests/test_kernel_layout.py so
@@ -71,6 +75,15 @@ template <int S> struct FGeo {
   static constexpr int XM = (mhx<S>(N - 1) / 2 + 4) & ~3;     // words of the magnitude array (int16 per bin, padded)
   static constexpr int ROW = XB + XM;                        // words per chirp
   static constexpr int NW = TPC / 32;                        // warps per chirp
+  // Design study, off by default (-DRSP_FAST_TWSMEM_S=14 turns it on): at N = 16384 the twiddle tables of the first pass (stageN = N
+  // and N / 4: 96 + 24 KB) do not stay in L1 next to a 105 KB row, every row re-reads them from L2.  Keeping them in the shared
+  // memory of the SM's one CTA was measured 8 % SLOWER than reading them through L1/L2 with the cp.async staging on (151.0 vs
+  // 164.7 Gsamples/s, profiles/r01_l_tw_smem_ab.txt): the kernel is short of shared-memory issue slots (mio_throttle), not of L2.
+#ifndef RSP_FAST_TWSMEM_S
+#define RSP_FAST_TWSMEM_S 15
+#endif
+  static constexpr int TWE = S >= RSP_FAST_TWSMEM_S ? 3 * (N / 4) + 3 * (N / 16) : 0;   // entries kept in shared memory
+  static constexpr int TWS = 2 * TWE;                        // words
 };
 
 // Sign extensions and shifts go through inline PTX on purpose: when the compiler can prove a value fits 16 bits it rewrites the
@@ -80,6 +93,12 @@ __device__ __forceinline__ int sext16(int v) { int r; asm("prmt.b32 %0, %1, 0, 0
 __device__ __forceinline__ int hi16s(uint32_t v) { int r; asm("prmt.b32 %0, %1, 0, 0xbb32;" : "=r"(r) : "r"(v)); return r; }
 __device__ __forceinline__ int sar(int v, int n) { int r; asm("shr.s32 %0, %1, %2;" : "=r"(r) : "r"(v), "r"(n)); return r; }
 __device__ __forceinline__ uint32_t pack2(int re, int im) { return __byte_perm((uint32_t)im, (uint32_t)re, 0x5410); }
+// 16-byte asynchronous copy global -> shared, past L1 (LDGSTS.BYPASS.128): no registers are held while the line is in flight
+__device__ __forceinline__ void cp_async16(void *dst_shared, const void *src_global) {
+  asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" :: "r"((uint32_t)__cvta_generic_to_shared(dst_shared)), "l"(src_global) : "memory");
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
 
 // sa * A + sc * C with compile-time signs, as ONE IMAD (FMA pipe).  The multiplier is a run-time +-1 so that ptxas keeps the
 // IMAD instead of strength-reducing it to an IADD3: the ALU pipe (PRMT, SHF, compares) is the bound of this kernel and the
@@ -148,8 +167,8 @@ __device__ __forceinline__ int fjpl(int re, int im) {
 // Thread tl of the chirp works on the groups vt = g * TPC + tl, so a warp touches consecutive words in every pass.
 // WRAP = false: the row was found "quiet" (see quiet_beats): no value of the transform can reach +-32768, so the 16-bit wrap
 // of the butterfly differences is the identity and its PRMT is left out (13% of the ALU-pipe instructions of the kernel).
-template <int S, int K, bool WRAP>
-__device__ __forceinline__ void fast_pass(const FastArgs &a, int tl, const uint32_t (&pre)[16], uint32_t *xb, uint32_t *xm) {
+template <int S, int K, bool WRAP, bool TWSM = false>
+__device__ __forceinline__ void fast_pass(const FastArgs &a, int tl, const uint32_t (&pre)[16], uint32_t *xb, uint32_t *xm, const int2 *tws = nullptr) {
   using Gm = FGeo<S>;
   constexpr int m = fx_pass_size(S, K), i0 = fx_pass_start(S, K), LDl = S - i0 - m, Dl = 1 << LDl;
   constexpr int PTS = Gm::PTS, G = PTS >> m, R = 1 << m, TPC = Gm::TPC;
@@ -202,15 +221,17 @@ __device__ __forceinline__ void fast_pass(const FastArgs &a, int tl, const uint3
       if (i == S - 1 || rot) continue;
       const int L = S - i + 1;
       const int q = 1 << (L - 2);
-      const int2 *tab = a.tw + a.tw_off[L];
+      constexpr bool smt = TWSM && first;                      // this pass's tables sit in shared memory: [stageN = N | N / 4]
+      const int2 *tab = smt ? tws + (i == 1 ? 0 : 3 * (Gm::N / 4)) : a.tw + a.tw_off[L];
 #pragma unroll
       for (int rr = 0; rr < R; ++rr) {
         const int quarter = ((rr >> (m - 1 - s)) & 1) + 2 * ((rr >> (m - s)) & 1);
         if (quarter) {
           const int k = (rr & (dist - 1)) * Dl + low;
           const int slot = quarter == 1 ? 0 : (quarter == 2 ? 1 : 2);
-          if (WRAP || (s == m - 1 && !last)) fcmul<true>(sg[rr], re[rr], im[rr], __ldg(&tab[slot * q + k]), a.m1, a.rnd);
-          else fcmul<false>(sg[rr], re[rr], im[rr], __ldg(&tab[slot * q + k]), a.m1, a.rnd);
+          const int2 w = smt ? tab[slot * q + k] : __ldg(&tab[slot * q + k]);
+          if (WRAP || (s == m - 1 && !last)) fcmul<true>(sg[rr], re[rr], im[rr], w, a.m1, a.rnd);
+          else fcmul<false>(sg[rr], re[rr], im[rr], w, a.m1, a.rnd);
         }
       }
     }
@@ -253,12 +274,18 @@ __device__ __forceinline__ void fast_pass(const FastArgs &a, int tl, const uint3
 // The thread's 16 beats of a row, p = tl + rr * TPC (warp-contiguous 128-byte lines), times the window when there is one:
 // bits 16..31 of beat * (window << (16 - bp)) are wrap16(floor(beat * window >> bp)), the truncating assignment of
 // SDFFFT.scala:233-234; the windowed beats are packed again so that everything behind (the quiet test too) sees plain beats.
+template <int S> __device__ __forceinline__ void window_beats(const FastArgs &a, int tl, uint32_t (&pre)[16]);
 template <int S>
 __device__ __forceinline__ void load_beats(const FastArgs &a, uint32_t row, int tl, uint32_t (&pre)[16]) {
   constexpr int N = 1 << S, TPC = FGeo<S>::TPC;
   const uint32_t *gin = a.in + (size_t)row * N + tl;
 #pragma unroll
   for (int rr = 0; rr < 16; ++rr) pre[rr] = __ldg(&gin[rr * TPC]);
+  window_beats<S>(a, tl, pre);
+}
+template <int S>
+__device__ __forceinline__ void window_beats(const FastArgs &a, int tl, uint32_t (&pre)[16]) {
+  constexpr int TPC = FGeo<S>::TPC;
   if (a.win4 != nullptr) {
     const int32_t *gw = a.win4 + tl;
 #pragma unroll
@@ -297,12 +324,13 @@ __device__ __forceinline__ void fast_passes_from(const FastArgs &a, int c, int t
   if constexpr (K + 1 < fx_n_passes(S)) fast_passes_from<S, K + 1>(a, c, tl, quiet, pre, xb, xm);
 }
 
-template <int S, int K>
-__device__ __forceinline__ void fast_passes(const FastArgs &a, int c, int tl, const uint32_t (&pre)[16], uint32_t *xb, uint32_t *xm, int *loud) {
+template <int S, int K, bool TWSM = false>
+__device__ __forceinline__ void fast_passes(const FastArgs &a, int c, int tl, const uint32_t (&pre)[16], uint32_t *xb, uint32_t *xm, int *loud,
+                                            const int2 *tws = nullptr) {
   static_assert(K == 0 && fx_pass_size(S, 0) == 4, "the first pass takes the 16 prefetched beats of the thread");
   const bool warp_quiet = __all_sync(0xffffffffu, quiet_beats(pre));
   if (!warp_quiet && (tl & 31) == 0) loud[c] = 1;
-  if (warp_quiet) fast_pass<S, 0, false>(a, tl, pre, xb, xm); else fast_pass<S, 0, true>(a, tl, pre, xb, xm);
+  if (warp_quiet) fast_pass<S, 0, false, TWSM>(a, tl, pre, xb, xm, tws); else fast_pass<S, 0, true, TWSM>(a, tl, pre, xb, xm, tws);
   chirp_sync<S>(c);
   if constexpr (fx_n_passes(S) > 1) {
     const bool quiet = loud[c] == 0;
@@ -407,14 +435,43 @@ __global__ void __launch_bounds__(FGeo<S>::THREADS, 1024 / FGeo<S>::THREADS) cha
   const short *X = reinterpret_cast<const short *>(xm), *Xt = X + mhx<S>(tl);
   const int *pA = P + tl + a.G + a.W + 1, *pB = P + tl + a.G + 1, *pC = P + tl - a.G, *pD = P + tl - a.G - a.W;
   const uint32_t stride = gridDim.x * CPC;
+  // Staging (a.stage): the beats of the CTA's NEXT rows are copied global -> shared by cp.async (4 x 16 bytes per thread, no
+  // registers in flight) once this row's transform is done, and land while its CFAR phase runs; the row loop then starts from
+  // shared memory instead of waiting on HBM with every warp of the CTA at once (at N = 16384 one 1024-thread CTA owns the SM).
+  uint32_t *stg = smem + (size_t)CPC * Gm::ROW + (size_t)c * N;
+  const bool stage = a.stage != 0;
+  constexpr bool TWSM = Gm::TWS > 0;
+  const int2 *tws = reinterpret_cast<const int2 *>(smem + (size_t)CPC * Gm::ROW);   // shares the place of the staging area: one or the other
+  if (TWSM) {
+    int4 *dst = reinterpret_cast<int4 *>(smem + (size_t)CPC * Gm::ROW);
+    const int4 *s0 = reinterpret_cast<const int4 *>(a.tw + a.tw_off[S]), *s1 = reinterpret_cast<const int4 *>(a.tw + a.tw_off[S - 2]);
+    constexpr int n0 = 3 * (N / 4) / 2, n1 = 3 * (N / 16) / 2;   // int4 = two entries
+    for (int e = threadIdx.x; e < n0; e += Gm::THREADS) dst[e] = __ldg(&s0[e]);
+    for (int e = threadIdx.x; e < n1; e += Gm::THREADS) dst[n0 + e] = __ldg(&s1[e]);
+    __syncthreads();
+  }
+  auto prefetch = [&](uint32_t r0) {
+    const uint32_t rw = min(r0 + (uint32_t)c, a.n_rows - 1);
+    const uint32_t *g = a.in + (size_t)rw * N;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) { const int e = (k * TPC + tl) * 4; cp_async16(stg + e, g + e); }
+    cp_async_commit();
+  };
+  if (stage) { prefetch(blockIdx.x * CPC); cp_async_wait_all(); __syncthreads(); }
   // the loop bound is the same for every thread of the CTA (the barriers are CTA-wide); a chirp slot past the last row
   // recomputes the last row -- it stores the same beats again and reports no detections
   for (uint32_t row0 = blockIdx.x * CPC; row0 < a.n_rows; row0 += stride) {
     const bool active = row0 + c < a.n_rows;
     const uint32_t row = active ? row0 + c : a.n_rows - 1;
     uint32_t pre[PTS];
-    load_beats<S>(a, row, tl, pre);
-    fast_passes<S, 0>(a, c, tl, pre, xb, xm, loud);
+    if (stage) {
+#pragma unroll
+      for (int rr = 0; rr < 16; ++rr) pre[rr] = stg[tl + rr * TPC];
+      window_beats<S>(a, tl, pre);
+    } else load_beats<S>(a, row, tl, pre);
+    fast_passes<S, 0, TWSM>(a, c, tl, pre, xb, xm, loud, tws);
+    // every thread is past the first barrier of the passes: the staging area has been read and can take the next rows
+    if (stage && row0 + stride < a.n_rows) prefetch(row0 + stride);
     // prefix sums of the thread's 16 consecutive magnitudes
     int x[PTS];
     {
@@ -452,6 +509,7 @@ __global__ void __launch_bounds__(FGeo<S>::THREADS, 1024 / FGeo<S>::THREADS) cha
       const FastDetArgs da = {a.W, a.G, a.div_sum, a.scaler, a.thr_sext, a.row_base + row, a.det_cap, a.det_list, a.det_count};
       fast_detections<S, CMODE, LINEAR>(da, tl, (uint32_t)mask, P, X);
     }
+    if (stage) cp_async_wait_all();   // this thread's copies have landed; the barrier publishes everybody's
     chirp_sync<S>(c);
   }
 }
@@ -751,12 +809,25 @@ bool fast_chain_supported(const Plan &pl, const FxArgs &a) {
   return true;
 }
 
+// cp.async staging of the next row (FastArgs::stage).  Measured on B200 (scripts/gpu_stage_ab.sh, profiles/r01_l_stage_ab.txt): +1.9 %
+// at N = 16384 (one CTA per SM, nobody else to hide the row's first loads), nothing or slightly negative below, so it is on from
+// 2^14 points; RSP_FAST_STAGE=0 turns it off, RSP_FAST_STAGE_MIN_S=s moves the limit (tuning knobs, read once)
+static bool fast_stage_enabled(int S) {
+  static int on = -1, min_s = 0;
+  if (on < 0) {
+    const char *e = std::getenv("RSP_FAST_STAGE"), *m = std::getenv("RSP_FAST_STAGE_MIN_S");
+    on = (e != nullptr && e[0] == '0') ? 0 : 1;
+    min_s = m != nullptr ? std::atoi(m) : 14;
+  }
+  return on != 0 && S >= min_s;
+}
+
 template <int S, int CMODE, bool LINEAR, int EJ>
 static rsp_status launch_fast_inst(const LaunchCtx &c, const FastArgs &fa, cudaStream_t st, const char **err) {
   using Gm = FGeo<S>;
   static int occ_dev[64] = {0};
   int &occ = occ_dev[c.device & 63];
-  const size_t smem = (size_t)Gm::CPC * Gm::ROW * sizeof(uint32_t);
+  const size_t smem = ((size_t)Gm::CPC * (Gm::ROW + (Gm::TWS == 0 && fast_stage_enabled(S) ? Gm::N : 0)) + Gm::TWS) * sizeof(uint32_t);
   auto kernel = chain_fixed_fast_kernel<S, CMODE, LINEAR, EJ>;
   if (!occ) { const rsp_status s = launch_cfg(kernel, smem, Gm::THREADS, &occ, err); if (s != RSP_OK) return s; }
   const unsigned groups = (fa.n_rows + Gm::CPC - 1) / Gm::CPC;
@@ -806,6 +877,7 @@ rsp_status launch_fast_chain(const Plan &pl, const LaunchCtx &ctx, const FxArgs 
   fa.thr_mask = a.thr_w >= 32 ? 0xFFFFFFFFu : ((1u << a.thr_w) - 1u);
   fa.out_mul = (int)(1u << (a.binw + 1)); fa.thr_sext = 32 - a.thr_w;
   fa.det_list = a.det_list; fa.det_count = a.det_count; fa.det_cap = a.det_cap;
+  fa.stage = (pl.S < RSP_FAST_TWSMEM_S && fast_stage_enabled(pl.S) && (reinterpret_cast<uintptr_t>(a.in) & 15u) == 0) ? 1 : 0;   // rows are N * 4 bytes: the base decides
   const int cmode = a.cfar_mode == 0 ? 0 : (a.cfar_mode == 1 ? 1 : 2);   // MuxLookup default: smallestOf (CFARCoreWithMem.scala:138-141)
   const bool linear = a.log_or_linear != 0;
   if (a.core == CORE_LIS) {
