@@ -229,3 +229,34 @@ def test_generator_matches_oracle_and_c1_chain(cuda, oracle):
             _, bins, peak = decode_cfar_words(got_out, 1024)
             assert n_per_chirp == 3 * 255
             assert peak[0, 32] == 1     # (quantisation-noise bins next to an all-zero window may flag too: threshold 0)
+
+
+def test_fp32_chain_accepts_radix2(cuda, oracle):
+    """sdfRadix = "2" (DIF) in the DspReal flavour: the same FFT(x)/N within 1e-4 of the fp64 dataflow, identical detections, also at a
+    run-time size that drops an odd number of stages (legal for the radix-2 chain only, SDFChainRadix2.scala:127-134); DIT -> unsupported"""
+    n, W, G = 1024, 16, 2
+    p = f32_params(n, W, G)
+    p.fftParams.sdfRadix = "2"
+    for log_n in (10, 9):
+        m = 1 << log_n
+        xc = synth.chirps_complex(5, m, seed=log_n)
+        x32 = np.stack([xc.real, xc.imag], axis=-1).astype(np.float32)
+        xq = x32[..., 0].astype(np.float64) + 1j * x32[..., 1].astype(np.float64)
+        regs = dict(fftWin=m, logOrLinearMode=1, divSum=4, peakGrouping=0, cfarMode=0, windowCells=W, guardCells=G)
+        with R.FftMagCfarChainVanilla(p) as ch:
+            configure(ch, log_n, 2, regs)
+            ch.set_threshold_scaler_f32(3.5)
+            d_thr = cuda.empty((5, m), dtype=cuda.float32, device="cuda")
+            d_mask = cuda.zeros((5, max(1, m // 32)), dtype=cuda.int32, device="cuda")
+            ch.run(cuda.from_numpy(x32).cuda(), 5, 1, out=d_thr, peak_mask=d_mask)
+            cuda.cuda.synchronize()
+            thr = d_thr.cpu().numpy()
+            pk = unpack_mask(d_mask.cpu().numpy().view(np.uint32), m)
+        mag, want_thr, want_pk = f64_chain(oracle, xq, log_n, 2, regs, 3.5, W, G)
+        rel = np.abs(thr - want_thr) / np.maximum(np.abs(want_thr), 1e-3 * np.abs(want_thr).max())
+        assert rel.max() < REL_TOL
+        sure = np.abs(mag - want_thr) / np.maximum(np.abs(want_thr), 1e-30) > 10 * REL_TOL
+        assert (pk[sure] == want_pk[sure]).all()
+    p.fftParams.decimType = R.DITDecimType
+    with pytest.raises(R.RspError):
+        R.FftMagCfarChainVanilla(p)
