@@ -15,7 +15,7 @@ def oracle_cfgs(O, params, log_n, sel, cfar_regs: dict):
     # a run-time size of k stages is the LAST k stages in DIF, the FIRST k in DIT (SDFChainRadix2.scala:127-134,196-203)
     mask = (mask if dit else (mask >> (smax - log_n))) & ((1 << log_n) - 1)
     fft = O.fft_cfg(log_n, f.dataWidth, f.binPoint, f.twiddleWidth, f.trimType, f.use4Muls, f.useBitReverse, mask, f.fftDir,
-                    f.sdfRadix, dit)
+                    f.sdfRadix, dit, smax)
     mag = O.mag_cfg(m.dataWidth, m.binPoint, m.dataWidthLog, m.binPointLog, m.log2LookUpWidth, sel)
     if c.CFARAlgorithm == CACFARType:
         core = O.CORE_ASR if c.includeCASH else O.CORE_MEM

@@ -39,7 +39,7 @@ class FftCfg(C.Structure):
     _fields_ = [("log_n", C.c_int32), ("data_width", C.c_int32), ("bin_point", C.c_int32),
                 ("twiddle_width", C.c_int32), ("trim_type", C.c_int32), ("use4muls", C.c_int32),
                 ("bit_reverse", C.c_int32), ("keep_msb_mask", C.c_uint32), ("fft_dir", C.c_int32),
-                ("sdf_radix", C.c_int32), ("decim_dit", C.c_int32)]
+                ("sdf_radix", C.c_int32), ("decim_dit", C.c_int32), ("num_stages", C.c_int32)]
 
 
 class MagCfg(C.Structure):
@@ -119,11 +119,11 @@ def _f64(a):
 # ---------------------------------------------------------------------------------------------- configs
 
 def fft_cfg(log_n, data_width=16, bin_point=14, twiddle_width=16, trim="RoundHalfUp", use4muls=False,
-            bit_reverse=True, keep_msb_mask=0xFFFFFFFF, fft_dir=True, sdf_radix="2^2", decim_dit=False) -> FftCfg:
+            bit_reverse=True, keep_msb_mask=0xFFFFFFFF, fft_dir=True, sdf_radix="2^2", decim_dit=False, num_stages=0) -> FftCfg:
     """sdf_radix "2" selects SDFChainRadix2 (DIF or DIT); "2^2" SDFChainRadix22 (DIF only)"""
     return FftCfg(log_n, data_width, bin_point, twiddle_width, TRIM[trim] if isinstance(trim, str) else trim,
                   int(use4muls), int(bit_reverse), keep_msb_mask & 0xFFFFFFFF, int(fft_dir),
-                  2 if str(sdf_radix) == "2" else 4, int(decim_dit))
+                  2 if str(sdf_radix) == "2" else 4, int(decim_dit), int(num_stages))
 
 
 def mag_cfg(data_width=16, bin_point=14, data_width_log=16, bin_point_log=9, log2_lookup_width=9, sel=2,

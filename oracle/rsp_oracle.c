@@ -178,6 +178,16 @@ static int fft_tabs_build(fft_tabs *t, const rspo_fft_cfg *cfg) {
     }
     return 0;
   }
+  if (cfg->decim_dit) { /* DIT: stageN = 2 << (index + 1) (SDFChainRadix22.scala:228); slot = index */
+    for (int i = 1; i < S; ++i) {
+      const int stage_n = 4 << i;
+      t->re[i] = (int32_t *)malloc(sizeof(int32_t) * (size_t)stage_n);
+      t->im[i] = (int32_t *)malloc(sizeof(int32_t) * (size_t)stage_n);
+      if (!t->re[i] || !t->im[i]) { fft_tabs_free(t); return -2; }
+      rspo_twiddle_table(stage_n, tw, t->re[i], t->im[i]);
+    }
+    return 0;
+  }
   for (int i = 1; i < S - 1; i += 2) {
     const int stage_n = 4 << (S - 1 - i); /* 2 << (numStages - index) (SDFChainRadix22.scala:228) */
     t->re[i] = (int32_t *)malloc(sizeof(int32_t) * (size_t)stage_n);
@@ -244,13 +254,73 @@ static int fft_fixed_core_radix2(const rspo_fft_cfg *cfg, const fft_tabs *tabs, 
   return 0;
 }
 
+/* radix-2^2 SDF chain, DIT (SDFChainRadix22.scala:27,224-352 with decimType = DITDecimType).
+ * Delays 1, 2, .. N/2 (:27), bit-reversed input, natural output (SDFFFT.scala:140-170: with useBitReverse the ping-pong buffer
+ * sits in front).  What precedes the butterfly of stage `index` (delay D = 2^index) is decided by position alone:
+ *   index 0: nothing (doNothing, :227);
+ *   isMulTw (:229: index + 1 even when numStages is odd, odd when numStages is even -- numStages is the COMPILE-TIME stage count):
+ *     the input at position p is multiplied by twiddle [0]*D ++ [2k] ++ [k] ++ [3k] (p mod 4D), stageN = 4D (:228,255-259,282-284),
+ *     `stg_in context_* twiddles` under params.trimType, then trimBinary(bpos) (:298-308,314-316);
+ *   otherwise: x(-j) on positions [3D/2, 2D) of every 2D block (:323,339-342).
+ * Butterfly / div2 / keep-LSB as in every stage (:459-493).  A run-time size of k stages is the first k stages (:145-147,216-217). */
+static int fft_fixed_core_r22_dit(const rspo_fft_cfg *cfg, const fft_tabs *tabs, int64_t *xr, int64_t *xi,
+                                  const int32_t *in_re, const int32_t *in_im, int32_t *out_re, int32_t *out_im) {
+  const int S = cfg->log_n, N = 1 << S;
+  const int w = cfg->data_width, bp = cfg->bin_point, tw = cfg->twiddle_width, trim = cfg->trim_type;
+  const int smax = cfg->num_stages > 0 ? cfg->num_stages : S;
+  for (int p = 0; p < N; ++p) {
+    const int src = cfg->bit_reverse ? (int)bitrev((uint32_t)p, S) : p;
+    xr[p] = rspo_wrap(cfg->fft_dir ? in_re[src] : in_im[src], w);
+    xi[p] = rspo_wrap(cfg->fft_dir ? in_im[src] : in_re[src], w);
+  }
+  for (int i = 0; i < S; ++i) {
+    const int D = 1 << i;
+    const int scale = (cfg->keep_msb_mask >> i) & 1;
+    const int is_tw = i > 0 && (((i + 1) % 2 == 0 && smax % 2 == 1) || ((i + 1) % 2 == 1 && smax % 2 == 0));
+    if (is_tw) {
+      const int stage_n = 4 * D;
+      const int32_t *tr = tabs->re[i], *ti = tabs->im[i];
+      for (int p = 0; p < N; ++p) {
+        const int t = tw_index(p % stage_n, D);
+        cmul_fixed(xr[p], xi[p], tr[t], ti[t], bp, tw - 2, trim, cfg->use4muls, w, &xr[p], &xi[p]);
+      }
+    } else if (i > 0) {
+      for (int b = 0; b < N; b += 2 * D)
+        for (int k = 3 * D / 2; k < 2 * D; ++k) {
+          const int p = b + k;
+          const int64_t r = xr[p], im = xi[p];
+          xr[p] = im;
+          xi[p] = rspo_wrap(-r, w);
+        }
+    }
+    for (int b = 0; b < N; b += 2 * D)
+      for (int k = 0; k < D; ++k) {
+        const int p0 = b + k, p1 = b + k + D;
+        const int64_t sr = xr[p0] + xr[p1], si = xi[p0] + xi[p1];
+        const int64_t dr = xr[p0] - xr[p1], di = xi[p0] - xi[p1];
+        if (scale) {
+          xr[p0] = rspo_wrap(rspo_trim(sr, 1, trim), w); xi[p0] = rspo_wrap(rspo_trim(si, 1, trim), w);
+          xr[p1] = rspo_wrap(rspo_trim(dr, 1, trim), w); xi[p1] = rspo_wrap(rspo_trim(di, 1, trim), w);
+        } else {
+          xr[p0] = rspo_wrap(sr, w); xi[p0] = rspo_wrap(si, w);
+          xr[p1] = rspo_wrap(dr, w); xi[p1] = rspo_wrap(di, w);
+        }
+      }
+  }
+  for (int n = 0; n < N; ++n) {
+    out_re[n] = (int32_t)(cfg->fft_dir ? xr[n] : xi[n]);
+    out_im[n] = (int32_t)(cfg->fft_dir ? xi[n] : xr[n]);
+  }
+  return 0;
+}
+
 static int fft_fixed_core(const rspo_fft_cfg *cfg, const fft_tabs *tabs, int64_t *xr, int64_t *xi,
                           const int32_t *in_re, const int32_t *in_im, int32_t *out_re, int32_t *out_im) {
   const int S = cfg->log_n;
   const int N = 1 << S;
   const int w = cfg->data_width, bp = cfg->bin_point, tw = cfg->twiddle_width, trim = cfg->trim_type;
   if (cfg->sdf_radix == 2) return fft_fixed_core_radix2(cfg, tabs, xr, xi, in_re, in_im, out_re, out_im);
-  if (cfg->decim_dit) return -1; /* radix-2^2 DIT is not restated */
+  if (cfg->decim_dit) return fft_fixed_core_r22_dit(cfg, tabs, xr, xi, in_re, in_im, out_re, out_im);
   for (int p = 0; p < N; ++p) {
     /* ifft swaps real and imaginary on the way in (SDFChainRadix22.scala:205-211) */
     xr[p] = rspo_wrap(cfg->fft_dir ? in_re[p] : in_im[p], w);

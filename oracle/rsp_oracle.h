@@ -52,7 +52,9 @@ typedef struct {
   uint32_t keep_msb_mask; /* bit i = keepMSBorLSB(i) for stage i of THIS transform (1 = scale, 0 = keep LSB / wrap) */
   int32_t fft_dir;        /* 1 = FFT, 0 = IFFT (SDFChainRadix22.scala:205-211,362-383)        */
   int32_t sdf_radix;      /* 2 = sdfRadix "2" (SDFChainRadix2.scala); 0 or 4 = "2^2"          */
-  int32_t decim_dit;      /* 1 = DITDecimType (radix 2 only), 0 = DIFDecimType                */
+  int32_t decim_dit;      /* 1 = DITDecimType, 0 = DIFDecimType                               */
+  int32_t num_stages;     /* log2(numPoints) of the ELABORATED chain (radix-2^2 DIT: which stages carry twiddles depends on its
+                             parity, SDFChainRadix22.scala:229); 0 = same as log_n                                        */
 } rspo_fft_cfg;
 
 /* MAGParams (generators/logMagMux/src/main/scala/LogMagMux.scala:14-49) + run-time sel */

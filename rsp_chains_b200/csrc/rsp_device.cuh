@@ -48,6 +48,7 @@ struct FxArgs {
   // FFT
   int data_width, bp, tw_bp, trim, use4muls, bitrev, fft_dir;   // bitrev: the result is stored at the bit-reversed index
   int radix2, dit, load_rev;   // sdfRadix "2" (SDFChainRadix2.scala), DITDecimType, beats arrive in bit-reversed order (DIT without useBitReverse)
+  int dit_tw_par;              // radix-2^2 DIT: stage i > 0 carries the twiddle multiplier iff (i + dit_tw_par) is even, else the x(-j)
   uint32_t keep_mask;       // bit i: stage i of THIS transform scales (1) or keeps LSBs (0)
   const uint32_t *tw;       // packed (cos16 << 16 | sin16) twiddles, per stageN three runs [W^2k | W^k | W^3k]
   int tw_off[16];           // word offset of the table of stageN = 1 << L
@@ -223,6 +224,28 @@ RSP_HD void cmul_r2(const FxArgs &a, int &xr, int &xi, uint32_t tw) {
   xi = wrapw(trim_rt<int>(ar * bi + ai * br, a.tw_bp, a.trim), a.data_width);
 }
 
+// The MODE_RADIX2 kernels (three stage structures x every trim type, unrolled 16 points deep) call the two products out of line:
+// they are parity paths, and inlining both products into every unrolled point made their compile units the longest of the build.
+#if defined(__CUDACC__)
+static __device__ __noinline__ int2 cmul_r2_call(int xr, int xi, uint32_t tw, int tw_bp, int trim, int data_width) {
+  FxArgs a;
+  a.tw_bp = tw_bp; a.trim = trim; a.data_width = data_width;
+  cmul_r2(a, xr, xi, tw);
+  return make_int2(xr, xi);
+}
+static __device__ __noinline__ int2 cmul_generic_call(int xr, int xi, uint32_t tw, int bp, int tw_bp, int trim, int use4muls, int data_width) {
+  FxArgs a;
+  a.bp = bp; a.tw_bp = tw_bp; a.trim = trim; a.use4muls = use4muls; a.data_width = data_width;
+  cmul<MODE_GENERIC>(a, xr, xi, tw);
+  return make_int2(xr, xi);
+}
+#define RSP_CMUL_R2(a, re, im, tw) do { const int2 r_ = cmul_r2_call(re, im, tw, (a).tw_bp, (a).trim, (a).data_width); re = r_.x; im = r_.y; } while (0)
+#define RSP_CMUL_GEN(a, re, im, tw) do { const int2 r_ = cmul_generic_call(re, im, tw, (a).bp, (a).tw_bp, (a).trim, (a).use4muls, (a).data_width); re = r_.x; im = r_.y; } while (0)
+#else
+#define RSP_CMUL_R2(a, re, im, tw) cmul_r2(a, re, im, tw)
+#define RSP_CMUL_GEN(a, re, im, tw) cmul<MODE_GENERIC>(a, re, im, tw)
+#endif
+
 // ------------------------------------------------------------------------------------------------ LogMagMux
 // returns the low half-word value (.imag of the output beat); *out_re is the high half (.real)
 RSP_HD int mag_one(const FxArgs &a, int re, int im, int *out_re) {
@@ -316,14 +339,35 @@ RSP_HD void fft_pass(const FxArgs &a, int tl, const uint32_t *gin, uint32_t *buf
         // apart and multiplies the second one by W_2^(i+1)^k IN FRONT of the butterfly (:321-339), k = bitrev_i(block number).
         // Both ROMs are run 0 ([W^2k], k < stageN/4) of the table of stageN = 4 * delay.
         const uint32_t *tab = a.tw + a.tw_off[a.dit ? i + 2 : S - i + 1];
-        if (a.dit && i > 0) {
+        if (a.dit && i > 0 && a.radix2) {
 #pragma unroll
           for (int rr = 0; rr < R; ++rr)
             if (rr & dist) {
               const int blk = (high << s) | (rr >> (m - s));
               const int k = (int)bitrev_n((uint32_t)blk, i);
-              if (k) cmul_r2(a, re[rr], im[rr], ldg(&tab[k]));
+              if (k) RSP_CMUL_R2(a, re[rr], im[rr], ldg(&tab[k]));
             }
+        } else if (a.dit && i > 0) {
+          // Radix-2^2 DIT (SDFChainRadix22.scala:224-352), same index space: bit b of the reference's position p is bit S-1-b of q.
+          // Twiddle stages multiply EVERY input by [0]*D ++ [2k] ++ [k] ++ [3k] over p mod 4D (quarter = bits i, i+1 of p, k = the
+          // i bits below), the others turn positions [3D/2, 2D) of each 2D block (bits i and i-1 of p set) by -j.
+          const bool is_tw = ((i + a.dit_tw_par) & 1) == 0;
+#pragma unroll
+          for (int rr = 0; rr < R; ++rr) {
+            const int qi = base + rr * Dl;
+            const int b0 = (rr & dist) ? 1 : 0;
+            if (is_tw) {
+              const int b1 = i == S - 1 ? 0 : ((qi >> (S - 2 - i)) & 1);
+              const int quarter = b0 + 2 * b1;
+              if (quarter) {
+                const int k = (int)bitrev_n((uint32_t)(qi >> (S - i)), i);
+                const int slot = quarter == 1 ? 0 : (quarter == 2 ? 1 : 2);
+                RSP_CMUL_GEN(a, re[rr], im[rr], ldg(&tab[(slot << i) + k]));
+              }
+            } else if (b0 && ((qi >> (S - i)) & 1)) {
+              mul_mj<MODE>(a, re[rr], im[rr]);
+            }
+          }
         }
 #pragma unroll
         for (int rr = 0; rr < R; ++rr)
@@ -333,7 +377,7 @@ RSP_HD void fft_pass(const FxArgs &a, int tl, const uint32_t *gin, uint32_t *buf
           for (int rr = 0; rr < R; ++rr)
             if (rr & dist) {
               const int k = (rr & (dist - 1)) * Dl + low;
-              if (k) cmul_r2(a, re[rr], im[rr], ldg(&tab[k]));
+              if (k) RSP_CMUL_R2(a, re[rr], im[rr], ldg(&tab[k]));
             }
         }
         continue;

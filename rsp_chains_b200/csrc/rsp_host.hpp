@@ -58,8 +58,7 @@ inline rsp_status validate_params(const rsp_chain_params &p, std::string &err) {
   RSP_REQ(f.numPoints >= 2 && f.numPoints <= 16384, RSP_EUNSUPPORTED, "numPoints must be in 2..16384 (one chirp stays resident in shared memory)");
   RSP_REQ(f.sdfRadix == 2 || f.sdfRadix == 4, RSP_EINVAL, "Radix must be 2 or 2^2");   // SDFFFTParams.scala:61-64
   RSP_REQ(f.decimType == 0 || f.decimType == 1, RSP_EINVAL, "decimType must be DIF or DIT");
-  RSP_REQ(f.decimType == 0 || (f.sdfRadix == 2 && p.arith == RSP_ARITH_FIXED), RSP_EUNSUPPORTED,
-          "DITDecimType is built for the fixed-point radix-2 chain only");
+  RSP_REQ(f.decimType == 0 || p.arith == RSP_ARITH_FIXED, RSP_EUNSUPPORTED, "DITDecimType is built for the fixed-point chains only");
   RSP_REQ(!f.expandLogicAny, RSP_EUNSUPPORTED, "expandLogic (grow) stages are not built");
   RSP_REQ(f.windowFunc >= RSP_WINDOW_NONE && f.windowFunc <= RSP_WINDOW_USER, RSP_EINVAL, "unknown windowFunc");
   RSP_REQ(f.windowFunc == RSP_WINDOW_NONE || (f.windowWidth >= 3 && f.windowWidth <= 16), RSP_EUNSUPPORTED, "window dataWidth must be in 3..16");
@@ -321,13 +320,15 @@ inline rsp_status plan_fixed(const rsp_chain_params &p, const Regs &r, const Tab
   } else {
     S = f.runTime ? (int)r.fft[RSP_FFT_REG_FFTSIZE] : Smax;
     if (S < 1 || S > Smax) { err = "fftSize register must be in 1..log2(numPoints)"; return RSP_EINVAL; }
-    if (f.sdfRadix == 4 && ((Smax - S) & 1)) { err = "radix 2^2 run-time size must drop an even number of stages (Radix22RunTimeSpec.scala:18-19)"; return RSP_EINVAL; }
+    if (f.sdfRadix == 4 && f.decimType == 0 && ((Smax - S) & 1)) { err = "radix 2^2 run-time size must drop an even number of stages (Radix22RunTimeSpec.scala:18-19)"; return RSP_EINVAL; }
   }
   pl.S = S; pl.first_stage = first_stage; pl.last_stage = last_stage;
   a.first_stage = first_stage; a.last_stage = last_stage;
   a.data_width = f.dataWidth; a.bp = f.binPoint; a.tw_bp = f.twiddleWidth - 2; a.trim = f.trimType; a.use4muls = f.use4Muls ? 1 : 0;
   a.radix2 = f.sdfRadix == 2 ? 1 : 0;
-  a.dit = (a.radix2 && f.decimType == 1) ? 1 : 0;
+  a.dit = f.decimType == 1 ? 1 : 0;
+  // radix-2^2 DIT: isMulTw = (index + 1) even for an odd number of elaborated stages, odd for an even one (SDFChainRadix22.scala:229)
+  a.dit_tw_par = (Smax & 1) ? 1 : 0;
   // DIT runs natural-in / bit-reversed-out like DIF (rsp_device.cuh): its result always lands at the bit-reversed index, and
   // without useBitReverse the caller's beats are in bit-reversed order (SDFFFT.scala:217-270)
   a.bitrev = (f.useBitReverse || a.dit) ? 1 : 0;
@@ -361,7 +362,7 @@ inline rsp_status plan_fixed(const rsp_chain_params &p, const Regs &r, const Tab
   const bool common = f.dataWidth == 16 && f.trimType == RSP_TRIM_ROUND_HALF_UP && a.keep_mask == smask && a.fft_dir == 1 &&
                       p.mag.dataWidth == 16;
   pl.mode = MODE_GENERIC;
-  if (a.radix2) { pl.mode = MODE_RADIX2; return RSP_OK; }   // run-time-parameter kernel with the radix-2 stage structure
+  if (a.radix2 || a.dit) { pl.mode = MODE_RADIX2; return RSP_OK; }   // run-time-parameter kernel with the radix-2 stage structure
   if (common && s1 <= 0) pl.mode = MODE_FAST;
   else if (common && s1 >= 1 && !f.use4Muls) pl.mode = MODE_FAST3;
   return RSP_OK;

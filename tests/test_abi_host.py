@@ -84,8 +84,12 @@ def test_requires_and_no_cpu_fallback():
     assert st == _abi.RSP_EINVAL                                                # CFARParams.scala:42
     st, msg = _create(variant(cfar__includeCASH=1, cfar__minSubWindowSize=0))
     assert st == _abi.RSP_EINVAL and "minSubWindowSize" in msg                  # CFARParams.scala:43-44
-    st, msg = _create(variant(fft__decimType=1))
-    assert st == _abi.RSP_EUNSUPPORTED
+    st, msg = _create(variant(fft__expandLogicAny=1))                           # legal in the reference, not built
+    assert st == _abi.RSP_EUNSUPPORTED and "expandLogic" in msg
+    st, msg = _create(variant(fft__decimType=2))
+    assert st == _abi.RSP_EINVAL
+    st, msg = _create(variant(fft__sdfRadix=8))
+    assert st == _abi.RSP_EINVAL and "Radix" in msg                             # SDFFFTParams.scala:61-64
     st, msg = _create(variant(nco__ditherEnable=1))
     assert st == _abi.RSP_EUNSUPPORTED
     if not torch.cuda.is_available():

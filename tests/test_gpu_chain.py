@@ -418,7 +418,52 @@ def test_radix2_fft_block_variants(cuda, oracle, dit, bp, trim, use4, bitrev, fw
         assert (got == want).all(), f"log_n={log_n}: {(got != want).sum()} beats differ"
 
 
-def test_radix22_dit_is_unsupported(cuda):
-    p = chain_params(256, 0, W=16, G=2, decimType=R.DITDecimType)
-    with pytest.raises(R.RspError):
-        R.FftMagCfarChainVanilla(p)
+@pytest.mark.parametrize("log_n", [1, 2, 3, 4, 6, 7, 9, 10, 11, 12, 14])
+def test_radix22_dit_chain_all_sizes(cuda, oracle, log_n):
+    """sdfRadix = "2^2" with DITDecimType (SDFChainRadix22.scala:224-352): even and odd stage counts (the twiddle stages swap parity),
+    full-range random beats, whole chain and FFT block alone"""
+    n = 1 << log_n
+    beats = synth.random_beats(21 if log_n < 13 else 4, n, seed=400 + log_n)
+    W, G = max(2, min(16, n // 8)), 1
+    p = chain_params(n, 0, W=W, G=G, decimType=R.DITDecimType)
+    if n > 2 * W + 2 * G + 1:
+        regs = dict(fftWin=n, thresholdScaler=3, logOrLinearMode=1, divSum=max(0, W.bit_length() - 1), peakGrouping=1, cfarMode=2,
+                    windowCells=W, guardCells=G)
+        run_and_compare(cuda, oracle, p, log_n, 2, regs, beats)
+    fft, _, _ = oracle_cfgs(oracle, p, log_n, 2, {})
+    with R.FftMagCfarChainVanilla(p) as ch:
+        ch.memWriteWord(p.fftAddress.base, log_n)
+        d_in = to_dev(cuda, beats)
+        d_f = cuda.empty_like(d_in)
+        ch.fft(d_in, beats.shape[0], d_f)
+        cuda.cuda.synchronize()
+        if n > 2 * W + 2 * G + 1:
+            assert "radix22-dit" in ch.variant
+        assert (from_dev_u32(d_f) == oracle.fft_fixed_words(fft, beats)).all()
+
+
+@pytest.mark.parametrize("numpoints", [1024, 2048])
+@pytest.mark.parametrize("bp,trim,use4,bitrev,fwd,keep", [
+    (14, "Convergent", False, True, True, None), (12, "RoundDown", True, False, True, None), (0, "RoundHalfUp", False, False, False, None),
+    (12, "RoundHalfToOdd", False, True, True, 0b1011011101), (9, "RoundTowardsZero", False, True, False, 0b0000011111)])
+def test_radix22_dit_fft_block_variants(cuda, oracle, numpoints, bp, trim, use4, bitrev, fwd, keep):
+    """radix-2^2 DIT FFT block: binary points (3-multiplier per-product trim and use4Muls), trim types, bit-reversed input without the
+    ping-pong buffer, IFFT, keep-LSB stages, run-time sizes = the FIRST k stages, any k, for an even and an odd elaborated stage count"""
+    smax = numpoints.bit_length() - 1
+    kw = dict(decimType=R.DITDecimType, use4Muls=use4, fftDir=fwd)
+    if keep is not None:
+        kw["keepMSBorLSB"] = [bool((keep >> i) & 1) for i in range(smax)]
+    p = chain_params(numpoints, bp, trim, **kw)
+    p.fftParams.useBitReverse = bitrev
+    for log_n in (smax, smax - 1, 6, 5, 1):
+        beats = synth.random_beats(7, 1 << log_n, seed=log_n + 11 * bp, full_range=keep is None)
+        fft, _, _ = oracle_cfgs(oracle, p, log_n, 2, {})
+        with R.FftMagCfarChainVanilla(p) as ch:
+            ch.memWriteWord(p.fftAddress.base, log_n)
+            d_in = to_dev(cuda, beats)
+            d_f = cuda.empty_like(d_in)
+            ch.fft(d_in, beats.shape[0], d_f)
+            cuda.cuda.synchronize()
+            got = from_dev_u32(d_f)
+        want = oracle.fft_fixed_words(fft, beats)
+        assert (got == want).all(), f"log_n={log_n}: {(got != want).sum()} beats differ"

@@ -191,6 +191,27 @@ def test_fft_radix2_orders_runtime_size_and_ifft(oracle):
         assert max(np.abs(br - sre).max(), np.abs(bi - sim).max()) <= 3
 
 
+@pytest.mark.parametrize("n", [4, 8, 16, 32, 64, 128, 256, 512, 1024])
+def test_fft_radix22_dit_tolerance(oracle, n):
+    """radix 2^2 with DITDecimType (Radix22Spec.scala:31-85 runs both decimation types with testFFT(3, ...) on a real tone;
+    Radix22RandomSpec's recipe added): within t = 3 of fft(x) / N, for an even and an odd elaborated stage count (a run-time size of the
+    first k stages of a chain one stage longer), and equal to DIF within the rounding noise"""
+    log_n = n.bit_length() - 1
+    mask = (1 << log_n) - 1
+    x = real_tone(n, 1.0 / n)
+    re, im = java_rand_signal(oracle, n, 11110)
+    for smax in (log_n, log_n + 1):
+        cfg = oracle.fft_cfg(log_n, 16, 14, 16, "Convergent", False, True, mask, True, "2^2", True, smax)
+        for sr, si in ((x, np.zeros(n)), (re, im)):
+            ore, oim = oracle.fft_fixed(cfg, quantize(sr, 14), quantize(si, 14))
+            want = np.fft.fft(sr + 1j * si) / n * (1 << 14)
+            err = max(np.abs(ore - want.real).max(), np.abs(oim - want.imag).max())
+            assert err <= 7, f"N={n} numStages={smax}: max raw error {err:.2f} LSB"
+    dif = oracle.fft_fixed(oracle.fft_cfg(log_n, 16, 14, 16, "Convergent", False, True, mask, True), quantize(re, 14), quantize(im, 14))
+    dit = oracle.fft_fixed(oracle.fft_cfg(log_n, 16, 14, 16, "Convergent", False, True, mask, True, "2^2", True), quantize(re, 14), quantize(im, 14))
+    assert max(np.abs(dif[0] - dit[0]).max(), np.abs(dif[1] - dit[1]).max()) <= 6
+
+
 def test_radix2_rom_is_run_0_of_the_radix22_table(oracle):
     """W_(2 delay)^k (SDFChainRadix2.scala:300-306) equals W_(4 delay)^(2k) (SDFChainRadix22.scala:262-267) bit for bit: the CUDA
     library reads the radix-2 stage ROMs out of its radix-2^2 tables (rsp_host.hpp build_tables)"""
