@@ -65,7 +65,7 @@ typedef struct {
   int32_t fftDir;           /* 1 = FFT, 0 = IFFT (reset value of the fftDir register)                     */
   int32_t runTime;          /* 1: the fftSize register may select a smaller transform                     */
   uint32_t keepMSBorLSB;    /* bit i = keepMSBorLSB(i): 1 scale by 1/2 with trimType, 0 keep LSBs (wrap)   */
-  int32_t decimType;        /* 0 = DIFDecimType, 1 = DITDecimType (DIT: fixed-point chains only, else RSP_EUNSUPPORTED)  */
+  int32_t decimType;        /* 0 = DIFDecimType, 1 = DITDecimType (either radix, fixed point and fp32)                   */
   int32_t sdfRadix;         /* 4 = "2^2" (SDFChainRadix22.scala), 2 = "2" (SDFChainRadix2.scala)            */
   int32_t expandLogicAny;   /* 1 if any expandLogic(i) != 0 (grow mode -> RSP_EUNSUPPORTED)                */
   int32_t keepMSBorLSBReg;  /* 1: the keepMSBorLSBReg register overrides keepMSBorLSB (FFTBlock.scala:92-93)   */

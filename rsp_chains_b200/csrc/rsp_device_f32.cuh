@@ -21,6 +21,8 @@ struct F32Args {
   uint32_t n_rows, row_base;
   int first_stage, last_stage;
   int bitrev, fft_dir;
+  int load_rev;          // DITDecimType without useBitReverse: the beats arrive in bit-reversed order (SDFFFT.scala:254-270); the DspReal
+                         // DIT chain computes the same FFT(x)/N as the DIF one, so the DIF dataflow serves both
   const F2 *tw;
   int tw_off[16];
   const float *win;      // window coefficients, read when win_on
@@ -74,7 +76,7 @@ RSP_HD void fft_pass_f32(const F32Args &a, int tl, const F2 *gin, F2 *bufA, floa
       const int p = base + rr * Dl;
       F2 v;
       if (first) {
-        v = gin[p];
+        v = gin[a.load_rev ? (int)bitrev_n((uint32_t)p, S) : p];
         if (!a.fft_dir) { const float t = v.x; v.x = v.y; v.y = t; }
         else if (a.win_on) { const float w = a.win[p]; v.x *= w; v.y *= w; }   // SDFFFT.scala:233-234
       }

@@ -373,7 +373,7 @@ static int f32_edge_iters(int S, int W, int G) { const int tpc = (1 << S) / 16; 
 bool fast_f32_chain_supported(const Plan &pl, const F32Args &a) {
   if (pl.first_stage != STAGE_FFT || pl.last_stage != STAGE_CFAR) return false;
   if (pl.S < RSP_FAST_SMIN || pl.S > RSP_FAST_SMAX) return false;
-  if (!a.bitrev || a.fft_dir != 1 || a.sel != 2) return false;
+  if (!a.bitrev || a.load_rev || a.fft_dir != 1 || a.sel != 2) return false;
   if (a.core != CORE_MEM || a.send_cut || a.peak_grouping) return false;
   if (a.G < 1 || a.W < 1 || a.div_sum < 0 || a.div_sum > 30) return false;
   if ((a.W & 15) || a.W > 128) return false;   // the block-of-16 window sums (see the kernel)

@@ -58,7 +58,6 @@ inline rsp_status validate_params(const rsp_chain_params &p, std::string &err) {
   RSP_REQ(f.numPoints >= 2 && f.numPoints <= 16384, RSP_EUNSUPPORTED, "numPoints must be in 2..16384 (one chirp stays resident in shared memory)");
   RSP_REQ(f.sdfRadix == 2 || f.sdfRadix == 4, RSP_EINVAL, "Radix must be 2 or 2^2");   // SDFFFTParams.scala:61-64
   RSP_REQ(f.decimType == 0 || f.decimType == 1, RSP_EINVAL, "decimType must be DIF or DIT");
-  RSP_REQ(f.decimType == 0 || p.arith == RSP_ARITH_FIXED, RSP_EUNSUPPORTED, "DITDecimType is built for the fixed-point chains only");
   RSP_REQ(!f.expandLogicAny, RSP_EUNSUPPORTED, "expandLogic (grow) stages are not built");
   RSP_REQ(f.windowFunc >= RSP_WINDOW_NONE && f.windowFunc <= RSP_WINDOW_USER, RSP_EINVAL, "unknown windowFunc");
   RSP_REQ(f.windowFunc == RSP_WINDOW_NONE || (f.windowWidth >= 3 && f.windowWidth <= 16), RSP_EUNSUPPORTED, "window dataWidth must be in 3..16");
@@ -384,7 +383,9 @@ inline rsp_status plan_f32(const rsp_chain_params &p, const Regs &r, const Table
   }
   pl.S = S; pl.mode = 0; pl.first_stage = first_stage; pl.last_stage = last_stage;
   a.first_stage = first_stage; a.last_stage = last_stage;
-  a.bitrev = f.useBitReverse ? 1 : 0;
+  // DIT (either radix): natural output always; bit-reversed input unless the ping-pong buffer is elaborated in front
+  a.bitrev = (f.useBitReverse || f.decimType == 1) ? 1 : 0;
+  a.load_rev = (f.decimType == 1 && !f.useBitReverse) ? 1 : 0;
   a.fft_dir = f.fftDirReg ? (int)(r.fft[RSP_FFT_REG_FFTDIR] & 1u) : (f.fftDir ? 1 : 0);
   for (int L = 0; L < 16; ++L) a.tw_off[L] = t.tw_off[L];
   a.win_on = (first_stage == STAGE_FFT && f.windowFunc != RSP_WINDOW_NONE && a.fft_dir == 1) ? 1 : 0;

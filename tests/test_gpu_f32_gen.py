@@ -257,6 +257,26 @@ def test_fp32_chain_accepts_radix2(cuda, oracle):
         assert rel.max() < REL_TOL
         sure = np.abs(mag - want_thr) / np.maximum(np.abs(want_thr), 1e-30) > 10 * REL_TOL
         assert (pk[sure] == want_pk[sure]).all()
-    p.fftParams.decimType = R.DITDecimType
-    with pytest.raises(R.RspError):
-        R.FftMagCfarChainVanilla(p)
+
+
+@pytest.mark.parametrize("radix", ["2", "2^2"])
+def test_fp32_dit_orders(cuda, oracle, radix):
+    """DITDecimType in the DspReal flavour: same FFT(x)/N; with useBitReverse natural in / natural out (fast kernel), without it the
+    beats arrive bit-reversed and the bins leave in natural order (SDFFFT.scala:217-270)"""
+    n, log_n = 2048, 11
+    rev = np.array([int(format(i, f"0{log_n}b")[::-1], 2) for i in range(n)])
+    xc = synth.chirps_complex(4, n, seed=21)
+    x32 = np.stack([xc.real, xc.imag], axis=-1).astype(np.float32)
+    want = np.fft.fft(x32[..., 0].astype(np.float64) + 1j * x32[..., 1].astype(np.float64), axis=1) / n
+    for use_br in (True, False):
+        p = f32_params(n, 32, 4)
+        p.fftParams.sdfRadix, p.fftParams.decimType, p.fftParams.useBitReverse = radix, R.DITDecimType, use_br
+        with R.FftMagCfarChainVanilla(p) as ch:
+            ch.memWriteWord(p.fftAddress.base, log_n)
+            d_in = cuda.from_numpy(np.ascontiguousarray(x32 if use_br else x32[:, rev])).cuda()
+            d_out = cuda.empty_like(d_in)
+            ch.fft(d_in, 4, d_out)
+            cuda.cuda.synchronize()
+            got = d_out.cpu().numpy().astype(np.float64)
+        err = np.abs((got[..., 0] + 1j * got[..., 1]) - want).max() / np.abs(want).max()
+        assert err < REL_TOL, f"useBitReverse={use_br}: {err:.2e}"
