@@ -90,14 +90,40 @@ __global__ void __launch_bounds__(256) mag_f32_kernel(const F32Args a, unsigned 
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
-// PLFG -> NCO: one sample per thread-iteration, evaluated in closed form from the flattened segment list
+// PLFG -> NCO: a thread produces runs of 8 consecutive samples (closed form for the first, recurrences for the rest, rsp_device_gen.cuh)
+// and stores them as two 16-byte words when the buffers allow: a warp writes 1 KB contiguous per run
 __global__ void __launch_bounds__(256) generator_kernel(const GenArgs g, unsigned long long n_samples, uint32_t *nco_out, int32_t *plfg_out) {
-  const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
-  for (unsigned long long k = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; k < n_samples; k += stride) {
-    int v;
-    const uint32_t beat = gen_sample(g, k, &v);
-    if (nco_out) nco_out[k] = beat;
-    if (plfg_out) plfg_out[k] = v;
+  constexpr int V = 8;
+  const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x * V;
+  const bool vec = ((reinterpret_cast<uintptr_t>(nco_out) | reinterpret_cast<uintptr_t>(plfg_out)) & 15u) == 0;
+  for (unsigned long long k0 = ((unsigned long long)blockIdx.x * blockDim.x + threadIdx.x) * V; k0 < n_samples; k0 += stride) {
+    uint32_t beat[V];
+    int val[V];
+    GenState st;
+    gen_start(g, k0, st);
+    beat[0] = gen_beat(g, st, &val[0]);
+#pragma unroll
+    for (int j = 1; j < V; ++j) {
+      gen_next(g, k0 + j, st);          // past the end of the request: computed, never stored
+      beat[j] = gen_beat(g, st, &val[j]);
+    }
+    if (vec && k0 + V <= n_samples) {
+      if (nco_out) {
+        *reinterpret_cast<uint4 *>(nco_out + k0) = make_uint4(beat[0], beat[1], beat[2], beat[3]);
+        *reinterpret_cast<uint4 *>(nco_out + k0 + 4) = make_uint4(beat[4], beat[5], beat[6], beat[7]);
+      }
+      if (plfg_out) {
+        *reinterpret_cast<int4 *>(plfg_out + k0) = make_int4(val[0], val[1], val[2], val[3]);
+        *reinterpret_cast<int4 *>(plfg_out + k0 + 4) = make_int4(val[4], val[5], val[6], val[7]);
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < V; ++j)
+        if (k0 + j < n_samples) {
+          if (nco_out) nco_out[k0 + j] = beat[j];
+          if (plfg_out) plfg_out[k0 + j] = val[j];
+        }
+    }
   }
 }
 
@@ -404,7 +430,7 @@ extern "C" rsp_status rsp_generate(rsp_chain *c, uint64_t n_samples, uint32_t *d
   GenArgs g;
   const rsp_status s = prepare_generator(c, n_samples, g, st);
   if (s != RSP_OK) return s;
-  generator_kernel<<<ew_grid(c, n_samples), 256, 0, st>>>(g, n_samples, d_nco_out, d_plfg_out);
+  generator_kernel<<<ew_grid(c, (n_samples + 7) / 8), 256, 0, st>>>(g, n_samples, d_nco_out, d_plfg_out);
   CUDA_TRY(cudaGetLastError());
   ++c->launches;
   return RSP_OK;

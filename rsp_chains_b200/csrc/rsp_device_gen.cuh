@@ -83,4 +83,46 @@ RSP_HD uint32_t gen_sample(const GenArgs &g, unsigned long long k, int *plfg_val
   return nco_lookup(g, (phase + g.poff) & pmask);
 }
 
+// Running form for a thread that produces consecutive samples: the first one in closed form (gen_start), the following ones by
+// the recurrences value += step, accumulator += value while the segment lasts (gen_next), all modulo 2^32, which contains the
+// moduli 2^outputWidth and 2^phaseWidth (phaseWidth <= outputWidth <= 16); a sample that opens a new segment (or period) is
+// evaluated in closed form again.  Same bits as gen_sample, without its 64-bit division and segment search per sample.
+struct GenState {
+  uint32_t left;      // samples of the current segment after this one
+  uint32_t v;         // PLFG value of this sample, unwrapped (mod 2^32)
+  uint32_t acc;       // NCO accumulator including this sample (mod 2^32)
+  uint32_t step;      // 0 in constant segments
+};
+
+RSP_HD void gen_start(const GenArgs &g, unsigned long long k, GenState &st) {
+  unsigned long long per;
+  if (((k | g.period_len) >> 32) == 0) per = (uint32_t)k / (uint32_t)g.period_len;   // the common case without the 64-bit division
+  else per = k / g.period_len;
+  k -= per * g.period_len;
+  uint32_t lo = 0, hi = g.n_segs;
+  while (hi - lo > 1) {
+    const uint32_t mid = (lo + hi) >> 1;
+    if (ldg(&g.segs[mid].start) <= k) lo = mid; else hi = mid;
+  }
+  const GenSegment sg = g.segs[lo];
+  const uint32_t q = (uint32_t)(k - sg.start);
+  const bool constant = (sg.flags & 1u) != 0;
+  st.step = constant ? 0u : (uint32_t)sg.step;
+  st.left = sg.n - 1u - q;
+  st.v = (uint32_t)sg.f0 + q * st.step;
+  const uint32_t tri = (uint32_t)(((unsigned long long)q * ((unsigned long long)q + 1ULL)) >> 1);
+  st.acc = sg.phase0 + (uint32_t)per * g.period_phase + (q + 1u) * (uint32_t)sg.f0 + st.step * tri;
+}
+RSP_HD void gen_next(const GenArgs &g, unsigned long long k, GenState &st) {   // k = index of the sample stepped TO
+  if (st.left != 0u) { --st.left; st.v += st.step; st.acc += st.v; }
+  else gen_start(g, k, st);
+}
+RSP_HD uint32_t gen_beat(const GenArgs &g, const GenState &st, int *plfg_value) {
+  const int v = wrapw((int)st.v, g.out_width);
+  *plfg_value = v;
+  const uint32_t pmask = g.phase_width >= 32 ? 0xFFFFFFFFu : ((1u << g.phase_width) - 1u);
+  const uint32_t phase = (g.phase_acc_enable ? st.acc : (uint32_t)v) & pmask;
+  return nco_lookup(g, (phase + g.poff) & pmask);
+}
+
 }  // namespace rsp

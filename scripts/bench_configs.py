@@ -75,6 +75,41 @@ def run_case(name, params, log_n, regs, rows, n_rx, fp32=False, scaler=3.5, dist
     torch.cuda.empty_cache()
 
 
+def run_generator_case(rows, peak):
+    """RspChainVanilla with the PLFG enabled (rsp_run_from_generator: generator kernel -> scratch beats -> fused chain) and the
+    PLFG -> NCO generator alone (rsp_generate, 4 B/sample written): a triangle chirp of three segments, RspChainVanillaApp parameters"""
+    p = R.rsp_chain_vanilla_app_params()
+    n, bb = 1024, p.beatBytes
+    regs = dict(fftWin=n, thresholdScaler=4, logOrLinearMode=1, divSum=5, peakGrouping=0, cfarMode=0, windowCells=32, guardCells=4)
+    segs = [(1, 200, True, False), (2, 180, False, False), (0, 100, False, True)]   # (slope, nSamples, up, reset)
+    W, OW = p.plfgParams.maxNumOfSamplesWidth, p.plfgParams.outputWidthInt
+
+    def ram_word(slope, ns, up, rst):   # {reset, sign, nSamples, slope} (PLFGDspBlockMem.scala:168-178)
+        return (int(rst) << (OW + W + 1)) | (int(up) << (OW + W)) | ((ns & ((1 << W) - 1)) << OW) | (slope & ((1 << OW) - 1))
+
+    with R.RspChainVanilla(p) as ch:
+        ch.configure(10, 2, regs)
+        for i, sg in enumerate(segs):
+            ch.memWriteWord(p.plfgRAM.base + i * bb, ram_word(*sg))
+        seg0 = 6
+        rep0 = seg0 + p.plfgParams.maxChirpOrdinalNum
+        ord0 = rep0 + p.plfgParams.maxNumOfDifferentChirps
+        for idx, v in ((2, 0), (3, 7), (4, 1), (5, 3), (seg0, len(segs)), (rep0, 2), (ord0, 0), (1, 0), (0, 1)):   # as RspChainVanillaTester.scala:86-130
+            ch.memWriteWord(p.plfgAddress.base + idx * bb, v)
+        d_out = torch.empty((rows, n), dtype=torch.int32, device="cuda")
+        d_nco = torch.empty((rows, n), dtype=torch.int32, device="cuda")
+        ms_chain = timed(lambda: ch.run_from_generator(rows, 1, out=d_out))
+        ms_gen = timed(lambda: ch.generate(rows * n, d_nco))
+        variant = ch.variant
+    samples = rows * n
+    for name, ms, bps, var in (("PLFG -> NCO -> chain from the generator (C1 parameters), 2 launches", ms_chain, 12.0, "generator + " + variant),
+                               ("PLFG -> NCO generator alone", ms_gen, 4.0, "generator_kernel")):
+        gbs = samples * bps / (ms * 1e-3) / 1e9
+        print(json.dumps({"config": name, "variant": var, "rows": rows, "n": n, "ms": round(ms, 4), "Msamples_per_s": round(samples / ms / 1e3, 1),
+                          "GBps_algorithmic": round(gbs, 1), "frac_of_measured_hbm_peak": round(gbs / peak, 4), "bytes_per_sample": bps,
+                          "footprint_MiB": round(samples * bps / 2 ** 20, 1)}), flush=True)
+
+
 def main():
     quick = "--quick" in sys.argv
     try:
@@ -98,6 +133,7 @@ def main():
     run_case("C5 8 RX x 4096 x 16384 fixed CA (W64 G8), one frame", fixed_params(16384, 64, 8), 14, ca(16384, 64, 8, 6),
              4096 if quick else 32768, 8, peak=peak)
     run_case("C5 shape fp32 CA, 1/4 frame", f32_params(16384, 64, 8), 14, ca(16384, 64, 8, 6), 8192, 8, fp32=True, bytes_per_sample=12.125, peak=peak)
+    run_generator_case(4096 if quick else 65536, peak)
 
 
 if __name__ == "__main__":
