@@ -90,10 +90,13 @@ __global__ void __launch_bounds__(256) mag_f32_kernel(const F32Args a, unsigned 
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
-// PLFG -> NCO: a thread produces runs of 8 consecutive samples (closed form for the first, recurrences for the rest, rsp_device_gen.cuh)
-// and stores them as two 16-byte words when the buffers allow: a warp writes 1 KB contiguous per run
+#ifndef RSP_GEN_RUN
+#define RSP_GEN_RUN 8
+#endif
+// PLFG -> NCO: a thread produces runs of RSP_GEN_RUN consecutive samples (closed form for the first, recurrences for the rest, rsp_device_gen.cuh)
+// and stores them as 16-byte words when the buffers allow: a warp writes 1 KB contiguous per run (runs of 16 measured slower: 280 vs 328 Gsamples/s)
 __global__ void __launch_bounds__(256) generator_kernel(const GenArgs g, unsigned long long n_samples, uint32_t *nco_out, int32_t *plfg_out) {
-  constexpr int V = 8;
+  constexpr int V = RSP_GEN_RUN;
   const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x * V;
   const bool vec = ((reinterpret_cast<uintptr_t>(nco_out) | reinterpret_cast<uintptr_t>(plfg_out)) & 15u) == 0;
   for (unsigned long long k0 = ((unsigned long long)blockIdx.x * blockDim.x + threadIdx.x) * V; k0 < n_samples; k0 += stride) {
@@ -109,12 +112,12 @@ __global__ void __launch_bounds__(256) generator_kernel(const GenArgs g, unsigne
     }
     if (vec && k0 + V <= n_samples) {
       if (nco_out) {
-        *reinterpret_cast<uint4 *>(nco_out + k0) = make_uint4(beat[0], beat[1], beat[2], beat[3]);
-        *reinterpret_cast<uint4 *>(nco_out + k0 + 4) = make_uint4(beat[4], beat[5], beat[6], beat[7]);
+#pragma unroll
+        for (int j = 0; j < V; j += 4) *reinterpret_cast<uint4 *>(nco_out + k0 + j) = make_uint4(beat[j], beat[j + 1], beat[j + 2], beat[j + 3]);
       }
       if (plfg_out) {
-        *reinterpret_cast<int4 *>(plfg_out + k0) = make_int4(val[0], val[1], val[2], val[3]);
-        *reinterpret_cast<int4 *>(plfg_out + k0 + 4) = make_int4(val[4], val[5], val[6], val[7]);
+#pragma unroll
+        for (int j = 0; j < V; j += 4) *reinterpret_cast<int4 *>(plfg_out + k0 + j) = make_int4(val[j], val[j + 1], val[j + 2], val[j + 3]);
       }
     } else {
 #pragma unroll
@@ -430,7 +433,7 @@ extern "C" rsp_status rsp_generate(rsp_chain *c, uint64_t n_samples, uint32_t *d
   GenArgs g;
   const rsp_status s = prepare_generator(c, n_samples, g, st);
   if (s != RSP_OK) return s;
-  generator_kernel<<<ew_grid(c, (n_samples + 7) / 8), 256, 0, st>>>(g, n_samples, d_nco_out, d_plfg_out);
+  generator_kernel<<<ew_grid(c, (n_samples + RSP_GEN_RUN - 1) / RSP_GEN_RUN), 256, 0, st>>>(g, n_samples, d_nco_out, d_plfg_out);
   CUDA_TRY(cudaGetLastError());
   ++c->launches;
   return RSP_OK;
