@@ -46,6 +46,7 @@ struct rsp_chain {
   F2 *d_twf = nullptr;
   float *d_twf4 = nullptr;
   int32_t *d_log_tab = nullptr, *d_nco_tab = nullptr, *d_win = nullptr, *d_win4 = nullptr;
+  uint32_t *d_nco_full = nullptr;
   float *d_winf = nullptr;
   GenSegment *d_segs = nullptr;
   size_t segs_cap = 0;
@@ -199,7 +200,7 @@ extern "C" void rsp_chain_destroy(rsp_chain *c) {
   cudaSetDevice(c->device);
   free_pipe(c);
   for (int i = 0; i < N_PIPE; ++i) if (c->pipe_stream[i]) cudaStreamDestroy(c->pipe_stream[i]);
-  cudaFree(c->d_tw); cudaFree(c->d_tw2); cudaFree(c->d_twf); cudaFree(c->d_twf4); cudaFree(c->d_win); cudaFree(c->d_win4); cudaFree(c->d_winf); cudaFree(c->d_log_tab); cudaFree(c->d_nco_tab); cudaFree(c->d_segs);
+  cudaFree(c->d_tw); cudaFree(c->d_tw2); cudaFree(c->d_twf); cudaFree(c->d_twf4); cudaFree(c->d_win); cudaFree(c->d_win4); cudaFree(c->d_winf); cudaFree(c->d_log_tab); cudaFree(c->d_nco_tab); cudaFree(c->d_nco_full); cudaFree(c->d_segs);
   cudaFree(c->d_gen_scratch); cudaFree(c->d_det_list); cudaFree(c->d_det_count);
   delete c;
 }
@@ -241,6 +242,7 @@ extern "C" rsp_status rsp_chain_create(const rsp_chain_params *params, int devic
   if (s == RSP_OK) s = upload(c->t.winf, &c->d_winf);
   if (s == RSP_OK) s = upload(c->t.log_tab, &c->d_log_tab);
   if (s == RSP_OK) s = upload(c->t.nco_tab, &c->d_nco_tab);
+  if (s == RSP_OK && !c->t.nco_full.empty()) s = upload(c->t.nco_full, &c->d_nco_full);
   if (s != RSP_OK) { rsp_chain_destroy(c); return s; }
   *out = c;
   return RSP_OK;
@@ -417,6 +419,7 @@ static rsp_status prepare_generator(rsp_chain *c, uint64_t n_samples, GenArgs &g
   g.segs = c->d_segs; g.n_segs = (uint32_t)c->gen_plan.segs.size();
   g.period_len = c->gen_plan.period_len; g.period_phase = c->gen_plan.period_phase;
   g.nco_tab = c->d_nco_tab;
+  g.nco_full = c->d_nco_full;   // null when phaseWidth > 12
   g.table_size = c->p.nco.tableSize; g.addr_bits = log2_ceil((uint32_t)c->p.nco.tableSize);
   g.table_width = c->p.nco.tableWidth; g.phase_width = c->p.nco.phaseWidth;
   g.out_width = c->p.plfg.outputWidthInt + c->p.plfg.outputWidthFrac;

@@ -32,6 +32,8 @@ struct GenArgs {
   unsigned long long period_len;   // samples per period
   uint32_t period_phase;           // accumulator advance per period
   const int32_t *nco_tab;   // tableSize entries, T[i] = round(sin(pi/2 * i/tableSize) * 2^(tableWidth-2))
+  const uint32_t *nco_full; // or null: the beat Cat(cos16, sin16) of EVERY phase word, 2^phaseWidth entries built by the host with
+                            // nco_lookup itself (phaseWidth <= 12): one load instead of two look-ups and the quadrant logic
   int table_size, addr_bits, table_width, phase_width, out_width, phase_acc_enable;
   uint32_t poff;
 };
@@ -122,7 +124,8 @@ RSP_HD uint32_t gen_beat(const GenArgs &g, const GenState &st, int *plfg_value) 
   *plfg_value = v;
   const uint32_t pmask = g.phase_width >= 32 ? 0xFFFFFFFFu : ((1u << g.phase_width) - 1u);
   const uint32_t phase = (g.phase_acc_enable ? st.acc : (uint32_t)v) & pmask;
-  return nco_lookup(g, (phase + g.poff) & pmask);
+  const uint32_t ph = (phase + g.poff) & pmask;
+  return g.nco_full != nullptr ? ldg(&g.nco_full[ph]) : nco_lookup(g, ph);
 }
 
 }  // namespace rsp

@@ -40,6 +40,7 @@ struct Tables {
   int tw_off[16];
   std::vector<int32_t> log_tab;
   std::vector<int32_t> nco_tab;
+  std::vector<uint32_t> nco_full;   // beat of every phase word (GenArgs::nco_full), empty when phaseWidth > 12
   std::vector<int32_t> win;   // window ROM, protoWin raw values (empty: WindowFunctionTypes.None)
   std::vector<int32_t> win4;  // win << (16 - (windowWidth - 2)) for the fast fixed kernels
   std::vector<float> winf;    // the same coefficients as floats (fp32 flavour: protoWin = DspReal)
@@ -239,6 +240,16 @@ inline void build_tables(const rsp_chain_params &p, Tables &t) {
     for (int i = 0; i < p.nco.tableSize; ++i)
       t.nco_tab[(size_t)i] = (int32_t)from_double(std::sin(((double)i * 0.5 * PI) / (double)p.nco.tableSize), p.nco.tableWidth - 2);
   } else t.nco_tab.push_back(0);
+  t.nco_full.clear();
+  if (p.hasGenerator && p.nco.phaseWidth <= 12) {
+    GenArgs g;
+    std::memset(&g, 0, sizeof(g));
+    g.nco_tab = t.nco_tab.data();   // host pointer: nco_lookup is the same code on both sides
+    g.table_size = p.nco.tableSize; g.addr_bits = log2_ceil((uint32_t)p.nco.tableSize);
+    g.table_width = p.nco.tableWidth; g.phase_width = p.nco.phaseWidth;
+    t.nco_full.resize((size_t)1 << p.nco.phaseWidth);
+    for (uint32_t ph = 0; ph < (1u << p.nco.phaseWidth); ++ph) t.nco_full[ph] = nco_lookup(g, ph);
+  }
 }
 
 // window ROM (SDFFFT.scala:53-66): the periodic forms of WindowFunc.scala:41-65 evaluated in double, then
