@@ -15,7 +15,12 @@
  *   - the caller owns every buffer it passes; the handle owns tables, registers and scratch
  *   - device entry points are asynchronous on the given stream (a cudaStream_t passed as void*; NULL = the
  *     legacy default stream); host entry points (rsp_*_host) return after the results are in the host buffer
- *   - a handle is not thread-safe; distinct handles are independent
+ *   - a handle serves ONE thread and ONE stream at a time: its scratch (generator beats, segment list, detection staging,
+ *     the chunk buffers of rsp_run_host) is shared by every call, so two calls of one handle on different streams must be
+ *     ordered by the caller; distinct handles are independent.  A buffer that has to grow is reallocated inside the call
+ *     after a cudaDeviceSynchronize (first call, or a larger batch than any before)
+ *   - every entry point runs on the handle's device and restores the caller's current device before it returns
+ *   - rsp_last_error() points into thread-local storage: copy the text before the thread ends
  *   - parameter checks reproduce the reference's `require`s / `assert`s and return RSP_EINVAL
  *   - there is no CPU fallback: without a CUDA device every compute entry point fails with RSP_ECUDA
  */

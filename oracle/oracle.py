@@ -66,7 +66,8 @@ class PlfgCfg(C.Structure):
                 ("output_width", C.c_int32), ("frame_num", C.c_int32), ("interframe_num_of_samples", C.c_int32),
                 ("different_chirps_num", C.c_int32), ("starting_point", C.c_int32),
                 ("segment_nums", C.POINTER(C.c_uint32)), ("repeated_chirp_nums", C.POINTER(C.c_uint32)),
-                ("chirp_ordinal_nums", C.POINTER(C.c_uint32)), ("ram", C.POINTER(C.c_uint32))]
+                ("chirp_ordinal_nums", C.POINTER(C.c_uint32)), ("ram", C.POINTER(C.c_uint32)),
+                ("output_width_int", C.c_int32), ("pause_model", C.c_int32)]
 
 
 class NcoCfg(C.Structure):
@@ -333,6 +334,8 @@ class Plfg:
     repeated_chirp_nums: list = field(default_factory=list)
     chirp_ordinal_nums: list = field(default_factory=list)
     ram: list = field(default_factory=list)
+    output_width_int: int = 0       # outputWidthInt when outputWidthFrac > 0 (0 = output_width): the RAM word is sliced there
+    pause_model: str = "rtl"        # "rtl": inter - 1 pause samples (PLFGDspBlockMem.scala:242-275); "script": inter (plfg_script.py:50-53)
 
     def run(self, n_out):
         seg = np.ones(self.max_chirp_ordinal_num, np.uint32)
@@ -345,7 +348,8 @@ class Plfg:
         ram[:len(self.ram)] = self.ram
         cfg = PlfgCfg(self.max_num_of_segments, self.max_num_of_samples_width, self.output_width, self.frame_num,
                       self.interframe_num_of_samples, self.different_chirps_num, self.starting_point,
-                      _p(seg, C.c_uint32), _p(rep, C.c_uint32), _p(ordn, C.c_uint32), _p(ram, C.c_uint32))
+                      _p(seg, C.c_uint32), _p(rep, C.c_uint32), _p(ordn, C.c_uint32), _p(ram, C.c_uint32),
+                      self.output_width_int, 1 if self.pause_model == "script" else 0)
         out = np.zeros(n_out, np.int32)
         k = lib().rspo_plfg(C.byref(cfg), _p(out, C.c_int32), C.c_int64(n_out))
         return out[:k]

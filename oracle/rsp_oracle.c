@@ -638,7 +638,7 @@ int rspo_cfar_fixed(const rspo_cfar_cfg *c, const int32_t *x, int64_t *thr_full,
        * (CFARCoreWithLis.scala:191-192, CFARCoreWithASR.scala:326-327). Out-of-chirp cells are defined as 0. */
       const int gfull = (G == c->guard_window_size);
       int64_t left, right;
-      if (G == 0) { left = 0; right = 0; } /* G = 0 substitutes window ends; excluded by CFARParams.scala:41 */
+      if (G == 0) { left = 0; right = 0; } /* the guardCells REGISTER may be 0 on these cores (CFARParams.scala:41 only bounds the compile-time guardWindowSize): the reference then substitutes the window ends (CFARCoreWithLis.scala:191-192, CFARCoreWithASR.scala:326-327); not restated -- the product refuses peakGrouping with guardCells = 0 on the Lis / ASR cores (RSP_EUNSUPPORTED) */
       else {
         left = gfull ? xat(x, N, n + 1) : 0;
         right = (c->core == RSPO_CFAR_CORE_MEM) ? xat(x, N, n + G) : xat(x, N, n - 1);
@@ -844,7 +844,13 @@ int rspo_golden_cfar_cash(const double *sig, int n, int R, int sub, int G, doubl
 
 int64_t rspo_plfg(const rspo_plfg_cfg *c, int32_t *out, int64_t n_out) {
   const int ow = c->output_width, nsw = c->max_num_of_samples_width;
-  const int64_t start = rspo_wrap(c->starting_point, ow); /* startingPoint.asTypeOf(protoOut) */
+  const int owi = c->output_width_int > 0 ? c->output_width_int : ow;  /* field offsets come from outputWidthInt (:161-171) */
+  /* startingPoint is UInt(outputWidthInt.W), slopes is the low outputWidthInt bits of the word: asTypeOf(protoOut) zero-extends both
+   * into the (Int + Frac)-bit output and reads the result as a signed raw value (same width when Frac = 0: plain reinterpretation) */
+  const int64_t start = rspo_wrap((int64_t)((uint64_t)(uint32_t)c->starting_point & ((1ULL << owi) - 1)), ow);
+  /* pause samples between frames: RTL (:242-275) inter - 1, the Python golden (plfg_script.py:50-53) inter */
+  const int64_t pause = c->pause_model == 1 ? c->interframe_num_of_samples
+                                            : (c->interframe_num_of_samples > 1 ? c->interframe_num_of_samples - 1 : 0);
   int64_t cur = start, k = 0;
   for (int64_t frame = 0; c->frame_num == 0 || frame < c->frame_num; ++frame) {
     for (int d = 0; d < (c->different_chirps_num < 1 ? 1 : c->different_chirps_num); ++d) {
@@ -854,10 +860,10 @@ int64_t rspo_plfg(const rspo_plfg_cfg *c, int32_t *out, int64_t n_out) {
         const uint32_t nseg = c->segment_nums[chirp] < 1 ? 1 : c->segment_nums[chirp];
         for (uint32_t seg = 0; seg < nseg; ++seg) {
           const uint64_t wd = c->ram[chirp * (uint32_t)c->max_num_of_segments + seg]; /* r_addr (:383) */
-          const int64_t slope = rspo_wrap((int64_t)(wd & ((1ULL << ow) - 1)), ow);    /* slopes.asTypeOf(protoOut) */
-          uint32_t ns = (uint32_t)((wd >> ow) & ((1ULL << nsw) - 1));
+          const int64_t slope = rspo_wrap((int64_t)(wd & ((1ULL << owi) - 1)), ow);   /* slopes.asTypeOf(protoOut) */
+          uint32_t ns = (uint32_t)((wd >> owi) & ((1ULL << nsw) - 1));
           if (!(ns > 1)) ns += 1;                                                      /* (:175) */
-          const int sign = (int)((wd >> (ow + nsw)) & 1), reset = (int)((wd >> (ow + nsw + 1)) & 1);
+          const int sign = (int)((wd >> (owi + nsw)) & 1), reset = (int)((wd >> (owi + nsw + 1)) & 1);
           for (uint32_t s = 0; s < ns; ++s) {
             if (reset || (seg == 0 && s == 0)) cur = start;                            /* plfg_script.py:46-47 */
             else cur = rspo_wrap(sign ? cur + slope : cur - slope, ow);                /* (:343) */
@@ -867,8 +873,8 @@ int64_t rspo_plfg(const rspo_plfg_cfg *c, int32_t *out, int64_t n_out) {
         }
       }
     }
-    if (c->frame_num == 0 || frame < c->frame_num - 1) { /* inter-frame pause emits startingPoint (plfg_script.py:50-53) */
-      for (int i = 0; i < c->interframe_num_of_samples; ++i) {
+    if (c->frame_num == 0 || frame < c->frame_num - 1) { /* the inter-frame pause emits startingPoint */
+      for (int64_t i = 0; i < pause; ++i) {
         cur = start;
         if (k >= n_out) return k;
         out[k++] = (int32_t)cur;

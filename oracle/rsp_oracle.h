@@ -156,6 +156,12 @@ typedef struct {
   const uint32_t *repeated_chirp_nums; /* [maxNumOfDifferentChirps]   */
   const uint32_t *chirp_ordinal_nums;  /* [maxNumOfDifferentChirps]   */
   const uint32_t *ram;                 /* config RAM words {reset,sign,nSamples,slope} (PLFGDspBlockMem.scala:168-178) */
+  int32_t output_width_int;        /* outputWidthInt: the RAM word is sliced at outputWidthInt (point4, :161-171), the slope field and
+                                      startingPoint are zero-extended into the (Int + Frac)-bit protoOut by asTypeOf; 0 = output_width */
+  int32_t pause_model;             /* inter-frame pause.  0 = the RTL counter tree (:242-275): framePauseCounter starts on the tick of the
+                                      frame's last sample and the frame restarts when fpc + 1 >= interframeNumOfSamples -> inter - 1
+                                      pause samples (none for inter <= 1).  1 = plfg_script.py:50-53 (inter pause samples).  The two
+                                      models of the reference disagree; its value-checked tests use frameNum = 1 only. */
 } rspo_plfg_cfg;
 /* returns number of samples produced (<= n_out); out = raw output_width-bit values, sign-extended */
 int64_t rspo_plfg(const rspo_plfg_cfg *cfg, int32_t *out, int64_t n_out);

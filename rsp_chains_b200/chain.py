@@ -205,6 +205,18 @@ class _Chain:
         _abi.check(self._lib.rsp_run_host(self._h, in_ptr, n_chirps, n_rx, out_ptr or None, mask_ptr or None, None, 0, None))
 
 
+    def run_host_dets_raw(self, in_ptr: int, n_chirps: int, n_rx: int, max_dets: int) -> int:
+        """rsp_run_host with h_out = NULL: the detection list (kept in self.last_detections, a ctypes array reused between calls)
+        is the only result copied back; returns the number of detections found (may exceed max_dets = overflow)"""
+        if getattr(self, "_det_buf_cap", 0) < max_dets:
+            self._det_buf = (_abi.Detection * max(1, max_dets))()
+            self._det_buf_cap = max_dets
+        n_dets = C.c_uint32(0)
+        _abi.check(self._lib.rsp_run_host(self._h, in_ptr, n_chirps, n_rx, None, None, self._det_buf, max_dets, C.byref(n_dets)))
+        self.last_detections = self._det_buf
+        return int(n_dets.value)
+
+
 def host_alloc(nbytes: int, dtype=np.uint32) -> np.ndarray:
     """pinned host memory from rsp_host_alloc as a numpy array (freed with host_free)"""
     p = C.c_void_p()

@@ -24,6 +24,21 @@ static rsp_status fail(rsp_status st, const std::string &msg) { g_last_error = m
     if (e__ != cudaSuccess) return fail(RSP_ECUDA, std::string(#expr) + ": " + cudaGetErrorString(e__));     \
   } while (0)
 
+// Every entry point runs on the handle's device and leaves the caller's current device as it found it (a single-process program
+// with several GPUs, e.g. torch, keeps its own notion of the current device).
+struct DeviceGuard {
+  int prev = -1;
+  cudaError_t err = cudaSuccess;
+  explicit DeviceGuard(int dev) {
+    if (cudaGetDevice(&prev) != cudaSuccess) prev = -1;
+    if (prev != dev) err = cudaSetDevice(dev); else prev = -1;
+  }
+  ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+};
+#define RSP_ON_DEVICE(c)                                                                                     \
+  DeviceGuard dev_guard__((c)->device);                                                                      \
+  if (dev_guard__.err != cudaSuccess) return fail(RSP_ECUDA, std::string("cudaSetDevice: ") + cudaGetErrorString(dev_guard__.err))
+
 static const int N_PIPE = 6;   // most chunks in flight in rsp_run_host (pipe_depth() of them are used)
 // tuning knobs of the host pipeline (defaults measured on B200 / PCIe Gen5, scripts/e2e_sweep.py)
 static int env_int(const char *name, int dflt, int lo, int hi) {
@@ -139,7 +154,7 @@ static rsp_status launch_fixed(rsp_chain *c, const Plan &pl, const FxArgs &a, cu
   if (a.n_rows == 0) return RSP_OK;
   const LaunchCtx ctx = {c->device, c->sm_count};
   const char *err = "";
-  const rsp_status s = (a.out && fast_chain_supported(pl, a)) ? launch_fast_chain(pl, ctx, a, st, &err)
+  const rsp_status s = fast_chain_supported(pl, a) ? launch_fast_chain(pl, ctx, a, st, &err)
                                                    : launch_fixed_inst(pl.mode, pl.S, ctx, a, st, &err);
   if (s != RSP_OK) return fail(s, err);
   ++c->launches;
@@ -197,7 +212,7 @@ static void free_pipe(rsp_chain *c) {
 
 extern "C" void rsp_chain_destroy(rsp_chain *c) {
   if (!c) return;
-  cudaSetDevice(c->device);
+  DeviceGuard guard(c->device);
   free_pipe(c);
   for (int i = 0; i < N_PIPE; ++i) if (c->pipe_stream[i]) cudaStreamDestroy(c->pipe_stream[i]);
   cudaFree(c->d_tw); cudaFree(c->d_tw2); cudaFree(c->d_twf); cudaFree(c->d_twf4); cudaFree(c->d_win); cudaFree(c->d_win4); cudaFree(c->d_winf); cudaFree(c->d_log_tab); cudaFree(c->d_nco_tab); cudaFree(c->d_nco_full); cudaFree(c->d_segs);
@@ -222,7 +237,8 @@ extern "C" rsp_status rsp_chain_create(const rsp_chain_params *params, int devic
   if (cudaGetDeviceCount(&n_dev) != cudaSuccess || n_dev < 1)
     return fail(RSP_ECUDA, "no CUDA device: librsp_b200 has no CPU path");
   if (device < 0 || device >= n_dev) return fail(RSP_EINVAL, "device index out of range");
-  CUDA_TRY(cudaSetDevice(device));
+  DeviceGuard guard(device);
+  if (guard.err != cudaSuccess) return fail(RSP_ECUDA, std::string("cudaSetDevice: ") + cudaGetErrorString(guard.err));
   rsp_chain *c = new (std::nothrow) rsp_chain();
   if (!c) return fail(RSP_ENOMEM, "out of host memory");
   c->p = *params;
@@ -292,7 +308,7 @@ extern "C" rsp_status rsp_fft_window_user(rsp_chain *c, const double *coeffs, ui
   if (!c || !coeffs) return fail(RSP_EINVAL, "null argument");
   if (c->p.fft.windowFunc != RSP_WINDOW_USER) return fail(RSP_EINVAL, "the chain was not created with windowFunc = RSP_WINDOW_USER");
   if (n != (uint32_t)c->p.fft.numPoints) return fail(RSP_EINVAL, "Length of specified window function is not the same as fft size");
-  CUDA_TRY(cudaSetDevice(c->device));
+  RSP_ON_DEVICE(c);
   CUDA_TRY(cudaDeviceSynchronize());   // a kernel in flight may still read the old ROM
   c->t.win_user.assign(coeffs, coeffs + n);
   build_window(c->p, c->t);
@@ -352,26 +368,26 @@ extern "C" rsp_status rsp_run(rsp_chain *c, const void *d_in, uint32_t n_chirps,
   uint32_t rows;
   rsp_status s = rows_of(n_chirps, n_rx, &rows);
   if (s != RSP_OK) return s;
-  CUDA_TRY(cudaSetDevice(c->device));
+  RSP_ON_DEVICE(c);
   return run_stages(c, STAGE_FFT, STAGE_CFAR, d_in, rows, d_out, d_peak_mask, dets, static_cast<cudaStream_t>(stream));
 }
 
 extern "C" rsp_status rsp_fft_run(rsp_chain *c, const void *d_in, uint32_t n_chirps, void *d_out, void *stream) {
   if (!c || !d_in || !d_out) return fail(RSP_EINVAL, "null argument");
-  CUDA_TRY(cudaSetDevice(c->device));
+  RSP_ON_DEVICE(c);
   return run_stages(c, STAGE_FFT, STAGE_FFT, d_in, n_chirps, d_out, nullptr, nullptr, static_cast<cudaStream_t>(stream));
 }
 
 extern "C" rsp_status rsp_cfar_run(rsp_chain *c, const void *d_in, uint32_t n_chirps, void *d_out, uint32_t *d_peak_mask,
                                    const rsp_dets *dets, void *stream) {
   if (!c || !d_in) return fail(RSP_EINVAL, "null argument");
-  CUDA_TRY(cudaSetDevice(c->device));
+  RSP_ON_DEVICE(c);
   return run_stages(c, STAGE_CFAR, STAGE_CFAR, d_in, n_chirps, d_out, d_peak_mask, dets, static_cast<cudaStream_t>(stream));
 }
 
 extern "C" rsp_status rsp_mag_run(rsp_chain *c, const void *d_in, uint64_t n_beats, void *d_out, void *stream) {
   if (!c || !d_in || !d_out) return fail(RSP_EINVAL, "null argument");
-  CUDA_TRY(cudaSetDevice(c->device));
+  RSP_ON_DEVICE(c);
   if (n_beats == 0) return RSP_OK;
   std::string err;
   Plan pl;
@@ -430,7 +446,7 @@ static rsp_status prepare_generator(rsp_chain *c, uint64_t n_samples, GenArgs &g
 
 extern "C" rsp_status rsp_generate(rsp_chain *c, uint64_t n_samples, uint32_t *d_nco_out, int32_t *d_plfg_out, void *stream) {
   if (!c || (!d_nco_out && !d_plfg_out)) return fail(RSP_EINVAL, "null argument");
-  CUDA_TRY(cudaSetDevice(c->device));
+  RSP_ON_DEVICE(c);
   if (n_samples == 0) return RSP_OK;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   GenArgs g;
@@ -449,7 +465,7 @@ extern "C" rsp_status rsp_run_from_generator(rsp_chain *c, uint32_t n_chirps, ui
   uint32_t rows;
   rsp_status s = rows_of(n_chirps, n_rx, &rows);
   if (s != RSP_OK) return s;
-  CUDA_TRY(cudaSetDevice(c->device));
+  RSP_ON_DEVICE(c);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const int S = c->p.fft.runTime ? (int)c->r.fft[RSP_FFT_REG_FFTSIZE] : log2_ceil((uint32_t)c->p.fft.numPoints);
   const uint64_t n_samples = (uint64_t)rows << S;
@@ -510,7 +526,7 @@ extern "C" rsp_status rsp_run_host(rsp_chain *c, const void *h_in, uint32_t n_ch
   uint32_t rows;
   rsp_status s = rows_of(n_chirps, n_rx, &rows);
   if (s != RSP_OK) return s;
-  CUDA_TRY(cudaSetDevice(c->device));
+  RSP_ON_DEVICE(c);
   const bool fixed = c->p.arith == RSP_ARITH_FIXED;
   const int S = c->p.fft.runTime ? (int)c->r.fft[RSP_FFT_REG_FFTSIZE] : log2_ceil((uint32_t)c->p.fft.numPoints);
   if (S < 1 || S > 14) return fail(RSP_EINVAL, "fftSize register out of range");
@@ -631,6 +647,7 @@ extern "C" const char *rsp_variant_name(rsp_chain *c) {
   if (c->p.arith == RSP_ARITH_FIXED) {
     FxArgs a;
     if (plan_fixed(c->p, c->r, c->t, STAGE_FFT, STAGE_CFAR, a, pl, err) != RSP_OK) { c->variant = "invalid: " + err; return c->variant.c_str(); }
+    a.out = reinterpret_cast<uint32_t *>(c);   // any non-null output: the name is that of the full chain with output beats requested
     const char *m = pl.mode == MODE_FAST ? "fast" : (pl.mode == MODE_FAST3 ? "fast3" : (a.radix2 ? (a.dit ? "radix2-dit" : "radix2-dif") : (a.dit ? "radix22-dit" : "generic")));
     if (fast_chain_supported(pl, a)) std::snprintf(buf, sizeof(buf), a.core == CORE_LIS ? "chain_fixed_fast_gos<%d>" : "chain_fixed_fast<%d>", pl.S);
     else std::snprintf(buf, sizeof(buf), "chain_fixed<%d,%s>", pl.S, m);

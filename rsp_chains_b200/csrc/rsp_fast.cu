@@ -62,9 +62,18 @@ template <int S> __host__ __device__ constexpr int fidx(int p) {
 // thread's 16 consecutive bins contiguous and 16-byte aligned; additive over tl + j * TPC.
 template <int S> __host__ __device__ constexpr int mhx(int n) { return n + ((n >> 6) << 3) + (S == 14 ? ((n >> 10) << 3) : 0); }
 
-template <int S> struct FGeo {
+// LP = log2 of the points a thread owns.  16 points everywhere but at N = 16384 (RSP_FAST_LP14, default 5): there 1024 threads x 16
+// points is ONE CTA per SM with every warp in the same phase of the row (issue slots 59 % busy, profiles/r01_i_ncu_full_fx14_kernel.txt);
+// 512 threads x 32 points (the passes stay 4 + 4 + 4 + 2 stages on groups of 16 points, two / eight groups per thread) gives two
+// independent CTAs per SM at the same 64 registers per thread, each with its own barriers, so the rows of an SM drift out of phase.
+#ifndef RSP_FAST_LP14
+#define RSP_FAST_LP14 5
+#endif
+constexpr int fast_lp(int S) { return S == 14 ? RSP_FAST_LP14 : 4; }
+template <int S, int LP = 4> struct FGeo {
   static constexpr int N = 1 << S;
-  static constexpr int PTS = 16;
+  static constexpr int LPTS = LP;
+  static constexpr int PTS = 1 << LP;
   static constexpr int TPC = N / PTS;                        // threads per chirp
 #ifndef RSP_FAST_CTA
 #define RSP_FAST_CTA 128
@@ -138,6 +147,12 @@ __device__ __forceinline__ int imad(int x, int y, int z) { int r; asm("mad.lo.s3
 __device__ __forceinline__ int imad_sub(int x, int y, int z) {   // x * y - z
   int r; asm("{.reg .s32 t; neg.s32 t, %3; mad.lo.s32 %0, %1, %2, t;}" : "=r"(r) : "r"(x), "r"(y), "r"(z)); return r;
 }
+#ifndef RSP_FAST_TW_VOLATILE
+#define RSP_FAST_TW_VOLATILE 0   // A/B knob: 1 = every group of a pass re-reads its twiddles (no values live across groups)
+#endif
+__device__ __forceinline__ int2 ldg_tw_volatile(const int2 *p) {
+  int2 w; asm volatile("ld.global.nc.v2.s32 {%0, %1}, [%2];" : "=r"(w.x), "=r"(w.y) : "l"(p)); return w;
+}
 // rnd = {0x8000, -0x8000, 0x7FFF, -0x7FFF} come from the kernel arguments so that they are constant-bank operands of the IMADs
 // (written as literals the compiler splits them off into VIADDs on the ALU pipe, the pipe that bounds the kernel)
 template <bool TRUE_OUT>
@@ -163,137 +178,164 @@ __device__ __forceinline__ int fjpl(int re, int im) {
   return max(u + (v >> 3), (u - (u >> 3)) + (v >> 1));
 }
 
-// One pass = m radix-2 stages in registers on 2^m points Dl apart (same decomposition as rsp_device.cuh, fx_pass_*).
-// Thread tl of the chirp works on the groups vt = g * TPC + tl, so a warp touches consecutive words in every pass.
+// One pass = m radix-2 stages in registers on 2^m points Dl apart (same decomposition as rsp_device.cuh, fx_pass_*); a thread
+// owns G = PTS >> m such groups per pass.  Thread tl of the chirp works on the groups vt = g * TPC + tl, so a warp touches
+// consecutive words in every pass.  fast_group is ONE group (g is a compile-time value after unrolling).
 // WRAP = false: the row was found "quiet" (see quiet_beats): no value of the transform can reach +-32768, so the 16-bit wrap
 // of the butterfly differences is the identity and its PRMT is left out (13% of the ALU-pipe instructions of the kernel).
-template <int S, int K, bool WRAP, bool TWSM = false>
-__device__ __forceinline__ void fast_pass(const FastArgs &a, int tl, const uint32_t (&pre)[16], uint32_t *xb, uint32_t *xm, const int2 *tws = nullptr) {
-  using Gm = FGeo<S>;
+template <int S, int LP, int K, bool WRAP, bool TWSM = false>
+__device__ __forceinline__ void fast_group(const FastArgs &a, int tl, int g, const uint32_t (&pre)[16], uint32_t *xb, int (&mags)[1 << LP],
+                                           const int2 *tws = nullptr) {
+  using Gm = FGeo<S, LP>;
   constexpr int m = fx_pass_size(S, K), i0 = fx_pass_start(S, K), LDl = S - i0 - m, Dl = 1 << LDl;
-  constexpr int PTS = Gm::PTS, G = PTS >> m, R = 1 << m, TPC = Gm::TPC;
+  constexpr int R = 1 << m, TPC = Gm::TPC;
   constexpr bool first = (K == 0), last = (K == fx_n_passes(S) - 1);
   static_assert((i0 & 1) == 0, "passes start on even stages");
-  int mags[last ? PTS : 1];
-  // exchange-buffer address of point (g, rr) = xf[fidx(g * TPC * R) + fidx(rr * Dl)]: one run-time base per pass, the rest
-  // folds into the instruction's immediate (fidx is additive over these disjoint bit fields)
+  static_assert(!first || m == 4, "the first pass takes 16 beats per group");
+  // exchange-buffer address of point (g, rr) = xf[fidx(group offset) + fidx(rr * Dl)]: one run-time base per pass, the rest
+  // folds into the instruction's immediate (fidx is additive over these disjoint bit fields).  Dl <= TPC: the groups of a thread
+  // are TPC * R points apart and share low = tl mod Dl; Dl > TPC (first pass with 32 points per thread): they are TPC apart and
+  // low = g * TPC + tl.
+  constexpr bool wide = Dl > TPC;
   const int low0 = tl & (Dl - 1);
   uint32_t *xf = xb + fidx<S>(((tl >> LDl) << (m + LDl)) | low0);
+  const int go = fidx<S>(wide ? g * TPC : g * TPC * R);
+  const int klow = wide ? g * TPC : 0;     // compile-time part of low
+  int re[R], im[R];
+  if (last && !first) {   // R consecutive points: 128-bit loads
 #pragma unroll
-  for (int g = 0; g < G; ++g) {
-    const int low = low0;   // (g * TPC + tl) & (Dl - 1): Dl divides TPC
-    const int go = fidx<S>(g * TPC * R);
-    int re[R], im[R];
-    if (last && !first) {   // R consecutive points: 128-bit loads
+    for (int q = 0; q < R / 4; ++q) {
+      const uint4 v = *reinterpret_cast<const uint4 *>(&xf[go + fidx<S>(4 * q)]);
+      const uint32_t wd[4] = {v.x, v.y, v.z, v.w};
 #pragma unroll
-      for (int q = 0; q < R / 4; ++q) {
-        const uint4 v = *reinterpret_cast<const uint4 *>(&xf[go + fidx<S>(4 * q)]);
-        const uint32_t wd[4] = {v.x, v.y, v.z, v.w};
-#pragma unroll
-        for (int k = 0; k < 4; ++k) { re[4 * q + k] = hi16s(wd[k]); im[4 * q + k] = sext16((int)wd[k]); }
-      }
-    } else {
-#pragma unroll
-      for (int rr = 0; rr < R; ++rr) {
-        const uint32_t wd = first ? pre[rr] : xf[go + fidx<S>(rr * Dl)];   // first pass: m = 4, one group, p = tl + rr * TPC
-        re[rr] = hi16s(wd); im[rr] = sext16((int)wd);
-      }
+      for (int k = 0; k < 4; ++k) { re[4 * q + k] = hi16s(wd[k]); im[4 * q + k] = sext16((int)wd[k]); }
     }
-    int sg[R];   // sign each point is held with (compile-time after unrolling): value = sg * register
-#pragma unroll
-    for (int rr = 0; rr < R; ++rr) sg[rr] = 1;
-#pragma unroll
-    for (int s = 0; s < m; ++s) {
-      const int i = i0 + s;
-      const int dist = 1 << (m - 1 - s);
-      const bool rot = (i != S - 1) && ((i & 1) == 0);   // x(-j) on the last quarter of each 4D block follows (SDFChainRadix22.scala:319-337)
-      const bool wrap = WRAP && !(last && s == m - 1);    // the magnitude only takes |d| (|wrap16(32768)| == 32768)
-#pragma unroll
-      for (int rr = 0; rr < R; ++rr)
-        if (!(rr & dist)) {
-          const int rc = rr + dist;
-          const bool mj = rot && (rc & (dist >> 1));      // the difference point is rotated: (re, im) <- (im, -re)
-          fbf1(sg[rr], re[rr], sg[rc], re[rc], mj, wrap, a.one, a.m1);
-          fbf1(sg[rr], im[rr], sg[rc], im[rc], false, wrap, a.one, a.m1);
-          if (mj) { const int t = re[rc]; re[rc] = im[rc]; im[rc] = t; }
-          sg[rr] = -1; sg[rc] = 1;
-        }
-      if (i == S - 1 || rot) continue;
-      const int L = S - i + 1;
-      const int q = 1 << (L - 2);
-      constexpr bool smt = TWSM && first;                      // this pass's tables sit in shared memory: [stageN = N | N / 4]
-      const int2 *tab = smt ? tws + (i == 1 ? 0 : 3 * (Gm::N / 4)) : a.tw + a.tw_off[L];
-#pragma unroll
-      for (int rr = 0; rr < R; ++rr) {
-        const int quarter = ((rr >> (m - 1 - s)) & 1) + 2 * ((rr >> (m - s)) & 1);
-        if (quarter) {
-          const int k = (rr & (dist - 1)) * Dl + low;
-          const int slot = quarter == 1 ? 0 : (quarter == 2 ? 1 : 2);
-          const int2 w = smt ? tab[slot * q + k] : __ldg(&tab[slot * q + k]);
-          if (WRAP || (s == m - 1 && !last)) fcmul<true>(sg[rr], re[rr], im[rr], w, a.m1, a.rnd);
-          else fcmul<false>(sg[rr], re[rr], im[rr], w, a.m1, a.rnd);
-        }
-      }
-    }
-    if (!last) {   // the exchange buffer holds true values: un-negate what is still held negated
-#pragma unroll
-      for (int rr = 0; rr < R; ++rr)
-        if (sg[rr] < 0) { re[rr] = fadd(-1, re[rr], 1, 0, a.one, a.m1); im[rr] = fadd(-1, im[rr], 1, 0, a.one, a.m1); }
-    }
-    if (!last) {
-#pragma unroll
-      for (int rr = 0; rr < R; ++rr) xf[go + fidx<S>(rr * Dl)] = pack2(re[rr], im[rr]);
-    } else {
-#pragma unroll
-      for (int rr = 0; rr < R; ++rr) mags[g * R + rr] = fjpl(re[rr], im[rr]);
-    }
-  }
-  if (last) {
-    // bin of point p = (vt << m) + rr is bitrev_S(p) = rev_m(rr) << (S - m) | rev_{S-4}(tl) << (4 - m) | rev_{4-m}(g):
-    // for a fixed rr the G groups of the thread are G consecutive bins -> one G * 16-bit store per rr
-    const uint32_t rtl = (__brev((uint32_t)tl) >> (32 - (S - 4))) << (4 - m);
-    uint16_t *xm16 = reinterpret_cast<uint16_t *>(xm) + mhx<S>((int)rtl);
+  } else {
 #pragma unroll
     for (int rr = 0; rr < R; ++rr) {
-      const uint32_t rrr = (__brev((uint32_t)rr) >> (32 - m)) << (S - m);   // compile-time
-      const int bin0 = mhx<S>((int)rrr);                                     // mhx is additive over rrr | rtl
-      if (G == 4) {   // groups in bin order: rev2(g) = 0,1,2,3 <- g = 0,2,1,3
-        uint2 v;
-        v.x = __byte_perm((uint32_t)mags[0 * R + rr], (uint32_t)mags[2 * R + rr], 0x5410);
-        v.y = __byte_perm((uint32_t)mags[1 * R + rr], (uint32_t)mags[3 * R + rr], 0x5410);
-        *reinterpret_cast<uint2 *>(&xm16[bin0]) = v;
-      } else if (G == 2) {
-        *reinterpret_cast<uint32_t *>(&xm16[bin0]) = __byte_perm((uint32_t)mags[0 * R + rr], (uint32_t)mags[1 * R + rr], 0x5410);
-      } else {
-        xm16[bin0] = (uint16_t)mags[rr];
+      const uint32_t wd = first ? pre[rr] : xf[go + fidx<S>(rr * Dl)];   // first pass: the group's 16 beats, p = tl + (rr * G + g) * TPC
+      re[rr] = hi16s(wd); im[rr] = sext16((int)wd);
+    }
+  }
+  int sg[R];   // sign each point is held with (compile-time after unrolling): value = sg * register
+#pragma unroll
+  for (int rr = 0; rr < R; ++rr) sg[rr] = 1;
+#pragma unroll
+  for (int s = 0; s < m; ++s) {
+    const int i = i0 + s;
+    const int dist = 1 << (m - 1 - s);
+    const bool rot = (i != S - 1) && ((i & 1) == 0);   // x(-j) on the last quarter of each 4D block follows (SDFChainRadix22.scala:319-337)
+    const bool wrap = WRAP && !(last && s == m - 1);    // the magnitude only takes |d| (|wrap16(32768)| == 32768)
+#pragma unroll
+    for (int rr = 0; rr < R; ++rr)
+      if (!(rr & dist)) {
+        const int rc = rr + dist;
+        const bool mj = rot && (rc & (dist >> 1));      // the difference point is rotated: (re, im) <- (im, -re)
+        fbf1(sg[rr], re[rr], sg[rc], re[rc], mj, wrap, a.one, a.m1);
+        fbf1(sg[rr], im[rr], sg[rc], im[rc], false, wrap, a.one, a.m1);
+        if (mj) { const int t = re[rc]; re[rc] = im[rc]; im[rc] = t; }
+        sg[rr] = -1; sg[rc] = 1;
       }
+    if (i == S - 1 || rot) continue;
+    const int L = S - i + 1;
+    const int q = 1 << (L - 2);
+    constexpr bool smt = TWSM && first;                      // this pass's tables sit in shared memory: [stageN = N | N / 4]
+    const int2 *tab = smt ? tws + (i == 1 ? 0 : 3 * (Gm::N / 4)) : a.tw + a.tw_off[L];
+#pragma unroll
+    for (int rr = 0; rr < R; ++rr) {
+      const int quarter = ((rr >> (m - 1 - s)) & 1) + 2 * ((rr >> (m - s)) & 1);
+      if (quarter) {
+        const int k = (rr & (dist - 1)) * Dl + klow + low0;   // p mod q, q = stageN / 4 = Dl * dist
+        const int slot = quarter == 1 ? 0 : (quarter == 2 ? 1 : 2);
+        // several groups per pass (32 points per thread) use the same twiddles: left to CSE, the compiler keeps all 15 pairs of a
+        // pass live across the groups and spills the row loop's invariants; a volatile load per group re-reads them from L1 instead
+        const int2 w = smt ? tab[slot * q + k] : ((RSP_FAST_TW_VOLATILE && LP > 4 && !first) ? ldg_tw_volatile(&tab[slot * q + k]) : __ldg(&tab[slot * q + k]));
+        if (WRAP || (s == m - 1 && !last)) fcmul<true>(sg[rr], re[rr], im[rr], w, a.m1, a.rnd);
+        else fcmul<false>(sg[rr], re[rr], im[rr], w, a.m1, a.rnd);
+      }
+    }
+  }
+  if (!last) {   // the exchange buffer holds true values: un-negate what is still held negated
+#pragma unroll
+    for (int rr = 0; rr < R; ++rr)
+      if (sg[rr] < 0) { re[rr] = fadd(-1, re[rr], 1, 0, a.one, a.m1); im[rr] = fadd(-1, im[rr], 1, 0, a.one, a.m1); }
+#pragma unroll
+    for (int rr = 0; rr < R; ++rr) xf[go + fidx<S>(rr * Dl)] = pack2(re[rr], im[rr]);
+  } else {
+#pragma unroll
+    for (int rr = 0; rr < R; ++rr) mags[g * R + rr] = fjpl(re[rr], im[rr]);
+  }
+}
+
+// Bit reversal = scatter of the last pass's magnitudes (16 bits each) into the magnitude array.
+// bin of point p = (vt << m) + rr, vt = g * TPC + tl, is bitrev_S(p) = rev_m(rr) << (S - m) | rev_{S-LP}(tl) << (LP - m) | rev_{LP-m}(g):
+// for a fixed rr the G groups of the thread are G consecutive bins -> one G * 16-bit store per rr
+template <int S, int LP>
+__device__ __forceinline__ void fast_scatter(int tl, const int (&mags)[1 << LP], uint32_t *xm) {
+  constexpr int K = fx_n_passes(S) - 1, m = fx_pass_size(S, K), R = 1 << m, G = (1 << LP) >> m;
+  const uint32_t rtl = (__brev((uint32_t)tl) >> (32 - (S - LP))) << (LP - m);
+  uint16_t *xm16 = reinterpret_cast<uint16_t *>(xm) + mhx<S>((int)rtl);
+#pragma unroll
+  for (int rr = 0; rr < R; ++rr) {
+    const uint32_t rrr = (__brev((uint32_t)rr) >> (32 - m)) << (S - m);   // compile-time
+    const int bin0 = mhx<S>((int)rrr);                                     // mhx is additive over rrr | rtl
+    auto pk = [&](int g0, int g1) { return __byte_perm((uint32_t)mags[g0 * R + rr], (uint32_t)mags[g1 * R + rr], 0x5410); };
+    if (G == 8) {          // groups in bin order: rev3(g) = 0..7 <- g = 0,4,2,6,1,5,3,7
+      *reinterpret_cast<uint4 *>(&xm16[bin0]) = make_uint4(pk(0, 4), pk(2, 6), pk(1, 5), pk(3, 7));
+    } else if (G == 4) {   // rev2(g) = 0,1,2,3 <- g = 0,2,1,3
+      *reinterpret_cast<uint2 *>(&xm16[bin0]) = make_uint2(pk(0, 2), pk(1, 3));
+    } else if (G == 2) {
+      *reinterpret_cast<uint32_t *>(&xm16[bin0]) = pk(0, 1);
+    } else {
+      static_assert(G == 8 || G == 4 || G == 2 || G == 1, "groups of the last pass");
+      xm16[bin0] = (uint16_t)mags[rr];
     }
   }
 }
 
-// The thread's 16 beats of a row, p = tl + rr * TPC (warp-contiguous 128-byte lines), times the window when there is one:
-// bits 16..31 of beat * (window << (16 - bp)) are wrap16(floor(beat * window >> bp)), the truncating assignment of
-// SDFFFT.scala:233-234; the windowed beats are packed again so that everything behind (the quiet test too) sees plain beats.
-template <int S> __device__ __forceinline__ void window_beats(const FastArgs &a, int tl, uint32_t (&pre)[16]);
-template <int S>
-__device__ __forceinline__ void load_beats(const FastArgs &a, uint32_t row, int tl, uint32_t (&pre)[16]) {
-  constexpr int N = 1 << S, TPC = FGeo<S>::TPC;
-  const uint32_t *gin = a.in + (size_t)row * N + tl;
+// a whole pass whose groups need no beats from global memory (every pass but the first, and the first one with 16 points per thread)
+template <int S, int LP, int K, bool WRAP, bool TWSM = false>
+__device__ __forceinline__ void fast_pass(const FastArgs &a, int tl, const uint32_t (&pre)[16], uint32_t *xb, uint32_t *xm, const int2 *tws = nullptr) {
+  constexpr int m = fx_pass_size(S, K), G = (1 << LP) >> m;
+  constexpr bool last = (K == fx_n_passes(S) - 1);
+  static_assert(K > 0 || G == 1, "first pass with several groups: fast_first_pass_groups");
+  int mags[1 << LP];
+  // last pass: the groups in the order in which their magnitudes pair up in the scatter's packed words (rev(g) ascending), so that
+  // a pair is packed as soon as it exists instead of 2^LP magnitudes staying live
 #pragma unroll
-  for (int rr = 0; rr < 16; ++rr) pre[rr] = __ldg(&gin[rr * TPC]);
-  window_beats<S>(a, tl, pre);
+  for (int gi = 0; gi < G; ++gi) {
+    const int g = !last ? gi : (G == 8 ? ((gi & 1) << 2 | (gi & 2) | (gi >> 2)) : (G == 4 ? ((gi & 1) << 1 | (gi >> 1)) : gi));
+    fast_group<S, LP, K, WRAP, TWSM>(a, tl, g, pre, xb, mags, tws);
+    // keep the next group's shared-memory loads behind this group's stores: hoisted, 32 points are live and the 64-register
+    // budget spills (the other warps of the SM hide the load latency, not this thread's next group)
+    // (ptxas moves shared-memory accesses with distinct immediate offsets across a compiler-level fence; WARPSYNC holds them)
+    if (!last && gi + 1 < G) __syncwarp();
+  }
+  if (last) fast_scatter<S, LP>(tl, mags, xm);
 }
-template <int S>
-__device__ __forceinline__ void window_beats(const FastArgs &a, int tl, uint32_t (&pre)[16]) {
-  constexpr int TPC = FGeo<S>::TPC;
+
+// Beats j = 0 .. 15 of group g of the thread, p = tl + (j * G + g) * TPC (warp-contiguous 128-byte lines), times the window when
+// there is one: bits 16..31 of beat * (window << (16 - bp)) are wrap16(floor(beat * window >> bp)), the truncating assignment of
+// SDFFFT.scala:233-234; the windowed beats are packed again so that everything behind (the quiet test too) sees plain beats.
+template <int S, int LP>
+__device__ __forceinline__ void window_beats(const FastArgs &a, int tl, int g, uint32_t (&pre)[16]) {
+  constexpr int TPC = FGeo<S, LP>::TPC, G = (1 << LP) / 16;
   if (a.win4 != nullptr) {
-    const int32_t *gw = a.win4 + tl;
+    const int32_t *gw = a.win4 + tl + g * TPC;
 #pragma unroll
     for (int rr = 0; rr < 16; ++rr) {
-      const int w = __ldg(&gw[rr * TPC]);
+      const int w = __ldg(&gw[rr * G * TPC]);
       pre[rr] = __byte_perm((uint32_t)(sext16((int)pre[rr]) * w), (uint32_t)(hi16s(pre[rr]) * w), 0x7632);
     }
   }
+}
+template <int S, int LP>
+__device__ __forceinline__ void load_beats(const FastArgs &a, const uint32_t *grow, int tl, int g, uint32_t (&pre)[16]) {
+  constexpr int TPC = FGeo<S, LP>::TPC, G = (1 << LP) / 16;
+  const uint32_t *gin = grow + tl + g * TPC;
+#pragma unroll
+  for (int rr = 0; rr < 16; ++rr) pre[rr] = __ldg(&gin[rr * G * TPC]);
+  window_beats<S, LP>(a, tl, g, pre);
 }
 
 // Barrier between the phases of a row.  The chirps of a CTA share nothing, so a named barrier per chirp (bar.sync c + 1, TPC)
@@ -315,26 +357,43 @@ __device__ __forceinline__ bool quiet_beats(const uint32_t (&pre)[16]) {
   return __vmins2(mx, lim) == mx && __vmaxs2(mn, nlim) == mn;
 }
 
-// The first pass works on the thread's own 16 beats, so each warp decides for itself; the later passes mix the whole chirp and
-// decide by the chirp's flag, which every warp of the chirp has or-ed into before the barrier that ends the first pass.
-template <int S, int K>
+// The first pass works on the thread's own beats, so each warp decides for itself (per group of 16 beats); the later passes mix
+// the whole chirp and decide by the chirp's flag, which every warp of the chirp has or-ed into before the barrier that ends the
+// first pass.
+template <int S, int LP, int K>
 __device__ __forceinline__ void fast_passes_from(const FastArgs &a, int c, int tl, bool quiet, const uint32_t (&pre)[16], uint32_t *xb, uint32_t *xm) {
-  if (quiet) fast_pass<S, K, false>(a, tl, pre, xb, xm); else fast_pass<S, K, true>(a, tl, pre, xb, xm);
+  if (quiet) fast_pass<S, LP, K, false>(a, tl, pre, xb, xm); else fast_pass<S, LP, K, true>(a, tl, pre, xb, xm);
   chirp_sync<S>(c);
-  if constexpr (K + 1 < fx_n_passes(S)) fast_passes_from<S, K + 1>(a, c, tl, quiet, pre, xb, xm);
+  if constexpr (K + 1 < fx_n_passes(S)) fast_passes_from<S, LP, K + 1>(a, c, tl, quiet, pre, xb, xm);
 }
 
-template <int S, int K, bool TWSM = false>
-__device__ __forceinline__ void fast_passes(const FastArgs &a, int c, int tl, const uint32_t (&pre)[16], uint32_t *xb, uint32_t *xm, int *loud,
-                                            const int2 *tws = nullptr) {
-  static_assert(K == 0 && fx_pass_size(S, 0) == 4, "the first pass takes the 16 prefetched beats of the thread");
-  const bool warp_quiet = __all_sync(0xffffffffu, quiet_beats(pre));
-  if (!warp_quiet && (tl & 31) == 0) loud[c] = 1;
-  if (warp_quiet) fast_pass<S, 0, false, TWSM>(a, tl, pre, xb, xm, tws); else fast_pass<S, 0, true, TWSM>(a, tl, pre, xb, xm, tws);
+// pre: the thread's 16 beats (LP = 4; loaded or staged by the caller).  grow: the row in global memory (LP = 5: each of the two
+// groups of the first pass loads its own 16 beats, so that no more than one group's beats are live at a time).
+template <int S, int LP, bool TWSM = false>
+__device__ __forceinline__ void fast_passes(const FastArgs &a, int c, int tl, uint32_t (&pre)[16], const uint32_t *grow, uint32_t *xb, uint32_t *xm,
+                                            int *loud, const int2 *tws = nullptr) {
+  static_assert(fx_pass_size(S, 0) == 4, "the first pass works on groups of 16 beats");
+  constexpr int G0 = (1 << LP) / 16;
+  if constexpr (G0 == 1) {
+    const bool warp_quiet = __all_sync(0xffffffffu, quiet_beats(pre));
+    if (!warp_quiet && (tl & 31) == 0) loud[c] = 1;
+    if (warp_quiet) fast_pass<S, LP, 0, false, TWSM>(a, tl, pre, xb, xm, tws); else fast_pass<S, LP, 0, true, TWSM>(a, tl, pre, xb, xm, tws);
+  } else {
+    int mags[1 << LP];   // not used by a first pass
+    bool all_quiet = true;
+#pragma unroll
+    for (int g = 0; g < G0; ++g) {
+      load_beats<S, LP>(a, grow, tl, g, pre);
+      const bool warp_quiet = __all_sync(0xffffffffu, quiet_beats(pre));
+      all_quiet = all_quiet && warp_quiet;
+      if (warp_quiet) fast_group<S, LP, 0, false, TWSM>(a, tl, g, pre, xb, mags, tws); else fast_group<S, LP, 0, true, TWSM>(a, tl, g, pre, xb, mags, tws);
+    }
+    if (!all_quiet && (tl & 31) == 0) loud[c] = 1;
+  }
   chirp_sync<S>(c);
   if constexpr (fx_n_passes(S) > 1) {
     const bool quiet = loud[c] == 0;
-    fast_passes_from<S, 1>(a, c, tl, quiet, pre, xb, xm);     // ends with a barrier: every thread has read the flag
+    fast_passes_from<S, LP, 1>(a, c, tl, quiet, pre, xb, xm);     // ends with a barrier: every thread has read the flag
     if (tl == 0) loud[c] = 0;                                 // next written before the first barrier of the next row
   }
 }
@@ -344,9 +403,9 @@ __device__ __forceinline__ void fast_passes(const FastArgs &a, int c, int tl, co
 // lagging sum of bin n = P[n+G+W+1] - P[n+G+1], leading sum = P[n-G] - P[n-G-W].
 
 // exclusive prefix of `total` over the TPC threads of one chirp: warp shuffles, then one shared-memory hop across the warps
-template <int S>
+template <int S, int LP>
 __device__ __forceinline__ int chirp_scan_exclusive(int total, int c, int tl, int *wsum) {
-  constexpr int NW = FGeo<S>::NW;
+  constexpr int NW = FGeo<S, LP>::NW;
   const int lane = tl & 31;
   int incl = total;
 #pragma unroll
@@ -368,10 +427,11 @@ __device__ __forceinline__ int chirp_scan_exclusive(int total, int c, int tl, in
 // Threshold, peak and output beat of bin n = tl + j * TPC; returns the peak bit.  pA..pD point at P[tl + offset] for the four
 // window borders, so every load is [register + immediate].  EDGE: the bin may miss one of its windows (one-sided threshold,
 // CFARCoreWithMem.scala:154-171); the indices are clamped so that no load leaves the chirp's arrays.
-template <int S, int CMODE, bool LINEAR, bool EDGE>
+// !has_out (the caller wants the detection list only): no output beat is built or stored.
+template <int S, int LP, int CMODE, bool LINEAR, bool EDGE>
 __device__ __forceinline__ int fast_cfar_bin(const FastArgs &a, int j, int tl, int n2, const int *P, const int *pA, const int *pB,
-                                             const int *pC, const int *pD, const short *X, uint32_t *gout) {
-  constexpr int N = 1 << S, TPC = FGeo<S>::TPC;
+                                             const int *pC, const int *pD, const short *X, uint32_t *gout, bool has_out) {
+  constexpr int N = 1 << S, TPC = FGeo<S, LP>::TPC;
   const int n = tl + j * TPC;
   int L, R;
   bool lagg_full = true, lead_full = true;
@@ -392,18 +452,20 @@ __device__ __forceinline__ int fast_cfar_bin(const FastArgs &a, int j, int tl, i
   const int cut = X[mhx<S>(j * TPC)];   // X points at the thread's first bin (mhx is additive over tl + j * TPC)
   // peak = cut > thr as the sign bit of thr - cut (|thr| < 2^31 - 2^16 is checked by the host)
   const int pk = (int)((uint32_t)fadd(1, thr, -1, cut, a.one, a.m1) >> 31);
-  const int w0 = (int)(((uint32_t)thr & a.thr_mask) * (uint32_t)a.out_mul + (uint32_t)n2);   // threshold field | bin field (n << 1)
-  gout[n] = (uint32_t)fadd(1, pk, 1, w0, a.one, a.m1);
+  if (has_out) {
+    const int w0 = (int)(((uint32_t)thr & a.thr_mask) * (uint32_t)a.out_mul + (uint32_t)n2);   // threshold field | bin field (n << 1)
+    gout[n] = (uint32_t)fadd(1, pk, 1, w0, a.one, a.m1);
+  }
   return pk;
 }
 
-// detections of one thread: bit (15 - j) of `mask` = peak of bin tl + j * TPC.  Rare path, recomputes from shared memory.
+// detections of one thread: bit (PTS - 1 - j) of `mask` = peak of bin tl + j * TPC.  Rare path, recomputes from shared memory.
 struct FastDetArgs { int W, G, div_sum, scaler, thr_sext;   /* div_sum as in FastArgs */ uint32_t chirp, det_cap; Detection *det_list; uint32_t *det_count; };
-template <int S, int CMODE, bool LINEAR>
+template <int S, int LP, int CMODE, bool LINEAR>
 __device__ __noinline__ void fast_detections(const FastDetArgs a, int tl, uint32_t mask, const int *P, const short *X) {
-  constexpr int N = 1 << S, TPC = FGeo<S>::TPC;
-  for (int j = 0; j < 16; ++j) {
-    if (!((mask >> (15 - j)) & 1u)) continue;
+  constexpr int N = 1 << S, TPC = FGeo<S, LP>::TPC, PTS = 1 << LP;
+  for (int j = 0; j < PTS; ++j) {
+    if (!((mask >> (PTS - 1 - j)) & 1u)) continue;
     const int n = tl + j * TPC, W = a.W, G = a.G;
     const bool lagg_full = (n + G + W <= N - 1), lead_full = (n - G - W >= 0);
     const int hi = min(n + G + W + 1, N), lo = max(n - G - W, 0);
@@ -420,9 +482,9 @@ __device__ __noinline__ void fast_detections(const FastDetArgs a, int tl, uint32
 }
 
 // EJ = number of leading / trailing iterations j whose bins may miss a window (ceil((W + G) / TPC), checked by the host)
-template <int S, int CMODE, bool LINEAR, int EJ>
-__global__ void __launch_bounds__(FGeo<S>::THREADS, 1024 / FGeo<S>::THREADS) chain_fixed_fast_kernel(const FastArgs a) {
-  using Gm = FGeo<S>;
+template <int S, int LP, int CMODE, bool LINEAR, int EJ>
+__global__ void __launch_bounds__(FGeo<S, LP>::THREADS, 1024 / FGeo<S, LP>::THREADS) chain_fixed_fast_kernel(const FastArgs a) {
+  using Gm = FGeo<S, LP>;
   constexpr int N = Gm::N, TPC = Gm::TPC, CPC = Gm::CPC, PTS = Gm::PTS;
   extern __shared__ __align__(16) uint32_t smem[];
   __shared__ int wsum[CPC * Gm::NW];
@@ -435,11 +497,11 @@ __global__ void __launch_bounds__(FGeo<S>::THREADS, 1024 / FGeo<S>::THREADS) cha
   const short *X = reinterpret_cast<const short *>(xm), *Xt = X + mhx<S>(tl);
   const int *pA = P + tl + a.G + a.W + 1, *pB = P + tl + a.G + 1, *pC = P + tl - a.G, *pD = P + tl - a.G - a.W;
   const uint32_t stride = gridDim.x * CPC;
-  // Staging (a.stage): the beats of the CTA's NEXT rows are copied global -> shared by cp.async (4 x 16 bytes per thread, no
-  // registers in flight) once this row's transform is done, and land while its CFAR phase runs; the row loop then starts from
-  // shared memory instead of waiting on HBM with every warp of the CTA at once (at N = 16384 one 1024-thread CTA owns the SM).
+  // Staging (a.stage, 16 points per thread only): the beats of the CTA's NEXT rows are copied global -> shared by cp.async (4 x 16
+  // bytes per thread, no registers in flight) once this row's transform is done, and land while its CFAR phase runs; the row loop
+  // then starts from shared memory instead of waiting on HBM with every warp of the CTA at once.
   uint32_t *stg = smem + (size_t)CPC * Gm::ROW + (size_t)c * N;
-  const bool stage = a.stage != 0;
+  const bool stage = LP == 4 && a.stage != 0;
   constexpr bool TWSM = Gm::TWS > 0;
   const int2 *tws = reinterpret_cast<const int2 *>(smem + (size_t)CPC * Gm::ROW);   // shares the place of the staging area: one or the other
   if (TWSM) {
@@ -463,51 +525,62 @@ __global__ void __launch_bounds__(FGeo<S>::THREADS, 1024 / FGeo<S>::THREADS) cha
   for (uint32_t row0 = blockIdx.x * CPC; row0 < a.n_rows; row0 += stride) {
     const bool active = row0 + c < a.n_rows;
     const uint32_t row = active ? row0 + c : a.n_rows - 1;
-    uint32_t pre[PTS];
-    if (stage) {
+    const uint32_t *grow = a.in + (size_t)row * N;
+    uint32_t pre[16];
+    if (LP == 4) {
+      if (stage) {
 #pragma unroll
-      for (int rr = 0; rr < 16; ++rr) pre[rr] = stg[tl + rr * TPC];
-      window_beats<S>(a, tl, pre);
-    } else load_beats<S>(a, row, tl, pre);
-    fast_passes<S, 0, TWSM>(a, c, tl, pre, xb, xm, loud, tws);
+        for (int rr = 0; rr < 16; ++rr) pre[rr] = stg[tl + rr * TPC];
+        window_beats<S, LP>(a, tl, 0, pre);
+      } else load_beats<S, LP>(a, grow, tl, 0, pre);
+    }
+    fast_passes<S, LP, TWSM>(a, c, tl, pre, grow, xb, xm, loud, tws);
     // every thread is past the first barrier of the passes: the staging area has been read and can take the next rows
     if (stage && row0 + stride < a.n_rows) prefetch(row0 + stride);
-    // prefix sums of the thread's 16 consecutive magnitudes
-    int x[PTS];
-    {
-      const uint32_t *xq = xm + mhx<S>(16 * tl) / 2;   // the thread's 16 consecutive bins
-      const uint4 v0 = *reinterpret_cast<const uint4 *>(xq), v1 = *reinterpret_cast<const uint4 *>(xq + 4);
+    // prefix sums of the thread's PTS consecutive magnitudes, 16 at a time (32 points per thread: the second read of the magnitudes
+    // is cheaper than keeping them in registers across the scan)
+    const uint32_t *xq = xm + mhx<S>(PTS * tl) / 2;   // the thread's PTS consecutive bins (inside one 64-bin block of the padded array)
+    auto load16 = [&](int h, int (&x)[16]) {
+      const uint4 v0 = *reinterpret_cast<const uint4 *>(xq + 8 * h), v1 = *reinterpret_cast<const uint4 *>(xq + 8 * h + 4);
       const uint32_t wd[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
 #pragma unroll
       for (int k = 0; k < 8; ++k) { x[2 * k] = sext16((int)wd[k]); x[2 * k + 1] = hi16s(wd[k]); }
-    }
+    };
+    int x[16];
     int total = 0;
 #pragma unroll
-    for (int k = 0; k < PTS; ++k) total = (int)((uint32_t)x[k] * (uint32_t)a.wmul + (uint32_t)total);   // mod 2^32 on purpose
-    int acc = chirp_scan_exclusive<S>(total, c, tl, wsum);
-    {
-      int pv[PTS];
+    for (int h = 0; h < PTS / 16; ++h) {
+      load16(h, x);
 #pragma unroll
-      for (int k = 0; k < PTS; ++k) { pv[k] = acc; acc = (int)((uint32_t)x[k] * (uint32_t)a.wmul + (uint32_t)acc); }
-#pragma unroll
-      for (int k = 0; k < PTS; k += 4) *reinterpret_cast<int4 *>(&P[tl * PTS + k]) = make_int4(pv[k], pv[k + 1], pv[k + 2], pv[k + 3]);
-      if (tl == TPC - 1) P[N] = acc;
+      for (int k = 0; k < 16; ++k) total = (int)((uint32_t)x[k] * (uint32_t)a.wmul + (uint32_t)total);   // mod 2^32 on purpose
     }
+    int acc = chirp_scan_exclusive<S, LP>(total, c, tl, wsum);
+#pragma unroll
+    for (int h = 0; h < PTS / 16; ++h) {
+      if (PTS > 16) load16(h, x);
+      int pv[16];
+#pragma unroll
+      for (int k = 0; k < 16; ++k) { pv[k] = acc; acc = (int)((uint32_t)x[k] * (uint32_t)a.wmul + (uint32_t)acc); }
+#pragma unroll
+      for (int k = 0; k < 16; k += 4) *reinterpret_cast<int4 *>(&P[tl * PTS + 16 * h + k]) = make_int4(pv[k], pv[k + 1], pv[k + 2], pv[k + 3]);
+    }
+    if (tl == TPC - 1) P[N] = acc;
     chirp_sync<S>(c);
-    uint32_t *gout = a.out + (size_t)row * N;
-    int mask = 0;
+    uint32_t *gout = a.out + (size_t)row * N;   // formed from the kernel argument unconditionally: a select with nullptr would make the stores generic (ST.E)
+    const bool has_out = a.out != nullptr;
+    uint32_t mask = 0;
     int n2 = tl << 1;
 #pragma unroll
     for (int j = 0; j < PTS; ++j) {
       int pk;
-      if (j < EJ || j >= PTS - EJ) pk = fast_cfar_bin<S, CMODE, LINEAR, true>(a, j, tl, n2, P, pA, pB, pC, pD, Xt, gout);
-      else pk = fast_cfar_bin<S, CMODE, LINEAR, false>(a, j, tl, n2, P, pA, pB, pC, pD, Xt, gout);
-      mask = mask * 2 + pk;
+      if (j < EJ || j >= PTS - EJ) pk = fast_cfar_bin<S, LP, CMODE, LINEAR, true>(a, j, tl, n2, P, pA, pB, pC, pD, Xt, gout, has_out);
+      else pk = fast_cfar_bin<S, LP, CMODE, LINEAR, false>(a, j, tl, n2, P, pA, pB, pC, pD, Xt, gout, has_out);
+      mask = mask * 2u + (uint32_t)pk;
       n2 += 2 * TPC;
     }
     if (mask != 0 && a.det_list != nullptr && active) {
       const FastDetArgs da = {a.W, a.G, a.div_sum, a.scaler, a.thr_sext, a.row_base + row, a.det_cap, a.det_list, a.det_count};
-      fast_detections<S, CMODE, LINEAR>(da, tl, (uint32_t)mask, P, X);
+      fast_detections<S, LP, CMODE, LINEAR>(da, tl, mask, P, X);
     }
     if (stage) cp_async_wait_all();   // this thread's copies have landed; the barrier publishes everybody's
     chirp_sync<S>(c);
@@ -728,9 +801,10 @@ __global__ void __launch_bounds__(FGeo<S>::THREADS, 1024 / FGeo<S>::THREADS) cha
   for (uint32_t row0 = blockIdx.x * CPC; row0 < a.n_rows; row0 += stride) {
     const bool active = row0 + c < a.n_rows;
     const uint32_t row = active ? row0 + c : a.n_rows - 1;
+    const uint32_t *grow = a.in + (size_t)row * N;
     uint32_t pre[PTS];
-    load_beats<S>(a, row, tl, pre);
-    fast_passes<S, 0>(a, c, tl, pre, xb, xm, loud);
+    load_beats<S, 4>(a, grow, tl, 0, pre);
+    fast_passes<S, 4>(a, c, tl, pre, grow, xb, xm, loud);
     uint32_t wide = 0;
     {   // the thread's 16 cells as 32-bit words in the padded array (the exchange buffer is dead)
       const uint32_t *xq = xm + mhx<S>(16 * tl) / 2;   // the thread's 16 consecutive bins
@@ -779,39 +853,17 @@ __global__ void __launch_bounds__(FGeo<S>::THREADS, 1024 / FGeo<S>::THREADS) cha
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
-// host side
-static int fast_edge_iters(int S, int W, int G) { const int tpc = (1 << S) / 16; return (W + G + tpc - 1) / tpc; }
-
-static bool fast_gos_supported(const FxArgs &a) {
-  if (a.core != CORE_LIS || a.cfar_algorithm != 1) return false;
-  if (a.in_w != 16 || a.in_bp != 0 || a.sc_bp != 0 || a.thr_bp != 0 || a.send_cut || a.peak_grouping) return false;
-  if (a.thr_w < 1 || a.thr_w > 32 || a.G < 0 || a.W < 8 || a.W > 128 || (a.W & 7)) return false;
-  if (a.idx_lagg < 1 || a.idx_lagg > a.W || a.idx_lead < 1 || a.idx_lead > a.W) return false;
-  return a.binw + 1 <= 31;
-}
-
-bool fast_chain_supported(const Plan &pl, const FxArgs &a) {
-  if (pl.mode != MODE_FAST || pl.first_stage != STAGE_FFT || pl.last_stage != STAGE_CFAR) return false;
-  if (pl.S < RSP_FAST_SMIN || pl.S > RSP_FAST_SMAX) return false;
-  if (a.bp != 0 || a.tw_bp != 14 || !a.bitrev || a.sel != 2 || a.mag_w != 16 || a.mag_bp != 0) return false;
-  if (a.core == CORE_LIS) return fast_gos_supported(a);
-  if (a.core != CORE_MEM || a.in_w != 16 || a.in_bp != 0 || a.sc_bp != 0 || a.thr_bp != 0 || a.send_cut || a.peak_grouping) return false;
-  if (a.thr_w < 1 || a.thr_w > 32 || a.G < 1 || a.W < 1 || a.div_sum < 0 || a.div_sum > 30) return false;
-  const int ej = fast_edge_iters(pl.S, a.W, a.G);
-  if (ej > (pl.S == 10 ? 2 : 1)) return false;
-  // the scaled threshold must fit 32 bits (the window sums wrap at sumw bits like the reference's registers, see FastArgs::wmul)
-  if (a.sumw < 2 || a.sumw > 31) return false;
-  const long long smax = std::min<long long>((long long)a.W * 32768, 1LL << (a.sumw - 1));
-  const long long tmax = (smax >> a.div_sum) + 1, sc = a.scaler < 0 ? -(long long)a.scaler : a.scaler;
-  const long long lim = (1LL << 31) - (1LL << 16);   // the peak is the sign bit of thr - cut
-  if (a.log_or_linear ? (tmax * sc >= lim) : (tmax + sc >= lim)) return false;
-  if (a.binw + 1 > 31) return false;
-  return true;
-}
+// host side.  This file is compiled once per transform size (-DRSP_FAST_S=10 .. 14, see Makefile) so that the sizes build in
+// parallel; the unit of the smallest size also holds the dispatcher.
+#ifndef RSP_FAST_S
+#error "compile with -DRSP_FAST_S=10..14"
+#endif
+static int fast_edge_iters(int S, int W, int G) { const int tpc = (1 << S) >> fast_lp(S); return (W + G + tpc - 1) / tpc; }
 
 // cp.async staging of the next row (FastArgs::stage).  Measured on B200 (scripts/gpu_stage_ab.sh, profiles/r01_l_stage_ab.txt): +1.9 %
-// at N = 16384 (one CTA per SM, nobody else to hide the row's first loads), nothing or slightly negative below, so it is on from
-// 2^14 points; RSP_FAST_STAGE=0 turns it off, RSP_FAST_STAGE_MIN_S=s moves the limit (tuning knobs, read once)
+// at N = 16384 with 16 points per thread (one CTA per SM, nobody else to hide the row's first loads), nothing or slightly negative
+// below, so it is on from 2^14 points (and only with 16 points per thread: two 105 KB rows leave no room for a staging area);
+// RSP_FAST_STAGE=0 turns it off, RSP_FAST_STAGE_MIN_S=s moves the limit (tuning knobs, read once)
 static bool fast_stage_enabled(int S) {
   static int on = -1, min_s = 0;
   if (on < 0) {
@@ -819,16 +871,17 @@ static bool fast_stage_enabled(int S) {
     on = (e != nullptr && e[0] == '0') ? 0 : 1;
     min_s = m != nullptr ? std::atoi(m) : 14;
   }
-  return on != 0 && S >= min_s;
+  return on != 0 && S >= min_s && fast_lp(S) == 4;
 }
 
 template <int S, int CMODE, bool LINEAR, int EJ>
 static rsp_status launch_fast_inst(const LaunchCtx &c, const FastArgs &fa, cudaStream_t st, const char **err) {
-  using Gm = FGeo<S>;
+  constexpr int LP = fast_lp(S);
+  using Gm = FGeo<S, LP>;
   static int occ_dev[64] = {0};
   int &occ = occ_dev[c.device & 63];
   const size_t smem = ((size_t)Gm::CPC * (Gm::ROW + (Gm::TWS == 0 && fast_stage_enabled(S) ? Gm::N : 0)) + Gm::TWS) * sizeof(uint32_t);
-  auto kernel = chain_fixed_fast_kernel<S, CMODE, LINEAR, EJ>;
+  auto kernel = chain_fixed_fast_kernel<S, LP, CMODE, LINEAR, EJ>;
   if (!occ) { const rsp_status s = launch_cfg(kernel, smem, Gm::THREADS, &occ, err); if (s != RSP_OK) return s; }
   const unsigned groups = (fa.n_rows + Gm::CPC - 1) / Gm::CPC;
   const unsigned grid = std::max(1u, std::min(groups, (unsigned)(c.sm_count * occ)));
@@ -866,6 +919,52 @@ static rsp_status launch_fast_gos(const LaunchCtx &c, const FastArgs &fa, const 
   return RSP_OK;
 }
 
+// one transform size per compile unit
+#define RSP_CAT2(a, b) a##b
+#define RSP_CAT(a, b) RSP_CAT2(a, b)
+rsp_status RSP_CAT(launch_fast_size_, RSP_FAST_S)(int core, int cmode, bool linear, int ej, const LaunchCtx &ctx, const FastArgs &fa, const GosArgs &ga,
+                                                  cudaStream_t st, const char **err) {
+  constexpr int S = RSP_FAST_S;
+  if (core == CORE_LIS) return launch_fast_gos<S>(ctx, fa, ga, st, err);
+#if RSP_FAST_S == 10
+  if (ej == 2) return launch_fast_modes<S, 2>(cmode, linear, ctx, fa, st, err);
+#endif
+  return launch_fast_modes<S, 1>(cmode, linear, ctx, fa, st, err);
+}
+
+#if RSP_FAST_S == 10
+#define RSP_DECL_FAST(s) rsp_status launch_fast_size_##s(int, int, bool, int, const LaunchCtx &, const FastArgs &, const GosArgs &, cudaStream_t, const char **)
+RSP_DECL_FAST(11); RSP_DECL_FAST(12); RSP_DECL_FAST(13); RSP_DECL_FAST(14);
+#undef RSP_DECL_FAST
+
+static bool fast_gos_supported(const FxArgs &a) {
+  if (a.core != CORE_LIS || a.cfar_algorithm != 1) return false;
+  if (a.in_w != 16 || a.in_bp != 0 || a.sc_bp != 0 || a.thr_bp != 0 || a.send_cut || a.peak_grouping) return false;
+  if (a.thr_w < 1 || a.thr_w > 32 || a.G < 0 || a.W < 8 || a.W > 128 || (a.W & 7)) return false;
+  if (a.idx_lagg < 1 || a.idx_lagg > a.W || a.idx_lead < 1 || a.idx_lead > a.W) return false;
+  return a.out != nullptr && a.binw + 1 <= 31;
+}
+
+bool fast_chain_supported(const Plan &pl, const FxArgs &a) {
+  if (pl.mode != MODE_FAST || pl.first_stage != STAGE_FFT || pl.last_stage != STAGE_CFAR) return false;
+  if (pl.S < RSP_FAST_SMIN || pl.S > RSP_FAST_SMAX) return false;
+  if (a.bp != 0 || a.tw_bp != 14 || !a.bitrev || a.sel != 2 || a.mag_w != 16 || a.mag_bp != 0) return false;
+  if (a.core == CORE_LIS) return fast_gos_supported(a);
+  if (a.core != CORE_MEM || a.in_w != 16 || a.in_bp != 0 || a.sc_bp != 0 || a.thr_bp != 0 || a.send_cut || a.peak_grouping) return false;
+  if (a.out == nullptr && a.det_list == nullptr) return false;
+  if (a.thr_w < 1 || a.thr_w > 32 || a.G < 1 || a.W < 1 || a.div_sum < 0 || a.div_sum > 30) return false;
+  const int ej = fast_edge_iters(pl.S, a.W, a.G);
+  if (ej > (pl.S == 10 ? 2 : 1)) return false;
+  // the scaled threshold must fit 32 bits (the window sums wrap at sumw bits like the reference's registers, see FastArgs::wmul)
+  if (a.sumw < 2 || a.sumw > 31) return false;
+  const long long smax = std::min<long long>((long long)a.W * 32768, 1LL << (a.sumw - 1));
+  const long long tmax = (smax >> a.div_sum) + 1, sc = a.scaler < 0 ? -(long long)a.scaler : a.scaler;
+  const long long lim = (1LL << 31) - (1LL << 16);   // the peak is the sign bit of thr - cut
+  if (a.log_or_linear ? (tmax * sc >= lim) : (tmax + sc >= lim)) return false;
+  if (a.binw + 1 > 31) return false;
+  return true;
+}
+
 rsp_status launch_fast_chain(const Plan &pl, const LaunchCtx &ctx, const FxArgs &a, cudaStream_t st, const char **err) {
   FastArgs fa;
   fa.in = a.in; fa.out = a.out; fa.n_rows = a.n_rows; fa.row_base = a.row_base;
@@ -880,28 +979,17 @@ rsp_status launch_fast_chain(const Plan &pl, const LaunchCtx &ctx, const FxArgs 
   fa.stage = (pl.S < RSP_FAST_TWSMEM_S && fast_stage_enabled(pl.S) && (reinterpret_cast<uintptr_t>(a.in) & 15u) == 0) ? 1 : 0;   // rows are N * 4 bytes: the base decides
   const int cmode = a.cfar_mode == 0 ? 0 : (a.cfar_mode == 1 ? 1 : 2);   // MuxLookup default: smallestOf (CFARCoreWithMem.scala:138-141)
   const bool linear = a.log_or_linear != 0;
-  if (a.core == CORE_LIS) {
-    const GosArgs ga = {cmode, linear ? 1 : 0, a.idx_lagg - 1, a.idx_lead - 1};
-    switch (pl.S) {
-    case 10: return launch_fast_gos<10>(ctx, fa, ga, st, err);
-    case 11: return launch_fast_gos<11>(ctx, fa, ga, st, err);
-    case 12: return launch_fast_gos<12>(ctx, fa, ga, st, err);
-    case 13: return launch_fast_gos<13>(ctx, fa, ga, st, err);
-    case 14: return launch_fast_gos<14>(ctx, fa, ga, st, err);
-    default: *err = "no fast variant for this size"; return RSP_EUNSUPPORTED;
-    }
-  }
-  const int ej = fast_edge_iters(pl.S, a.W, a.G);
+  const GosArgs ga = {cmode, linear ? 1 : 0, a.idx_lagg - 1, a.idx_lead - 1};
+  const int ej = a.core == CORE_LIS ? 1 : fast_edge_iters(pl.S, a.W, a.G);
   switch (pl.S) {
-  case 10: return ej == 2 ? launch_fast_modes<10, 2>(cmode, linear, ctx, fa, st, err) : launch_fast_modes<10, 1>(cmode, linear, ctx, fa, st, err);
-#if RSP_FAST_SMAX > 10
-  case 11: return launch_fast_modes<11, 1>(cmode, linear, ctx, fa, st, err);
-  case 12: return launch_fast_modes<12, 1>(cmode, linear, ctx, fa, st, err);
-  case 13: return launch_fast_modes<13, 1>(cmode, linear, ctx, fa, st, err);
-  case 14: return launch_fast_modes<14, 1>(cmode, linear, ctx, fa, st, err);
-#endif
+  case 10: return launch_fast_size_10(a.core, cmode, linear, ej, ctx, fa, ga, st, err);
+  case 11: return launch_fast_size_11(a.core, cmode, linear, ej, ctx, fa, ga, st, err);
+  case 12: return launch_fast_size_12(a.core, cmode, linear, ej, ctx, fa, ga, st, err);
+  case 13: return launch_fast_size_13(a.core, cmode, linear, ej, ctx, fa, ga, st, err);
+  case 14: return launch_fast_size_14(a.core, cmode, linear, ej, ctx, fa, ga, st, err);
   default: *err = "no fast variant for this size"; return RSP_EUNSUPPORTED;
   }
 }
+#endif
 
 }  // namespace rsp

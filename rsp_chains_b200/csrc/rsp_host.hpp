@@ -313,6 +313,9 @@ inline rsp_status plan_cfar_common(const rsp_chain_params &p, const Regs &r, int
       (a.idx_lagg < 1 || a.idx_lagg > a.W || a.idx_lead < 1 || a.idx_lead > a.W)) { err = "indexLagg/indexLead must be in 1..windowCells"; return RSP_EINVAL; }
   if (a.core == CORE_ASR && (a.sub_cells < 1 || a.sub_cells > a.W || !is_pow2(a.sub_cells) || (a.W % a.sub_cells))) {
     err = "subWindowSize must be a power of 2 dividing windowCells"; return RSP_EINVAL; }
+  // Peak grouping with guardCells = 0 on the Lis / ASR cores: the reference substitutes the ends of the reference windows for the
+  // missing guard cells (CFARCoreWithLis.scala:191-192, CFARCoreWithASR.scala:326-327); that substitution is not built
+  if (a.core != CORE_MEM && a.peak_grouping && a.G == 0) { err = "peakGrouping with guardCells = 0 is not built for the Lis / ASR cores"; return RSP_EUNSUPPORTED; }
   if (a.core != CORE_ASR && a.cfar_mode == 3) { /* MuxLookup default: smallestOf (CFARCoreWithMem.scala:138-141) */ }
   return RSP_OK;
 }
@@ -426,10 +429,12 @@ struct GenPlan {
 
 inline rsp_status plan_generator(const rsp_chain_params &p, const Regs &r, GenPlan &gp, std::string &err) {
   const rsp_plfg_params &g = p.plfg;
-  const int ow = g.outputWidthInt + g.outputWidthFrac, nsw = g.maxNumOfSamplesWidth, pw = p.nco.phaseWidth;
+  // The config word is sliced at outputWidthInt (point4 of PLFGDspBlockMem.scala:161-171); the slope field and startingPoint (both
+  // outputWidthInt bits) are zero-extended into the (Int + Frac)-bit protoOut by asTypeOf and read as a signed raw value.
+  const int owi = g.outputWidthInt, ow = g.outputWidthInt + g.outputWidthFrac, nsw = g.maxNumOfSamplesWidth, pw = p.nco.phaseWidth;
   if (pw > ow) { err = "phaseWidth > PLFG output width is not built (closed-form accumulator needs phaseWidth <= outputWidth)"; return RSP_EUNSUPPORTED; }
   const uint32_t pmask = pw >= 32 ? 0xFFFFFFFFu : ((1u << pw) - 1u);
-  const long long start = wrap_host((long long)r.plfg[RSP_PLFG_REG_STARTINGPOINT], ow);
+  const long long start = wrap_host((long long)(r.plfg[RSP_PLFG_REG_STARTINGPOINT] & ((1ULL << owi) - 1)), ow);
   const uint32_t frame_num = r.plfg[RSP_PLFG_REG_FRAMENUM];
   const uint32_t inter = r.plfg[RSP_PLFG_REG_INTERFRAMENUMOFSAMPLES];
   const uint32_t ndiff = r.plfg[RSP_PLFG_REG_DIFFERENTCHIRPSNUM] < 1 ? 1 : r.plfg[RSP_PLFG_REG_DIFFERENTCHIRPSNUM];
@@ -448,10 +453,10 @@ inline rsp_status plan_generator(const rsp_chain_params &p, const Regs &r, GenPl
       if (nseg > (uint32_t)g.maxNumOfSegments) { err = "segmentNums entry exceeds maxNumOfSegments"; return RSP_EINVAL; }
       for (uint32_t sg = 0; sg < nseg; ++sg) {
         const uint64_t wd = r.plfg_ram[(size_t)chirp * g.maxNumOfSegments + sg];
-        const long long slope = wrap_host((long long)(wd & ((1ULL << ow) - 1)), ow);
-        uint32_t ns = (uint32_t)((wd >> ow) & ((1ULL << nsw) - 1));
+        const long long slope = wrap_host((long long)(wd & ((1ULL << owi) - 1)), ow);
+        uint32_t ns = (uint32_t)((wd >> owi) & ((1ULL << nsw) - 1));
         if (!(ns > 1)) ns += 1;                                   // PLFGDspBlockMem.scala:175
-        const int sign = (int)((wd >> (ow + nsw)) & 1), reset = (int)((wd >> (ow + nsw + 1)) & 1);
+        const int sign = (int)((wd >> (owi + nsw)) & 1), reset = (int)((wd >> (owi + nsw + 1)) & 1);
         const long long step = sign ? slope : -slope;
         GenSegment s; s.pad_ = 0; s.start = k; s.n = ns; s.phase0 = phase; s.step = (int32_t)step;
         if (reset) { s.f0 = (int32_t)start; s.flags = 1u; }
@@ -469,16 +474,23 @@ inline rsp_status plan_generator(const rsp_chain_params &p, const Regs &r, GenPl
     }
   }
   gp.frame_len = k;
-  if (inter > 0) {   // inter-frame pause emits startingPoint (plfg_script.py:50-53)
-    GenSegment s; s.pad_ = 0; s.start = k; s.n = inter; s.f0 = (int32_t)start; s.step = 0; s.phase0 = phase; s.flags = 1u;
+  // Inter-frame pause, as the RTL counter tree does it (PLFGDspBlockMem.scala:242-275): framePauseCounter starts counting on the tick
+  // of the frame's LAST sample and the frame restarts when fpc + 1 >= interframeNumOfSamples, so the stream holds inter - 1 pause
+  // samples of startingPoint (none for inter <= 1).  The reference's Python model (plfg_script.py:50-53) emits inter samples; its
+  // value-checked tests use frameNum = 1, where both agree.  framePauseCounter is UInt(6.W) (:144): fpc + 1 never reaches 64, so
+  // inter >= 64 never leaves the pause in hardware -- refused here when a second frame would be needed.
+  const uint32_t pause = inter > 1 ? inter - 1 : 0;
+  if (frame_num != 1 && inter > 63) { err = "interframeNumOfSamples > 63 never ends the pause (framePauseCounter is 6 bits wide)"; return RSP_EUNSUPPORTED; }
+  if (pause > 0) {
+    GenSegment s; s.pad_ = 0; s.start = k; s.n = pause; s.f0 = (int32_t)start; s.step = 0; s.phase0 = phase; s.flags = 1u;
     gp.segs.push_back(s);
-    for (uint32_t q = 0; q < inter; ++q) phase = (phase + ((uint32_t)start & pmask)) & pmask;
-    k += inter;
+    for (uint32_t q = 0; q < pause; ++q) phase = (phase + ((uint32_t)start & pmask)) & pmask;
+    k += pause;
   }
   gp.period_len = k;
   gp.period_phase = phase;
   // frameNum frames with a pause between them, none after the last; 0 = forever
-  gp.total = frame_num == 0 ? ~0ULL : (uint64_t)frame_num * gp.period_len - (uint64_t)inter;
+  gp.total = frame_num == 0 ? ~0ULL : (uint64_t)frame_num * gp.period_len - (uint64_t)pause;
   return RSP_OK;
 }
 

@@ -62,7 +62,7 @@ def test_plfg_matches_reference_python_golden(oracle, case):
     p = oracle.Plfg(max_num_of_segments=4, max_chirp_ordinal_num=4, frame_num=case["numOfFrames"],
                     interframe_num_of_samples=case["interFrameNumOfSamples"], different_chirps_num=n_chirps,
                     starting_point=case["startingPoint"] & 0xFFFF, segment_nums=case["numOfSegments"],
-                    repeated_chirp_nums=[1] * n_chirps, chirp_ordinal_nums=list(range(n_chirps)), ram=ram)
+                    repeated_chirp_nums=[1] * n_chirps, chirp_ordinal_nums=list(range(n_chirps)), ram=ram, pause_model="script")
     want = case["output"]
     got = p.run(len(want) + 100)
     assert got.tolist() == want        # and the PLFG stops after frameNum frames (no trailing pause)
@@ -124,3 +124,94 @@ def test_java_random_known_answer(oracle):
     r = oracle.JavaRandom(0)
     assert abs(r.next_double() - 0.730967787376657) < 1e-15
     assert abs(r.next_double() - 0.24053641567148587) < 1e-15
+
+
+# ---------------------------------------------------------------------------------------------------- RTL counter tree
+def _rtl_plfg_ticks(n_out, *, max_seg, nsw, ow, owi, frame_num, inter, ndiff, start_reg, seg_nums, rep_nums, ord_nums, ram):
+    """Tick-level restatement of the PLFG counter tree (PLFGDspBlockMem.scala:242-295) with the value path of :298-345 applied in
+    emission order: one sample per tick while enable && !end; the pause is the ticks on which every counter sits at its terminal
+    value and framePauseCounter (UInt(6.W), truncating +) is above 0.  Written from the Scala, not from the oracle's nested loops."""
+    def wrap(v, w):
+        v &= (1 << w) - 1
+        return v - (1 << w) if v >> (w - 1) else v
+    start = wrap(start_reg & ((1 << owi) - 1), ow)
+    sc = seg = rep = dc = fc = fpc = 0
+    end, cur, out = False, start, []
+    while len(out) < n_out and not end:
+        chirp = ord_nums[dc]
+        wd = ram[chirp * max_seg + seg]
+        slope = wrap(wd & ((1 << owi) - 1), ow)
+        ns = (wd >> owi) & ((1 << nsw) - 1)
+        ns = ns if ns > 1 else ns + 1
+        sign, rst = (wd >> (owi + nsw)) & 1, (wd >> (owi + nsw + 1)) & 1
+        if fpc > 0 or rst or (seg == 0 and sc == 0):
+            cur = start
+        else:
+            cur = wrap(cur + slope if sign else cur - slope, ow)
+        out.append(cur)
+        if sc + 1 >= ns:
+            if seg + 1 >= seg_nums[chirp]:
+                if rep + 1 >= rep_nums[dc]:
+                    if dc + 1 >= ndiff:
+                        if frame_num != 0 and fc + 1 >= frame_num:
+                            end = True
+                        elif ((fpc + 1) & 63) >= inter:
+                            sc = seg = rep = dc = fpc = 0
+                            fc = 0 if frame_num == 0 else fc + 1
+                        else:
+                            fpc = (fpc + 1) & 63
+                    else:
+                        sc = seg = rep = 0; dc += 1
+                else:
+                    sc = seg = 0; rep += 1
+            else:
+                sc = 0; seg += 1
+        else:
+            sc += 1
+    return out
+
+
+@pytest.mark.parametrize("frame_num,inter", [(3, 17), (2, 1), (2, 2), (0, 5), (4, 63), (1, 63)])
+def test_plfg_pause_follows_the_rtl_counter_tree(oracle, frame_num, inter):
+    """multi-frame streams: inter - 1 pause samples between frames (none for inter <= 1), none after the last frame; several chirp
+    types through chirpOrdinalNums, repeated chirps, a reset segment"""
+    W = oracle.plfg_ram_word
+    ram = [0] * 16
+    ram[0:2] = [W(3, 20, True, False), W(5, 7, False, False)]                    # chirp 0: up, down
+    ram[4:7] = [W(1, 9, True, False), W(0, 4, False, True), W(2, 11, False, False)]   # chirp 1: up, reset, down
+    ram[8:9] = [W(7, 1, True, False)]                                            # chirp 2: nSamples 1 is bumped to 2
+    cfg = dict(frame_num=frame_num, interframe_num_of_samples=inter, different_chirps_num=3, starting_point=40,
+               segment_nums=[2, 3, 1, 1], repeated_chirp_nums=[2, 1, 3], chirp_ordinal_nums=[1, 0, 2], ram=ram)
+    n = 700
+    got = oracle.Plfg(**cfg).run(n).tolist()
+    want = _rtl_plfg_ticks(n, max_seg=4, nsw=8, ow=16, owi=16, frame_num=frame_num, inter=inter, ndiff=3, start_reg=40,
+                           seg_nums=[2, 3, 1, 1], rep_nums=[2, 1, 3], ord_nums=[1, 0, 2], ram=ram)
+    assert got == want
+    frame_len = 2 * (9 + 4 + 11) + (20 + 7) + 3 * 2
+    if frame_num == 0:
+        assert len(got) == n
+    else:
+        assert len(got) == min(n, frame_num * frame_len + (frame_num - 1) * max(inter - 1, 0))
+    # the script model of the reference's Python golden differs by exactly one sample per pause
+    if frame_num not in (0, 1) and inter >= 1:
+        script = oracle.Plfg(pause_model="script", **cfg).run(n + 10)
+        assert len(script) == min(n + 10, frame_num * frame_len + (frame_num - 1) * inter)
+
+
+def test_plfg_output_width_frac_slices_at_int_width(oracle):
+    """outputWidthFrac > 0 (PLFGDspBlockMem.scala:161-178): the config word is sliced at outputWidthInt, slope and startingPoint are
+    zero-extended into the (Int + Frac)-bit protoOut.  Hand-derived: Int 8, Frac 4 -> 12-bit output; slope field 0xF0 = +240 raw (not -16),
+    startingPoint 0x90 = +144 raw (not -112): 144, 384, ..., 144 + 240 * 7 = 1824, then 2064 wraps to -2032 at 12 bits"""
+    wd = oracle.plfg_ram_word(0xF0, 12, True, False, output_width=8, samples_width=8)
+    assert wd == (1 << 16) | (12 << 8) | 0xF0
+    p = oracle.Plfg(output_width=12, output_width_int=8, frame_num=1, different_chirps_num=1, starting_point=0x90, segment_nums=[1],
+                    repeated_chirp_nums=[1], chirp_ordinal_nums=[0], ram=[wd])
+    got = p.run(50).tolist()
+    want, v = [], 144
+    for k in range(12):
+        want.append(v if v < 2048 else v - 4096)
+        v = (v + 240) % 4096
+    assert got == want
+    tick = _rtl_plfg_ticks(50, max_seg=4, nsw=8, ow=12, owi=8, frame_num=1, inter=63, ndiff=1, start_reg=0x90, seg_nums=[1, 1, 1, 1],
+                           rep_nums=[1], ord_nums=[0], ram=[wd, 0, 0, 0])
+    assert tick == want
