@@ -93,7 +93,12 @@ typedef struct {
 } rsp_mag_params;
 
 /* CFARParams (generators/cfar/src/main/scala/CFARParams.scala:24-49) */
-typedef enum { RSP_CFAR_CA = 0 /* CACFARType */, RSP_CFAR_GOS = 1 /* GOSCFARType */, RSP_CFAR_GOSCA = 2 /* GOSCACFARType */ } rsp_cfar_type;
+typedef enum { RSP_CFAR_CA = 0 /* CACFARType */, RSP_CFAR_GOS = 1 /* GOSCFARType */, RSP_CFAR_GOSCA = 2 /* GOSCACFARType */,
+               /* not a CFARType of the reference: the combined-window ordered statistic of its Scala golden model cfarOS
+                * (generators/cfar/src/main/scala/CFARUtils.scala:159-196): threshold = scaler (*|+) the cell at ascending index
+                * floor(1.5 * windowCells) of the 2 * windowCells reference cells (lead ++ lagg), 0 and no peak within
+                * windowCells + guardCells of either end.  Registers as for the Lis core; cfarMode / indexLagg / indexLead unused. */
+               RSP_CFAR_OS_GOLDEN = 3 } rsp_cfar_type;
 typedef struct {
   int32_t inWidth, inBinPoint;               /* protoIn         */
   int32_t thresholdWidth, thresholdBinPoint; /* protoThreshold  */

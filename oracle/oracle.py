@@ -21,7 +21,7 @@ TRIM = {
     "RoundTowardsZero": 4, "RoundTowardsInfinity": 5, "RoundHalfDown": 6, "RoundHalfTowardsZero": 7,
     "RoundHalfTowardsInfinity": 8, "RoundHalfToOdd": 9, "NoTrim": 10,
 }
-CORE_MEM, CORE_LIS, CORE_ASR = 0, 1, 2
+CORE_MEM, CORE_LIS, CORE_ASR, CORE_OS = 0, 1, 2, 3
 
 
 def build(force: bool = False) -> str:

@@ -559,7 +559,7 @@ int rspo_cfar_fixed(const rspo_cfar_cfg *c, const int32_t *x, int64_t *thr_full,
   const int bp_in = c->in_bp, bp_s = c->scaler_bp;
   const int64_t scaler = rspo_wrap(c->threshold_scaler, c->scaler_width);
   int32_t *sorted = NULL;
-  if (c->core == RSPO_CFAR_CORE_LIS) { sorted = (int32_t *)malloc(sizeof(int32_t) * 2 * (size_t)W); if (!sorted) return -2; }
+  if (c->core == RSPO_CFAR_CORE_LIS || c->core == RSPO_CFAR_CORE_OS) { sorted = (int32_t *)malloc(sizeof(int32_t) * 2 * (size_t)W); if (!sorted) return -2; }
   int rc = 0;
   for (int n = 0; n < N; ++n) {
     const int lagg_full = (n + G + W <= N - 1);
@@ -572,6 +572,14 @@ int rspo_cfar_fixed(const rspo_cfar_cfg *c, const int32_t *x, int64_t *thr_full,
       if (lead_full) for (int j = n - G - W; j <= n - G - 1; ++j) sr += x[j];
       L = rspo_wrap(sl, sumw) >> c->div_sum; /* BinaryRepresentation.shr: arithmetic (S7) (:132-133) */
       R = rspo_wrap(sr, sumw) >> c->div_sum;
+    } else if (c->core == RSPO_CFAR_CORE_OS) {
+      /* cfarOS (CFARUtils.scala:165-171): thr = (lead ++ lagg).sorted((1.5 * referenceCells).toInt), ascending; only where both
+       * windows exist (the golden's loop runs ix = windowCells until totalCells - windowCells and pads the rest with 0) */
+      if (lagg_full && lead_full) {
+        for (int j = 0; j < W; ++j) { sorted[j] = x[n - G - W + j]; sorted[W + j] = x[n + G + 1 + j]; }
+        qsort(sorted, 2 * (size_t)W, sizeof(int32_t), cmp_desc_i32);
+        L = R = sorted[2 * W - 1 - (3 * W) / 2];   /* ascending index floor(1.5 W) of 2 W cells */
+      }
     } else if (c->core == RSPO_CFAR_CORE_LIS) {
       /* descending sorted windows, 1-based rank from the largest (CFARCoreWithLis.scala:32-39,136-143) */
       if (c->index_lagg < 1 || c->index_lagg > W || c->index_lead < 1 || c->index_lead > W) { rc = -1; break; }
@@ -594,6 +602,7 @@ int rspo_cfar_fixed(const rspo_cfar_cfg *c, const int32_t *x, int64_t *thr_full,
     case 2: by_mode = so; break;
     default: by_mode = so; break;
     }
+    if (c->core == RSPO_CFAR_CORE_OS) by_mode = L;
     if (c->core == RSPO_CFAR_CORE_ASR && c->cfar_mode == 3 && lagg_full && lead_full) {
       /* CASH: min over sub-windows of max(laggSum_i, leadSum_i), >> log2(subCells) (CFARCoreWithASR.scala:193-209) */
       const int sub = c->sub_cells, ns = W / sub;
@@ -631,6 +640,7 @@ int rspo_cfar_fixed(const rspo_cfar_cfg *c, const int32_t *x, int64_t *thr_full,
     const int64_t cut = x[n];
     const int64_t cut_al = cut << (thr_bp - bp_in); /* compare at full precision (:185) */
     int is_peak = cut_al > thr;
+    if (c->core == RSPO_CFAR_CORE_OS && !(lagg_full && lead_full)) { is_peak = 0; thr = 0; }   /* no edge bins in the golden's loop; padded with 0.0 */
     if (c->peak_grouping) {
       /* neighbours come from guard shift registers at their compile-time ends (parallelOut.last / .head);
        * registers past the run-time depth never load and read 0.  The Mem core takes BOTH from the lagging
@@ -681,27 +691,80 @@ int rspo_cfar_words(const rspo_cfar_cfg *c, const uint32_t *in, uint32_t *out, i
   return rc;
 }
 
+static int cmp_desc_f64_(const void *a, const void *b) {
+  const double x = *(const double *)a, y = *(const double *)b;
+  return (x < y) - (x > y);
+}
+/* The DspReal flavour of the three cores: the same window / edge / mode / peak-grouping policy as rspo_cfar_fixed above
+ * (CFARCoreWithMem.scala:102-189, CFARCoreWithLis.scala:136-194, CFARCoreWithASR.scala:193-209,285-332) with doubles in place of
+ * the fixed-point registers: no sum wrap, `>> divSum` is a division by 2^divSum, CASH divides by subCells. */
 int rspo_cfar_f64(const rspo_cfar_cfg *c, double scaler, const double *x, double *thr, uint8_t *peak) {
   const int N = c->fft_win, W = c->window_cells, G = c->guard_cells;
-  if (!(N > 2 * W + 2 * G + 1) || W < 1 || G < 1) return -1;
+  if (!(N > 2 * W + 2 * G + 1) || W < 1 || G < 0) return -1;
+  if (c->core == RSPO_CFAR_CORE_MEM && G < 1) return -1;
   const double div = ldexp(1.0, c->div_sum);
+  const int gos = (c->core == RSPO_CFAR_CORE_LIS && c->cfar_algorithm != 0);
+  const int os = c->core == RSPO_CFAR_CORE_OS;
+  double *sorted = NULL;
+  if (gos || os) {
+    if (gos && (c->index_lagg < 1 || c->index_lagg > W || c->index_lead < 1 || c->index_lead > W)) return -1;
+    sorted = (double *)malloc(sizeof(double) * 2 * (size_t)W);
+    if (!sorted) return -2;
+  }
+  const int sub = c->sub_cells;
+  if (c->core == RSPO_CFAR_CORE_ASR && (sub < 1 || sub > W || (sub & (sub - 1)) || (W % sub))) return -1;
   for (int n = 0; n < N; ++n) {
     const int lagg_full = (n + G + W <= N - 1), lead_full = (n - G - W >= 0);
-    double sl = 0, sr = 0;
-    if (lagg_full) for (int j = n + G + 1; j <= n + G + W; ++j) sl += x[j];
-    if (lead_full) for (int j = n - G - W; j <= n - G - 1; ++j) sr += x[j];
-    const double L = sl / div, R = sr / div;
+    double L = 0, R = 0;
+    if (os) {
+      if (lagg_full && lead_full) {
+        for (int j = 0; j < W; ++j) { sorted[j] = x[n - G - W + j]; sorted[W + j] = x[n + G + 1 + j]; }
+        qsort(sorted, 2 * (size_t)W, sizeof(double), cmp_desc_f64_);
+        L = R = sorted[2 * W - 1 - (3 * W) / 2];
+      }
+    } else if (gos) {
+      if (lagg_full) { for (int j = 0; j < W; ++j) sorted[j] = x[n + G + 1 + j]; qsort(sorted, (size_t)W, sizeof(double), cmp_desc_f64_); L = sorted[c->index_lagg - 1]; }
+      if (lead_full) { for (int j = 0; j < W; ++j) sorted[j] = x[n - G - W + j]; qsort(sorted, (size_t)W, sizeof(double), cmp_desc_f64_); R = sorted[c->index_lead - 1]; }
+    } else {
+      const int wl = c->core == RSPO_CFAR_CORE_ASR ? sub : W;   /* ASR: the newest subCells cells of each window (:285-288) */
+      double sl = 0, sr = 0;
+      if (lagg_full) for (int j = 0; j < wl; ++j) sl += x[n + G + W - j];
+      if (lead_full) for (int j = 0; j < wl; ++j) sr += x[n - G - 1 - j];
+      L = sl / div; R = sr / div;
+    }
+    double by_mode = c->cfar_mode == 0 ? 0.5 * (L + R) : (c->cfar_mode == 1 ? (L > R ? L : R) : (L < R ? L : R));
+    if (os) by_mode = L;
+    if (c->core == RSPO_CFAR_CORE_ASR && c->cfar_mode == 3 && lagg_full && lead_full) {
+      const int ns = W / sub;
+      double mn = 0;
+      for (int i = 0; i < ns; ++i) {
+        double sl = 0, sr = 0;
+        for (int j = 0; j < sub; ++j) { sl += x[n + G + W - i * sub - j]; sr += x[n - G - 1 - i * sub - j]; }
+        const double mx = sl > sr ? sl : sr;
+        if (i == 0 || mx < mn) mn = mx;
+      }
+      by_mode = mn / (double)sub;
+    }
     double t0;
-    const double by_mode = c->cfar_mode == 0 ? 0.5 * (L + R) : (c->cfar_mode == 1 ? (L > R ? L : R) : (L < R ? L : R));
-    if (!lead_full) t0 = L; else if (!lagg_full) t0 = R; else t0 = by_mode;
-    const double t = c->log_or_linear ? t0 * scaler : t0 + scaler;
+    if (c->core == RSPO_CFAR_CORE_MEM) {
+      if (!lead_full && !lagg_full) t0 = 0; else if (!lead_full) t0 = L; else if (!lagg_full) t0 = R; else t0 = by_mode;
+    } else t0 = (lagg_full && lead_full) ? by_mode : 0;
+    double t = c->log_or_linear ? t0 * scaler : t0 + scaler;
     int pk = x[n] > t;
+    if (os && !(lagg_full && lead_full)) { pk = 0; t = 0; }
     if (c->peak_grouping) {
-      const double left = (n + 1 < N) ? x[n + 1] : 0.0, right = (n + G < N) ? x[n + G] : 0.0;
+      const int gfull = (G == c->guard_window_size);
+      double left = 0, right = 0;
+      if (G != 0) {
+        left = (gfull && n + 1 < N) ? x[n + 1] : 0.0;
+        if (c->core == RSPO_CFAR_CORE_MEM) right = (n + G < N) ? x[n + G] : 0.0;
+        else right = (n - 1 >= 0) ? x[n - 1] : 0.0;
+      }
       pk = pk && x[n] > left && x[n] > right;
     }
     thr[n] = t; peak[n] = (uint8_t)pk;
   }
+  free(sorted);
   return 0;
 }
 

@@ -68,7 +68,8 @@ typedef struct {
 
 /* CFARParams + run-time registers (generators/cfar/src/main/scala/CFARParams.scala:24-49,
  * CFARDspBlock.scala:96-130) */
-enum { RSPO_CFAR_CORE_MEM = 0, RSPO_CFAR_CORE_LIS = 1, RSPO_CFAR_CORE_ASR = 2 };
+enum { RSPO_CFAR_CORE_MEM = 0, RSPO_CFAR_CORE_LIS = 1, RSPO_CFAR_CORE_ASR = 2,
+       RSPO_CFAR_CORE_OS = 3 /* integer form of the golden cfarOS (CFARUtils.scala:159-196): combined window, ascending index floor(1.5 W) */ };
 typedef struct {
   int32_t core;              /* which CFARCore variant is elaborated (CFARcore.scala:62-64)      */
   int32_t in_width, in_bp;   /* protoIn                                                          */

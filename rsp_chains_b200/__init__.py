@@ -5,7 +5,7 @@ from . import _abi
 from ._abi import RspError
 from .chain import (FftMagCfarChainVanilla, RspChainVanilla, gather_detections, host_alloc, host_free, shard_rows)
 from .params import (AddressSet, CACFARType, CFARParams, Convergent, DIFDecimType, DITDecimType, FFTParams,
-                     FftMagCfarVanillaParameters, FixedNCOParams, FixedPLFGParams, FixedPoint, GOSCACFARType, GOSCFARType,
+                     FftMagCfarVanillaParameters, FixedNCOParams, FixedPLFGParams, FixedPoint, GOSCACFARType, GOSCFARType, OSGoldenCFARType,
                      MAGParams, RoundDown, RoundHalfUp, RspChainVanillaParameters, WindowFunctionType, WindowFunctionTypes, fft_mag_cfar_chain_vanilla_app_params,
                      log2Up, rsp_chain_vanilla_app_params)
 

@@ -27,7 +27,8 @@ namespace rsp {
 enum { TRIM_ROUND_HALF_UP = 0, TRIM_FLOOR = 1, TRIM_CONVERGENT = 2, TRIM_ROUND_UP = 3, TRIM_ROUND_TOWARDS_ZERO = 4,
        TRIM_ROUND_TOWARDS_INFINITY = 5, TRIM_ROUND_HALF_DOWN = 6, TRIM_ROUND_HALF_TOWARDS_ZERO = 7,
        TRIM_ROUND_HALF_TOWARDS_INFINITY = 8, TRIM_ROUND_HALF_TO_ODD = 9, TRIM_NO_TRIM = 10 };
-enum { CORE_MEM = 0, CORE_LIS = 1, CORE_ASR = 2 };
+enum { CORE_MEM = 0, CORE_LIS = 1, CORE_ASR = 2,
+       CORE_OS = 3 };   // the combined-window ordered statistic of the Scala golden cfarOS (CFARUtils.scala:159-196); no hardware core
 enum { STAGE_FFT = 0, STAGE_MAG = 1, STAGE_CFAR = 2 };
 // kernel variants of the fixed-point chain
 enum { MODE_GENERIC = 0,   // every parameter read at run time
@@ -452,13 +453,15 @@ template <int S> RSP_HD void cfar_write_prefix(const FxArgs &a, int tl, int offs
 
 // k-th largest (1-based) of W cells starting at `start`: the value the descending linear insertion sorter holds at
 // index k-1 (CFARCoreWithLis.scala:32-39,136-143).  Bitwise search on the biased value.
-RSP_HD int cfar_kth_largest(const FxArgs &a, const uint32_t *bufM, int start, int W, int k) {
+// `start2` >= 0: the window is the union of [start, start + W) and [start2, start2 + W) (cfarOS: lead ++ lagg)
+RSP_HD int cfar_kth_largest(const FxArgs &a, const uint32_t *bufM, int start, int W, int k, int start2 = -1) {
   const int bias = 1 << (a.in_w - 1);
   int ans = 0;
   for (int b = a.in_w - 1; b >= 0; --b) {
     const int cand = ans | (1 << b);
     int cnt = 0;
     for (int j = 0; j < W; ++j) cnt += (cfar_x(a, bufM, start + j) + bias >= cand) ? 1 : 0;
+    if (start2 >= 0) for (int j = 0; j < W; ++j) cnt += (cfar_x(a, bufM, start2 + j) + bias >= cand) ? 1 : 0;
     if (cnt >= k) ans = cand;
   }
   return ans - bias;
@@ -478,6 +481,10 @@ RSP_HD void cfar_bin(const FxArgs &a, uint32_t row, int n, const uint32_t *bufM,
     if (lead_full) sr = (int)(bufP[pad(n - G)] - bufP[pad(n - G - W)]);
     Lv = wrapw(sl, a.sumw) >> a.div_sum;
     Rv = wrapw(sr, a.sumw) >> a.div_sum;
+  } else if (a.core == CORE_OS) {
+    // cfarOS (CFARUtils.scala:165-171): (lead ++ lagg).sorted((1.5 * referenceCells).toInt), i.e. ascending index floor(1.5 W) of the
+    // 2 W reference cells = the (2 W - floor(1.5 W))-th largest; only where both windows exist (the golden pads the edges with 0)
+    if (lagg_full && lead_full) Lv = Rv = cfar_kth_largest(a, bufM, n - G - W, W, 2 * W - (3 * W) / 2, n + G + 1);
   } else if (a.core == CORE_LIS) {
     if (lagg_full) Lv = cfar_kth_largest(a, bufM, n + G + 1, W, a.idx_lagg);
     if (lead_full) Rv = cfar_kth_largest(a, bufM, n - G - W, W, a.idx_lead);
@@ -491,6 +498,7 @@ RSP_HD void cfar_bin(const FxArgs &a, uint32_t row, int n, const uint32_t *bufM,
   }
   const long long go = Lv > Rv ? Lv : Rv, so = Lv < Rv ? Lv : Rv;
   long long by_mode = a.cfar_mode == 0 ? ((Rv + Lv) >> 1) : (a.cfar_mode == 1 ? go : so);
+  if (a.core == CORE_OS) by_mode = Lv;   // one statistic: cfarMode does not apply
   if (a.core == CORE_ASR && a.cfar_mode == 3 && lagg_full && lead_full) {
     // CASH: min over sub-windows of max(laggSum_i, leadSum_i), >> log2(subCells) (CFARCoreWithASR.scala:193-209)
     const int sub = a.sub_cells, ns = W / sub;
@@ -523,6 +531,7 @@ RSP_HD void cfar_bin(const FxArgs &a, uint32_t row, int n, const uint32_t *bufM,
   }
   const int cut = cfar_x(a, bufM, n);
   bool pk = ((long long)cut << (tbp - a.in_bp)) > thr;
+  if (a.core == CORE_OS && !(lagg_full && lead_full)) { pk = false; thr = 0; }   // the golden's loop runs over windowCells until totalCells - windowCells only; the rest is padded with 0.0 (log mode too)
   if (a.peak_grouping) {
     // neighbours come from the guard registers (CFARCoreWithMem.scala:182-184; CFARCoreWithLis.scala:191-192)
     int left = 0, right = 0;

@@ -158,12 +158,13 @@ RSP_HD int32_t f32_bits(float f) {
 #endif
 }
 
-RSP_HD float cfar_kth_largest_f32(const float *bufM, int start, int W, int k) {
+RSP_HD float cfar_kth_largest_f32(const float *bufM, int start, int W, int k, int start2 = -1) {   // start2 >= 0: union of two windows (cfarOS)
   uint32_t ans = 0;
   for (int b = 31; b >= 0; --b) {
     const uint32_t cand = ans | (1u << b);
     int cnt = 0;
     for (int j = 0; j < W; ++j) cnt += (f32_key(bufM[pad(start + j)]) >= cand) ? 1 : 0;
+    if (start2 >= 0) for (int j = 0; j < W; ++j) cnt += (f32_key(bufM[pad(start2 + j)]) >= cand) ? 1 : 0;
     if (cnt >= k) ans = cand;
   }
   return f32_unkey(ans);
@@ -201,12 +202,15 @@ RSP_HD uint32_t cfar_thread_f32(const F32Args &a, uint32_t row, int tl, const fl
       }
       Lv = lagg_full ? sl * a.inv_div : 0.f;
       Rv = lead_full ? sr * a.inv_div : 0.f;
+    } else if (a.core == CORE_OS) {   // cfarOS (CFARUtils.scala:165-171), see cfar_bin
+      if (lagg_full && lead_full) Lv = Rv = cfar_kth_largest_f32(bufM, n - G - W, W, 2 * W - (3 * W) / 2, n + G + 1);
     } else {
       if (lagg_full) Lv = cfar_kth_largest_f32(bufM, n + G + 1, W, a.idx_lagg);
       if (lead_full) Rv = cfar_kth_largest_f32(bufM, n - G - W, W, a.idx_lead);
     }
     const float go = Lv > Rv ? Lv : Rv, so = Lv < Rv ? Lv : Rv;
     float by_mode = a.cfar_mode == 0 ? 0.5f * (Rv + Lv) : (a.cfar_mode == 1 ? go : so);
+    if (a.core == CORE_OS) by_mode = Lv;
     if (a.core == CORE_ASR && a.cfar_mode == 3 && lagg_full && lead_full) {
       const int sub = a.sub_cells, ns = W / sub;
       float mn = 0.f;
@@ -225,9 +229,10 @@ RSP_HD uint32_t cfar_thread_f32(const F32Args &a, uint32_t row, int tl, const fl
       else if (!lagg_full) t0 = Rv;
       else t0 = by_mode;
     } else t0 = (lagg_full && lead_full) ? by_mode : 0.f;
-    const float thr = a.log_or_linear ? t0 * a.scaler : t0 + a.scaler;
+    float thr = a.log_or_linear ? t0 * a.scaler : t0 + a.scaler;
     const float cut = bufM[pad(n)];
     bool pk = cut > thr;
+    if (a.core == CORE_OS && !(lagg_full && lead_full)) { pk = false; thr = 0.f; }
     if (a.peak_grouping) {
       float left = 0.f, right = 0.f;
       if (G != 0) {

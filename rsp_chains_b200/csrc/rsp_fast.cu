@@ -858,7 +858,7 @@ __global__ void __launch_bounds__(FGeo<S>::THREADS, 1024 / FGeo<S>::THREADS) cha
 #ifndef RSP_FAST_S
 #error "compile with -DRSP_FAST_S=10..14"
 #endif
-static int fast_edge_iters(int S, int W, int G) { const int tpc = (1 << S) >> fast_lp(S); return (W + G + tpc - 1) / tpc; }
+static int fast_edge_iters(int S, int W, int G) { const int tpc = (1 << S) >> (S == 14 ? 5 : 4); return (W + G + tpc - 1) / tpc; }   // threads per chirp of the narrower geometry
 
 // cp.async staging of the next row (FastArgs::stage).  Measured on B200 (scripts/gpu_stage_ab.sh, profiles/r01_l_stage_ab.txt): +1.9 %
 // at N = 16384 with 16 points per thread (one CTA per SM, nobody else to hide the row's first loads), nothing or slightly negative
@@ -871,16 +871,25 @@ static bool fast_stage_enabled(int S) {
     on = (e != nullptr && e[0] == '0') ? 0 : 1;
     min_s = m != nullptr ? std::atoi(m) : 14;
   }
-  return on != 0 && S >= min_s && fast_lp(S) == 4;
+  return on != 0 && S >= min_s;
 }
 
-template <int S, int CMODE, bool LINEAR, int EJ>
-static rsp_status launch_fast_inst(const LaunchCtx &c, const FastArgs &fa, cudaStream_t st, const char **err) {
-  constexpr int LP = fast_lp(S);
+// points per thread at N = 16384: 32 (two CTAs per SM) unless RSP_FAST_LP14=4 asks for the one-CTA form (A/B knob, read once)
+static int fast_lp_runtime(int S) {
+  static int lp14 = -1;
+  if (lp14 < 0) { const char *e = std::getenv("RSP_FAST_LP14"); lp14 = (e != nullptr && e[0] == '4') ? 4 : RSP_FAST_LP14; }
+  return S == 14 ? lp14 : 4;
+}
+
+template <int S, int LP, int CMODE, bool LINEAR, int EJ>
+static rsp_status launch_fast_inst_lp(const LaunchCtx &c, const FastArgs &fa_in, cudaStream_t st, const char **err) {
   using Gm = FGeo<S, LP>;
   static int occ_dev[64] = {0};
   int &occ = occ_dev[c.device & 63];
-  const size_t smem = ((size_t)Gm::CPC * (Gm::ROW + (Gm::TWS == 0 && fast_stage_enabled(S) ? Gm::N : 0)) + Gm::TWS) * sizeof(uint32_t);
+  FastArgs fa = fa_in;
+  if (LP != 4) fa.stage = 0;
+  const bool stage = LP == 4 && fast_stage_enabled(S);
+  const size_t smem = ((size_t)Gm::CPC * (Gm::ROW + (Gm::TWS == 0 && stage ? Gm::N : 0)) + Gm::TWS) * sizeof(uint32_t);
   auto kernel = chain_fixed_fast_kernel<S, LP, CMODE, LINEAR, EJ>;
   if (!occ) { const rsp_status s = launch_cfg(kernel, smem, Gm::THREADS, &occ, err); if (s != RSP_OK) return s; }
   const unsigned groups = (fa.n_rows + Gm::CPC - 1) / Gm::CPC;
@@ -888,6 +897,11 @@ static rsp_status launch_fast_inst(const LaunchCtx &c, const FastArgs &fa, cudaS
   kernel<<<grid, Gm::THREADS, smem, st>>>(fa);
   if (cudaGetLastError() != cudaSuccess) { *err = "chain_fixed_fast_kernel launch failed"; return RSP_ECUDA; }
   return RSP_OK;
+}
+template <int S, int CMODE, bool LINEAR, int EJ>
+static rsp_status launch_fast_inst(const LaunchCtx &c, const FastArgs &fa, cudaStream_t st, const char **err) {
+  if constexpr (S == 14) { if (fast_lp_runtime(S) == 5) return launch_fast_inst_lp<S, 5, CMODE, LINEAR, EJ>(c, fa, st, err); }
+  return launch_fast_inst_lp<S, 4, CMODE, LINEAR, EJ>(c, fa, st, err);
 }
 
 template <int S, int EJ>

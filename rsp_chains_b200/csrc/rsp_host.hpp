@@ -79,7 +79,7 @@ inline rsp_status validate_params(const rsp_chain_params &p, std::string &err) {
   RSP_REQ(c.leadLaggWindowSize > 0 && c.guardWindowSize > 0, RSP_EINVAL, "leadLaggWindowSize and guardWindowSize must be positive");
   RSP_REQ(c.leadLaggWindowSize > c.guardWindowSize, RSP_EINVAL, "leadLaggWindowSize must exceed guardWindowSize");
   RSP_REQ(c.fftSize <= 16384 && c.leadLaggWindowSize <= 4096, RSP_EUNSUPPORTED, "CFAR fftSize must be <= 16384");
-  RSP_REQ(c.CFARAlgorithm >= RSP_CFAR_CA && c.CFARAlgorithm <= RSP_CFAR_GOSCA, RSP_EINVAL, "unknown CFARAlgorithm");
+  RSP_REQ(c.CFARAlgorithm >= RSP_CFAR_CA && c.CFARAlgorithm <= RSP_CFAR_OS_GOLDEN, RSP_EINVAL, "unknown CFARAlgorithm");
   if (c.includeCASH)
     RSP_REQ(c.minSubWindowSize > 0, RSP_EINVAL, "If includeCash parameter is set then minSubWindowSize needs to be defined as a positive value");
   if (p.hasGenerator) {
@@ -287,7 +287,7 @@ struct Plan {
 template <typename A>
 inline rsp_status plan_cfar_common(const rsp_chain_params &p, const Regs &r, int N, A &a, std::string &err) {
   const rsp_cfar_params &c = p.cfar;
-  a.core = (c.CFARAlgorithm == RSP_CFAR_CA) ? (c.includeCASH ? CORE_ASR : CORE_MEM) : CORE_LIS;   // CFARcore.scala:62-64
+  a.core = (c.CFARAlgorithm == RSP_CFAR_CA) ? (c.includeCASH ? CORE_ASR : CORE_MEM) : (c.CFARAlgorithm == RSP_CFAR_OS_GOLDEN ? CORE_OS : CORE_LIS);   // CFARcore.scala:62-64
   a.W = (int)r.cfar[RSP_CFAR_REG_WINDOWCELLS];
   a.G = (int)r.cfar[RSP_CFAR_REG_GUARDCELLS];
   a.div_sum = (int)r.cfar[RSP_CFAR_REG_DIVSUM];
@@ -315,6 +315,7 @@ inline rsp_status plan_cfar_common(const rsp_chain_params &p, const Regs &r, int
     err = "subWindowSize must be a power of 2 dividing windowCells"; return RSP_EINVAL; }
   // Peak grouping with guardCells = 0 on the Lis / ASR cores: the reference substitutes the ends of the reference windows for the
   // missing guard cells (CFARCoreWithLis.scala:191-192, CFARCoreWithASR.scala:326-327); that substitution is not built
+  if (a.core == CORE_OS && a.peak_grouping) { err = "peakGrouping does not exist in the cfarOS golden"; return RSP_EINVAL; }
   if (a.core != CORE_MEM && a.peak_grouping && a.G == 0) { err = "peakGrouping with guardCells = 0 is not built for the Lis / ASR cores"; return RSP_EUNSUPPORTED; }
   if (a.core != CORE_ASR && a.cfar_mode == 3) { /* MuxLookup default: smallestOf (CFARCoreWithMem.scala:138-141) */ }
   return RSP_OK;

@@ -74,7 +74,7 @@ __global__ void __launch_bounds__(Geo<S>::THREADS) chain_fixed_kernel(const FxAr
       __syncthreads();
       continue;
     }
-    const bool need_sums = !(a.core == CORE_LIS && a.cfar_algorithm == 1);
+    const bool need_sums = !((a.core == CORE_LIS && a.cfar_algorithm == 1) || a.core == CORE_OS);
     if (need_sums) {
       const int total = cfar_thread_total<S>(a, tl, bufM);
       const int offset = row_scan_exclusive<S>(total, c, tl, wsum);

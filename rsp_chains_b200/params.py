@@ -19,7 +19,9 @@ from . import _abi
 
 # CFARType objects (CFARParams.scala:10-22)
 CACFARType, GOSCFARType, GOSCACFARType = "CACFARType", "GOSCFARType", "GOSCACFARType"
-_CFAR_TYPES = {CACFARType: 0, GOSCFARType: 1, GOSCACFARType: 2}
+# not a CFARType of the reference: the combined-window ordered statistic of its Scala golden cfarOS (CFARUtils.scala:159-196)
+OSGoldenCFARType = "OSGoldenCFARType"
+_CFAR_TYPES = {CACFARType: 0, GOSCFARType: 1, GOSCACFARType: 2, OSGoldenCFARType: 3}
 # DecimType objects (SDFFFTParams.scala:18-20)
 DIFDecimType, DITDecimType = "DIFDecimType", "DITDecimType"
 # trim types

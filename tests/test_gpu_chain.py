@@ -272,7 +272,7 @@ def test_fast_gos_kernel_variants(cuda, oracle, log_n, W, G, kl, kr):
         run_and_compare(cuda, oracle, p, log_n, 2, regs, beats)
 
 
-@pytest.mark.parametrize("log_n", [10, 12])
+@pytest.mark.parametrize("log_n", [10, 12, 14])
 def test_fast_kernel_quiet_and_loud_rows(cuda, oracle, log_n):
     """the fast kernel leaves the 16-bit wraps of the butterflies out for rows whose beats are all within +-23150 (they cannot wrap)
     and keeps them for the others, warp by warp in the first pass and chirp by chirp afterwards: rows at the limit, one beat over it,

@@ -21,28 +21,7 @@ def f32_params(n, W, G, cfar_type=CACFARType):
         cfarParams=CFARParams(leadLaggWindowSize=W, guardWindowSize=G, fftSize=n, CFARAlgorithm=cfar_type, sendCut=False))
 
 
-def f64_chain(oracle, x, log_n, sel, regs, scaler, W, G):
-    """the DspReal dataflow in fp64: FFT/N (natural order), magnitude, CFARCoreWithMem edge policy"""
-    n = 1 << log_n
-    thr = np.zeros((x.shape[0], n)); peak = np.zeros((x.shape[0], n), np.uint8); mag = np.zeros((x.shape[0], n))
-    cfg = oracle.cfar_cfg(n, W, G, 0, core=oracle.CORE_MEM, cfar_mode=regs["cfarMode"], div_sum=regs["divSum"],
-                          log_or_linear=regs["logOrLinearMode"], peak_grouping=regs.get("peakGrouping", 0))
-    for r in range(x.shape[0]):
-        fr, fi = oracle.fft_f64(log_n, x[r].real, x[r].imag)
-        if sel == 2:
-            m = np.array([oracle.jpl_f64(a, b) for a, b in zip(fr, fi)])
-        elif sel == 1:
-            m = fr * fr + fi * fi
-        else:
-            m = np.log2(np.array([oracle.jpl_f64(a, b) for a, b in zip(fr, fi)]))
-        mag[r] = m
-        thr[r], peak[r] = oracle.cfar_f64(cfg, scaler, m)
-    return mag, thr, peak
-
-
-def unpack_mask(mask, n):
-    bits = np.unpackbits(mask.view(np.uint8), bitorder="little").reshape(mask.shape[0], -1)
-    return bits[:, :n]
+from oracle.glue import f64_chain, unpack_mask  # noqa: E402  (fp64 dataflow of the DspReal flavour, all three CFAR cores)
 
 
 @pytest.mark.parametrize("mode", [1, 2, 0])

@@ -1,0 +1,338 @@
+"""GPU parity, part 3 (through the C ABI): configurations that were built but untested after round 1 (VERDICT r01 "what's weak" 2-3):
+sendCut, LogMagMux bypass through the chain, the detection-list-only mode of the fast kernel, the fp32 flavour with the Lis / ASR cores,
+peak grouping and the other magnitude modes, C3 at its full row count, and the generator beyond one chirp type."""
+import numpy as np
+import pytest
+
+import rsp_chains_b200 as R
+from rsp_chains_b200 import synth
+from rsp_chains_b200.params import (CACFARType, CFARParams, FFTParams, FftMagCfarVanillaParameters, FixedPoint, GOSCFARType,
+                                    MAGParams)
+from oracle.glue import f64_chain, oracle_plfg, unpack_mask, write_plfg
+from tests.util import configure, decode_cfar_words, from_dev_u32, oracle_cfgs, to_dev
+
+pytestmark = pytest.mark.gpu
+REL_TOL = 1e-4
+
+
+def fixed_params(n, W, G, bp=0, ctype=CACFARType, send_cut=False, cash=False):
+    return FftMagCfarVanillaParameters(
+        fftParams=FFTParams.fixed(dataWidth=16, twiddleWidth=16, numPoints=n, useBitReverse=True, runTime=True, binPoint=bp),
+        magParams=MAGParams.fixed(dataWidth=16, binPoint=bp, dataWidthLog=16, binPointLog=9, log2LookUpWidth=9),
+        cfarParams=CFARParams(protoIn=FixedPoint(16, bp), protoThreshold=FixedPoint(16, bp), protoScaler=FixedPoint(16, 0),
+                              leadLaggWindowSize=W, guardWindowSize=G, fftSize=n, CFARAlgorithm=ctype, sendCut=send_cut,
+                              includeCASH=cash, minSubWindowSize=4 if cash else None))
+
+
+def run_fixed(cuda, p, log_n, sel, regs, beats, **kw):
+    n = 1 << log_n
+    with R.FftMagCfarChainVanilla(p) as ch:
+        configure(ch, log_n, sel, regs)
+        d_out = cuda.empty((beats.shape[0], n), dtype=cuda.int32, device="cuda")
+        ch.run(to_dev(cuda, beats), beats.shape[0], 1, out=d_out, **kw)
+        cuda.cuda.synchronize()
+        return from_dev_u32(d_out), ch.variant
+
+
+@pytest.mark.parametrize("ctype,cash", [(CACFARType, False), (GOSCFARType, False), (CACFARType, True)])
+@pytest.mark.parametrize("log_n", [9, 10])
+def test_send_cut_outputs_the_cell_under_test(cuda, oracle, log_n, ctype, cash):
+    """CFARParams.sendCut = true (CFARDspBlock.scala:78-79): the output beat is the cell under test, whatever the core"""
+    n = 1 << log_n
+    p = fixed_params(n, 16, 2, ctype=ctype, send_cut=True, cash=cash)
+    regs = dict(fftWin=n, thresholdScaler=3, logOrLinearMode=1, divSum=4, peakGrouping=0, cfarMode=0, windowCells=16, guardCells=2, indexLagg=12, indexLead=5,
+                subWindowSize=8)
+    beats = np.concatenate([synth.chirps_fixed(9, n, seed=log_n), synth.random_beats(3, n, seed=3)])
+    got, variant = run_fixed(cuda, p, log_n, 2, regs, beats)
+    fft, mag, cfar = oracle_cfgs(oracle, p, log_n, 2, regs)
+    want, _, want_mag = oracle.chain_fixed_words(fft, mag, cfar, beats, want_stages=True)
+    assert (got == want).all(), variant
+    assert (got == (want_mag & 0xFFFF)).all()        # the CUT is the magnitude beat's low half
+
+
+@pytest.mark.parametrize("log_n", [6, 10, 12])
+def test_mag_bypass_through_the_chain(cuda, oracle, log_n):
+    """LogMagMux sel = 0 (bypass, LogMagMux.scala:68-90) inside the chain: the CFAR sees the low 16 bits (imaginary part) of the FFT beat"""
+    n = 1 << log_n
+    W = 8 if log_n == 6 else 16
+    p = fixed_params(n, W, 2)
+    regs = dict(fftWin=n, thresholdScaler=2, logOrLinearMode=1, divSum=int(np.log2(W)), peakGrouping=0, cfarMode=1, windowCells=W, guardCells=2)
+    beats = np.concatenate([synth.chirps_fixed(6, n, seed=log_n + 40), synth.random_beats(4, n, seed=log_n)])
+    got, variant = run_fixed(cuda, p, log_n, 0, regs, beats)
+    fft, mag, cfar = oracle_cfgs(oracle, p, log_n, 0, regs)
+    want, want_fft, want_mag = oracle.chain_fixed_words(fft, mag, cfar, beats, want_stages=True)
+    assert (want_mag == want_fft).all()
+    assert (got == want).all(), variant
+
+
+@pytest.mark.parametrize("log_n", [10, 14])
+def test_fast_kernel_detection_list_only(cuda, oracle, log_n):
+    """rsp_run with d_out = NULL: the fast kernel builds no output beats and reports the same detections as the full run"""
+    n = 1 << log_n
+    W, G = (16, 4) if log_n == 10 else (64, 8)
+    p = fixed_params(n, W, G)
+    regs = dict(fftWin=n, thresholdScaler=4, logOrLinearMode=1, divSum=int(np.log2(W)), peakGrouping=0, cfarMode=0, windowCells=W, guardCells=G)
+    rows = 77 if log_n == 10 else 7
+    beats = synth.chirps_fixed(rows, n, seed=5 + log_n)
+    fft, mag, cfar = oracle_cfgs(oracle, p, log_n, 2, regs)
+    want, _, want_mag = oracle.chain_fixed_words(fft, mag, cfar, beats, want_stages=True)
+    thr, bins, peak = decode_cfar_words(want, n)
+    exp = {(r, b): (int(thr[r, b]), int(np.int16(want_mag[r, b] & 0xFFFF))) for r, b in np.argwhere(peak == 1)}
+    with R.FftMagCfarChainVanilla(p) as ch:
+        configure(ch, log_n, 2, regs)
+        assert ch.variant == f"chain_fixed_fast<{log_n}>"
+        det_list = cuda.zeros((1 << 16, 4), dtype=cuda.int32, device="cuda")
+        det_count = cuda.zeros(1, dtype=cuda.int32, device="cuda")
+        l0 = ch.kernel_launches
+        ch.run(to_dev(cuda, beats), rows, 1, out=None, det_list=det_list, det_count=det_count)
+        cuda.cuda.synchronize()
+        assert ch.kernel_launches == l0 + 1
+        k = int(det_count.item())
+        dets = det_list[:k].cpu().numpy()
+        # the host entry point with h_out = NULL
+        n_found = ch.run_host_dets_raw(np.ascontiguousarray(beats).ctypes.data, rows, 1, 1 << 16)
+        host = np.frombuffer(ch.last_detections, dtype=np.int32).reshape(-1, 4)[:n_found].copy()
+    assert k == len(exp) and k > 0
+    assert {(int(d[0]), int(d[1])): (int(d[2]) & 0xFFFF, int(d[3])) for d in dets} == exp
+    assert n_found == k and {(int(d[0]), int(d[1])): (int(d[2]) & 0xFFFF, int(d[3])) for d in host} == exp
+
+
+def test_peak_grouping_without_guard_cells_is_refused_on_lis_and_asr(cuda):
+    """the reference substitutes the window ends for the missing guard cells (CFARCoreWithLis.scala:191-192); not built -> RSP_EUNSUPPORTED"""
+    p = fixed_params(1024, 16, 2, ctype=GOSCFARType)
+    regs = dict(fftWin=1024, thresholdScaler=3, logOrLinearMode=1, peakGrouping=1, cfarMode=0, windowCells=16, guardCells=0, indexLagg=8, indexLead=8)
+    with R.FftMagCfarChainVanilla(p) as ch:
+        configure(ch, 10, 2, regs)
+        d = cuda.zeros((2, 1024), dtype=cuda.int32, device="cuda")
+        with pytest.raises(R.RspError) as e:
+            ch.run(d, 2, 1, out=d.clone())
+        assert e.value.status == R._abi.RSP_EUNSUPPORTED
+
+
+# ---------------------------------------------------------------------------------------------------- fp32 flavour
+def f32_params(n, W, G, ctype=CACFARType, cash=False):
+    return FftMagCfarVanillaParameters(
+        fftParams=FFTParams.DSPReal(numPoints=n, useBitReverse=True, runTime=True), magParams=MAGParams.fixed(),
+        cfarParams=CFARParams(leadLaggWindowSize=W, guardWindowSize=G, fftSize=n, CFARAlgorithm=ctype, sendCut=False,
+                              includeCASH=cash, minSubWindowSize=4 if cash else None))
+
+
+def run_f32(cuda, p, log_n, sel, regs, scaler, x32):
+    n, rows = 1 << log_n, x32.shape[0]
+    with R.FftMagCfarChainVanilla(p) as ch:
+        configure(ch, log_n, sel, regs)
+        ch.set_threshold_scaler_f32(scaler)
+        d_thr = cuda.empty((rows, n), dtype=cuda.float32, device="cuda")
+        d_mask = cuda.zeros((rows, max(1, n // 32)), dtype=cuda.int32, device="cuda")
+        ch.run(cuda.from_numpy(x32).cuda(), rows, 1, out=d_thr, peak_mask=d_mask)
+        cuda.cuda.synchronize()
+        return d_thr.cpu().numpy(), unpack_mask(d_mask.cpu().numpy().view(np.uint32), n), ch.variant
+
+
+def check_f32(thr, pk, mag, want_thr, want_pk, what):
+    scale = np.abs(want_thr).max()
+    rel = np.abs(thr - want_thr) / np.maximum(np.abs(want_thr), 1e-3 * scale)
+    assert rel.max() < REL_TOL, f"{what}: max relative threshold error {rel.max():.3e}"
+    sure = np.abs(mag - want_thr) / np.maximum(np.abs(want_thr), 1e-3 * scale) > 10 * REL_TOL
+    assert (pk[sure] == want_pk[sure]).all(), f"{what}: detections differ"
+    assert sure.mean() > 0.99
+
+
+@pytest.mark.parametrize("core", ["gos", "gos-ca", "cash", "asr-ca"])
+@pytest.mark.parametrize("pg", [0, 1])
+def test_fp32_lis_and_asr_cores(cuda, oracle, core, pg):
+    """the DspReal flavour with CFARCoreWithLis (ordered statistic and its cell-averaging mode) and CFARCoreWithASR (CASH and the
+    sub-window averages), with and without peak grouping: thresholds zero unless both windows are full (CFARCoreWithLis.scala:172-173)"""
+    log_n, W, G = 10, 16, 2
+    n = 1 << log_n
+    xc = synth.chirps_complex(6, n, seed=17)
+    xc[2] *= 1e-2
+    x32 = np.stack([xc.real, xc.imag], axis=-1).astype(np.float32)
+    xq = x32[..., 0].astype(np.float64) + 1j * x32[..., 1].astype(np.float64)
+    regs = dict(fftWin=n, logOrLinearMode=1, divSum=4, peakGrouping=pg, cfarMode=0, windowCells=W, guardCells=G, indexLagg=12, indexLead=6, subWindowSize=4)
+    kw = {}
+    if core == "gos":
+        p, kw = f32_params(n, W, G, GOSCFARType), dict(core=oracle.CORE_LIS, index_lagg=12, index_lead=6)
+    elif core == "gos-ca":
+        p, kw = f32_params(n, W, G, R.GOSCACFARType), dict(core=oracle.CORE_LIS)
+        regs["cfarAlgorithm"] = 0
+    elif core == "cash":
+        p, kw = f32_params(n, W, G, cash=True), dict(core=oracle.CORE_ASR, sub_cells=4)
+        regs["cfarMode"] = 3
+        regs["divSum"] = 2
+    else:
+        p, kw = f32_params(n, W, G, cash=True), dict(core=oracle.CORE_ASR, sub_cells=4)
+        regs["cfarMode"] = 1
+        regs["divSum"] = 2
+    for sel in (2, 1):
+        thr, pk, variant = run_f32(cuda, p, log_n, sel, regs, 3.0, x32)
+        assert variant == f"chain_f32<{log_n}>", variant
+        mag, want_thr, want_pk = f64_chain(oracle, xq, log_n, sel, regs, 3.0, W, G, **kw)
+        check_f32(thr, pk, mag, want_thr, want_pk, f"{core} pg {pg} sel {sel}")
+        assert (want_thr[:, :W + G] == 0).all() and (thr[:, :W + G] == 0).all()
+
+
+@pytest.mark.parametrize("sel", [1, 3])
+@pytest.mark.parametrize("pg", [0, 1])
+def test_fp32_mem_core_other_magnitudes_and_peak_grouping(cuda, oracle, sel, pg):
+    """|z|^2 and log2 magnitude, peak grouping, on the Mem core (log mode for the log2 magnitude: threshold = mean + scaler)"""
+    log_n, W, G = 11, 32, 4
+    n = 1 << log_n
+    xc = synth.chirps_complex(5, n, seed=23)
+    x32 = np.stack([xc.real, xc.imag], axis=-1).astype(np.float32)
+    xq = x32[..., 0].astype(np.float64) + 1j * x32[..., 1].astype(np.float64)
+    regs = dict(fftWin=n, logOrLinearMode=0 if sel == 3 else 1, divSum=5, peakGrouping=pg, cfarMode=0, windowCells=W, guardCells=G)
+    scaler = 2.0 if sel == 3 else 6.0
+    thr, pk, variant = run_f32(cuda, f32_params(n, W, G), log_n, sel, regs, scaler, x32)
+    assert variant.startswith("chain_f32")
+    mag, want_thr, want_pk = f64_chain(oracle, xq, log_n, sel, regs, scaler, W, G)
+    if sel == 3:      # log2 of a magnitude known to 1e-6 relative: absolute error ~1e-6 on values of order 10
+        assert np.abs(thr - want_thr).max() < 1e-4 * np.abs(want_thr).max()
+        sure = np.abs(mag - want_thr) > 1e-3
+        assert (pk[sure] == want_pk[sure]).all()
+    else:
+        check_f32(thr, pk, mag, want_thr, want_pk, f"sel {sel} pg {pg}")
+    assert want_pk.sum() >= 5
+
+
+def test_c3_full_frame_fp32(cuda, oracle):
+    """BASELINE config 2 at its full size: 4 RX x 512 chirps x 2048 points, fp32, GO-CFAR (W 32, G 4).  The fp64 dataflow checks the 16
+    distinct rows; the size-independent property is row independence: every replica of the 16-row block equals the first."""
+    n, log_n, W, G, n_rx, n_chirps = 2048, 11, 32, 4, 4, 512
+    rows = n_rx * n_chirps
+    xc = synth.chirps_complex(16, n, seed=3, rx_phase=np.repeat(np.arange(4) * np.pi / 8, 4))
+    x32 = np.stack([xc.real, xc.imag], axis=-1).astype(np.float32)
+    xq = x32[..., 0].astype(np.float64) + 1j * x32[..., 1].astype(np.float64)
+    regs = dict(fftWin=n, logOrLinearMode=1, divSum=5, peakGrouping=0, cfarMode=1, windowCells=W, guardCells=G)
+    with R.FftMagCfarChainVanilla(f32_params(n, W, G)) as ch:
+        configure(ch, log_n, 2, regs)
+        ch.set_threshold_scaler_f32(3.5)
+        assert ch.variant == "chain_f32_fast<11>"
+        d_in = cuda.from_numpy(x32).cuda().repeat(rows // 16, 1, 1).contiguous()
+        d_thr = cuda.empty((rows, n), dtype=cuda.float32, device="cuda")
+        d_mask = cuda.zeros((rows, n // 32), dtype=cuda.int32, device="cuda")
+        ch.run(d_in, n_chirps, n_rx, out=d_thr, peak_mask=d_mask)
+        cuda.cuda.synchronize()
+        assert bool((d_thr.view(rows // 16, 16, n) == d_thr[:16].unsqueeze(0)).all().item())
+        assert bool((d_mask.view(rows // 16, 16, n // 32) == d_mask[:16].unsqueeze(0)).all().item())
+        thr = d_thr[:16].cpu().numpy()
+        pk = unpack_mask(d_mask[:16].cpu().numpy().view(np.uint32), n)
+    mag, want_thr, want_pk = f64_chain(oracle, xq, log_n, 2, regs, 3.5, W, G)
+    check_f32(thr, pk, mag, want_thr, want_pk, "C3")
+    assert (pk == want_pk).all() and want_pk.sum() >= 32
+
+
+# ---------------------------------------------------------------------------------------------------- PLFG -> NCO generator
+CHIRPS = [[(3, 200, True, False), (5, 120, False, False)],                       # chirp 0: up, down
+          [(1, 255, True, False), (0, 40, False, True), (2, 180, False, False)],  # chirp 1: up, reset plateau, down
+          [(7, 1, True, False)],                                                  # chirp 2: nSamples 1 is bumped to 2
+          [(11, 90, False, False), (11, 90, True, False), (4, 33, True, False)]]  # chirp 3: down, up, up
+
+
+@pytest.mark.parametrize("nco_kw,plfg_kw", [
+    (dict(), dict()),                                                   # RspChainVanillaApp: phaseWidth 9, full-wave beat table
+    (dict(phaseAccEnable=False), dict()),                               # the PLFG word is the phase
+    (dict(phaseWidth=14, tableSize=1024), dict()),                      # phaseWidth > 12: the in-kernel quarter-wave look-up (nco_lookup)
+    (dict(phaseWidth=14, tableSize=256, tableWidth=12), dict()),        # phase bits below the table address are dropped
+    (dict(phaseWidth=14, tableSize=1024), dict(outputWidthInt=12, outputWidthFrac=4)),   # config word sliced at outputWidthInt
+])
+@pytest.mark.parametrize("frame_num,inter", [(3, 9), (0, 5), (2, 1)])
+def test_generator_many_chirp_types_frames_and_pauses(cuda, oracle, nco_kw, plfg_kw, frame_num, inter):
+    """four chirp types addressed through chirpOrdinalNums, repeated chirps, finite frameNum crossing two inter-frame pauses (RTL
+    pause length, PLFGDspBlockMem.scala:242-275) and the period wrap of an endless schedule; PLFG words and NCO beats bit-exact, then
+    the chain fed by the generator (rsp_run_from_generator)"""
+    p = R.rsp_chain_vanilla_app_params()
+    for k, v in nco_kw.items():
+        setattr(p.ncoParams, k, v)
+    for k, v in plfg_kw.items():
+        setattr(p.plfgParams, k, v)
+    order, repeats = [2, 0, 1, 3, 0], [2, 1, 3, 1, 2]
+    regs = dict(fftWin=1024, thresholdScaler=4, logOrLinearMode=1, divSum=5, peakGrouping=0, cfarMode=0, windowCells=32, guardCells=4)
+    start = 37
+    op = oracle_plfg(oracle, p, start, CHIRPS, order, repeats, frame_num, inter)
+    frame_len = 2 * 2 + 320 + 3 * 475 + 213 + 2 * 320
+    total = frame_num * frame_len + (frame_num - 1) * max(inter - 1, 0) if frame_num else 6 * frame_len + 100
+    n_rows = min(total // 1024, 6)
+    with R.RspChainVanilla(p) as ch:
+        configure(ch, 10, 2, regs)
+        write_plfg(ch, p, oracle, start, CHIRPS, order, repeats, frame_num, inter)
+        d_nco = cuda.zeros(total, dtype=cuda.int32, device="cuda")
+        d_plfg = cuda.zeros(total, dtype=cuda.int32, device="cuda")
+        ch.generate(total, d_nco, d_plfg)
+        d_out = cuda.zeros((n_rows, 1024), dtype=cuda.int32, device="cuda")
+        ch.run_from_generator(n_rows, 1, out=d_out)
+        cuda.cuda.synchronize()
+        got_nco, got_plfg, got_out = from_dev_u32(d_nco), d_plfg.cpu().numpy(), from_dev_u32(d_out)
+        if frame_num:   # the schedule ends after frameNum frames: one sample more is refused
+            with pytest.raises(R.RspError):
+                ch.generate(total + 1, cuda.zeros(total + 1, dtype=cuda.int32, device="cuda"), None)
+    want_plfg = op.run(total)
+    assert len(want_plfg) == total
+    assert (got_plfg == want_plfg).all(), f"first difference at {np.argwhere(got_plfg != want_plfg)[:3].ravel()}"
+    n = p.ncoParams
+    want_nco, _ = oracle.nco_words(want_plfg, n.tableSize, n.tableWidth, n.phaseWidth, n.phaseAccEnable)
+    assert (got_nco == want_nco).all(), f"first difference at {np.argwhere(got_nco != want_nco)[:3].ravel()}"
+    fft, mag, cfar = oracle_cfgs(oracle, p, 10, 2, regs)
+    want_out = oracle.chain_fixed_words(fft, mag, cfar, want_nco[:n_rows * 1024].reshape(n_rows, 1024))
+    assert (got_out == want_out).all()
+
+
+def test_generator_refuses_a_pause_the_hardware_never_leaves(cuda, oracle):
+    """framePauseCounter is UInt(6.W): interframeNumOfSamples >= 64 never restarts the frame (PLFGDspBlockMem.scala:144,262)"""
+    p = R.rsp_chain_vanilla_app_params()
+    with R.RspChainVanilla(p) as ch:
+        write_plfg(ch, p, oracle, 0, CHIRPS[:1], frame_num=2, inter=64)
+        with pytest.raises(R.RspError) as e:
+            ch.generate(100, cuda.zeros(100, dtype=cuda.int32, device="cuda"), None)
+        assert e.value.status == R._abi.RSP_EUNSUPPORTED
+
+
+# ---------------------------------------------------------------------------------------------------- C4 reading (B): golden cfarOS
+def test_c4_reading_b_combined_window_os(cuda, oracle):
+    """BASELINE configs[3], reading (B) of "ref window 64, k = 48": the Scala golden cfarOS (CFARUtils.scala:159-196) with
+    referenceCells = 32 per side -> 64 cells in one sorted window, ascending index floor(1.5 * 32) = 48.  Full chain on 4096-point rows
+    (bit-exact against the oracle's integer core, itself equal to the golden, tests/test_oracle_cfar.py) and CFAR alone on stored
+    16-bit magnitude profiles (exponential clutter + targets) checked against the golden directly."""
+    n, log_n, Rc, G = 4096, 12, 32, 4
+    p = fixed_params(n, 64, G, ctype=R.OSGoldenCFARType)
+    regs = dict(fftWin=n, thresholdScaler=2, logOrLinearMode=1, peakGrouping=0, cfarMode=0, windowCells=Rc, guardCells=G)
+    beats = np.concatenate([synth.chirps_fixed(5, n, seed=44), synth.random_beats(2, n, seed=45)])
+    got, variant = run_fixed(cuda, p, log_n, 2, regs, beats)
+    fft, mag, cfar = oracle_cfgs(oracle, p, log_n, 2, regs)
+    want = oracle.chain_fixed_words(fft, mag, cfar, beats)
+    assert (got == want).all(), variant
+    # CFAR alone on stored profiles
+    rng = np.random.default_rng(4)
+    prof = np.floor(rng.exponential(256.0, (6, n))).astype(np.int32)
+    prof[:, [300, 1200, 2500, 3900]] += 4096
+    pw = fixed_params(n, 64, G, ctype=R.OSGoldenCFARType)
+    pw.cfarParams.protoThreshold = FixedPoint(18, 0)       # room for 2 * (clutter + target)
+    with R.FftMagCfarChainVanilla(pw) as ch:
+        configure(ch, log_n, 2, regs)
+        d_out = cuda.empty((6, n), dtype=cuda.int32, device="cuda")
+        ch.cfar(to_dev(cuda, prof.astype(np.uint32)), 6, out=d_out)
+        cuda.cuda.synchronize()
+        out = from_dev_u32(d_out)
+    thr, bins, peak = out >> 13, (out >> 1) & 4095, out & 1
+    for r in range(6):
+        g_thr, g_peaks = oracle.golden_cfar_os(prof[r].astype(np.float64), Rc, G, 2.0)
+        assert (thr[r] == g_thr.astype(np.int64)).all()
+        assert np.flatnonzero(peak[r]).tolist() == sorted(set(g_peaks.tolist()))
+    assert (bins == np.arange(n)[None, :]).all() and peak.sum() >= 24
+
+
+def test_fp32_combined_window_os(cuda, oracle):
+    """the same statistic in the DspReal flavour: the threshold is one of the magnitudes times the scaler"""
+    log_n, W, G = 11, 32, 4
+    n = 1 << log_n
+    xc = synth.chirps_complex(4, n, seed=29)
+    x32 = np.stack([xc.real, xc.imag], axis=-1).astype(np.float32)
+    xq = x32[..., 0].astype(np.float64) + 1j * x32[..., 1].astype(np.float64)
+    regs = dict(fftWin=n, logOrLinearMode=1, peakGrouping=0, cfarMode=0, windowCells=W, guardCells=G)
+    thr, pk, variant = run_f32(cuda, f32_params(n, 64, G, R.OSGoldenCFARType), log_n, 2, regs, 2.5, x32)
+    assert variant == f"chain_f32<{log_n}>"
+    mag, want_thr, want_pk = f64_chain(oracle, xq, log_n, 2, regs, 2.5, W, G, core=oracle.CORE_OS)
+    check_f32(thr, pk, mag, want_thr, want_pk, "fp32 OS")
+    for r in range(4):
+        g_thr, g_peaks = oracle.golden_cfar_os(mag[r], W, G, 2.5)
+        assert np.allclose(want_thr[r], g_thr, rtol=0, atol=0)
