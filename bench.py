@@ -169,7 +169,9 @@ def time_oracle(beats, target_s=12.0):
 def host_rows(frame: int):
     """DISTINCT_ROWS chirps of frame `frame` (its own seed: every rank / frame processes different data)"""
     from rsp_chains_b200 import synth
-    return synth.chirps_fixed(DISTINCT_ROWS, N_POINTS, seed=11110 + frame)
+    # noise 2^-2 of full scale: after the 1/N of the scale-every-stage transform the noise floor of a 16384-point row is ~16 LSB
+    # (at the 2^-7 of the 1024-point recipe it would quantise to 0 and every second bin would be a "detection")
+    return synth.chirps_fixed(DISTINCT_ROWS, N_POINTS, seed=11110 + frame, noise=2.0 ** -2)
 
 
 def run_reference(args):

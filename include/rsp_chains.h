@@ -32,7 +32,7 @@
 extern "C" {
 #endif
 
-#define RSP_ABI_VERSION 1
+#define RSP_ABI_VERSION 2
 
 typedef enum {
   RSP_OK = 0,
@@ -61,9 +61,9 @@ typedef enum {
 /* FFTParams.fixed (generators/sdf-fft/src/main/scala/SDFFFTParams.scala:22-46,90-149) */
 typedef struct {
   int32_t numPoints;        /* power of two, 2..16384                                                    */
-  int32_t dataWidth;        /* 2..16 (protoIQ = FixedPoint(dataWidth.W, binPoint.BP))                    */
+  int32_t dataWidth;        /* 2..16 in a chain; 17..32 for the FFT block alone (wide beats, see rsp_fft_run) */
   int32_t binPoint;
-  int32_t twiddleWidth;     /* 3..16, twiddles are Q2.(twiddleWidth-2) (:116)                             */
+  int32_t twiddleWidth;     /* 3..16 in a chain, up to 32 for the wide FFT block; twiddles are Q2.(twiddleWidth-2) (:116) */
   int32_t trimType;         /* rsp_trim, used by div2 / context_* / trimBinary                            */
   int32_t use4Muls;         /* complexUse4Muls                                                            */
   int32_t useBitReverse;    /* 1: natural-order output (BitReversePingPong), 0: bit-reversed              */
@@ -72,7 +72,8 @@ typedef struct {
   uint32_t keepMSBorLSB;    /* bit i = keepMSBorLSB(i): 1 scale by 1/2 with trimType, 0 keep LSBs (wrap)   */
   int32_t decimType;        /* 0 = DIFDecimType, 1 = DITDecimType (either radix, fixed point and fp32)                   */
   int32_t sdfRadix;         /* 4 = "2^2" (SDFChainRadix22.scala), 2 = "2" (SDFChainRadix2.scala)            */
-  int32_t expandLogicAny;   /* 1 if any expandLogic(i) != 0 (grow mode -> RSP_EUNSUPPORTED)                */
+  uint32_t expandLogic;     /* bit i = expandLogic(i): stage i keeps the grown butterfly outputs in a type one bit wider
+                             * (SDFFFTParams.scala:119-123, SDFChainRadix22.scala:453-457); radix 2^2 DIF, FFT block alone (wide beats) */
   int32_t keepMSBorLSBReg;  /* 1: the keepMSBorLSBReg register overrides keepMSBorLSB (FFTBlock.scala:92-93)   */
   int32_t fftDirReg;        /* 1: the fftDir register overrides fftDir (FFTBlock.scala:90-91)                 */
   /* windowFunc (generators/sdf-fft/src/main/scala/WindowFunc.scala:10-38): the coefficient ROM of numPoints entries of type
@@ -81,6 +82,9 @@ typedef struct {
   int32_t windowFunc;       /* rsp_window; RSP_WINDOW_NONE = no multiply                                    */
   int32_t windowWidth;      /* WindowFunctionType.dataWidth, 3..16                                           */
   double windowA0, windowA1, windowA2;   /* Hamming: alpha, beta; Blackman: a0, a1, a2 (WindowFunc.scala:13-28)      */
+  int32_t overflowReg;      /* FFTParams.overflowReg: the per-stage overflow status is computed (RSP_FFT_REG_OVERFLOW, rsp_fft_overflow_flags);
+                             * such a chain runs on the run-time-parameter kernels                                                      */
+  int32_t reserved_;
 } rsp_fft_params;
 typedef enum { RSP_WINDOW_NONE = 0, RSP_WINDOW_HAMMING = 1, RSP_WINDOW_HANNING = 2, RSP_WINDOW_BLACKMAN = 3, RSP_WINDOW_TRIANGULAR = 4,
                RSP_WINDOW_USER = 5 } rsp_window;
@@ -220,6 +224,19 @@ rsp_status rsp_run_from_generator(rsp_chain *c, uint32_t n_chirps, uint32_t n_rx
 /* ---- single blocks (each reference DspBlock is usable on its own) ----------------------------------------- */
 /* replaces AXI4FFTBlock (generators/sdf-fft/src/main/scala/FFTBlock.scala:122-124): beats in -> beats out */
 rsp_status rsp_fft_run(rsp_chain *c, const void *d_in, uint32_t n_chirps, void *d_out, void *stream);
+/* Wide FFT block (dataWidth > 16, twiddleWidth > 16 or expandLogic != 0; radix 2^2 DIF; numPoints <= 8192): beats are 64 bits wide
+ * in (the low 2 * dataWidth bits are Cat(re, im), `in.bits.data.asTypeOf(params.protoIQ)`, FFTBlock.scala:106) and
+ * rsp_fft_out_beat_bytes() wide out: Cat(re, im) of the last stage's type, dataWidth + sum(expandLogic) bits per half
+ * (`fft.io.out.bits.asUInt`, :113), one uint64, or two (low word first) when that needs more than 64 bits.  rsp_run (the chain) refuses
+ * such a configuration: LogMagMux and CFAR take 16-bit cells. */
+uint32_t rsp_fft_in_beat_bytes(rsp_chain *c);    /* 4 or 8 */
+uint32_t rsp_fft_out_beat_bytes(rsp_chain *c);   /* 4, 8 or 16 */
+/* FFTParams.overflowReg = 1: the per-stage overflow status of the handle's most recent rsp_fft_run / rsp_run call on `stream`
+ * (waits for it): bit i = some butterfly of PHYSICAL stage i produced a sum or difference at or above 2^(w - 1), w the width of the
+ * stage's input type (`tooBig`, SDFChainRadix22.scala:473-481; the check looks at the value before div2, so it also reports stages
+ * that scale).  The hardware register reloads every clock; this is its OR over the call.  RSP_FFT_REG_OVERFLOW reads the same word
+ * through the reference's log2Ceil(numStages)-bit field (FFTBlock.scala:67,97), i.e. its low bits only. */
+rsp_status rsp_fft_overflow_flags(rsp_chain *c, uint32_t *mask, void *stream);
 /* replaces AXI4LogMagMuxBlock (generators/logMagMux/src/main/scala/LogMagMuxDspBlock.scala:59-61); n_beats beats */
 rsp_status rsp_mag_run(rsp_chain *c, const void *d_in, uint64_t n_beats, void *d_out, void *stream);
 /* replaces AXI4CFARBlock (generators/cfar/src/main/scala/CFARDspBlock.scala:134-136): n_chirps rows of fftWin beats

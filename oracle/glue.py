@@ -14,8 +14,12 @@ def oracle_cfgs(O, params, log_n, sel, cfar_regs: dict):
     dit = f.decimType == DITDecimType
     # a run-time size of k stages is the LAST k stages in DIF, the FIRST k in DIT (SDFChainRadix2.scala:127-134,196-203)
     mask = (mask if dit else (mask >> (smax - log_n))) & ((1 << log_n) - 1)
+    # grow stages (DIF): a run-time size keeps the last log_n stages; the ones in front have already widened the types
+    emask = sum((1 if e else 0) << i for i, e in enumerate(f.expandLogic))
+    expand = (emask >> (smax - log_n)) & ((1 << log_n) - 1)
+    base_growth = bin(emask & ((1 << (smax - log_n)) - 1)).count("1")
     fft = O.fft_cfg(log_n, f.dataWidth, f.binPoint, f.twiddleWidth, f.trimType, f.use4Muls, f.useBitReverse, mask, f.fftDir,
-                    f.sdfRadix, dit, smax)
+                    f.sdfRadix, dit, smax, expand_mask=expand, base_growth=base_growth)
     mag = O.mag_cfg(m.dataWidth, m.binPoint, m.dataWidthLog, m.binPointLog, m.log2LookUpWidth, sel)
     if c.CFARAlgorithm == CACFARType:
         core = O.CORE_ASR if c.includeCASH else O.CORE_MEM

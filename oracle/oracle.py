@@ -39,7 +39,8 @@ class FftCfg(C.Structure):
     _fields_ = [("log_n", C.c_int32), ("data_width", C.c_int32), ("bin_point", C.c_int32),
                 ("twiddle_width", C.c_int32), ("trim_type", C.c_int32), ("use4muls", C.c_int32),
                 ("bit_reverse", C.c_int32), ("keep_msb_mask", C.c_uint32), ("fft_dir", C.c_int32),
-                ("sdf_radix", C.c_int32), ("decim_dit", C.c_int32), ("num_stages", C.c_int32)]
+                ("sdf_radix", C.c_int32), ("decim_dit", C.c_int32), ("num_stages", C.c_int32),
+                ("expand_mask", C.c_uint32), ("base_growth", C.c_int32)]
 
 
 class MagCfg(C.Structure):
@@ -120,11 +121,12 @@ def _f64(a):
 # ---------------------------------------------------------------------------------------------- configs
 
 def fft_cfg(log_n, data_width=16, bin_point=14, twiddle_width=16, trim="RoundHalfUp", use4muls=False,
-            bit_reverse=True, keep_msb_mask=0xFFFFFFFF, fft_dir=True, sdf_radix="2^2", decim_dit=False, num_stages=0) -> FftCfg:
+            bit_reverse=True, keep_msb_mask=0xFFFFFFFF, fft_dir=True, sdf_radix="2^2", decim_dit=False, num_stages=0,
+            expand_mask=0, base_growth=0) -> FftCfg:
     """sdf_radix "2" selects SDFChainRadix2 (DIF or DIT); "2^2" SDFChainRadix22 (DIF only)"""
     return FftCfg(log_n, data_width, bin_point, twiddle_width, TRIM[trim] if isinstance(trim, str) else trim,
                   int(use4muls), int(bit_reverse), keep_msb_mask & 0xFFFFFFFF, int(fft_dir),
-                  2 if str(sdf_radix) == "2" else 4, int(decim_dit), int(num_stages))
+                  2 if str(sdf_radix) == "2" else 4, int(decim_dit), int(num_stages), expand_mask & 0xFFFFFFFF, int(base_growth))
 
 
 def mag_cfg(data_width=16, bin_point=14, data_width_log=16, bin_point_log=9, log2_lookup_width=9, sel=2,
@@ -197,6 +199,50 @@ def fft_fixed(cfg: FftCfg, re, im):
     if rc:
         raise ValueError(f"rspo_fft_fixed rc={rc}")
     return ore, oim
+
+
+def fft_fixed_ex(cfg: FftCfg, re, im):
+    """as fft_fixed, plus the per-stage overflow mask (SDFChainRadix22.scala:473-486)"""
+    re, im = _i32(re), _i32(im)
+    n = 1 << cfg.log_n
+    ore, oim = np.zeros(n, np.int32), np.zeros(n, np.int32)
+    m = C.c_uint32(0)
+    rc = lib().rspo_fft_fixed_ex(C.byref(cfg), _p(re, C.c_int32), _p(im, C.c_int32), _p(ore, C.c_int32), _p(oim, C.c_int32), C.byref(m))
+    if rc:
+        raise ValueError(f"rspo_fft_fixed_ex rc={rc}")
+    return ore, oim, m.value
+
+
+def fft_stage_width(cfg: FftCfg, stage):
+    return int(lib().rspo_fft_stage_width(C.byref(cfg), int(stage)))
+
+
+def fft_fixed_words64(cfg: FftCfg, words):
+    """64-bit beats Cat(re, im) (wide data / grow stages); returns (beats, overflow mask)"""
+    words = np.ascontiguousarray(words, dtype=np.uint64)
+    n = 1 << cfg.log_n
+    flat = words.reshape(-1)
+    assert flat.size % n == 0
+    wo = fft_stage_width(cfg, cfg.log_n - 1)
+    k = 2 if 2 * wo > 64 else 1          # 128-bit beats: two words per beat, low word first
+    out = np.zeros(flat.size * k, np.uint64)
+    m = C.c_uint32(0)
+    rc = lib().rspo_fft_fixed_words64(C.byref(cfg), _p(flat, C.c_uint64), _p(out, C.c_uint64), flat.size // n, C.byref(m))
+    if rc:
+        raise ValueError(f"rspo_fft_fixed_words64 rc={rc}")
+    return (out.reshape(words.shape) if k == 1 else out.reshape(words.shape + (2,))), m.value
+
+
+def fft_fixed_words_ovf(cfg: FftCfg, words):
+    words = _u32(words)
+    n = 1 << cfg.log_n
+    flat = words.reshape(-1)
+    out = np.zeros_like(flat)
+    m = C.c_uint32(0)
+    rc = lib().rspo_fft_fixed_words_ovf(C.byref(cfg), _p(flat, C.c_uint32), _p(out, C.c_uint32), flat.size // n, C.byref(m))
+    if rc:
+        raise ValueError(f"rspo_fft_fixed_words_ovf rc={rc}")
+    return out.reshape(words.shape), m.value
 
 
 def fft_f64(log_n, re, im, bit_reverse=True):

@@ -208,8 +208,9 @@ static int fft_tabs_build(fft_tabs *t, const rspo_fft_cfg *cfg) {
  * output (:26, SDFFFT.scala:217-270: with useBitReverse the ping-pong buffer sits behind DIF / in front of DIT).
  * A run-time size of k stages is the last k stages in DIF and the first k in DIT (:127-134,196-203); the caller's
  * keep_msb_mask is already aligned to the stages of THIS transform. */
+static inline int bf_too_big(int64_t v, int w_in);
 static int fft_fixed_core_radix2(const rspo_fft_cfg *cfg, const fft_tabs *tabs, int64_t *xr, int64_t *xi,
-                                 const int32_t *in_re, const int32_t *in_im, int32_t *out_re, int32_t *out_im) {
+                                 const int64_t *in_re, const int64_t *in_im, int64_t *out_re, int64_t *out_im, uint32_t *ovf) {
   const int S = cfg->log_n, N = 1 << S;
   const int w = cfg->data_width, tbp = cfg->twiddle_width - 2, trim = cfg->trim_type;
   const int dit = cfg->decim_dit;
@@ -232,6 +233,7 @@ static int fft_fixed_core_radix2(const rspo_fft_cfg *cfg, const fft_tabs *tabs, 
         }
         const int64_t sr = xr[p0] + xr[p1], si = xi[p0] + xi[p1];
         const int64_t dr = xr[p0] - xr[p1], di = xi[p0] - xi[p1];
+        if (ovf && (bf_too_big(sr, w) || bf_too_big(si, w) || bf_too_big(dr, w) || bf_too_big(di, w))) *ovf |= 1u << i;
         if (scale) {
           xr[p0] = rspo_wrap(rspo_trim(sr, 1, trim), w); xi[p0] = rspo_wrap(rspo_trim(si, 1, trim), w);
           xr[p1] = rspo_wrap(rspo_trim(dr, 1, trim), w); xi[p1] = rspo_wrap(rspo_trim(di, 1, trim), w);
@@ -248,8 +250,8 @@ static int fft_fixed_core_radix2(const rspo_fft_cfg *cfg, const fft_tabs *tabs, 
   }
   for (int n = 0; n < N; ++n) {
     const int p = (!dit && cfg->bit_reverse) ? (int)bitrev((uint32_t)n, S) : n;
-    out_re[n] = (int32_t)(cfg->fft_dir ? xr[p] : xi[p]); /* ifft: swap on the way out, scalar 1.0 (:280,289-300) */
-    out_im[n] = (int32_t)(cfg->fft_dir ? xi[p] : xr[p]);
+    out_re[n] = (cfg->fft_dir ? xr[p] : xi[p]); /* ifft: swap on the way out, scalar 1.0 (:280,289-300) */
+    out_im[n] = (cfg->fft_dir ? xi[p] : xr[p]);
   }
   return 0;
 }
@@ -264,7 +266,7 @@ static int fft_fixed_core_radix2(const rspo_fft_cfg *cfg, const fft_tabs *tabs, 
  *   otherwise: x(-j) on positions [3D/2, 2D) of every 2D block (:323,339-342).
  * Butterfly / div2 / keep-LSB as in every stage (:459-493).  A run-time size of k stages is the first k stages (:145-147,216-217). */
 static int fft_fixed_core_r22_dit(const rspo_fft_cfg *cfg, const fft_tabs *tabs, int64_t *xr, int64_t *xi,
-                                  const int32_t *in_re, const int32_t *in_im, int32_t *out_re, int32_t *out_im) {
+                                  const int64_t *in_re, const int64_t *in_im, int64_t *out_re, int64_t *out_im, uint32_t *ovf) {
   const int S = cfg->log_n, N = 1 << S;
   const int w = cfg->data_width, bp = cfg->bin_point, tw = cfg->twiddle_width, trim = cfg->trim_type;
   const int smax = cfg->num_stages > 0 ? cfg->num_stages : S;
@@ -298,6 +300,7 @@ static int fft_fixed_core_r22_dit(const rspo_fft_cfg *cfg, const fft_tabs *tabs,
         const int p0 = b + k, p1 = b + k + D;
         const int64_t sr = xr[p0] + xr[p1], si = xi[p0] + xi[p1];
         const int64_t dr = xr[p0] - xr[p1], di = xi[p0] - xi[p1];
+        if (ovf && (bf_too_big(sr, w) || bf_too_big(si, w) || bf_too_big(dr, w) || bf_too_big(di, w))) *ovf |= 1u << i;
         if (scale) {
           xr[p0] = rspo_wrap(rspo_trim(sr, 1, trim), w); xi[p0] = rspo_wrap(rspo_trim(si, 1, trim), w);
           xr[p1] = rspo_wrap(rspo_trim(dr, 1, trim), w); xi[p1] = rspo_wrap(rspo_trim(di, 1, trim), w);
@@ -314,27 +317,47 @@ static int fft_fixed_core_r22_dit(const rspo_fft_cfg *cfg, const fft_tabs *tabs,
   return 0;
 }
 
+/* `tooBig` of the overflow check (SDFChainRadix22.scala:473-481) on a butterfly output grown from w_in to w_in + 1 bits */
+static inline int bf_too_big(int64_t v, int w_in) { return v >= ((int64_t)1 << (w_in - 1)); }
+#define BF_OVERFLOW(sr, si, dr, di, w_in) (bf_too_big(sr, w_in) || bf_too_big(si, w_in) || bf_too_big(dr, w_in) || bf_too_big(di, w_in))
+
+int rspo_fft_stage_width(const rspo_fft_cfg *cfg, int stage) {
+  int w = cfg->data_width + cfg->base_growth;
+  for (int i = 0; i <= stage; ++i) w += (cfg->expand_mask >> i) & 1;
+  return w;
+}
+
 static int fft_fixed_core(const rspo_fft_cfg *cfg, const fft_tabs *tabs, int64_t *xr, int64_t *xi,
-                          const int32_t *in_re, const int32_t *in_im, int32_t *out_re, int32_t *out_im) {
+                          const int64_t *in_re, const int64_t *in_im, int64_t *out_re, int64_t *out_im, uint32_t *ovf) {
   const int S = cfg->log_n;
   const int N = 1 << S;
-  const int w = cfg->data_width, bp = cfg->bin_point, tw = cfg->twiddle_width, trim = cfg->trim_type;
-  if (cfg->sdf_radix == 2) return fft_fixed_core_radix2(cfg, tabs, xr, xi, in_re, in_im, out_re, out_im);
-  if (cfg->decim_dit) return fft_fixed_core_r22_dit(cfg, tabs, xr, xi, in_re, in_im, out_re, out_im);
+  const int w0 = cfg->data_width, bp = cfg->bin_point, tw = cfg->twiddle_width, trim = cfg->trim_type;
+  if (ovf) *ovf = 0;
+  if ((cfg->expand_mask || cfg->base_growth) && (cfg->sdf_radix == 2 || cfg->decim_dit)) return -3; /* grow: radix 2^2 DIF only here */
+  if (cfg->sdf_radix == 2) return fft_fixed_core_radix2(cfg, tabs, xr, xi, in_re, in_im, out_re, out_im, ovf);
+  if (cfg->decim_dit) return fft_fixed_core_r22_dit(cfg, tabs, xr, xi, in_re, in_im, out_re, out_im, ovf);
   for (int p = 0; p < N; ++p) {
     /* ifft swaps real and imaginary on the way in (SDFChainRadix22.scala:205-211) */
-    xr[p] = rspo_wrap(cfg->fft_dir ? in_re[p] : in_im[p], w);
-    xi[p] = rspo_wrap(cfg->fft_dir ? in_im[p] : in_re[p], w);
+    xr[p] = rspo_wrap(cfg->fft_dir ? in_re[p] : in_im[p], w0);
+    xi[p] = rspo_wrap(cfg->fft_dir ? in_im[p] : in_re[p], w0);
   }
   for (int i = 0; i < S; ++i) {
     const int D = 1 << (S - 1 - i); /* SDFChainRadix22.scala:27,33 */
     const int scale = (cfg->keep_msb_mask >> i) & 1;
+    const int grow = (cfg->expand_mask >> i) & 1;            /* useGrow (:156,453-457) */
+    const int w = rspo_fft_stage_width(cfg, i);              /* protoIQstages(i) (SDFFFTParams.scala:119-123) */
+    const int w_in = w - grow;                               /* the type the butterfly's inputs arrive in */
     for (int b = 0; b < N; b += 2 * D)
       for (int k = 0; k < D; ++k) {
         const int p0 = b + k, p1 = b + k + D;
         /* Butterfly: context_+ / context_- with Grow (SDFFFTUtil.scala:54-59) */
         const int64_t sr = xr[p0] + xr[p1], si = xi[p0] + xi[p1];
         const int64_t dr = xr[p0] - xr[p1], di = xi[p0] - xi[p1];
+        if (grow) { /* the grown outputs are kept as they are; no overflow possible (:454-457) */
+          xr[p0] = sr; xi[p0] = si; xr[p1] = dr; xi[p1] = di;
+          continue;
+        }
+        if (ovf && BF_OVERFLOW(sr, si, dr, di, w_in)) *ovf |= 1u << i;
         if (scale) { /* div2(1), binaryPointGrowth 0, trimType (SDFChainRadix22.scala:459-464), stored to protoIQ (:492-493) */
           xr[p0] = rspo_wrap(rspo_trim(sr, 1, trim), w); xi[p0] = rspo_wrap(rspo_trim(si, 1, trim), w);
           xr[p1] = rspo_wrap(rspo_trim(dr, 1, trim), w); xi[p1] = rspo_wrap(rspo_trim(di, 1, trim), w);
@@ -367,22 +390,31 @@ static int fft_fixed_core(const rspo_fft_cfg *cfg, const fft_tabs *tabs, int64_t
     /* DIF output is bit-reversed; BitReversePingPong reads at Reverse(cnt) (BitReversePingPong.scala:93-109) */
     const int p = cfg->bit_reverse ? (int)bitrev((uint32_t)n, S) : n;
     /* ifft swaps again on the way out; scalar is 1.0 when no stage grows (:362,366-372) */
-    out_re[n] = (int32_t)(cfg->fft_dir ? xr[p] : xi[p]);
-    out_im[n] = (int32_t)(cfg->fft_dir ? xi[p] : xr[p]);
+    out_re[n] = (cfg->fft_dir ? xr[p] : xi[p]);
+    out_im[n] = (cfg->fft_dir ? xi[p] : xr[p]);
   }
   return 0;
 }
 
 int rspo_fft_fixed(const rspo_fft_cfg *cfg, const int32_t *in_re, const int32_t *in_im, int32_t *out_re,
                    int32_t *out_im) {
+  return rspo_fft_fixed_ex(cfg, in_re, in_im, out_re, out_im, NULL);
+}
+
+int rspo_fft_fixed_ex(const rspo_fft_cfg *cfg, const int32_t *in_re, const int32_t *in_im, int32_t *out_re, int32_t *out_im,
+                      uint32_t *overflow_mask) {
   const int S = cfg->log_n;
   if (S < 1 || S > 24 || cfg->data_width < 2 || cfg->data_width > 32) return -1;
+  if (rspo_fft_stage_width(cfg, S - 1) > 32) return -1; /* int32 interface; wider results through rspo_fft_fixed_words64 */
   const int N = 1 << S;
   fft_tabs tabs;
   if (fft_tabs_build(&tabs, cfg)) return -2;
-  int64_t *xr = (int64_t *)malloc(sizeof(int64_t) * 2 * (size_t)N);
+  int64_t *xr = (int64_t *)malloc(sizeof(int64_t) * 6 * (size_t)N);
   if (!xr) { fft_tabs_free(&tabs); return -2; }
-  const int rc = fft_fixed_core(cfg, &tabs, xr, xr + N, in_re, in_im, out_re, out_im);
+  int64_t *ir = xr + 2 * N, *ii = xr + 3 * N, *orr = xr + 4 * N, *oi = xr + 5 * N;
+  for (int p = 0; p < N; ++p) { ir[p] = in_re[p]; ii[p] = in_im[p]; }
+  const int rc = fft_fixed_core(cfg, &tabs, xr, xr + N, ir, ii, orr, oi, overflow_mask);
+  for (int p = 0; p < N; ++p) { out_re[p] = (int32_t)orr[p]; out_im[p] = (int32_t)oi[p]; }
   free(xr);
   fft_tabs_free(&tabs);
   return rc;
@@ -441,16 +473,78 @@ static int fft_fixed_words_tabs(const rspo_fft_cfg *cfg, const fft_tabs *tabs, c
                                 int n_chirps) {
   const int N = 1 << cfg->log_n;
   int rc = 0;
-  int32_t *buf = (int32_t *)malloc(sizeof(int32_t) * 4 * (size_t)N);
+  int64_t *buf = (int64_t *)malloc(sizeof(int64_t) * 4 * (size_t)N);
   int64_t *x = (int64_t *)malloc(sizeof(int64_t) * 2 * (size_t)N);
   if (!buf || !x) { free(buf); free(x); return -2; }
-  int32_t *ir = buf, *ii = buf + N, *orr = buf + 2 * N, *oi = buf + 3 * N;
+  int64_t *ir = buf, *ii = buf + N, *orr = buf + 2 * N, *oi = buf + 3 * N;
   for (int c = 0; c < n_chirps && rc == 0; ++c) {
-    for (int p = 0; p < N; ++p) unpack_iq(in[(size_t)c * N + p], cfg->data_width, &ir[p], &ii[p]);
-    rc = fft_fixed_core(cfg, tabs, x, x + N, ir, ii, orr, oi);
-    for (int p = 0; p < N; ++p) out[(size_t)c * N + p] = pack_iq(orr[p], oi[p]);
+    for (int p = 0; p < N; ++p) { int32_t a, b; unpack_iq(in[(size_t)c * N + p], cfg->data_width, &a, &b); ir[p] = a; ii[p] = b; }
+    rc = fft_fixed_core(cfg, tabs, x, x + N, ir, ii, orr, oi, NULL);
+    for (int p = 0; p < N; ++p) out[(size_t)c * N + p] = pack_iq((int32_t)orr[p], (int32_t)oi[p]);
   }
   free(buf); free(x);
+  return rc;
+}
+
+/* AXI4FFTBlock with wide data or grow stages: 64-bit beats (beatBytes = 8), or 128-bit beats (two uint64 words per beat, low word
+ * first) when the output Cat(re, im) needs more than 64 bits.  in = low 2 * dataWidth bits Cat(re, im) of a 64-bit beat
+ * (`in.bits.data.asTypeOf(params.protoIQ)`, FFTBlock.scala:106), out = Cat(re, im) of the last stage's type
+ * (`fft.io.out.bits.asUInt`, :113; SDFFFT.scala:20).  overflow_mask (may be NULL): OR over the chirps of rspo_fft_fixed_ex's mask. */
+int rspo_fft_fixed_words64(const rspo_fft_cfg *cfg, const uint64_t *in, uint64_t *out, int n_chirps, uint32_t *overflow_mask) {
+  const int S = cfg->log_n, N = 1 << S, w0 = cfg->data_width;
+  if (S < 1 || S > 24 || w0 < 2 || w0 > 32) return -1;
+  const int wo = rspo_fft_stage_width(cfg, S - 1);
+  if (wo > 40) return -1;
+  const int words = 2 * wo > 64 ? 2 : 1;
+  fft_tabs tabs;
+  if (fft_tabs_build(&tabs, cfg)) return -2;
+  int64_t *buf = (int64_t *)malloc(sizeof(int64_t) * 6 * (size_t)N);
+  if (!buf) { fft_tabs_free(&tabs); return -2; }
+  int64_t *x = buf, *ir = buf + 2 * N, *ii = buf + 3 * N, *orr = buf + 4 * N, *oi = buf + 5 * N;
+  int rc = 0;
+  uint32_t all = 0;
+  const uint64_t mo = (1ULL << wo) - 1;
+  for (int c = 0; c < n_chirps && rc == 0; ++c) {
+    for (int p = 0; p < N; ++p) {
+      const uint64_t wd = in[(size_t)c * N + p];
+      ir[p] = rspo_wrap((int64_t)(wd >> w0), w0);
+      ii[p] = rspo_wrap((int64_t)wd, w0);
+    }
+    uint32_t m = 0;
+    rc = fft_fixed_core(cfg, &tabs, x, x + N, ir, ii, orr, oi, &m);
+    all |= m;
+    for (int p = 0; p < N; ++p) {
+      const uint64_t re = (uint64_t)orr[p] & mo, im = (uint64_t)oi[p] & mo;
+      uint64_t *o = out + ((size_t)c * N + p) * (size_t)words;
+      o[0] = (wo < 64 ? (re << wo) : 0) | im;          /* bits 63..0 of Cat(re, im) */
+      if (words == 2) o[1] = re >> (64 - wo);          /* bits 127..64 */
+    }
+  }
+  if (overflow_mask) *overflow_mask = all;
+  free(buf); fft_tabs_free(&tabs);
+  return rc;
+}
+
+/* 32-bit beats, plus the overflow mask OR-ed over the chirps */
+int rspo_fft_fixed_words_ovf(const rspo_fft_cfg *cfg, const uint32_t *in, uint32_t *out, int n_chirps, uint32_t *overflow_mask) {
+  const int N = 1 << cfg->log_n;
+  if (cfg->data_width > 16 || cfg->log_n < 1 || cfg->log_n > 24 || cfg->expand_mask || cfg->base_growth) return -1;
+  fft_tabs tabs;
+  if (fft_tabs_build(&tabs, cfg)) return -2;
+  int64_t *buf = (int64_t *)malloc(sizeof(int64_t) * 6 * (size_t)N);
+  if (!buf) { fft_tabs_free(&tabs); return -2; }
+  int64_t *x = buf, *ir = buf + 2 * N, *ii = buf + 3 * N, *orr = buf + 4 * N, *oi = buf + 5 * N;
+  int rc = 0;
+  uint32_t all = 0;
+  for (int c = 0; c < n_chirps && rc == 0; ++c) {
+    for (int p = 0; p < N; ++p) { int32_t a, b; unpack_iq(in[(size_t)c * N + p], cfg->data_width, &a, &b); ir[p] = a; ii[p] = b; }
+    uint32_t m = 0;
+    rc = fft_fixed_core(cfg, &tabs, x, x + N, ir, ii, orr, oi, &m);
+    all |= m;
+    for (int p = 0; p < N; ++p) out[(size_t)c * N + p] = pack_iq((int32_t)orr[p], (int32_t)oi[p]);
+  }
+  if (overflow_mask) *overflow_mask = all;
+  free(buf); fft_tabs_free(&tabs);
   return rc;
 }
 

@@ -55,7 +55,12 @@ typedef struct {
   int32_t decim_dit;      /* 1 = DITDecimType, 0 = DIFDecimType                               */
   int32_t num_stages;     /* log2(numPoints) of the ELABORATED chain (radix-2^2 DIT: which stages carry twiddles depends on its
                              parity, SDFChainRadix22.scala:229); 0 = same as log_n                                        */
+  uint32_t expand_mask;   /* bit i = expandLogic(i) of stage i of THIS transform: the stage keeps the grown butterfly outputs in a type one
+                             bit wider than its input (SDFFFTParams.scala:119-123, SDFChainRadix22.scala:453-457); radix 2^2 DIF only   */
+  int32_t base_growth;    /* bits the stages in front of THIS transform's first stage have already added to the types (run-time size) */
 } rspo_fft_cfg;
+/* width of the output type of stage i of this transform: dataWidth + base_growth + sum expandLogic(0..i) */
+int rspo_fft_stage_width(const rspo_fft_cfg *cfg, int stage);
 
 /* MAGParams (generators/logMagMux/src/main/scala/LogMagMux.scala:14-49) + run-time sel */
 typedef struct {
@@ -110,6 +115,13 @@ void rspo_log2_table(int lookup_width, int bp_log, int32_t *tab);
 
 /* ---- FFT ---- */
 /* radix-2^2 DIF, scale-or-wrap per stage; in/out raw fixed-point integers (SDFChainRadix22.scala:224-352,410-505) */
+/* as rspo_fft_fixed; *overflow_mask (may be NULL) receives bit i = some butterfly output of stage i of this transform had the
+ * grown sum / difference at or above 2^(w-1), w = the stage's input width: `tooBig` of SDFChainRadix22.scala:473-481 (`tooSmall`
+ * can never fire: an arithmetic right shift of a negative value is never 0); grow stages report 0 (:455-457) */
+int rspo_fft_fixed_ex(const rspo_fft_cfg *cfg, const int32_t *in_re, const int32_t *in_im, int32_t *out_re, int32_t *out_im,
+                      uint32_t *overflow_mask);
+int rspo_fft_fixed_words64(const rspo_fft_cfg *cfg, const uint64_t *in, uint64_t *out, int n_chirps, uint32_t *overflow_mask);
+int rspo_fft_fixed_words_ovf(const rspo_fft_cfg *cfg, const uint32_t *in, uint32_t *out, int n_chirps, uint32_t *overflow_mask);
 int rspo_fft_fixed(const rspo_fft_cfg *cfg, const int32_t *in_re, const int32_t *in_im,
                    int32_t *out_re, int32_t *out_im);
 /* the DspReal "golden" flavour of the same dataflow: every stage halves, twiddles exact */

@@ -22,6 +22,7 @@ EXPORTS = [
     "rsp_plfg_ram_write", "rsp_fft_window_user", "rsp_run", "rsp_run_from_generator", "rsp_fft_run", "rsp_mag_run", "rsp_cfar_run",
     "rsp_generate", "rsp_run_host", "rsp_host_alloc", "rsp_host_free", "rsp_status_str", "rsp_last_error",
     "rsp_abi_version", "rsp_kernel_launches", "rsp_variant_name", "rsp_bytes_per_chirp",
+    "rsp_fft_in_beat_bytes", "rsp_fft_out_beat_bytes", "rsp_fft_overflow_flags",
 ]
 
 
@@ -32,8 +33,8 @@ def _i32s(*names):
 class FftParams(C.Structure):
     _fields_ = _i32s("numPoints", "dataWidth", "binPoint", "twiddleWidth", "trimType", "use4Muls", "useBitReverse",
                      "fftDir", "runTime") + [("keepMSBorLSB", C.c_uint32)] + _i32s(
-        "decimType", "sdfRadix", "expandLogicAny", "keepMSBorLSBReg", "fftDirReg", "windowFunc", "windowWidth") + [
-        ("windowA0", C.c_double), ("windowA1", C.c_double), ("windowA2", C.c_double)]
+        "decimType", "sdfRadix") + [("expandLogic", C.c_uint32)] + _i32s("keepMSBorLSBReg", "fftDirReg", "windowFunc", "windowWidth") + [
+        ("windowA0", C.c_double), ("windowA1", C.c_double), ("windowA2", C.c_double)] + _i32s("overflowReg", "reserved_")
 
 
 class MagParams(C.Structure):
@@ -117,6 +118,11 @@ def lib():
         L.rsp_variant_name.restype = C.c_char_p
         L.rsp_bytes_per_chirp.argtypes = [vp]
         L.rsp_bytes_per_chirp.restype = u64
+        L.rsp_fft_in_beat_bytes.argtypes = [vp]
+        L.rsp_fft_in_beat_bytes.restype = u32
+        L.rsp_fft_out_beat_bytes.argtypes = [vp]
+        L.rsp_fft_out_beat_bytes.restype = u32
+        L.rsp_fft_overflow_flags.argtypes = [vp, C.POINTER(u32), vp]
         _lib = L
     return _lib
 

@@ -166,6 +166,22 @@ class _Chain:
         _abi.check(self._lib.rsp_fft_run(self._h, d_in.data_ptr(), n_chirps, out.data_ptr(), _stream_ptr(stream)))
         return out
 
+    @property
+    def fft_in_beat_bytes(self) -> int:
+        """bytes per input beat of the FFT block: 4 (Cat(re16, im16)), 8 for the wide block (dataWidth / twiddleWidth > 16, grow stages)"""
+        return int(self._lib.rsp_fft_in_beat_bytes(self._h))
+
+    @property
+    def fft_out_beat_bytes(self) -> int:
+        """bytes per output beat of the FFT block: 4, 8, or 16 when Cat(re, im) of the last stage's type needs more than 64 bits"""
+        return int(self._lib.rsp_fft_out_beat_bytes(self._h))
+
+    def fft_overflow_flags(self, stream=None) -> int:
+        """per-stage overflow status of the most recent call (FFTParams.overflowReg; SDFChainRadix22.scala:473-486), all stages"""
+        m = C.c_uint32(0)
+        _abi.check(self._lib.rsp_fft_overflow_flags(self._h, C.byref(m), _stream_ptr(stream)))
+        return int(m.value)
+
     def mag(self, d_in, n_beats: int, out, stream=None):
         """AXI4LogMagMuxBlock alone (rsp_mag_run)"""
         _abi.check(self._lib.rsp_mag_run(self._h, d_in.data_ptr(), n_beats, out.data_ptr(), _stream_ptr(stream)))

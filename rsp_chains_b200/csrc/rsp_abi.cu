@@ -57,7 +57,8 @@ struct rsp_chain {
   Tables t;
   int device = 0, sm_count = 0;
   uint32_t *d_tw = nullptr;
-  int32_t *d_tw2 = nullptr;
+  int32_t *d_tw2 = nullptr, *d_tww = nullptr;
+  uint32_t *d_ovf = nullptr;           // per-stage overflow status of the last call (FFTParams.overflowReg)
   F2 *d_twf = nullptr;
   float *d_twf4 = nullptr;
   int32_t *d_log_tab = nullptr, *d_nco_tab = nullptr, *d_win = nullptr, *d_win4 = nullptr;
@@ -189,7 +190,7 @@ extern "C" void rsp_chain_params_default(rsp_chain_params *p) {
   p->nco.tableSize = 128; p->nco.tableWidth = 16; p->nco.phaseWidth = 9; p->nco.phaseAccEnable = 1;
   rsp_fft_params &f = p->fft;
   f.numPoints = 1024; f.dataWidth = 16; f.binPoint = 0; f.twiddleWidth = 16; f.trimType = RSP_TRIM_ROUND_HALF_UP; f.use4Muls = 0;
-  f.useBitReverse = 1; f.fftDir = 1; f.runTime = 1; f.keepMSBorLSB = 0x3FF; f.decimType = 0; f.sdfRadix = 4; f.expandLogicAny = 0;
+  f.useBitReverse = 1; f.fftDir = 1; f.runTime = 1; f.keepMSBorLSB = 0x3FF; f.decimType = 0; f.sdfRadix = 4; f.expandLogic = 0;
   f.keepMSBorLSBReg = 0; f.fftDirReg = 0; f.windowFunc = RSP_WINDOW_NONE; f.windowWidth = 16;
   p->mag = {16, 0, 16, 9, 9};
   rsp_cfar_params &c = p->cfar;
@@ -215,7 +216,7 @@ extern "C" void rsp_chain_destroy(rsp_chain *c) {
   DeviceGuard guard(c->device);
   free_pipe(c);
   for (int i = 0; i < N_PIPE; ++i) if (c->pipe_stream[i]) cudaStreamDestroy(c->pipe_stream[i]);
-  cudaFree(c->d_tw); cudaFree(c->d_tw2); cudaFree(c->d_twf); cudaFree(c->d_twf4); cudaFree(c->d_win); cudaFree(c->d_win4); cudaFree(c->d_winf); cudaFree(c->d_log_tab); cudaFree(c->d_nco_tab); cudaFree(c->d_nco_full); cudaFree(c->d_segs);
+  cudaFree(c->d_tw); cudaFree(c->d_tw2); cudaFree(c->d_tww); cudaFree(c->d_ovf); cudaFree(c->d_twf); cudaFree(c->d_twf4); cudaFree(c->d_win); cudaFree(c->d_win4); cudaFree(c->d_winf); cudaFree(c->d_log_tab); cudaFree(c->d_nco_tab); cudaFree(c->d_nco_full); cudaFree(c->d_segs);
   cudaFree(c->d_gen_scratch); cudaFree(c->d_det_list); cudaFree(c->d_det_count);
   delete c;
 }
@@ -251,6 +252,10 @@ extern "C" rsp_status rsp_chain_create(const rsp_chain_params *params, int devic
   build_window(c->p, c->t);
   rsp_status s = upload(c->t.tw, &c->d_tw);
   if (s == RSP_OK) s = upload(c->t.tw2, &c->d_tw2);
+  if (s == RSP_OK && fft_is_wide(c->p.fft)) s = upload(c->t.tww, &c->d_tww);
+  if (s == RSP_OK && c->p.fft.overflowReg) {
+    if (cudaMalloc((void **)&c->d_ovf, sizeof(uint32_t)) != cudaSuccess || cudaMemset(c->d_ovf, 0, sizeof(uint32_t)) != cudaSuccess) s = fail(RSP_ECUDA, "allocating the overflow status word failed");
+  }
   if (s == RSP_OK) s = upload(c->t.twf, &c->d_twf);
   if (s == RSP_OK) s = upload(c->t.twf4, &c->d_twf4);
   if (s == RSP_OK) s = upload(c->t.win, &c->d_win);
@@ -290,7 +295,16 @@ extern "C" rsp_status rsp_reg_read(rsp_chain *c, rsp_block blk, uint32_t idx, ui
   if (reg_width(c->p, blk, idx, &ro) < 0) return fail(RSP_EINVAL, "no such register");
   uint32_t *slot = reg_slot(c->r, blk, idx);
   if (!slot) return fail(RSP_EINVAL, "no such register");
-  *value = *slot;   // busy / overflow read 0: calls are synchronous with respect to the registers, overflow flags are not built
+  *value = *slot;   // busy reads 0: calls are synchronous with respect to the registers
+  if (blk == RSP_BLK_FFT && idx == RSP_FFT_REG_OVERFLOW && c->d_ovf != nullptr) {
+    // the status of the most recent call, through the reference's log2Ceil(numStages)-bit field (FFTBlock.scala:67,82,97)
+    RSP_ON_DEVICE(c);
+    uint32_t m = 0;
+    CUDA_TRY(cudaDeviceSynchronize());
+    CUDA_TRY(cudaMemcpy(&m, c->d_ovf, sizeof(uint32_t), cudaMemcpyDeviceToHost));
+    const int w = reg_width(c->p, blk, idx, &ro);
+    *value = m & ((1u << w) - 1u);
+  }
   return RSP_OK;
 }
 
@@ -336,6 +350,10 @@ static rsp_status run_stages(rsp_chain *c, int first, int last, const void *d_in
     const rsp_status s = plan_fixed(c->p, c->r, c->t, first, last, a, pl, err);
     if (s != RSP_OK) return fail(s, err);
     bind_fixed(c, a);
+    if (first == STAGE_FFT && c->d_ovf != nullptr) {
+      a.ovf_flags = c->d_ovf;
+      if (row_base == 0) CUDA_TRY(cudaMemsetAsync(c->d_ovf, 0, sizeof(uint32_t), st));   // the status is that of this call (all its chunks)
+    }
     a.in = static_cast<const uint32_t *>(d_in); a.out = static_cast<uint32_t *>(d_out); a.n_rows = n_rows; a.row_base = row_base;
     bind_dets(dets, &a.det_list, &a.det_count, &a.det_cap);
     if (!a.out && !(last == STAGE_CFAR && a.det_list)) return fail(RSP_EINVAL, "no output requested");
@@ -375,6 +393,24 @@ extern "C" rsp_status rsp_run(rsp_chain *c, const void *d_in, uint32_t n_chirps,
 extern "C" rsp_status rsp_fft_run(rsp_chain *c, const void *d_in, uint32_t n_chirps, void *d_out, void *stream) {
   if (!c || !d_in || !d_out) return fail(RSP_EINVAL, "null argument");
   RSP_ON_DEVICE(c);
+  if (c->p.arith == RSP_ARITH_FIXED && fft_is_wide(c->p.fft)) {
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    WideArgs a;
+    std::string err;
+    const rsp_status s = plan_wide(c->p, c->r, c->t, a, err);
+    if (s != RSP_OK) return fail(s, err);
+    if (n_chirps == 0) return RSP_OK;
+    a.in = static_cast<const unsigned long long *>(d_in); a.out = static_cast<unsigned long long *>(d_out); a.n_rows = n_chirps;
+    a.tw = reinterpret_cast<const int2 *>(c->d_tww); a.win = c->d_win;
+    a.ovf_flags = c->d_ovf;
+    if (c->d_ovf != nullptr) CUDA_TRY(cudaMemsetAsync(c->d_ovf, 0, sizeof(uint32_t), st));
+    const LaunchCtx ctx = {c->device, c->sm_count};
+    const char *e = "";
+    const rsp_status ls = launch_fft_wide(ctx, a, st, &e);
+    if (ls != RSP_OK) return fail(ls, e);
+    ++c->launches;
+    return RSP_OK;
+  }
   return run_stages(c, STAGE_FFT, STAGE_FFT, d_in, n_chirps, d_out, nullptr, nullptr, static_cast<cudaStream_t>(stream));
 }
 
@@ -660,6 +696,29 @@ extern "C" const char *rsp_variant_name(rsp_chain *c) {
   }
   c->variant = buf;
   return c->variant.c_str();
+}
+
+extern "C" uint32_t rsp_fft_in_beat_bytes(rsp_chain *c) {
+  if (!c) return 0;
+  if (c->p.arith != RSP_ARITH_FIXED) return 8;   // float2
+  return fft_is_wide(c->p.fft) ? 8 : 4;
+}
+extern "C" uint32_t rsp_fft_out_beat_bytes(rsp_chain *c) {
+  if (!c) return 0;
+  if (c->p.arith != RSP_ARITH_FIXED) return 8;
+  if (!fft_is_wide(c->p.fft)) return 4;
+  WideArgs a; std::string err;
+  if (plan_wide(c->p, c->r, c->t, a, err) != RSP_OK) return 0;
+  return 8u * (uint32_t)a.out_words;
+}
+extern "C" rsp_status rsp_fft_overflow_flags(rsp_chain *c, uint32_t *mask, void *stream) {
+  if (!c || !mask) return fail(RSP_EINVAL, "null argument");
+  *mask = 0;
+  if (c->d_ovf == nullptr) return RSP_OK;   // overflowReg = false: no status register elaborated, reads 0
+  RSP_ON_DEVICE(c);
+  CUDA_TRY(cudaStreamSynchronize(static_cast<cudaStream_t>(stream)));
+  CUDA_TRY(cudaMemcpy(mask, c->d_ovf, sizeof(uint32_t), cudaMemcpyDeviceToHost));
+  return RSP_OK;
 }
 
 extern "C" uint64_t rsp_bytes_per_chirp(rsp_chain *c) {

@@ -1,10 +1,8 @@
 // rsp_device.cuh -- per-thread device code of the rsp-chains hot path (FFT -> LogMagMux -> CFAR).
 //
 // Every function here is the work of ONE thread during ONE phase of a chirp; phases are separated by a
-// block-wide barrier.  The CUDA kernels (rsp_kernels.cuh) call the phases with threadIdx-derived indices;
-// tests/emu compiles this same header with g++ and runs the phases thread by thread, so index maps and
-// integer arithmetic are checked against the oracle on the CPU box before any GPU time is spent.
-// (That emulation is test infrastructure: the product library only ever runs the CUDA kernels.)
+// block-wide barrier.  The CUDA kernels (rsp_kernels.cuh) call the phases with threadIdx-derived indices.  The functions are
+// host-callable as well (RSP_HD): the host builds tables with the very code the device reads them with (nco_lookup).
 //
 // Arithmetic follows the reference generators (paths relative to the rsp-chains repository):
 //   butterfly + div2        generators/sdf-fft/src/main/scala/SDFFFTUtil.scala:51-61, SDFChainRadix22.scala:459-464,487-493
@@ -67,6 +65,10 @@ struct FxArgs {
   Detection *det_list;
   uint32_t *det_count;
   uint32_t det_cap;
+  // per-stage overflow status (FFTParams.overflowReg, SDFChainRadix22.scala:473-486): one device word, bit (ovf_shift + i) is OR-ed
+  // in when a butterfly of stage i of this transform has a grown output at or above 2^(dataWidth - 1); null = not elaborated
+  uint32_t *ovf_flags;
+  int ovf_shift;
 };
 
 // ------------------------------------------------------------------------------------------------ helpers
@@ -148,8 +150,15 @@ template <int S> struct Geo {
 };
 
 // ------------------------------------------------------------------------------------------------ FFT arithmetic
-template <int MODE> RSP_HD void butterfly(const FxArgs &a, int scale, int &ar, int &ai, int &cr, int &ci) {
+// returns `tooBig` of the reference's overflow check on the four grown outputs (generic modes with the status register elaborated);
+// `tooSmall` can never fire: an arithmetic right shift of a negative value is never 0 (SDFChainRadix22.scala:476-479)
+template <int MODE> RSP_HD bool butterfly(const FxArgs &a, int scale, int &ar, int &ai, int &cr, int &ci) {
   const int sr = ar + cr, si = ai + ci, dr = ar - cr, di = ai - ci;
+  bool ov = false;
+  if (mode_is_generic(MODE) && a.ovf_flags != nullptr) {
+    const int lim = 1 << (a.data_width - 1);
+    ov = sr >= lim || si >= lim || dr >= lim || di >= lim;
+  }
   if (!mode_is_generic(MODE)) {
     // RoundHalfUp div2: (v + 1) >> 1.  The sum cannot leave 16 bits; the difference can (+32768) and wraps.
     ar = (sr + 1) >> 1; ai = (si + 1) >> 1;
@@ -163,6 +172,7 @@ template <int MODE> RSP_HD void butterfly(const FxArgs &a, int scale, int &ar, i
       ar = wrapw(sr, w); ai = wrapw(si, w); cr = wrapw(dr, w); ci = wrapw(di, w);
     }
   }
+  return ov;
 }
 
 // multiply by -j: (re, im) <- (im, -re)
@@ -304,6 +314,7 @@ RSP_HD void fft_pass(const FxArgs &a, int tl, const uint32_t *gin, uint32_t *buf
     const int low = vt & (Dl - 1), high = vt >> LDl;
     const int base = (high << (m + LDl)) | low;
     int re[R], im[R];
+    uint32_t ovf = 0;
 #pragma unroll
     for (int rr = 0; rr < R; ++rr) {
       const int p = base + rr * Dl;
@@ -372,7 +383,7 @@ RSP_HD void fft_pass(const FxArgs &a, int tl, const uint32_t *gin, uint32_t *buf
         }
 #pragma unroll
         for (int rr = 0; rr < R; ++rr)
-          if (!(rr & dist)) butterfly<MODE>(a, scale, re[rr], im[rr], re[rr + dist], im[rr + dist]);
+          if (!(rr & dist)) { if (butterfly<MODE>(a, scale, re[rr], im[rr], re[rr + dist], im[rr + dist])) ovf |= 1u << i; }
         if (!a.dit && i != S - 1) {
 #pragma unroll
           for (int rr = 0; rr < R; ++rr)
@@ -385,7 +396,7 @@ RSP_HD void fft_pass(const FxArgs &a, int tl, const uint32_t *gin, uint32_t *buf
       }
 #pragma unroll
       for (int rr = 0; rr < R; ++rr)
-        if (!(rr & dist)) butterfly<MODE>(a, scale, re[rr], im[rr], re[rr + dist], im[rr + dist]);
+        if (!(rr & dist)) { if (butterfly<MODE>(a, scale, re[rr], im[rr], re[rr + dist], im[rr + dist])) ovf |= 1u << i; }
       if (i == S - 1) continue;
       if ((i & 1) == 0) {
 #pragma unroll
@@ -405,6 +416,13 @@ RSP_HD void fft_pass(const FxArgs &a, int tl, const uint32_t *gin, uint32_t *buf
           }
         }
       }
+    }
+    if (mode_is_generic(MODE) && ovf != 0) {
+#if defined(__CUDA_ARCH__)
+      atomicOr(a.ovf_flags, ovf << a.ovf_shift);
+#else
+      *a.ovf_flags |= ovf << a.ovf_shift;
+#endif
     }
 #pragma unroll
     for (int rr = 0; rr < R; ++rr) {

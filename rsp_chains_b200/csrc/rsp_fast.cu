@@ -42,6 +42,8 @@ struct FastArgs {
   Detection *det_list;
   uint32_t *det_count;
   uint32_t det_cap;
+  int skew_ns;           // A/B knob (RSP_FAST_SKEW_NS): CTAs of the second half of the grid start this much later, so that the CTAs
+                         // sharing an SM are in different phases of their rows from the start
   int stage;             // 1: the next row's beats are fetched with cp.async into a staging area behind the CTA's rows while this
                          // row's CFAR phase runs (chain_fixed_fast_kernel); needs 16-byte aligned rows and N more words per chirp
 };
@@ -520,6 +522,9 @@ __global__ void __launch_bounds__(FGeo<S, LP>::THREADS, 1024 / FGeo<S, LP>::THRE
     cp_async_commit();
   };
   if (stage) { prefetch(blockIdx.x * CPC); cp_async_wait_all(); __syncthreads(); }
+  if (a.skew_ns > 0 && 2 * blockIdx.x >= gridDim.x) {
+    for (int left = a.skew_ns; left > 0; left -= 1000) __nanosleep(1000);
+  }
   // the loop bound is the same for every thread of the CTA (the barriers are CTA-wide); a chirp slot past the last row
   // recomputes the last row -- it stores the same beats again and reports no detections
   for (uint32_t row0 = blockIdx.x * CPC; row0 < a.n_rows; row0 += stride) {
@@ -990,6 +995,7 @@ rsp_status launch_fast_chain(const Plan &pl, const LaunchCtx &ctx, const FxArgs 
   fa.thr_mask = a.thr_w >= 32 ? 0xFFFFFFFFu : ((1u << a.thr_w) - 1u);
   fa.out_mul = (int)(1u << (a.binw + 1)); fa.thr_sext = 32 - a.thr_w;
   fa.det_list = a.det_list; fa.det_count = a.det_count; fa.det_cap = a.det_cap;
+  { static int skew = -1; if (skew < 0) { const char *e = std::getenv("RSP_FAST_SKEW_NS"); skew = e ? std::atoi(e) : 0; } fa.skew_ns = skew; }
   fa.stage = (pl.S < RSP_FAST_TWSMEM_S && fast_stage_enabled(pl.S) && (reinterpret_cast<uintptr_t>(a.in) & 15u) == 0) ? 1 : 0;   // rows are N * 4 bytes: the base decides
   const int cmode = a.cfar_mode == 0 ? 0 : (a.cfar_mode == 1 ? 1 : 2);   // MuxLookup default: smallestOf (CFARCoreWithMem.scala:138-141)
   const bool linear = a.log_or_linear != 0;

@@ -1,7 +1,6 @@
 // rsp_host.hpp -- host-side state of a chain: parameter checks (the reference's `require`s), register files with the
 // reference's field widths and reset values, table generation, and the translation of (params, registers) into the
-// kernel argument blocks.  No CUDA in this header: the C-ABI library (rsp_abi.cu) and the CPU emulation harness under
-// tests/emu both include it.
+// kernel argument blocks.  Included by the translation units of the C-ABI library (rsp_abi.cu, rsp_fast*.cu).
 #pragma once
 #include <cmath>
 #include <cstdint>
@@ -13,10 +12,14 @@
 #include "rsp_device.cuh"
 #include "rsp_device_f32.cuh"
 #include "rsp_device_gen.cuh"
+#include "rsp_wide.cuh"
 
 namespace rsp {
 
 inline bool is_pow2(int v) { return v > 0 && (v & (v - 1)) == 0; }
+inline int popcount32(uint32_t v) { int n = 0; while (v) { n += (int)(v & 1u); v >>= 1; } return n; }
+// the FFT block needs beats wider than Cat(re16, im16): the 64-bit kernel of rsp_wide.cu (FFT block alone)
+inline bool fft_is_wide(const rsp_fft_params &f) { return f.dataWidth > 16 || f.twiddleWidth > 16 || f.expandLogic != 0; }
 inline int log2_ceil(uint32_t v) { int n = 0; while ((1u << n) < v) ++n; return n; }   // chisel3.util.log2Ceil
 inline int bit_length(uint32_t v) { int n = 0; while (v) { ++n; v >>= 1; } return n; }
 inline long long wrap_host(long long v, int w) { return wrapw64(v, w); }
@@ -35,6 +38,7 @@ struct Tables {
   std::vector<uint32_t> tw;   // fixed twiddles, packed (cos16 << 16 | sin16 & 0xFFFF); per stageN three runs [W^2k | W^k | W^3k]
   std::vector<F2> twf;        // fp32 twiddles, same layout
   std::vector<float> twf4;    // fp32 twiddles again as (c, s, -s, c) quads: the two operands of the packed complex product (rsp_fast_f32.cu)
+  std::vector<int32_t> tww;   // fixed twiddles as raw int32 pairs (c, s) in Q2.(twiddleWidth - 2), any twiddleWidth up to 32 (rsp_wide.cu)
   std::vector<int32_t> tw2;   // fixed twiddles again as int32 pairs (c, s) << (16 - (twiddleWidth - 2)): the fast kernels'
                               // product then carries its rounded, wrapped result in bits 16..31 (rsp_fast.cu)
   int tw_off[16];
@@ -59,13 +63,20 @@ inline rsp_status validate_params(const rsp_chain_params &p, std::string &err) {
   RSP_REQ(f.numPoints >= 2 && f.numPoints <= 16384, RSP_EUNSUPPORTED, "numPoints must be in 2..16384 (one chirp stays resident in shared memory)");
   RSP_REQ(f.sdfRadix == 2 || f.sdfRadix == 4, RSP_EINVAL, "Radix must be 2 or 2^2");   // SDFFFTParams.scala:61-64
   RSP_REQ(f.decimType == 0 || f.decimType == 1, RSP_EINVAL, "decimType must be DIF or DIT");
-  RSP_REQ(!f.expandLogicAny, RSP_EUNSUPPORTED, "expandLogic (grow) stages are not built");
+  RSP_REQ(!f.expandLogic || (f.sdfRadix == 4 && f.decimType == 0 && p.arith == RSP_ARITH_FIXED), RSP_EUNSUPPORTED,
+          "expandLogic (grow) stages are built for the fixed-point radix 2^2 DIF chain only");
   RSP_REQ(f.windowFunc >= RSP_WINDOW_NONE && f.windowFunc <= RSP_WINDOW_USER, RSP_EINVAL, "unknown windowFunc");
   RSP_REQ(f.windowFunc == RSP_WINDOW_NONE || (f.windowWidth >= 3 && f.windowWidth <= 16), RSP_EUNSUPPORTED, "window dataWidth must be in 3..16");
   if (p.arith == RSP_ARITH_FIXED) {
-    RSP_REQ(f.dataWidth >= 2 && f.dataWidth <= 16, RSP_EUNSUPPORTED, "dataWidth must be in 2..16 (32-bit beats carry Cat(re16, im16))");
-    RSP_REQ(f.binPoint >= 0 && f.binPoint <= 15, RSP_EINVAL, "binPoint must be in 0..15");
-    RSP_REQ(f.twiddleWidth >= 3 && f.twiddleWidth <= 16, RSP_EUNSUPPORTED, "twiddleWidth must be in 3..16");
+    RSP_REQ(f.dataWidth >= 2 && f.dataWidth <= 32, RSP_EUNSUPPORTED, "dataWidth must be in 2..32");
+    RSP_REQ(f.binPoint >= 0 && f.binPoint < f.dataWidth, RSP_EINVAL, "binPoint must be in 0..dataWidth-1");
+    RSP_REQ(f.twiddleWidth >= 3 && f.twiddleWidth <= 32, RSP_EUNSUPPORTED, "twiddleWidth must be in 3..32");
+    if (fft_is_wide(f)) {   // wide beats: the FFT block alone (rsp_fft_run) on the 64-bit kernel
+      RSP_REQ(f.sdfRadix == 4 && f.decimType == 0, RSP_EUNSUPPORTED, "wide data / twiddles / grow stages are built for the radix 2^2 DIF chain only");
+      RSP_REQ(f.numPoints <= 8192, RSP_EUNSUPPORTED, "the wide FFT block keeps a row of 64-bit points in shared memory: numPoints <= 8192");
+      RSP_REQ(f.dataWidth + popcount32(f.expandLogic) <= 40, RSP_EUNSUPPORTED, "stage types wider than 40 bits are not built");
+      RSP_REQ(f.windowFunc == RSP_WINDOW_NONE || f.windowWidth <= 16, RSP_EUNSUPPORTED, "window dataWidth must be in 3..16");
+    }
     RSP_REQ(f.trimType >= 0 && f.trimType <= RSP_TRIM_NO_TRIM, RSP_EINVAL, "unknown trimType");
     RSP_REQ(m.dataWidth >= 2 && m.dataWidth <= 16 && m.binPoint >= 0 && m.binPoint <= 15, RSP_EUNSUPPORTED, "MAGParams proto must fit 16 bits");
     RSP_REQ(m.dataWidthLog >= 2 && m.dataWidthLog <= 32 && m.binPointLog >= 0 && m.binPointLog < 31, RSP_EINVAL, "bad protoLog");
@@ -144,7 +155,7 @@ inline int reg_width(const rsp_chain_params &p, rsp_block blk, uint32_t idx, boo
     case RSP_FFT_REG_FFTDIR: return 1;
     case RSP_FFT_REG_KEEPMSBORLSB: return numStages;
     case RSP_FFT_REG_BUSY: *ro = true; return 1;
-    case RSP_FFT_REG_OVERFLOW: *ro = true; return numStages;
+    case RSP_FFT_REG_OVERFLOW: *ro = true; return log2_ceil((uint32_t)numStages);   // RegInit(0.U(log2Ceil(numStages).W)) (FFTBlock.scala:67,97)
     default: return -1;
     }
   case RSP_BLK_MAG: return idx == RSP_MAG_REG_SEL ? 2 : -1;
@@ -198,7 +209,7 @@ inline uint32_t *reg_slot(Regs &r, rsp_block blk, uint32_t idx) {
 inline void build_tables(const rsp_chain_params &p, Tables &t) {
   const int Smax = log2_ceil((uint32_t)p.fft.numPoints);
   const int tww = p.fft.twiddleWidth, twbp = tww - 2;
-  t.tw.clear(); t.twf.clear(); t.tw2.clear(); t.twf4.clear();
+  t.tw.clear(); t.twf.clear(); t.tw2.clear(); t.twf4.clear(); t.tww.clear();
   const int pre = 16 - twbp > 0 ? 16 - twbp : 0;
   for (int L = 0; L < 16; ++L) t.tw_off[L] = 0;
   const double PI = 3.14159265358979323846;  // scala.math.Pi
@@ -216,14 +227,15 @@ inline void build_tables(const rsp_chain_params &p, Tables &t) {
         const double c = std::cos(ang), s = -std::sin(ang);
         const long long re = wrap_host(from_double(c, twbp), tww), im = wrap_host(from_double(s, twbp), tww);
         t.tw.push_back(pack_iq((int)re, (int)im));
-        const int32_t c4 = (int32_t)(re * (1LL << pre)), s4 = (int32_t)(im * (1LL << pre));
+        t.tww.push_back((int32_t)re); t.tww.push_back((int32_t)im);
+        const int32_t c4 = (int32_t)(re * (1LL << pre)), s4 = (int32_t)(im * (1LL << pre));   // (meaningful for twiddleWidth <= 16 only)
         t.tw2.push_back(c4); t.tw2.push_back(s4);
         F2 f; f.x = (float)c; f.y = (float)s;
         t.twf.push_back(f);
         t.twf4.push_back(f.x); t.twf4.push_back(f.y); t.twf4.push_back(-f.y); t.twf4.push_back(f.x);
       }
   }
-  if (t.tw.empty()) { t.tw.push_back(0); for (int z = 0; z < 2; ++z) t.tw2.push_back(0); F2 f; f.x = 1.f; f.y = 0.f; t.twf.push_back(f);
+  if (t.tw.empty()) { t.tw.push_back(0); for (int z = 0; z < 2; ++z) { t.tw2.push_back(0); t.tww.push_back(0); } F2 f; f.x = 1.f; f.y = 0.f; t.twf.push_back(f);
                       t.twf4.push_back(1.f); t.twf4.push_back(0.f); t.twf4.push_back(0.f); t.twf4.push_back(1.f); }
   // log2 LUT (LogMagMux.scala:120-131)
   const int Lw = p.mag.log2LookUpWidth, num = 1 << Lw;
@@ -336,6 +348,10 @@ inline rsp_status plan_fixed(const rsp_chain_params &p, const Regs &r, const Tab
     if (S < 1 || S > Smax) { err = "fftSize register must be in 1..log2(numPoints)"; return RSP_EINVAL; }
     if (f.sdfRadix == 4 && f.decimType == 0 && ((Smax - S) & 1)) { err = "radix 2^2 run-time size must drop an even number of stages (Radix22RunTimeSpec.scala:18-19)"; return RSP_EINVAL; }
   }
+  if (first_stage == STAGE_FFT && fft_is_wide(f)) {
+    err = "beats wider than Cat(re16, im16) (dataWidth / twiddleWidth > 16 or grow stages): only the FFT block alone runs (rsp_fft_run); LogMagMux and CFAR take 16-bit cells";
+    return RSP_EUNSUPPORTED;
+  }
   pl.S = S; pl.first_stage = first_stage; pl.last_stage = last_stage;
   a.first_stage = first_stage; a.last_stage = last_stage;
   a.data_width = f.dataWidth; a.bp = f.binPoint; a.tw_bp = f.twiddleWidth - 2; a.trim = f.trimType; a.use4muls = f.use4Muls ? 1 : 0;
@@ -348,6 +364,10 @@ inline rsp_status plan_fixed(const rsp_chain_params &p, const Regs &r, const Tab
   a.bitrev = (f.useBitReverse || a.dit) ? 1 : 0;
   a.load_rev = (a.dit && !f.useBitReverse) ? 1 : 0;
   a.fft_dir = f.fftDirReg ? (int)(r.fft[RSP_FFT_REG_FFTDIR] & 1u) : (f.fftDir ? 1 : 0);
+  // IFFT output scalar (SDFChainRadix22.scala:362, SDFChainRadix2.scala:250): 1.0 unless a stage grows or keepMSBorLSBReg is elaborated;
+  // then it is the literal fromDouble(1.0 / numPoints), whose binary point is dsptools-context dependent and pinned by nothing
+  if (first_stage == STAGE_FFT && !a.fft_dir && f.keepMSBorLSBReg) {
+    err = "IFFT with keepMSBorLSBReg: the 1/numPoints output scalar of the reference is not built"; return RSP_EUNSUPPORTED; }
   const uint32_t phys = f.keepMSBorLSBReg ? r.fft[RSP_FFT_REG_KEEPMSBORLSB] : f.keepMSBorLSB;
   const uint32_t smask = S >= 32 ? 0xFFFFFFFFu : ((1u << S) - 1u);
   // a run-time size uses the LAST S stages in DIF and the FIRST S in DIT (SDFChainRadix2.scala:127-134,196-203)
@@ -376,7 +396,9 @@ inline rsp_status plan_fixed(const rsp_chain_params &p, const Regs &r, const Tab
   const bool common = f.dataWidth == 16 && f.trimType == RSP_TRIM_ROUND_HALF_UP && a.keep_mask == smask && a.fft_dir == 1 &&
                       p.mag.dataWidth == 16;
   pl.mode = MODE_GENERIC;
+  a.ovf_shift = a.dit ? 0 : Smax - S;    // physical stage of this transform's stage 0 (a run-time size uses the last S stages in DIF)
   if (a.radix2 || a.dit) { pl.mode = MODE_RADIX2; return RSP_OK; }   // run-time-parameter kernel with the radix-2 stage structure
+  if (f.overflowReg && first_stage == STAGE_FFT) return RSP_OK;      // the overflow status is computed by the run-time-parameter kernels
   if (common && s1 <= 0) pl.mode = MODE_FAST;
   else if (common && s1 >= 1 && !f.use4Muls) pl.mode = MODE_FAST3;
   return RSP_OK;
@@ -411,6 +433,33 @@ inline rsp_status plan_f32(const rsp_chain_params &p, const Regs &r, const Table
     if (st != RSP_OK) return st;
     a.inv_div = std::ldexp(1.0f, -a.div_sum);
   }
+  return RSP_OK;
+}
+
+// the FFT block alone with wide beats (rsp_wide.cu): radix 2^2 DIF, any dataWidth / twiddleWidth up to 32, grow stages
+inline rsp_status plan_wide(const rsp_chain_params &p, const Regs &r, const Tables &t, WideArgs &a, std::string &err) {
+  std::memset(&a, 0, sizeof(a));
+  const rsp_fft_params &f = p.fft;
+  const int Smax = log2_ceil((uint32_t)f.numPoints);
+  const int S = f.runTime ? (int)r.fft[RSP_FFT_REG_FFTSIZE] : Smax;
+  if (S < 1 || S > Smax) { err = "fftSize register must be in 1..log2(numPoints)"; return RSP_EINVAL; }
+  if ((Smax - S) & 1) { err = "radix 2^2 run-time size must drop an even number of stages (Radix22RunTimeSpec.scala:18-19)"; return RSP_EINVAL; }
+  a.S = S; a.w0 = f.dataWidth; a.bp = f.binPoint; a.tw_bp = f.twiddleWidth - 2; a.trim = f.trimType; a.use4muls = f.use4Muls ? 1 : 0;
+  a.bitrev = f.useBitReverse ? 1 : 0;
+  a.fft_dir = f.fftDirReg ? (int)(r.fft[RSP_FFT_REG_FFTDIR] & 1u) : (f.fftDir ? 1 : 0);
+  if (!a.fft_dir && (f.expandLogic != 0 || f.keepMSBorLSBReg)) {
+    err = "IFFT with grow stages or keepMSBorLSBReg: the 1/numPoints output scalar of the reference (SDFChainRadix22.scala:362) is not built"; return RSP_EUNSUPPORTED; }
+  const uint32_t phys = f.keepMSBorLSBReg ? r.fft[RSP_FFT_REG_KEEPMSBORLSB] : f.keepMSBorLSB;
+  const uint32_t smask = (1u << S) - 1u;
+  a.keep_mask = (phys >> (Smax - S)) & smask;               // a run-time size uses the LAST S stages (SDFChainRadix22.scala:146-150)
+  a.expand_mask = (f.expandLogic >> (Smax - S)) & smask;
+  a.base_growth = popcount32(f.expandLogic & ((1u << (Smax - S)) - 1u));
+  a.wo = f.dataWidth + a.base_growth + popcount32(a.expand_mask);
+  a.out_words = 2 * a.wo > 64 ? 2 : 1;
+  for (int L = 0; L < 16; ++L) a.tw_off[L] = t.tw_off[L];
+  a.win_on = (f.windowFunc != RSP_WINDOW_NONE && a.fft_dir == 1) ? 1 : 0;
+  a.win_shift = f.windowWidth - 2;
+  a.ovf_shift = Smax - S;
   return RSP_OK;
 }
 

@@ -147,8 +147,8 @@ class FFTParams:
             self.numPoints, self.dataWidth, self.binPoint, self.twiddleWidth, _abi.TRIM[self.trimType],
             int(self.use4Muls), int(self.useBitReverse), int(self.fftDir), int(self.runTime), mask,
             0 if self.decimType == DIFDecimType else 1, 4 if self.sdfRadix == "2^2" else 2,
-            int(any(e != 0 for e in self.expandLogic)), int(self.keepMSBorLSBReg), int(self.fftDirReg),
-            *(self.windowFunc.to_c() if self.windowFunc is not None else (0, 16, 0.0, 0.0, 0.0)))
+            sum((1 if e else 0) << i for i, e in enumerate(self.expandLogic)), int(self.keepMSBorLSBReg), int(self.fftDirReg),
+            *(self.windowFunc.to_c() if self.windowFunc is not None else (0, 16, 0.0, 0.0, 0.0)), int(self.overflowReg), 0)
 
 
 @dataclass

@@ -31,7 +31,7 @@ def test_library_exports_every_declared_symbol():
     for s in syms:
         assert hasattr(lib, s), f"librsp_b200.so lacks {s}"
     assert sorted(_abi.EXPORTS) == syms
-    assert lib.rsp_abi_version() == 1
+    assert lib.rsp_abi_version() == 2
     assert lib.rsp_status_str(1) == b"RSP_EINVAL"
 
 
@@ -84,8 +84,12 @@ def test_requires_and_no_cpu_fallback():
     assert st == _abi.RSP_EINVAL                                                # CFARParams.scala:42
     st, msg = _create(variant(cfar__includeCASH=1, cfar__minSubWindowSize=0))
     assert st == _abi.RSP_EINVAL and "minSubWindowSize" in msg                  # CFARParams.scala:43-44
-    st, msg = _create(variant(fft__expandLogicAny=1))                           # legal in the reference, not built
+    st, msg = _create(variant(fft__expandLogic=1, fft__sdfRadix=2))             # grow stages: built for the radix 2^2 DIF chain only
     assert st == _abi.RSP_EUNSUPPORTED and "expandLogic" in msg
+    st, msg = _create(variant(fft__dataWidth=24, fft__numPoints=16384))         # the wide FFT block keeps a row of 64-bit points in shared memory
+    assert st == _abi.RSP_EUNSUPPORTED and "8192" in msg
+    st, msg = _create(variant(fft__dataWidth=33))
+    assert st == _abi.RSP_EUNSUPPORTED
     st, msg = _create(variant(fft__decimType=2))
     assert st == _abi.RSP_EINVAL
     st, msg = _create(variant(fft__sdfRadix=8))

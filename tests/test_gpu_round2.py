@@ -73,10 +73,11 @@ def test_fast_kernel_detection_list_only(cuda, oracle, log_n):
     p = fixed_params(n, W, G)
     regs = dict(fftWin=n, thresholdScaler=4, logOrLinearMode=1, divSum=int(np.log2(W)), peakGrouping=0, cfarMode=0, windowCells=W, guardCells=G)
     rows = 77 if log_n == 10 else 7
-    beats = synth.chirps_fixed(rows, n, seed=5 + log_n)
+    beats = synth.chirps_fixed(rows, n, seed=5 + log_n, noise=2.0 ** -7 if log_n == 10 else 2.0 ** -2)   # a noise floor above 1 LSB after the 1/N
     fft, mag, cfar = oracle_cfgs(oracle, p, log_n, 2, regs)
     want, _, want_mag = oracle.chain_fixed_words(fft, mag, cfar, beats, want_stages=True)
     thr, bins, peak = decode_cfar_words(want, n)
+    assert peak.sum() < 1 << 16
     exp = {(r, b): (int(thr[r, b]), int(np.int16(want_mag[r, b] & 0xFFFF))) for r, b in np.argwhere(peak == 1)}
     with R.FftMagCfarChainVanilla(p) as ch:
         configure(ch, log_n, 2, regs)
@@ -336,3 +337,130 @@ def test_fp32_combined_window_os(cuda, oracle):
     for r in range(4):
         g_thr, g_peaks = oracle.golden_cfar_os(mag[r], W, G, 2.5)
         assert np.allclose(want_thr[r], g_thr, rtol=0, atol=0)
+
+
+# ---------------------------------------------------------------------------------------------------- wide FFT block, grow stages, overflow status
+def pack_beats64(re, im, w):
+    m = np.uint64((1 << w) - 1)
+    return ((np.asarray(re, np.int64).astype(np.uint64) & m) << np.uint64(w)) | (np.asarray(im, np.int64).astype(np.uint64) & m)
+
+
+def wide_params(n, dw, bp, tw, grow=None, keep=None, **kw):
+    s = n.bit_length() - 1
+    fp = FFTParams.fixed(dataWidth=dw, twiddleWidth=tw, numPoints=n, binPoint=bp, expandLogic=list(grow or [0] * s),
+                         keepMSBorLSB=list(keep or [True] * s), **kw)
+    return FftMagCfarVanillaParameters(fftParams=fp, magParams=MAGParams.fixed(dataWidth=16, binPoint=0, dataWidthLog=16, binPointLog=9, log2LookUpWidth=9),
+                                       cfarParams=CFARParams(protoIn=FixedPoint(16, 0), protoThreshold=FixedPoint(16, 0), protoScaler=FixedPoint(16, 0),
+                                                             leadLaggWindowSize=16, guardWindowSize=2, fftSize=max(n, 64), CFARAlgorithm=CACFARType))
+
+
+@pytest.mark.parametrize("name,n,dw,bp,tw,grow,kw", [
+    ("24-bit scaled", 1024, 24, 22, 24, None, dict(trimType="Convergent", useBitReverse=True)),
+    ("16-bit grow", 1024, 16, 14, 16, [1] * 10, dict(trimType="Convergent", useBitReverse=True)),
+    ("24-bit grow (128-bit beats)", 1024, 24, 22, 24, [1] * 10, dict(trimType="Convergent", useBitReverse=True)),
+    ("20-bit, some stages grow, one keeps LSBs, 4 multipliers, bit-reversed out", 256, 20, 10, 18, [1, 0, 0, 1, 0, 1, 0, 0],
+     dict(trimType="RoundHalfUp", use4Muls=True, useBitReverse=False, keepMSBorLSB=[True, True, False, True, True, True, True, True])),
+    ("32-bit data, floor", 64, 32, 20, 32, None, dict(trimType="RoundDown", useBitReverse=True)),
+    ("24-bit run-time size 256 of 4096, grow in the skipped stages", 4096, 24, 12, 20, [1, 0, 1, 1, 0, 1, 0, 0, 1, 0, 0, 0],
+     dict(trimType="RoundHalfUp", useBitReverse=True, runTime=True)),
+    ("8192-point 17-bit", 8192, 17, 8, 16, None, dict(trimType="Convergent", useBitReverse=True)),
+])
+def test_wide_fft_block(cuda, oracle, name, n, dw, bp, tw, grow, kw):
+    """AXI4FFTBlock with beats wider than Cat(re16, im16): the configurations behind the reference's 24-bit and grow SQNR results
+    (Radix22SQNRSpec.scala:60-150).  Bit-exact against the oracle (which reproduces the published SQNR points,
+    tests/test_oracle_fft_mag.py), full-range random inputs, overflow status included."""
+    keep = kw.pop("keepMSBorLSB", None)
+    p = wide_params(n, dw, bp, tw, grow, keep, overflowReg=True, **kw)
+    log_n = 8 if "run-time" in name else n.bit_length() - 1
+    m = 1 << log_n
+    rng = np.random.default_rng(len(name))
+    rows = 5
+    re = rng.integers(-(1 << (dw - 1)), 1 << (dw - 1), (rows, m)); im = rng.integers(-(1 << (dw - 1)), 1 << (dw - 1), (rows, m))
+    re[1] >>= 3; im[1] >>= 3                    # a row that stays clear of the wrap corners
+    beats = pack_beats64(re, im, dw)
+    fft, _, _ = oracle_cfgs(oracle, p, log_n, 2, dict(fftWin=max(m, 64)))
+    want, want_ovf = oracle.fft_fixed_words64(fft, beats)
+    with R.FftMagCfarChainVanilla(p) as ch:
+        if p.fftParams.runTime:
+            ch.memWriteWord(p.fftAddress.base, log_n)
+        assert ch.fft_in_beat_bytes == 8
+        k = ch.fft_out_beat_bytes // 8
+        assert k == (2 if want.ndim == 3 else 1)
+        d_in = cuda.from_numpy(beats.view(np.int64)).cuda()
+        d_out = cuda.zeros((rows, m, k), dtype=cuda.int64, device="cuda")
+        ch.fft(d_in, rows, d_out)
+        got = d_out.cpu().numpy().view(np.uint64).reshape(want.shape)
+        ovf = ch.fft_overflow_flags()
+        with pytest.raises(R.RspError):          # LogMagMux / CFAR take 16-bit cells: the chain refuses wide beats
+            ch.run(d_in, rows, 1, out=d_out)
+    bad = np.argwhere(got != want)
+    assert bad.size == 0, f"{name}: {bad.shape[0]} beats differ, first at {bad[0]}"
+    smax = n.bit_length() - 1
+    assert ovf == want_ovf << (smax - log_n), f"{name}: overflow status {ovf:#x} vs {want_ovf << (smax - log_n):#x}"
+
+
+def test_wide_fft_window_and_ifft(cuda, oracle):
+    """window multiply in front of the wide transform (in * window truncated on assignment, SDFFFT.scala:233-234) and the IFFT of a
+    24-bit chain without grow (output scalar 1.0); IFFT with grow stages is refused (the 1/N literal of SDFChainRadix22.scala:362)"""
+    from rsp_chains_b200 import WindowFunctionTypes as WT
+    n, dw, bp, tw = 512, 24, 20, 24
+    rng = np.random.default_rng(5)
+    re = rng.integers(-(1 << 22), 1 << 22, (3, n)); im = rng.integers(-(1 << 22), 1 << 22, (3, n))
+    for fwd in (True, False):
+        p = wide_params(n, dw, bp, tw, trimType="RoundHalfUp", useBitReverse=True, fftDir=fwd, windowFunc=WT.Hanning(16))
+        fft, _, _ = oracle_cfgs(oracle, p, 9, 2, dict(fftWin=n))
+        wre, wim = re, im
+        if fwd:        # the window acts on the forward transform only (SDFFFT.scala:229-245)
+            raw = oracle.window_raw(oracle.window_coeffs(2, n), 16).astype(np.int64)
+            wrap = lambda v: ((v + (1 << (dw - 1))) & ((1 << dw) - 1)) - (1 << (dw - 1))   # noqa: E731
+            wre, wim = wrap((re * raw[None, :]) >> 14), wrap((im * raw[None, :]) >> 14)
+        want, _ = oracle.fft_fixed_words64(fft, pack_beats64(wre, wim, dw))
+        with R.FftMagCfarChainVanilla(p) as ch:
+            d_out = cuda.zeros((3, n), dtype=cuda.int64, device="cuda")
+            ch.fft(cuda.from_numpy(pack_beats64(re, im, dw).view(np.int64)).cuda(), 3, d_out)
+            got = d_out.cpu().numpy().view(np.uint64)
+        assert (got == want).all(), f"fftDir {fwd}"
+    p = wide_params(n, dw, bp, tw, [1] * 9, fftDir=False)
+    with R.FftMagCfarChainVanilla(p) as ch:
+        with pytest.raises(R.RspError) as e:
+            ch.fft(cuda.zeros((1, n), dtype=cuda.int64, device="cuda"), 1, cuda.zeros((1, n, 2), dtype=cuda.int64, device="cuda"))
+        assert e.value.status == R._abi.RSP_EUNSUPPORTED
+
+
+@pytest.mark.parametrize("radix,dit", [("2^2", False), ("2", False), ("2", True), ("2^2", True)])
+def test_fft_overflow_status_register(cuda, oracle, radix, dit):
+    """FFTParams.overflowReg (FFTBlock.scala:67,81-82,97; SDFChainRadix22.scala:473-486): the per-stage status of the last call through
+    rsp_fft_overflow_flags (all stages) and through the register's log2Ceil(numStages)-bit field; rows below half scale report nothing,
+    a run-time size reports on the physical stages it uses; the chain (rsp_run) reports it too"""
+    n, smax = 1024, 10
+    p = R.fft_mag_cfar_chain_vanilla_app_params()
+    p.fftParams.binPoint = 0
+    p.magParams.binPoint = 0
+    p.cfarParams.protoIn = p.cfarParams.protoThreshold = p.cfarParams.protoScaler = FixedPoint(16, 0)
+    p.fftParams.overflowReg = True
+    p.fftParams.sdfRadix = radix
+    p.fftParams.decimType = R.DITDecimType if dit else R.DIFDecimType
+    regs = dict(fftWin=n, thresholdScaler=4, logOrLinearMode=1, divSum=4, peakGrouping=0, cfarMode=0, windowCells=16, guardCells=4)
+    quiet = synth.chirps_fixed(4, n, seed=9)
+    loud = synth.random_beats(4, n, seed=10)
+    dc = np.full((2, n), (20000 << 16) & 0xFFFFFFFF, dtype=np.uint32)          # re = 20000: the DC path flags every stage
+    with R.FftMagCfarChainVanilla(p) as ch:
+        configure(ch, 10, 2, regs)
+        for beats in (quiet, loud, dc):
+            fft, _, _ = oracle_cfgs(oracle, p, 10, 2, regs)
+            want_out, want_ovf = oracle.fft_fixed_words_ovf(fft, beats)
+            d_out = cuda.empty((beats.shape[0], n), dtype=cuda.int32, device="cuda")
+            ch.fft(to_dev(cuda, beats), beats.shape[0], d_out)
+            assert (from_dev_u32(d_out) == want_out).all()
+            assert ch.fft_overflow_flags() == want_ovf
+            assert ch.memReadWord(p.fftAddress.base + 4 * p.beatBytes) == want_ovf & 0xF      # log2Ceil(10) = 4 bits
+            ch.run(to_dev(cuda, beats), beats.shape[0], 1, out=d_out)
+            assert ch.fft_overflow_flags() == want_ovf
+        assert oracle.fft_fixed_words_ovf(fft, quiet)[1] == 0 and oracle.fft_fixed_words_ovf(fft, dc)[1] != 0
+        if not dit and radix == "2^2":      # run-time size 256: the last 8 physical stages
+            configure(ch, 8, 2, dict(regs, fftWin=256))
+            fft, _, _ = oracle_cfgs(oracle, p, 8, 2, dict(regs, fftWin=256))
+            want_out, want_ovf = oracle.fft_fixed_words_ovf(fft, dc[:, :256])
+            d_out = cuda.empty((2, 256), dtype=cuda.int32, device="cuda")
+            ch.fft(to_dev(cuda, np.ascontiguousarray(dc[:, :256])), 2, d_out)
+            assert ch.fft_overflow_flags() == want_ovf << 2 and want_ovf != 0

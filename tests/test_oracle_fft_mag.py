@@ -330,3 +330,76 @@ def test_window_rom_and_multiply():
     assert O.apply_window_words(b, O.window_raw([0.5], 16))[0, 0] == 0xFFFF0000
     # run-time size below numPoints: the first n ROM entries
     assert (O.apply_window_words(beats[:, :64], raw) == O.apply_window_words(np.pad(beats[:, :64], ((0, 0), (0, n - 64))), raw)[:, :64]).all()
+
+
+# ---------------------------------------------------------------------------------------------------- wide data, grow stages, overflow flags
+def pack_beats64(re, im, w):
+    m = (1 << w) - 1
+    return ((np.asarray(re, np.int64).astype(np.uint64) & np.uint64(m)) << np.uint64(w)) | (np.asarray(im, np.int64).astype(np.uint64) & np.uint64(m))
+
+
+def unpack_beats64(words, w):
+    """Cat(re, im) with w-bit halves out of 64-bit beats [..., n] or 128-bit beats [..., n, 2] (low word first)"""
+    words = np.asarray(words, np.uint64)
+    if words.ndim >= 2 and words.shape[-1] == 2 and 2 * w > 64:
+        lo, hi = words[..., 0].astype(object), words[..., 1].astype(object)
+        full = lo + (hi << 64)
+    else:
+        full = words.astype(object)
+    m = (1 << w) - 1
+    def sx(v):
+        v = v & m
+        return v - (1 << w) if v >> (w - 1) else v
+    f = np.vectorize(lambda v: sx(int(v) >> w), otypes=[object])
+    g = np.vectorize(lambda v: sx(int(v)), otypes=[object])
+    return f(full).astype(np.float64), g(full).astype(np.float64)
+
+
+@pytest.mark.parametrize("name,dw,bp,grow,want_db", [("24-bit scaled", 24, 22, False, 98), ("16-bit grow", 16, 14, True, 82), ("24-bit grow", 24, 22, True, 130)])
+def test_fft_reproduces_published_sqnr_of_wide_and_grow_configs(oracle, name, dw, bp, grow, want_db):
+    """Radix22SQNRSpec.scala:60-150 at N = 1024, Convergent, twiddleWidth = dataWidth: the published chart (SQNRdataWidth.png) reads
+    ~98 dB (24-bit, scale every stage), ~82 dB (16-bit, expandLogic all ones), ~130 dB (24-bit, expandLogic all ones); +-3 dB.
+    Grow stages keep the butterfly outputs in a type one bit wider (SDFFFTParams.scala:119-123): the result is FFT(x), not FFT(x)/N,
+    and a 24-bit input comes out 34 bits wide (128-bit beats)."""
+    log_n, n = 10, 1024
+    cfg = oracle.fft_cfg(log_n, dw, bp, dw, "Convergent", False, True, (1 << log_n) - 1, True, expand_mask=(1 << log_n) - 1 if grow else 0)
+    wo = oracle.fft_stage_width(cfg, log_n - 1)
+    assert wo == dw + (log_n if grow else 0)
+    vals = []
+    for rep in range(6):
+        re, im = java_rand_signal(oracle, n, 300 + rep)
+        out, ovf = oracle.fft_fixed_words64(cfg, pack_beats64(quantize(re, bp), quantize(im, bp), dw)[None, :])
+        ore, oim = unpack_beats64(out[0], wo)
+        ref = np.fft.fft(re + 1j * im) / (1 if grow else n)
+        vals.append(sqnr_db((ore + 1j * oim) / (1 << bp), ref))
+        if grow:
+            assert ovf == 0          # a grow stage cannot overflow (SDFChainRadix22.scala:455-457)
+    assert abs(np.mean(vals) - want_db) < 3.0, f"{name}: {np.mean(vals):.1f} dB vs published ~{want_db}"
+
+
+def test_fft_overflow_flags(oracle):
+    """per-stage overflow status (SDFChainRadix22.scala:473-486): `tooBig` = a grown butterfly output at or above 2^(w-1); the check
+    looks at the sum BEFORE div2, so it also fires on stages that scale.  Hand-derived: a constant row x = (A, 0) doubles its DC term
+    at every stage's sum before the halving: flag at stage 0 iff 2A >= 2^15; a row below half scale never flags; full-scale square
+    wave flags the stages where it adds up."""
+    log_n, n = 6, 64
+    cfg = oracle.fft_cfg(log_n, 16, 0, 16, "RoundHalfUp", False, True, (1 << log_n) - 1, True)
+    for amp, want0 in ((16383, 0), (16384, 1)):
+        _, _, m = oracle.fft_fixed_ex(cfg, np.full(n, amp), np.zeros(n, np.int64))
+        # the sum outputs keep the value (A + A) / 2 = A: the same test repeats at every stage, on the DC path
+        assert m == (((1 << log_n) - 1) if want0 else 0)
+    # difference path: +A, -A alternating at distance N/2 -> stage 0 difference 2A
+    x = np.where(np.arange(n) < n // 2, 20000, -20000)
+    _, _, m = oracle.fft_fixed_ex(cfg, x, np.zeros(n, np.int64))
+    assert m & 1
+    # keep-LSB stages (no scaling) report the same flag, and there the value really wraps
+    cfg2 = oracle.fft_cfg(log_n, 16, 0, 16, "RoundHalfUp", False, True, 0, True)
+    ore, _, m2 = oracle.fft_fixed_ex(cfg2, np.full(n, 600), np.zeros(n, np.int64))
+    assert ore[0] == ((600 * 64 + 32768) % 65536) - 32768 and m2 == 0b100000     # 600 * 2^6 = 38400 wraps at the last stage only
+    # radix-2 chain and DIT carry the same check (SDFChainRadix2.scala:409-423)
+    for radix, dit in (("2", False), ("2", True), ("2^2", True)):
+        c = oracle.fft_cfg(log_n, 16, 0, 16, "RoundHalfUp", False, True, (1 << log_n) - 1, True, sdf_radix=radix, decim_dit=dit, num_stages=log_n)
+        _, _, m = oracle.fft_fixed_ex(c, np.full(n, 16384), np.zeros(n, np.int64))
+        assert m != 0
+        _, _, m = oracle.fft_fixed_ex(c, np.full(n, 100), np.zeros(n, np.int64))
+        assert m == 0
