@@ -437,13 +437,27 @@ def main():
     det_count = torch.zeros(1, dtype=torch.int32, device="cuda")
     ch.run(d_in, n_chirps, N_RX, out=d_out, det_list=det_list, det_count=det_count)
     torch.cuda.synchronize()
-    gathered = R.gather_detections(det_list, det_count)      # warm-up (NCCL communicator set-up)
-    barrier()
-    t0 = time.perf_counter()
-    gathered = R.gather_detections(det_list, det_count)
-    torch.cuda.synchronize()
-    gather_ms = max_over_ranks((time.perf_counter() - t0) * 1e3)
-    n_gathered = int(gathered.shape[0])
+    slot = 1 << 18
+    gather_api = "rsp_gather_detections (C ABI: ncclAllGather of counts + one slot of %d entries per rank)" % slot
+    try:
+        comm = R.NcclComm(local_rank)
+        R.gather_detections_nccl(ch, comm, det_list, det_count, slot)      # warm-up
+        barrier()
+        t0 = time.perf_counter()
+        gathered, counts = R.gather_detections_nccl(ch, comm, det_list, det_count, slot)
+        torch.cuda.synchronize()
+        gather_ms = max_over_ranks((time.perf_counter() - t0) * 1e3)
+        n_gathered = int(torch.clamp(counts, max=slot).sum().item())
+        comm.close()
+    except Exception as e:      # no NCCL library on the box: the torch.distributed helper does the same exchange
+        gather_api = f"gather_detections (torch.distributed all_gather; the C ABI path failed: {e!r})"
+        gathered = R.gather_detections(det_list, det_count)
+        barrier()
+        t0 = time.perf_counter()
+        gathered = R.gather_detections(det_list, det_count)
+        torch.cuda.synchronize()
+        gather_ms = max_over_ranks((time.perf_counter() - t0) * 1e3)
+        n_gathered = int(gathered.shape[0])
 
     if rank == 0:
         peak, peak_src = measured_peak()
@@ -469,7 +483,7 @@ def main():
                                         "d2h_bytes_per_step": int(min(n_dets, max_dets)) * 16 + 4, "detections_per_step": int(n_dets),
                                         "peak_bits_in_full_output": n_peaks_out,
                                         "api": "rsp_run_host(h_out = NULL, h_dets): the detection list is the only result copied back"}},
-            "gather_ms": gather_ms, "gather": f"all-gather of {n_gathered} detections x 16 B over {world} rank(s) (NCCL when N > 1), outside the timed step",
+            "gather_ms": gather_ms, "gather": f"{gather_api}: {n_gathered} detections x 16 B over {world} rank(s), outside the timed step",
             "gpu_launches": int(launches), "e2e_gpu_launches": int(e2e_launches), "clocks": clocks,
         }
         if world == 1 and not args.no_cpu_baseline:

@@ -257,6 +257,21 @@ rsp_status rsp_run_host(rsp_chain *c, const void *h_in, uint32_t n_chirps, uint3
 rsp_status rsp_host_alloc(void **p, size_t bytes); /* pinned host memory */
 void rsp_host_free(void *p);
 
+/* ---- multi-GPU: gathering the detection lists ------------------------------------------------------------------
+ * Frames / chirps are sharded over the GPUs with no collective on the data path (rows are independent:
+ * generators/cfar/src/main/scala/CFARCoreWithMem.scala:93-104); the detection lists are the only exchange.  One process per GPU.
+ * replaces: nothing in the reference (one stream, one FPGA); this is SURVEY 8b's rsp_gather_detections.
+ * nccl_comm is an ncclComm_t (any communicator of the process: the helpers below create one without another NCCL binding; NCCL itself
+ * is bound at run time from libnccl.so.2).  Every rank passes the same slot_capacity (<= its local->capacity).  On return (asynchronous
+ * on `stream`) d_counts[r] = rank r's detection count and d_gathered[r * slot_capacity + i], i < min(d_counts[r], slot_capacity), its
+ * detections; d_gathered has room for n_ranks * slot_capacity entries, d_counts for n_ranks words (both on the device). */
+#define RSP_NCCL_UNIQUE_ID_BYTES 128
+rsp_status rsp_gather_detections(rsp_chain *c, void *nccl_comm, const rsp_dets *local, uint32_t slot_capacity,
+                                 rsp_detection *d_gathered, uint32_t *d_counts, void *stream);
+rsp_status rsp_nccl_get_unique_id(uint8_t id[RSP_NCCL_UNIQUE_ID_BYTES]);                 /* ncclGetUniqueId, on one rank; ship it to the others */
+rsp_status rsp_nccl_comm_init_rank(void **comm, int n_ranks, const uint8_t id[RSP_NCCL_UNIQUE_ID_BYTES], int rank, int device);
+void rsp_nccl_comm_destroy(void *comm);
+
 /* ---- introspection ------------------------------------------------------------------------------------------ */
 const char *rsp_status_str(rsp_status s);
 const char *rsp_last_error(void);

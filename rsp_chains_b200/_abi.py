@@ -6,7 +6,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "librsp_b200.so")
+# RSP_B200_LIB: another build of the library (A/B studies of compile-time kernel knobs, scripts/build_variant.sh)
+LIB_PATH = os.environ.get("RSP_B200_LIB") or os.path.join(_HERE, "librsp_b200.so")
 
 RSP_OK, RSP_EINVAL, RSP_ECUDA, RSP_ENOMEM, RSP_EUNSUPPORTED = 0, 1, 2, 3, 4
 BLK_PLFG, BLK_NCO, BLK_FFT, BLK_MAG, BLK_CFAR = 0, 1, 2, 3, 4
@@ -23,6 +24,7 @@ EXPORTS = [
     "rsp_generate", "rsp_run_host", "rsp_host_alloc", "rsp_host_free", "rsp_status_str", "rsp_last_error",
     "rsp_abi_version", "rsp_kernel_launches", "rsp_variant_name", "rsp_bytes_per_chirp",
     "rsp_fft_in_beat_bytes", "rsp_fft_out_beat_bytes", "rsp_fft_overflow_flags",
+    "rsp_gather_detections", "rsp_nccl_get_unique_id", "rsp_nccl_comm_init_rank", "rsp_nccl_comm_destroy",
 ]
 
 
@@ -123,6 +125,11 @@ def lib():
         L.rsp_fft_out_beat_bytes.argtypes = [vp]
         L.rsp_fft_out_beat_bytes.restype = u32
         L.rsp_fft_overflow_flags.argtypes = [vp, C.POINTER(u32), vp]
+        L.rsp_gather_detections.argtypes = [vp, vp, C.POINTER(Dets), u32, vp, vp, vp]
+        L.rsp_nccl_get_unique_id.argtypes = [C.c_char_p]
+        L.rsp_nccl_comm_init_rank.argtypes = [C.POINTER(vp), i32, C.c_char_p, i32, i32]
+        L.rsp_nccl_comm_destroy.argtypes = [vp]
+        L.rsp_nccl_comm_destroy.restype = None
         _lib = L
     return _lib
 

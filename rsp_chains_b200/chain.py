@@ -324,6 +324,46 @@ def gather_detections(det_list, det_count, group=None):
     return torch.cat(parts, dim=0) if parts else torch.zeros((0, 5), dtype=det_list.dtype, device=det_list.device)
 
 
+class NcclComm:
+    """An ncclComm_t created through the C ABI (rsp_nccl_get_unique_id / rsp_nccl_comm_init_rank): what a host without its own NCCL
+    binding (the Scala side of INTEGRATION.md) does.  The 128-byte unique id of rank 0 travels through torch.distributed here."""
+
+    def __init__(self, device: int, group=None):
+        torch = _torch()
+        import torch.distributed as dist
+        self._lib = _abi.lib()
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        buf = C.create_string_buffer(128)
+        if self.rank == 0:
+            _abi.check(self._lib.rsp_nccl_get_unique_id(buf))
+        if self.world > 1:
+            box = [bytes(buf.raw)]
+            dist.broadcast_object_list(box, src=0, group=group)
+            buf = C.create_string_buffer(box[0], 128)
+        self._h = C.c_void_p()
+        _abi.check(self._lib.rsp_nccl_comm_init_rank(C.byref(self._h), self.world, buf, self.rank, int(device)))
+        torch.cuda.synchronize()
+
+    def close(self):
+        if self._h and self._h.value:
+            self._lib.rsp_nccl_comm_destroy(self._h)
+            self._h = C.c_void_p()
+
+
+def gather_detections_nccl(chain, comm: NcclComm, det_list, det_count, slot_capacity: int, stream=None):
+    """rsp_gather_detections: the detection lists of all ranks through two ncclAllGather calls on `stream` (asynchronous).
+    Returns (gathered int32 [world, slot_capacity, 4], counts int32 [world]) device tensors: rank r's detections are
+    gathered[r, :min(counts[r], slot_capacity)]."""
+    torch = _torch()
+    gathered = torch.empty((comm.world, slot_capacity, 4), dtype=torch.int32, device=det_list.device)
+    counts = torch.zeros(comm.world, dtype=torch.int32, device=det_list.device)
+    d = _abi.Dets(det_list.data_ptr(), det_count.data_ptr(), det_list.shape[0])
+    _abi.check(_abi.lib().rsp_gather_detections(chain._h, comm._h, C.byref(d), slot_capacity, gathered.data_ptr(), counts.data_ptr(),
+                                                _stream_ptr(stream)))
+    return gathered, counts
+
+
 def shard_rows(n_units: int, world_size: int, rank: int):
     """contiguous block of units (frames / chirps) owned by `rank`: unit u goes to gpu u * world / n_units"""
     lo = (rank * n_units + world_size - 1) // world_size

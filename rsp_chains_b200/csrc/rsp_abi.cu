@@ -18,6 +18,7 @@ using namespace rsp;
 
 static thread_local std::string g_last_error;
 static rsp_status fail(rsp_status st, const std::string &msg) { g_last_error = msg; return st; }
+extern "C" void rsp_set_last_error_(const char *msg) { g_last_error = msg ? msg : ""; }   // for the other units of the library (rsp_nccl.cu)
 #define CUDA_TRY(expr)                                                                                       \
   do {                                                                                                       \
     cudaError_t e__ = (expr);                                                                                \

@@ -484,8 +484,19 @@ __device__ __noinline__ void fast_detections(const FastDetArgs a, int tl, uint32
 }
 
 // EJ = number of leading / trailing iterations j whose bins may miss a window (ceil((W + G) / TPC), checked by the host)
+// resident CTAs per SM the register budget is cut for: 1024 threads at 64 registers by default; RSP_FAST_MINB<S> (A/B knob) asks for
+// fewer CTAs with more registers each
+#ifndef RSP_FAST_MINB14
+#define RSP_FAST_MINB14 0
+#endif
+#ifndef RSP_FAST_MINB10
+#define RSP_FAST_MINB10 0
+#endif
+template <int S, int LP> constexpr int fast_min_blocks() {
+  return (S == 14 && RSP_FAST_MINB14 > 0) ? RSP_FAST_MINB14 : ((S == 10 && RSP_FAST_MINB10 > 0) ? RSP_FAST_MINB10 : 1024 / FGeo<S, LP>::THREADS);
+}
 template <int S, int LP, int CMODE, bool LINEAR, int EJ>
-__global__ void __launch_bounds__(FGeo<S, LP>::THREADS, 1024 / FGeo<S, LP>::THREADS) chain_fixed_fast_kernel(const FastArgs a) {
+__global__ void __launch_bounds__(FGeo<S, LP>::THREADS, fast_min_blocks<S, LP>()) chain_fixed_fast_kernel(const FastArgs a) {
   using Gm = FGeo<S, LP>;
   constexpr int N = Gm::N, TPC = Gm::TPC, CPC = Gm::CPC, PTS = Gm::PTS;
   extern __shared__ __align__(16) uint32_t smem[];

@@ -130,10 +130,10 @@ def run_f32(cuda, p, log_n, sel, regs, scaler, x32):
         return d_thr.cpu().numpy(), unpack_mask(d_mask.cpu().numpy().view(np.uint32), n), ch.variant
 
 
-def check_f32(thr, pk, mag, want_thr, want_pk, what):
+def check_f32(thr, pk, mag, want_thr, want_pk, what, tol=REL_TOL):
     scale = np.abs(want_thr).max()
     rel = np.abs(thr - want_thr) / np.maximum(np.abs(want_thr), 1e-3 * scale)
-    assert rel.max() < REL_TOL, f"{what}: max relative threshold error {rel.max():.3e}"
+    assert rel.max() < tol, f"{what}: max relative threshold error {rel.max():.3e}"
     sure = np.abs(mag - want_thr) / np.maximum(np.abs(want_thr), 1e-3 * scale) > 10 * REL_TOL
     assert (pk[sure] == want_pk[sure]).all(), f"{what}: detections differ"
     assert sure.mean() > 0.99
@@ -169,7 +169,8 @@ def test_fp32_lis_and_asr_cores(cuda, oracle, core, pg):
         thr, pk, variant = run_f32(cuda, p, log_n, sel, regs, 3.0, x32)
         assert variant == f"chain_f32<{log_n}>", variant
         mag, want_thr, want_pk = f64_chain(oracle, xq, log_n, sel, regs, 3.0, W, G, **kw)
-        check_f32(thr, pk, mag, want_thr, want_pk, f"{core} pg {pg} sel {sel}")
+        # |z|^2 carries twice the relative error of |z|, and an ordered statistic is ONE cell, not an average of W of them: 2e-4 there
+        check_f32(thr, pk, mag, want_thr, want_pk, f"{core} pg {pg} sel {sel}", tol=2 * REL_TOL if sel == 1 else REL_TOL)
         assert (want_thr[:, :W + G] == 0).all() and (thr[:, :W + G] == 0).all()
 
 
