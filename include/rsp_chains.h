@@ -84,7 +84,10 @@ typedef struct {
   double windowA0, windowA1, windowA2;   /* Hamming: alpha, beta; Blackman: a0, a1, a2 (WindowFunc.scala:13-28)      */
   int32_t overflowReg;      /* FFTParams.overflowReg: the per-stage overflow status is computed (RSP_FFT_REG_OVERFLOW, rsp_fft_overflow_flags);
                              * such a chain runs on the run-time-parameter kernels                                                      */
-  int32_t reserved_;
+  int32_t windowRam;        /* 1: the block is FFTBlockWithWindowing (generators/sdf-fft/src/main/scala/FFTBlockWithWindowing.scala:18-176): a RAM of
+                             * numPoints protoWin coefficients written at run time (rsp_fft_window_ram_write) multiplies the input,
+                             * `inComplex.real * winCoeff` (:159-166), when the doWindowing register is 1 -- in both transform directions;
+                             * requires windowFunc = RSP_WINDOW_NONE (:19); the register file is RSP_FFTW_REG_* below                  */
 } rsp_fft_params;
 typedef enum { RSP_WINDOW_NONE = 0, RSP_WINDOW_HAMMING = 1, RSP_WINDOW_HANNING = 2, RSP_WINDOW_BLACKMAN = 3, RSP_WINDOW_TRIANGULAR = 4,
                RSP_WINDOW_USER = 5 } rsp_window;
@@ -126,7 +129,10 @@ typedef struct {
 typedef struct {
   int32_t tableSize, tableWidth, phaseWidth;
   int32_t phaseAccEnable;
-  int32_t rasterizedMode, nInterpolationTerms, ditherEnable, useMultiplier, useQAM; /* non-zero -> RSP_EUNSUPPORTED */
+  int32_t rasterizedMode, nInterpolationTerms, ditherEnable;   /* non-zero -> RSP_EUNSUPPORTED */
+  int32_t useMultiplier;   /* the output multiplier and its two registers RSP_NCO_REG_* (NCOLazyModuleBlock.scala:262-269,354-364)   */
+  int32_t useQAM;          /* non-zero -> RSP_EUNSUPPORTED */
+  int32_t roundingMode;    /* rsp_trim, FixedNCOParams.roundingMode (default RoundHalfUp = 0): trim of the multiplier's product     */
 } rsp_nco_params;
 
 /* RspChainVanillaParameters / FftMagCfarVanillaParameters (src/main/scala/RspChain.scala:24-33,
@@ -148,6 +154,9 @@ void rsp_chain_params_default(rsp_chain_params *p);
 enum { /* AXI4FFTBlock (generators/sdf-fft/src/main/scala/FFTBlock.scala:86-102) */
   RSP_FFT_REG_FFTSIZE = 0 /* log2 of the run-time size */, RSP_FFT_REG_FFTDIR = 1, RSP_FFT_REG_KEEPMSBORLSB = 2,
   RSP_FFT_REG_BUSY = 3 /* RO */, RSP_FFT_REG_OVERFLOW = 4 /* RO */ };
+enum { /* FFTBlockWithWindowing (generators/sdf-fft/src/main/scala/FFTBlockWithWindowing.scala:134-152): used instead when windowRam = 1 */
+  RSP_FFTW_REG_FFTSIZE = 0, RSP_FFTW_REG_FFTDIR = 1, RSP_FFTW_REG_DOWINDOWING = 2, RSP_FFTW_REG_KEEPMSBORLSB = 3,
+  RSP_FFTW_REG_BUSY = 4 /* RO */, RSP_FFTW_REG_OVERFLOW = 5 /* RO */ };
 enum { /* AXI4LogMagMuxBlock (generators/logMagMux/src/main/scala/LogMagMuxDspBlock.scala:31-39) */
   RSP_MAG_REG_SEL = 0 /* 0 bypass, 1 |z|^2, 2 JPL magnitude, 3 log2 magnitude */ };
 enum { /* AXI4CFARBlock (generators/cfar/src/main/scala/CFARDspBlock.scala:96-130) */
@@ -158,6 +167,9 @@ enum { /* PLFGDspBlockMem (generators/plfg/src/main/scala/PLFGDspBlockMem.scala:
   RSP_PLFG_REG_ENABLE = 0, RSP_PLFG_REG_RESET = 1, RSP_PLFG_REG_FRAMENUM = 2, RSP_PLFG_REG_INTERFRAMENUMOFSAMPLES = 3,
   RSP_PLFG_REG_DIFFERENTCHIRPSNUM = 4, RSP_PLFG_REG_STARTINGPOINT = 5, RSP_PLFG_REG_SEGMENTNUMS0 = 6
   /* then segmentNums[maxChirpOrdinalNum], repeatedChirpNums[maxNumOfDifferentChirps], chirpOrdinalNums[maxNumOfDifferentChirps] */ };
+enum { /* AXI4NCOLazyModuleBlock with pincType Streaming, poffType Fixed and useMultiplier (NCOLazyModuleBlock.scala:262-269); without
+        * the multiplier this configuration has no register file */
+  RSP_NCO_REG_ENABLEMULTIPLYING = 0, RSP_NCO_REG_MULTIPLYINGFACTOR = 1 /* tableWidth bits, read as FixedPoint(w, w - 2) */ };
 /* fp32 chains only: the threshold scaler as a float (the FixedPoint register has no fp32 meaning) */
 #define RSP_CFAR_REG_THRESHOLDSCALER_F32 0x100u
 
@@ -197,6 +209,11 @@ rsp_status rsp_plfg_ram_write(rsp_chain *c, uint32_t word_index, uint32_t value)
  * must have been created with windowFunc = RSP_WINDOW_USER (until this call its window is all ones).  n must equal numPoints
  * (SDFFFT.scala:59: "Length of specified window function is not the same as fft size").  Synchronises the device.            */
 rsp_status rsp_fft_window_user(rsp_chain *c, const double *coeffs, uint32_t n);
+/* replaces: memWriteWord(ramAddress.base + word_index * beatBytes, value) into the window RAM of FFTBlockWithWindowing
+ *           (FFTBlockWithWindowing.scala:44-63; generators/sdf-fft/src/test/scala/FFTBlockWithWindowingSpec.scala:104-108): the low
+ *           windowWidth bits of value are one protoWin coefficient, FixedPoint(windowWidth, windowWidth - 2).  The RAM starts as zeros.
+ *           Takes effect with the next run call. */
+rsp_status rsp_fft_window_ram_write(rsp_chain *c, uint32_t word_index, uint32_t value);
 
 /* ---- the hot path, device buffers ------------------------------------------------------------------------
  * replaces: streaming n_rx*n_chirps chirps of fftSize beats into FftMagCfarChainVanilla.streamNode and reading

@@ -1067,6 +1067,12 @@ uint32_t rspo_nco_words(const rspo_nco_cfg *c, const int32_t *freq, uint32_t *ou
     case 2: s = -tab[addr]; co = -((addr == 0) ? one : tab[raddr]); break;
     default: s = -((addr == 0) ? one : tab[raddr]); co = tab[addr]; break;
     }
+    if (c->use_multiplier) { /* (NCOLazyModuleBlock.scala:354-364) beatBytes = 4 */
+      const int w = c->table_width;
+      const int64_t f = rspo_wrap(c->enable_multiplying ? (int64_t)c->multiplying_factor : ((int64_t)1 << 14), w);
+      s = (int32_t)rspo_wrap(rspo_trim((int64_t)s * f, w - 2, c->rounding_mode), w);
+      co = (int32_t)rspo_wrap(rspo_trim((int64_t)co * f, w - 2, c->rounding_mode), w);
+    }
     out[i] = (((uint32_t)co & 0xFFFFu) << 16) | ((uint32_t)s & 0xFFFFu); /* Cat(cos, sin) (:452) */
   }
   free(tab);

@@ -184,6 +184,12 @@ typedef struct {
   int32_t phase_acc_enable;
   uint32_t phase0;     /* accumulator state before the first sample */
   uint32_t poff;
+  /* output multiplier (FixedNCOParams.useMultiplier, NCOLazyModuleBlock.scala:354-364): sin and cos are each multiplied by
+   * factor = enableMultiplying ? multiplyingFactor : 1 << (beatBytes * 4 - 2), both read as FixedPoint(w, w - 2), context_* with
+   * binaryPointGrowth 0 under roundingMode, result reinterpreted as protoOut (low w bits) */
+  int32_t use_multiplier, enable_multiplying;
+  uint32_t multiplying_factor;
+  int32_t rounding_mode;   /* rspo trim type */
 } rspo_nco_cfg;
 /* freq: PLFG words; out: Cat(cos16, sin16) beats (NCOLazyModuleBlock.scala:452); returns final phase */
 uint32_t rspo_nco_words(const rspo_nco_cfg *cfg, const int32_t *freq, uint32_t *out, int64_t n);

@@ -3,7 +3,7 @@ hand-written sm_100a CUDA behind a C ABI (include/rsp_chains.h), with a host-sid
 case classes and chain/block interface.  CUDA-only: there is no CPU fallback."""
 from . import _abi
 from ._abi import RspError
-from .chain import (FftMagCfarChainVanilla, NcclComm, RspChainVanilla, gather_detections, gather_detections_nccl, host_alloc, host_free, shard_rows)
+from .chain import (FFTBlockWithWindowing, FftMagCfarChainVanilla, NcclComm, RspChainVanilla, gather_detections, gather_detections_nccl, host_alloc, host_free, shard_rows)
 from .params import (AddressSet, CACFARType, CFARParams, Convergent, DIFDecimType, DITDecimType, FFTParams,
                      FftMagCfarVanillaParameters, FixedNCOParams, FixedPLFGParams, FixedPoint, GOSCACFARType, GOSCFARType, OSGoldenCFARType,
                      MAGParams, RoundDown, RoundHalfUp, RspChainVanillaParameters, WindowFunctionType, WindowFunctionTypes, fft_mag_cfar_chain_vanilla_app_params,

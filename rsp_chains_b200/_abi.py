@@ -20,7 +20,7 @@ TRIM = {"RoundHalfUp": 0, "RoundDown": 1, "Floor": 1, "Convergent": 2, "RoundHal
 
 EXPORTS = [
     "rsp_chain_params_default", "rsp_chain_create", "rsp_chain_destroy", "rsp_reg_write", "rsp_reg_read",
-    "rsp_plfg_ram_write", "rsp_fft_window_user", "rsp_run", "rsp_run_from_generator", "rsp_fft_run", "rsp_mag_run", "rsp_cfar_run",
+    "rsp_plfg_ram_write", "rsp_fft_window_user", "rsp_fft_window_ram_write", "rsp_run", "rsp_run_from_generator", "rsp_fft_run", "rsp_mag_run", "rsp_cfar_run",
     "rsp_generate", "rsp_run_host", "rsp_host_alloc", "rsp_host_free", "rsp_status_str", "rsp_last_error",
     "rsp_abi_version", "rsp_kernel_launches", "rsp_variant_name", "rsp_bytes_per_chirp",
     "rsp_fft_in_beat_bytes", "rsp_fft_out_beat_bytes", "rsp_fft_overflow_flags",
@@ -36,7 +36,7 @@ class FftParams(C.Structure):
     _fields_ = _i32s("numPoints", "dataWidth", "binPoint", "twiddleWidth", "trimType", "use4Muls", "useBitReverse",
                      "fftDir", "runTime") + [("keepMSBorLSB", C.c_uint32)] + _i32s(
         "decimType", "sdfRadix") + [("expandLogic", C.c_uint32)] + _i32s("keepMSBorLSBReg", "fftDirReg", "windowFunc", "windowWidth") + [
-        ("windowA0", C.c_double), ("windowA1", C.c_double), ("windowA2", C.c_double)] + _i32s("overflowReg", "reserved_")
+        ("windowA0", C.c_double), ("windowA1", C.c_double), ("windowA2", C.c_double)] + _i32s("overflowReg", "windowRam")
 
 
 class MagParams(C.Structure):
@@ -56,7 +56,7 @@ class PlfgParams(C.Structure):
 
 class NcoParams(C.Structure):
     _fields_ = _i32s("tableSize", "tableWidth", "phaseWidth", "phaseAccEnable", "rasterizedMode",
-                     "nInterpolationTerms", "ditherEnable", "useMultiplier", "useQAM")
+                     "nInterpolationTerms", "ditherEnable", "useMultiplier", "useQAM", "roundingMode")
 
 
 class ChainParams(C.Structure):
@@ -100,6 +100,7 @@ def lib():
         L.rsp_reg_read.argtypes = [vp, i32, u32, C.POINTER(u32)]
         L.rsp_plfg_ram_write.argtypes = [vp, u32, u32]
         L.rsp_fft_window_user.argtypes = [vp, C.POINTER(C.c_double), u32]
+        L.rsp_fft_window_ram_write.argtypes = [vp, u32, u32]
         L.rsp_run.argtypes = [vp, vp, u32, u32, vp, vp, C.POINTER(Dets), vp]
         L.rsp_run_from_generator.argtypes = [vp, u32, u32, vp, vp, C.POINTER(Dets), vp, vp]
         L.rsp_fft_run.argtypes = [vp, vp, u32, vp, vp]

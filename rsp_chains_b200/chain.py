@@ -89,8 +89,8 @@ class _Chain:
 
     def memReadWord(self, addr: int) -> int:
         blk, idx = self._decode(addr)
-        if blk == "plfg_ram":
-            raise ValueError("the PLFG config RAM is write-only on this bus")
+        if blk in ("plfg_ram", "fft_win_ram"):
+            raise ValueError("this RAM is write-only on this bus")
         v = C.c_uint32(0)
         _abi.check(self._lib.rsp_reg_read(self._h, blk, idx, C.byref(v)))
         return v.value
@@ -268,6 +268,35 @@ class FftMagCfarChainVanilla(_Chain):
         amap = [(params.fftAddress, _abi.BLK_FFT), (params.magAddress, _abi.BLK_MAG), (params.cfarAddress, _abi.BLK_CFAR)]
         super().__init__(_c_params(params.fftParams, params.magParams, params.cfarParams), amap, params.beatBytes, device)
         self._load_user_window(params.fftParams)
+
+
+class FFTBlockWithWindowing(_Chain):
+    """The FFT block with a run-time window RAM (generators/sdf-fft/src/main/scala/FFTBlockWithWindowing.scala:18-176): same constructor
+    arguments as the reference (csrAddress, ramAddress, params, beatBytes).  Registers: fftSize 0, fftDir 1, doWindowing 2,
+    keepMSBorLSBReg 3, busy 4, overflowReg 5 (:134-152); memWriteWord(ramAddress.base + i * beatBytes, raw) writes coefficient i."""
+
+    def __init__(self, csrAddress: AddressSet, ramAddress: AddressSet, params: FFTParams, beatBytes: int = 4, device: int = 0,
+                 windowDataWidth: int = 16):
+        import copy
+        assert params.windowFunc is None or params.windowFunc.kind == 0, \
+            "Parameter for window function inside SDFFFT module must be set to None type"
+        fp = copy.copy(params)
+        fp.windowRam = True
+        fp.windowRamWidth = params.windowFunc.dataWidth if params.windowFunc is not None else windowDataWidth
+        self.fftParams = fp
+        self.csrAddress, self.ramAddress = csrAddress, ramAddress
+        n = max(params.numPoints, 64)
+        mag = MAGParams.fixed(dataWidth=16, binPoint=0, dataWidthLog=16, binPointLog=9, log2LookUpWidth=9)
+        cfar = CFARParams(leadLaggWindowSize=16, guardWindowSize=2, fftSize=n)
+        amap = [(ramAddress, "fft_win_ram"), (csrAddress, _abi.BLK_FFT)]
+        super().__init__(_c_params(fp, mag, cfar), amap, beatBytes, device)
+
+    def memWriteWord(self, addr: int, value: int):
+        blk, idx = self._decode(addr)
+        if blk == "fft_win_ram":
+            _abi.check(self._lib.rsp_fft_window_ram_write(self._h, idx, int(value) & 0xFFFFFFFF))
+        else:
+            _abi.check(self._lib.rsp_reg_write(self._h, blk, idx, int(value) & 0xFFFFFFFF))
 
 
 class RspChainVanilla(_Chain):

@@ -25,6 +25,7 @@ extern "C" void rsp_set_last_error_(const char *msg) { g_last_error = msg ? msg 
     if (e__ != cudaSuccess) return fail(RSP_ECUDA, std::string(#expr) + ": " + cudaGetErrorString(e__));     \
   } while (0)
 
+static int env_int_early(const char *name) { const char *v = std::getenv(name); return (v && *v && *v != '0') ? 1 : 0; }
 // Every entry point runs on the handle's device and leaves the caller's current device as it found it (a single-process program
 // with several GPUs, e.g. torch, keeps its own notion of the current device).
 struct DeviceGuard {
@@ -36,7 +37,15 @@ struct DeviceGuard {
   }
   ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
 };
+// RSP_DEBUG_ERRORS=1: report (stderr) a CUDA error left pending by an earlier call as soon as the next entry point sees it
+static void debug_stale(const char *where) {
+  static const int on = env_int_early("RSP_DEBUG_ERRORS");
+  if (!on) return;
+  const cudaError_t e = cudaPeekAtLastError();
+  if (e != cudaSuccess) std::fprintf(stderr, "[rsp] pending CUDA error at entry of %s: %s\n", where, cudaGetErrorString(e));
+}
 #define RSP_ON_DEVICE(c)                                                                                     \
+  debug_stale(__func__);                                                                                     \
   DeviceGuard dev_guard__((c)->device);                                                                      \
   if (dev_guard__.err != cudaSuccess) return fail(RSP_ECUDA, std::string("cudaSetDevice: ") + cudaGetErrorString(dev_guard__.err))
 
@@ -67,9 +76,12 @@ struct rsp_chain {
   float *d_winf = nullptr;
   GenSegment *d_segs = nullptr;
   size_t segs_cap = 0;
+  uint16_t *d_gen_phase = nullptr;     // GenPlan::phase_tab on the device (the generator fused into the chain kernel)
+  size_t gen_phase_cap = 0;
   uint32_t *d_gen_scratch = nullptr;   // NCO beats between generator and chain when the caller does not want them
   size_t gen_scratch_cap = 0;
   bool gen_dirty = true;               // PLFG registers / RAM changed since the segment list was uploaded
+  bool win_dirty = false;              // window RAM of FFTBlockWithWindowing written since the coefficient arrays were uploaded
   GenPlan gen_plan;
   uint64_t launches = 0;
   std::string variant;
@@ -214,11 +226,16 @@ static void free_pipe(rsp_chain *c) {
 
 extern "C" void rsp_chain_destroy(rsp_chain *c) {
   if (!c) return;
+  debug_stale("rsp_chain_destroy");
   DeviceGuard guard(c->device);
   free_pipe(c);
   for (int i = 0; i < N_PIPE; ++i) if (c->pipe_stream[i]) cudaStreamDestroy(c->pipe_stream[i]);
-  cudaFree(c->d_tw); cudaFree(c->d_tw2); cudaFree(c->d_tww); cudaFree(c->d_ovf); cudaFree(c->d_twf); cudaFree(c->d_twf4); cudaFree(c->d_win); cudaFree(c->d_win4); cudaFree(c->d_winf); cudaFree(c->d_log_tab); cudaFree(c->d_nco_tab); cudaFree(c->d_nco_full); cudaFree(c->d_segs);
-  cudaFree(c->d_gen_scratch); cudaFree(c->d_det_list); cudaFree(c->d_det_count);
+#define RSP_FREE(ptr) do { const cudaError_t e__ = cudaFree(ptr); if (e__ != cudaSuccess && env_int_early("RSP_DEBUG_ERRORS")) std::fprintf(stderr, "[rsp] cudaFree(" #ptr "): %s\n", cudaGetErrorString(e__)); } while (0)
+  RSP_FREE(c->d_tw); RSP_FREE(c->d_tw2); RSP_FREE(c->d_tww); RSP_FREE(c->d_ovf); RSP_FREE(c->d_twf); RSP_FREE(c->d_twf4); RSP_FREE(c->d_win); RSP_FREE(c->d_win4);
+  RSP_FREE(c->d_winf); RSP_FREE(c->d_log_tab); RSP_FREE(c->d_nco_tab); RSP_FREE(c->d_nco_full); RSP_FREE(c->d_segs);
+  RSP_FREE(c->d_gen_scratch); RSP_FREE(c->d_gen_phase); RSP_FREE(c->d_det_list); RSP_FREE(c->d_det_count);
+#undef RSP_FREE
+  debug_stale("rsp_chain_destroy (end)");
   delete c;
 }
 
@@ -272,8 +289,20 @@ extern "C" rsp_status rsp_chain_create(const rsp_chain_params *params, int devic
 
 // ---------------------------------------------------------------------------------------------------------------------
 // registers
+// FFTBlockWithWindowing has doWindowing at word 2 and the rest of AXI4FFTBlock's file one word further (FFTBlockWithWindowing.scala:134-152)
+static bool fftw_translate(const rsp_chain *c, rsp_block blk, uint32_t *idx, bool *is_dowin) {
+  *is_dowin = false;
+  if (blk != RSP_BLK_FFT || !c->p.fft.windowRam) return true;
+  if (*idx == RSP_FFTW_REG_DOWINDOWING) { *is_dowin = true; return true; }
+  if (*idx > RSP_FFTW_REG_DOWINDOWING) *idx -= 1;
+  return true;
+}
+
 extern "C" rsp_status rsp_reg_write(rsp_chain *c, rsp_block blk, uint32_t idx, uint32_t value) {
   if (!c) return fail(RSP_EINVAL, "null handle");
+  bool dowin = false;
+  fftw_translate(c, blk, &idx, &dowin);
+  if (dowin) { c->r.fft_dowin = value & 1u; return RSP_OK; }
   bool ro = false;
   const int w = reg_width(c->p, blk, idx, &ro);
   if (blk == RSP_BLK_CFAR && idx == RSP_CFAR_REG_THRESHOLDSCALER_F32) {
@@ -292,6 +321,9 @@ extern "C" rsp_status rsp_reg_write(rsp_chain *c, rsp_block blk, uint32_t idx, u
 extern "C" rsp_status rsp_reg_read(rsp_chain *c, rsp_block blk, uint32_t idx, uint32_t *value) {
   if (!c || !value) return fail(RSP_EINVAL, "null argument");
   if (blk == RSP_BLK_CFAR && idx == RSP_CFAR_REG_THRESHOLDSCALER_F32) { std::memcpy(value, &c->r.scaler_f32, 4); return RSP_OK; }
+  bool dowin = false;
+  fftw_translate(c, blk, &idx, &dowin);
+  if (dowin) { *value = c->r.fft_dowin; return RSP_OK; }
   bool ro = false;
   if (reg_width(c->p, blk, idx, &ro) < 0) return fail(RSP_EINVAL, "no such register");
   uint32_t *slot = reg_slot(c->r, blk, idx);
@@ -333,6 +365,30 @@ extern "C" rsp_status rsp_fft_window_user(rsp_chain *c, const double *coeffs, ui
   return RSP_OK;
 }
 
+extern "C" rsp_status rsp_fft_window_ram_write(rsp_chain *c, uint32_t idx, uint32_t value) {
+  if (!c) return fail(RSP_EINVAL, "null handle");
+  if (!c->p.fft.windowRam) return fail(RSP_EINVAL, "this chain's FFT block has no window RAM (windowRam = 0)");
+  // w_addr keeps log2Ceil(numPoints) address bits (FFTBlockWithWindowing.scala:54): higher word indices alias
+  idx &= (uint32_t)c->p.fft.numPoints - 1u;
+  const int w = c->p.fft.windowWidth;
+  if (c->t.win_ram.size() != (size_t)c->p.fft.numPoints) c->t.win_ram.assign((size_t)c->p.fft.numPoints, 0);
+  c->t.win_ram[idx] = (int32_t)wrap_host((long long)value, w);   // wdata.asTypeOf(protoWin) (:51)
+  c->win_dirty = true;
+  return RSP_OK;
+}
+
+// coefficient arrays on the device follow the window RAM lazily: uploaded by the first run call after a write
+static rsp_status sync_window(rsp_chain *c) {
+  if (!c->win_dirty) return RSP_OK;
+  CUDA_TRY(cudaDeviceSynchronize());   // a kernel in flight may still read the old coefficients
+  build_window(c->p, c->t);
+  CUDA_TRY(cudaMemcpy(c->d_win, c->t.win.data(), c->t.win.size() * sizeof(int32_t), cudaMemcpyHostToDevice));
+  CUDA_TRY(cudaMemcpy(c->d_win4, c->t.win4.data(), c->t.win4.size() * sizeof(int32_t), cudaMemcpyHostToDevice));
+  CUDA_TRY(cudaMemcpy(c->d_winf, c->t.winf.data(), c->t.winf.size() * sizeof(float), cudaMemcpyHostToDevice));
+  c->win_dirty = false;
+  return RSP_OK;
+}
+
 // ---------------------------------------------------------------------------------------------------------------------
 // planning glue
 static void bind_fixed(rsp_chain *c, FxArgs &a) { a.tw = c->d_tw; a.tw2 = c->d_tw2; a.log_tab = c->d_log_tab; a.win = c->d_win; a.win4 = c->d_win4; }
@@ -342,10 +398,12 @@ static void bind_dets(const rsp_dets *d, Detection **list, uint32_t **count, uin
   else { *list = nullptr; *count = nullptr; *cap = 0; }
 }
 
+struct FusedGen { const uint16_t *phase; const uint32_t *full; uint32_t period, pp, mask; };
 static rsp_status run_stages(rsp_chain *c, int first, int last, const void *d_in, uint32_t n_rows, void *d_out, uint32_t *d_peak_mask,
-                             const rsp_dets *dets, cudaStream_t st, uint32_t row_base = 0) {
+                             const rsp_dets *dets, cudaStream_t st, uint32_t row_base = 0, const FusedGen *fg = nullptr) {
   std::string err;
   Plan pl;
+  { const rsp_status ws = sync_window(c); if (ws != RSP_OK) return ws; }
   if (c->p.arith == RSP_ARITH_FIXED) {
     FxArgs a;
     const rsp_status s = plan_fixed(c->p, c->r, c->t, first, last, a, pl, err);
@@ -358,6 +416,10 @@ static rsp_status run_stages(rsp_chain *c, int first, int last, const void *d_in
     a.in = static_cast<const uint32_t *>(d_in); a.out = static_cast<uint32_t *>(d_out); a.n_rows = n_rows; a.row_base = row_base;
     bind_dets(dets, &a.det_list, &a.det_count, &a.det_cap);
     if (!a.out && !(last == STAGE_CFAR && a.det_list)) return fail(RSP_EINVAL, "no output requested");
+    if (fg != nullptr) {   // the generator fused into the first pass: only the fast CA kernel reads these
+      if (!(fast_chain_supported(pl, a) && a.core == CORE_MEM)) return fail(RSP_EUNSUPPORTED, "no fused-generator kernel for this configuration");
+      a.gen_phase = fg->phase; a.gen_full = fg->full; a.gen_period = fg->period; a.gen_pp = fg->pp; a.gen_mask = fg->mask; a.gen_k0 = 0;
+    }
     return launch_fixed(c, pl, a, st);
   }
   F32Args a;
@@ -401,6 +463,7 @@ extern "C" rsp_status rsp_fft_run(rsp_chain *c, const void *d_in, uint32_t n_chi
     const rsp_status s = plan_wide(c->p, c->r, c->t, a, err);
     if (s != RSP_OK) return fail(s, err);
     if (n_chirps == 0) return RSP_OK;
+    { const rsp_status ws = sync_window(c); if (ws != RSP_OK) return ws; }
     a.in = static_cast<const unsigned long long *>(d_in); a.out = static_cast<unsigned long long *>(d_out); a.n_rows = n_chirps;
     a.tw = reinterpret_cast<const int2 *>(c->d_tww); a.win = c->d_win;
     a.ovf_flags = c->d_ovf;
@@ -463,6 +526,14 @@ static rsp_status prepare_generator(rsp_chain *c, uint64_t n_samples, GenArgs &g
       CUDA_TRY(cudaMalloc((void **)&c->d_segs, n * sizeof(GenSegment)));
       c->segs_cap = n;
     }
+    const size_t np = c->gen_plan.phase_tab.size();
+    if (np > c->gen_phase_cap) {
+      CUDA_TRY(cudaDeviceSynchronize());
+      cudaFree(c->d_gen_phase); c->d_gen_phase = nullptr; c->gen_phase_cap = 0;
+      CUDA_TRY(cudaMalloc((void **)&c->d_gen_phase, np * sizeof(uint16_t)));
+      c->gen_phase_cap = np;
+    }
+    if (np) CUDA_TRY(cudaMemcpyAsync(c->d_gen_phase, c->gen_plan.phase_tab.data(), np * sizeof(uint16_t), cudaMemcpyHostToDevice, st));
     CUDA_TRY(cudaMemcpyAsync(c->d_segs, c->gen_plan.segs.data(), n * sizeof(GenSegment), cudaMemcpyHostToDevice, st));
     CUDA_TRY(cudaStreamSynchronize(st));   // the host vector may be rebuilt by the next register write
     c->gen_dirty = false;
@@ -478,6 +549,13 @@ static rsp_status prepare_generator(rsp_chain *c, uint64_t n_samples, GenArgs &g
   g.out_width = c->p.plfg.outputWidthInt + c->p.plfg.outputWidthFrac;
   g.phase_acc_enable = c->p.nco.phaseAccEnable ? 1 : 0;
   g.poff = 0;   // poffType Fixed: no phase-offset port (NCOLazyModuleBlock.scala:246-271)
+  g.mult_on = 0; g.mult_f = 0; g.mult_trim = c->p.nco.roundingMode;
+  if (c->p.nco.useMultiplier) {
+    const int w = c->p.nco.tableWidth;
+    // factor = Mux(enableMultiplying, multiplyingFactor, 1.U << (beatBytes * 4 - 2)) read as FixedPoint(w, w - 2) (NCOLazyModuleBlock.scala:354)
+    g.mult_f = (int)wrap_host((c->r.nco[0] & 1u) ? (long long)c->r.nco[1] : (1LL << 14), w);
+    g.mult_on = (g.mult_f != (1 << (w - 2))) ? 1 : 0;   // times exactly 1.0 is the identity under every trim type
+  }
   return RSP_OK;
 }
 
@@ -506,6 +584,29 @@ extern "C" rsp_status rsp_run_from_generator(rsp_chain *c, uint32_t n_chirps, ui
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const int S = c->p.fft.runTime ? (int)c->r.fft[RSP_FFT_REG_FFTSIZE] : log2_ceil((uint32_t)c->p.fft.numPoints);
   const uint64_t n_samples = (uint64_t)rows << S;
+  // One launch when the caller does not ask for the NCO beats and the configuration runs on the fast CA kernel: the first pass of the
+  // chain kernel generates its own beats from the period's phase table (no beats in HBM: 0 B in + 4 B out per sample).
+  // RSP_GEN_FUSED=0 keeps the two-launch path (generator -> scratch beats -> chain), which is also what every other case takes.
+  static const int fused_on = env_int("RSP_GEN_FUSED", 1, 0, 1);
+  if (!d_nco_out && fused_on && c->d_nco_full != nullptr && c->p.hasGenerator && (c->r.plfg[RSP_PLFG_REG_ENABLE] & 1u)) {
+    GenArgs g;
+    s = prepare_generator(c, n_samples, g, st);
+    if (s != RSP_OK) return s;
+    if (!c->gen_plan.phase_tab.empty() && !g.mult_on) {   // (the beat table holds unmultiplied beats)
+      std::string err; Plan pl; FxArgs a;
+      if (plan_fixed(c->p, c->r, c->t, STAGE_FFT, STAGE_CFAR, a, pl, err) == RSP_OK) {
+        a.out = static_cast<uint32_t *>(d_out);
+        Detection *dl; uint32_t *dc; uint32_t cap;
+        bind_dets(dets, &dl, &dc, &cap);
+        a.det_list = dl;
+        if (fast_chain_supported(pl, a) && a.core == CORE_MEM) {
+          const uint32_t pw = (uint32_t)c->p.nco.phaseWidth;
+          const FusedGen fg = {c->d_gen_phase, c->d_nco_full, (uint32_t)c->gen_plan.period_len, c->gen_plan.period_phase, (1u << pw) - 1u};
+          return run_stages(c, STAGE_FFT, STAGE_CFAR, c->d_nco_full /* not read */, rows, d_out, d_peak_mask, dets, st, 0, &fg);
+        }
+      }
+    }
+  }
   uint32_t *beats = d_nco_out;
   if (!beats) {
     if (n_samples > c->gen_scratch_cap) {

@@ -69,6 +69,11 @@ struct FxArgs {
   // in when a butterfly of stage i of this transform has a grown output at or above 2^(dataWidth - 1); null = not elaborated
   uint32_t *ovf_flags;
   int ovf_shift;
+  // PLFG -> NCO fused into the first pass of the fast chain kernel (rsp_fast.cu, FastArgs::gen_*); gen_full null = beats come from `in`
+  const uint16_t *gen_phase;
+  const uint32_t *gen_full;
+  uint32_t gen_period, gen_pp, gen_mask;
+  unsigned long long gen_k0;
 };
 
 // ------------------------------------------------------------------------------------------------ helpers

@@ -184,22 +184,17 @@ RSP_HD uint32_t cfar_thread_f32(const F32Args &a, uint32_t row, int tl, const fl
   const bool sums = (a.core == CORE_MEM) || (a.core == CORE_LIS && a.cfar_algorithm == 0);
   const int wl = a.core == CORE_ASR ? a.sub_cells : W;   // cells in the running sums
   float sl = 0.f, sr = 0.f;
-  bool have_l = false, have_r = false;
   uint32_t bits = 0;
   for (int j = 0; j < PTS; ++j) {
     const int n = tl * PTS + j;
     const bool lagg_full = (n + G + W <= N - 1), lead_full = (n - G - W >= 0);
     float Lv = 0.f, Rv = 0.f;
     if (sums || a.core == CORE_ASR) {
-      // lagging running sum over [n+G+W-wl+1, n+G+W], leading over [n-G-wl, n-G-1]
-      if (lagg_full) {
-        if (!have_l) { sl = cfar_sum_f32(bufM, n + G + W - wl + 1, wl); have_l = true; }
-        else sl += bufM[pad(n + G + W)] - bufM[pad(n + G + W - wl)];
-      }
-      if (lead_full) {
-        if (!have_r) { sr = cfar_sum_f32(bufM, n - G - wl, wl); have_r = true; }
-        else sr += bufM[pad(n - G - 1)] - bufM[pad(n - G - 1 - wl)];
-      }
+      // lagging sum over [n+G+W-wl+1, n+G+W], leading over [n-G-wl, n-G-1], each summed afresh: a sliding float sum (add the
+      // entering cell, subtract the leaving one) keeps the rounding error of the largest cell that ever passed through the window,
+      // which buries the noise floor behind a strong target (power cells span 7 decades: 1.7e-2 relative error measured on B200)
+      if (lagg_full) sl = cfar_sum_f32(bufM, n + G + W - wl + 1, wl);
+      if (lead_full) sr = cfar_sum_f32(bufM, n - G - wl, wl);
       Lv = lagg_full ? sl * a.inv_div : 0.f;
       Rv = lead_full ? sr * a.inv_div : 0.f;
     } else if (a.core == CORE_OS) {   // cfarOS (CFARUtils.scala:165-171), see cfar_bin

@@ -36,7 +36,18 @@ struct GenArgs {
                             // nco_lookup itself (phaseWidth <= 12): one load instead of two look-ups and the quadrant logic
   int table_size, addr_bits, table_width, phase_width, out_width, phase_acc_enable;
   uint32_t poff;
+  // output multiplier (NCOLazyModuleBlock.scala:354-364): mult_on = the factor is not exactly 1.0, mult_f = factor as FixedPoint(w, w - 2) raw
+  int mult_on, mult_f, mult_trim;
 };
+
+// sin / cos times the multiplier's factor: context_* with binaryPointGrowth 0 under roundingMode, reinterpreted as protoOut
+RSP_HD uint32_t nco_multiply(const GenArgs &g, uint32_t beat) {
+  const int w = g.table_width;
+  const int co = wrapw((int)(beat >> 16), w), s = wrapw((int)(beat & 0xFFFFu), w);
+  const int mc = wrapw((int)trim_rt<long long>((long long)co * g.mult_f, w - 2, g.mult_trim), w);
+  const int ms = wrapw((int)trim_rt<long long>((long long)s * g.mult_f, w - 2, g.mult_trim), w);
+  return (((uint32_t)mc & 0xFFFFu) << 16) | ((uint32_t)ms & 0xFFFFu);
+}
 
 // Cat(cos16, sin16) of one phase word (NCOTable.scala:193-235; NCOLazyModuleBlock.scala:452)
 RSP_HD uint32_t nco_lookup(const GenArgs &g, uint32_t ph) {
@@ -82,7 +93,8 @@ RSP_HD uint32_t gen_sample(const GenArgs &g, unsigned long long k, int *plfg_val
   } else {
     phase = (uint32_t)v & pmask;
   }
-  return nco_lookup(g, (phase + g.poff) & pmask);
+  const uint32_t beat = nco_lookup(g, (phase + g.poff) & pmask);
+  return g.mult_on ? nco_multiply(g, beat) : beat;
 }
 
 // Running form for a thread that produces consecutive samples: the first one in closed form (gen_start), the following ones by
@@ -125,7 +137,8 @@ RSP_HD uint32_t gen_beat(const GenArgs &g, const GenState &st, int *plfg_value) 
   const uint32_t pmask = g.phase_width >= 32 ? 0xFFFFFFFFu : ((1u << g.phase_width) - 1u);
   const uint32_t phase = (g.phase_acc_enable ? st.acc : (uint32_t)v) & pmask;
   const uint32_t ph = (phase + g.poff) & pmask;
-  return g.nco_full != nullptr ? ldg(&g.nco_full[ph]) : nco_lookup(g, ph);
+  const uint32_t beat = g.nco_full != nullptr ? ldg(&g.nco_full[ph]) : nco_lookup(g, ph);
+  return g.mult_on ? nco_multiply(g, beat) : beat;
 }
 
 }  // namespace rsp

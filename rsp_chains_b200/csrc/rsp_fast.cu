@@ -44,6 +44,14 @@ struct FastArgs {
   uint32_t det_cap;
   int skew_ns;           // A/B knob (RSP_FAST_SKEW_NS): CTAs of the second half of the grid start this much later, so that the CTAs
                          // sharing an SM are in different phases of their rows from the start
+  // PLFG -> NCO fused into the first pass (rsp_run_from_generator as ONE launch, no beats in HBM): sample k of the generator's stream has
+  // the NCO phase (gen_phase[k mod gen_period] + (k div gen_period) * gen_pp) mod 2^phaseWidth (rsp_host.hpp, GenPlan::phase_tab) and
+  // its beat is gen_full[phase] (Tables::nco_full, built with nco_lookup); row r of the call starts at sample gen_k0 + r * N
+  const uint16_t *gen_phase;
+  const uint32_t *gen_full;   // null: beats come from `in`
+  uint32_t gen_period, gen_pp, gen_mask;
+  unsigned long long gen_k0;
+  int l2_prefetch;       // 1: one thread asks the L2 for the CTA's next row (cp.async.bulk.prefetch.L2) while this row is transformed
   int stage;             // 1: the next row's beats are fetched with cp.async into a staging area behind the CTA's rows while this
                          // row's CFAR phase runs (chain_fixed_fast_kernel); needs 16-byte aligned rows and N more words per chirp
 };
@@ -331,12 +339,32 @@ __device__ __forceinline__ void window_beats(const FastArgs &a, int tl, int g, u
     }
   }
 }
+// position of a sample in the generator's periodic schedule: k = per * gen_period + q
+struct GenRow { uint32_t q, per; };
+__device__ __forceinline__ void gen_advance(uint32_t &q, uint32_t &per, uint32_t dq, uint32_t dper, uint32_t P) {
+  q += dq; per += dper;
+  if (q >= P) { q -= P; ++per; }
+}
 template <int S, int LP>
-__device__ __forceinline__ void load_beats(const FastArgs &a, const uint32_t *grow, int tl, int g, uint32_t (&pre)[16]) {
+__device__ __forceinline__ void load_beats(const FastArgs &a, const uint32_t *grow, const GenRow &gr, int tl, int g, uint32_t (&pre)[16]) {
   constexpr int TPC = FGeo<S, LP>::TPC, G = (1 << LP) / 16;
-  const uint32_t *gin = grow + tl + g * TPC;
+  if (a.gen_full != nullptr) {   // the beats of this group from the PLFG -> NCO schedule: points p = tl + (rr * G + g) * TPC of the row
+    const uint32_t P = a.gen_period;
+    const uint32_t dq1 = (uint32_t)TPC % P, dper1 = (uint32_t)TPC / P, dqG = (uint32_t)(G * TPC) % P, dperG = (uint32_t)(G * TPC) / P;
+    uint32_t q = gr.q, per = gr.per;
 #pragma unroll
-  for (int rr = 0; rr < 16; ++rr) pre[rr] = __ldg(&gin[rr * G * TPC]);
+    for (int i = 0; i < g; ++i) gen_advance(q, per, dq1, dper1, P);
+#pragma unroll
+    for (int rr = 0; rr < 16; ++rr) {
+      const uint32_t ph = ((uint32_t)__ldg(&a.gen_phase[q]) + per * a.gen_pp) & a.gen_mask;
+      pre[rr] = __ldg(&a.gen_full[ph]);
+      gen_advance(q, per, dqG, dperG, P);
+    }
+  } else {
+    const uint32_t *gin = grow + tl + g * TPC;
+#pragma unroll
+    for (int rr = 0; rr < 16; ++rr) pre[rr] = __ldg(&gin[rr * G * TPC]);
+  }
   window_beats<S, LP>(a, tl, g, pre);
 }
 
@@ -372,8 +400,8 @@ __device__ __forceinline__ void fast_passes_from(const FastArgs &a, int c, int t
 // pre: the thread's 16 beats (LP = 4; loaded or staged by the caller).  grow: the row in global memory (LP = 5: each of the two
 // groups of the first pass loads its own 16 beats, so that no more than one group's beats are live at a time).
 template <int S, int LP, bool TWSM = false>
-__device__ __forceinline__ void fast_passes(const FastArgs &a, int c, int tl, uint32_t (&pre)[16], const uint32_t *grow, uint32_t *xb, uint32_t *xm,
-                                            int *loud, const int2 *tws = nullptr) {
+__device__ __forceinline__ void fast_passes(const FastArgs &a, int c, int tl, uint32_t (&pre)[16], const uint32_t *grow, const GenRow &gr, uint32_t *xb,
+                                            uint32_t *xm, int *loud, const int2 *tws = nullptr) {
   static_assert(fx_pass_size(S, 0) == 4, "the first pass works on groups of 16 beats");
   constexpr int G0 = (1 << LP) / 16;
   if constexpr (G0 == 1) {
@@ -385,7 +413,7 @@ __device__ __forceinline__ void fast_passes(const FastArgs &a, int c, int tl, ui
     bool all_quiet = true;
 #pragma unroll
     for (int g = 0; g < G0; ++g) {
-      load_beats<S, LP>(a, grow, tl, g, pre);
+      load_beats<S, LP>(a, grow, gr, tl, g, pre);
       const bool warp_quiet = __all_sync(0xffffffffu, quiet_beats(pre));
       all_quiet = all_quiet && warp_quiet;
       if (warp_quiet) fast_group<S, LP, 0, false, TWSM>(a, tl, g, pre, xb, mags, tws); else fast_group<S, LP, 0, true, TWSM>(a, tl, g, pre, xb, mags, tws);
@@ -533,6 +561,16 @@ __global__ void __launch_bounds__(FGeo<S, LP>::THREADS, fast_min_blocks<S, LP>()
     cp_async_commit();
   };
   if (stage) { prefetch(blockIdx.x * CPC); cp_async_wait_all(); __syncthreads(); }
+  // generator fused in: schedule position of point tl of the CTA's current row, advanced by stride * N samples per iteration
+  GenRow gr = {0u, 0u};
+  uint32_t g_dq = 0, g_dper = 0;
+  const bool gen = a.gen_full != nullptr;
+  if (gen) {
+    const unsigned long long k = a.gen_k0 + ((unsigned long long)(blockIdx.x * CPC + c) << S) + (unsigned)tl;
+    gr.per = (uint32_t)(k / a.gen_period); gr.q = (uint32_t)(k - (unsigned long long)gr.per * a.gen_period);
+    const uint32_t dk = stride << S;
+    g_dper = dk / a.gen_period; g_dq = dk - g_dper * a.gen_period;
+  }
   if (a.skew_ns > 0 && 2 * blockIdx.x >= gridDim.x) {
     for (int left = a.skew_ns; left > 0; left -= 1000) __nanosleep(1000);
   }
@@ -543,16 +581,26 @@ __global__ void __launch_bounds__(FGeo<S, LP>::THREADS, fast_min_blocks<S, LP>()
     const uint32_t row = active ? row0 + c : a.n_rows - 1;
     const uint32_t *grow = a.in + (size_t)row * N;
     uint32_t pre[16];
+    GenRow grr = gr;
+    if (gen && !active) {   // a chirp slot past the last row recomputes the last row: its own schedule position
+      const unsigned long long k = a.gen_k0 + ((unsigned long long)row << S) + (unsigned)tl;
+      grr.per = (uint32_t)(k / a.gen_period); grr.q = (uint32_t)(k - (unsigned long long)grr.per * a.gen_period);
+    }
     if (LP == 4) {
       if (stage) {
 #pragma unroll
         for (int rr = 0; rr < 16; ++rr) pre[rr] = stg[tl + rr * TPC];
         window_beats<S, LP>(a, tl, 0, pre);
-      } else load_beats<S, LP>(a, grow, tl, 0, pre);
+      } else load_beats<S, LP>(a, grow, grr, tl, 0, pre);
     }
-    fast_passes<S, LP, TWSM>(a, c, tl, pre, grow, xb, xm, loud, tws);
+    fast_passes<S, LP, TWSM>(a, c, tl, pre, grow, grr, xb, xm, loud, tws);
+    if (gen) gen_advance(gr.q, gr.per, g_dq, g_dper, a.gen_period);
     // every thread is past the first barrier of the passes: the staging area has been read and can take the next rows
     if (stage && row0 + stride < a.n_rows) prefetch(row0 + stride);
+    if (a.l2_prefetch && tl == 0 && row0 + stride + c < a.n_rows) {   // the next row's 4 N bytes into L2: its first-pass loads then miss L1 only
+      const uint32_t *nxt = a.in + (size_t)(row0 + stride + c) * N;
+      asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" :: "l"(nxt), "r"(4 * N) : "memory");
+    }
     // prefix sums of the thread's PTS consecutive magnitudes, 16 at a time (32 points per thread: the second read of the magnitudes
     // is cheaper than keeping them in registers across the scan)
     const uint32_t *xq = xm + mhx<S>(PTS * tl) / 2;   // the thread's PTS consecutive bins (inside one 64-bin block of the padded array)
@@ -819,8 +867,9 @@ __global__ void __launch_bounds__(FGeo<S>::THREADS, 1024 / FGeo<S>::THREADS) cha
     const uint32_t row = active ? row0 + c : a.n_rows - 1;
     const uint32_t *grow = a.in + (size_t)row * N;
     uint32_t pre[PTS];
-    load_beats<S, 4>(a, grow, tl, 0, pre);
-    fast_passes<S, 4>(a, c, tl, pre, grow, xb, xm, loud);
+    const GenRow no_gen = {0u, 0u};   // (the generator is fused into the CA kernel only; a.gen_full is null here)
+    load_beats<S, 4>(a, grow, no_gen, tl, 0, pre);
+    fast_passes<S, 4>(a, c, tl, pre, grow, no_gen, xb, xm, loud);
     uint32_t wide = 0;
     {   // the thread's 16 cells as 32-bit words in the padded array (the exchange buffer is dead)
       const uint32_t *xq = xm + mhx<S>(16 * tl) / 2;   // the thread's 16 consecutive bins
@@ -1006,8 +1055,13 @@ rsp_status launch_fast_chain(const Plan &pl, const LaunchCtx &ctx, const FxArgs 
   fa.thr_mask = a.thr_w >= 32 ? 0xFFFFFFFFu : ((1u << a.thr_w) - 1u);
   fa.out_mul = (int)(1u << (a.binw + 1)); fa.thr_sext = 32 - a.thr_w;
   fa.det_list = a.det_list; fa.det_count = a.det_count; fa.det_cap = a.det_cap;
+  // measured on B200 (profiles/r02_d_l2prefetch.txt): N = 16384 +5.3 %, N = 4096 +1.9 %, N = 1024 +1.3 %; RSP_FAST_L2_PREFETCH=0 turns it off
+  { static int l2p = -1; if (l2p < 0) { const char *e = std::getenv("RSP_FAST_L2_PREFETCH"); l2p = e ? std::atoi(e) : 1; }
+    fa.l2_prefetch = (l2p != 0 && a.gen_full == nullptr && (reinterpret_cast<uintptr_t>(a.in) & 15u) == 0) ? 1 : 0; }
+  fa.gen_phase = a.gen_phase; fa.gen_full = a.core == CORE_MEM ? a.gen_full : nullptr; fa.gen_period = a.gen_period; fa.gen_pp = a.gen_pp;
+  fa.gen_mask = a.gen_mask; fa.gen_k0 = a.gen_k0;
   { static int skew = -1; if (skew < 0) { const char *e = std::getenv("RSP_FAST_SKEW_NS"); skew = e ? std::atoi(e) : 0; } fa.skew_ns = skew; }
-  fa.stage = (pl.S < RSP_FAST_TWSMEM_S && fast_stage_enabled(pl.S) && (reinterpret_cast<uintptr_t>(a.in) & 15u) == 0) ? 1 : 0;   // rows are N * 4 bytes: the base decides
+  fa.stage = (pl.S < RSP_FAST_TWSMEM_S && fast_stage_enabled(pl.S) && a.gen_full == nullptr && (reinterpret_cast<uintptr_t>(a.in) & 15u) == 0) ? 1 : 0;   // rows are N * 4 bytes: the base decides
   const int cmode = a.cfar_mode == 0 ? 0 : (a.cfar_mode == 1 ? 1 : 2);   // MuxLookup default: smallestOf (CFARCoreWithMem.scala:138-141)
   const bool linear = a.log_or_linear != 0;
   const GosArgs ga = {cmode, linear ? 1 : 0, a.idx_lagg - 1, a.idx_lead - 1};

@@ -26,6 +26,8 @@ inline long long wrap_host(long long v, int w) { return wrapw64(v, w); }
 inline long long from_double(double x, int bp) { return (long long)std::floor(std::ldexp(x, bp) + 0.5); } // FixedPoint.fromDouble
 
 struct Regs {
+  uint32_t nco[2] = {0, 0};   // enableMultiplying, multiplyingFactor (useMultiplier; NCOLazyModuleBlock.scala:242-243)
+  uint32_t fft_dowin = 0;   // doWindowing of FFTBlockWithWindowing (FFTBlockWithWindowing.scala:109,141)
   uint32_t fft[5];
   uint32_t mag[1];
   uint32_t cfar[12];
@@ -49,6 +51,7 @@ struct Tables {
   std::vector<int32_t> win4;  // win << (16 - (windowWidth - 2)) for the fast fixed kernels
   std::vector<float> winf;    // the same coefficients as floats (fp32 flavour: protoWin = DspReal)
   std::vector<double> win_user;   // WindowFunctionTypes.User coefficients (rsp_fft_window_user)
+  std::vector<int32_t> win_ram;   // FFTBlockWithWindowing: the coefficient RAM, raw protoWin values (rsp_fft_window_ram_write)
 };
 
 // ---- the reference's elaboration-time checks -------------------------------------------------------------------
@@ -66,6 +69,9 @@ inline rsp_status validate_params(const rsp_chain_params &p, std::string &err) {
   RSP_REQ(!f.expandLogic || (f.sdfRadix == 4 && f.decimType == 0 && p.arith == RSP_ARITH_FIXED), RSP_EUNSUPPORTED,
           "expandLogic (grow) stages are built for the fixed-point radix 2^2 DIF chain only");
   RSP_REQ(f.windowFunc >= RSP_WINDOW_NONE && f.windowFunc <= RSP_WINDOW_USER, RSP_EINVAL, "unknown windowFunc");
+  RSP_REQ(!f.windowRam || f.windowFunc == RSP_WINDOW_NONE, RSP_EINVAL, "Parameter for window function inside SDFFFT module must be set to None type");   // FFTBlockWithWindowing.scala:19
+  RSP_REQ(!f.windowRam || p.arith == RSP_ARITH_FIXED, RSP_EUNSUPPORTED, "FFTBlockWithWindowing is built for the fixed-point flavour");
+  RSP_REQ(!f.windowRam || (f.windowWidth >= 3 && f.windowWidth <= 16), RSP_EUNSUPPORTED, "window dataWidth must be in 3..16");
   RSP_REQ(f.windowFunc == RSP_WINDOW_NONE || (f.windowWidth >= 3 && f.windowWidth <= 16), RSP_EUNSUPPORTED, "window dataWidth must be in 3..16");
   if (p.arith == RSP_ARITH_FIXED) {
     RSP_REQ(f.dataWidth >= 2 && f.dataWidth <= 32, RSP_EUNSUPPORTED, "dataWidth must be in 2..32");
@@ -107,8 +113,9 @@ inline rsp_status validate_params(const rsp_chain_params &p, std::string &err) {
     RSP_REQ(n.tableWidth >= 3 && n.tableWidth <= 16, RSP_EINVAL, "tableWidth must be in 3..16");
     RSP_REQ(is_pow2(n.tableSize) && n.tableSize <= 65536, RSP_EINVAL, "tableSize must be a power of 2");
     RSP_REQ(n.phaseWidth >= log2_ceil((uint32_t)n.tableSize) + 2 && n.phaseWidth <= 32, RSP_EINVAL, "phaseWidth must cover quadrant + table address");
-    RSP_REQ(!n.rasterizedMode && !n.nInterpolationTerms && !n.ditherEnable && !n.useMultiplier && !n.useQAM, RSP_EUNSUPPORTED,
-            "NCO rasterized mode, Taylor terms, dither, multiplier and QAM are not built");
+    RSP_REQ(!n.rasterizedMode && !n.nInterpolationTerms && !n.ditherEnable && !n.useQAM, RSP_EUNSUPPORTED,
+            "NCO rasterized mode, Taylor terms, dither and QAM are not built");
+    RSP_REQ(n.roundingMode >= 0 && n.roundingMode <= RSP_TRIM_NO_TRIM, RSP_EINVAL, "unknown NCO roundingMode");
     RSP_REQ(p.arith == RSP_ARITH_FIXED, RSP_EUNSUPPORTED, "the PLFG/NCO generator feeds the fixed-point chain only");
   }
 #undef RSP_REQ
@@ -120,6 +127,7 @@ inline int plfg_reg_count(const rsp_plfg_params &g) { return 6 + g.maxChirpOrdin
 
 inline void regs_reset(const rsp_chain_params &p, Regs &r) {
   const int numStages = log2_ceil((uint32_t)p.fft.numPoints);
+  r.fft_dowin = 0; r.nco[0] = r.nco[1] = 0;
   std::memset(r.fft, 0, sizeof(r.fft)); std::memset(r.mag, 0, sizeof(r.mag)); std::memset(r.cfar, 0, sizeof(r.cfar));
   r.fft[RSP_FFT_REG_FFTSIZE] = (uint32_t)numStages;           // FFTBlock.scala:62
   r.fft[RSP_FFT_REG_FFTDIR] = 1;                               // :63
@@ -187,7 +195,11 @@ inline int reg_width(const rsp_chain_params &p, rsp_block blk, uint32_t idx, boo
     if (idx >= d && idx < e) return log2_ceil((uint32_t)g.maxChirpOrdinalNum);
     return -1;
   }
-  case RSP_BLK_NCO: return -1;  // chain configuration: pinc Streaming, poff Fixed, no multiplier => no regmap (NCOLazyModuleBlock.scala:246-271)
+  case RSP_BLK_NCO:   // chain configuration: pinc Streaming, poff Fixed: registers exist with the multiplier only (NCOLazyModuleBlock.scala:246-271)
+    if (!p.hasGenerator || !p.nco.useMultiplier) return -1;
+    if (idx == RSP_NCO_REG_ENABLEMULTIPLYING) return 1;
+    if (idx == RSP_NCO_REG_MULTIPLYINGFACTOR) return p.nco.tableWidth;
+    return -1;
   default: return -1;
   }
 }
@@ -198,6 +210,7 @@ inline uint32_t *reg_slot(Regs &r, rsp_block blk, uint32_t idx) {
   case RSP_BLK_MAG: return &r.mag[idx];
   case RSP_BLK_CFAR: return &r.cfar[idx];
   case RSP_BLK_PLFG: return &r.plfg[idx];
+  case RSP_BLK_NCO: return &r.nco[idx];
   default: return nullptr;
   }
 }
@@ -269,6 +282,16 @@ inline void build_tables(const rsp_chain_params &p, Tables &t) {
 inline void build_window(const rsp_chain_params &p, Tables &t) {
   const rsp_fft_params &f = p.fft;
   t.win.clear(); t.winf.clear(); t.win4.clear();
+  if (f.windowRam) {   // FFTBlockWithWindowing: the ROM is a RAM the host writes; SyncReadMem content before that: zeros
+    const int n = f.numPoints, wbp = f.windowWidth - 2;
+    if (t.win_ram.size() != (size_t)n) t.win_ram.assign((size_t)n, 0);
+    for (int k = 0; k < n; ++k) {
+      t.win.push_back(t.win_ram[(size_t)k]);
+      t.win4.push_back((int32_t)(t.win.back() * (1 << (16 - wbp))));
+      t.winf.push_back((float)std::ldexp((double)t.win.back(), -wbp));
+    }
+    return;
+  }
   if (f.windowFunc == RSP_WINDOW_NONE) return;
   const int n = f.numPoints, wbp = f.windowWidth - 2;
   const double PI = 3.14159265358979323846;
@@ -375,6 +398,8 @@ inline rsp_status plan_fixed(const rsp_chain_params &p, const Regs &r, const Tab
   for (int L = 0; L < 16; ++L) a.tw_off[L] = t.tw_off[L];
   // windowing happens on the forward transform only (SDFFFT.scala:229-245: `when (fftDir)`); win itself is bound by the caller
   a.win_on = (first_stage == STAGE_FFT && f.windowFunc != RSP_WINDOW_NONE && a.fft_dir == 1) ? 1 : 0;
+  // FFTBlockWithWindowing multiplies in front of the core whenever doWindowing is set, in both directions (FFTBlockWithWindowing.scala:159-166)
+  if (f.windowRam) a.win_on = (first_stage == STAGE_FFT && (r.fft_dowin & 1u)) ? 1 : 0;
   a.win_shift = f.windowWidth - 2;
   a.sel = (int)(r.mag[RSP_MAG_REG_SEL] & 3u);
   a.mag_w = p.mag.dataWidth; a.mag_bp = p.mag.binPoint; a.log_w = p.mag.dataWidthLog; a.log_bp = p.mag.binPointLog;
@@ -458,6 +483,7 @@ inline rsp_status plan_wide(const rsp_chain_params &p, const Regs &r, const Tabl
   a.out_words = 2 * a.wo > 64 ? 2 : 1;
   for (int L = 0; L < 16; ++L) a.tw_off[L] = t.tw_off[L];
   a.win_on = (f.windowFunc != RSP_WINDOW_NONE && a.fft_dir == 1) ? 1 : 0;
+  if (f.windowRam) a.win_on = (r.fft_dowin & 1u) ? 1 : 0;
   a.win_shift = f.windowWidth - 2;
   a.ovf_shift = Smax - S;
   return RSP_OK;
@@ -475,6 +501,9 @@ struct GenPlan {
   uint64_t frame_len = 0;      // samples of one frame without the pause
   uint32_t period_phase = 0;   // accumulator advance over one period (mod 2^phaseWidth)
   uint64_t total = 0;          // samples the PLFG produces before it stops (~0 = forever)
+  // the NCO phase word of every sample of period 0 (phaseWidth <= 16, period up to 2^20 samples; empty otherwise): sample k of period j
+  // has phase (phase_tab[k] + j * period_phase) mod 2^phaseWidth, which lets the fused chain kernel generate its own beats at any stride
+  std::vector<uint16_t> phase_tab;
 };
 
 inline rsp_status plan_generator(const rsp_chain_params &p, const Regs &r, GenPlan &gp, std::string &err) {
@@ -490,7 +519,14 @@ inline rsp_status plan_generator(const rsp_chain_params &p, const Regs &r, GenPl
   const uint32_t ndiff = r.plfg[RSP_PLFG_REG_DIFFERENTCHIRPSNUM] < 1 ? 1 : r.plfg[RSP_PLFG_REG_DIFFERENTCHIRPSNUM];
   const uint32_t seg0 = RSP_PLFG_REG_SEGMENTNUMS0, rep0 = seg0 + g.maxChirpOrdinalNum, ord0 = rep0 + g.maxNumOfDifferentChirps;
   if (ndiff > (uint32_t)g.maxNumOfDifferentChirps) { err = "differentChirpsNum exceeds maxNumOfDifferentChirps"; return RSP_EINVAL; }
-  gp.segs.clear();
+  gp.segs.clear(); gp.phase_tab.clear();
+  const bool acc_on = p.nco.phaseAccEnable != 0;
+  bool tab_ok = pw <= 16;
+  auto tab_push = [&](uint32_t acc, long long v) {
+    if (!tab_ok) return;
+    if (gp.phase_tab.size() >= (1u << 20)) { tab_ok = false; gp.phase_tab.clear(); return; }
+    gp.phase_tab.push_back((uint16_t)(acc_on ? acc : ((uint32_t)v & pmask)));
+  };
   uint64_t k = 0;
   long long cur = start;
   uint32_t phase = 0;
@@ -518,6 +554,7 @@ inline rsp_status plan_generator(const rsp_chain_params &p, const Regs &r, GenPl
           const long long v = (s.flags & 1u) ? start : wrap_host((long long)s.f0 + (long long)q * step, ow);
           cur = v;
           phase = (phase + ((uint32_t)v & pmask)) & pmask;
+          tab_push(phase, v);
         }
         k += ns;
       }
@@ -534,11 +571,12 @@ inline rsp_status plan_generator(const rsp_chain_params &p, const Regs &r, GenPl
   if (pause > 0) {
     GenSegment s; s.pad_ = 0; s.start = k; s.n = pause; s.f0 = (int32_t)start; s.step = 0; s.phase0 = phase; s.flags = 1u;
     gp.segs.push_back(s);
-    for (uint32_t q = 0; q < pause; ++q) phase = (phase + ((uint32_t)start & pmask)) & pmask;
+    for (uint32_t q = 0; q < pause; ++q) { phase = (phase + ((uint32_t)start & pmask)) & pmask; tab_push(phase, start); }
     k += pause;
   }
   gp.period_len = k;
-  gp.period_phase = phase;
+  gp.period_phase = acc_on ? phase : 0;
+  if (!tab_ok || gp.phase_tab.size() != k) gp.phase_tab.clear();
   // frameNum frames with a pause between them, none after the last; 0 = forever
   gp.total = frame_num == 0 ? ~0ULL : (uint64_t)frame_num * gp.period_len - (uint64_t)pause;
   return RSP_OK;

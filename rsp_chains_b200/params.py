@@ -116,6 +116,8 @@ class FFTParams:
     minSRAMdepth: int = 0
     windowFunc: Optional["WindowFunctionType"] = None    # None = WindowFunctionTypes.None()
     arith: str = "fixed"       # "fixed" (FFTParams.fixed) or "fp32" (FFTParams.DSPReal run in single precision)
+    windowRam: bool = False    # set by FFTBlockWithWindowing (chain.py): the block carries the run-time coefficient RAM + doWindowing register
+    windowRamWidth: int = 16   # width of protoWin for that RAM (FixedPoint(w, w - 2)), WindowFunctionTypes.None(dataWidth_tmp)
 
     @staticmethod
     def fixed(**kw) -> "FFTParams":
@@ -148,7 +150,8 @@ class FFTParams:
             int(self.use4Muls), int(self.useBitReverse), int(self.fftDir), int(self.runTime), mask,
             0 if self.decimType == DIFDecimType else 1, 4 if self.sdfRadix == "2^2" else 2,
             sum((1 if e else 0) << i for i, e in enumerate(self.expandLogic)), int(self.keepMSBorLSBReg), int(self.fftDirReg),
-            *(self.windowFunc.to_c() if self.windowFunc is not None else (0, 16, 0.0, 0.0, 0.0)), int(self.overflowReg), 0)
+            *(self.windowFunc.to_c() if self.windowFunc is not None else (0, self.windowRamWidth, 0.0, 0.0, 0.0)), int(self.overflowReg),
+            int(self.windowRam))
 
 
 @dataclass
@@ -229,7 +232,7 @@ class FixedNCOParams:
     def to_c(self) -> _abi.NcoParams:
         return _abi.NcoParams(self.tableSize, self.tableWidth, self.phaseWidth, int(self.phaseAccEnable),
                               int(self.rasterizedMode), self.nInterpolationTerms, int(self.ditherEnable),
-                              int(self.useMultiplier), int(self.useQAM))
+                              int(self.useMultiplier), int(self.useQAM), _abi.TRIM[self.roundingMode])
 
 
 @dataclass

@@ -215,3 +215,24 @@ def test_plfg_output_width_frac_slices_at_int_width(oracle):
     tick = _rtl_plfg_ticks(50, max_seg=4, nsw=8, ow=12, owi=8, frame_num=1, inter=63, ndiff=1, start_reg=0x90, seg_nums=[1, 1, 1, 1],
                            rep_nums=[1], ord_nums=[0], ram=[wd, 0, 0, 0])
     assert tick == want
+
+
+def test_nco_output_multiplier(oracle):
+    """FixedNCOParams.useMultiplier (NCOLazyModuleBlock.scala:354-364; NCOMultiplierSpec.scala:100 writes the factor 0x1000 = 0.25 in
+    Q2.14): sin and cos times the factor, product trimmed back to Q2.14 under roundingMode; with enableMultiplying = 0 the factor is
+    1 << 14 = 1.0 and the output is unchanged"""
+    freq = np.full(1024, 5, np.int32)
+    plain, _ = oracle.nco_words(freq, 256, 16, 10)
+    same, _ = oracle.nco_words(freq, 256, 16, 10, use_multiplier=True, enable_multiplying=False, multiplying_factor=0x1000)
+    assert (same == plain).all()
+    quarter, _ = oracle.nco_words(freq, 256, 16, 10, use_multiplier=True, enable_multiplying=True, multiplying_factor=0x1000)
+    pc, ps = oracle.unpack_iq(plain)
+    qc, qs = oracle.unpack_iq(quarter)
+    assert (qc == (pc + 2) >> 2).all() and (qs == (ps + 2) >> 2).all()          # RoundHalfUp of x / 4
+    ph = 2 * np.pi * np.cumsum(freq) / 1024
+    assert np.abs(qc - 0.25 * 16384 * np.cos(ph)).max() <= 1.5 and np.abs(qs - 0.25 * 16384 * np.sin(ph)).max() <= 1.5
+    neg, _ = oracle.nco_words(freq, 256, 16, 10, use_multiplier=True, enable_multiplying=True, multiplying_factor=0xC000)   # -1.0
+    nc, ns = oracle.unpack_iq(neg)
+    assert (nc == np.where(pc == 16384, -16384, -pc)).all() and (ns == -ps).all()
+    fl, _ = oracle.nco_words(freq, 256, 16, 10, use_multiplier=True, enable_multiplying=True, multiplying_factor=0x1000, rounding_mode="Floor")
+    assert (oracle.unpack_iq(fl)[0] == pc >> 2).all()
