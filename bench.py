@@ -194,7 +194,7 @@ def run_reference(args):
         O.chain_fixed_words(fft, mag, cfar, sample, n_threads=threads)
     dt = time.perf_counter() - t0
     val = sample.size * args.steps / dt / 1e6
-    print(json.dumps({
+    emit({
         "impl": "reference", "metric": METRIC, "value": val, "unit": "Msamples/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "int16 fixed point (Q16.0, int64 intermediates)", "data": "synthetic",
@@ -203,7 +203,7 @@ def run_reference(args):
                          "sample": f"{rows} chirps x {N_POINTS} per step, {args.steps} steps"},
         "e2e": {"value": val, "unit": "Msamples/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "note": "reference is a Scala/Chisel hardware generator (no JVM here): CPU arm = oracle/ C port of its arithmetic, OpenMP over chirps",
-    }))
+    })
 
 
 # ---------------------------------------------------------------------------------------------------------------------
@@ -320,7 +320,29 @@ def generator_lines(torch, peak, rows=65536):
     return res
 
 
+_JSON_FD = None
+
+
+def claim_stdout():
+    """stdout carries the ONE JSON line and nothing else: libraries that print there (NCCL's version banner under NCCL_DEBUG=VERSION,
+    torchrun notices) are sent to stderr for the whole run; emit() writes the line to the real stdout"""
+    global _JSON_FD
+    if _JSON_FD is None:
+        sys.stdout.flush()
+        _JSON_FD = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(obj):
+    line = (json.dumps(obj) + "\n").encode()
+    if _JSON_FD is None:
+        sys.stdout.write(line.decode()); sys.stdout.flush()
+    else:
+        os.write(_JSON_FD, line)
+
+
 def main():
+    claim_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
@@ -500,7 +522,7 @@ def main():
                 out["configs"] = config_lines(torch, peak)
             except Exception as e:   # the headline line must survive a failing side configuration
                 out["configs"] = [{"error": repr(e)}]
-        print(json.dumps(out))
+        emit(out)
     ch.close()
     if world > 1:
         dist.barrier()

@@ -165,7 +165,9 @@ __device__ __forceinline__ int2 ldg_tw_volatile(const int2 *p) {
 }
 // rnd = {0x8000, -0x8000, 0x7FFF, -0x7FFF} come from the kernel arguments so that they are constant-bank operands of the IMADs
 // (written as literals the compiler splits them off into VIADDs on the ALU pipe, the pipe that bounds the kernel)
-template <bool TRUE_OUT>
+// RAW: the products are left unshifted (the 16-bit results sit in bits 16..31 of xr / xi): the caller packs the high halves straight
+// into the exchange word (one PRMT instead of two shifts and a PRMT)
+template <bool TRUE_OUT, bool RAW = false>
 __device__ __forceinline__ void fcmul(int &sg, int &xr, int &xi, const int2 w, int m1, const int (&rnd)[4]) {
   const int c = w.x, s = w.y;
   int r, i;
@@ -178,7 +180,21 @@ __device__ __forceinline__ void fcmul(int &sg, int &xr, int &xi, const int2 w, i
     i = imad(imad(xr, s, u), m1, 0);
     sg = 1;
   }
-  xr = sar(r, 16); xi = sar(i, 16);
+  if (RAW) { xr = r; xi = i; } else { xr = sar(r, 16); xi = sar(i, 16); }
+}
+
+// The same scaled butterfly producing both outputs with their TRUE sign (used by the last stage of a pass, whose outputs leave the
+// registers): s = (a + c + 1) >> 1 with the +1 as the third addend of one IADD3 (ALU pipe), d = s - c.  Same three instructions per
+// component as fbf1, and nothing is left to un-negate before the exchange store.
+#ifndef RSP_FAST_TRUE_LAST
+#define RSP_FAST_TRUE_LAST 1   // A/B knob: 0 = the negated form everywhere + un-negating IMADs at the end of a pass (round 1)
+#endif
+__device__ __forceinline__ void fbf_true(int sa, int &A, int sc, int &C, bool wrap, int one, int m1) {
+  const int t = (sa > 0 ? A : -A) + (sc > 0 ? C : -C) + 1;
+  const int sv = sar(t, 1);
+  const int d = fadd(1, sv, -sc, C, one, m1);
+  A = sv;
+  C = wrap ? sext16(d) : d;
 }
 
 // JPL magnitude approximation (generators/logMagMux/src/main/scala/LogMagMux.scala:92-110), stored to 16 bits by the caller
@@ -228,18 +244,27 @@ __device__ __forceinline__ void fast_group(const FastArgs &a, int tl, int g, con
     }
   }
   int sg[R];   // sign each point is held with (compile-time after unrolling): value = sg * register
+  bool raw[R]; // the point's components sit in bits 16..31 of its registers (unshifted twiddle product of the pass's last stage)
 #pragma unroll
-  for (int rr = 0; rr < R; ++rr) sg[rr] = 1;
+  for (int rr = 0; rr < R; ++rr) { sg[rr] = 1; raw[rr] = false; }
 #pragma unroll
   for (int s = 0; s < m; ++s) {
     const int i = i0 + s;
     const int dist = 1 << (m - 1 - s);
     const bool rot = (i != S - 1) && ((i & 1) == 0);   // x(-j) on the last quarter of each 4D block follows (SDFChainRadix22.scala:319-337)
     const bool wrap = WRAP && !(last && s == m - 1);    // the magnitude only takes |d| (|wrap16(32768)| == 32768)
+    const bool true_stage = RSP_FAST_TRUE_LAST && !last && s == m - 1;   // the outputs go to the exchange buffer: true signs, raw products
+    static_assert(last || (((i0 + m - 1) & 1) == 1), "a pass that is not the last ends on an odd stage (no rotation pending)");
 #pragma unroll
     for (int rr = 0; rr < R; ++rr)
       if (!(rr & dist)) {
         const int rc = rr + dist;
+        if (true_stage) {
+          fbf_true(sg[rr], re[rr], sg[rc], re[rc], wrap, a.one, a.m1);
+          fbf_true(sg[rr], im[rr], sg[rc], im[rc], wrap, a.one, a.m1);
+          sg[rr] = 1; sg[rc] = 1;
+          continue;
+        }
         const bool mj = rot && (rc & (dist >> 1));      // the difference point is rotated: (re, im) <- (im, -re)
         fbf1(sg[rr], re[rr], sg[rc], re[rc], mj, wrap, a.one, a.m1);
         fbf1(sg[rr], im[rr], sg[rc], im[rc], false, wrap, a.one, a.m1);
@@ -260,7 +285,8 @@ __device__ __forceinline__ void fast_group(const FastArgs &a, int tl, int g, con
         // several groups per pass (32 points per thread) use the same twiddles: left to CSE, the compiler keeps all 15 pairs of a
         // pass live across the groups and spills the row loop's invariants; a volatile load per group re-reads them from L1 instead
         const int2 w = smt ? tab[slot * q + k] : ((RSP_FAST_TW_VOLATILE && LP > 4 && !first) ? ldg_tw_volatile(&tab[slot * q + k]) : __ldg(&tab[slot * q + k]));
-        if (WRAP || (s == m - 1 && !last)) fcmul<true>(sg[rr], re[rr], im[rr], w, a.m1, a.rnd);
+        if (true_stage) { fcmul<true, true>(sg[rr], re[rr], im[rr], w, a.m1, a.rnd); raw[rr] = true; }
+        else if (WRAP || (s == m - 1 && !last)) fcmul<true>(sg[rr], re[rr], im[rr], w, a.m1, a.rnd);
         else fcmul<false>(sg[rr], re[rr], im[rr], w, a.m1, a.rnd);
       }
     }
@@ -270,7 +296,8 @@ __device__ __forceinline__ void fast_group(const FastArgs &a, int tl, int g, con
     for (int rr = 0; rr < R; ++rr)
       if (sg[rr] < 0) { re[rr] = fadd(-1, re[rr], 1, 0, a.one, a.m1); im[rr] = fadd(-1, im[rr], 1, 0, a.one, a.m1); }
 #pragma unroll
-    for (int rr = 0; rr < R; ++rr) xf[go + fidx<S>(rr * Dl)] = pack2(re[rr], im[rr]);
+    for (int rr = 0; rr < R; ++rr)
+      xf[go + fidx<S>(rr * Dl)] = raw[rr] ? __byte_perm((uint32_t)im[rr], (uint32_t)re[rr], 0x7632) : pack2(re[rr], im[rr]);
   } else {
 #pragma unroll
     for (int rr = 0; rr < R; ++rr) mags[g * R + rr] = fjpl(re[rr], im[rr]);
