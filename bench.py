@@ -74,16 +74,17 @@ def ncu_traffic():
     files = [f for p in pats for f in sorted(glob.glob(os.path.join(ROOT, "profiles", p)))]
     for f in files:
         rd = wr = None
+        unit = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}
         for line in open(f):
             c = line.rstrip("\n").split("\t")
-            if len(c) == 3 and c[0] == "dram__bytes_read.sum" and c[1] == "Mbyte":
-                rd = float(c[2])
-            if len(c) == 3 and c[0] == "dram__bytes_write.sum" and c[1] == "Mbyte":
-                wr = float(c[2])
+            if len(c) == 3 and c[0] == "dram__bytes_read.sum" and c[1] in unit:
+                rd = float(c[2]) * unit[c[1]]
+            if len(c) == 3 and c[0] == "dram__bytes_write.sum" and c[1] in unit:
+                wr = float(c[2]) * unit[c[1]]
         if rd is not None and wr is not None:
             # r01 captured 1/8 frame (4096 rows) per launch: scale to the bench launch; r02 captures are of the bench launch itself
             scale = 8.0 if os.path.basename(f).startswith("r01") else 1.0
-            best = ((rd + wr) * 1e6 * scale, os.path.basename(f) + (" (x8: captured on 4096 rows)" if scale != 1.0 else ""))
+            best = ((rd + wr) * scale, os.path.basename(f) + (" (x8: captured on 4096 rows)" if scale != 1.0 else ""))
     return best
 
 

@@ -59,7 +59,14 @@ static int env_int(const char *name, int dflt, int lo, int hi) {
 }
 static int pipe_depth() { static const int d = env_int("RSP_PIPE_DEPTH", 3, 1, N_PIPE); return d; }
 static bool pipe_ramp() { static const int r = env_int("RSP_PIPE_RAMP", 1, 0, 1); return r != 0; }
-static size_t pipe_chunk_bytes() { static const int m = env_int("RSP_PIPE_CHUNK_MIB", 16, 1, 1024); return (size_t)m << 20; }
+// chunk size of rsp_run_host: RSP_PIPE_CHUNK_MIB when set, else 1/32 of the batch within 16 .. 64 MiB (measured on B200 / PCIe Gen5:
+// 512 MiB batches 16 MiB chunks 42.7 GB/s each way (8 MiB 39.9), 2 GiB batches 16 / 32 / 64 / 128 MiB 43.2 / 45.3 / 45.7 / 45.4,
+// profiles/r01_e_e2e_pipeline_sweep.txt, profiles/r02_l_e2e_sweep.txt)
+static size_t pipe_chunk_bytes(size_t batch_bytes) {
+  static const int m = env_int("RSP_PIPE_CHUNK_MIB", 0, 0, 1024);
+  if (m > 0) return (size_t)m << 20;
+  return std::min<size_t>((size_t)64 << 20, std::max<size_t>((size_t)16 << 20, batch_bytes / 32));
+}
 
 struct rsp_chain {
   rsp_chain_params p;
@@ -672,7 +679,7 @@ extern "C" rsp_status rsp_run_host(rsp_chain *c, const void *h_in, uint32_t n_ch
   const size_t row_in = N * (fixed ? 4 : 8), row_out = h_out ? N * 4 : 0;
   const size_t row_mask = (!fixed && h_peak_mask) ? ((N + 31) / 32) * 4 : 0;
   // chunks of ~16 MiB of input (42.7 GB/s each way on PCIe Gen5 against 39.9 at 8 MiB; both directions at once peak at 49.8) keep three copies/kernels in flight
-  size_t rows_per_chunk = std::max<size_t>(1, pipe_chunk_bytes() / row_in);
+  size_t rows_per_chunk = std::max<size_t>(1, pipe_chunk_bytes((size_t)rows * row_in) / row_in);
   rows_per_chunk = std::min<size_t>(rows_per_chunk, std::max<uint32_t>(rows, 1));
   const bool in_pinned = is_pinned(h_in), out_pinned = !h_out || is_pinned(h_out);
   const bool mask_pinned = !row_mask || is_pinned(h_peak_mask);

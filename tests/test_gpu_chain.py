@@ -57,10 +57,21 @@ def test_chain_all_sizes_random(cuda, oracle, log_n):
     n = 1 << log_n
     W = max(1, min(16, n // 8))
     G = 1
-    if not (n > 2 * W + 2 * G + 1):
-        pytest.skip("CFAR window does not fit this size")
     p = chain_params(n, 0, W=max(2, W), G=max(1, G))
     beats = synth.random_beats(37 if log_n < 13 else 5, n, seed=log_n)
+    if not (n > 2 * W + 2 * G + 1):
+        # 2 and 4 points: no CFAR window fits (fftWin > 2 W + 2 G + 1, CFARCoreWithMem.scala:31-32): the FFT block alone, and the chain refuses
+        fft, _, _ = oracle_cfgs(oracle, p, log_n, 2, dict(fftWin=n))
+        want = oracle.fft_fixed_words(fft, beats)
+        with R.FftMagCfarChainVanilla(p) as ch:
+            ch.memWriteWord(p.fftAddress.base, log_n)
+            d_out = cuda.empty((beats.shape[0], n), dtype=cuda.int32, device="cuda")
+            ch.fft(to_dev(cuda, beats), beats.shape[0], d_out)
+            assert (from_dev_u32(d_out) == want).all()
+            configure(ch, log_n, 2, dict(fftWin=n, windowCells=W, guardCells=G))
+            with pytest.raises(R.RspError):
+                ch.run(to_dev(cuda, beats), beats.shape[0], 1, out=d_out)
+        return
     for mode in (0, 1, 2):
         regs = dict(fftWin=n, thresholdScaler=3, logOrLinearMode=1, divSum=max(0, W.bit_length() - 1), peakGrouping=mode & 1,
                     cfarMode=mode, windowCells=W, guardCells=G)
