@@ -2,7 +2,10 @@
 //
 // Every function here is the work of ONE thread during ONE phase of a chirp; phases are separated by a
 // block-wide barrier.  The CUDA kernels (rsp_kernels.cuh) call the phases with threadIdx-derived indices.  The functions are
-// host-callable as well (RSP_HD): the host builds tables with the very code the device reads them with (nco_lookup).
+// host-callable as well (RSP_HD): the host builds tables with the very code the device reads them with (nco_lookup), and
+// tests/emu/emu.cpp (test infrastructure) compiles this header with g++ and runs the phases thread by thread on argument blocks from
+// the product's planner, so index maps, integer arithmetic and planning are held to the oracle on a box without a GPU
+// (tests/test_emu_cpu.py).  The product library only ever runs the CUDA kernels.
 //
 // Arithmetic follows the reference generators (paths relative to the rsp-chains repository):
 //   butterfly + div2        generators/sdf-fft/src/main/scala/SDFFFTUtil.scala:51-61, SDFChainRadix22.scala:459-464,487-493
