@@ -17,6 +17,7 @@
 //    reuses the exchange buffer; bins are taken interleaved so that loads have immediate offsets and stores are coalesced
 //  * the peak bits of 32 consecutive bins are one warp ballot.
 #include <algorithm>
+#include <cstdlib>
 
 #include "rsp_fast.cuh"
 
@@ -38,6 +39,7 @@ struct FastF32Args {
   Detection *det_list;
   uint32_t *det_count;
   uint32_t det_cap;
+  int l2_prefetch;         // 1: one thread asks the L2 for the CTA's next row while this one is transformed (cp.async.bulk.prefetch.L2)
 };
 
 template <int S> struct FGeoF {
@@ -249,9 +251,30 @@ __device__ __noinline__ void f32_detections(const FastF32DetArgs a, int tl, cons
   }
 }
 
+// Resident CTAs per SM the register budget is cut for.  Shared memory already limits N = 4096 to three CTAs, N = 8192 and 16384 to one;
+// below that the cap is a trade of warps for registers: at 7 CTAs of 128 threads ptxas has 72 registers and spills the 16-point
+// butterflies, at 5 it has 96 and does not -- measured on B200 (profiles/r02_q_f32_variants.txt): C3 x 16 239 -> 275 Gsamples/s
+// from 7 -> 5, N = 4096 195 -> 211 from 4 -> 3.
+#ifndef RSP_F32_MAXB
+#define RSP_F32_MAXB 5
+#endif
+#ifndef RSP_F32_MAXB12
+#define RSP_F32_MAXB12 2
+#endif
+#ifndef RSP_F32_MAXB13
+#define RSP_F32_MAXB13 1
+#endif
+template <int S> constexpr int f32_min_blocks() {
+  constexpr int by_threads = 1024 / FGeoF<S>::THREADS;
+  constexpr int by_smem = (int)((size_t)228 * 1024 / (FGeoF<S>::ROW_BYTES * FGeoF<S>::CPC + 1024));   // 1 KiB per CTA is the system's
+  constexpr int m = by_threads < by_smem ? by_threads : by_smem;
+  constexpr int cap = S == 13 ? RSP_F32_MAXB13 : (S == 12 ? RSP_F32_MAXB12 : RSP_F32_MAXB);
+  return m > cap ? cap : (m < 1 ? 1 : m);
+}
+
 // EJ = number of leading / trailing iterations j whose bins may miss a window (ceil((W + G) / TPC), checked by the host)
 template <int S, int CMODE, bool LINEAR, int EJ>
-__global__ void __launch_bounds__(FGeoF<S>::THREADS, (1024 / FGeoF<S>::THREADS) > 7 ? 7 : (1024 / FGeoF<S>::THREADS))
+__global__ void __launch_bounds__(FGeoF<S>::THREADS, f32_min_blocks<S>())
 chain_f32_fast_kernel(const FastF32Args a) {
   using Gm = FGeoF<S>;
   constexpr int N = Gm::N, TPC = Gm::TPC, CPC = Gm::CPC, PTS = Gm::PTS, JSTEP = Gm::JSTEP;
@@ -283,6 +306,10 @@ chain_f32_fast_kernel(const FastF32Args a) {
 #pragma unroll
         for (int rr = 0; rr < PTS; ++rr) { const float w = __ldg(&gw[rr * TPC]); pre[rr] = mul2(pre[rr], pk2(w, w)); }
       }
+    }
+    if (a.l2_prefetch && tl == 0 && row0 + stride + c < a.n_rows) {   // the first pass is 1/3 of the row's time, half of it waiting for these loads
+      const u64 *nxt = a.in + (size_t)(row0 + stride + c) * N;
+      asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" :: "l"(nxt), "r"(8 * N) : "memory");
     }
     f32_passes<S, 0>(a, tl, pre, xb, mg);
     // window sums without a row-wide prefix (which would lose the noise floor behind a strong target in fp32): bins are
@@ -422,6 +449,8 @@ rsp_status launch_fast_f32_chain(const Plan &pl, const LaunchCtx &ctx, const F32
   fa.k_both = linear ? both * a.scaler : both;
   fa.k_one = linear ? a.inv_div * a.scaler : a.inv_div;
   fa.det_list = a.det_list; fa.det_count = a.det_count; fa.det_cap = a.det_cap;
+  { static int l2p = -1; if (l2p < 0) { const char *e = std::getenv("RSP_FAST_L2_PREFETCH"); l2p = e ? std::atoi(e) : 1; }
+    fa.l2_prefetch = (l2p != 0 && (reinterpret_cast<uintptr_t>(a.in) & 15u) == 0) ? 1 : 0; }
   const int ej = f32_edge_iters(pl.S, a.W, a.G);
   switch (pl.S) {
   case 10: return ej == 2 ? launch_f32_fast_modes<10, 2>(cmode, linear, ctx, fa, st, err) : launch_f32_fast_modes<10, 1>(cmode, linear, ctx, fa, st, err);
