@@ -42,9 +42,17 @@ struct FastF32Args {
   int l2_prefetch;         // 1: one thread asks the L2 for the CTA's next row while this one is transformed (cp.async.bulk.prefetch.L2)
 };
 
+// Points per thread: 16, or two sets of 16 (NQ = 2) from N = 2^RSP_F32_NQ2_SMIN on.  N = 16384 at 16 points per thread is one CTA of 1024
+// threads, which leaves ptxas 64 registers and 116 bytes of spills; at 32 points it is 512 threads with 128 registers.  A pass still
+// works on 16 points at a time, the thread just owns twice as many groups (and two blocks of 16 bins in the CFAR).
+#ifndef RSP_F32_NQ2_SMIN
+#define RSP_F32_NQ2_SMIN 14
+#endif
 template <int S> struct FGeoF {
   static constexpr int N = 1 << S;
-  static constexpr int PTS = 16;
+  static constexpr int NQ = S >= RSP_F32_NQ2_SMIN ? 2 : 1;
+  static constexpr int LP = NQ == 2 ? 5 : 4;
+  static constexpr int PTS = 16 * NQ;
   static constexpr int TPC = N / PTS;                         // threads per chirp
   static constexpr int CPC = TPC >= 128 ? 1 : 128 / TPC;      // chirps per CTA
   static constexpr int THREADS = TPC * CPC;
@@ -122,35 +130,37 @@ __device__ __forceinline__ void jpl2_scaled(u64 z0, u64 z1, float sc, float &m0,
 
 // One pass = m radix-2 stages in registers on 2^m points Dl apart (the decomposition of rsp_device.cuh, fx_pass_*).
 // Thread tl of the chirp works on the groups vt = g * TPC + tl, so a warp touches consecutive points in every pass.
-// Every shared-memory address is one run-time base plus a compile-time offset: xidx(base + g * TPC * R + rr * Dl) =
-// xidx(base) + xidx(g * TPC * R + rr * Dl) for all the shapes used here (checked exhaustively, tests/test_kernel_layout.py).
+// Every shared-memory address is one run-time base plus a compile-time offset: with gbase(v) = the first point of group v (m zero bits
+// inserted at bit LDl of v), gbase(g * TPC + tl) = gbase(tl) + gbase(g * TPC) and xidx(gbase(tl) + gbase(g * TPC) + rr * Dl) =
+// xidx(gbase(tl)) + xidx(gbase(g * TPC) + rr * Dl) for all the shapes used here (checked exhaustively, tests/test_kernel_layout.py).
+template <int m, int LDl> __host__ __device__ constexpr int gbase(int v) { return ((v >> LDl) << (m + LDl)) | (v & ((1 << LDl) - 1)); }
 template <int S, int K>
-__device__ __forceinline__ void f32_pass(const FastF32Args &a, int tl, const u64 (&pre)[16], u64 *xb, float *mg) {
+__device__ __forceinline__ void f32_pass(const FastF32Args &a, int tl, const u64 (&pre)[FGeoF<S>::PTS], u64 *xb, float *mg) {
   using Gm = FGeoF<S>;
   constexpr int m = fx_pass_size(S, K), i0 = fx_pass_start(S, K), LDl = S - i0 - m, Dl = 1 << LDl;
-  constexpr int PTS = Gm::PTS, G = PTS >> m, R = 1 << m, TPC = Gm::TPC;
+  constexpr int PTS = Gm::PTS, G = PTS >> m, R = 1 << m, TPC = Gm::TPC, LP = Gm::LP;
   constexpr bool first = (K == 0), last = (K == fx_n_passes(S) - 1);
   static_assert((i0 & 1) == 0, "passes start on even stages");
   static_assert(!last || Dl == 1, "the last pass works on neighbouring points");
   float mags[last ? PTS : 1];
   const int low = tl & (Dl - 1);
-  const int base0 = ((tl >> LDl) << (m + LDl)) | low;        // group g starts at base0 + g * TPC * R
+  const int base0 = ((tl >> LDl) << (m + LDl)) | low;        // gbase(tl); group g starts at base0 + gbase(g * TPC)
   u64 *xp = xb + xidx<S>(base0);
 #pragma unroll
   for (int g = 0; g < G; ++g) {
     u64 z[R];
     if (first) {
 #pragma unroll
-      for (int rr = 0; rr < R; ++rr) z[rr] = pre[rr];        // m = 4, one group, p = tl + rr * TPC
+      for (int rr = 0; rr < R; ++rr) z[rr] = pre[g + G * rr];   // m = 4, G = NQ groups, p = tl + g * TPC + rr * (NQ * TPC)
     } else if (last) {                                        // 2^m neighbouring points: 128-bit loads
 #pragma unroll
       for (int rr = 0; rr < R; rr += 2) {
-        const ulonglong2 v = *reinterpret_cast<const ulonglong2 *>(&xp[xidx<S>(g * TPC * R + rr)]);
+        const ulonglong2 v = *reinterpret_cast<const ulonglong2 *>(&xp[xidx<S>(gbase<m, LDl>(g * TPC) + rr)]);
         z[rr] = v.x; z[rr + 1] = v.y;
       }
     } else {
 #pragma unroll
-      for (int rr = 0; rr < R; ++rr) z[rr] = xp[xidx<S>(g * TPC * R + rr * Dl)];
+      for (int rr = 0; rr < R; ++rr) z[rr] = xp[xidx<S>(gbase<m, LDl>(g * TPC) + rr * Dl)];
     }
 #pragma unroll
     for (int s = 0; s < m; ++s) {
@@ -169,7 +179,7 @@ __device__ __forceinline__ void f32_pass(const FastF32Args &a, int tl, const u64
       const int q = 1 << (L - 2);
       // one table read per distinct k: W^k with both operand pairs A = (c, s), B = (-s, c); W^2k = W^k W^k and
       // W^3k = W^2k W^k follow by the same packed product (B' = j W' = (j W) W), which saves two thirds of the loads
-      const float4 *tab = a.tw + a.tw_off[L] + q + low;       // the W^k run
+      const float4 *tab = a.tw + a.tw_off[L] + q + low + ((g * TPC) & (Dl - 1));   // the W^k run; k = (vt mod Dl) + (rr mod dist) Dl
 #pragma unroll
       for (int kk = 0; kk < dist; ++kk) {
         const float4 w1 = __ldg(&tab[kk * Dl]);
@@ -188,32 +198,37 @@ __device__ __forceinline__ void f32_pass(const FastF32Args &a, int tl, const u64
     }
     if (!last) {
 #pragma unroll
-      for (int rr = 0; rr < R; ++rr) xp[xidx<S>(g * TPC * R + rr * Dl)] = z[rr];
+      for (int rr = 0; rr < R; ++rr) xp[xidx<S>(gbase<m, LDl>(g * TPC) + rr * Dl)] = z[rr];
     } else {
 #pragma unroll
       for (int rr = 0; rr < R; rr += 2) jpl2_scaled(z[rr], z[rr + 1], a.inv_n, mags[g * R + rr], mags[g * R + rr + 1]);
     }
   }
   if (last) {
-    // bin of point p = (vt << m) + rr is bitrev_S(p) = rev_m(rr) << (S - m) | rev_{S-4}(tl) << (4 - m) | rev_{4-m}(g):
+    // bin of point p = (vt << m) + rr is bitrev_S(p) = rev_m(rr) << (S - m) | rev_{S-LP}(tl) << (LP - m) | rev_{LP-m}(g):
     // for a fixed rr the G groups of the thread are G neighbouring bins -> one G-float store per rr
-    const uint32_t rtl = (__brev((uint32_t)tl) >> (32 - (S - 4))) << (4 - m);
+    const uint32_t rtl = (__brev((uint32_t)tl) >> (32 - (S - LP))) << (LP - m);
     float *mp = mg + midx((int)rtl);
 #pragma unroll
     for (int rr = 0; rr < R; ++rr) {
       constexpr int SH = S - m;
       const int rrr = (int)((__brev((uint32_t)rr) >> (32 - m)) << SH);   // compile-time, a multiple of 32
       float *dst = mp + rrr + ((rrr >> 5) << 2);
-      if (G == 4) *reinterpret_cast<float4 *>(dst) = make_float4(mags[0 * R + rr], mags[2 * R + rr], mags[1 * R + rr], mags[3 * R + rr]);
-      else if (G == 2) *reinterpret_cast<float2 *>(dst) = make_float2(mags[0 * R + rr], mags[1 * R + rr]);
+      if constexpr (G >= 4) {
+        float o[G];
+#pragma unroll
+        for (int g = 0; g < G; ++g) o[(int)(__brev((uint32_t)g) >> (32 - (LP - m)))] = mags[g * R + rr];
+#pragma unroll
+        for (int q = 0; q < G; q += 4) *reinterpret_cast<float4 *>(dst + q) = make_float4(o[q], o[q + 1], o[q + 2], o[q + 3]);
+      } else if constexpr (G == 2) *reinterpret_cast<float2 *>(dst) = make_float2(mags[0 * R + rr], mags[1 * R + rr]);
       else *dst = mags[rr];
     }
   }
 }
 
 template <int S, int K>
-__device__ __forceinline__ void f32_passes(const FastF32Args &a, int tl, const u64 (&pre)[16], u64 *xb, float *mg) {
-  static_assert(K != 0 || fx_pass_size(S, 0) == 4, "the first pass takes the 16 prefetched points of the thread");
+__device__ __forceinline__ void f32_passes(const FastF32Args &a, int tl, const u64 (&pre)[FGeoF<S>::PTS], u64 *xb, float *mg) {
+  static_assert(K != 0 || fx_pass_size(S, 0) == 4, "the first pass takes the prefetched points of the thread, 16 at a time");
   f32_pass<S, K>(a, tl, pre, xb, mg);
   __syncthreads();
   if constexpr (K + 1 < fx_n_passes(S)) f32_passes<S, K + 1>(a, tl, pre, xb, mg);
@@ -236,7 +251,7 @@ struct FastF32DetArgs { int W, G; float k_both, k_one, scaler; uint32_t chirp, m
 template <int S, int CMODE, bool LINEAR>
 __device__ __noinline__ void f32_detections(const FastF32DetArgs a, int tl, const float *QP, const float *AS, const float *X) {
   constexpr int N = 1 << S, TPC = FGeoF<S>::TPC;
-  for (int j = 0; j < 16; ++j) {
+  for (int j = 0; j < FGeoF<S>::PTS; ++j) {
     if (!((a.mask >> j) & 1u)) continue;
     const int n = tl + j * TPC, W = a.W, G = a.G;
     const bool lagg_full = (n + G + W <= N - 1), lead_full = (n - G - W >= 0);
@@ -268,7 +283,7 @@ template <int S> constexpr int f32_min_blocks() {
   constexpr int by_threads = 1024 / FGeoF<S>::THREADS;
   constexpr int by_smem = (int)((size_t)228 * 1024 / (FGeoF<S>::ROW_BYTES * FGeoF<S>::CPC + 1024));   // 1 KiB per CTA is the system's
   constexpr int m = by_threads < by_smem ? by_threads : by_smem;
-  constexpr int cap = S == 13 ? RSP_F32_MAXB13 : (S == 12 ? RSP_F32_MAXB12 : RSP_F32_MAXB);
+  constexpr int cap = FGeoF<S>::NQ == 2 ? 8 : (S == 13 ? RSP_F32_MAXB13 : (S == 12 ? RSP_F32_MAXB12 : RSP_F32_MAXB));
   return m > cap ? cap : (m < 1 ? 1 : m);
 }
 
@@ -277,20 +292,22 @@ template <int S, int CMODE, bool LINEAR, int EJ>
 __global__ void __launch_bounds__(FGeoF<S>::THREADS, f32_min_blocks<S>())
 chain_f32_fast_kernel(const FastF32Args a) {
   using Gm = FGeoF<S>;
-  constexpr int N = Gm::N, TPC = Gm::TPC, CPC = Gm::CPC, PTS = Gm::PTS, JSTEP = Gm::JSTEP;
+  constexpr int N = Gm::N, TPC = Gm::TPC, CPC = Gm::CPC, PTS = Gm::PTS, JSTEP = Gm::JSTEP, NQ = Gm::NQ;
   extern __shared__ __align__(16) unsigned char smem_raw[];
   const int c = threadIdx.x / TPC, tl = threadIdx.x % TPC;
   u64 *xb = reinterpret_cast<u64 *>(smem_raw + (size_t)c * Gm::ROW_BYTES);
   float *mg = reinterpret_cast<float *>(xb + Gm::XB);
   // QP, AS and the block totals (+ 8 zeros for the blocks past the end of the row) reuse the exchange buffer, dead after the last FFT pass
   float *QP = reinterpret_cast<float *>(xb), *AS = QP + N + 16, *tsum = AS + N;
-  static_assert((size_t)(2 * N + 16 + TPC + 8) * 4 <= (size_t)Gm::XB * 8, "the CFAR arrays fit the exchange buffer");
+  static_assert((size_t)(2 * N + 16 + NQ * TPC + 8) * 4 <= (size_t)Gm::XB * 8, "the CFAR arrays fit the exchange buffer");
   // the leading borders of the first iterations are negative: only dereferenced from j >= EJ on, where the index is >= 0
   const float *pA = AS + (tl + a.G + 1), *pB = QP + (tl + a.G + a.W + 1), *pC = AS + (tl - a.G - a.W), *pD = QP + (tl - a.G);
   const int nblk = a.W >> 4;
   const float *pX = mg + midx(tl);
-  const float *pX16 = mg + midx(tl * PTS);   // the thread's 16 neighbouring bins: midx(16 tl + k) = midx(16 tl) + k
-  float *pP16 = QP + tl * PTS, *pS16 = AS + tl * PTS;
+  // the thread's blocks of 16 neighbouring bins: block tl + h TPC, h < NQ; midx(16 b + k) = midx(16 b) + k
+  const float *pX16 = mg + midx(tl * 16);
+  float *pP16 = QP + tl * 16, *pS16 = AS + tl * 16;
+  constexpr int XH = 16 * TPC + ((16 * TPC) >> 3);   // midx(16 (tl + TPC)) - midx(16 tl)
   const int prot = (tl >> 1) & 3;
   const uint32_t stride = gridDim.x * CPC;
   for (uint32_t row0 = blockIdx.x * CPC; row0 < a.n_rows; row0 += stride) {
@@ -316,35 +333,41 @@ chain_f32_fast_kernel(const FastF32Args a) {
     // cut into the threads' blocks of 16; QP[n] = sum of the block of n before n, AS[n] = sum of the block of n from n on
     // plus the W/16 - 1 blocks that follow.  A window [a, a + W) with W a multiple of 16 is AS[a] + QP[a + W]: additions
     // of non-negative terms only, every partial sum no larger than the window's own.
-    float x[PTS];
+    float x[NQ][16];
 #pragma unroll
-    for (int k = 0; k < PTS; k += 4) {
-      const float4 v = *reinterpret_cast<const float4 *>(&pX16[k]);
-      x[k] = v.x; x[k + 1] = v.y; x[k + 2] = v.z; x[k + 3] = v.w;
+    for (int h = 0; h < NQ; ++h) {
+#pragma unroll
+      for (int k = 0; k < 16; k += 4) {
+        const float4 v = *reinterpret_cast<const float4 *>(&pX16[h * XH + k]);
+        x[h][k] = v.x; x[h][k + 1] = v.y; x[h][k + 2] = v.z; x[h][k + 3] = v.w;
+      }
+      float t = x[h][15];
+#pragma unroll
+      for (int k = 14; k >= 0; --k) t += x[h][k];
+      tsum[tl + h * TPC] = t;
     }
-    float sv[PTS];
-    sv[PTS - 1] = x[PTS - 1];
-#pragma unroll
-    for (int k = PTS - 2; k >= 0; --k) sv[k] = sv[k + 1] + x[k];
-    tsum[tl] = sv[0];
-    if (tl < 8) tsum[TPC + tl] = 0.f;
+    if (tl < 8) tsum[NQ * TPC + tl] = 0.f;
     __syncthreads();
-    float follow = 0.f;
-    for (int i = 1; i < nblk; ++i) follow += tsum[tl + i];
-    {
-      float pv[PTS];
+#pragma unroll
+    for (int h = 0; h < NQ; ++h) {
+      float follow = 0.f;
+      for (int i = 1; i < nblk; ++i) follow += tsum[tl + h * TPC + i];
+      float sv[16], pv[16];
+      sv[15] = x[h][15];
+#pragma unroll
+      for (int k = 14; k >= 0; --k) sv[k] = sv[k + 1] + x[h][k];
       pv[0] = 0.f;
 #pragma unroll
-      for (int k = 1; k < PTS; ++k) pv[k] = pv[k - 1] + x[k - 1];
+      for (int k = 1; k < 16; ++k) pv[k] = pv[k - 1] + x[h][k - 1];
 #pragma unroll
-      for (int k = 0; k < PTS; ++k) sv[k] += follow;
-      // The thread's 16 values are 64 bytes: lanes 64 bytes apart would hit two 16-byte bank groups only, so lane l stores
+      for (int k = 0; k < 16; ++k) sv[k] += follow;
+      // The block's 16 values are 64 bytes: lanes 64 bytes apart would hit two 16-byte bank groups only, so lane l stores
       // its four quads in the order rotated by (l >> 1) & 3, which spreads the 8 lanes of a quarter warp over all 8 groups.
       const bool r1 = (tl >> 1) & 1, r2 = (tl >> 2) & 1;
 #pragma unroll
       for (int arr = 0; arr < 2; ++arr) {
         const float *src = arr ? sv : pv;
-        float *dst = arr ? pS16 : pP16;
+        float *dst = (arr ? pS16 : pP16) + h * 16 * TPC;
         float4 f4[4], g4[4];
 #pragma unroll
         for (int k = 0; k < 4; ++k) f4[k] = make_float4(src[4 * k], src[4 * k + 1], src[4 * k + 2], src[4 * k + 3]);
@@ -360,8 +383,8 @@ chain_f32_fast_kernel(const FastF32Args a) {
           *reinterpret_cast<float4 *>(&dst[((k + prot) & 3) * 4]) = v;
         }
       }
-      if (tl == 0) QP[N] = 0.f;
     }
+    if (tl == 0) QP[N] = 0.f;
     __syncthreads();
     float *gout = a.out ? a.out + (size_t)row * N + tl : nullptr;
     uint32_t *gmask = a.peak_mask ? a.peak_mask + (size_t)row * Gm::MASKW + (tl >> 5) : nullptr;
@@ -395,7 +418,7 @@ chain_f32_fast_kernel(const FastF32Args a) {
 
 // ---------------------------------------------------------------------------------------------------------------------
 // host side
-static int f32_edge_iters(int S, int W, int G) { const int tpc = (1 << S) / 16; return (W + G + tpc - 1) / tpc; }
+static int f32_edge_iters(int S, int W, int G) { const int tpc = (1 << S) / (S >= RSP_F32_NQ2_SMIN ? 32 : 16); return (W + G + tpc - 1) / tpc; }
 
 bool fast_f32_chain_supported(const Plan &pl, const F32Args &a) {
   if (pl.first_stage != STAGE_FFT || pl.last_stage != STAGE_CFAR) return false;

@@ -25,6 +25,18 @@ def xidx(p, S=10): return p + ((p >> 4) << 1) + (0 if S == 12 else ((p >> 6) << 
 def midx(n): return n + ((n >> 5) << 2)
 
 
+def _rev(x, bits):
+    r = 0
+    for i in range(bits): r |= ((x >> i) & 1) << (bits - 1 - i)
+    return r
+
+
+def f32_pts(S): return 32 if S >= 14 else 16     # FGeoF<S>::PTS: two sets of 16 points per thread from RSP_F32_NQ2_SMIN on
+
+
+def gbase(v, m, LDl): return ((v >> LDl) << (m + LDl)) | (v & ((1 << LDl) - 1))
+
+
 def wavefronts(addrs, width):
     """shared-memory wavefronts of one warp access: `width` bytes per lane, 128 bytes per wavefront group"""
     group, tot = 128 // width, 0
@@ -39,31 +51,52 @@ def wavefronts(addrs, width):
 
 @pytest.mark.parametrize("S", [10, 11, 12, 13, 14])
 def test_exchange_buffer_offsets_are_additive_and_passes_start_even(S):
-    N, TPC = 1 << S, (1 << S) // 16
+    PTS = f32_pts(S)
+    N, TPC = 1 << S, (1 << S) // PTS
     assert sum(pass_size(S, k) for k in range(n_passes(S))) == S
+    seen = set()
     for K in range(n_passes(S)):
         m, i0 = pass_size(S, K), pass_start(S, K)
         assert i0 % 2 == 0                       # a radix-2^2 pair (butterfly, -j, butterfly, twiddle) never straddles two passes
-        LDl = S - i0 - m; Dl = 1 << LDl; G = 16 >> m; R = 1 << m
+        LDl = S - i0 - m; Dl = 1 << LDl; G = PTS >> m; R = 1 << m
         for tl in range(TPC):
-            base0 = ((tl >> LDl) << (m + LDl)) | (tl & (Dl - 1))
+            base0 = gbase(tl, m, LDl)
             for g in range(G):
                 vt = g * TPC + tl
-                base = ((vt >> LDl) << (m + LDl)) | (vt & (Dl - 1))
-                assert base == base0 + g * TPC * R
+                base = gbase(vt, m, LDl)
+                assert base == base0 + gbase(g * TPC, m, LDl)
+                assert (vt & (Dl - 1)) == (tl & (Dl - 1)) + ((g * TPC) & (Dl - 1))      # the twiddle index of the group
                 for rr in range(R):
-                    assert xidx(base + rr * Dl, S) == xidx(base0, S) + xidx(g * TPC * R + rr * Dl, S)
+                    assert xidx(base + rr * Dl, S) == xidx(base0, S) + xidx(gbase(g * TPC, m, LDl) + rr * Dl, S)
+                    if K == 0: seen.add(base + rr * Dl)
             assert midx(16 * tl + 15) == midx(16 * tl) + 15
+            for h in range(PTS // 16):           # the thread's CFAR blocks of 16 bins
+                assert midx(16 * (tl + h * TPC)) == midx(16 * tl) + h * (16 * TPC + ((16 * TPC) >> 3))
         assert xidx(N - 1, S) < N + (N >> 3) + (N >> 4) + 8
+    assert seen == set(range(N))
+    # first pass: group g, leg rr is the prefetched point pre[g + G rr] = in[tl + (g + G rr) TPC]
+    G0 = PTS >> 4
+    for tl in (0, 1, TPC - 1):
+        for g in range(G0):
+            for rr in range(16):
+                assert gbase(g * TPC + tl, 4, S - 4) + rr * (N >> 4) == tl + (g + G0 * rr) * TPC
+    # last pass: bin of point (vt << m) + rr = rev_m(rr) << (S - m) | rev_{S-LP}(tl) << (LP - m) | rev_{LP-m}(g)
+    m = pass_size(S, n_passes(S) - 1); LP = PTS.bit_length() - 1
+    for tl in (0, 1, 5, TPC - 1):
+        for g in range(PTS >> m):
+            for rr in range(1 << m):
+                p = ((g * TPC + tl) << m) + rr
+                assert _rev(p, S) == (_rev(rr, m) << (S - m)) | (_rev(tl, S - LP) << (LP - m)) | _rev(g, LP - m)
 
 
 @pytest.mark.parametrize("S,worst", [(10, 1.0), (11, 1.0), (12, 1.0), (13, 1.25), (14, 1.0)])
 def test_exchange_buffer_padding_is_conflict_free(S, worst):
-    N, TPC = 1 << S, (1 << S) // 16
+    PTS = f32_pts(S)
+    N, TPC = 1 << S, (1 << S) // PTS
     tot = ideal = 0
     for K in range(n_passes(S)):
         m, i0 = pass_size(S, K), pass_start(S, K)
-        LDl = S - i0 - m; Dl = 1 << LDl; G = 16 >> m; R = 1 << m
+        LDl = S - i0 - m; Dl = 1 << LDl; G = PTS >> m; R = 1 << m
         last = K == n_passes(S) - 1
         for warp0 in range(0, min(TPC, 64), 32):
             for g in range(G):
@@ -71,8 +104,7 @@ def test_exchange_buffer_padding_is_conflict_free(S, worst):
                     addrs = []
                     for lane in range(32):
                         vt = g * TPC + (warp0 + lane) % TPC
-                        base = ((vt >> LDl) << (m + LDl)) | (vt & (Dl - 1))
-                        addrs.append(xidx(base + rr * Dl, S) * 8)
+                        addrs.append(xidx(gbase(vt, m, LDl) + rr * Dl, S) * 8)
                     if last and rr % 2:
                         continue                     # the last pass reads two neighbouring points per 128-bit load
                     w, i = wavefronts(addrs, 16 if last else 8)
@@ -91,12 +123,6 @@ def fidx_fixed(p, S):
 
 
 def mhx(n, S): return n + ((n >> 6) << 3) + (((n >> 10) << 3) if S == 14 else 0)
-
-
-def _rev(x, bits):
-    r = 0
-    for i in range(bits): r |= ((x >> i) & 1) << (bits - 1 - i)
-    return r
 
 
 def fixed_kernel_wavefronts(S):
