@@ -45,6 +45,9 @@ struct FastF32Args {
 // Points per thread: 16, or two sets of 16 (NQ = 2) from N = 2^RSP_F32_NQ2_SMIN on.  N = 16384 at 16 points per thread is one CTA of 1024
 // threads, which leaves ptxas 64 registers and 116 bytes of spills; at 32 points it is 512 threads with 128 registers.  A pass still
 // works on 16 points at a time, the thread just owns twice as many groups (and two blocks of 16 bins in the CFAR).
+#ifndef RSP_F32_REGPF
+#define RSP_F32_REGPF 1   // next row's beats into registers behind the first pass (A/B knob)
+#endif
 #ifndef RSP_F32_NQ2_SMIN
 #define RSP_F32_NQ2_SMIN 14
 #endif
@@ -228,7 +231,7 @@ __device__ __forceinline__ void f32_pass(const FastF32Args &a, int tl, const u64
 
 template <int S, int K>
 __device__ __forceinline__ void f32_passes(const FastF32Args &a, int tl, const u64 (&pre)[FGeoF<S>::PTS], u64 *xb, float *mg) {
-  static_assert(K != 0 || fx_pass_size(S, 0) == 4, "the first pass takes the prefetched points of the thread, 16 at a time");
+  static_assert(fx_pass_size(S, 0) == 4, "the first pass takes the prefetched points of the thread, 16 at a time");
   f32_pass<S, K>(a, tl, pre, xb, mg);
   __syncthreads();
   if constexpr (K + 1 < fx_n_passes(S)) f32_passes<S, K + 1>(a, tl, pre, xb, mg);
@@ -310,25 +313,39 @@ chain_f32_fast_kernel(const FastF32Args a) {
   constexpr int XH = 16 * TPC + ((16 * TPC) >> 3);   // midx(16 (tl + TPC)) - midx(16 tl)
   const int prot = (tl >> 1) & 3;
   const uint32_t stride = gridDim.x * CPC;
+  // The thread's points of a row, p = tl + rr * TPC (warp-contiguous 256-byte runs), are only used by the first pass: the next row's are
+  // loaded into the same registers right behind it and land while the other passes and the CFAR of this row run (from N = 4096 on, where
+  // few warps are resident: +1 % there, -2 % below; profiles/r02_q_f32_variants.txt).  The L2 prefetch runs one row further ahead.
+  constexpr bool PF = RSP_F32_REGPF && S >= 12;
+  u64 pre[PTS];
+  auto load_row = [&](uint32_t r0, int g_lo, int g_hi) {   // the points of the first-pass groups g_lo .. g_hi - 1 (pre[g + NQ * rr])
+    const uint32_t r = r0 + c < a.n_rows ? r0 + c : a.n_rows - 1;
+    const u64 *gin = a.in + (size_t)r * N + tl;
+#pragma unroll
+    for (int q = 0; q < PTS; ++q) if (q % NQ >= g_lo && q % NQ < g_hi) pre[q] = __ldg(&gin[q * TPC]);
+  };
+  auto l2_row = [&](uint32_t r0) {
+    if (a.l2_prefetch && tl == 0 && r0 + c < a.n_rows) {
+      const u64 *nxt = a.in + (size_t)(r0 + c) * N;
+      asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" :: "l"(nxt), "r"(8 * N) : "memory");
+    }
+  };
+  // with 32 points per thread only the first group's 16 are taken ahead (64 more registers would spill); the others follow at the top of the row
+  if (PF && blockIdx.x * CPC < a.n_rows) { load_row(blockIdx.x * CPC, 0, 1); l2_row(blockIdx.x * CPC + stride); }
   for (uint32_t row0 = blockIdx.x * CPC; row0 < a.n_rows; row0 += stride) {
     const bool active = row0 + c < a.n_rows;
     const uint32_t row = active ? row0 + c : a.n_rows - 1;
-    u64 pre[PTS];   // the thread's 16 points of the row: p = tl + rr * TPC, warp-contiguous 256-byte runs
-    {
-      const u64 *gin = a.in + (size_t)row * N + tl;
+    load_row(row0, PF ? 1 : 0, NQ);
+    l2_row(row0 + (PF ? 2 : 1) * stride);
+    if (a.win != nullptr) {
+      const float *gw = a.win + tl;
 #pragma unroll
-      for (int rr = 0; rr < PTS; ++rr) pre[rr] = __ldg(&gin[rr * TPC]);
-      if (a.win != nullptr) {
-        const float *gw = a.win + tl;
-#pragma unroll
-        for (int rr = 0; rr < PTS; ++rr) { const float w = __ldg(&gw[rr * TPC]); pre[rr] = mul2(pre[rr], pk2(w, w)); }
-      }
+      for (int rr = 0; rr < PTS; ++rr) { const float w = __ldg(&gw[rr * TPC]); pre[rr] = mul2(pre[rr], pk2(w, w)); }
     }
-    if (a.l2_prefetch && tl == 0 && row0 + stride + c < a.n_rows) {   // the first pass is 1/3 of the row's time, half of it waiting for these loads
-      const u64 *nxt = a.in + (size_t)(row0 + stride + c) * N;
-      asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" :: "l"(nxt), "r"(8 * N) : "memory");
-    }
-    f32_passes<S, 0>(a, tl, pre, xb, mg);
+    f32_pass<S, 0>(a, tl, pre, xb, mg);
+    if (PF && row0 + stride < a.n_rows) load_row(row0 + stride, 0, 1);
+    __syncthreads();
+    f32_passes<S, 1>(a, tl, pre, xb, mg);
     // window sums without a row-wide prefix (which would lose the noise floor behind a strong target in fp32): bins are
     // cut into the threads' blocks of 16; QP[n] = sum of the block of n before n, AS[n] = sum of the block of n from n on
     // plus the W/16 - 1 blocks that follow.  A window [a, a + W) with W a multiple of 16 is AS[a] + QP[a + W]: additions
