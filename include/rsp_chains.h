@@ -32,7 +32,7 @@
 extern "C" {
 #endif
 
-#define RSP_ABI_VERSION 2
+#define RSP_ABI_VERSION 3
 
 typedef enum {
   RSP_OK = 0,
@@ -288,6 +288,29 @@ rsp_status rsp_gather_detections(rsp_chain *c, void *nccl_comm, const rsp_dets *
 rsp_status rsp_nccl_get_unique_id(uint8_t id[RSP_NCCL_UNIQUE_ID_BYTES]);                 /* ncclGetUniqueId, on one rank; ship it to the others */
 rsp_status rsp_nccl_comm_init_rank(void **comm, int n_ranks, const uint8_t id[RSP_NCCL_UNIQUE_ID_BYTES], int rank, int device);
 void rsp_nccl_comm_destroy(void *comm);
+
+/* ---- wire formats of the FPGA builds: host-side decoders, no device work ------------------------
+ * replaces: generators/jtag2mm (JtagController + JTAGToMasterAXI4, jtagToMaster.scala:32-123,525-590) as the way register writes reach
+ * the chain, and the AXI4StreamWidthAdapters around the UART of src/main/scala/RxFftCfarMagTxChain.scala:27-46.
+ * rsp_jtag_decode turns a GPIO capture (one byte per sample; TCK / TMS / TDI on the bits given by the masks, as
+ * generators/jtag2mm/src/test/python/gpio_for_jtag.py:27-52 writes them: 0x10 / 0x20 / 0x40) into the bus transactions the JTAG master
+ * issues: instructions 0x1 write, 0x2 address (upper half of the data register), 0x3 data, 0x4 read, 0x8 burst count, 0x9 burst write,
+ * 0xA burst index, 0xB burst data, 0xC burst read (README "User manual").  The caller applies them (memWriteWord(base + addr, data):
+ * rsp_reg_write / rsp_plfg_ram_write after its own address decode).  Returns RSP_ENOMEM with *n_ops = the number needed when ops_cap is
+ * too small.  rsp_uart_to_beats / rsp_beats_to_uart regroup a byte stream into stream beats and back (beats are native little-endian
+ * words in memory); msb_first selects which byte of a beat travels first -- the adapter's source is not in the reference tree, so this is
+ * the caller's statement about the capture (0 = least significant byte first). */
+typedef enum rsp_bus_kind { RSP_BUS_WRITE = 0, RSP_BUS_READ = 1 } rsp_bus_kind;
+typedef struct rsp_bus_op {
+  uint32_t kind;             /* rsp_bus_kind */
+  uint32_t addr;             /* addressValue (+ beatBytes per burst element): UInt((beatBytes * 4).W), jtagToMaster.scala:534 */
+  uint32_t data_lo, data_hi; /* the data word of a write (data_hi only with beatBytes = 8) */
+} rsp_bus_op;
+rsp_status rsp_jtag_decode(const uint8_t *samples, size_t n_samples, uint8_t tck_mask, uint8_t tms_mask, uint8_t tdi_mask,
+                           uint32_t ir_length, uint32_t beat_bytes, uint32_t burst_max, rsp_bus_op *ops, uint32_t ops_cap,
+                           uint32_t *n_ops);
+rsp_status rsp_uart_to_beats(const uint8_t *bytes, size_t n_bytes, uint32_t beat_bytes, int msb_first, void *beats, size_t *n_beats);
+rsp_status rsp_beats_to_uart(const void *beats, size_t n_beats, uint32_t beat_bytes, int msb_first, uint8_t *bytes);
 
 /* ---- introspection ------------------------------------------------------------------------------------------ */
 const char *rsp_status_str(rsp_status s);

@@ -25,6 +25,7 @@ EXPORTS = [
     "rsp_abi_version", "rsp_kernel_launches", "rsp_variant_name", "rsp_bytes_per_chirp",
     "rsp_fft_in_beat_bytes", "rsp_fft_out_beat_bytes", "rsp_fft_overflow_flags",
     "rsp_gather_detections", "rsp_nccl_get_unique_id", "rsp_nccl_comm_init_rank", "rsp_nccl_comm_destroy",
+    "rsp_jtag_decode", "rsp_uart_to_beats", "rsp_beats_to_uart",
 ]
 
 
@@ -37,6 +38,10 @@ class FftParams(C.Structure):
                      "fftDir", "runTime") + [("keepMSBorLSB", C.c_uint32)] + _i32s(
         "decimType", "sdfRadix") + [("expandLogic", C.c_uint32)] + _i32s("keepMSBorLSBReg", "fftDirReg", "windowFunc", "windowWidth") + [
         ("windowA0", C.c_double), ("windowA1", C.c_double), ("windowA2", C.c_double)] + _i32s("overflowReg", "windowRam")
+
+
+class BusOp(C.Structure):
+    _fields_ = [("kind", C.c_uint32), ("addr", C.c_uint32), ("data_lo", C.c_uint32), ("data_hi", C.c_uint32)]
 
 
 class MagParams(C.Structure):
@@ -131,6 +136,9 @@ def lib():
         L.rsp_nccl_comm_init_rank.argtypes = [C.POINTER(vp), i32, C.c_char_p, i32, i32]
         L.rsp_nccl_comm_destroy.argtypes = [vp]
         L.rsp_nccl_comm_destroy.restype = None
+        L.rsp_jtag_decode.argtypes = [C.c_char_p, C.c_size_t, C.c_uint8, C.c_uint8, C.c_uint8, u32, u32, u32, C.POINTER(BusOp), u32, C.POINTER(u32)]
+        L.rsp_uart_to_beats.argtypes = [C.c_char_p, C.c_size_t, u32, i32, vp, C.POINTER(C.c_size_t)]
+        L.rsp_beats_to_uart.argtypes = [vp, C.c_size_t, u32, i32, vp]
         _lib = L
     return _lib
 

@@ -31,7 +31,7 @@ def test_library_exports_every_declared_symbol():
     for s in syms:
         assert hasattr(lib, s), f"librsp_b200.so lacks {s}"
     assert sorted(_abi.EXPORTS) == syms
-    assert lib.rsp_abi_version() == 2
+    assert lib.rsp_abi_version() == 3
     assert lib.rsp_status_str(1) == b"RSP_EINVAL"
 
 
