@@ -289,6 +289,18 @@ rsp_status rsp_nccl_get_unique_id(uint8_t id[RSP_NCCL_UNIQUE_ID_BYTES]);        
 rsp_status rsp_nccl_comm_init_rank(void **comm, int n_ranks, const uint8_t id[RSP_NCCL_UNIQUE_ID_BYTES], int rank, int device);
 void rsp_nccl_comm_destroy(void *comm);
 
+/* ---- slow-time (Doppler) dimension, SURVEY 8(f)2 -----------------------------------------------------------------
+ * replaces: nothing in the reference -- its chains stop at the 1-D range CFAR.  The reference's own blocks run along slow time as a
+ * second handle whose FFT has numPoints = chirps per frame (rsp_fft_run / rsp_cfar_run on Doppler-major rows); these two calls are the
+ * data movements in between, asynchronous on `stream` like every other call.
+ * rsp_corner_turn: d_out[b][c][r] = d_in[b][r][c] for b < batch, r < n_rows, c < n_cols, elements of 2, 4 or 8 bytes; out of place.
+ * rsp_mag_combine_run: non-coherent RX combining.  d_in holds n_rx maps of n_beats beats each, one after the other; every beat goes
+ * through the handle's LogMagMux (selector 1, 2 or 3) and d_out[i] = (sum over rx of the magnitudes of beat i) >> log2(n_rx), as one
+ * LogMagMux output beat Cat(0, value) (fp32: the mean as a float).  n_rx is a power of two. */
+rsp_status rsp_corner_turn(rsp_chain *c, const void *d_in, void *d_out, uint32_t n_rows, uint32_t n_cols, uint32_t batch,
+                           uint32_t elem_bytes, void *stream);
+rsp_status rsp_mag_combine_run(rsp_chain *c, const void *d_in, uint64_t n_beats, uint32_t n_rx, void *d_out, void *stream);
+
 /* ---- wire formats of the FPGA builds: host-side decoders, no device work ------------------------
  * replaces: generators/jtag2mm (JtagController + JTAGToMasterAXI4, jtagToMaster.scala:32-123,525-590) as the way register writes reach
  * the chain, and the AXI4StreamWidthAdapters around the UART of src/main/scala/RxFftCfarMagTxChain.scala:27-46.

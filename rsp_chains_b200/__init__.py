@@ -8,6 +8,7 @@ from .params import (AddressSet, CACFARType, CFARParams, Convergent, DIFDecimTyp
                      FftMagCfarVanillaParameters, FixedNCOParams, FixedPLFGParams, FixedPoint, GOSCACFARType, GOSCFARType, OSGoldenCFARType,
                      MAGParams, RoundDown, RoundHalfUp, RspChainVanillaParameters, WindowFunctionType, WindowFunctionTypes, fft_mag_cfar_chain_vanilla_app_params,
                      log2Up, rsp_chain_vanilla_app_params)
+from .doppler import RangeDopplerChain
 from .wire import BusOp, JtagReplay, RxFftMagCfarTxChain, beats_to_uart, jtag_decode, uart_to_beats
 
 __all__ = [n for n in dir() if not n.startswith("_")]

@@ -195,6 +195,18 @@ class _Chain:
                                           C.byref(d) if d is not None else None, _stream_ptr(stream)))
         return out
 
+    # ---- slow-time dimension (not in the reference)
+    def corner_turn(self, d_in, n_rows: int, n_cols: int, out, batch: int = 1, stream=None):
+        """out[b][c][r] = d_in[b][r][c] (rsp_corner_turn); element size from the tensor (2, 4 or 8 bytes; float32 [..., 2] counts as 8)"""
+        eb = d_in.element_size() * (2 if (d_in.dim() and d_in.shape[-1] == 2 and d_in.is_floating_point()) else 1)
+        _abi.check(self._lib.rsp_corner_turn(self._h, d_in.data_ptr(), out.data_ptr(), n_rows, n_cols, batch, eb, _stream_ptr(stream)))
+        return out
+
+    def mag_combine(self, d_in, n_beats: int, n_rx: int, out, stream=None):
+        """LogMagMux of n_rx maps + their mean (rsp_mag_combine_run): non-coherent RX combining"""
+        _abi.check(self._lib.rsp_mag_combine_run(self._h, d_in.data_ptr(), n_beats, n_rx, out.data_ptr(), _stream_ptr(stream)))
+        return out
+
     # ---- stream: host buffers (numpy), the call a reference tester makes
     def run_host(self, h_in: np.ndarray, n_chirps: int, n_rx: int = 1, out: Optional[np.ndarray] = None,
                  peak_mask: Optional[np.ndarray] = None, max_dets: int = 0):

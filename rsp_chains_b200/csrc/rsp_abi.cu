@@ -13,6 +13,7 @@
 #include "rsp_host.hpp"
 #include "rsp_launch.hpp"
 #include "rsp_fast.cuh"
+#include "rsp_doppler.cuh"
 
 using namespace rsp;
 
@@ -512,6 +513,63 @@ extern "C" rsp_status rsp_mag_run(rsp_chain *c, const void *d_in, uint64_t n_bea
     if (s != RSP_OK) return fail(s, err);
     a.in = static_cast<const F2 *>(d_in); a.out = static_cast<float *>(d_out);
     mag_f32_kernel<<<ew_grid(c, n_beats), 256, 0, st>>>(a, n_beats);
+  }
+  CUDA_TRY(cudaGetLastError());
+  ++c->launches;
+  return RSP_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// slow-time dimension (kernels in rsp_doppler.cuh)
+template <typename T, int TILE>
+static void launch_corner_turn(const rsp_chain *c, const void *d_in, void *d_out, uint32_t n_rows, uint32_t n_cols, uint32_t batch, cudaStream_t st) {
+  const uint32_t tr = (n_rows + TILE - 1) / TILE, tc = (n_cols + TILE - 1) / TILE;
+  const unsigned long long n_tiles = (unsigned long long)tr * tc * batch;
+  const unsigned grid = (unsigned)std::max<unsigned long long>(1, std::min<unsigned long long>(n_tiles, (unsigned long long)c->sm_count * 8));
+  corner_turn_kernel<T, TILE><<<grid, 256, 0, st>>>(static_cast<const T *>(d_in), static_cast<T *>(d_out), n_rows, n_cols, tr, tc, n_tiles);
+}
+
+extern "C" rsp_status rsp_corner_turn(rsp_chain *c, const void *d_in, void *d_out, uint32_t n_rows, uint32_t n_cols, uint32_t batch,
+                                      uint32_t elem_bytes, void *stream) {
+  if (!c || !d_in || !d_out) return fail(RSP_EINVAL, "null argument");
+  if (d_in == d_out) return fail(RSP_EINVAL, "rsp_corner_turn is out of place");
+  if (elem_bytes != 2 && elem_bytes != 4 && elem_bytes != 8) return fail(RSP_EINVAL, "rsp_corner_turn: elem_bytes must be 2, 4 or 8");
+  RSP_ON_DEVICE(c);
+  if (n_rows == 0 || n_cols == 0 || batch == 0) return RSP_OK;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (elem_bytes == 2) launch_corner_turn<uint16_t, 64>(c, d_in, d_out, n_rows, n_cols, batch, st);
+  else if (elem_bytes == 4) launch_corner_turn<uint32_t, 32>(c, d_in, d_out, n_rows, n_cols, batch, st);
+  else launch_corner_turn<unsigned long long, 32>(c, d_in, d_out, n_rows, n_cols, batch, st);
+  CUDA_TRY(cudaGetLastError());
+  ++c->launches;
+  return RSP_OK;
+}
+
+extern "C" rsp_status rsp_mag_combine_run(rsp_chain *c, const void *d_in, uint64_t n_beats, uint32_t n_rx, void *d_out, void *stream) {
+  if (!c || !d_in || !d_out) return fail(RSP_EINVAL, "null argument");
+  if (n_rx == 0 || (n_rx & (n_rx - 1)) || n_rx > 64) return fail(RSP_EINVAL, "rsp_mag_combine_run: n_rx must be a power of two <= 64 (the mean is a shift)");
+  RSP_ON_DEVICE(c);
+  if (n_beats == 0) return RSP_OK;
+  std::string err;
+  Plan pl;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  int shift = 0;
+  while ((1u << shift) < n_rx) ++shift;
+  if (c->p.arith == RSP_ARITH_FIXED) {
+    FxArgs a;
+    const rsp_status s = plan_fixed(c->p, c->r, c->t, STAGE_MAG, STAGE_MAG, a, pl, err);
+    if (s != RSP_OK) return fail(s, err);
+    if (a.sel == 0) return fail(RSP_EINVAL, "rsp_mag_combine_run: the magnitude selector is 0 (bypass): there is no magnitude to combine");
+    bind_fixed(c, a);
+    a.in = static_cast<const uint32_t *>(d_in); a.out = static_cast<uint32_t *>(d_out);
+    mag_combine_fixed_kernel<<<ew_grid(c, n_beats), 256, 0, st>>>(a, n_beats, n_rx, shift);
+  } else {
+    F32Args a;
+    const rsp_status s = plan_f32(c->p, c->r, c->t, STAGE_MAG, STAGE_MAG, a, pl, err);
+    if (s != RSP_OK) return fail(s, err);
+    if (a.sel == 0) return fail(RSP_EINVAL, "rsp_mag_combine_run: the magnitude selector is 0 (bypass): there is no magnitude to combine");
+    a.in = static_cast<const F2 *>(d_in); a.out = static_cast<float *>(d_out);
+    mag_combine_f32_kernel<<<ew_grid(c, n_beats), 256, 0, st>>>(a, n_beats, n_rx, 1.0f / (float)n_rx);
   }
   CUDA_TRY(cudaGetLastError());
   ++c->launches;
