@@ -276,7 +276,42 @@ def config_lines(torch, peak):
     case("C4 OS-CFAR 1024 x 4096 fixed, reading (B): golden cfarOS, 32 + 32 cells in one sorted window, ascending index 48", fixed_params(4096, 64, 4, R.OSGoldenCFARType), 12, os_b, 1024, 1, 1,
          note="CFARUtils.scala:159-196 (no hardware core in the reference); run-time-parameter kernel, bitwise rank search")
     out.extend(generator_lines(torch, peak))
+    out.extend(doppler_lines(torch, peak))
     return out
+
+
+def doppler_lines(torch, peak, n_rx=8, m=1024, n=4096):
+    """SURVEY 8(f)2 (not in the reference): one frame of n_rx x m chirps x n samples through RangeDopplerChain, and its corner turn alone"""
+    import rsp_chains_b200 as R
+    from rsp_chains_b200 import synth
+    W, G = 16, 2
+    regs = dict(fftWin=m, thresholdScaler=5, logOrLinearMode=1, divSum=4, peakGrouping=0, cfarMode=0, windowCells=W, guardCells=G)
+    base = torch.from_numpy(synth.chirps_fixed(64, n, seed=3).view(np.int32)).cuda()
+    d_in = base.repeat(n_rx * m // 64, 1).view(n_rx, m, n).contiguous()
+    d_out = torch.empty((n, m), dtype=torch.int32, device="cuda")
+    lines = []
+    with R.RangeDopplerChain(fixed_params(n, W, G), fixed_params(m, W, G), n_rx) as rd:
+        rd.range.configure(n.bit_length() - 1, 2, dict(regs, fftWin=n))
+        rd.doppler.configure(m.bit_length() - 1, 2, regs)
+        l0 = rd.kernel_launches
+        ms = _timed(torch, lambda: rd.run(d_in, out=d_out))
+        launches = (rd.kernel_launches - l0)
+        a, b = torch.empty_like(d_in), torch.empty_like(d_in)
+        ms_t = _timed(torch, lambda: rd.range.corner_turn(d_in, m, n, a, batch=n_rx))
+        ms_f = _timed(torch, lambda: rd.range.fft(d_in, n_rx * m, b))
+    cells = n_rx * m * n
+    bps = 8.0 + 8.0 + 8.0 + (4.0 + 4.0 / n_rx) + 8.0 / n_rx          # range FFT, corner turn, Doppler FFT, LogMagMux + RX mean, CFAR
+    gbs = cells * bps / (ms * 1e-3) / 1e9
+    lines.append({"config": f"range-Doppler frame {n_rx} RX x {m} chirps x {n} samples, fixed, CFAR along Doppler", "variant": "RangeDopplerChain (5 launches)",
+                  "rows": n_rx * m, "n": n, "ms": round(ms, 4), "Msamples_per_s": round(cells / ms / 1e3, 1), "GBps_algorithmic": round(gbs, 1),
+                  "frac": round(gbs / peak, 4), "bytes_per_sample": round(bps, 3), "footprint_MiB": round(cells * 4 / 2 ** 20, 1),
+                  "note": "SURVEY 8(f)2, not in the reference: the reference's FFT / LogMagMux / CFAR blocks run a second time along slow time; "
+                          "every stage crosses HBM (no fusion across the corner turn)"})
+    for name, t, b_ in (("corner turn alone (rsp_corner_turn, 4-byte beats)", ms_t, 8.0), ("range FFT block alone (rsp_fft_run)", ms_f, 8.0)):
+        g = cells * b_ / (t * 1e-3) / 1e9
+        lines.append({"config": f"{name}, {n_rx} x {m} x {n}", "variant": name.split(" (")[0], "rows": n_rx * m, "n": n, "ms": round(t, 4),
+                      "Msamples_per_s": round(cells / t / 1e3, 1), "GBps_algorithmic": round(g, 1), "frac": round(g / peak, 4), "bytes_per_sample": b_})
+    return lines
 
 
 def generator_lines(torch, peak, rows=65536):
