@@ -177,6 +177,7 @@ static rsp_status launch_fixed(rsp_chain *c, const Plan &pl, const FxArgs &a, cu
   const LaunchCtx ctx = {c->device, c->sm_count};
   const char *err = "";
   const rsp_status s = fast_chain_supported(pl, a) ? launch_fast_chain(pl, ctx, a, st, &err)
+                       : fast_fft_supported(pl, a) ? launch_fast_fft(pl, ctx, a, st, &err)
                                                    : launch_fixed_inst(pl.mode, pl.S, ctx, a, st, &err);
   if (s != RSP_OK) return fail(s, err);
   ++c->launches;

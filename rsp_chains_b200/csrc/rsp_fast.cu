@@ -209,7 +209,9 @@ __device__ __forceinline__ int fjpl(int re, int im) {
 // consecutive words in every pass.  fast_group is ONE group (g is a compile-time value after unrolling).
 // WRAP = false: the row was found "quiet" (see quiet_beats): no value of the transform can reach +-32768, so the 16-bit wrap
 // of the butterfly differences is the identity and its PRMT is left out (13% of the ALU-pipe instructions of the kernel).
-template <int S, int LP, int K, bool WRAP, bool TWSM = false>
+// FFTO (the FFT block alone, fft_fixed_fast_kernel): the last pass ends like the others -- true signs -- and leaves the packed output
+// beats Cat(re16, im16) in `mags` instead of the magnitudes.
+template <int S, int LP, int K, bool WRAP, bool TWSM = false, bool FFTO = false>
 __device__ __forceinline__ void fast_group(const FastArgs &a, int tl, int g, const uint32_t (&pre)[16], uint32_t *xb, int (&mags)[1 << LP],
                                            const int2 *tws = nullptr) {
   using Gm = FGeo<S, LP>;
@@ -253,7 +255,7 @@ __device__ __forceinline__ void fast_group(const FastArgs &a, int tl, int g, con
     const int dist = 1 << (m - 1 - s);
     const bool rot = (i != S - 1) && ((i & 1) == 0);   // x(-j) on the last quarter of each 4D block follows (SDFChainRadix22.scala:319-337)
     const bool wrap = WRAP && !(last && s == m - 1);    // the magnitude only takes |d| (|wrap16(32768)| == 32768)
-    const bool true_stage = RSP_FAST_TRUE_LAST && !last && s == m - 1;   // the outputs go to the exchange buffer: true signs, raw products
+    const bool true_stage = RSP_FAST_TRUE_LAST && (!last || FFTO) && s == m - 1;   // the outputs leave the registers: true signs, raw products
     static_assert(last || (((i0 + m - 1) & 1) == 1), "a pass that is not the last ends on an odd stage (no rotation pending)");
 #pragma unroll
     for (int rr = 0; rr < R; ++rr)
@@ -291,13 +293,15 @@ __device__ __forceinline__ void fast_group(const FastArgs &a, int tl, int g, con
       }
     }
   }
-  if (!last) {   // the exchange buffer holds true values: un-negate what is still held negated
+  if (!last || FFTO) {   // the exchange buffer (the output) holds true values: un-negate what is still held negated
 #pragma unroll
     for (int rr = 0; rr < R; ++rr)
       if (sg[rr] < 0) { re[rr] = fadd(-1, re[rr], 1, 0, a.one, a.m1); im[rr] = fadd(-1, im[rr], 1, 0, a.one, a.m1); }
 #pragma unroll
-    for (int rr = 0; rr < R; ++rr)
-      xf[go + fidx<S>(rr * Dl)] = raw[rr] ? __byte_perm((uint32_t)im[rr], (uint32_t)re[rr], 0x7632) : pack2(re[rr], im[rr]);
+    for (int rr = 0; rr < R; ++rr) {
+      const uint32_t wd = raw[rr] ? __byte_perm((uint32_t)im[rr], (uint32_t)re[rr], 0x7632) : pack2(re[rr], im[rr]);
+      if (last) mags[g * R + rr] = (int)wd; else xf[go + fidx<S>(rr * Dl)] = wd;
+    }
   } else {
 #pragma unroll
     for (int rr = 0; rr < R; ++rr) mags[g * R + rr] = fjpl(re[rr], im[rr]);
@@ -331,8 +335,9 @@ __device__ __forceinline__ void fast_scatter(int tl, const int (&mags)[1 << LP],
 }
 
 // a whole pass whose groups need no beats from global memory (every pass but the first, and the first one with 16 points per thread)
-template <int S, int LP, int K, bool WRAP, bool TWSM = false>
-__device__ __forceinline__ void fast_pass(const FastArgs &a, int tl, const uint32_t (&pre)[16], uint32_t *xb, uint32_t *xm, const int2 *tws = nullptr) {
+template <int S, int LP, int K, bool WRAP, bool TWSM = false, bool FFTO = false>
+__device__ __forceinline__ void fast_pass(const FastArgs &a, int tl, const uint32_t (&pre)[16], uint32_t *xb, uint32_t *xm, const int2 *tws = nullptr,
+                                          int *wout = nullptr) {
   constexpr int m = fx_pass_size(S, K), G = (1 << LP) >> m;
   constexpr bool last = (K == fx_n_passes(S) - 1);
   static_assert(K > 0 || G == 1, "first pass with several groups: fast_first_pass_groups");
@@ -342,13 +347,18 @@ __device__ __forceinline__ void fast_pass(const FastArgs &a, int tl, const uint3
 #pragma unroll
   for (int gi = 0; gi < G; ++gi) {
     const int g = !last ? gi : (G == 8 ? ((gi & 1) << 2 | (gi & 2) | (gi >> 2)) : (G == 4 ? ((gi & 1) << 1 | (gi >> 1)) : gi));
-    fast_group<S, LP, K, WRAP, TWSM>(a, tl, g, pre, xb, mags, tws);
+    fast_group<S, LP, K, WRAP, TWSM, FFTO>(a, tl, g, pre, xb, mags, tws);
     // keep the next group's shared-memory loads behind this group's stores: hoisted, 32 points are live and the 64-register
     // budget spills (the other warps of the SM hide the load latency, not this thread's next group)
     // (ptxas moves shared-memory accesses with distinct immediate offsets across a compiler-level fence; WARPSYNC holds them)
     if (!last && gi + 1 < G) __syncwarp();
   }
-  if (last) fast_scatter<S, LP>(tl, mags, xm);
+  if (last) {
+    if (FFTO) {   // the output beats stay in registers: the exchange buffer they go to is still being read by the other threads' last pass
+#pragma unroll
+      for (int e = 0; e < (1 << LP); ++e) wout[e] = mags[e];
+    } else fast_scatter<S, LP>(tl, mags, xm);
+  }
 }
 
 // Beats j = 0 .. 15 of group g of the thread, p = tl + (j * G + g) * TPC (warp-contiguous 128-byte lines), times the window when
@@ -417,18 +427,20 @@ __device__ __forceinline__ bool quiet_beats(const uint32_t (&pre)[16]) {
 // The first pass works on the thread's own beats, so each warp decides for itself (per group of 16 beats); the later passes mix
 // the whole chirp and decide by the chirp's flag, which every warp of the chirp has or-ed into before the barrier that ends the
 // first pass.
-template <int S, int LP, int K>
-__device__ __forceinline__ void fast_passes_from(const FastArgs &a, int c, int tl, bool quiet, const uint32_t (&pre)[16], uint32_t *xb, uint32_t *xm) {
-  if (quiet) fast_pass<S, LP, K, false>(a, tl, pre, xb, xm); else fast_pass<S, LP, K, true>(a, tl, pre, xb, xm);
+template <int S, int LP, int K, bool FFTO = false>
+__device__ __forceinline__ void fast_passes_from(const FastArgs &a, int c, int tl, bool quiet, const uint32_t (&pre)[16], uint32_t *xb, uint32_t *xm,
+                                                 int *wout = nullptr) {
+  if (quiet) fast_pass<S, LP, K, false, false, FFTO>(a, tl, pre, xb, xm, nullptr, wout);
+  else fast_pass<S, LP, K, true, false, FFTO>(a, tl, pre, xb, xm, nullptr, wout);
   chirp_sync<S>(c);
-  if constexpr (K + 1 < fx_n_passes(S)) fast_passes_from<S, LP, K + 1>(a, c, tl, quiet, pre, xb, xm);
+  if constexpr (K + 1 < fx_n_passes(S)) fast_passes_from<S, LP, K + 1, FFTO>(a, c, tl, quiet, pre, xb, xm, wout);
 }
 
 // pre: the thread's 16 beats (LP = 4; loaded or staged by the caller).  grow: the row in global memory (LP = 5: each of the two
 // groups of the first pass loads its own 16 beats, so that no more than one group's beats are live at a time).
-template <int S, int LP, bool TWSM = false>
+template <int S, int LP, bool TWSM = false, bool FFTO = false>
 __device__ __forceinline__ void fast_passes(const FastArgs &a, int c, int tl, uint32_t (&pre)[16], const uint32_t *grow, const GenRow &gr, uint32_t *xb,
-                                            uint32_t *xm, int *loud, const int2 *tws = nullptr) {
+                                            uint32_t *xm, int *loud, const int2 *tws = nullptr, int *wout = nullptr) {
   static_assert(fx_pass_size(S, 0) == 4, "the first pass works on groups of 16 beats");
   constexpr int G0 = (1 << LP) / 16;
   if constexpr (G0 == 1) {
@@ -450,7 +462,7 @@ __device__ __forceinline__ void fast_passes(const FastArgs &a, int c, int tl, ui
   chirp_sync<S>(c);
   if constexpr (fx_n_passes(S) > 1) {
     const bool quiet = loud[c] == 0;
-    fast_passes_from<S, LP, 1>(a, c, tl, quiet, pre, xb, xm);     // ends with a barrier: every thread has read the flag
+    fast_passes_from<S, LP, 1, FFTO>(a, c, tl, quiet, pre, xb, xm, wout);     // ends with a barrier: every thread has read the flag
     if (tl == 0) loud[c] = 0;                                 // next written before the first barrier of the next row
   }
 }
@@ -674,6 +686,69 @@ __global__ void __launch_bounds__(FGeo<S, LP>::THREADS, fast_min_blocks<S, LP>()
       fast_detections<S, LP, CMODE, LINEAR>(da, tl, mask, P, X);
     }
     if (stage) cp_async_wait_all();   // this thread's copies have landed; the barrier publishes everybody's
+    chirp_sync<S>(c);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// The FFT block alone (AXI4FFTBlock, rsp_fft_run) on the fast passes: same transform, the bit-reversed output beats Cat(re16, im16)
+// instead of the magnitudes.  The beats are scattered into the row's shared memory (the exchange buffer is dead after the last pass; its
+// words and the magnitude array behind it are one region here) at wx(bin) and leave in natural order, one warp-contiguous line per store.
+// A lane's run of G = 2^(LP - m) neighbouring bins starts at rev_m(rr) << (S - m) | rev_{S-LP}(tl) << (LP - m): the lanes of a warp differ in
+// rev5(lane) << (S - m - 5), all in one bank without padding.  wx pads by one store width per 2^sh words with sh chosen per size so that
+// the 8 (128-bit), 16 (64-bit) or 32 (32-bit stores) lanes of a store phase fall into distinct banks (tests/test_kernel_layout.py).
+template <int S> __host__ __device__ constexpr int wx(int n) {
+  return S == 10 ? n + ((n >> 5) << 2) : S == 11 ? n + ((n >> 4) << 1) : S == 12 ? n + (n >> 3) : S == 13 ? n + ((n >> 6) << 1) : n + ((n >> 9) << 2);
+}
+template <int S, int LP>
+__device__ __forceinline__ void fast_scatter_words(int tl, const int (&w)[1 << LP], uint32_t *xw) {
+  constexpr int K = fx_n_passes(S) - 1, m = fx_pass_size(S, K), R = 1 << m, G = (1 << LP) >> m;
+  const uint32_t rtl = (__brev((uint32_t)tl) >> (32 - (S - LP))) << (LP - m);
+  uint32_t *base = xw + wx<S>((int)rtl);
+#pragma unroll
+  for (int rr = 0; rr < R; ++rr) {
+    const uint32_t rrr = (__brev((uint32_t)rr) >> (32 - m)) << (S - m);   // compile-time; wx is additive over rrr | rtl
+    uint32_t *dst = base + wx<S>((int)rrr);
+    auto at = [&](int e) { return (uint32_t)w[(int)(__brev((uint32_t)e) >> (32 - (LP - m))) * R + rr]; };   // bin e of the run <- group rev(e)
+    if constexpr (G == 8) {
+      *reinterpret_cast<uint4 *>(dst) = make_uint4(at(0), at(1), at(2), at(3));
+      *reinterpret_cast<uint4 *>(dst + 4) = make_uint4(at(4), at(5), at(6), at(7));
+    } else if constexpr (G == 4) *reinterpret_cast<uint4 *>(dst) = make_uint4(at(0), at(1), at(2), at(3));
+    else if constexpr (G == 2) *reinterpret_cast<uint2 *>(dst) = make_uint2(at(0), at(1));
+    else *dst = (uint32_t)w[rr];
+  }
+}
+
+template <int S, int LP>
+__global__ void __launch_bounds__(FGeo<S, LP>::THREADS, fast_min_blocks<S, LP>()) fft_fixed_fast_kernel(const FastArgs a) {
+  using Gm = FGeo<S, LP>;
+  constexpr int N = Gm::N, TPC = Gm::TPC, CPC = Gm::CPC, PTS = Gm::PTS;
+  static_assert(wx<S>(N - 1) < Gm::ROW, "the padded output row fits the chirp's shared memory");
+  extern __shared__ __align__(16) uint32_t smem[];
+  __shared__ int loud[CPC];
+  if (threadIdx.x < CPC) loud[threadIdx.x] = 0;
+  __syncthreads();
+  const int c = threadIdx.x / TPC, tl = threadIdx.x % TPC;
+  uint32_t *xb = smem + (size_t)c * Gm::ROW, *xm = xb + Gm::XB;
+  const uint32_t *xo = xb + wx<S>(tl);
+  const uint32_t stride = gridDim.x * CPC;
+  const GenRow gr = {0u, 0u};
+  for (uint32_t row0 = blockIdx.x * CPC; row0 < a.n_rows; row0 += stride) {
+    const uint32_t row = row0 + c < a.n_rows ? row0 + c : a.n_rows - 1;   // a chirp slot past the last row recomputes the last row
+    const uint32_t *grow = a.in + (size_t)row * N;
+    uint32_t pre[16];
+    if (LP == 4) load_beats<S, LP>(a, grow, gr, tl, 0, pre);
+    int w[PTS];
+    fast_passes<S, LP, false, true>(a, c, tl, pre, grow, gr, xb, xm, loud, nullptr, w);   // ends with a barrier: the exchange buffer is free
+    if (a.l2_prefetch && tl == 0 && row0 + stride + c < a.n_rows) {
+      const uint32_t *nxt = a.in + (size_t)(row0 + stride + c) * N;
+      asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" :: "l"(nxt), "r"(4 * N) : "memory");
+    }
+    fast_scatter_words<S, LP>(tl, w, xb);
+    chirp_sync<S>(c);
+    uint32_t *gout = a.out + (size_t)row * N + tl;
+#pragma unroll
+    for (int j = 0; j < PTS; ++j) gout[j * TPC] = xo[wx<S>(j * TPC)];
     chirp_sync<S>(c);
   }
 }
@@ -1025,6 +1100,21 @@ static rsp_status launch_fast_gos(const LaunchCtx &c, const FastArgs &fa, const 
   return RSP_OK;
 }
 
+template <int S, int LP>
+static rsp_status launch_fast_fft_lp(const LaunchCtx &c, const FastArgs &fa, cudaStream_t st, const char **err) {
+  using Gm = FGeo<S, LP>;
+  static int occ_dev[64] = {0};
+  int &occ = occ_dev[c.device & 63];
+  const size_t smem = (size_t)Gm::CPC * Gm::ROW * sizeof(uint32_t);
+  auto kernel = fft_fixed_fast_kernel<S, LP>;
+  if (!occ) { const rsp_status s = launch_cfg(kernel, smem, Gm::THREADS, &occ, err); if (s != RSP_OK) return s; }
+  const unsigned groups = (fa.n_rows + Gm::CPC - 1) / Gm::CPC;
+  const unsigned grid = std::max(1u, std::min(groups, (unsigned)(c.sm_count * occ)));
+  kernel<<<grid, Gm::THREADS, smem, st>>>(fa);
+  if (cudaGetLastError() != cudaSuccess) { *err = "fft_fixed_fast_kernel launch failed"; return RSP_ECUDA; }
+  return RSP_OK;
+}
+
 // one transform size per compile unit
 #define RSP_CAT2(a, b) a##b
 #define RSP_CAT(a, b) RSP_CAT2(a, b)
@@ -1038,10 +1128,46 @@ rsp_status RSP_CAT(launch_fast_size_, RSP_FAST_S)(int core, int cmode, bool line
   return launch_fast_modes<S, 1>(cmode, linear, ctx, fa, st, err);
 }
 
+rsp_status RSP_CAT(launch_fast_fft_size_, RSP_FAST_S)(const LaunchCtx &ctx, const FastArgs &fa, cudaStream_t st, const char **err) {
+  constexpr int S = RSP_FAST_S;
+  if constexpr (S == 14) { if (fast_lp_runtime(S) == 5) return launch_fast_fft_lp<S, 5>(ctx, fa, st, err); }
+  return launch_fast_fft_lp<S, 4>(ctx, fa, st, err);
+}
+
 #if RSP_FAST_S == 10
-#define RSP_DECL_FAST(s) rsp_status launch_fast_size_##s(int, int, bool, int, const LaunchCtx &, const FastArgs &, const GosArgs &, cudaStream_t, const char **)
+#define RSP_DECL_FAST(s) rsp_status launch_fast_size_##s(int, int, bool, int, const LaunchCtx &, const FastArgs &, const GosArgs &, cudaStream_t, const char **); \
+                         rsp_status launch_fast_fft_size_##s(const LaunchCtx &, const FastArgs &, cudaStream_t, const char **)
 RSP_DECL_FAST(11); RSP_DECL_FAST(12); RSP_DECL_FAST(13); RSP_DECL_FAST(14);
 #undef RSP_DECL_FAST
+
+// the FFT block alone on the fast passes: the configuration of the fast chain's transform (16-bit data and twiddles, binPoint 0, RoundHalfUp,
+// every stage scaled, forward, natural output order), any window
+bool fast_fft_supported(const Plan &pl, const FxArgs &a) {
+  if (pl.mode != MODE_FAST || pl.first_stage != STAGE_FFT || pl.last_stage != STAGE_FFT) return false;
+  if (pl.S < RSP_FAST_SMIN || pl.S > RSP_FAST_SMAX) return false;
+  static int on = -1;
+  if (on < 0) { const char *e = std::getenv("RSP_FAST_FFT"); on = (e != nullptr && e[0] == '0') ? 0 : 1; }   // A/B knob
+  return on && a.bp == 0 && a.tw_bp == 14 && a.bitrev && a.out != nullptr && a.in != nullptr;
+}
+
+rsp_status launch_fast_fft(const Plan &pl, const LaunchCtx &ctx, const FxArgs &a, cudaStream_t st, const char **err) {
+  FastArgs fa = {};
+  fa.in = a.in; fa.out = a.out; fa.n_rows = a.n_rows; fa.row_base = a.row_base;
+  fa.tw = reinterpret_cast<const int2 *>(a.tw2);
+  fa.win4 = a.win_on ? a.win4 : nullptr;
+  for (int L = 0; L < 16; ++L) fa.tw_off[L] = a.tw_off[L];
+  fa.one = 1; fa.m1 = -1; fa.rnd[0] = 0x8000; fa.rnd[1] = -0x8000; fa.rnd[2] = 0x7FFF; fa.rnd[3] = -0x7FFF;
+  { static int l2p = -1; if (l2p < 0) { const char *e = std::getenv("RSP_FAST_L2_PREFETCH"); l2p = e ? std::atoi(e) : 1; }
+    fa.l2_prefetch = (l2p != 0 && (reinterpret_cast<uintptr_t>(a.in) & 15u) == 0) ? 1 : 0; }
+  switch (pl.S) {
+  case 10: return launch_fast_fft_size_10(ctx, fa, st, err);
+  case 11: return launch_fast_fft_size_11(ctx, fa, st, err);
+  case 12: return launch_fast_fft_size_12(ctx, fa, st, err);
+  case 13: return launch_fast_fft_size_13(ctx, fa, st, err);
+  case 14: return launch_fast_fft_size_14(ctx, fa, st, err);
+  default: *err = "no fast variant for this size"; return RSP_EUNSUPPORTED;
+  }
+}
 
 static bool fast_gos_supported(const FxArgs &a) {
   if (a.core != CORE_LIS || a.cfar_algorithm != 1) return false;

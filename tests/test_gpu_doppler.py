@@ -114,3 +114,44 @@ def test_mag_combine_fp32_and_argument_checks(cuda, oracle):
         ch.memWriteWord(ch.params.magAddress.base, 0)
         assert _abi.lib().rsp_mag_combine_run(ch._h, d_in.data_ptr(), 5 * n, 4, d_out.data_ptr(), None) == _abi.RSP_EINVAL
         assert "bypass" in _abi.lib().rsp_last_error().decode()
+
+
+@pytest.mark.parametrize("log_n", [10, 11, 12, 13, 14])
+def test_fft_block_alone_on_the_fast_passes(cuda, oracle, log_n):
+    """rsp_fft_run in the fast chain's FFT configuration runs fft_fixed_fast_kernel<S> (the fast passes + a bit-reversed scatter of the
+    output beats): quiet rows, full-scale random rows (every wrap, the -32768 corners), a DC row at full scale, ragged row counts
+    (two chirps per CTA at N = 1024), a window; bit for bit against the oracle and against the run-time-parameter kernel."""
+    import os
+    n = 1 << log_n
+    rows = 13 if log_n <= 12 else 5
+    beats = np.concatenate([synth.chirps_fixed(rows - 4, n, seed=40 + log_n), synth.random_beats(3, n, seed=60 + log_n),
+                            np.full((1, n), 0x7FFF8000, dtype=np.uint32)])
+    p = chain_params(n, 0, W=16, G=2)
+    regs = dict(fftWin=n, thresholdScaler=4, logOrLinearMode=1, divSum=4, peakGrouping=0, cfarMode=0, windowCells=16, guardCells=2)
+    fft, _, _ = oracle_cfgs(oracle, p, log_n, 2, regs)
+    want = oracle.fft_fixed_words(fft, beats)
+    with R.FftMagCfarChainVanilla(p) as ch:
+        configure(ch, log_n, 2, regs)
+        d_in = to_dev(cuda, beats)
+        d_out = cuda.zeros_like(d_in)
+        ch.fft(d_in, beats.shape[0], d_out)
+        cuda.cuda.synchronize()
+        assert (from_dev_u32(d_out) == want).all()
+        for k in (1, 2, 3):      # ragged counts
+            d_out.zero_()
+            ch.fft(d_in, k, d_out)
+            cuda.cuda.synchronize()
+            got = from_dev_u32(d_out)
+            assert (got[:k] == want[:k]).all() and not got[k:].any()
+    # with a window (the product multiplies, the oracle gets the windowed beats)
+    from oracle.glue import apply_window
+    from rsp_chains_b200.params import WindowFunctionTypes as WT
+    pw = chain_params(n, 0, W=16, G=2)
+    pw.fftParams.windowFunc = WT.Hamming(16, 0.54, 0.46)
+    want_w = oracle.fft_fixed_words(fft, apply_window(oracle, pw, beats))
+    with R.FftMagCfarChainVanilla(pw) as ch:
+        configure(ch, log_n, 2, regs)
+        d_out = cuda.zeros_like(d_in)
+        ch.fft(d_in, beats.shape[0], d_out)
+        cuda.cuda.synchronize()
+        assert (from_dev_u32(d_out) == want_w).all()
