@@ -189,3 +189,46 @@ def test_fixed_kernel_bank_conflicts(S, worst):
     16- to 32-way conflicts of the unpadded layout back"""
     got, ideal = fixed_kernel_wavefronts(S)
     assert got <= worst * ideal, (got, ideal)
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# FFT block alone on the fast passes (fft_fixed_fast_kernel): the bit-reversed scatter of the output beats, index wx<S>
+
+def wx(n, S):
+    return {10: n + ((n >> 5) << 2), 11: n + ((n >> 4) << 1), 12: n + (n >> 3), 13: n + ((n >> 6) << 1), 14: n + ((n >> 9) << 2)}[S]
+
+
+def fixed_row_words(S):
+    """FGeo<S>::ROW: exchange buffer + magnitude array, in words"""
+    N = 1 << S
+    xb = (fidx_fixed(N - 1, S) + 4) & ~3
+    xm = (mhx(N - 1, S) // 2 + 4) & ~3
+    return xb + xm
+
+
+@pytest.mark.parametrize("S,LP", [(10, 4), (11, 4), (12, 4), (13, 4), (14, 4), (14, 5)])
+def test_fft_only_output_scatter_is_conflict_free_and_covers_the_row(S, LP):
+    m = pass_size(S, n_passes(S) - 1)
+    R, G, N, TPC = 1 << m, (1 << LP) >> m, 1 << S, (1 << S) >> LP
+    width = min(G, 4)                                   # words per store instruction (G = 8: two 128-bit stores)
+    seen = set()
+    for rr in range(R):
+        rrr = _rev(rr, m) << (S - m)
+        for w0 in range(0, TPC, 32):
+            for part in range(max(1, G // 4)):
+                addrs = []
+                for lane in range(32):
+                    n0 = rrr | (_rev(w0 + lane, S - LP) << (LP - m))
+                    assert wx(n0, S) == wx(rrr, S) + wx(n0 - rrr, S)                 # one run-time base + a compile-time offset
+                    assert wx(n0 + G - 1, S) == wx(n0, S) + G - 1 and wx(n0, S) % width == 0   # the run is contiguous and aligned
+                    addrs.append(4 * (wx(n0, S) + 4 * part))
+                    seen.update(range(n0, n0 + G))
+                got, ideal = wavefronts(addrs, 4 * width)
+                assert got == ideal, (S, LP, rr, w0)
+    assert seen == set(range(N))
+    assert wx(N - 1, S) < fixed_row_words(S)            # the padded output row fits the chirp's shared memory
+    # reading back in natural order (bin tl + j TPC): at most two wavefronts per warp load
+    for j in range(1 << LP):
+        for w0 in range(0, TPC, 32):
+            got, ideal = wavefronts([4 * wx(w0 + lane + j * TPC, S) for lane in range(32)], 4)
+            assert got <= 2 * ideal
