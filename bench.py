@@ -273,8 +273,8 @@ def config_lines(torch, peak):
     case("C4 OS-CFAR 1024 x 4096 fixed, reading (A): GOS core, 64 cells per side, k=48", fixed_params(4096, 64, 4, R.GOSCFARType), 12, os_regs, 1024, 1, 16,
          note="CFARCoreWithLis (indexLagg = indexLead = 48); one frame is 32 MiB (L2-resident)")
     os_b = dict(fftWin=4096, thresholdScaler=2, logOrLinearMode=1, peakGrouping=0, cfarMode=0, windowCells=32, guardCells=4)
-    case("C4 OS-CFAR 1024 x 4096 fixed, reading (B): golden cfarOS, 32 + 32 cells in one sorted window, ascending index 48", fixed_params(4096, 64, 4, R.OSGoldenCFARType), 12, os_b, 1024, 1, 1,
-         note="CFARUtils.scala:159-196 (no hardware core in the reference); run-time-parameter kernel, bitwise rank search")
+    case("C4 OS-CFAR 1024 x 4096 fixed, reading (B): golden cfarOS, 32 + 32 cells in one sorted window, ascending index 48", fixed_params(4096, 64, 4, R.OSGoldenCFARType), 12, os_b, 1024, 1, 16,
+         note="CFARUtils.scala:159-196 (no hardware core in the reference); radix selection on bit planes (chain_fixed_fast_os)")
     out.extend(generator_lines(torch, peak))
     out.extend(doppler_lines(torch, peak))
     return out

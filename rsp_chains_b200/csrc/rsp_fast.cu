@@ -1020,6 +1020,127 @@ __global__ void __launch_bounds__(FGeo<S>::THREADS, 1024 / FGeo<S>::THREADS) cha
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
+// Combined-window ordered statistic (CORE_OS: the golden cfarOS, CFARUtils.scala:159-196; BASELINE configs[3] reading (B)) by radix
+// selection on bit planes.  The row's biased magnitudes (x + 2^15, 16 bits) are transposed into 16 bit planes of N bits each (one warp
+// ballot per plane and 32 bins); the reference cells of a bin -- R <= 32 leading and R lagging ones -- are then two 32-bit masks cut out
+// of a plane by funnel shifts, and the k-th largest of the 2 R cells is found from the top plane down: with the candidates' bit in hand,
+// c = popc(cand & plane) says whether the statistic has the bit set (c >= k: keep those) or not (k -= c, keep the others).  About 12
+// instructions per plane and bin, independent of R, against 2 R compares per plane for the bitwise rank search of the run-time-parameter
+// kernel.  A thread owns 16 neighbouring bins, 8 at a time: their windows are 8 consecutive bit offsets of the same three plane words.
+template <int S> struct OGeo {
+  static constexpr int N = 1 << S;
+  static constexpr int MW = 3;                       // margin words in front of and behind each plane (windows of the edge bins)
+  static constexpr int PW = N / 32 + 2 * MW + 1;     // words per plane (odd: the planes of one word index fall into distinct banks)
+  static_assert(16 * PW <= FGeo<S>::XB, "the bit planes fit the exchange buffer");
+};
+
+// 8 consecutive window pairs: leading words start at bit s0 + j, lagging words at bit s1 + j (j < 8) of every plane; m0 / m1 mask the
+// cells that belong to the window; kk0 = rank (1-based, descending).  Leaves the candidate masks of the statistic in cl / cr.
+template <int S>
+__device__ __forceinline__ void os_select8(const uint32_t *bp, int s0, int s1, uint32_t m0, uint32_t m1, int kk0, uint32_t (&cl)[8], uint32_t (&cr)[8]) {
+  constexpr int PW = OGeo<S>::PW;
+  const uint32_t *p0 = bp + (s0 >> 5), *p1 = bp + (s1 >> 5);   // arithmetic shift: the margin words take the negative starts
+  const int sh0 = s0 & 31, sh1 = s1 & 31;
+  int kk[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) { cl[j] = m0; cr[j] = m1; kk[j] = kk0; }
+#pragma unroll 4
+  for (int b = 15; b >= 0; --b) {
+    const uint32_t a0 = p0[b * PW], a1 = p0[b * PW + 1], a2 = p0[b * PW + 2];
+    const uint32_t c0 = p1[b * PW], c1 = p1[b * PW + 1], c2 = p1[b * PW + 2];
+    const uint32_t l0 = __funnelshift_r(a0, a1, sh0), l1 = __funnelshift_r(a1, a2, sh0);   // bits s0 .. s0 + 63
+    const uint32_t r0 = __funnelshift_r(c0, c1, sh1), r1 = __funnelshift_r(c1, c2, sh1);
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const uint32_t wl = __funnelshift_r(l0, l1, j), wr = __funnelshift_r(r0, r1, j);
+      const uint32_t ml = cl[j] & wl, mr = cr[j] & wr;
+      const int t = kk[j] - __popc(ml) - __popc(mr);
+      const bool take = t <= 0;                      // at least kk candidates have the bit: the statistic has it too
+      const uint32_t tm = take ? 0u : 0xFFFFFFFFu;
+      cl[j] = ml ^ (tm & cl[j]);                     // take: the candidates with the bit; else: those without
+      cr[j] = mr ^ (tm & cr[j]);
+      kk[j] = take ? kk[j] : t;
+    }
+  }
+}
+
+template <int S>
+__global__ void __launch_bounds__(FGeo<S>::THREADS, 1024 / FGeo<S>::THREADS) chain_fixed_fast_os_kernel(const FastArgs a, const GosArgs ga) {
+  using Gm = FGeo<S>;
+  using Go = OGeo<S>;
+  constexpr int N = Gm::N, TPC = Gm::TPC, CPC = Gm::CPC, PTS = Gm::PTS, PW = Go::PW;
+  extern __shared__ __align__(16) uint32_t smem[];
+  __shared__ int loud[CPC];
+  if (threadIdx.x < CPC) loud[threadIdx.x] = 0;
+  __syncthreads();
+  const int c = threadIdx.x / TPC, tl = threadIdx.x % TPC;
+  uint32_t *xb = smem + (size_t)c * Gm::ROW, *xm = xb + Gm::XB;
+  const short *X = reinterpret_cast<const short *>(xm);
+  uint32_t *bp = xb + Go::MW;                         // plane b, word w (bins 32 w .. 32 w + 31): bp[b * PW + w]
+  const int R = a.W, G = a.G;
+  const uint32_t mR = R >= 32 ? 0xFFFFFFFFu : ((1u << R) - 1u);
+  const int kk0 = 2 * R - (3 * R) / 2;                // ascending index floor(1.5 R) of 2 R cells = the (2 R - floor(1.5 R))-th largest
+  const uint32_t stride = gridDim.x * CPC;
+  for (uint32_t row0 = blockIdx.x * CPC; row0 < a.n_rows; row0 += stride) {
+    const bool active = row0 + c < a.n_rows;
+    const uint32_t row = active ? row0 + c : a.n_rows - 1;
+    const uint32_t *grow = a.in + (size_t)row * N;
+    uint32_t pre[PTS];
+    const GenRow no_gen = {0u, 0u};
+    load_beats<S, 4>(a, grow, no_gen, tl, 0, pre);
+    fast_passes<S, 4>(a, c, tl, pre, grow, no_gen, xb, xm, loud);   // ends with a barrier: magnitudes in X, the exchange buffer is free
+    // bit planes: in iteration j the warp holds bins 32 w .. 32 w + 31, w = (j * TPC + tl) / 32; lane b keeps plane b's ballot and stores it
+#pragma unroll 2
+    for (int j = 0; j < PTS; ++j) {
+      const int n = j * TPC + tl;
+      const uint32_t xv = (uint32_t)(X[mhx<S>(n)] + 0x8000);
+      uint32_t mine = 0;
+#pragma unroll
+      for (int b = 0; b < 16; ++b) {
+        const uint32_t bal = __ballot_sync(0xffffffffu, (xv >> b) & 1u);
+        mine = (tl & 31) == b ? bal : mine;
+      }
+      if ((tl & 31) < 16) bp[(tl & 31) * PW + (n >> 5)] = mine;
+    }
+    chirp_sync<S>(c);
+    uint32_t *gout = a.out + (size_t)row * N + PTS * tl;
+#pragma unroll 1
+    for (int h = 0; h < PTS / 8; ++h) {
+      const int n0 = PTS * tl + 8 * h;
+      uint32_t cl[8], cr[8];
+      os_select8<S>(bp, n0 - G - R, n0 + G + 1, mR, mR, kk0, cl, cr);
+      uint32_t ow[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const int n = n0 + j;
+        const bool both = (n + G + R <= N - 1) && (n - G - R >= 0);
+        // every remaining candidate equals the statistic: read one back from the magnitudes
+        int pos = cl[j] != 0 ? (n - G - R) + __ffs((int)cl[j]) - 1 : (n + G + 1) + __ffs((int)cr[j]) - 1;
+        pos = min(max(pos, 0), N - 1);
+        const int t = X[mhx<S>(pos)];
+        int thr = ga.linear ? t * a.scaler : t + a.scaler;
+        thr = both ? thr : 0;                         // the golden pads the edges with 0 (linear and log)
+        const int cut = X[mhx<S>(n)];
+        const int pk = (both && cut > thr) ? 1 : 0;
+        ow[j] = ((uint32_t)thr & a.thr_mask) * (uint32_t)a.out_mul + (uint32_t)(n << 1) + (uint32_t)pk;
+        if (pk && a.det_list != nullptr && active) {
+          const uint32_t slot = atomicAdd(a.det_count, 1u);
+          if (slot < a.det_cap) {
+            Detection d; d.chirp = a.row_base + row; d.bin = (uint32_t)n; d.threshold = (int)((uint32_t)thr << a.thr_sext) >> a.thr_sext; d.cut = cut;
+            a.det_list[slot] = d;
+          }
+        }
+      }
+      if (a.out != nullptr) {
+        *reinterpret_cast<uint4 *>(gout + 8 * h) = make_uint4(ow[0], ow[1], ow[2], ow[3]);
+        *reinterpret_cast<uint4 *>(gout + 8 * h + 4) = make_uint4(ow[4], ow[5], ow[6], ow[7]);
+      }
+    }
+    chirp_sync<S>(c);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
 // host side.  This file is compiled once per transform size (-DRSP_FAST_S=10 .. 14, see Makefile) so that the sizes build in
 // parallel; the unit of the smallest size also holds the dispatcher.
 #ifndef RSP_FAST_S
@@ -1100,6 +1221,21 @@ static rsp_status launch_fast_gos(const LaunchCtx &c, const FastArgs &fa, const 
   return RSP_OK;
 }
 
+template <int S>
+static rsp_status launch_fast_os(const LaunchCtx &c, const FastArgs &fa, const GosArgs &ga, cudaStream_t st, const char **err) {
+  using Gm = FGeo<S>;
+  static int occ_dev[64] = {0};
+  int &occ = occ_dev[c.device & 63];
+  const size_t smem = (size_t)Gm::CPC * Gm::ROW * sizeof(uint32_t);
+  auto kernel = chain_fixed_fast_os_kernel<S>;
+  if (!occ) { const rsp_status s = launch_cfg(kernel, smem, Gm::THREADS, &occ, err); if (s != RSP_OK) return s; }
+  const unsigned groups = (fa.n_rows + Gm::CPC - 1) / Gm::CPC;
+  const unsigned grid = std::max(1u, std::min(groups, (unsigned)(c.sm_count * occ)));
+  kernel<<<grid, Gm::THREADS, smem, st>>>(fa, ga);
+  if (cudaGetLastError() != cudaSuccess) { *err = "chain_fixed_fast_os_kernel launch failed"; return RSP_ECUDA; }
+  return RSP_OK;
+}
+
 template <int S, int LP>
 static rsp_status launch_fast_fft_lp(const LaunchCtx &c, const FastArgs &fa, cudaStream_t st, const char **err) {
   using Gm = FGeo<S, LP>;
@@ -1122,6 +1258,7 @@ rsp_status RSP_CAT(launch_fast_size_, RSP_FAST_S)(int core, int cmode, bool line
                                                   cudaStream_t st, const char **err) {
   constexpr int S = RSP_FAST_S;
   if (core == CORE_LIS) return launch_fast_gos<S>(ctx, fa, ga, st, err);
+  if (core == CORE_OS) return launch_fast_os<S>(ctx, fa, ga, st, err);
 #if RSP_FAST_S == 10
   if (ej == 2) return launch_fast_modes<S, 2>(cmode, linear, ctx, fa, st, err);
 #endif
@@ -1177,11 +1314,23 @@ static bool fast_gos_supported(const FxArgs &a) {
   return a.out != nullptr && a.binw + 1 <= 31;
 }
 
+// the golden cfarOS on bit planes: up to 32 reference cells per side
+static bool fast_os_supported(const FxArgs &a) {
+  static int on = -1;
+  if (on < 0) { const char *e = std::getenv("RSP_FAST_OS"); on = (e != nullptr && e[0] == '0') ? 0 : 1; }   // A/B knob
+  if (!on || a.core != CORE_OS) return false;
+  if (a.in_w != 16 || a.in_bp != 0 || a.sc_bp != 0 || a.thr_bp != 0 || a.send_cut || a.peak_grouping) return false;
+  if (a.thr_w < 1 || a.thr_w > 32 || a.G < 0 || a.W < 1 || a.W > 32 || a.G + a.W > 64) return false;
+  if (a.out == nullptr && a.det_list == nullptr) return false;
+  return (reinterpret_cast<uintptr_t>(a.out) & 15u) == 0 && a.binw + 1 <= 31;
+}
+
 bool fast_chain_supported(const Plan &pl, const FxArgs &a) {
   if (pl.mode != MODE_FAST || pl.first_stage != STAGE_FFT || pl.last_stage != STAGE_CFAR) return false;
   if (pl.S < RSP_FAST_SMIN || pl.S > RSP_FAST_SMAX) return false;
   if (a.bp != 0 || a.tw_bp != 14 || !a.bitrev || a.sel != 2 || a.mag_w != 16 || a.mag_bp != 0) return false;
   if (a.core == CORE_LIS) return fast_gos_supported(a);
+  if (a.core == CORE_OS) return fast_os_supported(a);
   if (a.core != CORE_MEM || a.in_w != 16 || a.in_bp != 0 || a.sc_bp != 0 || a.thr_bp != 0 || a.send_cut || a.peak_grouping) return false;
   if (a.out == nullptr && a.det_list == nullptr) return false;
   if (a.thr_w < 1 || a.thr_w > 32 || a.G < 1 || a.W < 1 || a.div_sum < 0 || a.div_sum > 30) return false;
@@ -1218,7 +1367,7 @@ rsp_status launch_fast_chain(const Plan &pl, const LaunchCtx &ctx, const FxArgs 
   const int cmode = a.cfar_mode == 0 ? 0 : (a.cfar_mode == 1 ? 1 : 2);   // MuxLookup default: smallestOf (CFARCoreWithMem.scala:138-141)
   const bool linear = a.log_or_linear != 0;
   const GosArgs ga = {cmode, linear ? 1 : 0, a.idx_lagg - 1, a.idx_lead - 1};
-  const int ej = a.core == CORE_LIS ? 1 : fast_edge_iters(pl.S, a.W, a.G);
+  const int ej = a.core != CORE_MEM ? 1 : fast_edge_iters(pl.S, a.W, a.G);
   switch (pl.S) {
   case 10: return launch_fast_size_10(a.core, cmode, linear, ej, ctx, fa, ga, st, err);
   case 11: return launch_fast_size_11(a.core, cmode, linear, ej, ctx, fa, ga, st, err);

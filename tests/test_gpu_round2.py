@@ -586,3 +586,39 @@ def test_nco_output_multiplier(cuda, oracle, rounding):
     with R.RspChainVanilla(p) as ch:
         with pytest.raises(R.RspError):          # no register file without the multiplier
             ch.memWriteWord(p.ncoAddress.base, 1)
+
+
+@pytest.mark.parametrize("log_n,Rc,G,lin", [(10, 32, 4, 1), (10, 8, 0, 0), (11, 16, 2, 1), (12, 32, 4, 1), (12, 31, 7, 0), (13, 5, 1, 1), (14, 32, 16, 1),
+                                            (14, 24, 3, 0)])
+def test_fast_os_kernel_bit_planes(cuda, oracle, log_n, Rc, G, lin):
+    """chain_fixed_fast_os<S> (radix selection on bit planes) against the oracle's integer cfarOS core: every size, window sizes that are
+    not powers of two, no guard cells, linear and log thresholds, full-scale random rows (negative magnitudes, ties), long runs of equal
+    cells, ragged row counts, the detection list."""
+    n = 1 << log_n
+    rows = 9 if log_n <= 12 else 3
+    beats = np.concatenate([synth.chirps_fixed(rows - 2, n, seed=70 + log_n), synth.random_beats(2, n, seed=90 + log_n)])
+    beats[0, n // 2:] = beats[0, 5]                      # equal cells: every candidate set keeps many members to the last plane
+    p = fixed_params(n, 64, max(G, 1), ctype=R.OSGoldenCFARType)
+    regs = dict(fftWin=n, thresholdScaler=3, logOrLinearMode=lin, peakGrouping=0, cfarMode=0, windowCells=Rc, guardCells=G)
+    fft, mag, cfar = oracle_cfgs(oracle, p, log_n, 2, regs)
+    want = oracle.chain_fixed_words(fft, mag, cfar, beats)
+    with R.FftMagCfarChainVanilla(p) as ch:
+        configure(ch, log_n, 2, regs)
+        assert ch.variant == f"chain_fixed_fast_os<{log_n}>", ch.variant
+        d_in = to_dev(cuda, beats)
+        d_out = cuda.zeros_like(d_in)
+        det_list = cuda.zeros((rows * n, 4), dtype=cuda.int32, device="cuda")
+        det_count = cuda.zeros(1, dtype=cuda.int32, device="cuda")
+        ch.run(d_in, rows, 1, out=d_out, det_list=det_list, det_count=det_count)
+        cuda.cuda.synchronize()
+        got = from_dev_u32(d_out)
+        k = int(det_count.item())
+        dets = det_list[:k].cpu().numpy()
+        assert (got == want).all()
+        assert k == int((want & 1).sum())
+        assert set(map(tuple, dets[:, :2].tolist())) == set(map(tuple, np.argwhere((want & 1) == 1).tolist()))
+        d_out.zero_()
+        ch.run(d_in, 1, 1, out=d_out)                   # one row: the second chirp slot of a CTA (N = 1024) recomputes it
+        cuda.cuda.synchronize()
+        got1 = from_dev_u32(d_out)
+        assert (got1[0] == want[0]).all() and not got1[1:].any()
