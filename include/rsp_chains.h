@@ -237,6 +237,17 @@ rsp_status rsp_run(rsp_chain *c, const void *d_in, uint32_t n_chirps, uint32_t n
  * d_nco_out (optional) receives the NCO beats Cat(cos16, sin16) (generators/nco/src/main/scala/NCOLazyModuleBlock.scala:452). */
 rsp_status rsp_run_from_generator(rsp_chain *c, uint32_t n_chirps, uint32_t n_rx, void *d_out, uint32_t *d_peak_mask,
                                   const rsp_dets *dets, uint32_t *d_nco_out, void *stream);
+/* rsp_run_from_generator for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * it).  No counterpart in the reference.  Same results as rsp_run_from_generator (without the
+ * d_nco_out option), but the NCO beats between the generator and the chain kernel, and the PLFG segment list, live in two file-scope device
+ * arrays of fixed size instead of buffers the handle allocates: the call performs no cudaMalloc / cudaFree.  Limits: n_rx * n_chirps *
+ * fftSize <= RSP_STATIC_SCRATCH_BEATS samples and <= RSP_STATIC_MAX_SEGMENTS PLFG segments per period; beyond them RSP_EINVAL (the message
+ * names the limit).  Every GPU that loads the library holds the arrays (4 MiB + 16 KiB) until exit.  All calls on a GPU share them: calls that
+ * overlap on the GPU (other streams, other handles) race; the arrays keep the last call's contents and nothing in them needs to start at 0. */
+#define RSP_STATIC_SCRATCH_BEATS (1u << 20)
+#define RSP_STATIC_MAX_SEGMENTS 512
+rsp_status rsp_run_from_generator_static(rsp_chain *c, uint32_t n_chirps, uint32_t n_rx, void *d_out, uint32_t *d_peak_mask,
+                                         const rsp_dets *dets, void *stream);
 
 /* ---- single blocks (each reference DspBlock is usable on its own) ----------------------------------------- */
 /* replaces AXI4FFTBlock (generators/sdf-fft/src/main/scala/FFTBlock.scala:122-124): beats in -> beats out */

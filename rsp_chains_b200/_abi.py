@@ -25,7 +25,7 @@ EXPORTS = [
     "rsp_abi_version", "rsp_kernel_launches", "rsp_variant_name", "rsp_bytes_per_chirp",
     "rsp_fft_in_beat_bytes", "rsp_fft_out_beat_bytes", "rsp_fft_overflow_flags",
     "rsp_gather_detections", "rsp_nccl_get_unique_id", "rsp_nccl_comm_init_rank", "rsp_nccl_comm_destroy",
-    "rsp_jtag_decode", "rsp_uart_to_beats", "rsp_beats_to_uart", "rsp_corner_turn", "rsp_mag_combine_run",
+    "rsp_jtag_decode", "rsp_uart_to_beats", "rsp_beats_to_uart", "rsp_corner_turn", "rsp_mag_combine_run", "rsp_run_from_generator_static",
 ]
 
 
@@ -141,6 +141,7 @@ def lib():
         L.rsp_beats_to_uart.argtypes = [vp, C.c_size_t, u32, i32, vp]
         L.rsp_corner_turn.argtypes = [vp, vp, vp, u32, u32, u32, u32, vp]
         L.rsp_mag_combine_run.argtypes = [vp, vp, u64, u32, vp, vp]
+        L.rsp_run_from_generator_static.argtypes = [vp, u32, u32, vp, vp, C.POINTER(Dets), vp]
         _lib = L
     return _lib
 

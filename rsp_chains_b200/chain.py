@@ -338,6 +338,15 @@ class RspChainVanilla(_Chain):
             nco_out.data_ptr() if nco_out is not None else None, _stream_ptr(stream)))
         return out
 
+    def run_from_generator_static(self, n_chirps: int, n_rx: int = 1, out=None, peak_mask=None, det_list=None, det_count=None, stream=None):
+        """rsp_run_from_generator_static: the same results with the scratch beats in a fixed device array of the library -- no cudaMalloc in
+        the call (at most RSP_STATIC_SCRATCH_BEATS = 2^20 samples per call; calls that overlap on the GPU race on the array)"""
+        d = self._dets_struct(det_list, det_count)
+        _abi.check(self._lib.rsp_run_from_generator_static(
+            self._h, n_chirps, n_rx, out.data_ptr() if out is not None else None,
+            peak_mask.data_ptr() if peak_mask is not None else None, C.byref(d) if d is not None else None, _stream_ptr(stream)))
+        return out
+
 
 def gather_detections(det_list, det_count, group=None):
     """Gather the per-rank detection lists on every rank (torch.distributed all_gather; NCCL on GPUs, gloo on CPU).

@@ -689,6 +689,84 @@ extern "C" rsp_status rsp_run_from_generator(rsp_chain *c, uint32_t n_chirps, ui
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
+// rsp_run_from_generator without any allocation (no counterpart in the reference; added for callers
+// that cannot call cudaMalloc: CUDA graph capture, tight serving loops, harnesses that forbid it).  The two-launch form of the path --
+// generator_kernel -> NCO beats in scratch -> chain kernel -- with the scratch beats and the PLFG segment list in file-scope device arrays
+// of a fixed size instead of the handle's cudaMalloc'ed buffers.  Every GPU that loads the library holds both arrays (4 MiB + 16 KiB) until
+// exit.  All calls on a GPU share them and they keep the last call's contents: nothing has to start at zero (a call overwrites every beat
+// and every segment it reads), but two calls that overlap on the GPU (different streams, different handles) race on them.
+static __device__ __align__(256) uint32_t g_static_beats[RSP_STATIC_SCRATCH_BEATS];
+static __device__ __align__(256) GenSegment g_static_segs[RSP_STATIC_MAX_SEGMENTS];
+
+// In host code the arrays' names are host-side stand-ins, not device addresses: the addresses come from cudaGetSymbolAddress, once per
+// device, with that device current (the caller's RSP_ON_DEVICE guard).
+static rsp_status static_scratch(int device, uint32_t **beats, GenSegment **segs) {
+  static void *beats_of[64] = {}, *segs_of[64] = {};
+  if (device < 0 || device >= 64) return fail(RSP_EUNSUPPORTED, "rsp_run_from_generator_static: device ordinal above 63");
+  if (beats_of[device] == nullptr) {
+    void *pb = nullptr, *ps = nullptr;
+    CUDA_TRY(cudaGetSymbolAddress(&pb, g_static_beats));
+    CUDA_TRY(cudaGetSymbolAddress(&ps, g_static_segs));
+    segs_of[device] = ps; beats_of[device] = pb;
+  }
+  *beats = static_cast<uint32_t *>(beats_of[device]); *segs = static_cast<GenSegment *>(segs_of[device]);
+  return RSP_OK;
+}
+
+extern "C" rsp_status rsp_run_from_generator_static(rsp_chain *c, uint32_t n_chirps, uint32_t n_rx, void *d_out, uint32_t *d_peak_mask,
+                                                    const rsp_dets *dets, void *stream) {
+  if (!c) return fail(RSP_EINVAL, "null handle");
+  if (c->p.arith != RSP_ARITH_FIXED) return fail(RSP_EUNSUPPORTED, "the PLFG/NCO generator feeds the fixed-point chain only");
+  if (!c->p.hasGenerator) return fail(RSP_EINVAL, "this chain has no PLFG/NCO (hasGenerator = 0)");
+  if (!(c->r.plfg[RSP_PLFG_REG_ENABLE] & 1u)) return fail(RSP_EINVAL, "the PLFG enable register is 0");
+  uint32_t rows;
+  rsp_status s = rows_of(n_chirps, n_rx, &rows);
+  if (s != RSP_OK) return s;
+  const int S = c->p.fft.runTime ? (int)c->r.fft[RSP_FFT_REG_FFTSIZE] : log2_ceil((uint32_t)c->p.fft.numPoints);
+  const uint64_t n_samples = (uint64_t)rows << S;
+  if (n_samples > (uint64_t)RSP_STATIC_SCRATCH_BEATS)
+    return fail(RSP_EINVAL, "rsp_run_from_generator_static: " + std::to_string(n_samples) + " samples exceed the static scratch of " +
+                                std::to_string((unsigned long long)RSP_STATIC_SCRATCH_BEATS) + " beats (RSP_STATIC_SCRATCH_BEATS); use rsp_run_from_generator");
+  RSP_ON_DEVICE(c);
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (n_samples == 0) return RSP_OK;
+  uint32_t *beats; GenSegment *segs;
+  s = static_scratch(c->device, &beats, &segs);
+  if (s != RSP_OK) return s;
+  // the schedule is planned into a local (host) plan and uploaded on every call: the handle's own device copy belongs to the allocating path
+  GenPlan gp;
+  std::string err;
+  s = plan_generator(c->p, c->r, gp, err);
+  if (s != RSP_OK) return fail(s, err);
+  if (gp.segs.size() > (size_t)RSP_STATIC_MAX_SEGMENTS)
+    return fail(RSP_EINVAL, "rsp_run_from_generator_static: the PLFG schedule has " + std::to_string(gp.segs.size()) + " segments per period, the static list holds " +
+                                std::to_string((int)RSP_STATIC_MAX_SEGMENTS) + " (RSP_STATIC_MAX_SEGMENTS); use rsp_run_from_generator");
+  if (n_samples > gp.total)
+    return fail(RSP_EINVAL, "the PLFG schedule (frameNum frames) ends before the requested samples; frameNum = 0 runs forever");
+  CUDA_TRY(cudaMemcpyAsync(segs, gp.segs.data(), gp.segs.size() * sizeof(GenSegment), cudaMemcpyHostToDevice, st));
+  CUDA_TRY(cudaStreamSynchronize(st));   // gp is a local: the copy has left it before it goes away
+  GenArgs g;
+  g.segs = segs; g.n_segs = (uint32_t)gp.segs.size();
+  g.period_len = gp.period_len; g.period_phase = gp.period_phase;
+  g.nco_tab = c->d_nco_tab; g.nco_full = c->d_nco_full;
+  g.table_size = c->p.nco.tableSize; g.addr_bits = log2_ceil((uint32_t)c->p.nco.tableSize);
+  g.table_width = c->p.nco.tableWidth; g.phase_width = c->p.nco.phaseWidth;
+  g.out_width = c->p.plfg.outputWidthInt + c->p.plfg.outputWidthFrac;
+  g.phase_acc_enable = c->p.nco.phaseAccEnable ? 1 : 0;
+  g.poff = 0;
+  g.mult_on = 0; g.mult_f = 0; g.mult_trim = c->p.nco.roundingMode;
+  if (c->p.nco.useMultiplier) {   // as prepare_generator (NCOLazyModuleBlock.scala:354)
+    const int w = c->p.nco.tableWidth;
+    g.mult_f = (int)wrap_host((c->r.nco[0] & 1u) ? (long long)c->r.nco[1] : (1LL << 14), w);
+    g.mult_on = (g.mult_f != (1 << (w - 2))) ? 1 : 0;
+  }
+  generator_kernel<<<ew_grid(c, (n_samples + RSP_GEN_RUN - 1) / RSP_GEN_RUN), 256, 0, st>>>(g, n_samples, beats, nullptr);
+  CUDA_TRY(cudaGetLastError());
+  ++c->launches;
+  return run_stages(c, STAGE_FFT, STAGE_CFAR, beats, rows, d_out, d_peak_mask, dets, st);
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
 // host-buffer pipeline
 extern "C" rsp_status rsp_host_alloc(void **p, size_t bytes) {
   if (!p) return fail(RSP_EINVAL, "null argument");
