@@ -1027,25 +1027,64 @@ __global__ void __launch_bounds__(FGeo<S>::THREADS, 1024 / FGeo<S>::THREADS) cha
 // c = popc(cand & plane) says whether the statistic has the bit set (c >= k: keep those) or not (k -= c, keep the others).  About 12
 // instructions per plane and bin, independent of R, against 2 R compares per plane for the bitwise rank search of the run-time-parameter
 // kernel.  A thread owns 16 neighbouring bins, 8 at a time: their windows are 8 consecutive bit offsets of the same three plane words.
+// The planes are built by a 16 x 16 bit transpose in registers per thread; planes in which all cells of the chirp agree are skipped.
 template <int S> struct OGeo {
   static constexpr int N = 1 << S;
-  static constexpr int MW = 3;                       // margin words in front of and behind each plane (windows of the edge bins)
-  static constexpr int PW = N / 32 + 2 * MW + 1;     // words per plane (odd: the planes of one word index fall into distinct banks)
+  static constexpr int MW = 3, MB = 6;               // margin words in front of / behind each plane (windows that start before or end after the row)
+  static constexpr int PW = N / 32 + MW + MB;        // words per plane (odd: the planes of one word index fall into distinct banks)
+  static_assert(PW & 1, "odd plane stride");
   static_assert(16 * PW <= FGeo<S>::XB, "the bit planes fit the exchange buffer");
+  static constexpr int KW = N;                       // extra words of the (A) kernel: two int16 K arrays
 };
 
-// 8 consecutive window pairs: leading words start at bit s0 + j, lagging words at bit s1 + j (j < 8) of every plane; m0 / m1 mask the
-// cells that belong to the window; kk0 = rank (1-based, descending).  Leaves the candidate masks of the statistic in cl / cr.
+// 16 x 16 bit-matrix transpose in 8 registers (word k = rows 2k | 2k+1 << 16): block swaps of size 8, 4, 2, 1.  In: row r = the 16-bit
+// value of bin r; out: row c = bit c of the 16 bins (bin r at bit r).  ~100 instructions per 16 bins, against 4 per bin and plane for
+// warp ballots (tests/test_kernel_layout.py holds the same algorithm in Python).
+__device__ __forceinline__ void bit_transpose16(uint32_t (&A)[8]) {
+#pragma unroll
+  for (int k = 0; k < 4; ++k) { const uint32_t t = ((A[k] >> 8) ^ A[k + 4]) & 0x00FF00FFu; A[k + 4] ^= t; A[k] ^= t << 8; }
+#pragma unroll
+  for (int q = 0; q < 4; ++q) { const int k = (q & 1) | ((q & 2) << 1); const uint32_t t = ((A[k] >> 4) ^ A[k + 2]) & 0x0F0F0F0Fu; A[k + 2] ^= t; A[k] ^= t << 4; }
+#pragma unroll
+  for (int k = 0; k < 8; k += 2) { const uint32_t t = ((A[k] >> 2) ^ A[k + 1]) & 0x33333333u; A[k + 1] ^= t; A[k] ^= t << 2; }
+#pragma unroll
+  for (int k = 0; k < 8; ++k) { const uint32_t t = ((A[k] >> 1) ^ (A[k] >> 16)) & 0x5555u; A[k] ^= t * 0x10002u; }
+}
+
+// The thread's 16 neighbouring magnitudes (biased to offset binary: order preserved) -> its halfword of each of the 16 planes.
+// uni[0] / uni[1] collect the OR / AND of all cells of the chirp: a plane in which every cell has the same bit cannot change any
+// candidate set (all candidates have the bit: c >= k as long as k <= candidates; none has it: c = 0) and is skipped by the selection.
 template <int S>
-__device__ __forceinline__ void os_select8(const uint32_t *bp, int s0, int s1, uint32_t m0, uint32_t m1, int kk0, uint32_t (&cl)[8], uint32_t (&cr)[8]) {
+__device__ __forceinline__ void os_build_planes(const uint32_t *xm, int tl, uint32_t *bp, uint32_t *uni) {
+  constexpr int PW = OGeo<S>::PW;
+  const uint32_t *xq = xm + mhx<S>(16 * tl) / 2;
+  const uint4 v0 = *reinterpret_cast<const uint4 *>(xq), v1 = *reinterpret_cast<const uint4 *>(xq + 4);
+  uint32_t A[8] = {v0.x, v0.y, v0.z, v0.w, v1.x, v1.y, v1.z, v1.w};
+  uint32_t orv = 0, andv = 0xFFFFFFFFu;
+#pragma unroll
+  for (int k = 0; k < 8; ++k) { A[k] ^= 0x80008000u; orv |= A[k]; andv &= A[k]; }
+  orv = __reduce_or_sync(0xffffffffu, orv); andv = __reduce_and_sync(0xffffffffu, andv);
+  if ((tl & 31) == 0) { atomicOr(&uni[0], (orv | (orv >> 16)) & 0xFFFFu); atomicAnd(&uni[1], andv & (andv >> 16) & 0xFFFFu); }
+  bit_transpose16(A);
+  uint16_t *bph = reinterpret_cast<uint16_t *>(bp) + tl;
+#pragma unroll
+  for (int b = 0; b < 16; ++b) bph[b * 2 * PW] = (uint16_t)(A[b >> 1] >> (16 * (b & 1)));
+}
+
+// 8 consecutive window pairs of the combined-window statistic: leading words start at bit s0 + j, lagging words at bit s1 + j (j < 8) of
+// every plane; m0 / m1 mask the cells that belong to the window; kk0 = rank (1-based, descending); act = planes that are not uniform.
+// Leaves the candidate masks of the statistic in cl / cr.
+template <int S>
+__device__ __forceinline__ void os_select8(const uint32_t *bp, uint32_t act, int s0, int s1, uint32_t m0, uint32_t m1, int kk0, uint32_t (&cl)[8], uint32_t (&cr)[8]) {
   constexpr int PW = OGeo<S>::PW;
   const uint32_t *p0 = bp + (s0 >> 5), *p1 = bp + (s1 >> 5);   // arithmetic shift: the margin words take the negative starts
   const int sh0 = s0 & 31, sh1 = s1 & 31;
   int kk[8];
 #pragma unroll
   for (int j = 0; j < 8; ++j) { cl[j] = m0; cr[j] = m1; kk[j] = kk0; }
-#pragma unroll 4
-  for (int b = 15; b >= 0; --b) {
+  while (act) {
+    const int b = 31 - __clz((int)act);
+    act ^= 1u << b;
     const uint32_t a0 = p0[b * PW], a1 = p0[b * PW + 1], a2 = p0[b * PW + 2];
     const uint32_t c0 = p1[b * PW], c1 = p1[b * PW + 1], c2 = p1[b * PW + 2];
     const uint32_t l0 = __funnelshift_r(a0, a1, sh0), l1 = __funnelshift_r(a1, a2, sh0);   // bits s0 .. s0 + 63
@@ -1064,13 +1103,51 @@ __device__ __forceinline__ void os_select8(const uint32_t *bp, int s0, int s1, u
   }
 }
 
+// The same for ONE window of W <= 32 NWD cells per start (the hardware GOS core, CFARCoreWithLis.scala:136-143): 8 consecutive starts
+// s0 + j; mlast masks the cells of the last word.  Leaves the candidate masks in cw[j][0 .. NWD).
+template <int S, int NWD>
+__device__ __forceinline__ void gos_select8(const uint32_t *bp, uint32_t act, int s0, uint32_t mlast, int kk0, uint32_t (&cw)[8][NWD]) {
+  constexpr int PW = OGeo<S>::PW;
+  const uint32_t *p0 = bp + (s0 >> 5);
+  const int sh0 = s0 & 31;
+  int kk[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    kk[j] = kk0;
+#pragma unroll
+    for (int w = 0; w < NWD; ++w) cw[j][w] = w == NWD - 1 ? mlast : 0xFFFFFFFFu;
+  }
+  while (act) {
+    const int b = 31 - __clz((int)act);
+    act ^= 1u << b;
+    uint32_t raw[NWD + 2], al[NWD + 1];
+#pragma unroll
+    for (int w = 0; w < NWD + 2; ++w) raw[w] = p0[b * PW + w];
+#pragma unroll
+    for (int w = 0; w < NWD + 1; ++w) al[w] = __funnelshift_r(raw[w], raw[w + 1], sh0);   // bits s0 .. s0 + 32 (NWD + 1) - 1
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      uint32_t m[NWD];
+      int t = kk[j];
+#pragma unroll
+      for (int w = 0; w < NWD; ++w) { m[w] = cw[j][w] & __funnelshift_r(al[w], al[w + 1], j); t -= __popc(m[w]); }
+      const bool take = t <= 0;
+      const uint32_t tm = take ? 0u : 0xFFFFFFFFu;
+#pragma unroll
+      for (int w = 0; w < NWD; ++w) cw[j][w] = m[w] ^ (tm & cw[j][w]);
+      kk[j] = take ? kk[j] : t;
+    }
+  }
+}
+
 template <int S>
 __global__ void __launch_bounds__(FGeo<S>::THREADS, 1024 / FGeo<S>::THREADS) chain_fixed_fast_os_kernel(const FastArgs a, const GosArgs ga) {
   using Gm = FGeo<S>;
   using Go = OGeo<S>;
-  constexpr int N = Gm::N, TPC = Gm::TPC, CPC = Gm::CPC, PTS = Gm::PTS, PW = Go::PW;
+  constexpr int N = Gm::N, TPC = Gm::TPC, CPC = Gm::CPC, PTS = Gm::PTS;
   extern __shared__ __align__(16) uint32_t smem[];
   __shared__ int loud[CPC];
+  __shared__ uint32_t uni[CPC][2];
   if (threadIdx.x < CPC) loud[threadIdx.x] = 0;
   __syncthreads();
   const int c = threadIdx.x / TPC, tl = threadIdx.x % TPC;
@@ -1087,28 +1164,18 @@ __global__ void __launch_bounds__(FGeo<S>::THREADS, 1024 / FGeo<S>::THREADS) cha
     const uint32_t *grow = a.in + (size_t)row * N;
     uint32_t pre[PTS];
     const GenRow no_gen = {0u, 0u};
+    if (tl == 0) { uni[c][0] = 0u; uni[c][1] = 0xFFFFu; }
     load_beats<S, 4>(a, grow, no_gen, tl, 0, pre);
     fast_passes<S, 4>(a, c, tl, pre, grow, no_gen, xb, xm, loud);   // ends with a barrier: magnitudes in X, the exchange buffer is free
-    // bit planes: in iteration j the warp holds bins 32 w .. 32 w + 31, w = (j * TPC + tl) / 32; lane b keeps plane b's ballot and stores it
-#pragma unroll 2
-    for (int j = 0; j < PTS; ++j) {
-      const int n = j * TPC + tl;
-      const uint32_t xv = (uint32_t)(X[mhx<S>(n)] + 0x8000);
-      uint32_t mine = 0;
-#pragma unroll
-      for (int b = 0; b < 16; ++b) {
-        const uint32_t bal = __ballot_sync(0xffffffffu, (xv >> b) & 1u);
-        mine = (tl & 31) == b ? bal : mine;
-      }
-      if ((tl & 31) < 16) bp[(tl & 31) * PW + (n >> 5)] = mine;
-    }
+    os_build_planes<S>(xm, tl, bp, uni[c]);
     chirp_sync<S>(c);
+    const uint32_t act = uni[c][0] ^ uni[c][1];       // planes in which the chirp's cells differ
     uint32_t *gout = a.out + (size_t)row * N + PTS * tl;
 #pragma unroll 1
     for (int h = 0; h < PTS / 8; ++h) {
       const int n0 = PTS * tl + 8 * h;
       uint32_t cl[8], cr[8];
-      os_select8<S>(bp, n0 - G - R, n0 + G + 1, mR, mR, kk0, cl, cr);
+      os_select8<S>(bp, act, n0 - G - R, n0 + G + 1, mR, mR, kk0, cl, cr);
       uint32_t ow[8];
 #pragma unroll
       for (int j = 0; j < 8; ++j) {

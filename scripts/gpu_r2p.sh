@@ -1,6 +1,4 @@
 #!/bin/bash
 mkdir -p gpurun_out
-echo "== alone" | tee gpurun_out/pytest_noalloc.txt
-timeout 600 python -m pytest tests/test_zz_no_alloc.py -m gpu -x -q 2>&1 | tail -12 | tee -a gpurun_out/pytest_noalloc.txt
-echo "== full suite" | tee -a gpurun_out/pytest_noalloc.txt
-timeout 1500 python -m pytest tests -m gpu -x -q 2>&1 | tail -6 | tee -a gpurun_out/pytest_noalloc.txt
+timeout 900 python -m pytest tests/test_gpu_round2.py -m gpu -x -q -k "os or reading_b" 2>&1 | tail -8 | tee gpurun_out/pytest_os_z2.txt
+timeout 300 python scripts/bench_one.py c4osb 2>&1 | tail -1 | cut -c1-200 | tee gpurun_out/osb_bench2.txt
