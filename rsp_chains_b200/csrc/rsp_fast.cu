@@ -1208,6 +1208,85 @@ __global__ void __launch_bounds__(FGeo<S>::THREADS, 1024 / FGeo<S>::THREADS) cha
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
+// The hardware GOS core (CFARCoreWithLis, reading (A) of BASELINE configs[3]) on the same bit planes: K_k[s] = k-th largest of the W
+// cells starting at s is one radix selection per window start over NWD = ceil(W / 32) mask words (W <= 128), independent of k and -- per
+// mask word -- of W; the thresholds then read K[n + G + 1] and K[n - G - W] as in chain_fixed_fast_gos_kernel.  TWO: indexLagg and
+// indexLead differ, two selections.  No restriction on the cells' range (the bias makes them unsigned) or on W being a multiple of 8.
+template <int S, int NWD, bool TWO>
+__global__ void __launch_bounds__(FGeo<S>::THREADS, (NWD >= 3 ? 512 : 1024) / FGeo<S>::THREADS >= 1 ? (NWD >= 3 ? 512 : 1024) / FGeo<S>::THREADS : 1)
+chain_fixed_fast_gosb_kernel(const FastArgs a, const GosArgs ga) {
+  using Gm = FGeo<S>;
+  using Go = OGeo<S>;
+  constexpr int N = Gm::N, TPC = Gm::TPC, CPC = Gm::CPC, PTS = Gm::PTS, CROW = Gm::ROW + Go::KW;
+  extern __shared__ __align__(16) uint32_t smem[];
+  __shared__ int loud[CPC];
+  __shared__ uint32_t uni[CPC][2];
+  if (threadIdx.x < CPC) loud[threadIdx.x] = 0;
+  __syncthreads();
+  const int c = threadIdx.x / TPC, tl = threadIdx.x % TPC;
+  uint32_t *xb = smem + (size_t)c * CROW, *xm = xb + Gm::XB;
+  const short *X = reinterpret_cast<const short *>(xm);
+  short *KL = reinterpret_cast<short *>(xm + Gm::XM), *KR = TWO ? KL + N : KL;
+  uint32_t *bp = xb + Go::MW;
+  const int W = a.W, G = a.G;
+  const uint32_t mlast = (W & 31) ? ((1u << (W & 31)) - 1u) : 0xFFFFFFFFu;
+  const uint32_t stride = gridDim.x * CPC;
+  for (uint32_t row0 = blockIdx.x * CPC; row0 < a.n_rows; row0 += stride) {
+    const bool active = row0 + c < a.n_rows;
+    const uint32_t row = active ? row0 + c : a.n_rows - 1;
+    const uint32_t *grow = a.in + (size_t)row * N;
+    uint32_t pre[PTS];
+    const GenRow no_gen = {0u, 0u};
+    if (tl == 0) { uni[c][0] = 0u; uni[c][1] = 0xFFFFu; }
+    load_beats<S, 4>(a, grow, no_gen, tl, 0, pre);
+    fast_passes<S, 4>(a, c, tl, pre, grow, no_gen, xb, xm, loud);
+    os_build_planes<S>(xm, tl, bp, uni[c]);
+    chirp_sync<S>(c);
+    const uint32_t act = uni[c][0] ^ uni[c][1];
+#pragma unroll 1
+    for (int h = 0; h < (TWO ? 4 : 2); ++h) {          // window starts 16 tl + 8 (h & 1) + j; h >= 2: the leading statistic
+      const int s0 = PTS * tl + 8 * (h & 1);
+      uint32_t cw[8][NWD];
+      gos_select8<S, NWD>(bp, act, s0, mlast, (h < 2 ? ga.kl1 : ga.kr1) + 1, cw);
+      short *K = h < 2 ? KL : KR;
+      uint32_t kv[4];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        int pos = s0 + j;                               // every remaining candidate equals the statistic: read the first one back
+        bool found = false;
+#pragma unroll
+        for (int w = 0; w < NWD; ++w) { if (!found && cw[j][w] != 0) { pos += 32 * w + __ffs((int)cw[j][w]) - 1; found = true; } }
+        const uint32_t v = (uint16_t)X[mhx<S>(min(pos, N - 1))];
+        if (j & 1) kv[j >> 1] |= v << 16; else kv[j >> 1] = v;
+      }
+      *reinterpret_cast<uint4 *>(&K[s0]) = make_uint4(kv[0], kv[1], kv[2], kv[3]);
+    }
+    chirp_sync<S>(c);
+    uint32_t *gout = a.out + (size_t)row * N;
+#pragma unroll 4
+    for (int j = 0; j < PTS; ++j) {
+      const int n = tl + j * TPC;
+      const bool both = (n + G + W <= N - 1) && (n - G - W >= 0);
+      const int L = KL[min(n + G + 1, N - W)], R = KR[max(n - G - W, 0)];
+      int t = ga.cmode == 0 ? ((R + L) >> 1) : (ga.cmode == 1 ? max(L, R) : min(L, R));
+      t = both ? t : 0;                                                  // CFARCoreWithLis.scala:172-173
+      const int thr = ga.linear ? t * a.scaler : t + a.scaler;
+      const int cut = X[mhx<S>(n)];
+      const int pk = cut > thr ? 1 : 0;
+      if (a.out != nullptr) gout[n] = ((uint32_t)thr & a.thr_mask) * (uint32_t)a.out_mul + (uint32_t)(n << 1) + (uint32_t)pk;
+      if (pk && a.det_list != nullptr && active) {
+        const uint32_t slot = atomicAdd(a.det_count, 1u);
+        if (slot < a.det_cap) {
+          Detection d; d.chirp = a.row_base + row; d.bin = (uint32_t)n; d.threshold = (int)((uint32_t)thr << a.thr_sext) >> a.thr_sext; d.cut = cut;
+          a.det_list[slot] = d;
+        }
+      }
+    }
+    chirp_sync<S>(c);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
 // host side.  This file is compiled once per transform size (-DRSP_FAST_S=10 .. 14, see Makefile) so that the sizes build in
 // parallel; the unit of the smallest size also holds the dispatcher.
 #ifndef RSP_FAST_S
@@ -1288,6 +1367,42 @@ static rsp_status launch_fast_gos(const LaunchCtx &c, const FastArgs &fa, const 
   return RSP_OK;
 }
 
+template <int S, int NWD, bool TWO>
+static rsp_status launch_fast_gosb_inst(const LaunchCtx &c, const FastArgs &fa, const GosArgs &ga, cudaStream_t st, const char **err) {
+  using Gm = FGeo<S>;
+  static int occ_dev[64] = {0};
+  int &occ = occ_dev[c.device & 63];
+  const size_t smem = (size_t)Gm::CPC * (Gm::ROW + OGeo<S>::KW) * sizeof(uint32_t);
+  auto kernel = chain_fixed_fast_gosb_kernel<S, NWD, TWO>;
+  if (!occ) { const rsp_status s = launch_cfg(kernel, smem, Gm::THREADS, &occ, err); if (s != RSP_OK) return s; }
+  const unsigned groups = (fa.n_rows + Gm::CPC - 1) / Gm::CPC;
+  const unsigned grid = std::max(1u, std::min(groups, (unsigned)(c.sm_count * occ)));
+  kernel<<<grid, Gm::THREADS, smem, st>>>(fa, ga);
+  if (cudaGetLastError() != cudaSuccess) { *err = "chain_fixed_fast_gosb_kernel launch failed"; return RSP_ECUDA; }
+  return RSP_OK;
+}
+template <int S>
+static rsp_status launch_fast_gosb(const LaunchCtx &c, const FastArgs &fa, const GosArgs &ga, cudaStream_t st, const char **err) {
+  const int nwd = (fa.W + 31) / 32;
+  const bool two = ga.kl1 != ga.kr1;
+  switch (nwd * 2 + (two ? 1 : 0)) {
+    case 2: return launch_fast_gosb_inst<S, 1, false>(c, fa, ga, st, err);
+    case 3: return launch_fast_gosb_inst<S, 1, true>(c, fa, ga, st, err);
+    case 4: return launch_fast_gosb_inst<S, 2, false>(c, fa, ga, st, err);
+    case 5: return launch_fast_gosb_inst<S, 2, true>(c, fa, ga, st, err);
+    case 6: return launch_fast_gosb_inst<S, 3, false>(c, fa, ga, st, err);
+    case 7: return launch_fast_gosb_inst<S, 3, true>(c, fa, ga, st, err);
+    case 8: return launch_fast_gosb_inst<S, 4, false>(c, fa, ga, st, err);
+    default: return launch_fast_gosb_inst<S, 4, true>(c, fa, ga, st, err);
+  }
+}
+// the rank-counting kernel needs W to be a multiple of 8 and >= 8; RSP_FAST_GOS_BITPLANES=0 selects it where it can run (A/B knob)
+static bool gos_use_bitplanes(int W) {
+  static int on = -1;
+  if (on < 0) { const char *e = std::getenv("RSP_FAST_GOS_BITPLANES"); on = (e != nullptr && e[0] == '0') ? 0 : 1; }
+  return on || W < 8 || (W & 7);
+}
+
 template <int S>
 static rsp_status launch_fast_os(const LaunchCtx &c, const FastArgs &fa, const GosArgs &ga, cudaStream_t st, const char **err) {
   using Gm = FGeo<S>;
@@ -1324,7 +1439,7 @@ static rsp_status launch_fast_fft_lp(const LaunchCtx &c, const FastArgs &fa, cud
 rsp_status RSP_CAT(launch_fast_size_, RSP_FAST_S)(int core, int cmode, bool linear, int ej, const LaunchCtx &ctx, const FastArgs &fa, const GosArgs &ga,
                                                   cudaStream_t st, const char **err) {
   constexpr int S = RSP_FAST_S;
-  if (core == CORE_LIS) return launch_fast_gos<S>(ctx, fa, ga, st, err);
+  if (core == CORE_LIS) return gos_use_bitplanes(fa.W) ? launch_fast_gosb<S>(ctx, fa, ga, st, err) : launch_fast_gos<S>(ctx, fa, ga, st, err);
   if (core == CORE_OS) return launch_fast_os<S>(ctx, fa, ga, st, err);
 #if RSP_FAST_S == 10
   if (ej == 2) return launch_fast_modes<S, 2>(cmode, linear, ctx, fa, st, err);
@@ -1376,7 +1491,7 @@ rsp_status launch_fast_fft(const Plan &pl, const LaunchCtx &ctx, const FxArgs &a
 static bool fast_gos_supported(const FxArgs &a) {
   if (a.core != CORE_LIS || a.cfar_algorithm != 1) return false;
   if (a.in_w != 16 || a.in_bp != 0 || a.sc_bp != 0 || a.thr_bp != 0 || a.send_cut || a.peak_grouping) return false;
-  if (a.thr_w < 1 || a.thr_w > 32 || a.G < 0 || a.W < 8 || a.W > 128 || (a.W & 7)) return false;
+  if (a.thr_w < 1 || a.thr_w > 32 || a.G < 0 || a.W < 1 || a.W > 128) return false;   // (W not a multiple of 8: bit planes only)
   if (a.idx_lagg < 1 || a.idx_lagg > a.W || a.idx_lead < 1 || a.idx_lead > a.W) return false;
   return a.out != nullptr && a.binw + 1 <= 31;
 }

@@ -16,5 +16,5 @@ cap() { # name kernel-regex command...
 cap fx14 chain_fixed_fast_kernel python bench.py --steps 2 --warmup 3 --e2e-steps 1 --no-cpu-baseline --no-configs
 cap fx10 chain_fixed_fast_kernel python scripts/bench_one.py c2
 cap f32c3 chain_f32_fast_kernel python scripts/bench_one.py c3
-cap gos12 chain_fixed_fast_gos_kernel python scripts/bench_one.py c4os16
+cap gos12 chain_fixed_fast_gosb_kernel python scripts/bench_one.py c4os16
 ls -la gpurun_out | tail -20

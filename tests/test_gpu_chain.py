@@ -260,7 +260,8 @@ def test_c5_full_size_rows_are_independent(cuda, oracle):
 
 
 @pytest.mark.parametrize("log_n,W,G,kl,kr", [(10, 16, 2, 12, 12), (10, 64, 4, 48, 48), (11, 32, 0, 24, 7), (12, 64, 4, 48, 20), (13, 8, 1, 1, 8),
-                                              (14, 128, 8, 96, 96), (11, 24, 2, 20, 20), (12, 40, 3, 1, 40), (10, 72, 1, 72, 1)])
+                                              (14, 128, 8, 96, 96), (11, 24, 2, 20, 20), (12, 40, 3, 1, 40), (10, 72, 1, 72, 1),
+                                              (11, 13, 2, 5, 13), (12, 100, 3, 77, 30), (14, 97, 0, 50, 50), (13, 3, 0, 2, 2)])
 def test_fast_gos_kernel_variants(cuda, oracle, log_n, W, G, kl, kr):
     """chain_fixed_fast_gos<S> (rank-counting OS-CFAR): CA/GO/SO combination of the two order statistics, linear and log threshold,
     equal and different indexLagg / indexLead, ragged row counts, full-range random rows (ties, negative magnitudes)"""
