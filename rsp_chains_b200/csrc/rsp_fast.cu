@@ -1028,6 +1028,10 @@ __global__ void __launch_bounds__(FGeo<S>::THREADS, 1024 / FGeo<S>::THREADS) cha
 // instructions per plane and bin, independent of R, against 2 R compares per plane for the bitwise rank search of the run-time-parameter
 // kernel.  A thread owns 16 neighbouring bins, 8 at a time: their windows are 8 consecutive bit offsets of the same three plane words.
 // The planes are built by a 16 x 16 bit transpose in registers per thread; planes in which all cells of the chirp agree are skipped.
+#ifndef RSP_OS_SPARSE
+#define RSP_OS_SPARSE 1   // A/B knob: 0 = every window visits all the planes that are not uniform over the chirp
+#endif
+constexpr bool SPARSE = RSP_OS_SPARSE != 0;
 template <int S> struct OGeo {
   static constexpr int N = 1 << S;
   static constexpr int MW = 3, MB = 6;               // margin words in front of / behind each plane (windows that start before or end after the row)
@@ -1035,6 +1039,9 @@ template <int S> struct OGeo {
   static_assert(PW & 1, "odd plane stride");
   static_assert(16 * PW <= FGeo<S>::XB, "the bit planes fit the exchange buffer");
   static constexpr int KW = N;                       // extra words of the (A) kernel: two int16 K arrays
+  static constexpr int NZ = 16 * PW;                 // word offset (from the start of the exchange buffer) of the per-block plane masks
+  static constexpr int NZM = 16;                     // zero entries behind them (windows that end after the row)
+  static_assert(NZ + (N / 16 + NZM + 1) / 2 <= FGeo<S>::XB, "the plane masks fit the exchange buffer behind the planes");
 };
 
 // 16 x 16 bit-matrix transpose in 8 registers (word k = rows 2k | 2k+1 << 16): block swaps of size 8, 4, 2, 1.  In: row r = the 16-bit
@@ -1054,8 +1061,11 @@ __device__ __forceinline__ void bit_transpose16(uint32_t (&A)[8]) {
 // The thread's 16 neighbouring magnitudes (biased to offset binary: order preserved) -> its halfword of each of the 16 planes.
 // uni[0] / uni[1] collect the OR / AND of all cells of the chirp: a plane in which every cell has the same bit cannot change any
 // candidate set (all candidates have the bit: c >= k as long as k <= candidates; none has it: c = 0) and is skipped by the selection.
+// nz[t] = the planes in which at least one of thread t's 16 cells has its bit set: a selection step over a window whose cells all have
+// a 0 in the plane leaves every candidate set as it is (c = 0 < k), so the selection ORs the masks of the blocks its windows touch and
+// visits only those planes -- on radar rows (a few targets over a noise floor of a few LSB) most windows see three or four planes.
 template <int S>
-__device__ __forceinline__ void os_build_planes(const uint32_t *xm, int tl, uint32_t *bp, uint32_t *uni) {
+__device__ __forceinline__ void os_build_planes(const uint32_t *xm, int tl, uint32_t *bp, uint32_t *uni, uint16_t *nz) {
   constexpr int PW = OGeo<S>::PW;
   const uint32_t *xq = xm + mhx<S>(16 * tl) / 2;
   const uint4 v0 = *reinterpret_cast<const uint4 *>(xq), v1 = *reinterpret_cast<const uint4 *>(xq + 4);
@@ -1063,12 +1073,21 @@ __device__ __forceinline__ void os_build_planes(const uint32_t *xm, int tl, uint
   uint32_t orv = 0, andv = 0xFFFFFFFFu;
 #pragma unroll
   for (int k = 0; k < 8; ++k) { A[k] ^= 0x80008000u; orv |= A[k]; andv &= A[k]; }
+  nz[tl] = (uint16_t)(orv | (orv >> 16));
+  if (tl < OGeo<S>::NZM) nz[FGeo<S>::TPC + tl] = 0;
   orv = __reduce_or_sync(0xffffffffu, orv); andv = __reduce_and_sync(0xffffffffu, andv);
   if ((tl & 31) == 0) { atomicOr(&uni[0], (orv | (orv >> 16)) & 0xFFFFu); atomicAnd(&uni[1], andv & (andv >> 16) & 0xFFFFu); }
   bit_transpose16(A);
   uint16_t *bph = reinterpret_cast<uint16_t *>(bp) + tl;
 #pragma unroll
   for (int b = 0; b < 16; ++b) bph[b * 2 * PW] = (uint16_t)(A[b >> 1] >> (16 * (b & 1)));
+}
+
+// planes that can matter for windows over the bins lo .. hi (clamped to the row in front; the zero entries take care of the end)
+__device__ __forceinline__ uint32_t os_local_planes(const uint16_t *nz, uint32_t act, int lo, int hi) {
+  uint32_t m = 0;
+  for (int b = max(lo, 0) >> 4; b <= (hi >> 4); ++b) m |= nz[b];
+  return act & m;
 }
 
 // 8 consecutive window pairs of the combined-window statistic: leading words start at bit s0 + j, lagging words at bit s1 + j (j < 8) of
@@ -1154,6 +1173,7 @@ __global__ void __launch_bounds__(FGeo<S>::THREADS, 1024 / FGeo<S>::THREADS) cha
   uint32_t *xb = smem + (size_t)c * Gm::ROW, *xm = xb + Gm::XB;
   const short *X = reinterpret_cast<const short *>(xm);
   uint32_t *bp = xb + Go::MW;                         // plane b, word w (bins 32 w .. 32 w + 31): bp[b * PW + w]
+  uint16_t *nz = reinterpret_cast<uint16_t *>(xb + Go::NZ);
   const int R = a.W, G = a.G;
   const uint32_t mR = R >= 32 ? 0xFFFFFFFFu : ((1u << R) - 1u);
   const int kk0 = 2 * R - (3 * R) / 2;                // ascending index floor(1.5 R) of 2 R cells = the (2 R - floor(1.5 R))-th largest
@@ -1167,7 +1187,7 @@ __global__ void __launch_bounds__(FGeo<S>::THREADS, 1024 / FGeo<S>::THREADS) cha
     if (tl == 0) { uni[c][0] = 0u; uni[c][1] = 0xFFFFu; }
     load_beats<S, 4>(a, grow, no_gen, tl, 0, pre);
     fast_passes<S, 4>(a, c, tl, pre, grow, no_gen, xb, xm, loud);   // ends with a barrier: magnitudes in X, the exchange buffer is free
-    os_build_planes<S>(xm, tl, bp, uni[c]);
+    os_build_planes<S>(xm, tl, bp, uni[c], nz);
     chirp_sync<S>(c);
     const uint32_t act = uni[c][0] ^ uni[c][1];       // planes in which the chirp's cells differ
     uint32_t *gout = a.out + (size_t)row * N + PTS * tl;
@@ -1175,7 +1195,7 @@ __global__ void __launch_bounds__(FGeo<S>::THREADS, 1024 / FGeo<S>::THREADS) cha
     for (int h = 0; h < PTS / 8; ++h) {
       const int n0 = PTS * tl + 8 * h;
       uint32_t cl[8], cr[8];
-      os_select8<S>(bp, act, n0 - G - R, n0 + G + 1, mR, mR, kk0, cl, cr);
+      os_select8<S>(bp, SPARSE ? os_local_planes(nz, act, n0 - G - R, n0 + G + R + 7) : act, n0 - G - R, n0 + G + 1, mR, mR, kk0, cl, cr);
       uint32_t ow[8];
 #pragma unroll
       for (int j = 0; j < 8; ++j) {
@@ -1228,6 +1248,7 @@ chain_fixed_fast_gosb_kernel(const FastArgs a, const GosArgs ga) {
   const short *X = reinterpret_cast<const short *>(xm);
   short *KL = reinterpret_cast<short *>(xm + Gm::XM), *KR = TWO ? KL + N : KL;
   uint32_t *bp = xb + Go::MW;
+  uint16_t *nz = reinterpret_cast<uint16_t *>(xb + Go::NZ);
   const int W = a.W, G = a.G;
   const uint32_t mlast = (W & 31) ? ((1u << (W & 31)) - 1u) : 0xFFFFFFFFu;
   const uint32_t stride = gridDim.x * CPC;
@@ -1240,14 +1261,14 @@ chain_fixed_fast_gosb_kernel(const FastArgs a, const GosArgs ga) {
     if (tl == 0) { uni[c][0] = 0u; uni[c][1] = 0xFFFFu; }
     load_beats<S, 4>(a, grow, no_gen, tl, 0, pre);
     fast_passes<S, 4>(a, c, tl, pre, grow, no_gen, xb, xm, loud);
-    os_build_planes<S>(xm, tl, bp, uni[c]);
+    os_build_planes<S>(xm, tl, bp, uni[c], nz);
     chirp_sync<S>(c);
     const uint32_t act = uni[c][0] ^ uni[c][1];
 #pragma unroll 1
     for (int h = 0; h < (TWO ? 4 : 2); ++h) {          // window starts 16 tl + 8 (h & 1) + j; h >= 2: the leading statistic
       const int s0 = PTS * tl + 8 * (h & 1);
       uint32_t cw[8][NWD];
-      gos_select8<S, NWD>(bp, act, s0, mlast, (h < 2 ? ga.kl1 : ga.kr1) + 1, cw);
+      gos_select8<S, NWD>(bp, SPARSE ? os_local_planes(nz, act, s0, s0 + W + 6) : act, s0, mlast, (h < 2 ? ga.kl1 : ga.kr1) + 1, cw);
       short *K = h < 2 ? KL : KR;
       uint32_t kv[4];
 #pragma unroll

@@ -23,6 +23,27 @@ elif key == "c4os":
 elif key == "c4os16":
     os_regs = dict(fftWin=4096, thresholdScaler=2, logOrLinearMode=1, peakGrouping=0, cfarMode=0, windowCells=64, guardCells=4, indexLagg=48, indexLead=48)
     B.run_case("C4 x 16 GOS", B.fixed_params(4096, 64, 4, GOSCFARType), 12, os_regs, 16384, 1)
+elif key in ("c4os16d", "c4osbd"):      # the same on full-range random beats: every plane is populated everywhere (worst case of the bit-plane selection)
+    from rsp_chains_b200 import synth
+    from rsp_chains_b200.params import OSGoldenCFARType
+    import numpy as np
+    n, rows = 4096, 16384
+    b = key == "c4osbd"
+    regs = dict(fftWin=n, thresholdScaler=2, logOrLinearMode=1, peakGrouping=0, cfarMode=0, windowCells=32 if b else 64, guardCells=4, indexLagg=48, indexLead=48)
+    import rsp_chains_b200 as R, json
+    base = torch.from_numpy(synth.random_beats(64, n, seed=3).view(np.int32)).cuda()
+    d_in = base.repeat(rows // 64, 1).contiguous(); d_out = torch.empty_like(d_in)
+    with R.FftMagCfarChainVanilla(B.fixed_params(n, 64, 4, OSGoldenCFARType if b else GOSCFARType)) as ch:
+        ch.configure(12, 2, regs)
+        for _ in range(3): ch.run(d_in, rows, 1, out=d_out)
+        torch.cuda.synchronize()
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(11)]
+        ev[0].record()
+        for i in range(10):
+            ch.run(d_in, rows, 1, out=d_out); ev[i + 1].record()
+        torch.cuda.synchronize()
+        ms = float(np.median([ev[i].elapsed_time(ev[i + 1]) for i in range(10)]))
+        print(json.dumps({"config": key + " (full-range random beats)", "variant": ch.variant, "rows": rows, "n": n, "ms": round(ms, 4), "Msamples_per_s": round(rows * n / ms / 1e3, 1)}))
 elif key == "c4osb":
     from rsp_chains_b200.params import OSGoldenCFARType
     os_b = dict(fftWin=4096, thresholdScaler=2, logOrLinearMode=1, peakGrouping=0, cfarMode=0, windowCells=32, guardCells=4)

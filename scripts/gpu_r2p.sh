@@ -1,4 +1,4 @@
 #!/bin/bash
 mkdir -p gpurun_out
-timeout 900 python -m pytest tests/test_gpu_chain.py -m gpu -x -q -k "gos or os_cfar" 2>&1 | tail -8 | tee gpurun_out/pytest_gosb.txt
-for v in 1 0; do echo "RSP_FAST_GOS_BITPLANES=$v"; RSP_FAST_GOS_BITPLANES=$v timeout 300 python scripts/bench_one.py c4os16 2>&1 | tail -1 | cut -c1-200; done | tee gpurun_out/gosb_ab.txt
+timeout 900 python -m pytest tests/test_gpu_chain.py tests/test_gpu_round2.py -m gpu -x -q -k "gos or os" 2>&1 | tail -8 | tee gpurun_out/pytest_sparse.txt
+for k in c4os16 c4osb c4os16d c4osbd; do timeout 300 python scripts/bench_one.py $k 2>&1 | tail -1 | cut -c1-170; done | tee gpurun_out/sparse_ab.txt
