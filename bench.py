@@ -229,7 +229,7 @@ def config_lines(torch, peak):
     out = []
     ca = lambda n, W, G, ds, mode=0: dict(fftWin=n, thresholdScaler=4, logOrLinearMode=1, divSum=ds, peakGrouping=0, cfarMode=mode, windowCells=W, guardCells=G)  # noqa: E731
 
-    def case(name, params, log_n, regs, frame_rows, n_rx, frames, fp32=False, bps=8.0, note=None):
+    def case(name, params, log_n, regs, frame_rows, n_rx, frames, fp32=False, bps=8.0, note=None, dense=False):
         n = 1 << log_n
         rows = frame_rows * frames
         distinct = min(64, rows)
@@ -239,7 +239,8 @@ def config_lines(torch, peak):
             d_out = torch.empty((rows, n), dtype=torch.float32, device="cuda")
             d_mask = torch.zeros((rows, n // 32), dtype=torch.int32, device="cuda")
         else:
-            base = torch.from_numpy(synth.chirps_fixed(distinct, n, seed=1).view(np.int32)).cuda()
+            beats = synth.random_beats(distinct, n, seed=1) if dense else synth.chirps_fixed(distinct, n, seed=1)
+            base = torch.from_numpy(beats.view(np.int32)).cuda()
             d_in = base.repeat((rows + distinct - 1) // distinct, 1)[:rows].contiguous()
             d_out = torch.empty_like(d_in)
             d_mask = None
@@ -271,7 +272,9 @@ def config_lines(torch, peak):
              note="fp32 flavour; one frame is 48 MiB + 24 MiB out (L2-resident); batched = 16 frames")
     os_regs = dict(fftWin=4096, thresholdScaler=2, logOrLinearMode=1, peakGrouping=0, cfarMode=0, windowCells=64, guardCells=4, indexLagg=48, indexLead=48)
     case("C4 OS-CFAR 1024 x 4096 fixed, reading (A): GOS core, 64 cells per side, k=48", fixed_params(4096, 64, 4, R.GOSCFARType), 12, os_regs, 1024, 1, 16,
-         note="CFARCoreWithLis (indexLagg = indexLead = 48); one frame is 32 MiB (L2-resident)")
+         note="CFARCoreWithLis (indexLagg = indexLead = 48); radix selection on bit planes; one frame is 32 MiB (L2-resident)")
+    case("C4 reading (A) on full-range random beats (every bit plane populated everywhere: worst case of the selection)", fixed_params(4096, 64, 4, R.GOSCFARType), 12, os_regs, 1024, 1, 16,
+         dense=True, note="the bit-plane selection is data dependent; this is its slow end")
     os_b = dict(fftWin=4096, thresholdScaler=2, logOrLinearMode=1, peakGrouping=0, cfarMode=0, windowCells=32, guardCells=4)
     case("C4 OS-CFAR 1024 x 4096 fixed, reading (B): golden cfarOS, 32 + 32 cells in one sorted window, ascending index 48", fixed_params(4096, 64, 4, R.OSGoldenCFARType), 12, os_b, 1024, 1, 16,
          note="CFARUtils.scala:159-196 (no hardware core in the reference); radix selection on bit planes (chain_fixed_fast_os)")

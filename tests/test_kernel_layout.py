@@ -232,3 +232,61 @@ def test_fft_only_output_scatter_is_conflict_free_and_covers_the_row(S, LP):
         for w0 in range(0, TPC, 32):
             got, ideal = wavefronts([4 * wx(w0 + lane + j * TPC, S) for lane in range(32)], 4)
             assert got <= 2 * ideal
+
+
+# ---------------------------------------------------------------------------------------------------------------------
+# OS / GOS-CFAR on bit planes (chain_fixed_fast_os_kernel, chain_fixed_fast_gosb_kernel): the algorithms, step for step
+
+def bit_transpose16(A):
+    """rsp_fast.cu bit_transpose16: 8 words, word k = rows 2k | 2k+1 << 16; block swaps of size 8, 4, 2, 1"""
+    A = [int(a) for a in A]
+    M = 0xFFFFFFFF
+    for k in range(4):
+        t = ((A[k] >> 8) ^ A[k + 4]) & 0x00FF00FF; A[k + 4] ^= t; A[k] ^= (t << 8) & M
+    for k in (0, 1, 4, 5):
+        t = ((A[k] >> 4) ^ A[k + 2]) & 0x0F0F0F0F; A[k + 2] ^= t; A[k] ^= (t << 4) & M
+    for k in (0, 2, 4, 6):
+        t = ((A[k] >> 2) ^ A[k + 1]) & 0x33333333; A[k + 1] ^= t; A[k] ^= (t << 2) & M
+    for k in range(8):
+        t = ((A[k] >> 1) ^ (A[k] >> 16)) & 0x5555; A[k] ^= (t * 0x10002) & M
+    return A
+
+
+def test_bit_transpose16_turns_16_values_into_16_plane_halfwords():
+    import numpy as np
+    rng = np.random.default_rng(0)
+    for _ in range(300):
+        rows = [int(v) for v in rng.integers(0, 1 << 16, 16)]
+        T = bit_transpose16([rows[2 * k] | (rows[2 * k + 1] << 16) for k in range(8)])
+        for c in range(16):
+            assert (T[c // 2] >> (16 * (c % 2))) & 0xFFFF == sum(((rows[r] >> c) & 1) << r for r in range(16))
+
+
+def test_radix_selection_on_bit_planes_is_the_kth_largest_and_skipped_planes_change_nothing():
+    """gos_select8 / os_select8 for one window: from the top plane down, t = k - popc(cand & plane); t <= 0 keeps the candidates with the bit,
+    else the others and k = t.  Planes that are uniform over the row, or all zero over the window, are skipped (exact)."""
+    import numpy as np
+    rng = np.random.default_rng(1)
+    for trial in range(400):
+        W = int(rng.integers(1, 129))
+        k = int(rng.integers(1, W + 1))
+        hi = int(rng.choice([4, 300, 1 << 15, 1 << 16]))
+        lo_bias = int(rng.choice([0, 1 << 15]))
+        x = [min((int(v) + lo_bias), 0xFFFF) for v in rng.integers(0, hi, W)]      # biased (offset-binary) cells
+        if trial % 7 == 0:
+            x = [x[0]] * W                                                          # all ties
+        row_or, row_and = 0, 0xFFFF
+        for v in x: row_or |= v; row_and &= v
+        act = row_or ^ row_and                                                      # planes that are not uniform
+        act &= row_or                                                               # ... and not all zero over the window (os_local_planes)
+        cand, kk = (1 << W) - 1, k
+        for b in range(15, -1, -1):
+            if not (act >> b) & 1: continue
+            plane = sum(((x[i] >> b) & 1) << i for i in range(W))
+            m = cand & plane
+            t = kk - bin(m).count("1")
+            if t <= 0: cand = m
+            else: cand, kk = cand & ~plane, t
+        assert cand != 0
+        want = sorted(x, reverse=True)[k - 1]
+        assert all(x[i] == want for i in range(W) if (cand >> i) & 1)
