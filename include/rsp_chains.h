@@ -125,11 +125,13 @@ typedef struct {
   int32_t maxNumOfSamplesWidth, outputWidthInt, outputWidthFrac;
 } rsp_plfg_params;
 
-/* FixedNCOParams, standard-mode table + accumulator (generators/nco/src/main/scala/NCO.scala:14-83) */
+/* FixedNCOParams, standard-mode or rasterized table + accumulator (generators/nco/src/main/scala/NCO.scala:14-83) */
 typedef struct {
   int32_t tableSize, tableWidth, phaseWidth;
   int32_t phaseAccEnable;
-  int32_t rasterizedMode, nInterpolationTerms, ditherEnable;   /* non-zero -> RSP_EUNSUPPORTED */
+  int32_t rasterizedMode;  /* NCOTableRasterizedMode (NCOTable.scala:322-464): tableSize need not be a power of two, address = phase mod
+                            * tableSize, quadrant = (phase / tableSize) mod 4; phaseWidth must be log2Ceil(tableSize) + 2 (NCO.scala:56-62)      */
+  int32_t nInterpolationTerms, ditherEnable;   /* non-zero -> RSP_EUNSUPPORTED */
   int32_t useMultiplier;   /* the output multiplier and its two registers RSP_NCO_REG_* (NCOLazyModuleBlock.scala:262-269,354-364)   */
   int32_t useQAM;          /* non-zero -> RSP_EUNSUPPORTED */
   int32_t roundingMode;    /* rsp_trim, FixedNCOParams.roundingMode (default RoundHalfUp = 0): trim of the multiplier's product     */

@@ -75,7 +75,7 @@ class NcoCfg(C.Structure):
     _fields_ = [("table_size", C.c_int32), ("table_width", C.c_int32), ("phase_width", C.c_int32),
                 ("phase_acc_enable", C.c_int32), ("phase0", C.c_uint32), ("poff", C.c_uint32),
                 ("use_multiplier", C.c_int32), ("enable_multiplying", C.c_int32), ("multiplying_factor", C.c_uint32),
-                ("rounding_mode", C.c_int32)]
+                ("rounding_mode", C.c_int32), ("rasterized", C.c_int32)]
 
 
 class JRand(C.Structure):
@@ -410,11 +410,11 @@ def plfg_ram_word(slope, n_samples, sign_plus, reset, output_width=16, samples_w
 
 
 def nco_words(freq, table_size=128, table_width=16, phase_width=9, phase_acc_enable=True, phase0=0, poff=0, use_multiplier=False,
-              enable_multiplying=False, multiplying_factor=0, rounding_mode="RoundHalfUp"):
+              enable_multiplying=False, multiplying_factor=0, rounding_mode="RoundHalfUp", rasterized=False):
     freq = _i32(freq)
     out = np.zeros(freq.size, np.uint32)
     cfg = NcoCfg(table_size, table_width, phase_width, int(phase_acc_enable), phase0, poff, int(use_multiplier), int(enable_multiplying),
-                 int(multiplying_factor) & 0xFFFFFFFF, TRIM[rounding_mode] if isinstance(rounding_mode, str) else rounding_mode)
+                 int(multiplying_factor) & 0xFFFFFFFF, TRIM[rounding_mode] if isinstance(rounding_mode, str) else rounding_mode, int(rasterized))
     ph = lib().rspo_nco_words(C.byref(cfg), _p(freq, C.c_int32), _p(out, C.c_uint32), C.c_int64(freq.size))
     return out, ph
 

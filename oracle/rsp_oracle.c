@@ -1057,9 +1057,19 @@ uint32_t rspo_nco_words(const rspo_nco_cfg *c, const int32_t *freq, uint32_t *ou
     const uint32_t f = (uint32_t)freq[i] & pmask;
     phase = c->phase_acc_enable ? ((phase + f) & pmask) : f; /* (:313-321) */
     const uint32_t ph = (phase + c->poff) & pmask;           /* (:324) */
-    const uint32_t msbs = ph >> (pw - 2);
-    const uint32_t addr = (ph >> (pw - 2 - ab)) & (uint32_t)(ts - 1);
-    const uint32_t raddr = (0u - addr) & (uint32_t)(ts - 1); /* addrReverse (:172-174) */
+    uint32_t msbs, addr, raddr;
+    if (c->rasterized) {
+      /* NCOTableRasterizedMode (:334-336): addrR = phase % tableSize, msbs = (phase / tableSize) % 4; addrReverse = tableSize - addr (:356-358),
+       * which for addr 0 points past the table: that look-up is replaced by 1.0 (cosIsOne / sinIsOne, :385-413) */
+      addr = ph % (uint32_t)ts;
+      msbs = (ph / (uint32_t)ts) % 4u;
+      raddr = (uint32_t)ts - addr;
+      if (raddr >= (uint32_t)ts) raddr = 0; /* only with addr == 0, where the value is not used */
+    } else {
+      msbs = ph >> (pw - 2);
+      addr = (ph >> (pw - 2 - ab)) & (uint32_t)(ts - 1);
+      raddr = (0u - addr) & (uint32_t)(ts - 1); /* addrReverse (:172-174) */
+    }
     int32_t s, co;
     switch (msbs) { /* (:193-235), reversed lookup replaced by 1.0 when addr == 0 (:201,211,262-263) */
     case 0: s = tab[addr]; co = (addr == 0) ? one : tab[raddr]; break;

@@ -190,6 +190,7 @@ typedef struct {
   int32_t use_multiplier, enable_multiplying;
   uint32_t multiplying_factor;
   int32_t rounding_mode;   /* rspo trim type */
+  int32_t rasterized;      /* NCOTableRasterizedMode (NCOTable.scala:322-464): table_size need not be a power of two, phase_width = log2Ceil(table_size) + 2 */
 } rspo_nco_cfg;
 /* freq: PLFG words; out: Cat(cos16, sin16) beats (NCOLazyModuleBlock.scala:452); returns final phase */
 uint32_t rspo_nco_words(const rspo_nco_cfg *cfg, const int32_t *freq, uint32_t *out, int64_t n);

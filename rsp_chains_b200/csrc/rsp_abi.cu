@@ -614,6 +614,7 @@ static rsp_status prepare_generator(rsp_chain *c, uint64_t n_samples, GenArgs &g
   g.table_width = c->p.nco.tableWidth; g.phase_width = c->p.nco.phaseWidth;
   g.out_width = c->p.plfg.outputWidthInt + c->p.plfg.outputWidthFrac;
   g.phase_acc_enable = c->p.nco.phaseAccEnable ? 1 : 0;
+  g.rasterized = c->p.nco.rasterizedMode ? 1 : 0;
   g.poff = 0;   // poffType Fixed: no phase-offset port (NCOLazyModuleBlock.scala:246-271)
   g.mult_on = 0; g.mult_f = 0; g.mult_trim = c->p.nco.roundingMode;
   if (c->p.nco.useMultiplier) {
@@ -753,6 +754,7 @@ extern "C" rsp_status rsp_run_from_generator_static(rsp_chain *c, uint32_t n_chi
   g.table_width = c->p.nco.tableWidth; g.phase_width = c->p.nco.phaseWidth;
   g.out_width = c->p.plfg.outputWidthInt + c->p.plfg.outputWidthFrac;
   g.phase_acc_enable = c->p.nco.phaseAccEnable ? 1 : 0;
+  g.rasterized = c->p.nco.rasterizedMode ? 1 : 0;
   g.poff = 0;
   g.mult_on = 0; g.mult_f = 0; g.mult_trim = c->p.nco.roundingMode;
   if (c->p.nco.useMultiplier) {   // as prepare_generator (NCOLazyModuleBlock.scala:354)

@@ -35,6 +35,7 @@ struct GenArgs {
   const uint32_t *nco_full; // or null: the beat Cat(cos16, sin16) of EVERY phase word, 2^phaseWidth entries built by the host with
                             // nco_lookup itself (phaseWidth <= 12): one load instead of two look-ups and the quadrant logic
   int table_size, addr_bits, table_width, phase_width, out_width, phase_acc_enable;
+  int rasterized;           // NCOTableRasterizedMode (NCOTable.scala:322-464): address = phase mod tableSize, quadrant = (phase / tableSize) mod 4
   uint32_t poff;
   // output multiplier (NCOLazyModuleBlock.scala:354-364): mult_on = the factor is not exactly 1.0, mult_f = factor as FixedPoint(w, w - 2) raw
   int mult_on, mult_f, mult_trim;
@@ -52,9 +53,14 @@ RSP_HD uint32_t nco_multiply(const GenArgs &g, uint32_t beat) {
 // Cat(cos16, sin16) of one phase word (NCOTable.scala:193-235; NCOLazyModuleBlock.scala:452)
 RSP_HD uint32_t nco_lookup(const GenArgs &g, uint32_t ph) {
   const int pw = g.phase_width, ab = g.addr_bits, ts = g.table_size;
-  const uint32_t msbs = ph >> (pw - 2);
-  const uint32_t addr = (ph >> (pw - 2 - ab)) & (uint32_t)(ts - 1);
-  const uint32_t raddr = (0u - addr) & (uint32_t)(ts - 1);
+  uint32_t msbs, addr, raddr;
+  if (g.rasterized) {   // tableSize need not be a power of two; the reversed address tableSize - 0 is outside the table and stands for 1.0 (:362-364)
+    addr = ph % (uint32_t)ts; msbs = (ph / (uint32_t)ts) & 3u; raddr = addr == 0 ? 0u : (uint32_t)ts - addr;
+  } else {
+    msbs = ph >> (pw - 2);
+    addr = (ph >> (pw - 2 - ab)) & (uint32_t)(ts - 1);
+    raddr = (0u - addr) & (uint32_t)(ts - 1);
+  }
   const int one = 1 << (g.table_width - 2);
   const int fwd = ldg(&g.nco_tab[addr]);
   const int rev = addr == 0 ? one : ldg(&g.nco_tab[raddr]);   // the reversed look-up of address 0 is exactly 1.0 (:201,211,262-263)

@@ -111,10 +111,14 @@ inline rsp_status validate_params(const rsp_chain_params &p, std::string &err) {
     RSP_REQ(g.maxNumOfSegments <= 64 && g.maxNumOfDifferentChirps <= 256 && g.maxChirpOrdinalNum <= 256, RSP_EUNSUPPORTED, "PLFG tables too large");
     // FixedNCOParams (NCO.scala:54-55)
     RSP_REQ(n.tableWidth >= 3 && n.tableWidth <= 16, RSP_EINVAL, "tableWidth must be in 3..16");
-    RSP_REQ(is_pow2(n.tableSize) && n.tableSize <= 65536, RSP_EINVAL, "tableSize must be a power of 2");
-    RSP_REQ(n.phaseWidth >= log2_ceil((uint32_t)n.tableSize) + 2 && n.phaseWidth <= 32, RSP_EINVAL, "phaseWidth must cover quadrant + table address");
-    RSP_REQ(!n.rasterizedMode && !n.nInterpolationTerms && !n.ditherEnable && !n.useQAM, RSP_EUNSUPPORTED,
-            "NCO rasterized mode, Taylor terms, dither and QAM are not built");
+    RSP_REQ(n.tableSize >= 1 && n.tableSize <= 65536, RSP_EINVAL, "tableSize must be in 1..65536");
+    if (n.rasterizedMode) {   // NCOTableRasterizedMode: any table size; the phase width is not a parameter (NCO.scala:56-62, NCOTable.scala:48-54)
+      RSP_REQ(n.phaseWidth == log2_ceil((uint32_t)n.tableSize) + 2, RSP_EINVAL, "in rasterized mode phaseWidth = log2Ceil(tableSize) + 2 (NCO.scala:57-58)");
+    } else {
+      RSP_REQ(is_pow2(n.tableSize), RSP_EINVAL, "Table Size must be a power of 2 when working in standard mode");   // NCOTable.scala:103
+      RSP_REQ(n.phaseWidth >= log2_ceil((uint32_t)n.tableSize) + 2 && n.phaseWidth <= 32, RSP_EINVAL, "phaseWidth must cover quadrant + table address");
+    }
+    RSP_REQ(!n.nInterpolationTerms && !n.ditherEnable && !n.useQAM, RSP_EUNSUPPORTED, "NCO Taylor terms, dither and QAM are not built");
     RSP_REQ(n.roundingMode >= 0 && n.roundingMode <= RSP_TRIM_NO_TRIM, RSP_EINVAL, "unknown NCO roundingMode");
     RSP_REQ(p.arith == RSP_ARITH_FIXED, RSP_EUNSUPPORTED, "the PLFG/NCO generator feeds the fixed-point chain only");
   }
@@ -271,7 +275,7 @@ inline void build_tables(const rsp_chain_params &p, Tables &t) {
     std::memset(&g, 0, sizeof(g));
     g.nco_tab = t.nco_tab.data();   // host pointer: nco_lookup is the same code on both sides
     g.table_size = p.nco.tableSize; g.addr_bits = log2_ceil((uint32_t)p.nco.tableSize);
-    g.table_width = p.nco.tableWidth; g.phase_width = p.nco.phaseWidth;
+    g.table_width = p.nco.tableWidth; g.phase_width = p.nco.phaseWidth; g.rasterized = p.nco.rasterizedMode ? 1 : 0;
     t.nco_full.resize((size_t)1 << p.nco.phaseWidth);
     for (uint32_t ph = 0; ph < (1u << p.nco.phaseWidth); ++ph) t.nco_full[ph] = nco_lookup(g, ph);
   }

@@ -229,7 +229,14 @@ class FixedNCOParams:
     useMultiplier: bool = False
     useQAM: bool = False
 
+    def __post_init__(self):
+        assert self.tableWidth >= 3                                     # NCO.scala:54
+        if self.rasterizedMode:                                         # phaseW = log2Ceil(tableSize) + 2 (NCO.scala:56-62)
+            self.phaseWidth = log2Up(self.tableSize) + 2 if self.tableSize > 1 else 2
+
     def to_c(self) -> _abi.NcoParams:
+        if self.rasterizedMode:
+            self.phaseWidth = log2Up(self.tableSize) + 2 if self.tableSize > 1 else 2
         return _abi.NcoParams(self.tableSize, self.tableWidth, self.phaseWidth, int(self.phaseAccEnable),
                               int(self.rasterizedMode), self.nInterpolationTerms, int(self.ditherEnable),
                               int(self.useMultiplier), int(self.useQAM), _abi.TRIM[self.roundingMode])

@@ -197,6 +197,7 @@ int rsp_emu_generate(const rsp_chain_params *p, const uint32_t *plfg_regs, int n
   g.table_size = h.p.nco.tableSize; g.addr_bits = log2_ceil((uint32_t)h.p.nco.tableSize); g.table_width = h.p.nco.tableWidth;
   g.phase_width = h.p.nco.phaseWidth; g.out_width = h.p.plfg.outputWidthInt + h.p.plfg.outputWidthFrac;
   g.phase_acc_enable = h.p.nco.phaseAccEnable ? 1 : 0;
+  g.rasterized = h.p.nco.rasterizedMode ? 1 : 0;
   g.mult_trim = h.p.nco.roundingMode;
   if (h.p.nco.useMultiplier) {
     const int w = h.p.nco.tableWidth;

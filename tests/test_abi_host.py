@@ -96,6 +96,10 @@ def test_requires_and_no_cpu_fallback():
     assert st == _abi.RSP_EINVAL and "Radix" in msg                             # SDFFFTParams.scala:61-64
     st, msg = _create(variant(nco__ditherEnable=1))
     assert st == _abi.RSP_EUNSUPPORTED
+    st, msg = _create(variant(nco__tableSize=100))                               # NCOTable.scala:103
+    assert st == _abi.RSP_EINVAL and "power of 2" in msg
+    st, msg = _create(variant(nco__tableSize=100, nco__rasterizedMode=1, nco__phaseWidth=10))   # NCO.scala:56-62: not a parameter in this mode
+    assert st == _abi.RSP_EINVAL and "log2Ceil(tableSize) + 2" in msg
     if not torch.cuda.is_available():
         st, msg = _create(base)
         assert st == _abi.RSP_ECUDA and "no CPU path" in msg

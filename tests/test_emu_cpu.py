@@ -216,7 +216,9 @@ def test_emu_fp32_flavour(emu, oracle, core):
 
 @pytest.mark.parametrize("nco_kw,plfg_kw", [(dict(), dict()), (dict(phaseAccEnable=False), dict()), (dict(phaseWidth=14, tableSize=1024), dict()),
                                             (dict(phaseWidth=12, tableSize=256, tableWidth=12), dict(outputWidthInt=12, outputWidthFrac=4)),
-                                            (dict(useMultiplier=True, roundingMode="Convergent"), dict())])
+                                            (dict(useMultiplier=True, roundingMode="Convergent"), dict()),
+                                            (dict(rasterizedMode=True, tableSize=100), dict()),                      # phaseWidth 9: beat table
+                                            (dict(rasterizedMode=True, tableSize=3000), dict())])                    # phaseWidth 14: look-up in the kernel
 @pytest.mark.parametrize("frame_num,inter", [(3, 9), (0, 5), (2, 1)])
 def test_emu_generator(emu, oracle, nco_kw, plfg_kw, frame_num, inter):
     """the planner's segment list + the device's closed form, running form (runs of 8 as generator_kernel) and the fused kernel's
@@ -256,7 +258,7 @@ def test_emu_generator(emu, oracle, nco_kw, plfg_kw, frame_num, inter):
     assert len(want_plfg) == total and (plfg == want_plfg).all()
     n = p.ncoParams
     want, _ = oracle.nco_words(want_plfg, n.tableSize, n.tableWidth, n.phaseWidth, n.phaseAccEnable, use_multiplier=n.useMultiplier,
-                               enable_multiplying=bool(mult[0]), multiplying_factor=mult[1], rounding_mode=n.roundingMode)
+                               enable_multiplying=bool(mult[0]), multiplying_factor=mult[1], rounding_mode=n.roundingMode, rasterized=n.rasterizedMode)
     assert (closed == want).all() and (running == want).all()
     if n.phaseWidth <= 12 and not n.useMultiplier:
         assert (table == want).all()      # the fused kernel's beats

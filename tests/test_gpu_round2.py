@@ -622,3 +622,40 @@ def test_fast_os_kernel_bit_planes(cuda, oracle, log_n, Rc, G, lin):
         cuda.cuda.synchronize()
         got1 = from_dev_u32(d_out)
         assert (got1[0] == want[0]).all() and not got1[1:].any()
+
+
+@pytest.mark.parametrize("table_size", [100, 96, 3000, 128])
+def test_nco_rasterized_mode(cuda, oracle, table_size):
+    """FixedNCOParams(rasterizedMode = true) (NCOTable.scala:322-464): a table that is not a power of two (phaseWidth 9 and 14: the host-built
+    beat table and the look-up in the kernel), the generator alone and the chain fed by it (fused first pass where the beat table exists),
+    bit for bit against the oracle; a power-of-two table equals the standard mode."""
+    p = R.rsp_chain_vanilla_app_params()
+    p.ncoParams.rasterizedMode = True
+    p.ncoParams.tableSize = table_size
+    regs = dict(fftWin=1024, thresholdScaler=4, logOrLinearMode=1, divSum=5, peakGrouping=0, cfarMode=0, windowCells=32, guardCells=4)
+    order, repeats, start = [2, 0, 1, 3, 0], [2, 1, 3, 1, 2], 37
+    total, n_rows = 6 * 1024 + 100, 6
+    with R.RspChainVanilla(p) as ch:
+        configure(ch, 10, 2, regs)
+        write_plfg(ch, p, oracle, start, CHIRPS, order, repeats, 0, 7)
+        d_nco = cuda.zeros(total, dtype=cuda.int32, device="cuda")
+        d_plfg = cuda.zeros(total, dtype=cuda.int32, device="cuda")
+        ch.generate(total, d_nco, d_plfg)
+        d_out = cuda.zeros((n_rows, 1024), dtype=cuda.int32, device="cuda")
+        ch.run_from_generator(n_rows, 1, out=d_out)
+        d_out2 = cuda.zeros((n_rows, 1024), dtype=cuda.int32, device="cuda")
+        ch.run_from_generator_static(n_rows, 1, out=d_out2)
+        cuda.cuda.synchronize()
+        got_nco, got_plfg, got_out, got_out2 = from_dev_u32(d_nco), d_plfg.cpu().numpy(), from_dev_u32(d_out), from_dev_u32(d_out2)
+    n = p.ncoParams
+    assert n.phaseWidth == max(1, (table_size - 1).bit_length()) + 2
+    want_plfg = oracle_plfg(oracle, p, start, CHIRPS, order, repeats, 0, 7).run(total)
+    assert (got_plfg == want_plfg).all()
+    want_nco, _ = oracle.nco_words(want_plfg, n.tableSize, n.tableWidth, n.phaseWidth, n.phaseAccEnable, rasterized=True)
+    assert (got_nco == want_nco).all(), f"first difference at {np.argwhere(got_nco != want_nco)[:3].ravel()}"
+    if table_size == 128:
+        std, _ = oracle.nco_words(want_plfg, 128, 16, 9, True)
+        assert (want_nco == std).all()
+    fft, mag, cfar = oracle_cfgs(oracle, p, 10, 2, regs)
+    want_out = oracle.chain_fixed_words(fft, mag, cfar, want_nco[:n_rows * 1024].reshape(n_rows, 1024))
+    assert (got_out == want_out).all() and (got_out2 == want_out).all()

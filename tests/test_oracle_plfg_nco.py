@@ -236,3 +236,30 @@ def test_nco_output_multiplier(oracle):
     assert (nc == np.where(pc == 16384, -16384, -pc)).all() and (ns == -ps).all()
     fl, _ = oracle.nco_words(freq, 256, 16, 10, use_multiplier=True, enable_multiplying=True, multiplying_factor=0x1000, rounding_mode="Floor")
     assert (oracle.unpack_iq(fl)[0] == pc >> 2).all()
+
+
+def test_nco_rasterized_mode():
+    """NCOTableRasterizedMode (NCOTable.scala:322-464): address = phase mod tableSize, quadrant = (phase / tableSize) mod 4, phaseWidth =
+    log2Ceil(tableSize) + 2 (NCO.scala:56-62).  With a power-of-two table it IS the standard mode; with any other size the 4 * tableSize
+    phase values of one turn give sin / cos within half an LSB of the real functions (the NCO specs' tolerance is looser), the reversed look-up of
+    address 0 is exactly 1.0, and the phase words past 4 * tableSize start the next turn (the accumulator still wraps at 2^phaseWidth)."""
+    from oracle import oracle as O
+    f = (np.arange(0, 2000, dtype=np.int32) * 7) % 41
+    for ts, pw in ((128, 9), (256, 10), (1024, 12)):
+        a, pa = O.nco_words(f, ts, 16, pw, True)
+        b, pb = O.nco_words(f, ts, 16, pw, True, rasterized=True)
+        assert (a == b).all() and pa == pb
+    for ts in (100, 96, 3, 1000, 3000):
+        pw = max(1, (ts - 1).bit_length()) + 2
+        ph = np.arange(1 << pw, dtype=np.int32)
+        w, _ = O.nco_words(ph, ts, 16, pw, False, rasterized=True)
+        s = ((w & 0xFFFF).astype(np.int64) ^ 0x8000) - 0x8000
+        c = (((w >> 16) & 0xFFFF).astype(np.int64) ^ 0x8000) - 0x8000
+        ang = 2 * np.pi * (ph % (4 * ts)) / (4 * ts)
+        assert np.abs(s - np.sin(ang) * 16384).max() <= 0.5 + 1e-9 and np.abs(c - np.cos(ang) * 16384).max() <= 0.5 + 1e-9
+        assert c[0] == 16384 and s[ts] == 16384 and c[2 * ts] == -16384 and s[3 * ts] == -16384     # the four exact 1.0
+        assert (w[4 * ts:] == w[:(1 << pw) - 4 * ts]).all()                                        # next turn before the accumulator wraps
+        # accumulating: phase = running sum mod 2^pw, then the same table
+        f2 = np.full(500, 37, dtype=np.int32)
+        acc, _ = O.nco_words(f2, ts, 16, pw, True, rasterized=True)
+        assert (acc == w[(np.cumsum(f2.astype(np.int64)) % (1 << pw))]).all()
