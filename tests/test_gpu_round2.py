@@ -659,3 +659,31 @@ def test_nco_rasterized_mode(cuda, oracle, table_size):
     fft, mag, cfar = oracle_cfgs(oracle, p, 10, 2, regs)
     want_out = oracle.chain_fixed_words(fft, mag, cfar, want_nco[:n_rows * 1024].reshape(n_rows, 1024))
     assert (got_out == want_out).all() and (got_out2 == want_out).all()
+
+
+def test_unaligned_output_pointers_take_the_other_kernel_and_give_the_same_beats(cuda, oracle):
+    """the bit-plane OS kernel stores 128-bit words and the fast kernels prefetch 16-byte aligned rows: a caller's buffer that starts at an
+    odd word must still give the same beats (the planner falls back to 32-bit stores / the run-time-parameter kernel)"""
+    n, log_n = 4096, 12
+    beats = synth.chirps_fixed(5, n, seed=123)
+    for ctype, regs in ((R.OSGoldenCFARType, dict(fftWin=n, thresholdScaler=2, logOrLinearMode=1, peakGrouping=0, cfarMode=0, windowCells=32, guardCells=4)),
+                        (GOSCFARType, dict(fftWin=n, thresholdScaler=2, logOrLinearMode=1, peakGrouping=0, cfarMode=0, windowCells=64, guardCells=4, indexLagg=48, indexLead=48)),
+                        (CACFARType, dict(fftWin=n, thresholdScaler=4, logOrLinearMode=1, divSum=6, peakGrouping=0, cfarMode=0, windowCells=64, guardCells=4))):
+        p = fixed_params(n, 64, 4, ctype=ctype)
+        fft, mag, cfar = oracle_cfgs(oracle, p, log_n, 2, regs)
+        want = oracle.chain_fixed_words(fft, mag, cfar, beats)
+        with R.FftMagCfarChainVanilla(p) as ch:
+            configure(ch, log_n, 2, regs)
+            flat_in = cuda.zeros(5 * n + 3, dtype=cuda.int32, device="cuda")
+            flat_out = cuda.zeros(5 * n + 3, dtype=cuda.int32, device="cuda")
+            for off in (0, 1, 3):
+                d_in = flat_in[off:off + 5 * n].view(5, n)
+                d_in.copy_(to_dev(cuda, beats))
+                d_out = flat_out[off:off + 5 * n].view(5, n)
+                d_out.zero_()
+                ch.run(d_in, 5, 1, out=d_out)
+                d_f = flat_out.new_zeros(5 * n + 3)[off:off + 5 * n].view(5, n)
+                ch.fft(d_in, 5, d_f)
+                cuda.cuda.synchronize()
+                assert (from_dev_u32(d_out) == want).all(), (ctype, off)
+                assert (from_dev_u32(d_f) == oracle.fft_fixed_words(fft, beats)).all(), (ctype, off)
