@@ -27,7 +27,11 @@ rows.append(f"| same through `rsp_run_host` (`e2e`, 2 GiB H2D + 2 GiB D2H per st
 d = e["detections_only"]
 rows.append(f"| same, detections only (`e2e.detections_only`: `h_out = NULL`, {d['detections_per_step']:,} detections back) | 3-deep chunk pipeline | 1 | {f(d['value'])} | "
             f"{d['value'] * 4 / 1e3:.1f} H2D | - | - | - |")
-rows.append("| C5, 2 frames on 2 GPUs (`gpurun --gpus 2`, visit i, before the last kernel changes) | `chain_fixed_fast<14>` | 2 | 335,798 (e2e 20,210) | - | - | 20.6 per GPU | - |")
+two = os.path.join(ROOT, "profiles", f"r02_{tag}_bench_2gpu.json")
+if os.path.exists(two):
+    t2 = last_json(two)
+    rows.append(f"| C5, 2 frames on 2 GPUs (`gpurun --gpus 2`, one frame per GPU per step) | `chain_fixed_fast<14>` | 2 | {f(t2['value'])} (e2e {f(t2['e2e']['value'])}) | "
+                f"{t2['value'] * 8 / 1e3:.0f} | - | {t2['value'] * 8 / 1e3 / PEAK / 2 * 100:.1f} per GPU | - |")
 for c in line["configs"]:
     one = f" (one frame {f(c['one_frame_Msamples_per_s'])})" if c.get("one_frame_Msamples_per_s") else ""
     g = c["GBps_algorithmic"]
@@ -42,5 +46,7 @@ s = re.sub(r"[0-9.]+ Msamples/s on 16384-point rows of the same workload; `e2e` 
            f"{ref['value']:.1f} Msamples/s on 16384-point rows of the same workload; `e2e` ÷ that = {e['value'] / ref['value']:.0f} ×, device-resident\n"
            f"`value` ÷ that = {v / ref['value']:.0f} ×", s)
 s = re.sub(r"\(`rsp_gather_detections`, outside the step\): [0-9.]+ ms at N = 1", f"(`rsp_gather_detections`, outside the step): {line['gather_ms']:.3f} ms at N = 1", s)
+if os.path.exists(two):
+    s = re.sub(r"ms at N = 1, [0-9.]+ ms at N = 2", f"ms at N = 1, {last_json(two)['gather_ms']:.3f} ms at N = 2", s)
 open(path, "w").write(s)
 print(len(rows), "rows;", "value", f(v), "e2e", f(e["value"]), "ref", f"{ref['value']:.1f}")
