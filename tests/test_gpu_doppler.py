@@ -155,3 +155,48 @@ def test_fft_block_alone_on_the_fast_passes(cuda, oracle, log_n):
         ch.fft(d_in, beats.shape[0], d_out)
         cuda.cuda.synchronize()
         assert (from_dev_u32(d_out) == want_w).all()
+
+
+def test_range_doppler_chain_fp32_flavour(cuda, oracle):
+    """the same chain in the DspReal flavour: float2 beats through both transforms (FFT(x)/N each), the 8-byte corner turn, JPL magnitude
+    + RX mean in floats, CA-CFAR along Doppler; 1e-4 relative against the fp64 dataflow and identical decided detections"""
+    from tests.test_gpu_f32_gen import f32_params
+    from oracle.glue import unpack_mask
+    n_rx, m, n, W, G, scaler = 4, 64, 256, 16, 2, 4.0
+    rng = np.random.default_rng(3)
+    t = np.arange(n)[None, None, :] / n
+    k = np.arange(m)[None, :, None]
+    rx = np.arange(n_rx)[:, None, None]
+    x = 0.35 * np.exp(2j * np.pi * (32 * t + k / 8 + rx / 16)) + 0.2 * np.exp(2j * np.pi * (64 * t + 3 * k / 4 - rx / 8))
+    x = x + (rng.normal(size=x.shape) + 1j * rng.normal(size=x.shape)) * 2.0 ** -6
+    x32 = np.stack([x.real, x.imag], axis=-1).astype(np.float32)
+    xq = x32[..., 0].astype(np.float64) + 1j * x32[..., 1].astype(np.float64)
+    regs = dict(fftWin=m, logOrLinearMode=1, divSum=4, peakGrouping=0, cfarMode=0, windowCells=W, guardCells=G)
+    with R.RangeDopplerChain(f32_params(n, W, G), f32_params(m, W, G), n_rx) as rd:
+        configure(rd.range, 8, 2, dict(regs, fftWin=n))
+        configure(rd.doppler, 6, 2, regs)
+        rd.doppler.set_threshold_scaler_f32(scaler)
+        d_in = cuda.from_numpy(x32).cuda()
+        d_thr = cuda.zeros((n, m), dtype=cuda.float32, device="cuda")
+        d_mask = cuda.zeros((n, m // 32), dtype=cuda.int32, device="cuda")
+        st = rd.stages(d_in)
+        rd.run(d_in, out=d_thr, peak_mask=d_mask)
+        cuda.cuda.synchronize()
+        comb = st["combined"].cpu().numpy().reshape(n, m)
+        thr = d_thr.cpu().numpy()
+        pk = unpack_mask(d_mask.cpu().numpy().view(np.uint32), m)
+    rd64 = np.fft.fft(np.fft.fft(xq, axis=2) / n, axis=1) / m                      # [rx][doppler][range]
+    re, im = np.abs(rd64.real), np.abs(rd64.imag)
+    u, v = np.maximum(re, im), np.minimum(re, im)
+    want_comb = np.maximum(u + v / 8, 7 * u / 8 + v / 2).mean(axis=0).T            # [range][doppler]
+    scale = want_comb.max()
+    assert (np.abs(comb - want_comb) / np.maximum(want_comb, 1e-3 * scale)).max() < 1e-4
+    cfg = oracle.cfar_cfg(m, W, G, 0, core=oracle.CORE_MEM, cfar_mode=0, div_sum=4, log_or_linear=1, peak_grouping=0, guard_window_size=G)
+    want_thr = np.zeros((n, m)); want_pk = np.zeros((n, m), np.uint8)
+    for r in range(n):
+        want_thr[r], want_pk[r] = oracle.cfar_f64(cfg, scaler, want_comb[r])
+    rel = np.abs(thr - want_thr) / np.maximum(np.abs(want_thr), 1e-3 * np.abs(want_thr).max())
+    assert rel.max() < 1e-4, rel.max()
+    decided = np.abs(want_comb - want_thr) / np.maximum(np.abs(want_thr), 1e-30) > 1e-3
+    assert (pk[decided] == want_pk[decided]).all()
+    assert pk[32, m // 8] and pk[64, (3 * m) // 4]
