@@ -54,6 +54,7 @@ struct FastArgs {
   int l2_prefetch;       // 1: one thread asks the L2 for the CTA's next row (cp.async.bulk.prefetch.L2) while this row is transformed
   int stage;             // 1: the next row's beats are fetched with cp.async into a staging area behind the CTA's rows while this
                          // row's CFAR phase runs (chain_fixed_fast_kernel); needs 16-byte aligned rows and N more words per chirp
+  int pg_full;   // peak grouping (PG kernels): 1 = guardCells equals the generator's guardWindowSize, the left neighbour is read (CFARCoreWithMem.scala:182-184)
 };
 
 // Exchange-buffer index of point p.  The pads are chosen per size by the shared-memory model in tests/test_kernel_layout.py so
@@ -497,9 +498,11 @@ __device__ __forceinline__ int chirp_scan_exclusive(int total, int c, int tl, in
 // window borders, so every load is [register + immediate].  EDGE: the bin may miss one of its windows (one-sided threshold,
 // CFARCoreWithMem.scala:154-171); the indices are clamped so that no load leaves the chirp's arrays.
 // !has_out (the caller wants the detection list only): no output beat is built or stored.
-template <int S, int LP, int CMODE, bool LINEAR, bool EDGE>
+// PG: peak grouping -- a peak must also exceed its two "neighbours" as the core's guard registers deliver them: laggGuard.last = x[n + 1]
+// (0 unless guardCells == guardWindowSize) and laggGuard.head = x[n + guardCells] (CFARCoreWithMem.scala:182-184; both from the lagging side).
+template <int S, int LP, int CMODE, bool LINEAR, bool EDGE, bool PG = false>
 __device__ __forceinline__ int fast_cfar_bin(const FastArgs &a, int j, int tl, int n2, const int *P, const int *pA, const int *pB,
-                                             const int *pC, const int *pD, const short *X, uint32_t *gout, bool has_out) {
+                                             const int *pC, const int *pD, const short *X, uint32_t *gout, bool has_out, const short *X0 = nullptr) {
   constexpr int N = 1 << S, TPC = FGeo<S, LP>::TPC;
   const int n = tl + j * TPC;
   int L, R;
@@ -520,7 +523,14 @@ __device__ __forceinline__ int fast_cfar_bin(const FastArgs &a, int j, int tl, i
   const int thr = LINEAR ? t * a.scaler : fadd(1, t, 1, a.scaler, a.one, a.m1);
   const int cut = X[mhx<S>(j * TPC)];   // X points at the thread's first bin (mhx is additive over tl + j * TPC)
   // peak = cut > thr as the sign bit of thr - cut (|thr| < 2^31 - 2^16 is checked by the host)
-  const int pk = (int)((uint32_t)fadd(1, thr, -1, cut, a.one, a.m1) >> 31);
+  int pk = (int)((uint32_t)fadd(1, thr, -1, cut, a.one, a.m1) >> 31);
+  if (PG) {
+    const int n1 = n + 1, ng = n + a.G;
+    int left = 0, right = 0;
+    if (a.pg_full && (!EDGE || n1 < N)) left = X0[mhx<S>(n1)];
+    if (!EDGE || ng < N) right = X0[mhx<S>(ng)];
+    pk = (pk != 0 && cut > left && cut > right) ? 1 : 0;
+  }
   if (has_out) {
     const int w0 = (int)(((uint32_t)thr & a.thr_mask) * (uint32_t)a.out_mul + (uint32_t)n2);   // threshold field | bin field (n << 1)
     gout[n] = (uint32_t)fadd(1, pk, 1, w0, a.one, a.m1);
@@ -562,7 +572,7 @@ __device__ __noinline__ void fast_detections(const FastDetArgs a, int tl, uint32
 template <int S, int LP> constexpr int fast_min_blocks() {
   return (S == 14 && RSP_FAST_MINB14 > 0) ? RSP_FAST_MINB14 : ((S == 10 && RSP_FAST_MINB10 > 0) ? RSP_FAST_MINB10 : 1024 / FGeo<S, LP>::THREADS);
 }
-template <int S, int LP, int CMODE, bool LINEAR, int EJ>
+template <int S, int LP, int CMODE, bool LINEAR, int EJ, bool PG = false>
 __global__ void __launch_bounds__(FGeo<S, LP>::THREADS, fast_min_blocks<S, LP>()) chain_fixed_fast_kernel(const FastArgs a) {
   using Gm = FGeo<S, LP>;
   constexpr int N = Gm::N, TPC = Gm::TPC, CPC = Gm::CPC, PTS = Gm::PTS;
@@ -676,8 +686,8 @@ __global__ void __launch_bounds__(FGeo<S, LP>::THREADS, fast_min_blocks<S, LP>()
 #pragma unroll
     for (int j = 0; j < PTS; ++j) {
       int pk;
-      if (j < EJ || j >= PTS - EJ) pk = fast_cfar_bin<S, LP, CMODE, LINEAR, true>(a, j, tl, n2, P, pA, pB, pC, pD, Xt, gout, has_out);
-      else pk = fast_cfar_bin<S, LP, CMODE, LINEAR, false>(a, j, tl, n2, P, pA, pB, pC, pD, Xt, gout, has_out);
+      if (j < EJ || j >= PTS - EJ) pk = fast_cfar_bin<S, LP, CMODE, LINEAR, true, PG>(a, j, tl, n2, P, pA, pB, pC, pD, Xt, gout, has_out, X);
+      else pk = fast_cfar_bin<S, LP, CMODE, LINEAR, false, PG>(a, j, tl, n2, P, pA, pB, pC, pD, Xt, gout, has_out, X);
       mask = mask * 2u + (uint32_t)pk;
       n2 += 2 * TPC;
     }
@@ -1336,7 +1346,7 @@ static int fast_lp_runtime(int S) {
   return S == 14 ? lp14 : 4;
 }
 
-template <int S, int LP, int CMODE, bool LINEAR, int EJ>
+template <int S, int LP, int CMODE, bool LINEAR, int EJ, bool PG = false>
 static rsp_status launch_fast_inst_lp(const LaunchCtx &c, const FastArgs &fa_in, cudaStream_t st, const char **err) {
   using Gm = FGeo<S, LP>;
   static int occ_dev[64] = {0};
@@ -1345,7 +1355,7 @@ static rsp_status launch_fast_inst_lp(const LaunchCtx &c, const FastArgs &fa_in,
   if (LP != 4) fa.stage = 0;
   const bool stage = LP == 4 && fast_stage_enabled(S);
   const size_t smem = ((size_t)Gm::CPC * (Gm::ROW + (Gm::TWS == 0 && stage ? Gm::N : 0)) + Gm::TWS) * sizeof(uint32_t);
-  auto kernel = chain_fixed_fast_kernel<S, LP, CMODE, LINEAR, EJ>;
+  auto kernel = chain_fixed_fast_kernel<S, LP, CMODE, LINEAR, EJ, PG>;
   if (!occ) { const rsp_status s = launch_cfg(kernel, smem, Gm::THREADS, &occ, err); if (s != RSP_OK) return s; }
   const unsigned groups = (fa.n_rows + Gm::CPC - 1) / Gm::CPC;
   const unsigned grid = std::max(1u, std::min(groups, (unsigned)(c.sm_count * occ)));
@@ -1354,22 +1364,26 @@ static rsp_status launch_fast_inst_lp(const LaunchCtx &c, const FastArgs &fa_in,
   return RSP_OK;
 }
 template <int S, int CMODE, bool LINEAR, int EJ>
-static rsp_status launch_fast_inst(const LaunchCtx &c, const FastArgs &fa, cudaStream_t st, const char **err) {
+static rsp_status launch_fast_inst(const LaunchCtx &c, const FastArgs &fa, bool pg, cudaStream_t st, const char **err) {
+  if (pg) {   // (one geometry per size: the peak-grouping kernels are the registers' other setting, not a tuning target)
+    if constexpr (S == 14) return launch_fast_inst_lp<S, 5, CMODE, LINEAR, EJ, true>(c, fa, st, err);
+    else return launch_fast_inst_lp<S, 4, CMODE, LINEAR, EJ, true>(c, fa, st, err);
+  }
   if constexpr (S == 14) { if (fast_lp_runtime(S) == 5) return launch_fast_inst_lp<S, 5, CMODE, LINEAR, EJ>(c, fa, st, err); }
   return launch_fast_inst_lp<S, 4, CMODE, LINEAR, EJ>(c, fa, st, err);
 }
 
 template <int S, int EJ>
-static rsp_status launch_fast_modes(int cmode, bool linear, const LaunchCtx &c, const FastArgs &fa, cudaStream_t st, const char **err) {
+static rsp_status launch_fast_modes(int cmode, bool linear, bool pg, const LaunchCtx &c, const FastArgs &fa, cudaStream_t st, const char **err) {
   if (linear) switch (cmode) {
-    case 0: return launch_fast_inst<S, 0, true, EJ>(c, fa, st, err);
-    case 1: return launch_fast_inst<S, 1, true, EJ>(c, fa, st, err);
-    default: return launch_fast_inst<S, 2, true, EJ>(c, fa, st, err);
+    case 0: return launch_fast_inst<S, 0, true, EJ>(c, fa, pg, st, err);
+    case 1: return launch_fast_inst<S, 1, true, EJ>(c, fa, pg, st, err);
+    default: return launch_fast_inst<S, 2, true, EJ>(c, fa, pg, st, err);
   }
   switch (cmode) {
-    case 0: return launch_fast_inst<S, 0, false, EJ>(c, fa, st, err);
-    case 1: return launch_fast_inst<S, 1, false, EJ>(c, fa, st, err);
-    default: return launch_fast_inst<S, 2, false, EJ>(c, fa, st, err);
+    case 0: return launch_fast_inst<S, 0, false, EJ>(c, fa, pg, st, err);
+    case 1: return launch_fast_inst<S, 1, false, EJ>(c, fa, pg, st, err);
+    default: return launch_fast_inst<S, 2, false, EJ>(c, fa, pg, st, err);
   }
 }
 
@@ -1463,9 +1477,9 @@ rsp_status RSP_CAT(launch_fast_size_, RSP_FAST_S)(int core, int cmode, bool line
   if (core == CORE_LIS) return gos_use_bitplanes(fa.W) ? launch_fast_gosb<S>(ctx, fa, ga, st, err) : launch_fast_gos<S>(ctx, fa, ga, st, err);
   if (core == CORE_OS) return launch_fast_os<S>(ctx, fa, ga, st, err);
 #if RSP_FAST_S == 10
-  if (ej == 2) return launch_fast_modes<S, 2>(cmode, linear, ctx, fa, st, err);
+  if (ej == 2) return launch_fast_modes<S, 2>(cmode, linear, fa.pg_full >= 0, ctx, fa, st, err);
 #endif
-  return launch_fast_modes<S, 1>(cmode, linear, ctx, fa, st, err);
+  return launch_fast_modes<S, 1>(cmode, linear, fa.pg_full >= 0, ctx, fa, st, err);
 }
 
 rsp_status RSP_CAT(launch_fast_fft_size_, RSP_FAST_S)(const LaunchCtx &ctx, const FastArgs &fa, cudaStream_t st, const char **err) {
@@ -1534,7 +1548,7 @@ bool fast_chain_supported(const Plan &pl, const FxArgs &a) {
   if (a.bp != 0 || a.tw_bp != 14 || !a.bitrev || a.sel != 2 || a.mag_w != 16 || a.mag_bp != 0) return false;
   if (a.core == CORE_LIS) return fast_gos_supported(a);
   if (a.core == CORE_OS) return fast_os_supported(a);
-  if (a.core != CORE_MEM || a.in_w != 16 || a.in_bp != 0 || a.sc_bp != 0 || a.thr_bp != 0 || a.send_cut || a.peak_grouping) return false;
+  if (a.core != CORE_MEM || a.in_w != 16 || a.in_bp != 0 || a.sc_bp != 0 || a.thr_bp != 0 || a.send_cut) return false;
   if (a.out == nullptr && a.det_list == nullptr) return false;
   if (a.thr_w < 1 || a.thr_w > 32 || a.G < 1 || a.W < 1 || a.div_sum < 0 || a.div_sum > 30) return false;
   const int ej = fast_edge_iters(pl.S, a.W, a.G);
@@ -1560,6 +1574,7 @@ rsp_status launch_fast_chain(const Plan &pl, const LaunchCtx &ctx, const FxArgs 
   fa.thr_mask = a.thr_w >= 32 ? 0xFFFFFFFFu : ((1u << a.thr_w) - 1u);
   fa.out_mul = (int)(1u << (a.binw + 1)); fa.thr_sext = 32 - a.thr_w;
   fa.det_list = a.det_list; fa.det_count = a.det_count; fa.det_cap = a.det_cap;
+  fa.pg_full = a.peak_grouping ? (a.G == a.guard_window_size ? 1 : 0) : -1;   // -1: no peak grouping
   // measured on B200 (profiles/r02_d_l2prefetch.txt): N = 16384 +5.3 %, N = 4096 +1.9 %, N = 1024 +1.3 %; RSP_FAST_L2_PREFETCH=0 turns it off
   { static int l2p = -1; if (l2p < 0) { const char *e = std::getenv("RSP_FAST_L2_PREFETCH"); l2p = e ? std::atoi(e) : 1; }
     fa.l2_prefetch = (l2p != 0 && a.gen_full == nullptr && (reinterpret_cast<uintptr_t>(a.in) & 15u) == 0) ? 1 : 0; }

@@ -17,6 +17,12 @@ elif key == "c2":
     B.run_case("C2 x 256 frames", B.fixed_params(1024, 64, 4), 10, ca(1024, 16, 4, 4), 65536, 1)
 elif key == "c5":
     B.run_case("C5 fixed one frame", B.fixed_params(16384, 64, 8), 14, ca(16384, 64, 8, 6), 32768, 8)
+elif key == "c5pg":
+    r = ca(16384, 64, 8, 6); r["peakGrouping"] = 1
+    B.run_case("C5 fixed one frame, peakGrouping = 1", B.fixed_params(16384, 64, 8), 14, r, 32768, 8)
+elif key == "c2pg":
+    r = ca(1024, 16, 4, 4); r["peakGrouping"] = 1
+    B.run_case("C2 x 256 frames, peakGrouping = 1", B.fixed_params(1024, 64, 4), 10, r, 65536, 1)
 elif key == "c4os":
     os_regs = dict(fftWin=4096, thresholdScaler=2, logOrLinearMode=1, peakGrouping=0, cfarMode=0, windowCells=64, guardCells=4, indexLagg=48, indexLead=48)
     B.run_case("C4 GOS", B.fixed_params(4096, 64, 4, GOSCFARType), 12, os_regs, 1024, 1)

@@ -687,3 +687,35 @@ def test_unaligned_output_pointers_take_the_other_kernel_and_give_the_same_beats
                 cuda.cuda.synchronize()
                 assert (from_dev_u32(d_out) == want).all(), (ctype, off)
                 assert (from_dev_u32(d_f) == oracle.fft_fixed_words(fft, beats)).all(), (ctype, off)
+
+
+@pytest.mark.parametrize("log_n,W,G,gws,mode,lin", [(10, 16, 4, 4, 0, 1), (10, 64, 8, 8, 1, 0), (11, 32, 2, 4, 2, 1), (12, 64, 4, 4, 0, 1), (13, 16, 1, 1, 1, 1),
+                                                    (14, 64, 8, 8, 0, 1), (14, 32, 3, 8, 2, 0)])
+def test_fast_kernel_peak_grouping(cuda, oracle, log_n, W, G, gws, mode, lin):
+    """peakGrouping = 1 on the specialised CA / GO / SO kernel (both neighbours come from the lagging guard, CFARCoreWithMem.scala:182-184;
+    the left one only when guardCells == guardWindowSize): every size, linear / log, quiet and full-scale rows, ragged counts, detection list"""
+    n = 1 << log_n
+    rows = 7 if log_n <= 12 else 3
+    beats = np.concatenate([synth.chirps_fixed(rows - 2, n, seed=130 + log_n, noise=2.0 ** -3), synth.random_beats(2, n, seed=140 + log_n)])
+    p = fixed_params(n, 64, gws)
+    regs = dict(fftWin=n, thresholdScaler=3, logOrLinearMode=lin, divSum=int(np.log2(W)), peakGrouping=1, cfarMode=mode, windowCells=W, guardCells=G)
+    fft, mag, cfar = oracle_cfgs(oracle, p, log_n, 2, regs)
+    want = oracle.chain_fixed_words(fft, mag, cfar, beats)
+    regs0 = dict(regs, peakGrouping=0)
+    _, _, cfar0 = oracle_cfgs(oracle, p, log_n, 2, regs0)
+    want0 = oracle.chain_fixed_words(fft, mag, cfar0, beats)
+    assert (want0 & 1).sum() >= (want & 1).sum() > 0         # the grouping can only remove peaks, and leaves some
+    with R.FftMagCfarChainVanilla(p) as ch:
+        configure(ch, log_n, 2, regs)
+        assert ch.variant == f"chain_fixed_fast<{log_n}>", ch.variant
+        d_in = to_dev(cuda, beats)
+        d_out = cuda.zeros_like(d_in)
+        det_list = cuda.zeros((rows * n, 4), dtype=cuda.int32, device="cuda")
+        det_count = cuda.zeros(1, dtype=cuda.int32, device="cuda")
+        ch.run(d_in, rows, 1, out=d_out, det_list=det_list, det_count=det_count)
+        cuda.cuda.synchronize()
+        got = from_dev_u32(d_out)
+        k = int(det_count.item())
+        assert (got == want).all(), f"{int((got != want).sum())} beats differ, first at {np.argwhere(got != want)[:3].tolist()}"
+        assert k == int((want & 1).sum())
+        assert set(map(tuple, det_list[:k].cpu().numpy()[:, :2].tolist())) == set(map(tuple, np.argwhere((want & 1) == 1).tolist()))
