@@ -18,6 +18,7 @@
 //  * the peak bits of 32 consecutive bins are one warp ballot.
 #include <algorithm>
 #include <cstdlib>
+#include <type_traits>
 
 #include "rsp_fast.cuh"
 
@@ -39,6 +40,7 @@ struct FastF32Args {
   Detection *det_list;
   uint32_t *det_count;
   uint32_t det_cap;
+  int pg_full;             // peak grouping: -1 off; else 1 = guardCells equals guardWindowSize (the left neighbour is read), 0 = it reads as 0
   int l2_prefetch;         // 1: one thread asks the L2 for the CTA's next row while this one is transformed (cp.async.bulk.prefetch.L2)
 };
 
@@ -291,7 +293,8 @@ template <int S> constexpr int f32_min_blocks() {
 }
 
 // EJ = number of leading / trailing iterations j whose bins may miss a window (ceil((W + G) / TPC), checked by the host)
-template <int S, int CMODE, bool LINEAR, int EJ>
+// PG: the peak-grouping instantiation (a run-time register; its own kernels so that the common ones keep their register budget)
+template <int S, int CMODE, bool LINEAR, int EJ, bool PG = false>
 __global__ void __launch_bounds__(FGeoF<S>::THREADS, f32_min_blocks<S>())
 chain_f32_fast_kernel(const FastF32Args a) {
   using Gm = FGeoF<S>;
@@ -406,6 +409,7 @@ chain_f32_fast_kernel(const FastF32Args a) {
     float *gout = a.out ? a.out + (size_t)row * N + tl : nullptr;
     uint32_t *gmask = a.peak_mask ? a.peak_mask + (size_t)row * Gm::MASKW + (tl >> 5) : nullptr;
     uint32_t mask = 0;
+    auto bins = [&](auto pgc) {
 #pragma unroll
     for (int j = 0; j < PTS; ++j) {
       float L, R;
@@ -419,12 +423,20 @@ chain_f32_fast_kernel(const FastF32Args a) {
         L = __fadd_rn(pA[j * TPC], pB[j * TPC]); R = __fadd_rn(pC[j * TPC], pD[j * TPC]);
       }
       const float thr = f32_threshold<CMODE, LINEAR>(a, L, R, lagg_full, lead_full);
-      const bool pk = pX[j * JSTEP] > thr;
+      bool pk = pX[j * JSTEP] > thr;
+      if (decltype(pgc)::value) {   // peakGrouping: both neighbours from the lagging guard (CFARCoreWithMem.scala:182-184)
+        const int n = tl + j * TPC, n1 = n + 1, ng = n + a.G;
+        const float cut = pX[j * JSTEP];
+        const float left = (a.pg_full && n1 < N) ? mg[midx(n1)] : 0.f, right = ng < N ? mg[midx(ng)] : 0.f;
+        pk = pk && cut > left && cut > right;
+      }
       if (gout) gout[j * TPC] = thr;
       const uint32_t word = __ballot_sync(0xffffffffu, pk);
       if (gmask && (tl & 31) == 0) gmask[j * (TPC / 32)] = word;
       mask |= (pk ? 1u : 0u) << j;
     }
+    };
+    bins(std::integral_constant<bool, PG>{});
     if (mask != 0 && a.det_list != nullptr && active) {
       const FastF32DetArgs da = {a.W, a.G, a.k_both, a.k_one, a.scaler, a.row_base + row, mask, a.det_cap, a.det_list, a.det_count};
       f32_detections<S, CMODE, LINEAR>(da, tl, QP, AS, mg);
@@ -441,26 +453,31 @@ bool fast_f32_chain_supported(const Plan &pl, const F32Args &a) {
   if (pl.first_stage != STAGE_FFT || pl.last_stage != STAGE_CFAR) return false;
   if (pl.S < RSP_FAST_SMIN || pl.S > RSP_FAST_SMAX) return false;
   if (!a.bitrev || a.load_rev || a.fft_dir != 1 || a.sel != 2) return false;
-  if (a.core != CORE_MEM || a.send_cut || a.peak_grouping) return false;
+  if (a.core != CORE_MEM || a.send_cut) return false;
   if (a.G < 1 || a.W < 1 || a.div_sum < 0 || a.div_sum > 30) return false;
   if ((a.W & 15) || a.W > 128) return false;   // the block-of-16 window sums (see the kernel)
   if (f32_edge_iters(pl.S, a.W, a.G) > (pl.S == 10 ? 2 : 1)) return false;
   return a.out != nullptr || a.peak_mask != nullptr || a.det_list != nullptr;
 }
 
-template <int S, int CMODE, bool LINEAR, int EJ>
-static rsp_status launch_f32_fast_inst(const LaunchCtx &c, const FastF32Args &fa, cudaStream_t st, const char **err) {
+template <int S, int CMODE, bool LINEAR, int EJ, bool PG = false>
+static rsp_status launch_f32_fast_pg(const LaunchCtx &c, const FastF32Args &fa, cudaStream_t st, const char **err) {
   using Gm = FGeoF<S>;
   static int occ_dev[64] = {0};
   int &occ = occ_dev[c.device & 63];
   const size_t smem = (size_t)Gm::CPC * Gm::ROW_BYTES;
-  auto kernel = chain_f32_fast_kernel<S, CMODE, LINEAR, EJ>;
+  auto kernel = chain_f32_fast_kernel<S, CMODE, LINEAR, EJ, PG>;
   if (!occ) { const rsp_status s = launch_cfg(kernel, smem, Gm::THREADS, &occ, err); if (s != RSP_OK) return s; }
   const unsigned groups = (fa.n_rows + Gm::CPC - 1) / Gm::CPC;
   const unsigned grid = std::max(1u, std::min(groups, (unsigned)(c.sm_count * occ)));
   kernel<<<grid, Gm::THREADS, smem, st>>>(fa);
   if (cudaGetLastError() != cudaSuccess) { *err = "chain_f32_fast_kernel launch failed"; return RSP_ECUDA; }
   return RSP_OK;
+}
+
+template <int S, int CMODE, bool LINEAR, int EJ>
+static rsp_status launch_f32_fast_inst(const LaunchCtx &c, const FastF32Args &fa, cudaStream_t st, const char **err) {
+  return fa.pg_full >= 0 ? launch_f32_fast_pg<S, CMODE, LINEAR, EJ, true>(c, fa, st, err) : launch_f32_fast_pg<S, CMODE, LINEAR, EJ, false>(c, fa, st, err);
 }
 
 template <int S, int EJ>
@@ -491,6 +508,7 @@ rsp_status launch_fast_f32_chain(const Plan &pl, const LaunchCtx &ctx, const F32
   fa.det_list = a.det_list; fa.det_count = a.det_count; fa.det_cap = a.det_cap;
   { static int l2p = -1; if (l2p < 0) { const char *e = std::getenv("RSP_FAST_L2_PREFETCH"); l2p = e ? std::atoi(e) : 1; }
     fa.l2_prefetch = (l2p != 0 && (reinterpret_cast<uintptr_t>(a.in) & 15u) == 0) ? 1 : 0; }
+  fa.pg_full = a.peak_grouping ? (a.G == a.guard_window_size ? 1 : 0) : -1;
   const int ej = f32_edge_iters(pl.S, a.W, a.G);
   switch (pl.S) {
   case 10: return ej == 2 ? launch_f32_fast_modes<10, 2>(cmode, linear, ctx, fa, st, err) : launch_f32_fast_modes<10, 1>(cmode, linear, ctx, fa, st, err);

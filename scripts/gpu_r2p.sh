@@ -1,3 +1,4 @@
 #!/bin/bash
 mkdir -p gpurun_out
-timeout 900 python -m pytest tests/test_gpu_round2.py tests/test_gpu_chain.py -m gpu -x -q -k "peak_grouping or fast_kernel or generator" 2>&1 | tail -8 | tee gpurun_out/pytest_pg.txt
+timeout 900 python -m pytest tests/test_gpu_round2.py tests/test_gpu_f32_gen.py -m gpu -x -q -k "f32 or fp32" 2>&1 | tail -12 | tee gpurun_out/pytest_pgf.txt
+timeout 300 python scripts/bench_one.py c3 2>&1 | tail -1 | cut -c1-170 | tee gpurun_out/pgf_bench.txt

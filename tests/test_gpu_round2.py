@@ -719,3 +719,21 @@ def test_fast_kernel_peak_grouping(cuda, oracle, log_n, W, G, gws, mode, lin):
         assert (got == want).all(), f"{int((got != want).sum())} beats differ, first at {np.argwhere(got != want)[:3].tolist()}"
         assert k == int((want & 1).sum())
         assert set(map(tuple, det_list[:k].cpu().numpy()[:, :2].tolist())) == set(map(tuple, np.argwhere((want & 1) == 1).tolist()))
+
+
+@pytest.mark.parametrize("log_n,W,G,gws,mode,lin", [(10, 16, 2, 2, 0, 1), (11, 32, 4, 4, 1, 1), (11, 32, 2, 4, 2, 0), (12, 64, 4, 4, 0, 1), (13, 16, 1, 1, 1, 1), (14, 64, 8, 8, 0, 1)])
+def test_fast_f32_kernel_peak_grouping(cuda, oracle, log_n, W, G, gws, mode, lin):
+    """peakGrouping = 1 on chain_f32_fast<S> (its own instantiation): thresholds 1e-4 against the fp64 dataflow, identical decided
+    detections, guardCells equal to and below guardWindowSize (the left neighbour then reads as 0)"""
+    n = 1 << log_n
+    xc = synth.chirps_complex(4, n, seed=150 + log_n, noise=2.0 ** -4)
+    x32 = np.stack([xc.real, xc.imag], axis=-1).astype(np.float32)
+    xq = x32[..., 0].astype(np.float64) + 1j * x32[..., 1].astype(np.float64)
+    regs = dict(fftWin=n, logOrLinearMode=lin, divSum=int(np.log2(W)), peakGrouping=1, cfarMode=mode, windowCells=W, guardCells=G)
+    scaler = 3.0 if lin else 1e-4
+    thr, pk, variant = run_f32(cuda, f32_params(n, max(W, 16), gws), log_n, 2, regs, scaler, x32)
+    assert variant == f"chain_f32_fast<{log_n}>", variant
+    mag, want_thr, want_pk = f64_chain(oracle, xq, log_n, 2, regs, scaler, W, G, guard_window_size=gws)
+    check_f32(thr, pk, mag, want_thr, want_pk, f"fp32 pg mode {mode} lin {lin}")
+    _, _, pk0 = f64_chain(oracle, xq, log_n, 2, dict(regs, peakGrouping=0), scaler, W, G, guard_window_size=gws)
+    assert pk0.sum() >= want_pk.sum() > 0
