@@ -267,6 +267,10 @@ def config_lines(torch, peak):
          note="one_frame = the single chirp of configs[0] (launch-latency bound, L2-resident)")
     case("C2 one frame 256 x 1024 fixed CA (W16 G4)", fixed_params(1024, 64, 4), 10, ca(1024, 16, 4, 4), 256, 1, 256,
          note="one frame is 2 MiB (L2-resident); batched line = 256 frames per launch")
+    app = R.fft_mag_cfar_chain_vanilla_app_params()
+    case("FftMagCfarChainVanillaApp parameters (binPoint 12, leadLagg 64, guard 4) 256 x 1024 fixed CA", app, 10,
+         dict(fftWin=1024, thresholdScaler=int(3.5 * 4096), logOrLinearMode=1, divSum=6, peakGrouping=0, cfarMode=0, windowCells=64, guardCells=4), 256, 1, 256,
+         note="src/main/scala/FftMagCfarChain.scala:76-120: dsptools' 3-multiplier product with per-product trim, thresholds with binary point 12")
     for mode, nm in ((1, "GOCA"), (2, "SOCA")):
         case(f"C3 4 RX x 512 x 2048 fp32 {nm} (W32 G4)", f32_params(2048, 32, 4), 11, ca(2048, 32, 4, 5, mode), 2048, 4, 16, fp32=True, bps=12.125,
              note="fp32 flavour; one frame is 48 MiB + 24 MiB out (L2-resident); batched = 16 frames")

@@ -279,7 +279,7 @@ extern "C" rsp_status rsp_chain_create(const rsp_chain_params *params, int devic
   build_window(c->p, c->t);
   rsp_status s = upload(c->t.tw, &c->d_tw);
   if (s == RSP_OK) s = upload(c->t.tw2, &c->d_tw2);
-  if (s == RSP_OK && fft_is_wide(c->p.fft)) s = upload(c->t.tww, &c->d_tww);
+  if (s == RSP_OK && (fft_is_wide(c->p.fft) || c->p.fft.binPoint >= 2)) s = upload(c->t.tww, &c->d_tww);   // raw twiddles: the wide block and the binPoint >= 2 fast kernels
   if (s == RSP_OK && c->p.fft.overflowReg) {
     if (cudaMalloc((void **)&c->d_ovf, sizeof(uint32_t)) != cudaSuccess || cudaMemset(c->d_ovf, 0, sizeof(uint32_t)) != cudaSuccess) s = fail(RSP_ECUDA, "allocating the overflow status word failed");
   }
@@ -400,7 +400,7 @@ static rsp_status sync_window(rsp_chain *c) {
 
 // ---------------------------------------------------------------------------------------------------------------------
 // planning glue
-static void bind_fixed(rsp_chain *c, FxArgs &a) { a.tw = c->d_tw; a.tw2 = c->d_tw2; a.log_tab = c->d_log_tab; a.win = c->d_win; a.win4 = c->d_win4; }
+static void bind_fixed(rsp_chain *c, FxArgs &a) { a.tw = c->d_tw; a.tw2 = c->d_tw2; a.tww = c->d_tww; a.log_tab = c->d_log_tab; a.win = c->d_win; a.win4 = c->d_win4; }
 static void bind_f32(rsp_chain *c, F32Args &a) { a.tw = c->d_twf; a.win = c->d_winf; }
 static void bind_dets(const rsp_dets *d, Detection **list, uint32_t **count, uint32_t *cap) {
   if (d && d->list && d->count) { *list = reinterpret_cast<Detection *>(d->list); *count = d->count; *cap = d->capacity; }
@@ -932,6 +932,7 @@ extern "C" const char *rsp_variant_name(rsp_chain *c) {
     FxArgs a;
     if (plan_fixed(c->p, c->r, c->t, STAGE_FFT, STAGE_CFAR, a, pl, err) != RSP_OK) { c->variant = "invalid: " + err; return c->variant.c_str(); }
     a.out = reinterpret_cast<uint32_t *>(c);   // any non-null output: the name is that of the full chain with output beats requested
+    bind_fixed(c, a);
     const char *m = pl.mode == MODE_FAST ? "fast" : (pl.mode == MODE_FAST3 ? "fast3" : (a.radix2 ? (a.dit ? "radix2-dit" : "radix2-dif") : (a.dit ? "radix22-dit" : "generic")));
     if (fast_chain_supported(pl, a)) std::snprintf(buf, sizeof(buf), a.core == CORE_LIS ? "chain_fixed_fast_gos<%d>" : (a.core == CORE_OS ? "chain_fixed_fast_os<%d>" : "chain_fixed_fast<%d>"), pl.S);
     else std::snprintf(buf, sizeof(buf), "chain_fixed<%d,%s>", pl.S, m);

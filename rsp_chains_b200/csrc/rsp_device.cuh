@@ -55,6 +55,7 @@ struct FxArgs {
   const uint32_t *tw;       // packed (cos16 << 16 | sin16) twiddles, per stageN three runs [W^2k | W^k | W^3k]
   int tw_off[16];           // word offset of the table of stageN = 1 << L
   const int32_t *tw2;       // same entries as int32 pairs (c, s) << (16 - tw_bp) (fast kernels, rsp_fast.cu)
+  const int32_t *tww;       // same entries as raw int32 pairs (fast kernels with binPoint >= 2; null when not uploaded)
   const int32_t *win;       // window ROM (protoWin raw values), read when win_on
   const int32_t *win4;      // the same << (16 - win_shift): bits 16..31 of beat * win4 are the windowed beat (fast kernels)
   int win_on, win_shift;    // win_shift = binary point of protoWin = windowWidth - 2

@@ -54,6 +54,11 @@ struct FastArgs {
   int l2_prefetch;       // 1: one thread asks the L2 for the CTA's next row (cp.async.bulk.prefetch.L2) while this row is transformed
   int stage;             // 1: the next row's beats are fetched with cp.async into a staging area behind the CTA's rows while this
                          // row's CFAR phase runs (chain_fixed_fast_kernel); needs 16-byte aligned rows and N more words per chirp
+  // binPoint >= 2 (TW3 kernels; FftMagCfarChainVanillaApp has 12): the 3-multiplier twiddle product with per-product trim of MODE_FAST3
+  // (rsp_device.cuh, cmul) on the raw twiddles, and the CFAR threshold with the operands' binary points (cfar_bin)
+  const int2 *tw3;       // raw (cos, -sin) in Q2.14, same order and offsets as tw
+  int s1, s2, h1, h1m, h2, h2m;   // product trim: >> s1 with h1 = 1 << (s1 - 1) (h1m = h1 - 1 for negated operands), result trim >> s2 with h2 / h2m
+  int thr_sh, ncut_mul, out_sh;   // linear threshold: (t * scaler) >> thr_sh has binary point tbp; peak = thr - cut * 2^(tbp - inBP) < 0 (ncut_mul = -2^(tbp - inBP)); field = thr >> out_sh
   int pg_full;   // peak grouping (PG kernels): 1 = guardCells equals the generator's guardWindowSize, the left neighbour is read (CFARCoreWithMem.scala:182-184)
 };
 
@@ -198,6 +203,22 @@ __device__ __forceinline__ void fbf_true(int sa, int &A, int sc, int &C, bool wr
   C = wrap ? sext16(d) : d;
 }
 
+// The twiddle product of the chains with binPoint >= 2 (MODE_FAST3: DspContext 3-multiplier form, every product trimmed to the context's
+// binary point, the result trimmed to the data's, both RoundHalfUp; rsp_device.cuh cmul):
+//   k1 = (a (br + bi) + h1) >> s1, k2 = ((a + b) bi + h1) >> s1, k3 = ((b - a) br + h1) >> s1, re = (k1 - k2 + h2) >> s2, im = (k1 + k3 + h2) >> s2
+// For a point held negated the same formulas with h - 1 give the negated result exactly: -((P + h) >> s) == (-P + h - 1) >> s.
+template <bool TRUE_OUT>
+__device__ __forceinline__ void fcmul3(const FastArgs &a, int &sg, int &xr, int &xi, const int2 w) {
+  const int br = w.x, bi = w.y, bs = br + bi;
+  int A = xr, B = xi, hh1 = a.h1, hh2 = a.h2;
+  if (sg < 0) {
+    if (TRUE_OUT) { A = -A; B = -B; sg = 1; }
+    else { hh1 = a.h1m; hh2 = a.h2m; }
+  }
+  const int k1 = sar(imad(A, bs, hh1), a.s1), k2 = sar(imad(A + B, bi, hh1), a.s1), k3 = sar(imad(B - A, br, hh1), a.s1);
+  xr = sar(k1 - k2 + hh2, a.s2); xi = sar(k1 + k3 + hh2, a.s2);
+}
+
 // JPL magnitude approximation (generators/logMagMux/src/main/scala/LogMagMux.scala:92-110), stored to 16 bits by the caller
 __device__ __forceinline__ int fjpl(int re, int im) {
   const int ar = abs(re), ai = abs(im);
@@ -212,7 +233,7 @@ __device__ __forceinline__ int fjpl(int re, int im) {
 // of the butterfly differences is the identity and its PRMT is left out (13% of the ALU-pipe instructions of the kernel).
 // FFTO (the FFT block alone, fft_fixed_fast_kernel): the last pass ends like the others -- true signs -- and leaves the packed output
 // beats Cat(re16, im16) in `mags` instead of the magnitudes.
-template <int S, int LP, int K, bool WRAP, bool TWSM = false, bool FFTO = false>
+template <int S, int LP, int K, bool WRAP, bool TWSM = false, bool FFTO = false, bool TW3 = false>
 __device__ __forceinline__ void fast_group(const FastArgs &a, int tl, int g, const uint32_t (&pre)[16], uint32_t *xb, int (&mags)[1 << LP],
                                            const int2 *tws = nullptr) {
   using Gm = FGeo<S, LP>;
@@ -278,7 +299,7 @@ __device__ __forceinline__ void fast_group(const FastArgs &a, int tl, int g, con
     const int L = S - i + 1;
     const int q = 1 << (L - 2);
     constexpr bool smt = TWSM && first;                      // this pass's tables sit in shared memory: [stageN = N | N / 4]
-    const int2 *tab = smt ? tws + (i == 1 ? 0 : 3 * (Gm::N / 4)) : a.tw + a.tw_off[L];
+    const int2 *tab = smt ? tws + (i == 1 ? 0 : 3 * (Gm::N / 4)) : (TW3 ? a.tw3 : a.tw) + a.tw_off[L];
 #pragma unroll
     for (int rr = 0; rr < R; ++rr) {
       const int quarter = ((rr >> (m - 1 - s)) & 1) + 2 * ((rr >> (m - s)) & 1);
@@ -288,7 +309,11 @@ __device__ __forceinline__ void fast_group(const FastArgs &a, int tl, int g, con
         // several groups per pass (32 points per thread) use the same twiddles: left to CSE, the compiler keeps all 15 pairs of a
         // pass live across the groups and spills the row loop's invariants; a volatile load per group re-reads them from L1 instead
         const int2 w = smt ? tab[slot * q + k] : ((RSP_FAST_TW_VOLATILE && LP > 4 && !first) ? ldg_tw_volatile(&tab[slot * q + k]) : __ldg(&tab[slot * q + k]));
-        if (true_stage) { fcmul<true, true>(sg[rr], re[rr], im[rr], w, a.m1, a.rnd); raw[rr] = true; }
+        if (TW3) {   // the result is a plain value: in loud rows it is wrapped like every other 16-bit assignment
+          if (true_stage || WRAP || (s == m - 1 && !last)) fcmul3<true>(a, sg[rr], re[rr], im[rr], w); else fcmul3<false>(a, sg[rr], re[rr], im[rr], w);
+          if (WRAP) { re[rr] = sext16(re[rr]); im[rr] = sext16(im[rr]); }
+        }
+        else if (true_stage) { fcmul<true, true>(sg[rr], re[rr], im[rr], w, a.m1, a.rnd); raw[rr] = true; }
         else if (WRAP || (s == m - 1 && !last)) fcmul<true>(sg[rr], re[rr], im[rr], w, a.m1, a.rnd);
         else fcmul<false>(sg[rr], re[rr], im[rr], w, a.m1, a.rnd);
       }
@@ -336,7 +361,7 @@ __device__ __forceinline__ void fast_scatter(int tl, const int (&mags)[1 << LP],
 }
 
 // a whole pass whose groups need no beats from global memory (every pass but the first, and the first one with 16 points per thread)
-template <int S, int LP, int K, bool WRAP, bool TWSM = false, bool FFTO = false>
+template <int S, int LP, int K, bool WRAP, bool TWSM = false, bool FFTO = false, bool TW3 = false>
 __device__ __forceinline__ void fast_pass(const FastArgs &a, int tl, const uint32_t (&pre)[16], uint32_t *xb, uint32_t *xm, const int2 *tws = nullptr,
                                           int *wout = nullptr) {
   constexpr int m = fx_pass_size(S, K), G = (1 << LP) >> m;
@@ -348,7 +373,7 @@ __device__ __forceinline__ void fast_pass(const FastArgs &a, int tl, const uint3
 #pragma unroll
   for (int gi = 0; gi < G; ++gi) {
     const int g = !last ? gi : (G == 8 ? ((gi & 1) << 2 | (gi & 2) | (gi >> 2)) : (G == 4 ? ((gi & 1) << 1 | (gi >> 1)) : gi));
-    fast_group<S, LP, K, WRAP, TWSM, FFTO>(a, tl, g, pre, xb, mags, tws);
+    fast_group<S, LP, K, WRAP, TWSM, FFTO, TW3>(a, tl, g, pre, xb, mags, tws);
     // keep the next group's shared-memory loads behind this group's stores: hoisted, 32 points are live and the 64-register
     // budget spills (the other warps of the SM hide the load latency, not this thread's next group)
     // (ptxas moves shared-memory accesses with distinct immediate offsets across a compiler-level fence; WARPSYNC holds them)
@@ -415,7 +440,7 @@ template <int S> __device__ __forceinline__ void chirp_sync(int) { __syncthreads
 // 32767 * 2^-14 * sqrt(2)/2 + sqrt(2)/2 (twiddle quantisation + rounding), the x(-j) keeps it: after S <= 14 stages and
 // 6 products no modulus, hence no component, exceeds 32739 + 14 * 0.71 + 6 * 2.2 < 32767, and nothing ever wraps.
 // Rows that are not quiet (full-scale inputs, the -32768 corners) take the passes with the wraps; both give the same bits.
-#define RSP_QUIET_MAX 23150
+#define RSP_QUIET_MAX 23100
 __device__ __forceinline__ bool quiet_beats(const uint32_t (&pre)[16]) {
   uint32_t mx = pre[0], mn = pre[0];
 #pragma unroll
@@ -428,18 +453,18 @@ __device__ __forceinline__ bool quiet_beats(const uint32_t (&pre)[16]) {
 // The first pass works on the thread's own beats, so each warp decides for itself (per group of 16 beats); the later passes mix
 // the whole chirp and decide by the chirp's flag, which every warp of the chirp has or-ed into before the barrier that ends the
 // first pass.
-template <int S, int LP, int K, bool FFTO = false>
+template <int S, int LP, int K, bool FFTO = false, bool TW3 = false>
 __device__ __forceinline__ void fast_passes_from(const FastArgs &a, int c, int tl, bool quiet, const uint32_t (&pre)[16], uint32_t *xb, uint32_t *xm,
                                                  int *wout = nullptr) {
-  if (quiet) fast_pass<S, LP, K, false, false, FFTO>(a, tl, pre, xb, xm, nullptr, wout);
-  else fast_pass<S, LP, K, true, false, FFTO>(a, tl, pre, xb, xm, nullptr, wout);
+  if (quiet) fast_pass<S, LP, K, false, false, FFTO, TW3>(a, tl, pre, xb, xm, nullptr, wout);
+  else fast_pass<S, LP, K, true, false, FFTO, TW3>(a, tl, pre, xb, xm, nullptr, wout);
   chirp_sync<S>(c);
-  if constexpr (K + 1 < fx_n_passes(S)) fast_passes_from<S, LP, K + 1, FFTO>(a, c, tl, quiet, pre, xb, xm, wout);
+  if constexpr (K + 1 < fx_n_passes(S)) fast_passes_from<S, LP, K + 1, FFTO, TW3>(a, c, tl, quiet, pre, xb, xm, wout);
 }
 
 // pre: the thread's 16 beats (LP = 4; loaded or staged by the caller).  grow: the row in global memory (LP = 5: each of the two
 // groups of the first pass loads its own 16 beats, so that no more than one group's beats are live at a time).
-template <int S, int LP, bool TWSM = false, bool FFTO = false>
+template <int S, int LP, bool TWSM = false, bool FFTO = false, bool TW3 = false>
 __device__ __forceinline__ void fast_passes(const FastArgs &a, int c, int tl, uint32_t (&pre)[16], const uint32_t *grow, const GenRow &gr, uint32_t *xb,
                                             uint32_t *xm, int *loud, const int2 *tws = nullptr, int *wout = nullptr) {
   static_assert(fx_pass_size(S, 0) == 4, "the first pass works on groups of 16 beats");
@@ -447,7 +472,7 @@ __device__ __forceinline__ void fast_passes(const FastArgs &a, int c, int tl, ui
   if constexpr (G0 == 1) {
     const bool warp_quiet = __all_sync(0xffffffffu, quiet_beats(pre));
     if (!warp_quiet && (tl & 31) == 0) loud[c] = 1;
-    if (warp_quiet) fast_pass<S, LP, 0, false, TWSM>(a, tl, pre, xb, xm, tws); else fast_pass<S, LP, 0, true, TWSM>(a, tl, pre, xb, xm, tws);
+    if (warp_quiet) fast_pass<S, LP, 0, false, TWSM, false, TW3>(a, tl, pre, xb, xm, tws); else fast_pass<S, LP, 0, true, TWSM, false, TW3>(a, tl, pre, xb, xm, tws);
   } else {
     int mags[1 << LP];   // not used by a first pass
     bool all_quiet = true;
@@ -456,14 +481,14 @@ __device__ __forceinline__ void fast_passes(const FastArgs &a, int c, int tl, ui
       load_beats<S, LP>(a, grow, gr, tl, g, pre);
       const bool warp_quiet = __all_sync(0xffffffffu, quiet_beats(pre));
       all_quiet = all_quiet && warp_quiet;
-      if (warp_quiet) fast_group<S, LP, 0, false, TWSM>(a, tl, g, pre, xb, mags, tws); else fast_group<S, LP, 0, true, TWSM>(a, tl, g, pre, xb, mags, tws);
+      if (warp_quiet) fast_group<S, LP, 0, false, TWSM, false, TW3>(a, tl, g, pre, xb, mags, tws); else fast_group<S, LP, 0, true, TWSM, false, TW3>(a, tl, g, pre, xb, mags, tws);
     }
     if (!all_quiet && (tl & 31) == 0) loud[c] = 1;
   }
   chirp_sync<S>(c);
   if constexpr (fx_n_passes(S) > 1) {
     const bool quiet = loud[c] == 0;
-    fast_passes_from<S, LP, 1, FFTO>(a, c, tl, quiet, pre, xb, xm, wout);     // ends with a barrier: every thread has read the flag
+    fast_passes_from<S, LP, 1, FFTO, TW3>(a, c, tl, quiet, pre, xb, xm, wout);     // ends with a barrier: every thread has read the flag
     if (tl == 0) loud[c] = 0;                                 // next written before the first barrier of the next row
   }
 }
@@ -500,7 +525,9 @@ __device__ __forceinline__ int chirp_scan_exclusive(int total, int c, int tl, in
 // !has_out (the caller wants the detection list only): no output beat is built or stored.
 // PG: peak grouping -- a peak must also exceed its two "neighbours" as the core's guard registers deliver them: laggGuard.last = x[n + 1]
 // (0 unless guardCells == guardWindowSize) and laggGuard.head = x[n + guardCells] (CFARCoreWithMem.scala:182-184; both from the lagging side).
-template <int S, int LP, int CMODE, bool LINEAR, bool EDGE, bool PG = false>
+// BPV: the operands carry a binary point (inBP = scalerBP = thresholdBP = b >= 1): the linear threshold is the product trimmed to the
+// context's binary point tbp (Floor: an arithmetic shift), the cell under test is compared at tbp, the field is the threshold at b.
+template <int S, int LP, int CMODE, bool LINEAR, bool EDGE, bool PG = false, bool BPV = false>
 __device__ __forceinline__ int fast_cfar_bin(const FastArgs &a, int j, int tl, int n2, const int *P, const int *pA, const int *pB,
                                              const int *pC, const int *pD, const short *X, uint32_t *gout, bool has_out, const short *X0 = nullptr) {
   constexpr int N = 1 << S, TPC = FGeo<S, LP>::TPC;
@@ -520,10 +547,10 @@ __device__ __forceinline__ int fast_cfar_bin(const FastArgs &a, int j, int tl, i
   L = sar(L, a.div_sum); R = sar(R, a.div_sum);
   int t = CMODE == 0 ? sar(fadd(1, R, 1, L, a.one, a.m1), 1) : (CMODE == 1 ? max(L, R) : min(L, R));
   if (EDGE) t = lead_full ? (lagg_full ? t : R) : L;
-  const int thr = LINEAR ? t * a.scaler : fadd(1, t, 1, a.scaler, a.one, a.m1);
+  const int thr = LINEAR ? ((BPV) ? sar(t * a.scaler, a.thr_sh) : t * a.scaler) : fadd(1, t, 1, a.scaler, a.one, a.m1);
   const int cut = X[mhx<S>(j * TPC)];   // X points at the thread's first bin (mhx is additive over tl + j * TPC)
   // peak = cut > thr as the sign bit of thr - cut (|thr| < 2^31 - 2^16 is checked by the host)
-  int pk = (int)((uint32_t)fadd(1, thr, -1, cut, a.one, a.m1) >> 31);
+  int pk = (BPV && LINEAR) ? (int)((uint32_t)imad(cut, a.ncut_mul, thr) >> 31) : (int)((uint32_t)fadd(1, thr, -1, cut, a.one, a.m1) >> 31);
   if (PG) {
     const int n1 = n + 1, ng = n + a.G;
     int left = 0, right = 0;
@@ -532,14 +559,15 @@ __device__ __forceinline__ int fast_cfar_bin(const FastArgs &a, int j, int tl, i
     pk = (pk != 0 && cut > left && cut > right) ? 1 : 0;
   }
   if (has_out) {
-    const int w0 = (int)(((uint32_t)thr & a.thr_mask) * (uint32_t)a.out_mul + (uint32_t)n2);   // threshold field | bin field (n << 1)
+    const int tf = (BPV && LINEAR) ? sar(thr, a.out_sh) : thr;
+    const int w0 = (int)(((uint32_t)tf & a.thr_mask) * (uint32_t)a.out_mul + (uint32_t)n2);   // threshold field | bin field (n << 1)
     gout[n] = (uint32_t)fadd(1, pk, 1, w0, a.one, a.m1);
   }
   return pk;
 }
 
 // detections of one thread: bit (PTS - 1 - j) of `mask` = peak of bin tl + j * TPC.  Rare path, recomputes from shared memory.
-struct FastDetArgs { int W, G, div_sum, scaler, thr_sext;   /* div_sum as in FastArgs */ uint32_t chirp, det_cap; Detection *det_list; uint32_t *det_count; };
+struct FastDetArgs { int W, G, div_sum, scaler, thr_sext;   /* div_sum as in FastArgs */ uint32_t chirp, det_cap; Detection *det_list; uint32_t *det_count; int thr_sh, out_sh; };
 template <int S, int LP, int CMODE, bool LINEAR>
 __device__ __noinline__ void fast_detections(const FastDetArgs a, int tl, uint32_t mask, const int *P, const short *X) {
   constexpr int N = 1 << S, TPC = FGeo<S, LP>::TPC, PTS = 1 << LP;
@@ -551,7 +579,7 @@ __device__ __noinline__ void fast_detections(const FastDetArgs a, int tl, uint32
     const int L = (int)((uint32_t)P[hi] - (uint32_t)P[hi - W]) >> a.div_sum, R = (int)((uint32_t)P[lo + W] - (uint32_t)P[lo]) >> a.div_sum;
     int t = CMODE == 0 ? ((R + L) >> 1) : (CMODE == 1 ? max(L, R) : min(L, R));
     t = lead_full ? (lagg_full ? t : R) : L;
-    const int thr = LINEAR ? t * a.scaler : t + a.scaler;
+    const int thr = LINEAR ? ((t * a.scaler) >> a.thr_sh) >> a.out_sh : t + a.scaler;   // (both shifts are 0 without binary points)
     const uint32_t slot = atomicAdd(a.det_count, 1u);
     if (slot < a.det_cap) {
       Detection d; d.chirp = a.chirp; d.bin = (uint32_t)n; d.threshold = (int)((uint32_t)thr << a.thr_sext) >> a.thr_sext; d.cut = X[mhx<S>(n)];
@@ -572,7 +600,7 @@ __device__ __noinline__ void fast_detections(const FastDetArgs a, int tl, uint32
 template <int S, int LP> constexpr int fast_min_blocks() {
   return (S == 14 && RSP_FAST_MINB14 > 0) ? RSP_FAST_MINB14 : ((S == 10 && RSP_FAST_MINB10 > 0) ? RSP_FAST_MINB10 : 1024 / FGeo<S, LP>::THREADS);
 }
-template <int S, int LP, int CMODE, bool LINEAR, int EJ, bool PG = false>
+template <int S, int LP, int CMODE, bool LINEAR, int EJ, bool PG = false, bool BPV = false>
 __global__ void __launch_bounds__(FGeo<S, LP>::THREADS, fast_min_blocks<S, LP>()) chain_fixed_fast_kernel(const FastArgs a) {
   using Gm = FGeo<S, LP>;
   constexpr int N = Gm::N, TPC = Gm::TPC, CPC = Gm::CPC, PTS = Gm::PTS;
@@ -642,7 +670,7 @@ __global__ void __launch_bounds__(FGeo<S, LP>::THREADS, fast_min_blocks<S, LP>()
         window_beats<S, LP>(a, tl, 0, pre);
       } else load_beats<S, LP>(a, grow, grr, tl, 0, pre);
     }
-    fast_passes<S, LP, TWSM>(a, c, tl, pre, grow, grr, xb, xm, loud, tws);
+    fast_passes<S, LP, TWSM, false, BPV>(a, c, tl, pre, grow, grr, xb, xm, loud, tws);
     if (gen) gen_advance(gr.q, gr.per, g_dq, g_dper, a.gen_period);
     // every thread is past the first barrier of the passes: the staging area has been read and can take the next rows
     if (stage && row0 + stride < a.n_rows) prefetch(row0 + stride);
@@ -686,13 +714,13 @@ __global__ void __launch_bounds__(FGeo<S, LP>::THREADS, fast_min_blocks<S, LP>()
 #pragma unroll
     for (int j = 0; j < PTS; ++j) {
       int pk;
-      if (j < EJ || j >= PTS - EJ) pk = fast_cfar_bin<S, LP, CMODE, LINEAR, true, PG>(a, j, tl, n2, P, pA, pB, pC, pD, Xt, gout, has_out, X);
-      else pk = fast_cfar_bin<S, LP, CMODE, LINEAR, false, PG>(a, j, tl, n2, P, pA, pB, pC, pD, Xt, gout, has_out, X);
+      if (j < EJ || j >= PTS - EJ) pk = fast_cfar_bin<S, LP, CMODE, LINEAR, true, PG, BPV>(a, j, tl, n2, P, pA, pB, pC, pD, Xt, gout, has_out, X);
+      else pk = fast_cfar_bin<S, LP, CMODE, LINEAR, false, PG, BPV>(a, j, tl, n2, P, pA, pB, pC, pD, Xt, gout, has_out, X);
       mask = mask * 2u + (uint32_t)pk;
       n2 += 2 * TPC;
     }
     if (mask != 0 && a.det_list != nullptr && active) {
-      const FastDetArgs da = {a.W, a.G, a.div_sum, a.scaler, a.thr_sext, a.row_base + row, a.det_cap, a.det_list, a.det_count};
+      const FastDetArgs da = {a.W, a.G, a.div_sum, a.scaler, a.thr_sext, a.row_base + row, a.det_cap, a.det_list, a.det_count, BPV ? a.thr_sh : 0, BPV ? a.out_sh : 0};
       fast_detections<S, LP, CMODE, LINEAR>(da, tl, mask, P, X);
     }
     if (stage) cp_async_wait_all();   // this thread's copies have landed; the barrier publishes everybody's
@@ -729,7 +757,7 @@ __device__ __forceinline__ void fast_scatter_words(int tl, const int (&w)[1 << L
   }
 }
 
-template <int S, int LP>
+template <int S, int LP, bool TW3 = false>
 __global__ void __launch_bounds__(FGeo<S, LP>::THREADS, fast_min_blocks<S, LP>()) fft_fixed_fast_kernel(const FastArgs a) {
   using Gm = FGeo<S, LP>;
   constexpr int N = Gm::N, TPC = Gm::TPC, CPC = Gm::CPC, PTS = Gm::PTS;
@@ -749,7 +777,7 @@ __global__ void __launch_bounds__(FGeo<S, LP>::THREADS, fast_min_blocks<S, LP>()
     uint32_t pre[16];
     if (LP == 4) load_beats<S, LP>(a, grow, gr, tl, 0, pre);
     int w[PTS];
-    fast_passes<S, LP, false, true>(a, c, tl, pre, grow, gr, xb, xm, loud, nullptr, w);   // ends with a barrier: the exchange buffer is free
+    fast_passes<S, LP, false, true, TW3>(a, c, tl, pre, grow, gr, xb, xm, loud, nullptr, w);   // ends with a barrier: the exchange buffer is free
     if (a.l2_prefetch && tl == 0 && row0 + stride + c < a.n_rows) {
       const uint32_t *nxt = a.in + (size_t)(row0 + stride + c) * N;
       asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" :: "l"(nxt), "r"(4 * N) : "memory");
@@ -1346,7 +1374,7 @@ static int fast_lp_runtime(int S) {
   return S == 14 ? lp14 : 4;
 }
 
-template <int S, int LP, int CMODE, bool LINEAR, int EJ, bool PG = false>
+template <int S, int LP, int CMODE, bool LINEAR, int EJ, bool PG = false, bool BPV = false>
 static rsp_status launch_fast_inst_lp(const LaunchCtx &c, const FastArgs &fa_in, cudaStream_t st, const char **err) {
   using Gm = FGeo<S, LP>;
   static int occ_dev[64] = {0};
@@ -1355,7 +1383,7 @@ static rsp_status launch_fast_inst_lp(const LaunchCtx &c, const FastArgs &fa_in,
   if (LP != 4) fa.stage = 0;
   const bool stage = LP == 4 && fast_stage_enabled(S);
   const size_t smem = ((size_t)Gm::CPC * (Gm::ROW + (Gm::TWS == 0 && stage ? Gm::N : 0)) + Gm::TWS) * sizeof(uint32_t);
-  auto kernel = chain_fixed_fast_kernel<S, LP, CMODE, LINEAR, EJ, PG>;
+  auto kernel = chain_fixed_fast_kernel<S, LP, CMODE, LINEAR, EJ, PG, BPV>;
   if (!occ) { const rsp_status s = launch_cfg(kernel, smem, Gm::THREADS, &occ, err); if (s != RSP_OK) return s; }
   const unsigned groups = (fa.n_rows + Gm::CPC - 1) / Gm::CPC;
   const unsigned grid = std::max(1u, std::min(groups, (unsigned)(c.sm_count * occ)));
@@ -1365,6 +1393,10 @@ static rsp_status launch_fast_inst_lp(const LaunchCtx &c, const FastArgs &fa_in,
 }
 template <int S, int CMODE, bool LINEAR, int EJ>
 static rsp_status launch_fast_inst(const LaunchCtx &c, const FastArgs &fa, bool pg, cudaStream_t st, const char **err) {
+  if (fa.tw3 != nullptr) {   // binPoint >= 2 (never together with peak grouping: fast_chain_supported)
+    if constexpr (S == 14) return launch_fast_inst_lp<S, 5, CMODE, LINEAR, EJ, false, true>(c, fa, st, err);
+    else return launch_fast_inst_lp<S, 4, CMODE, LINEAR, EJ, false, true>(c, fa, st, err);
+  }
   if (pg) {   // (one geometry per size: the peak-grouping kernels are the registers' other setting, not a tuning target)
     if constexpr (S == 14) return launch_fast_inst_lp<S, 5, CMODE, LINEAR, EJ, true>(c, fa, st, err);
     else return launch_fast_inst_lp<S, 4, CMODE, LINEAR, EJ, true>(c, fa, st, err);
@@ -1453,13 +1485,13 @@ static rsp_status launch_fast_os(const LaunchCtx &c, const FastArgs &fa, const G
   return RSP_OK;
 }
 
-template <int S, int LP>
+template <int S, int LP, bool TW3 = false>
 static rsp_status launch_fast_fft_lp(const LaunchCtx &c, const FastArgs &fa, cudaStream_t st, const char **err) {
   using Gm = FGeo<S, LP>;
   static int occ_dev[64] = {0};
   int &occ = occ_dev[c.device & 63];
   const size_t smem = (size_t)Gm::CPC * Gm::ROW * sizeof(uint32_t);
-  auto kernel = fft_fixed_fast_kernel<S, LP>;
+  auto kernel = fft_fixed_fast_kernel<S, LP, TW3>;
   if (!occ) { const rsp_status s = launch_cfg(kernel, smem, Gm::THREADS, &occ, err); if (s != RSP_OK) return s; }
   const unsigned groups = (fa.n_rows + Gm::CPC - 1) / Gm::CPC;
   const unsigned grid = std::max(1u, std::min(groups, (unsigned)(c.sm_count * occ)));
@@ -1484,6 +1516,10 @@ rsp_status RSP_CAT(launch_fast_size_, RSP_FAST_S)(int core, int cmode, bool line
 
 rsp_status RSP_CAT(launch_fast_fft_size_, RSP_FAST_S)(const LaunchCtx &ctx, const FastArgs &fa, cudaStream_t st, const char **err) {
   constexpr int S = RSP_FAST_S;
+  if (fa.tw3 != nullptr) {
+    if constexpr (S == 14) return launch_fast_fft_lp<S, 5, true>(ctx, fa, st, err);
+    else return launch_fast_fft_lp<S, 4, true>(ctx, fa, st, err);
+  }
   if constexpr (S == 14) { if (fast_lp_runtime(S) == 5) return launch_fast_fft_lp<S, 5>(ctx, fa, st, err); }
   return launch_fast_fft_lp<S, 4>(ctx, fa, st, err);
 }
@@ -1496,12 +1532,28 @@ RSP_DECL_FAST(11); RSP_DECL_FAST(12); RSP_DECL_FAST(13); RSP_DECL_FAST(14);
 
 // the FFT block alone on the fast passes: the configuration of the fast chain's transform (16-bit data and twiddles, binPoint 0, RoundHalfUp,
 // every stage scaled, forward, natural output order), any window
+// constants of the binPoint >= 2 kernels (FastArgs::tw3 ...): the twiddle product's two trims, and for the chain the threshold's binary points
+static void fast_fill_tw3(const FxArgs &a, FastArgs &fa, bool with_cfar) {
+  const int bp_a = a.bp, bp_b = a.tw_bp, ctx = (bp_a > bp_b ? bp_a : bp_b) + 1;
+  fa.tw3 = reinterpret_cast<const int2 *>(a.tww);
+  fa.s1 = bp_a + bp_b - ctx; fa.s2 = ctx - bp_a;
+  fa.h1 = 1 << (fa.s1 - 1); fa.h1m = fa.h1 - 1; fa.h2 = 1 << (fa.s2 - 1); fa.h2m = fa.h2 - 1;
+  fa.thr_sh = 0; fa.ncut_mul = -1; fa.out_sh = 0;
+  if (with_cfar) {   // cfar_bin: product binary point 2 b, context b + 1 -> trimmed by b - 1 (Floor), compared and reported from tbp = b + 1
+    const int b = a.in_bp, s1c = b >= 1 ? b - 1 : 0, tbp = 2 * b - s1c;
+    fa.thr_sh = s1c; fa.ncut_mul = -(1 << (tbp - b)); fa.out_sh = tbp - b;
+  }
+}
+static bool fast_tw3_ok(const Plan &pl, const FxArgs &a) {
+  return pl.mode == MODE_FAST3 && a.bp >= 2 && a.bp <= 15 && a.tw_bp == 14 && a.tww != nullptr && !a.use4muls;
+}
+
 bool fast_fft_supported(const Plan &pl, const FxArgs &a) {
-  if (pl.mode != MODE_FAST || pl.first_stage != STAGE_FFT || pl.last_stage != STAGE_FFT) return false;
+  if ((pl.mode != MODE_FAST && !fast_tw3_ok(pl, a)) || pl.first_stage != STAGE_FFT || pl.last_stage != STAGE_FFT) return false;
   if (pl.S < RSP_FAST_SMIN || pl.S > RSP_FAST_SMAX) return false;
   static int on = -1;
   if (on < 0) { const char *e = std::getenv("RSP_FAST_FFT"); on = (e != nullptr && e[0] == '0') ? 0 : 1; }   // A/B knob
-  return on && a.bp == 0 && a.tw_bp == 14 && a.bitrev && a.out != nullptr && a.in != nullptr;
+  return on && (a.bp == 0 || pl.mode == MODE_FAST3) && a.tw_bp == 14 && a.bitrev && a.out != nullptr && a.in != nullptr;
 }
 
 rsp_status launch_fast_fft(const Plan &pl, const LaunchCtx &ctx, const FxArgs &a, cudaStream_t st, const char **err) {
@@ -1511,6 +1563,7 @@ rsp_status launch_fast_fft(const Plan &pl, const LaunchCtx &ctx, const FxArgs &a
   fa.win4 = a.win_on ? a.win4 : nullptr;
   for (int L = 0; L < 16; ++L) fa.tw_off[L] = a.tw_off[L];
   fa.one = 1; fa.m1 = -1; fa.rnd[0] = 0x8000; fa.rnd[1] = -0x8000; fa.rnd[2] = 0x7FFF; fa.rnd[3] = -0x7FFF;
+  if (pl.mode == MODE_FAST3) fast_fill_tw3(a, fa, false);
   { static int l2p = -1; if (l2p < 0) { const char *e = std::getenv("RSP_FAST_L2_PREFETCH"); l2p = e ? std::atoi(e) : 1; }
     fa.l2_prefetch = (l2p != 0 && (reinterpret_cast<uintptr_t>(a.in) & 15u) == 0) ? 1 : 0; }
   switch (pl.S) {
@@ -1543,12 +1596,16 @@ static bool fast_os_supported(const FxArgs &a) {
 }
 
 bool fast_chain_supported(const Plan &pl, const FxArgs &a) {
-  if (pl.mode != MODE_FAST || pl.first_stage != STAGE_FFT || pl.last_stage != STAGE_CFAR) return false;
+  const bool tw3 = fast_tw3_ok(pl, a);   // binPoint >= 2: the CA kernel's binary-point variant (FftMagCfarChainVanillaApp has 12)
+  if ((pl.mode != MODE_FAST && !tw3) || pl.first_stage != STAGE_FFT || pl.last_stage != STAGE_CFAR) return false;
   if (pl.S < RSP_FAST_SMIN || pl.S > RSP_FAST_SMAX) return false;
-  if (a.bp != 0 || a.tw_bp != 14 || !a.bitrev || a.sel != 2 || a.mag_w != 16 || a.mag_bp != 0) return false;
-  if (a.core == CORE_LIS) return fast_gos_supported(a);
-  if (a.core == CORE_OS) return fast_os_supported(a);
-  if (a.core != CORE_MEM || a.in_w != 16 || a.in_bp != 0 || a.sc_bp != 0 || a.thr_bp != 0 || a.send_cut) return false;
+  if ((a.bp != 0 && !tw3) || a.tw_bp != 14 || !a.bitrev || a.sel != 2 || a.mag_w != 16) return false;   // (the JPL magnitude does not look at the binary point)
+  if (!tw3 && a.mag_bp != 0) return false;
+  if (a.core == CORE_LIS) return !tw3 && fast_gos_supported(a);
+  if (a.core == CORE_OS) return !tw3 && fast_os_supported(a);
+  if (a.core != CORE_MEM || a.in_w != 16 || a.send_cut) return false;
+  if (tw3 ? (a.in_bp != a.sc_bp || a.in_bp != a.thr_bp || a.in_bp < 0 || a.in_bp > 15 || a.peak_grouping || a.cfar_trim != TRIM_FLOOR)
+          : (a.in_bp != 0 || a.sc_bp != 0 || a.thr_bp != 0)) return false;
   if (a.out == nullptr && a.det_list == nullptr) return false;
   if (a.thr_w < 1 || a.thr_w > 32 || a.G < 1 || a.W < 1 || a.div_sum < 0 || a.div_sum > 30) return false;
   const int ej = fast_edge_iters(pl.S, a.W, a.G);
@@ -1575,6 +1632,8 @@ rsp_status launch_fast_chain(const Plan &pl, const LaunchCtx &ctx, const FxArgs 
   fa.out_mul = (int)(1u << (a.binw + 1)); fa.thr_sext = 32 - a.thr_w;
   fa.det_list = a.det_list; fa.det_count = a.det_count; fa.det_cap = a.det_cap;
   fa.pg_full = a.peak_grouping ? (a.G == a.guard_window_size ? 1 : 0) : -1;   // -1: no peak grouping
+  fa.tw3 = nullptr;
+  if (pl.mode == MODE_FAST3) fast_fill_tw3(a, fa, true);
   // measured on B200 (profiles/r02_d_l2prefetch.txt): N = 16384 +5.3 %, N = 4096 +1.9 %, N = 1024 +1.3 %; RSP_FAST_L2_PREFETCH=0 turns it off
   { static int l2p = -1; if (l2p < 0) { const char *e = std::getenv("RSP_FAST_L2_PREFETCH"); l2p = e ? std::atoi(e) : 1; }
     fa.l2_prefetch = (l2p != 0 && a.gen_full == nullptr && (reinterpret_cast<uintptr_t>(a.in) & 15u) == 0) ? 1 : 0; }

@@ -737,3 +737,41 @@ def test_fast_f32_kernel_peak_grouping(cuda, oracle, log_n, W, G, gws, mode, lin
     check_f32(thr, pk, mag, want_thr, want_pk, f"fp32 pg mode {mode} lin {lin}")
     _, _, pk0 = f64_chain(oracle, xq, log_n, 2, dict(regs, peakGrouping=0), scaler, W, G, guard_window_size=gws)
     assert pk0.sum() >= want_pk.sum() > 0
+
+
+@pytest.mark.parametrize("log_n,bp,W,G,mode,lin", [(10, 12, 64, 4, 0, 1), (10, 14, 16, 2, 1, 0), (11, 12, 32, 4, 2, 1), (12, 2, 64, 4, 0, 1), (13, 13, 16, 1, 1, 1),
+                                                    (14, 12, 64, 8, 0, 1), (14, 14, 32, 3, 2, 0), (12, 15, 32, 2, 0, 1)])
+def test_fast_kernel_binary_points(cuda, oracle, log_n, bp, W, G, mode, lin):
+    """binPoint >= 2 on the specialised kernels (FftMagCfarChainVanillaApp / RxFftMagCfarTxChainApp have 12: src/main/scala/FftMagCfarChain.scala:76-120):
+    the 3-multiplier twiddle product with per-product trim and the CFAR threshold with the operands' binary points, every size, quiet and
+    full-scale rows (every wrap), the -32768 corners, ragged counts, the detection list, and the FFT block alone (fft_fixed_fast_kernel)"""
+    n = 1 << log_n
+    rows = 7 if log_n <= 12 else 3
+    beats = np.concatenate([synth.chirps_fixed(rows - 3, n, seed=160 + log_n, noise=2.0 ** -4), synth.random_beats(2, n, seed=170 + log_n),
+                            np.full((1, n), 0x80008000, dtype=np.uint32)])
+    p = fixed_params(n, 64, max(G, 1), bp=bp)
+    p.cfarParams.protoScaler = FixedPoint(16, bp)          # the apps' choice: input, threshold and scaler share the binary point
+    regs = dict(fftWin=n, thresholdScaler=int(3.25 * (1 << bp)) if lin else int(0.01 * (1 << bp)), logOrLinearMode=lin, divSum=int(np.log2(W)),
+                peakGrouping=0, cfarMode=mode, windowCells=W, guardCells=G)
+    fft, mag, cfar = oracle_cfgs(oracle, p, log_n, 2, regs)
+    want, want_fft, _ = oracle.chain_fixed_words(fft, mag, cfar, beats, want_stages=True)
+    with R.FftMagCfarChainVanilla(p) as ch:
+        configure(ch, log_n, 2, regs)
+        assert ch.variant == f"chain_fixed_fast<{log_n}>", ch.variant
+        d_in = to_dev(cuda, beats)
+        d_out = cuda.zeros_like(d_in)
+        d_fft = cuda.zeros_like(d_in)
+        det_list = cuda.zeros((rows * n, 4), dtype=cuda.int32, device="cuda")
+        det_count = cuda.zeros(1, dtype=cuda.int32, device="cuda")
+        ch.run(d_in, rows, 1, out=d_out, det_list=det_list, det_count=det_count)
+        ch.fft(d_in, rows, d_fft)
+        cuda.cuda.synchronize()
+        got, got_fft = from_dev_u32(d_out), from_dev_u32(d_fft)
+        k = int(det_count.item())
+        dets = det_list[:k].cpu().numpy()
+    assert (got_fft == want_fft).all(), f"FFT: {int((got_fft != want_fft).sum())} beats differ, first at {np.argwhere(got_fft != want_fft)[:3].tolist()}"
+    assert (got == want).all(), f"{int((got != want).sum())} beats differ, first at {np.argwhere(got != want)[:3].tolist()}"
+    thr, bins, peak = decode_cfar_words(want, n)
+    assert k == int(peak.sum()) and k > 0
+    exp = {(r, b): int(thr[r, b]) for r, b in np.argwhere(peak == 1)}
+    assert {(int(d[0]), int(d[1])): int(d[2]) & 0xFFFF for d in dets} == exp
