@@ -58,7 +58,9 @@ struct FastArgs {
   // (rsp_device.cuh, cmul) on the raw twiddles, and the CFAR threshold with the operands' binary points (cfar_bin)
   const int2 *tw3;       // raw (cos, -sin) in Q2.14, same order and offsets as tw
   int s1, s2, h1, h1m, h2, h2m;   // product trim: >> s1 with h1 = 1 << (s1 - 1) (h1m = h1 - 1 for negated operands), result trim >> s2 with h2 / h2m
-  int thr_sh, ncut_mul, out_sh;   // linear threshold: (t * scaler) >> thr_sh has binary point tbp; peak = thr - cut * 2^(tbp - inBP) < 0 (ncut_mul = -2^(tbp - inBP)); field = thr >> out_sh
+  // BPC kernels (the CFAR operands carry binary points, cfar_bin): linear thr = (t * scaler) >> thr_sh, log thr = t * t_mul + sc_pre, both at binary
+  // point tbp; peak = thr - cut * 2^(tbp - inBP) < 0 (ncut_mul = -2^(tbp - inBP)); threshold field = thr >> out_sh (tbp -> thresholdBP)
+  int thr_sh, ncut_mul, out_sh, t_mul, sc_pre, bpc;
   int pg_full;   // peak grouping (PG kernels): 1 = guardCells equals the generator's guardWindowSize, the left neighbour is read (CFARCoreWithMem.scala:182-184)
 };
 
@@ -527,7 +529,7 @@ __device__ __forceinline__ int chirp_scan_exclusive(int total, int c, int tl, in
 // (0 unless guardCells == guardWindowSize) and laggGuard.head = x[n + guardCells] (CFARCoreWithMem.scala:182-184; both from the lagging side).
 // BPV: the operands carry a binary point (inBP = scalerBP = thresholdBP = b >= 1): the linear threshold is the product trimmed to the
 // context's binary point tbp (Floor: an arithmetic shift), the cell under test is compared at tbp, the field is the threshold at b.
-template <int S, int LP, int CMODE, bool LINEAR, bool EDGE, bool PG = false, bool BPV = false>
+template <int S, int LP, int CMODE, bool LINEAR, bool EDGE, bool PG = false, bool BPV = false>   // BPV here = the kernel's BPC
 __device__ __forceinline__ int fast_cfar_bin(const FastArgs &a, int j, int tl, int n2, const int *P, const int *pA, const int *pB,
                                              const int *pC, const int *pD, const short *X, uint32_t *gout, bool has_out, const short *X0 = nullptr) {
   constexpr int N = 1 << S, TPC = FGeo<S, LP>::TPC;
@@ -547,10 +549,10 @@ __device__ __forceinline__ int fast_cfar_bin(const FastArgs &a, int j, int tl, i
   L = sar(L, a.div_sum); R = sar(R, a.div_sum);
   int t = CMODE == 0 ? sar(fadd(1, R, 1, L, a.one, a.m1), 1) : (CMODE == 1 ? max(L, R) : min(L, R));
   if (EDGE) t = lead_full ? (lagg_full ? t : R) : L;
-  const int thr = LINEAR ? ((BPV) ? sar(t * a.scaler, a.thr_sh) : t * a.scaler) : fadd(1, t, 1, a.scaler, a.one, a.m1);
+  const int thr = LINEAR ? ((BPV) ? sar(t * a.scaler, a.thr_sh) : t * a.scaler) : (BPV ? imad(t, a.t_mul, a.sc_pre) : fadd(1, t, 1, a.scaler, a.one, a.m1));
   const int cut = X[mhx<S>(j * TPC)];   // X points at the thread's first bin (mhx is additive over tl + j * TPC)
   // peak = cut > thr as the sign bit of thr - cut (|thr| < 2^31 - 2^16 is checked by the host)
-  int pk = (BPV && LINEAR) ? (int)((uint32_t)imad(cut, a.ncut_mul, thr) >> 31) : (int)((uint32_t)fadd(1, thr, -1, cut, a.one, a.m1) >> 31);
+  int pk = BPV ? (int)((uint32_t)imad(cut, a.ncut_mul, thr) >> 31) : (int)((uint32_t)fadd(1, thr, -1, cut, a.one, a.m1) >> 31);
   if (PG) {
     const int n1 = n + 1, ng = n + a.G;
     int left = 0, right = 0;
@@ -559,7 +561,7 @@ __device__ __forceinline__ int fast_cfar_bin(const FastArgs &a, int j, int tl, i
     pk = (pk != 0 && cut > left && cut > right) ? 1 : 0;
   }
   if (has_out) {
-    const int tf = (BPV && LINEAR) ? sar(thr, a.out_sh) : thr;
+    const int tf = BPV ? sar(thr, a.out_sh) : thr;
     const int w0 = (int)(((uint32_t)tf & a.thr_mask) * (uint32_t)a.out_mul + (uint32_t)n2);   // threshold field | bin field (n << 1)
     gout[n] = (uint32_t)fadd(1, pk, 1, w0, a.one, a.m1);
   }
@@ -567,7 +569,7 @@ __device__ __forceinline__ int fast_cfar_bin(const FastArgs &a, int j, int tl, i
 }
 
 // detections of one thread: bit (PTS - 1 - j) of `mask` = peak of bin tl + j * TPC.  Rare path, recomputes from shared memory.
-struct FastDetArgs { int W, G, div_sum, scaler, thr_sext;   /* div_sum as in FastArgs */ uint32_t chirp, det_cap; Detection *det_list; uint32_t *det_count; int thr_sh, out_sh; };
+struct FastDetArgs { int W, G, div_sum, scaler, thr_sext;   /* div_sum as in FastArgs */ uint32_t chirp, det_cap; Detection *det_list; uint32_t *det_count; int thr_sh, out_sh, t_mul, sc_pre; };
 template <int S, int LP, int CMODE, bool LINEAR>
 __device__ __noinline__ void fast_detections(const FastDetArgs a, int tl, uint32_t mask, const int *P, const short *X) {
   constexpr int N = 1 << S, TPC = FGeo<S, LP>::TPC, PTS = 1 << LP;
@@ -579,7 +581,7 @@ __device__ __noinline__ void fast_detections(const FastDetArgs a, int tl, uint32
     const int L = (int)((uint32_t)P[hi] - (uint32_t)P[hi - W]) >> a.div_sum, R = (int)((uint32_t)P[lo + W] - (uint32_t)P[lo]) >> a.div_sum;
     int t = CMODE == 0 ? ((R + L) >> 1) : (CMODE == 1 ? max(L, R) : min(L, R));
     t = lead_full ? (lagg_full ? t : R) : L;
-    const int thr = LINEAR ? ((t * a.scaler) >> a.thr_sh) >> a.out_sh : t + a.scaler;   // (both shifts are 0 without binary points)
+    const int thr = (LINEAR ? (t * a.scaler) >> a.thr_sh : t * a.t_mul + a.sc_pre) >> a.out_sh;   // (without binary points: shifts 0, t_mul 1, sc_pre = scaler)
     const uint32_t slot = atomicAdd(a.det_count, 1u);
     if (slot < a.det_cap) {
       Detection d; d.chirp = a.chirp; d.bin = (uint32_t)n; d.threshold = (int)((uint32_t)thr << a.thr_sext) >> a.thr_sext; d.cut = X[mhx<S>(n)];
@@ -600,7 +602,7 @@ __device__ __noinline__ void fast_detections(const FastDetArgs a, int tl, uint32
 template <int S, int LP> constexpr int fast_min_blocks() {
   return (S == 14 && RSP_FAST_MINB14 > 0) ? RSP_FAST_MINB14 : ((S == 10 && RSP_FAST_MINB10 > 0) ? RSP_FAST_MINB10 : 1024 / FGeo<S, LP>::THREADS);
 }
-template <int S, int LP, int CMODE, bool LINEAR, int EJ, bool PG = false, bool BPV = false>
+template <int S, int LP, int CMODE, bool LINEAR, int EJ, bool PG = false, bool TW3 = false, bool BPC = false>
 __global__ void __launch_bounds__(FGeo<S, LP>::THREADS, fast_min_blocks<S, LP>()) chain_fixed_fast_kernel(const FastArgs a) {
   using Gm = FGeo<S, LP>;
   constexpr int N = Gm::N, TPC = Gm::TPC, CPC = Gm::CPC, PTS = Gm::PTS;
@@ -670,7 +672,7 @@ __global__ void __launch_bounds__(FGeo<S, LP>::THREADS, fast_min_blocks<S, LP>()
         window_beats<S, LP>(a, tl, 0, pre);
       } else load_beats<S, LP>(a, grow, grr, tl, 0, pre);
     }
-    fast_passes<S, LP, TWSM, false, BPV>(a, c, tl, pre, grow, grr, xb, xm, loud, tws);
+    fast_passes<S, LP, TWSM, false, TW3>(a, c, tl, pre, grow, grr, xb, xm, loud, tws);
     if (gen) gen_advance(gr.q, gr.per, g_dq, g_dper, a.gen_period);
     // every thread is past the first barrier of the passes: the staging area has been read and can take the next rows
     if (stage && row0 + stride < a.n_rows) prefetch(row0 + stride);
@@ -714,13 +716,13 @@ __global__ void __launch_bounds__(FGeo<S, LP>::THREADS, fast_min_blocks<S, LP>()
 #pragma unroll
     for (int j = 0; j < PTS; ++j) {
       int pk;
-      if (j < EJ || j >= PTS - EJ) pk = fast_cfar_bin<S, LP, CMODE, LINEAR, true, PG, BPV>(a, j, tl, n2, P, pA, pB, pC, pD, Xt, gout, has_out, X);
-      else pk = fast_cfar_bin<S, LP, CMODE, LINEAR, false, PG, BPV>(a, j, tl, n2, P, pA, pB, pC, pD, Xt, gout, has_out, X);
+      if (j < EJ || j >= PTS - EJ) pk = fast_cfar_bin<S, LP, CMODE, LINEAR, true, PG, BPC>(a, j, tl, n2, P, pA, pB, pC, pD, Xt, gout, has_out, X);
+      else pk = fast_cfar_bin<S, LP, CMODE, LINEAR, false, PG, BPC>(a, j, tl, n2, P, pA, pB, pC, pD, Xt, gout, has_out, X);
       mask = mask * 2u + (uint32_t)pk;
       n2 += 2 * TPC;
     }
     if (mask != 0 && a.det_list != nullptr && active) {
-      const FastDetArgs da = {a.W, a.G, a.div_sum, a.scaler, a.thr_sext, a.row_base + row, a.det_cap, a.det_list, a.det_count, BPV ? a.thr_sh : 0, BPV ? a.out_sh : 0};
+      const FastDetArgs da = {a.W, a.G, a.div_sum, a.scaler, a.thr_sext, a.row_base + row, a.det_cap, a.det_list, a.det_count, BPC ? a.thr_sh : 0, BPC ? a.out_sh : 0, BPC ? a.t_mul : 1, BPC ? a.sc_pre : a.scaler};
       fast_detections<S, LP, CMODE, LINEAR>(da, tl, mask, P, X);
     }
     if (stage) cp_async_wait_all();   // this thread's copies have landed; the barrier publishes everybody's
@@ -1374,7 +1376,7 @@ static int fast_lp_runtime(int S) {
   return S == 14 ? lp14 : 4;
 }
 
-template <int S, int LP, int CMODE, bool LINEAR, int EJ, bool PG = false, bool BPV = false>
+template <int S, int LP, int CMODE, bool LINEAR, int EJ, bool PG = false, bool TW3 = false, bool BPC = false>
 static rsp_status launch_fast_inst_lp(const LaunchCtx &c, const FastArgs &fa_in, cudaStream_t st, const char **err) {
   using Gm = FGeo<S, LP>;
   static int occ_dev[64] = {0};
@@ -1383,7 +1385,7 @@ static rsp_status launch_fast_inst_lp(const LaunchCtx &c, const FastArgs &fa_in,
   if (LP != 4) fa.stage = 0;
   const bool stage = LP == 4 && fast_stage_enabled(S);
   const size_t smem = ((size_t)Gm::CPC * (Gm::ROW + (Gm::TWS == 0 && stage ? Gm::N : 0)) + Gm::TWS) * sizeof(uint32_t);
-  auto kernel = chain_fixed_fast_kernel<S, LP, CMODE, LINEAR, EJ, PG, BPV>;
+  auto kernel = chain_fixed_fast_kernel<S, LP, CMODE, LINEAR, EJ, PG, TW3, BPC>;
   if (!occ) { const rsp_status s = launch_cfg(kernel, smem, Gm::THREADS, &occ, err); if (s != RSP_OK) return s; }
   const unsigned groups = (fa.n_rows + Gm::CPC - 1) / Gm::CPC;
   const unsigned grid = std::max(1u, std::min(groups, (unsigned)(c.sm_count * occ)));
@@ -1393,9 +1395,13 @@ static rsp_status launch_fast_inst_lp(const LaunchCtx &c, const FastArgs &fa_in,
 }
 template <int S, int CMODE, bool LINEAR, int EJ>
 static rsp_status launch_fast_inst(const LaunchCtx &c, const FastArgs &fa, bool pg, cudaStream_t st, const char **err) {
-  if (fa.tw3 != nullptr) {   // binPoint >= 2 (never together with peak grouping: fast_chain_supported)
-    if constexpr (S == 14) return launch_fast_inst_lp<S, 5, CMODE, LINEAR, EJ, false, true>(c, fa, st, err);
-    else return launch_fast_inst_lp<S, 4, CMODE, LINEAR, EJ, false, true>(c, fa, st, err);
+  if (fa.tw3 != nullptr) {   // binPoint >= 2 (never together with peak grouping: fast_chain_supported); its CFAR phase is the binary-point one
+    if constexpr (S == 14) return launch_fast_inst_lp<S, 5, CMODE, LINEAR, EJ, false, true, true>(c, fa, st, err);
+    else return launch_fast_inst_lp<S, 4, CMODE, LINEAR, EJ, false, true, true>(c, fa, st, err);
+  }
+  if (fa.bpc) {   // binPoint 0 in the transform, binary points in the CFAR (RspChainVanillaSpec: input 0, threshold 3, scaler 6)
+    if constexpr (S == 14) return launch_fast_inst_lp<S, 5, CMODE, LINEAR, EJ, false, false, true>(c, fa, st, err);
+    else return launch_fast_inst_lp<S, 4, CMODE, LINEAR, EJ, false, false, true>(c, fa, st, err);
   }
   if (pg) {   // (one geometry per size: the peak-grouping kernels are the registers' other setting, not a tuning target)
     if constexpr (S == 14) return launch_fast_inst_lp<S, 5, CMODE, LINEAR, EJ, true>(c, fa, st, err);
@@ -1533,16 +1539,30 @@ RSP_DECL_FAST(11); RSP_DECL_FAST(12); RSP_DECL_FAST(13); RSP_DECL_FAST(14);
 // the FFT block alone on the fast passes: the configuration of the fast chain's transform (16-bit data and twiddles, binPoint 0, RoundHalfUp,
 // every stage scaled, forward, natural output order), any window
 // constants of the binPoint >= 2 kernels (FastArgs::tw3 ...): the twiddle product's two trims, and for the chain the threshold's binary points
-static void fast_fill_tw3(const FxArgs &a, FastArgs &fa, bool with_cfar) {
+static void fast_fill_tw3(const FxArgs &a, FastArgs &fa) {
   const int bp_a = a.bp, bp_b = a.tw_bp, ctx = (bp_a > bp_b ? bp_a : bp_b) + 1;
   fa.tw3 = reinterpret_cast<const int2 *>(a.tww);
   fa.s1 = bp_a + bp_b - ctx; fa.s2 = ctx - bp_a;
   fa.h1 = 1 << (fa.s1 - 1); fa.h1m = fa.h1 - 1; fa.h2 = 1 << (fa.s2 - 1); fa.h2m = fa.h2 - 1;
-  fa.thr_sh = 0; fa.ncut_mul = -1; fa.out_sh = 0;
-  if (with_cfar) {   // cfar_bin: product binary point 2 b, context b + 1 -> trimmed by b - 1 (Floor), compared and reported from tbp = b + 1
-    const int b = a.in_bp, s1c = b >= 1 ? b - 1 : 0, tbp = 2 * b - s1c;
-    fa.thr_sh = s1c; fa.ncut_mul = -(1 << (tbp - b)); fa.out_sh = tbp - b;
-  }
+}
+// the CFAR threshold with binary points (rsp_device.cuh, cfar_bin): linear = the product trimmed (Floor) to the context's binary point
+// max(inBP, scalerBP) + 1, log = the sum at max(inBP, scalerBP); the cell under test is compared at that binary point tbp and the threshold is
+// reported at thresholdBP.  Returns false when a shift leaves the range the kernel's 32-bit arithmetic covers.
+static bool fast_cfar_bp(const FxArgs &a, FastArgs *fa) {
+  const int ib = a.in_bp, sb = a.sc_bp, tb = a.thr_bp;
+  int thr_sh = 0, tbp;
+  if (a.log_or_linear) { const int prod = ib + sb, ctx = (ib > sb ? ib : sb) + 1; thr_sh = prod > ctx ? prod - ctx : 0; tbp = prod - thr_sh; }
+  else tbp = ib > sb ? ib : sb;
+  const int cut_sh = tbp - ib, out_sh = tbp - tb, sc_sh = tbp - sb;
+  if (ib < 0 || sb < 0 || tb < 0 || cut_sh < 0 || cut_sh > 14 || out_sh < 0 || out_sh > 30 || thr_sh > 30) return false;
+  if (!a.log_or_linear) {
+    if (sc_sh < 0 || sc_sh > 14) return false;
+    const long long sp = (long long)a.scaler << sc_sh;
+    if (sp >= (1LL << 30) || sp <= -(1LL << 30)) return false;
+    if (fa) fa->sc_pre = (int)sp;
+  } else if (fa) fa->sc_pre = a.scaler;
+  if (fa) { fa->thr_sh = thr_sh; fa->ncut_mul = -(1 << cut_sh); fa->out_sh = out_sh; fa->t_mul = 1 << cut_sh; }
+  return true;
 }
 static bool fast_tw3_ok(const Plan &pl, const FxArgs &a) {
   return pl.mode == MODE_FAST3 && a.bp >= 2 && a.bp <= 15 && a.tw_bp == 14 && a.tww != nullptr && !a.use4muls;
@@ -1563,7 +1583,7 @@ rsp_status launch_fast_fft(const Plan &pl, const LaunchCtx &ctx, const FxArgs &a
   fa.win4 = a.win_on ? a.win4 : nullptr;
   for (int L = 0; L < 16; ++L) fa.tw_off[L] = a.tw_off[L];
   fa.one = 1; fa.m1 = -1; fa.rnd[0] = 0x8000; fa.rnd[1] = -0x8000; fa.rnd[2] = 0x7FFF; fa.rnd[3] = -0x7FFF;
-  if (pl.mode == MODE_FAST3) fast_fill_tw3(a, fa, false);
+  if (pl.mode == MODE_FAST3) fast_fill_tw3(a, fa);
   { static int l2p = -1; if (l2p < 0) { const char *e = std::getenv("RSP_FAST_L2_PREFETCH"); l2p = e ? std::atoi(e) : 1; }
     fa.l2_prefetch = (l2p != 0 && (reinterpret_cast<uintptr_t>(a.in) & 15u) == 0) ? 1 : 0; }
   switch (pl.S) {
@@ -1604,8 +1624,8 @@ bool fast_chain_supported(const Plan &pl, const FxArgs &a) {
   if (a.core == CORE_LIS) return !tw3 && fast_gos_supported(a);
   if (a.core == CORE_OS) return !tw3 && fast_os_supported(a);
   if (a.core != CORE_MEM || a.in_w != 16 || a.send_cut) return false;
-  if (tw3 ? (a.in_bp != a.sc_bp || a.in_bp != a.thr_bp || a.in_bp < 0 || a.in_bp > 15 || a.peak_grouping || a.cfar_trim != TRIM_FLOOR)
-          : (a.in_bp != 0 || a.sc_bp != 0 || a.thr_bp != 0)) return false;
+  const bool bpc = tw3 || a.in_bp != 0 || a.sc_bp != 0 || a.thr_bp != 0;   // binary points in the CFAR: its own instantiation, without peak grouping
+  if (bpc && (a.peak_grouping || a.cfar_trim != TRIM_FLOOR || !fast_cfar_bp(a, nullptr))) return false;
   if (a.out == nullptr && a.det_list == nullptr) return false;
   if (a.thr_w < 1 || a.thr_w > 32 || a.G < 1 || a.W < 1 || a.div_sum < 0 || a.div_sum > 30) return false;
   const int ej = fast_edge_iters(pl.S, a.W, a.G);
@@ -1615,7 +1635,8 @@ bool fast_chain_supported(const Plan &pl, const FxArgs &a) {
   const long long smax = std::min<long long>((long long)a.W * 32768, 1LL << (a.sumw - 1));
   const long long tmax = (smax >> a.div_sum) + 1, sc = a.scaler < 0 ? -(long long)a.scaler : a.scaler;
   const long long lim = (1LL << 31) - (1LL << 16);   // the peak is the sign bit of thr - cut
-  if (a.log_or_linear ? (tmax * sc >= lim) : (tmax + sc >= lim)) return false;
+  const int lsh = (a.in_bp > a.sc_bp ? a.in_bp : a.sc_bp);   // log mode adds at max(inBP, scalerBP)
+  if (a.log_or_linear ? (tmax * sc >= lim) : ((tmax << (lsh - a.in_bp)) + (sc << (lsh - a.sc_bp)) >= lim)) return false;
   if (a.binw + 1 > 31) return false;
   return true;
 }
@@ -1632,8 +1653,9 @@ rsp_status launch_fast_chain(const Plan &pl, const LaunchCtx &ctx, const FxArgs 
   fa.out_mul = (int)(1u << (a.binw + 1)); fa.thr_sext = 32 - a.thr_w;
   fa.det_list = a.det_list; fa.det_count = a.det_count; fa.det_cap = a.det_cap;
   fa.pg_full = a.peak_grouping ? (a.G == a.guard_window_size ? 1 : 0) : -1;   // -1: no peak grouping
-  fa.tw3 = nullptr;
-  if (pl.mode == MODE_FAST3) fast_fill_tw3(a, fa, true);
+  fa.tw3 = nullptr; fa.bpc = 0; fa.thr_sh = 0; fa.ncut_mul = -1; fa.out_sh = 0; fa.t_mul = 1; fa.sc_pre = a.scaler;
+  if (pl.mode == MODE_FAST3) fast_fill_tw3(a, fa);
+  if (a.core == CORE_MEM && (pl.mode == MODE_FAST3 || a.in_bp != 0 || a.sc_bp != 0 || a.thr_bp != 0)) { fast_cfar_bp(a, &fa); fa.bpc = 1; }
   // measured on B200 (profiles/r02_d_l2prefetch.txt): N = 16384 +5.3 %, N = 4096 +1.9 %, N = 1024 +1.3 %; RSP_FAST_L2_PREFETCH=0 turns it off
   { static int l2p = -1; if (l2p < 0) { const char *e = std::getenv("RSP_FAST_L2_PREFETCH"); l2p = e ? std::atoi(e) : 1; }
     fa.l2_prefetch = (l2p != 0 && a.gen_full == nullptr && (reinterpret_cast<uintptr_t>(a.in) & 15u) == 0) ? 1 : 0; }

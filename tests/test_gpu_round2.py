@@ -775,3 +775,37 @@ def test_fast_kernel_binary_points(cuda, oracle, log_n, bp, W, G, mode, lin):
     assert k == int(peak.sum()) and k > 0
     exp = {(r, b): int(thr[r, b]) for r, b in np.argwhere(peak == 1)}
     assert {(int(d[0]), int(d[1])): int(d[2]) & 0xFFFF for d in dets} == exp
+
+
+@pytest.mark.parametrize("log_n,ib,tb,sb,mode,lin,fast", [(10, 0, 3, 6, 0, 1, True), (10, 0, 3, 6, 1, 0, True), (12, 4, 5, 2, 2, 1, True), (14, 0, 3, 6, 0, 1, True),
+                                                           (11, 2, 0, 9, 1, 0, True), (10, 0, 8, 2, 0, 1, False)])
+def test_fast_kernel_cfar_binary_points(cuda, oracle, log_n, ib, tb, sb, mode, lin, fast):
+    """binary points in the CFAR alone (RspChainVanillaSpec: protoIn 16.0, protoThreshold 16.3, protoScaler 16.6; src/test/scala/RspChainVanillaTester.scala:229-231)
+    behind a binPoint-0 transform: the specialised kernel's BPC instantiation, linear and log, other mixes; a threshold type finer than the
+    context's binary point (the field would need a left shift) stays on the run-time-parameter kernel -- same beats either way"""
+    n = 1 << log_n
+    rows = 6 if log_n <= 12 else 3
+    W, G = 32, 4
+    beats = np.concatenate([synth.chirps_fixed(rows - 2, n, seed=180 + log_n, noise=2.0 ** -4), synth.random_beats(2, n, seed=190 + log_n)])
+    p = fixed_params(n, 64, G)
+    p.cfarParams.protoIn, p.cfarParams.protoThreshold, p.cfarParams.protoScaler = FixedPoint(16, ib), FixedPoint(16, tb), FixedPoint(16, sb)
+    regs = dict(fftWin=n, thresholdScaler=int(3.5 * (1 << sb)) if lin else int(2.0 * (1 << sb)), logOrLinearMode=lin, divSum=5, peakGrouping=0, cfarMode=mode,
+                windowCells=W, guardCells=G)
+    fft, mag, cfar = oracle_cfgs(oracle, p, log_n, 2, regs)
+    want = oracle.chain_fixed_words(fft, mag, cfar, beats)
+    with R.FftMagCfarChainVanilla(p) as ch:
+        configure(ch, log_n, 2, regs)
+        assert (ch.variant == f"chain_fixed_fast<{log_n}>") == fast, ch.variant
+        d_in = to_dev(cuda, beats)
+        d_out = cuda.zeros_like(d_in)
+        det_list = cuda.zeros((rows * n, 4), dtype=cuda.int32, device="cuda")
+        det_count = cuda.zeros(1, dtype=cuda.int32, device="cuda")
+        ch.run(d_in, rows, 1, out=d_out, det_list=det_list, det_count=det_count)
+        cuda.cuda.synchronize()
+        got = from_dev_u32(d_out)
+        k = int(det_count.item())
+        dets = det_list[:k].cpu().numpy()
+    assert (got == want).all(), f"{int((got != want).sum())} beats differ, first at {np.argwhere(got != want)[:3].tolist()}"
+    thr, bins, peak = decode_cfar_words(want, n)
+    assert k == int(peak.sum()) and k > 0
+    assert {(int(d[0]), int(d[1])): int(d[2]) & 0xFFFF for d in dets} == {(r, b): int(thr[r, b]) for r, b in np.argwhere(peak == 1)}
