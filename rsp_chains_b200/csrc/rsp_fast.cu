@@ -1199,7 +1199,7 @@ __device__ __forceinline__ void gos_select8(const uint32_t *bp, uint32_t act, in
   }
 }
 
-template <int S>
+template <int S, bool TW3 = false>
 __global__ void __launch_bounds__(FGeo<S>::THREADS, 1024 / FGeo<S>::THREADS) chain_fixed_fast_os_kernel(const FastArgs a, const GosArgs ga) {
   using Gm = FGeo<S>;
   using Go = OGeo<S>;
@@ -1226,7 +1226,7 @@ __global__ void __launch_bounds__(FGeo<S>::THREADS, 1024 / FGeo<S>::THREADS) cha
     const GenRow no_gen = {0u, 0u};
     if (tl == 0) { uni[c][0] = 0u; uni[c][1] = 0xFFFFu; }
     load_beats<S, 4>(a, grow, no_gen, tl, 0, pre);
-    fast_passes<S, 4>(a, c, tl, pre, grow, no_gen, xb, xm, loud);   // ends with a barrier: magnitudes in X, the exchange buffer is free
+    fast_passes<S, 4, false, false, TW3>(a, c, tl, pre, grow, no_gen, xb, xm, loud);   // ends with a barrier: magnitudes in X, the exchange buffer is free
     os_build_planes<S>(xm, tl, bp, uni[c], nz);
     chirp_sync<S>(c);
     const uint32_t act = uni[c][0] ^ uni[c][1];       // planes in which the chirp's cells differ
@@ -1245,10 +1245,11 @@ __global__ void __launch_bounds__(FGeo<S>::THREADS, 1024 / FGeo<S>::THREADS) cha
         int pos = cl[j] != 0 ? (n - G - R) + __ffs((int)cl[j]) - 1 : (n + G + 1) + __ffs((int)cr[j]) - 1;
         pos = min(max(pos, 0), N - 1);
         const int t = X[mhx<S>(pos)];
-        int thr = ga.linear ? t * a.scaler : t + a.scaler;
+        int thr = ga.linear ? sar(t * a.scaler, a.thr_sh) : t * a.t_mul + a.sc_pre;   // (binary points at run time, see the GOS kernel)
         thr = both ? thr : 0;                         // the golden pads the edges with 0 (linear and log)
         const int cut = X[mhx<S>(n)];
-        const int pk = (both && cut > thr) ? 1 : 0;
+        const int pk = (both && (cut * a.ncut_mul + thr) < 0) ? 1 : 0;
+        thr = sar(thr, a.out_sh);
         ow[j] = ((uint32_t)thr & a.thr_mask) * (uint32_t)a.out_mul + (uint32_t)(n << 1) + (uint32_t)pk;
         if (pk && a.det_list != nullptr && active) {
           const uint32_t slot = atomicAdd(a.det_count, 1u);
@@ -1272,7 +1273,7 @@ __global__ void __launch_bounds__(FGeo<S>::THREADS, 1024 / FGeo<S>::THREADS) cha
 // cells starting at s is one radix selection per window start over NWD = ceil(W / 32) mask words (W <= 128), independent of k and -- per
 // mask word -- of W; the thresholds then read K[n + G + 1] and K[n - G - W] as in chain_fixed_fast_gos_kernel.  TWO: indexLagg and
 // indexLead differ, two selections.  No restriction on the cells' range (the bias makes them unsigned) or on W being a multiple of 8.
-template <int S, int NWD, bool TWO>
+template <int S, int NWD, bool TW3>
 __global__ void __launch_bounds__(FGeo<S>::THREADS, (NWD >= 3 ? 512 : 1024) / FGeo<S>::THREADS >= 1 ? (NWD >= 3 ? 512 : 1024) / FGeo<S>::THREADS : 1)
 chain_fixed_fast_gosb_kernel(const FastArgs a, const GosArgs ga) {
   using Gm = FGeo<S>;
@@ -1286,7 +1287,8 @@ chain_fixed_fast_gosb_kernel(const FastArgs a, const GosArgs ga) {
   const int c = threadIdx.x / TPC, tl = threadIdx.x % TPC;
   uint32_t *xb = smem + (size_t)c * CROW, *xm = xb + Gm::XB;
   const short *X = reinterpret_cast<const short *>(xm);
-  short *KL = reinterpret_cast<short *>(xm + Gm::XM), *KR = TWO ? KL + N : KL;
+  const bool two = ga.kl1 != ga.kr1;   // indexLagg and indexLead differ: two selections, two K arrays
+  short *KL = reinterpret_cast<short *>(xm + Gm::XM), *KR = two ? KL + N : KL;
   uint32_t *bp = xb + Go::MW;
   uint16_t *nz = reinterpret_cast<uint16_t *>(xb + Go::NZ);
   const int W = a.W, G = a.G;
@@ -1300,12 +1302,12 @@ chain_fixed_fast_gosb_kernel(const FastArgs a, const GosArgs ga) {
     const GenRow no_gen = {0u, 0u};
     if (tl == 0) { uni[c][0] = 0u; uni[c][1] = 0xFFFFu; }
     load_beats<S, 4>(a, grow, no_gen, tl, 0, pre);
-    fast_passes<S, 4>(a, c, tl, pre, grow, no_gen, xb, xm, loud);
+    fast_passes<S, 4, false, false, TW3>(a, c, tl, pre, grow, no_gen, xb, xm, loud);
     os_build_planes<S>(xm, tl, bp, uni[c], nz);
     chirp_sync<S>(c);
     const uint32_t act = uni[c][0] ^ uni[c][1];
 #pragma unroll 1
-    for (int h = 0; h < (TWO ? 4 : 2); ++h) {          // window starts 16 tl + 8 (h & 1) + j; h >= 2: the leading statistic
+    for (int h = 0; h < (two ? 4 : 2); ++h) {          // window starts 16 tl + 8 (h & 1) + j; h >= 2: the leading statistic
       const int s0 = PTS * tl + 8 * (h & 1);
       uint32_t cw[8][NWD];
       gos_select8<S, NWD>(bp, SPARSE ? os_local_planes(nz, act, s0, s0 + W + 6) : act, s0, mlast, (h < 2 ? ga.kl1 : ga.kr1) + 1, cw);
@@ -1331,14 +1333,16 @@ chain_fixed_fast_gosb_kernel(const FastArgs a, const GosArgs ga) {
       const int L = KL[min(n + G + 1, N - W)], R = KR[max(n - G - W, 0)];
       int t = ga.cmode == 0 ? ((R + L) >> 1) : (ga.cmode == 1 ? max(L, R) : min(L, R));
       t = both ? t : 0;                                                  // CFARCoreWithLis.scala:172-173
-      const int thr = ga.linear ? t * a.scaler : t + a.scaler;
+      // (the binary-point form of fast_cfar_bin at run time: without binary points the shifts are 0, t_mul 1, ncut_mul -1, sc_pre = scaler)
+      const int thr = ga.linear ? sar(t * a.scaler, a.thr_sh) : t * a.t_mul + a.sc_pre;
       const int cut = X[mhx<S>(n)];
-      const int pk = cut > thr ? 1 : 0;
-      if (a.out != nullptr) gout[n] = ((uint32_t)thr & a.thr_mask) * (uint32_t)a.out_mul + (uint32_t)(n << 1) + (uint32_t)pk;
+      const int pk = (cut * a.ncut_mul + thr) < 0 ? 1 : 0;
+      const int tf = sar(thr, a.out_sh);
+      if (a.out != nullptr) gout[n] = ((uint32_t)tf & a.thr_mask) * (uint32_t)a.out_mul + (uint32_t)(n << 1) + (uint32_t)pk;
       if (pk && a.det_list != nullptr && active) {
         const uint32_t slot = atomicAdd(a.det_count, 1u);
         if (slot < a.det_cap) {
-          Detection d; d.chirp = a.row_base + row; d.bin = (uint32_t)n; d.threshold = (int)((uint32_t)thr << a.thr_sext) >> a.thr_sext; d.cut = cut;
+          Detection d; d.chirp = a.row_base + row; d.bin = (uint32_t)n; d.threshold = (int)((uint32_t)tf << a.thr_sext) >> a.thr_sext; d.cut = cut;
           a.det_list[slot] = d;
         }
       }
@@ -1440,13 +1444,13 @@ static rsp_status launch_fast_gos(const LaunchCtx &c, const FastArgs &fa, const 
   return RSP_OK;
 }
 
-template <int S, int NWD, bool TWO>
+template <int S, int NWD, bool TW3>
 static rsp_status launch_fast_gosb_inst(const LaunchCtx &c, const FastArgs &fa, const GosArgs &ga, cudaStream_t st, const char **err) {
   using Gm = FGeo<S>;
   static int occ_dev[64] = {0};
   int &occ = occ_dev[c.device & 63];
   const size_t smem = (size_t)Gm::CPC * (Gm::ROW + OGeo<S>::KW) * sizeof(uint32_t);
-  auto kernel = chain_fixed_fast_gosb_kernel<S, NWD, TWO>;
+  auto kernel = chain_fixed_fast_gosb_kernel<S, NWD, TW3>;
   if (!occ) { const rsp_status s = launch_cfg(kernel, smem, Gm::THREADS, &occ, err); if (s != RSP_OK) return s; }
   const unsigned groups = (fa.n_rows + Gm::CPC - 1) / Gm::CPC;
   const unsigned grid = std::max(1u, std::min(groups, (unsigned)(c.sm_count * occ)));
@@ -1457,8 +1461,8 @@ static rsp_status launch_fast_gosb_inst(const LaunchCtx &c, const FastArgs &fa, 
 template <int S>
 static rsp_status launch_fast_gosb(const LaunchCtx &c, const FastArgs &fa, const GosArgs &ga, cudaStream_t st, const char **err) {
   const int nwd = (fa.W + 31) / 32;
-  const bool two = ga.kl1 != ga.kr1;
-  switch (nwd * 2 + (two ? 1 : 0)) {
+  const bool tw3 = fa.tw3 != nullptr;
+  switch (nwd * 2 + (tw3 ? 1 : 0)) {
     case 2: return launch_fast_gosb_inst<S, 1, false>(c, fa, ga, st, err);
     case 3: return launch_fast_gosb_inst<S, 1, true>(c, fa, ga, st, err);
     case 4: return launch_fast_gosb_inst<S, 2, false>(c, fa, ga, st, err);
@@ -1476,19 +1480,24 @@ static bool gos_use_bitplanes(int W) {
   return on || W < 8 || (W & 7);
 }
 
-template <int S>
-static rsp_status launch_fast_os(const LaunchCtx &c, const FastArgs &fa, const GosArgs &ga, cudaStream_t st, const char **err) {
+template <int S, bool TW3>
+static rsp_status launch_fast_os_inst(const LaunchCtx &c, const FastArgs &fa, const GosArgs &ga, cudaStream_t st, const char **err) {
   using Gm = FGeo<S>;
   static int occ_dev[64] = {0};
   int &occ = occ_dev[c.device & 63];
   const size_t smem = (size_t)Gm::CPC * Gm::ROW * sizeof(uint32_t);
-  auto kernel = chain_fixed_fast_os_kernel<S>;
+  auto kernel = chain_fixed_fast_os_kernel<S, TW3>;
   if (!occ) { const rsp_status s = launch_cfg(kernel, smem, Gm::THREADS, &occ, err); if (s != RSP_OK) return s; }
   const unsigned groups = (fa.n_rows + Gm::CPC - 1) / Gm::CPC;
   const unsigned grid = std::max(1u, std::min(groups, (unsigned)(c.sm_count * occ)));
   kernel<<<grid, Gm::THREADS, smem, st>>>(fa, ga);
   if (cudaGetLastError() != cudaSuccess) { *err = "chain_fixed_fast_os_kernel launch failed"; return RSP_ECUDA; }
   return RSP_OK;
+}
+
+template <int S>
+static rsp_status launch_fast_os(const LaunchCtx &c, const FastArgs &fa, const GosArgs &ga, cudaStream_t st, const char **err) {
+  return fa.tw3 != nullptr ? launch_fast_os_inst<S, true>(c, fa, ga, st, err) : launch_fast_os_inst<S, false>(c, fa, ga, st, err);
 }
 
 template <int S, int LP, bool TW3 = false>
@@ -1512,7 +1521,7 @@ static rsp_status launch_fast_fft_lp(const LaunchCtx &c, const FastArgs &fa, cud
 rsp_status RSP_CAT(launch_fast_size_, RSP_FAST_S)(int core, int cmode, bool linear, int ej, const LaunchCtx &ctx, const FastArgs &fa, const GosArgs &ga,
                                                   cudaStream_t st, const char **err) {
   constexpr int S = RSP_FAST_S;
-  if (core == CORE_LIS) return gos_use_bitplanes(fa.W) ? launch_fast_gosb<S>(ctx, fa, ga, st, err) : launch_fast_gos<S>(ctx, fa, ga, st, err);
+  if (core == CORE_LIS) return (gos_use_bitplanes(fa.W) || fa.tw3 != nullptr || fa.bpc) ? launch_fast_gosb<S>(ctx, fa, ga, st, err) : launch_fast_gos<S>(ctx, fa, ga, st, err);
   if (core == CORE_OS) return launch_fast_os<S>(ctx, fa, ga, st, err);
 #if RSP_FAST_S == 10
   if (ej == 2) return launch_fast_modes<S, 2>(cmode, linear, fa.pg_full >= 0, ctx, fa, st, err);
@@ -1596,9 +1605,14 @@ rsp_status launch_fast_fft(const Plan &pl, const LaunchCtx &ctx, const FxArgs &a
   }
 }
 
+static bool fast_cfar_bp(const FxArgs &a, FastArgs *fa);
+static bool fast_bps_ok(const FxArgs &a) {   // binary points in the CFAR operands: the bit-plane kernels take them at run time
+  if (a.in_bp == 0 && a.sc_bp == 0 && a.thr_bp == 0) return true;
+  return a.cfar_trim == TRIM_FLOOR && fast_cfar_bp(a, nullptr);
+}
 static bool fast_gos_supported(const FxArgs &a) {
   if (a.core != CORE_LIS || a.cfar_algorithm != 1) return false;
-  if (a.in_w != 16 || a.in_bp != 0 || a.sc_bp != 0 || a.thr_bp != 0 || a.send_cut || a.peak_grouping) return false;
+  if (a.in_w != 16 || !fast_bps_ok(a) || a.send_cut || a.peak_grouping) return false;
   if (a.thr_w < 1 || a.thr_w > 32 || a.G < 0 || a.W < 1 || a.W > 128) return false;   // (W not a multiple of 8: bit planes only)
   if (a.idx_lagg < 1 || a.idx_lagg > a.W || a.idx_lead < 1 || a.idx_lead > a.W) return false;
   return a.out != nullptr && a.binw + 1 <= 31;
@@ -1609,7 +1623,7 @@ static bool fast_os_supported(const FxArgs &a) {
   static int on = -1;
   if (on < 0) { const char *e = std::getenv("RSP_FAST_OS"); on = (e != nullptr && e[0] == '0') ? 0 : 1; }   // A/B knob
   if (!on || a.core != CORE_OS) return false;
-  if (a.in_w != 16 || a.in_bp != 0 || a.sc_bp != 0 || a.thr_bp != 0 || a.send_cut || a.peak_grouping) return false;
+  if (a.in_w != 16 || !fast_bps_ok(a) || a.send_cut || a.peak_grouping) return false;
   if (a.thr_w < 1 || a.thr_w > 32 || a.G < 0 || a.W < 1 || a.W > 32 || a.G + a.W > 64) return false;
   if (a.out == nullptr && a.det_list == nullptr) return false;
   return (reinterpret_cast<uintptr_t>(a.out) & 15u) == 0 && a.binw + 1 <= 31;
@@ -1621,8 +1635,8 @@ bool fast_chain_supported(const Plan &pl, const FxArgs &a) {
   if (pl.S < RSP_FAST_SMIN || pl.S > RSP_FAST_SMAX) return false;
   if ((a.bp != 0 && !tw3) || a.tw_bp != 14 || !a.bitrev || a.sel != 2 || a.mag_w != 16) return false;   // (the JPL magnitude does not look at the binary point)
   if (!tw3 && a.mag_bp != 0) return false;
-  if (a.core == CORE_LIS) return !tw3 && fast_gos_supported(a);
-  if (a.core == CORE_OS) return !tw3 && fast_os_supported(a);
+  if (a.core == CORE_LIS) return fast_gos_supported(a);
+  if (a.core == CORE_OS) return fast_os_supported(a);
   if (a.core != CORE_MEM || a.in_w != 16 || a.send_cut) return false;
   const bool bpc = tw3 || a.in_bp != 0 || a.sc_bp != 0 || a.thr_bp != 0;   // binary points in the CFAR: its own instantiation, without peak grouping
   if (bpc && (a.peak_grouping || a.cfar_trim != TRIM_FLOOR || !fast_cfar_bp(a, nullptr))) return false;
@@ -1655,7 +1669,7 @@ rsp_status launch_fast_chain(const Plan &pl, const LaunchCtx &ctx, const FxArgs 
   fa.pg_full = a.peak_grouping ? (a.G == a.guard_window_size ? 1 : 0) : -1;   // -1: no peak grouping
   fa.tw3 = nullptr; fa.bpc = 0; fa.thr_sh = 0; fa.ncut_mul = -1; fa.out_sh = 0; fa.t_mul = 1; fa.sc_pre = a.scaler;
   if (pl.mode == MODE_FAST3) fast_fill_tw3(a, fa);
-  if (a.core == CORE_MEM && (pl.mode == MODE_FAST3 || a.in_bp != 0 || a.sc_bp != 0 || a.thr_bp != 0)) { fast_cfar_bp(a, &fa); fa.bpc = 1; }
+  if (pl.mode == MODE_FAST3 || a.in_bp != 0 || a.sc_bp != 0 || a.thr_bp != 0) { fast_cfar_bp(a, &fa); fa.bpc = 1; }
   // measured on B200 (profiles/r02_d_l2prefetch.txt): N = 16384 +5.3 %, N = 4096 +1.9 %, N = 1024 +1.3 %; RSP_FAST_L2_PREFETCH=0 turns it off
   { static int l2p = -1; if (l2p < 0) { const char *e = std::getenv("RSP_FAST_L2_PREFETCH"); l2p = e ? std::atoi(e) : 1; }
     fa.l2_prefetch = (l2p != 0 && a.gen_full == nullptr && (reinterpret_cast<uintptr_t>(a.in) & 15u) == 0) ? 1 : 0; }

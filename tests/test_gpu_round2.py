@@ -809,3 +809,27 @@ def test_fast_kernel_cfar_binary_points(cuda, oracle, log_n, ib, tb, sb, mode, l
     thr, bins, peak = decode_cfar_words(want, n)
     assert k == int(peak.sum()) and k > 0
     assert {(int(d[0]), int(d[1])): int(d[2]) & 0xFFFF for d in dets} == {(r, b): int(thr[r, b]) for r, b in np.argwhere(peak == 1)}
+
+
+@pytest.mark.parametrize("ctype,log_n,bp,W,G,kl,kr,lin", [("gos", 10, 12, 64, 4, 48, 48, 1), ("gos", 12, 12, 32, 2, 20, 7, 0), ("gos", 14, 14, 100, 3, 77, 77, 1),
+                                                           ("os", 10, 12, 32, 4, 0, 0, 1), ("os", 12, 14, 24, 2, 0, 0, 0), ("os", 14, 12, 32, 8, 0, 0, 1),
+                                                           ("gos", 11, 0, 16, 2, 12, 12, 1)])
+def test_bit_plane_kernels_with_binary_points(cuda, oracle, ctype, log_n, bp, W, G, kl, kr, lin):
+    """the OS / GOS bit-plane kernels behind a binPoint >= 2 transform (and, last case, with CFAR binary points behind a binPoint-0 one:
+    input 0, threshold 3, scaler 6): bit-exact, specialised variant"""
+    n = 1 << log_n
+    rows = 6 if log_n <= 12 else 3
+    beats = np.concatenate([synth.chirps_fixed(rows - 2, n, seed=200 + log_n, noise=2.0 ** -4), synth.random_beats(2, n, seed=210 + log_n)])
+    p = fixed_params(n, 128 if W > 64 else 64, max(G, 1), bp=bp, ctype=GOSCFARType if ctype == "gos" else R.OSGoldenCFARType)
+    sb = bp
+    if bp == 0:
+        p.cfarParams.protoThreshold, sb = FixedPoint(16, 3), 6
+    p.cfarParams.protoScaler = FixedPoint(16, sb)
+    regs = dict(fftWin=n, thresholdScaler=int(2.5 * (1 << sb)) if lin else max(1, int(0.002 * (1 << sb))), logOrLinearMode=lin, peakGrouping=0, cfarMode=0, windowCells=W,
+                guardCells=G, indexLagg=kl, indexLead=kr)
+    fft, mag, cfar = oracle_cfgs(oracle, p, log_n, 2, regs)
+    want = oracle.chain_fixed_words(fft, mag, cfar, beats)
+    got, variant = run_fixed(cuda, p, log_n, 2, regs, beats)
+    assert variant == (f"chain_fixed_fast_gos<{log_n}>" if ctype == "gos" else f"chain_fixed_fast_os<{log_n}>"), variant
+    assert (got == want).all(), f"{int((got != want).sum())} beats differ, first at {np.argwhere(got != want)[:3].tolist()}"
+    assert (want & 1).sum() > 0
