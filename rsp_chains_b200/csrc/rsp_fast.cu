@@ -98,10 +98,12 @@ template <int S, int LP = 4> struct FGeo {
 #endif
   static constexpr int CPC = TPC >= RSP_FAST_CTA ? 1 : RSP_FAST_CTA / TPC;     // chirps per CTA
   static constexpr int THREADS = TPC * CPC;
-  static constexpr int XB = (fidx<S>(N - 1) + 4) & ~3;        // words of the exchange buffer (also holds the N + 1 prefix sums)
+  static constexpr int XB0 = (fidx<S>(N - 1) + 4) & ~3;
+  static constexpr int XB = XB0 >= N + 4 ? XB0 : N + 4;       // words of the exchange buffer (also holds the N + 1 prefix sums)
   static constexpr int XM = (mhx<S>(N - 1) / 2 + 4) & ~3;     // words of the magnitude array (int16 per bin, padded)
   static constexpr int ROW = XB + XM;                        // words per chirp
-  static constexpr int NW = TPC / 32;                        // warps per chirp
+  static constexpr int NW = TPC >= 32 ? TPC / 32 : 1;        // warps per chirp (below 512 points several chirps share a warp)
+  static constexpr int LPW = TPC >= 32 ? 32 : TPC;           // lanes of one chirp inside a warp
   // Design study, off by default (-DRSP_FAST_TWSMEM_S=14 turns it on): at N = 16384 the twiddle tables of the first pass (stageN = N
   // and N / 4: 96 + 24 KB) do not stay in L1 next to a 105 KB row, every row re-reads them from L2.  Keeping them in the shared
   // memory of the SM's one CTA was measured 8 % SLOWER than reading them through L1/L2 with the cp.async staging on (151.0 vs
@@ -473,7 +475,7 @@ __device__ __forceinline__ void fast_passes(const FastArgs &a, int c, int tl, ui
   constexpr int G0 = (1 << LP) / 16;
   if constexpr (G0 == 1) {
     const bool warp_quiet = __all_sync(0xffffffffu, quiet_beats(pre));
-    if (!warp_quiet && (tl & 31) == 0) loud[c] = 1;
+    if (!warp_quiet && (tl & (FGeo<S, LP>::LPW - 1)) == 0) loud[c] = 1;   // (a warp that holds several chirps flags them all)
     if (warp_quiet) fast_pass<S, LP, 0, false, TWSM, false, TW3>(a, tl, pre, xb, xm, tws); else fast_pass<S, LP, 0, true, TWSM, false, TW3>(a, tl, pre, xb, xm, tws);
   } else {
     int mags[1 << LP];   // not used by a first pass
@@ -485,7 +487,7 @@ __device__ __forceinline__ void fast_passes(const FastArgs &a, int c, int tl, ui
       all_quiet = all_quiet && warp_quiet;
       if (warp_quiet) fast_group<S, LP, 0, false, TWSM, false, TW3>(a, tl, g, pre, xb, mags, tws); else fast_group<S, LP, 0, true, TWSM, false, TW3>(a, tl, g, pre, xb, mags, tws);
     }
-    if (!all_quiet && (tl & 31) == 0) loud[c] = 1;
+    if (!all_quiet && (tl & (FGeo<S, LP>::LPW - 1)) == 0) loud[c] = 1;
   }
   chirp_sync<S>(c);
   if constexpr (fx_n_passes(S) > 1) {
@@ -502,12 +504,12 @@ __device__ __forceinline__ void fast_passes(const FastArgs &a, int c, int tl, ui
 // exclusive prefix of `total` over the TPC threads of one chirp: warp shuffles, then one shared-memory hop across the warps
 template <int S, int LP>
 __device__ __forceinline__ int chirp_scan_exclusive(int total, int c, int tl, int *wsum) {
-  constexpr int NW = FGeo<S, LP>::NW;
-  const int lane = tl & 31;
+  constexpr int NW = FGeo<S, LP>::NW, LPW = FGeo<S, LP>::LPW;
+  const int lane = tl & (LPW - 1);
   int incl = total;
 #pragma unroll
-  for (int d = 1; d < 32; d <<= 1) {
-    const int v = __shfl_up_sync(0xffffffffu, incl, d);
+  for (int d = 1; d < LPW; d <<= 1) {
+    const int v = __shfl_up_sync(0xffffffffu, incl, d, LPW);   // segments of LPW lanes: the chirps that share a warp do not mix
     if (lane >= d) incl += v;
   }
   int offset = 0;
@@ -1521,12 +1523,22 @@ static rsp_status launch_fast_fft_lp(const LaunchCtx &c, const FastArgs &fa, cud
 rsp_status RSP_CAT(launch_fast_size_, RSP_FAST_S)(int core, int cmode, bool linear, int ej, const LaunchCtx &ctx, const FastArgs &fa, const GosArgs &ga,
                                                   cudaStream_t st, const char **err) {
   constexpr int S = RSP_FAST_S;
+#if RSP_FAST_S < 10
+  // 64 ... 512 points (the run-time sizes of a 1024-point generator): the CA family only, every bin on the edge path (a thread's 16 bins are
+  // N / 16 apart: the window borders of most of them would need it anyway)
+  if (core != CORE_MEM) { *err = "no OS / GOS variant below 1024 points"; return RSP_EUNSUPPORTED; }
+  (void)ga; (void)ej;
+  return launch_fast_modes<S, 8>(cmode, linear, fa.pg_full >= 0, ctx, fa, st, err);
+#else
   if (core == CORE_LIS) return (gos_use_bitplanes(fa.W) || fa.tw3 != nullptr || fa.bpc) ? launch_fast_gosb<S>(ctx, fa, ga, st, err) : launch_fast_gos<S>(ctx, fa, ga, st, err);
   if (core == CORE_OS) return launch_fast_os<S>(ctx, fa, ga, st, err);
+#endif
 #if RSP_FAST_S == 10
   if (ej == 2) return launch_fast_modes<S, 2>(cmode, linear, fa.pg_full >= 0, ctx, fa, st, err);
 #endif
+#if RSP_FAST_S >= 10
   return launch_fast_modes<S, 1>(cmode, linear, fa.pg_full >= 0, ctx, fa, st, err);
+#endif
 }
 
 rsp_status RSP_CAT(launch_fast_fft_size_, RSP_FAST_S)(const LaunchCtx &ctx, const FastArgs &fa, cudaStream_t st, const char **err) {
@@ -1542,7 +1554,7 @@ rsp_status RSP_CAT(launch_fast_fft_size_, RSP_FAST_S)(const LaunchCtx &ctx, cons
 #if RSP_FAST_S == 10
 #define RSP_DECL_FAST(s) rsp_status launch_fast_size_##s(int, int, bool, int, const LaunchCtx &, const FastArgs &, const GosArgs &, cudaStream_t, const char **); \
                          rsp_status launch_fast_fft_size_##s(const LaunchCtx &, const FastArgs &, cudaStream_t, const char **)
-RSP_DECL_FAST(11); RSP_DECL_FAST(12); RSP_DECL_FAST(13); RSP_DECL_FAST(14);
+RSP_DECL_FAST(6); RSP_DECL_FAST(7); RSP_DECL_FAST(8); RSP_DECL_FAST(9); RSP_DECL_FAST(11); RSP_DECL_FAST(12); RSP_DECL_FAST(13); RSP_DECL_FAST(14);
 #undef RSP_DECL_FAST
 
 // the FFT block alone on the fast passes: the configuration of the fast chain's transform (16-bit data and twiddles, binPoint 0, RoundHalfUp,
@@ -1596,6 +1608,10 @@ rsp_status launch_fast_fft(const Plan &pl, const LaunchCtx &ctx, const FxArgs &a
   { static int l2p = -1; if (l2p < 0) { const char *e = std::getenv("RSP_FAST_L2_PREFETCH"); l2p = e ? std::atoi(e) : 1; }
     fa.l2_prefetch = (l2p != 0 && (reinterpret_cast<uintptr_t>(a.in) & 15u) == 0) ? 1 : 0; }
   switch (pl.S) {
+  case 6: return launch_fast_fft_size_6(ctx, fa, st, err);
+  case 7: return launch_fast_fft_size_7(ctx, fa, st, err);
+  case 8: return launch_fast_fft_size_8(ctx, fa, st, err);
+  case 9: return launch_fast_fft_size_9(ctx, fa, st, err);
   case 10: return launch_fast_fft_size_10(ctx, fa, st, err);
   case 11: return launch_fast_fft_size_11(ctx, fa, st, err);
   case 12: return launch_fast_fft_size_12(ctx, fa, st, err);
@@ -1635,15 +1651,15 @@ bool fast_chain_supported(const Plan &pl, const FxArgs &a) {
   if (pl.S < RSP_FAST_SMIN || pl.S > RSP_FAST_SMAX) return false;
   if ((a.bp != 0 && !tw3) || a.tw_bp != 14 || !a.bitrev || a.sel != 2 || a.mag_w != 16) return false;   // (the JPL magnitude does not look at the binary point)
   if (!tw3 && a.mag_bp != 0) return false;
-  if (a.core == CORE_LIS) return fast_gos_supported(a);
-  if (a.core == CORE_OS) return fast_os_supported(a);
+  if (a.core == CORE_LIS) return pl.S >= 10 && fast_gos_supported(a);
+  if (a.core == CORE_OS) return pl.S >= 10 && fast_os_supported(a);
   if (a.core != CORE_MEM || a.in_w != 16 || a.send_cut) return false;
   const bool bpc = tw3 || a.in_bp != 0 || a.sc_bp != 0 || a.thr_bp != 0;   // binary points in the CFAR: its own instantiation, without peak grouping
   if (bpc && (a.peak_grouping || a.cfar_trim != TRIM_FLOOR || !fast_cfar_bp(a, nullptr))) return false;
   if (a.out == nullptr && a.det_list == nullptr) return false;
   if (a.thr_w < 1 || a.thr_w > 32 || a.G < 1 || a.W < 1 || a.div_sum < 0 || a.div_sum > 30) return false;
   const int ej = fast_edge_iters(pl.S, a.W, a.G);
-  if (ej > (pl.S == 10 ? 2 : 1)) return false;
+  if (pl.S >= 10 && ej > (pl.S == 10 ? 2 : 1)) return false;   // (below 1024 points every bin takes the edge path)
   // the scaled threshold must fit 32 bits (the window sums wrap at sumw bits like the reference's registers, see FastArgs::wmul)
   if (a.sumw < 2 || a.sumw > 31) return false;
   const long long smax = std::min<long long>((long long)a.W * 32768, 1LL << (a.sumw - 1));
@@ -1682,6 +1698,10 @@ rsp_status launch_fast_chain(const Plan &pl, const LaunchCtx &ctx, const FxArgs 
   const GosArgs ga = {cmode, linear ? 1 : 0, a.idx_lagg - 1, a.idx_lead - 1};
   const int ej = a.core != CORE_MEM ? 1 : fast_edge_iters(pl.S, a.W, a.G);
   switch (pl.S) {
+  case 6: return launch_fast_size_6(a.core, cmode, linear, ej, ctx, fa, ga, st, err);
+  case 7: return launch_fast_size_7(a.core, cmode, linear, ej, ctx, fa, ga, st, err);
+  case 8: return launch_fast_size_8(a.core, cmode, linear, ej, ctx, fa, ga, st, err);
+  case 9: return launch_fast_size_9(a.core, cmode, linear, ej, ctx, fa, ga, st, err);
   case 10: return launch_fast_size_10(a.core, cmode, linear, ej, ctx, fa, ga, st, err);
   case 11: return launch_fast_size_11(a.core, cmode, linear, ej, ctx, fa, ga, st, err);
   case 12: return launch_fast_size_12(a.core, cmode, linear, ej, ctx, fa, ga, st, err);

@@ -6,8 +6,9 @@
 #include "rsp_host.hpp"
 #include "rsp_launch.hpp"
 
+// fixed-point CA chain and FFT block: 64 ... 16384 points (the OS / GOS kernels and the fp32 flavour from 1024 on)
 #ifndef RSP_FAST_SMIN
-#define RSP_FAST_SMIN 10
+#define RSP_FAST_SMIN 6
 #endif
 #ifndef RSP_FAST_SMAX
 #define RSP_FAST_SMAX 14

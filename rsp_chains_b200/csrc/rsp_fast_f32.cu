@@ -451,7 +451,7 @@ static int f32_edge_iters(int S, int W, int G) { const int tpc = (1 << S) / (S >
 
 bool fast_f32_chain_supported(const Plan &pl, const F32Args &a) {
   if (pl.first_stage != STAGE_FFT || pl.last_stage != STAGE_CFAR) return false;
-  if (pl.S < RSP_FAST_SMIN || pl.S > RSP_FAST_SMAX) return false;
+  if (pl.S < 10 || pl.S > RSP_FAST_SMAX) return false;
   if (!a.bitrev || a.load_rev || a.fft_dir != 1 || a.sel != 2) return false;
   if (a.core != CORE_MEM || a.send_cut) return false;
   if (a.G < 1 || a.W < 1 || a.div_sum < 0 || a.div_sum > 30) return false;

@@ -63,6 +63,9 @@ elif key == "c4osb":
     from rsp_chains_b200.params import OSGoldenCFARType
     os_b = dict(fftWin=4096, thresholdScaler=2, logOrLinearMode=1, peakGrouping=0, cfarMode=0, windowCells=32, guardCells=4)
     B.run_case("C4 x 16 OS golden (reading B)", B.fixed_params(4096, 64, 4, OSGoldenCFARType), 12, os_b, 16384, 1)
+elif key.startswith("small"):   # smallS: fixed CA chain at N = 2^S < 1024 (run-time-parameter kernel, MODE_FAST instantiation)
+    S = int(key[5:]); n = 1 << S
+    B.run_case(f"fixed CA N={n}", B.fixed_params(n, 16, 2), S, ca(n, 16, 2, 4), (1 << 26) // n, 1)
 elif key.startswith("fx"):      # fxS: fixed CA chain at N = 2^S, 512 MiB footprint
     S = int(key[2:]); n = 1 << S
     B.run_case(f"fixed CA N={n}", B.fixed_params(n, 64, 8), S, ca(n, 64, 8, 6), (1 << 26) // n, 1)

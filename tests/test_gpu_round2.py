@@ -833,3 +833,42 @@ def test_bit_plane_kernels_with_binary_points(cuda, oracle, ctype, log_n, bp, W,
     assert variant == (f"chain_fixed_fast_gos<{log_n}>" if ctype == "gos" else f"chain_fixed_fast_os<{log_n}>"), variant
     assert (got == want).all(), f"{int((got != want).sum())} beats differ, first at {np.argwhere(got != want)[:3].tolist()}"
     assert (want & 1).sum() > 0
+
+
+@pytest.mark.parametrize("log_n,numpoints,bp,W,G,mode,lin,pg", [(6, 64, 0, 8, 1, 0, 1, 0), (6, 1024, 0, 16, 2, 1, 0, 0), (7, 128, 12, 16, 4, 2, 1, 0), (8, 1024, 0, 32, 4, 0, 1, 1),
+                                                                 (8, 256, 14, 64, 8, 1, 1, 0), (9, 512, 0, 64, 4, 0, 0, 0), (9, 2048, 12, 32, 2, 2, 1, 0), (7, 512, 0, 32, 8, 0, 1, 1)])
+def test_fast_kernel_below_1024_points(cuda, oracle, log_n, numpoints, bp, W, G, mode, lin, pg):
+    """the specialised CA kernel at 64 ... 512 points (also as the run-time size of a larger generator): 4 ... 32 chirps per CTA, several chirps
+    per warp, every bin on the edge path; binPoint 0 / 12 / 14, peak grouping, quiet and full-scale rows, row counts that do not fill the last CTA,
+    the detection list, and the FFT block alone"""
+    n = 1 << log_n
+    rows = 75
+    beats = np.concatenate([synth.chirps_fixed(rows - 9, n, seed=220 + log_n, noise=2.0 ** -4), synth.random_beats(8, n, seed=230 + log_n),
+                            np.full((1, n), 0x80008000, dtype=np.uint32)])
+    p = fixed_params(numpoints, 64, max(G, 1), bp=bp)
+    p.cfarParams.protoScaler = FixedPoint(16, bp)
+    regs = dict(fftWin=n, thresholdScaler=int(3.0 * (1 << bp)) if lin else max(1, int(0.004 * (1 << bp))), logOrLinearMode=lin, divSum=int(np.log2(W)),
+                peakGrouping=pg, cfarMode=mode, windowCells=W, guardCells=G)
+    if n <= 2 * W + 2 * G + 1:
+        pytest.skip("fftWin must exceed both windows")
+    fft, mag, cfar = oracle_cfgs(oracle, p, log_n, 2, regs)
+    want, want_fft, _ = oracle.chain_fixed_words(fft, mag, cfar, beats, want_stages=True)
+    with R.FftMagCfarChainVanilla(p) as ch:
+        configure(ch, log_n, 2, regs)
+        assert ch.variant == f"chain_fixed_fast<{log_n}>", ch.variant
+        d_in = to_dev(cuda, beats)
+        for k_rows in (rows, 1, 33):
+            d_out = cuda.zeros_like(d_in)
+            d_fft = cuda.zeros_like(d_in)
+            det_list = cuda.zeros((rows * n, 4), dtype=cuda.int32, device="cuda")
+            det_count = cuda.zeros(1, dtype=cuda.int32, device="cuda")
+            ch.run(d_in, k_rows, 1, out=d_out, det_list=det_list, det_count=det_count)
+            ch.fft(d_in, k_rows, d_fft)
+            cuda.cuda.synchronize()
+            got, got_fft = from_dev_u32(d_out), from_dev_u32(d_fft)
+            assert (got_fft[:k_rows] == want_fft[:k_rows]).all() and not got_fft[k_rows:].any()
+            assert (got[:k_rows] == want[:k_rows]).all(), f"{k_rows} rows: first difference at {np.argwhere(got[:k_rows] != want[:k_rows])[:3].tolist()}"
+            assert not got[k_rows:].any()
+            k = int(det_count.item())
+            assert k == int((want[:k_rows] & 1).sum())
+            assert set(map(tuple, det_list[:k].cpu().numpy()[:, :2].tolist())) == set(map(tuple, np.argwhere((want[:k_rows] & 1) == 1).tolist()))
