@@ -1,3 +1,3 @@
 #!/bin/bash
 mkdir -p gpurun_out
-timeout 900 python -m pytest tests/test_gpu_round2.py -m gpu -x -q -k "below_1024" 2>&1 | tail -12 | tee gpurun_out/pytest_small2.txt
+timeout 300 python scripts/latency_probe.py 2>&1 | tail -1 | tee gpurun_out/latency_probe2.txt

@@ -27,6 +27,19 @@ with R.FftMagCfarChainVanilla(bench.fixed_params(n, 64, 4)) as ch:
         res["rsp_run_us_per_call_device"] = e0.elapsed_time(e1) * 1e3 / reps
         res["rsp_run_us_per_call_host_issue"] = t_issue * 1e6 / reps
         res["rsp_run_us_per_call_wall"] = t_all * 1e6 / reps
+with R.FftMagCfarChainVanilla(bench.fixed_params(n, 64, 4)) as ch:      # the same calls captured once in a CUDA graph of 100 launches and replayed
+    ch.configure(10, 2, regs)
+    ch.run(d_in, 1, 1, out=d_out); torch.cuda.synchronize()
+    g, st = torch.cuda.CUDAGraph(), torch.cuda.Stream()
+    with torch.cuda.graph(g, stream=st):
+        for _ in range(100): ch.run(d_in, 1, 1, out=d_out, stream=st)
+    for _ in range(5): g.replay()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(20): g.replay()
+    e1.record(); torch.cuda.synchronize()
+    res["graph_replay_us_per_call_device"] = e0.elapsed_time(e1) * 1e3 / 2000
 x = torch.zeros(1, device="cuda")
 for _ in range(200): x.add_(1)
 torch.cuda.synchronize()

@@ -872,3 +872,32 @@ def test_fast_kernel_below_1024_points(cuda, oracle, log_n, numpoints, bp, W, G,
             k = int(det_count.item())
             assert k == int((want[:k_rows] & 1).sum())
             assert set(map(tuple, det_list[:k].cpu().numpy()[:, :2].tolist())) == set(map(tuple, np.argwhere((want[:k_rows] & 1) == 1).tolist()))
+
+
+def test_rsp_run_is_capturable_in_a_cuda_graph(cuda, oracle):
+    """after one warm-up call (kernel attributes, occupancy query) rsp_run issues nothing but its kernel launch on the caller's stream, so a
+    launch-bound loop of small batches can be captured once and replayed: the replayed graph gives the oracle's beats for new input contents"""
+    n, log_n = 1024, 10
+    p = fixed_params(n, 64, 4)
+    regs = dict(fftWin=n, thresholdScaler=4, logOrLinearMode=1, divSum=5, peakGrouping=0, cfarMode=0, windowCells=32, guardCells=4)
+    a, b = synth.chirps_fixed(4, n, seed=301), synth.chirps_fixed(4, n, seed=302)
+    fft, mag, cfar = oracle_cfgs(oracle, p, log_n, 2, regs)
+    with R.FftMagCfarChainVanilla(p) as ch:
+        configure(ch, log_n, 2, regs)
+        d_in = to_dev(cuda, a)
+        d_out = cuda.zeros_like(d_in)
+        ch.run(d_in, 4, 1, out=d_out)                      # warm-up outside the capture
+        cuda.cuda.synchronize()
+        g = cuda.cuda.CUDAGraph()
+        s = cuda.cuda.Stream()
+        with cuda.cuda.graph(g, stream=s):
+            for _ in range(3):                             # three launches in the graph (the last one's result stays)
+                ch.run(d_in, 4, 1, out=d_out, stream=s)
+        d_out.zero_()
+        g.replay()
+        cuda.cuda.synchronize()
+        assert (from_dev_u32(d_out) == oracle.chain_fixed_words(fft, mag, cfar, a)).all()
+        d_in.copy_(to_dev(cuda, b))
+        g.replay()
+        cuda.cuda.synchronize()
+        assert (from_dev_u32(d_out) == oracle.chain_fixed_words(fft, mag, cfar, b)).all()
