@@ -842,7 +842,7 @@ def test_fast_kernel_below_1024_points(cuda, oracle, log_n, numpoints, bp, W, G,
     per warp, every bin on the edge path; binPoint 0 / 12 / 14, peak grouping, quiet and full-scale rows, row counts that do not fill the last CTA,
     the detection list, and the FFT block alone"""
     n = 1 << log_n
-    rows = 75
+    rows = 75 if log_n < 12 else 11
     beats = np.concatenate([synth.chirps_fixed(rows - 9, n, seed=220 + log_n, noise=2.0 ** -4), synth.random_beats(8, n, seed=230 + log_n),
                             np.full((1, n), 0x80008000, dtype=np.uint32)])
     p = fixed_params(numpoints, 64, max(G, 1), bp=bp)
@@ -857,7 +857,7 @@ def test_fast_kernel_below_1024_points(cuda, oracle, log_n, numpoints, bp, W, G,
         configure(ch, log_n, 2, regs)
         assert ch.variant == f"chain_fixed_fast<{log_n}>", ch.variant
         d_in = to_dev(cuda, beats)
-        for k_rows in (rows, 1, 33):
+        for k_rows in (rows, 1, min(33, rows - 1)):
             d_out = cuda.zeros_like(d_in)
             d_fft = cuda.zeros_like(d_in)
             det_list = cuda.zeros((rows * n, 4), dtype=cuda.int32, device="cuda")
