@@ -355,7 +355,7 @@ def generator_lines(torch, peak, rows=65536):
     res = []
     chain_bps = 4.0 if launches_per_call == 1 else 12.0
     for name, ms, bps, var in ((f"C1 chain fed by the PLFG -> NCO generator (RspChainVanilla), {launches_per_call} launch(es) per call", ms_chain, chain_bps, "generator + " + variant),
-                               ("PLFG -> NCO generator alone", ms_gen, 4.0, "generator_kernel")):
+                               ("PLFG -> NCO generator alone", ms_gen, 4.0, "generator_table_kernel")):
         gbs = samples * bps / (ms * 1e-3) / 1e9
         res.append({"config": name, "variant": var, "rows": rows, "n": n, "ms": round(ms, 4), "Msamples_per_s": round(samples / ms / 1e3, 1),
                     "GBps_algorithmic": round(gbs, 1), "frac": round(gbs / peak, 4), "bytes_per_sample": bps,

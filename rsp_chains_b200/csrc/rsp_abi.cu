@@ -168,6 +168,36 @@ __global__ void __launch_bounds__(256) generator_kernel(const GenArgs g, unsigne
   }
 }
 
+// The NCO beats alone from the period's phase table (GenPlan::phase_tab, the table the fused chain kernel reads): sample k of the stream has
+// the phase (phase[k mod period] + (k div period) * pp) mod 2^phaseWidth and its beat is full[phase] -- two loads and a handful of integer
+// instructions per sample instead of the closed form's segment search and recurrences.  Taken when the caller does not ask for the PLFG
+// words and the tables exist (phaseWidth <= 12, period up to 2^20 samples).
+__global__ void __launch_bounds__(256) generator_table_kernel(const GenArgs g, const uint16_t *__restrict__ phase, uint32_t period, uint32_t pp, uint32_t mask,
+                                                              unsigned long long n_samples, uint32_t *__restrict__ nco_out) {
+  constexpr int V = RSP_GEN_RUN;
+  const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x * V;
+  const bool vec = (reinterpret_cast<uintptr_t>(nco_out) & 15u) == 0;
+  for (unsigned long long k0 = ((unsigned long long)blockIdx.x * blockDim.x + threadIdx.x) * V; k0 < n_samples; k0 += stride) {
+    unsigned long long per64 = k0 / period;
+    uint32_t q = (uint32_t)(k0 - per64 * period), per = (uint32_t)per64;   // (per * pp is taken mod 2^32, which contains 2^phaseWidth)
+    uint32_t beat[V];
+#pragma unroll
+    for (int j = 0; j < V; ++j) {
+      const uint32_t ph = ((uint32_t)__ldg(&phase[q]) + per * pp) & mask;
+      const uint32_t b = __ldg(&g.nco_full[ph]);
+      beat[j] = g.mult_on ? nco_multiply(g, b) : b;
+      if (++q == period) { q = 0; ++per; }
+    }
+    if (vec && k0 + V <= n_samples) {
+#pragma unroll
+      for (int j = 0; j < V; j += 4) *reinterpret_cast<uint4 *>(nco_out + k0 + j) = make_uint4(beat[j], beat[j + 1], beat[j + 2], beat[j + 3]);
+    } else {
+#pragma unroll
+      for (int j = 0; j < V; ++j) if (k0 + j < n_samples) nco_out[k0 + j] = beat[j];
+    }
+  }
+}
+
 }  // namespace rsp
 
 // ---------------------------------------------------------------------------------------------------------------------
@@ -634,7 +664,14 @@ extern "C" rsp_status rsp_generate(rsp_chain *c, uint64_t n_samples, uint32_t *d
   GenArgs g;
   const rsp_status s = prepare_generator(c, n_samples, g, st);
   if (s != RSP_OK) return s;
-  generator_kernel<<<ew_grid(c, (n_samples + RSP_GEN_RUN - 1) / RSP_GEN_RUN), 256, 0, st>>>(g, n_samples, d_nco_out, d_plfg_out);
+  static const int table_on = env_int("RSP_GEN_TABLE", 1, 0, 1);   // A/B knob
+  if (table_on && d_plfg_out == nullptr && c->d_nco_full != nullptr && !c->gen_plan.phase_tab.empty() && c->gen_plan.period_len <= 0xFFFFFFFFull) {
+    const uint32_t pw = (uint32_t)c->p.nco.phaseWidth;
+    generator_table_kernel<<<ew_grid(c, (n_samples + RSP_GEN_RUN - 1) / RSP_GEN_RUN), 256, 0, st>>>(g, c->d_gen_phase, (uint32_t)c->gen_plan.period_len,
+                                                                                                   c->gen_plan.period_phase, (1u << pw) - 1u, n_samples, d_nco_out);
+  } else {
+    generator_kernel<<<ew_grid(c, (n_samples + RSP_GEN_RUN - 1) / RSP_GEN_RUN), 256, 0, st>>>(g, n_samples, d_nco_out, d_plfg_out);
+  }
   CUDA_TRY(cudaGetLastError());
   ++c->launches;
   return RSP_OK;

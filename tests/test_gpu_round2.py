@@ -901,3 +901,30 @@ def test_rsp_run_is_capturable_in_a_cuda_graph(cuda, oracle):
         g.replay()
         cuda.cuda.synchronize()
         assert (from_dev_u32(d_out) == oracle.chain_fixed_words(fft, mag, cfar, b)).all()
+
+
+@pytest.mark.parametrize("nco_kw,frame_num,inter", [(dict(), 0, 5), (dict(phaseAccEnable=False), 3, 9), (dict(useMultiplier=True, roundingMode="Convergent"), 0, 1),
+                                                     (dict(rasterizedMode=True, tableSize=100), 2, 7), (dict(phaseWidth=12, tableSize=256), 0, 12)])
+def test_generator_table_kernel_equals_the_closed_form(cuda, oracle, nco_kw, frame_num, inter):
+    """rsp_generate without the PLFG words runs generator_table_kernel (the period's phase table + the beat table); with them the closed-form
+    generator_kernel: same beats, for lengths that are not multiples of the run length, buffers that start at an odd word, several periods"""
+    p = R.rsp_chain_vanilla_app_params()
+    for k, v in nco_kw.items():
+        setattr(p.ncoParams, k, v)
+    order, repeats, start = [2, 0, 1, 3, 0], [2, 1, 3, 1, 2], 37
+    frame_len = 2 * 2 + 320 + 3 * 475 + 213 + 2 * 320
+    total = frame_num * frame_len + (frame_num - 1) * max(inter - 1, 0) if frame_num else 5 * frame_len + 77
+    with R.RspChainVanilla(p) as ch:
+        configure(ch, 10, 2, dict(fftWin=1024, thresholdScaler=4, logOrLinearMode=1, divSum=5, peakGrouping=0, cfarMode=0, windowCells=32, guardCells=4))
+        write_plfg(ch, p, oracle, start, CHIRPS, order, repeats, frame_num, inter)
+        if nco_kw.get("useMultiplier"):
+            ch.reg_write(R._abi.BLK_NCO, 0, 1); ch.reg_write(R._abi.BLK_NCO, 1, 0x3000)
+        both = cuda.zeros(total, dtype=cuda.int32, device="cuda")
+        plfg = cuda.zeros(total, dtype=cuda.int32, device="cuda")
+        ch.generate(total, both, plfg)
+        for n_s, off in ((total, 0), (total - 3, 1), (5, 3), (1, 0)):
+            flat = cuda.zeros(total + 4, dtype=cuda.int32, device="cuda")
+            ch.generate(n_s, flat[off:off + total], None)
+            cuda.cuda.synchronize()
+            assert bool((flat[off:off + n_s] == both[:n_s]).all().item()), (n_s, off)
+            assert not bool(flat[off + n_s:].any().item()) and not bool(flat[:off].any().item())
