@@ -283,8 +283,30 @@ def config_lines(torch, peak):
     case("C4 OS-CFAR 1024 x 4096 fixed, reading (B): golden cfarOS, 32 + 32 cells in one sorted window, ascending index 48", fixed_params(4096, 64, 4, R.OSGoldenCFARType), 12, os_b, 1024, 1, 16,
          note="CFARUtils.scala:159-196 (no hardware core in the reference); radix selection on bit planes (chain_fixed_fast_os)")
     out.extend(generator_lines(torch, peak))
+    out.extend(cfar_only_lines(torch, peak))
     out.extend(doppler_lines(torch, peak))
     return out
+
+
+def cfar_only_lines(torch, peak, n=4096, rows=16384):
+    """BASELINE configs[3] as SURVEY 8d also states it: the CFAR block alone (rsp_cfar_run) on stored 16-bit magnitude profiles (exponential clutter, mean 256,
+    + 4 targets), both readings of "ref window 64, k = 48"; 4 B in (a beat per cell, CFARDspBlock.scala:49) + 4 B out per cell"""
+    import rsp_chains_b200 as R
+    rng = np.random.default_rng(1)
+    prof = np.floor(rng.exponential(256.0, (64, n))).astype(np.int32)
+    prof[:, [300, 1200, 2500, 3900]] += 4096
+    d_in = torch.from_numpy(prof).cuda().repeat(rows // 64, 1).contiguous()
+    d_out = torch.empty_like(d_in)
+    lines = []
+    for name, ctype, W in (("reading (A): GOS core, 64 cells per side, k=48", R.GOSCFARType, 64), ("reading (B): golden cfarOS, 32 + 32 cells, ascending index 48", R.OSGoldenCFARType, 32)):
+        regs = dict(fftWin=n, thresholdScaler=2, logOrLinearMode=1, peakGrouping=0, cfarMode=0, windowCells=W, guardCells=4, indexLagg=48, indexLead=48)
+        with R.FftMagCfarChainVanilla(fixed_params(n, 64, 4, ctype)) as ch:
+            ch.configure(12, 2, regs)
+            ms = _timed(torch, lambda: ch.cfar(d_in, rows, out=d_out))
+        g = rows * n * 8.0 / (ms * 1e-3) / 1e9
+        lines.append({"config": f"C4 CFAR block alone on stored magnitude profiles, 16 x 1024 x {n}, {name}", "variant": "bit-plane kernel, cfar_only", "rows": rows, "n": n,
+                      "ms": round(ms, 4), "Msamples_per_s": round(rows * n / ms / 1e3, 1), "GBps_algorithmic": round(g, 1), "frac": round(g / peak, 4), "bytes_per_sample": 8.0})
+    return lines
 
 
 def doppler_lines(torch, peak, n_rx=8, m=1024, n=4096):

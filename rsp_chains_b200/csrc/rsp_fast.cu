@@ -61,6 +61,7 @@ struct FastArgs {
   // BPC kernels (the CFAR operands carry binary points, cfar_bin): linear thr = (t * scaler) >> thr_sh, log thr = t * t_mul + sc_pre, both at binary
   // point tbp; peak = thr - cut * 2^(tbp - inBP) < 0 (ncut_mul = -2^(tbp - inBP)); threshold field = thr >> out_sh (tbp -> thresholdBP)
   int thr_sh, ncut_mul, out_sh, t_mul, sc_pre, bpc;
+  int cfar_only;  // OS / GOS bit-plane kernels: the rows are magnitude profiles (AXI4CFARBlock alone, rsp_cfar_run): no transform, the cells are the beats' low 16 bits
   int pg_full;   // peak grouping (PG kernels): 1 = guardCells equals the generator's guardWindowSize, the left neighbour is read (CFARCoreWithMem.scala:182-184)
 };
 
@@ -1227,8 +1228,15 @@ __global__ void __launch_bounds__(FGeo<S>::THREADS, 1024 / FGeo<S>::THREADS) cha
     uint32_t pre[PTS];
     const GenRow no_gen = {0u, 0u};
     if (tl == 0) { uni[c][0] = 0u; uni[c][1] = 0xFFFFu; }
-    load_beats<S, 4>(a, grow, no_gen, tl, 0, pre);
-    fast_passes<S, 4, false, false, TW3>(a, c, tl, pre, grow, no_gen, xb, xm, loud);   // ends with a barrier: magnitudes in X, the exchange buffer is free
+    if (a.cfar_only) {   // stored profiles: the cells straight into the magnitude array (bin n = tl + j TPC: warp-contiguous loads)
+      short *Xw = reinterpret_cast<short *>(xm);
+#pragma unroll
+      for (int j = 0; j < PTS; ++j) Xw[mhx<S>(tl + j * TPC)] = (short)__ldg(&grow[tl + j * TPC]);
+      chirp_sync<S>(c);
+    } else {
+      load_beats<S, 4>(a, grow, no_gen, tl, 0, pre);
+      fast_passes<S, 4, false, false, TW3>(a, c, tl, pre, grow, no_gen, xb, xm, loud);   // ends with a barrier: magnitudes in X, the exchange buffer is free
+    }
     os_build_planes<S>(xm, tl, bp, uni[c], nz);
     chirp_sync<S>(c);
     const uint32_t act = uni[c][0] ^ uni[c][1];       // planes in which the chirp's cells differ
@@ -1303,8 +1311,15 @@ chain_fixed_fast_gosb_kernel(const FastArgs a, const GosArgs ga) {
     uint32_t pre[PTS];
     const GenRow no_gen = {0u, 0u};
     if (tl == 0) { uni[c][0] = 0u; uni[c][1] = 0xFFFFu; }
-    load_beats<S, 4>(a, grow, no_gen, tl, 0, pre);
-    fast_passes<S, 4, false, false, TW3>(a, c, tl, pre, grow, no_gen, xb, xm, loud);
+    if (a.cfar_only) {   // stored profiles (rsp_cfar_run): see chain_fixed_fast_os_kernel
+      short *Xw = reinterpret_cast<short *>(xm);
+#pragma unroll
+      for (int j = 0; j < PTS; ++j) Xw[mhx<S>(tl + j * TPC)] = (short)__ldg(&grow[tl + j * TPC]);
+      chirp_sync<S>(c);
+    } else {
+      load_beats<S, 4>(a, grow, no_gen, tl, 0, pre);
+      fast_passes<S, 4, false, false, TW3>(a, c, tl, pre, grow, no_gen, xb, xm, loud);
+    }
     os_build_planes<S>(xm, tl, bp, uni[c], nz);
     chirp_sync<S>(c);
     const uint32_t act = uni[c][0] ^ uni[c][1];
@@ -1530,7 +1545,7 @@ rsp_status RSP_CAT(launch_fast_size_, RSP_FAST_S)(int core, int cmode, bool line
   (void)ga; (void)ej;
   return launch_fast_modes<S, 8>(cmode, linear, fa.pg_full >= 0, ctx, fa, st, err);
 #else
-  if (core == CORE_LIS) return (gos_use_bitplanes(fa.W) || fa.tw3 != nullptr || fa.bpc) ? launch_fast_gosb<S>(ctx, fa, ga, st, err) : launch_fast_gos<S>(ctx, fa, ga, st, err);
+  if (core == CORE_LIS) return (gos_use_bitplanes(fa.W) || fa.tw3 != nullptr || fa.bpc || fa.cfar_only) ? launch_fast_gosb<S>(ctx, fa, ga, st, err) : launch_fast_gos<S>(ctx, fa, ga, st, err);
   if (core == CORE_OS) return launch_fast_os<S>(ctx, fa, ga, st, err);
 #endif
 #if RSP_FAST_S == 10
@@ -1646,6 +1661,9 @@ static bool fast_os_supported(const FxArgs &a) {
 }
 
 bool fast_chain_supported(const Plan &pl, const FxArgs &a) {
+  // the CFAR block alone (rsp_cfar_run) with an ordered statistic: the bit-plane kernels on stored magnitude profiles
+  if (pl.first_stage == STAGE_CFAR && pl.last_stage == STAGE_CFAR && pl.S >= 10 && pl.S <= RSP_FAST_SMAX && a.in != nullptr)
+    return a.core == CORE_LIS ? fast_gos_supported(a) : (a.core == CORE_OS ? fast_os_supported(a) : false);
   const bool tw3 = fast_tw3_ok(pl, a);   // binPoint >= 2: the CA kernel's binary-point variant (FftMagCfarChainVanillaApp has 12)
   if ((pl.mode != MODE_FAST && !tw3) || pl.first_stage != STAGE_FFT || pl.last_stage != STAGE_CFAR) return false;
   if (pl.S < RSP_FAST_SMIN || pl.S > RSP_FAST_SMAX) return false;
@@ -1685,9 +1703,10 @@ rsp_status launch_fast_chain(const Plan &pl, const LaunchCtx &ctx, const FxArgs 
   fa.out_mul = (int)(1u << (a.binw + 1)); fa.thr_sext = 32 - a.thr_w;
   fa.det_list = a.det_list; fa.det_count = a.det_count; fa.det_cap = a.det_cap;
   fa.pg_full = a.peak_grouping ? (a.G == a.guard_window_size ? 1 : 0) : -1;   // -1: no peak grouping
+  fa.cfar_only = pl.first_stage == STAGE_CFAR ? 1 : 0;
   fa.tw3 = nullptr; fa.bpc = 0; fa.thr_sh = 0; fa.ncut_mul = -1; fa.out_sh = 0; fa.t_mul = 1; fa.sc_pre = a.scaler;
-  if (pl.mode == MODE_FAST3) fast_fill_tw3(a, fa);
-  if (pl.mode == MODE_FAST3 || a.in_bp != 0 || a.sc_bp != 0 || a.thr_bp != 0) { fast_cfar_bp(a, &fa); fa.bpc = 1; }
+  if (pl.mode == MODE_FAST3 && !fa.cfar_only) fast_fill_tw3(a, fa);
+  if ((pl.mode == MODE_FAST3 && !fa.cfar_only) || a.in_bp != 0 || a.sc_bp != 0 || a.thr_bp != 0) { fast_cfar_bp(a, &fa); fa.bpc = 1; }
   // measured on B200 (profiles/r02_d_l2prefetch.txt): N = 16384 +5.3 %, N = 4096 +1.9 %, N = 1024 +1.3 %; RSP_FAST_L2_PREFETCH=0 turns it off
   { static int l2p = -1; if (l2p < 0) { const char *e = std::getenv("RSP_FAST_L2_PREFETCH"); l2p = e ? std::atoi(e) : 1; }
     fa.l2_prefetch = (l2p != 0 && a.gen_full == nullptr && (reinterpret_cast<uintptr_t>(a.in) & 15u) == 0) ? 1 : 0; }

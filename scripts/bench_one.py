@@ -26,6 +26,27 @@ elif key in ("app12", "app12_14"):   # FftMagCfarChainVanillaApp / RxFftMagCfarT
         p.fftParams.numPoints = 16384; p.cfarParams.fftSize = 16384
         p.fftParams.keepMSBorLSB = [True] * 14; p.fftParams.expandLogic = [0] * 14
         B.run_case("the same parameters at 16384 points", p, 14, dict(fftWin=16384, thresholdScaler=int(3.5 * 4096), logOrLinearMode=1, divSum=6, peakGrouping=0, cfarMode=0, windowCells=64, guardCells=4), 4096, 1)
+elif key in ("c4cfar", "c4cfarb"):      # C4 "CFAR-only on stored 16-bit magnitude profiles": rsp_cfar_run, 1024 x 4096 x 16 frames
+    from rsp_chains_b200.params import OSGoldenCFARType
+    import rsp_chains_b200 as R, json, numpy as np
+    n, rows = 4096, 16384
+    b = key == "c4cfarb"
+    regs = dict(fftWin=n, thresholdScaler=2, logOrLinearMode=1, peakGrouping=0, cfarMode=0, windowCells=32 if b else 64, guardCells=4, indexLagg=48, indexLead=48)
+    rng = np.random.default_rng(1)
+    prof = np.floor(rng.exponential(256.0, (64, n))).astype(np.int32); prof[:, [300, 1200, 2500, 3900]] += 4096
+    d_in = torch.from_numpy(prof).cuda().repeat(rows // 64, 1).contiguous(); d_out = torch.empty_like(d_in)
+    with R.FftMagCfarChainVanilla(B.fixed_params(n, 64, 4, OSGoldenCFARType if b else GOSCFARType)) as ch:
+        ch.configure(12, 2, regs)
+        for _ in range(3): ch.cfar(d_in, rows, out=d_out)
+        torch.cuda.synchronize()
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(11)]
+        ev[0].record()
+        for i in range(10):
+            ch.cfar(d_in, rows, out=d_out); ev[i + 1].record()
+        torch.cuda.synchronize()
+        ms = float(np.median([ev[i].elapsed_time(ev[i + 1]) for i in range(10)]))
+        print(json.dumps({"config": key + " (CFAR block alone on stored profiles)", "rows": rows, "n": n, "ms": round(ms, 4), "Msamples_per_s": round(rows * n / ms / 1e3, 1),
+                          "GBps_algorithmic": round(rows * n * 8 / ms / 1e6, 1)}))
 elif key == "c5pg":
     r = ca(16384, 64, 8, 6); r["peakGrouping"] = 1
     B.run_case("C5 fixed one frame, peakGrouping = 1", B.fixed_params(16384, 64, 8), 14, r, 32768, 8)

@@ -928,3 +928,32 @@ def test_generator_table_kernel_equals_the_closed_form(cuda, oracle, nco_kw, fra
             cuda.cuda.synchronize()
             assert bool((flat[off:off + n_s] == both[:n_s]).all().item()), (n_s, off)
             assert not bool(flat[off + n_s:].any().item()) and not bool(flat[:off].any().item())
+
+
+@pytest.mark.parametrize("ctype,log_n,W,G,kl,kr,lin", [("gos", 12, 64, 4, 48, 48, 1), ("gos", 10, 16, 2, 12, 5, 0), ("gos", 14, 100, 3, 77, 77, 1), ("os", 12, 32, 4, 0, 0, 1),
+                                                       ("os", 11, 17, 0, 0, 0, 0)])
+def test_cfar_block_alone_on_stored_profiles_with_an_ordered_statistic(cuda, oracle, ctype, log_n, W, G, kl, kr, lin):
+    """BASELINE configs[3] "CFAR-only on stored 16-bit magnitude profiles" (SURVEY 8d): AXI4CFARBlock alone (rsp_cfar_run) with the hardware GOS
+    core and with the golden cfarOS, exponential clutter + targets and full-range cells (negative ones too), against the oracle's CFAR"""
+    n = 1 << log_n
+    rows = 6 if log_n <= 12 else 3
+    rng = np.random.default_rng(log_n * 7 + W)
+    prof = np.floor(rng.exponential(256.0, (rows, n))).astype(np.int64)
+    prof[:, [n // 8, n // 4, (3 * n) // 4]] += 4096
+    prof[-1] = rng.integers(-32768, 32768, n)                 # every 16-bit value, negative cells included
+    p = fixed_params(n, 128 if W > 64 else 64, max(G, 1), ctype=GOSCFARType if ctype == "gos" else R.OSGoldenCFARType)
+    p.cfarParams.protoThreshold = FixedPoint(18, 0)
+    regs = dict(fftWin=n, thresholdScaler=2 if lin else 300, logOrLinearMode=lin, peakGrouping=0, cfarMode=0, windowCells=W, guardCells=G, indexLagg=kl, indexLead=kr)
+    _, _, cfar = oracle_cfgs(oracle, p, log_n, 2, regs)
+    words = (prof & 0xFFFF).astype(np.uint32)
+    want = oracle.cfar_words(cfar, words)
+    with R.FftMagCfarChainVanilla(p) as ch:
+        configure(ch, log_n, 2, regs)
+        d_out = cuda.zeros((rows, n), dtype=cuda.int32, device="cuda")
+        launches = ch.kernel_launches
+        ch.cfar(to_dev(cuda, words), rows, out=d_out)
+        cuda.cuda.synchronize()
+        got = from_dev_u32(d_out)
+        assert ch.kernel_launches == launches + 1
+    assert (got == want).all(), f"{int((got != want).sum())} beats differ, first at {np.argwhere(got != want)[:3].tolist()}"
+    assert (want & 1).sum() >= 3
