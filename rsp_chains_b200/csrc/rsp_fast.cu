@@ -679,8 +679,8 @@ __global__ void __launch_bounds__(FGeo<S, LP>::THREADS, fast_min_blocks<S, LP>()
     if (gen) gen_advance(gr.q, gr.per, g_dq, g_dper, a.gen_period);
     // every thread is past the first barrier of the passes: the staging area has been read and can take the next rows
     if (stage && row0 + stride < a.n_rows) prefetch(row0 + stride);
-    if (a.l2_prefetch && tl == 0 && row0 + stride + c < a.n_rows) {   // the next row's 4 N bytes into L2: its first-pass loads then miss L1 only
-      const uint32_t *nxt = a.in + (size_t)(row0 + stride + c) * N;
+    if (a.l2_prefetch && tl == 0 && row0 + a.l2_prefetch * stride + c < a.n_rows) {   // a coming row's 4 N bytes into L2 (l2_prefetch rows ahead): its first-pass loads then miss L1 only
+      const uint32_t *nxt = a.in + (size_t)(row0 + a.l2_prefetch * stride + c) * N;
       asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" :: "l"(nxt), "r"(4 * N) : "memory");
     }
     // prefix sums of the thread's PTS consecutive magnitudes, 16 at a time (32 points per thread: the second read of the magnitudes
@@ -1709,7 +1709,7 @@ rsp_status launch_fast_chain(const Plan &pl, const LaunchCtx &ctx, const FxArgs 
   if ((pl.mode == MODE_FAST3 && !fa.cfar_only) || a.in_bp != 0 || a.sc_bp != 0 || a.thr_bp != 0) { fast_cfar_bp(a, &fa); fa.bpc = 1; }
   // measured on B200 (profiles/r02_d_l2prefetch.txt): N = 16384 +5.3 %, N = 4096 +1.9 %, N = 1024 +1.3 %; RSP_FAST_L2_PREFETCH=0 turns it off
   { static int l2p = -1; if (l2p < 0) { const char *e = std::getenv("RSP_FAST_L2_PREFETCH"); l2p = e ? std::atoi(e) : 1; }
-    fa.l2_prefetch = (l2p != 0 && a.gen_full == nullptr && (reinterpret_cast<uintptr_t>(a.in) & 15u) == 0) ? 1 : 0; }
+    fa.l2_prefetch = (l2p != 0 && a.gen_full == nullptr && (reinterpret_cast<uintptr_t>(a.in) & 15u) == 0) ? (l2p > 4 ? 4 : l2p) : 0; }   // value = rows ahead
   fa.gen_phase = a.gen_phase; fa.gen_full = a.core == CORE_MEM ? a.gen_full : nullptr; fa.gen_period = a.gen_period; fa.gen_pp = a.gen_pp;
   fa.gen_mask = a.gen_mask; fa.gen_k0 = a.gen_k0;
   { static int skew = -1; if (skew < 0) { const char *e = std::getenv("RSP_FAST_SKEW_NS"); skew = e ? std::atoi(e) : 0; } fa.skew_ns = skew; }
