@@ -957,3 +957,55 @@ def test_cfar_block_alone_on_stored_profiles_with_an_ordered_statistic(cuda, ora
         assert ch.kernel_launches == launches + 1
     assert (got == want).all(), f"{int((got != want).sum())} beats differ, first at {np.argwhere(got != want)[:3].tolist()}"
     assert (want & 1).sum() >= 3
+
+
+def test_randomised_chain_configurations_against_the_oracle(cuda, oracle):
+    """48 seeded random configurations over everything the specialised kernels and their fallbacks cover between them -- size (run-time sizes of a
+    larger generator included), binary points (equal and mixed), CFAR core, windows, guard cells, thresholds, modes, peak grouping, row counts --
+    each bit for bit against the oracle, whichever kernel the planner picks"""
+    import os
+    n_trials, seed = int(os.environ.get("RSP_FUZZ_TRIALS", "48")), int(os.environ.get("RSP_FUZZ_SEED", "20260"))   # a longer soak: RSP_FUZZ_TRIALS=600
+    rng = np.random.default_rng(seed)
+    picked = {}
+    for trial in range(n_trials):
+        log_n = int(rng.integers(6, 15))
+        n = 1 << log_n
+        extra = int(rng.choice([0, 0, 2])) if log_n <= 12 else 0          # generator larger than the transform: an even number of stages dropped
+        numpoints = n << extra
+        core = str(rng.choice(["ca", "ca", "ca", "gos", "os"])) if log_n >= 10 else "ca"
+        bp = int(rng.choice([0, 0, 12, 14, 3]))
+        mixed = bp == 0 and rng.random() < 0.3
+        wmax = min(64, n // 4)
+        W = int(rng.choice([w for w in (4, 8, 16, 32, 64) if w <= wmax])) if core != "gos" else int(rng.integers(3, min(100, n // 4)))
+        if core == "os":
+            W = min(W, 32)
+        G = int(rng.integers(1, max(2, min(9, W))))
+        lin = int(rng.integers(0, 2))
+        mode = int(rng.integers(0, 3))
+        pg = int(rng.random() < 0.2) if core == "ca" else 0
+        ctype = {"ca": CACFARType, "gos": GOSCFARType, "os": R.OSGoldenCFARType}[core]
+        p = fixed_params(numpoints, 128 if W > 64 else 64, max(G, 1) if rng.random() < 0.7 else 8, bp=bp, ctype=ctype)
+        ib, tb, sb = (bp, bp, bp)
+        if mixed:
+            ib, tb, sb = 0, int(rng.integers(0, 5)), int(rng.integers(0, 8))
+        p.cfarParams.protoIn, p.cfarParams.protoThreshold, p.cfarParams.protoScaler = FixedPoint(16, ib), FixedPoint(16, tb), FixedPoint(16, sb)
+        scaler = int(rng.uniform(1.5, 4.0) * (1 << sb)) if lin else int(rng.uniform(0.0, 0.02) * (1 << sb))
+        regs = dict(fftWin=n, thresholdScaler=scaler, logOrLinearMode=lin, divSum=max(0, int(np.log2(W))), peakGrouping=pg, cfarMode=mode, windowCells=W, guardCells=G,
+                    indexLagg=int(rng.integers(1, W + 1)), indexLead=int(rng.integers(1, W + 1)))
+        rows = int(rng.integers(1, 12)) if log_n >= 12 else int(rng.integers(1, 70))
+        beats = np.concatenate([synth.chirps_fixed(rows, n, seed=1000 + trial, noise=2.0 ** -int(rng.integers(2, 8))), synth.random_beats(1, n, seed=2000 + trial)])[:rows] \
+            if rows > 1 else synth.random_beats(1, n, seed=2000 + trial)
+        try:
+            fft, mag, cfar = oracle_cfgs(oracle, p, log_n, 2, regs)
+            want = oracle.chain_fixed_words(fft, mag, cfar, beats)
+        except Exception:
+            continue
+        try:
+            got, variant = run_fixed(cuda, p, log_n, 2, regs, beats)
+        except R.RspError as e:          # refused configurations must be refused for a stated reason, never computed wrongly
+            assert e.status in (R._abi.RSP_EINVAL, R._abi.RSP_EUNSUPPORTED), (trial, str(e))
+            continue
+        picked[variant.split("<")[0]] = picked.get(variant.split("<")[0], 0) + 1
+        assert (got == want).all(), (trial, variant, dict(log_n=log_n, numpoints=numpoints, core=core, bp=bp, bps=(ib, tb, sb), W=W, G=G, lin=lin, mode=mode, pg=pg, rows=rows),
+                                     np.argwhere(got != want)[:3].tolist())
+    assert picked.get("chain_fixed_fast", 0) >= 10 and sum(picked.values()) >= 30, picked
