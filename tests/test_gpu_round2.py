@@ -1009,3 +1009,37 @@ def test_randomised_chain_configurations_against_the_oracle(cuda, oracle):
         assert (got == want).all(), (trial, variant, dict(log_n=log_n, numpoints=numpoints, core=core, bp=bp, bps=(ib, tb, sb), W=W, G=G, lin=lin, mode=mode, pg=pg, rows=rows),
                                      np.argwhere(got != want)[:3].tolist())
     assert picked.get("chain_fixed_fast", 0) >= 10 and sum(picked.values()) >= 30, picked
+
+
+def test_randomised_fp32_configurations_against_the_fp64_dataflow(cuda, oracle):
+    """24 seeded random configurations of the DspReal flavour (sizes 256 ... 16384, window sizes that do and do not fit the fast kernel, guard cells,
+    CA / GO / SO, linear / log, peak grouping): thresholds within 1e-4 of the fp64 dataflow, identical decided detections"""
+    import os
+    n_trials, seed = int(os.environ.get("RSP_FUZZ_TRIALS", "24")), int(os.environ.get("RSP_FUZZ_SEED", "99"))
+    rng = np.random.default_rng(seed)
+    fast = 0
+    for trial in range(n_trials):
+        log_n = int(rng.integers(8, 15))
+        n = 1 << log_n
+        W = int(rng.choice([w for w in (8, 16, 32, 48, 64, 128) if w <= n // 4]))
+        G = int(rng.integers(1, min(9, W)))
+        gws = G if rng.random() < 0.6 else 8
+        mode, lin, pg = int(rng.integers(0, 3)), int(rng.integers(0, 2)), int(rng.random() < 0.3)
+        rows = int(rng.integers(1, 5))
+        xc = synth.chirps_complex(rows, n, seed=3000 + trial, noise=2.0 ** -int(rng.integers(3, 7)))
+        x32 = np.stack([xc.real, xc.imag], axis=-1).astype(np.float32)
+        xq = x32[..., 0].astype(np.float64) + 1j * x32[..., 1].astype(np.float64)
+        regs = dict(fftWin=n, logOrLinearMode=lin, divSum=int(np.log2(W)) if W & (W - 1) == 0 else 5, peakGrouping=pg, cfarMode=mode, windowCells=W, guardCells=G)
+        scaler = float(rng.uniform(2.0, 5.0)) if lin else float(rng.uniform(0.0, 2e-4))
+        thr, pk, variant = run_f32(cuda, f32_params(n, max(W, 16) if W & (W - 1) == 0 else 64, gws), log_n, 2, regs, scaler, x32)
+        fast += variant.startswith("chain_f32_fast")
+        mag, want_thr, want_pk = f64_chain(oracle, xq, log_n, 2, regs, scaler, W, G, guard_window_size=gws)
+        scale = np.abs(want_thr).max()
+        rel = np.abs(thr - want_thr) / np.maximum(np.abs(want_thr), 1e-3 * scale)
+        assert rel.max() < REL_TOL, (trial, variant, dict(log_n=log_n, W=W, G=G, gws=gws, mode=mode, lin=lin, pg=pg), float(rel.max()))
+        sure = np.abs(mag - want_thr) / np.maximum(np.abs(want_thr), 1e-3 * scale) > 10 * REL_TOL
+        if pg:      # a neighbour within the tolerance of the cell under test leaves the local-maximum test undecided
+            nb = np.minimum(np.abs(mag - np.roll(mag, -1, axis=1)), np.abs(mag - np.roll(mag, -G, axis=1))) / np.maximum(np.abs(mag), 1e-3 * scale) > 10 * REL_TOL
+            sure &= nb
+        assert (pk[sure] == want_pk[sure]).all(), (trial, variant, dict(log_n=log_n, W=W, G=G, gws=gws, mode=mode, lin=lin, pg=pg))
+    assert fast >= n_trials // 4, fast
