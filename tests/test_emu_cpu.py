@@ -214,6 +214,44 @@ def test_emu_fp32_flavour(emu, oracle, core):
     assert (pk[sure] == want_pk[sure]).all() and want_pk.sum() >= 5
 
 
+def emu_generate(emu, p, oracle, chirps, order, repeats, start, frame_num, inter, total, mult=(0, 0)):
+    """planner + device generator forms on the CPU for one PLFG programme: (rc, message, closed, running, table, plfg)"""
+    g = p.plfgParams
+    regs = [0] * (6 + g.maxChirpOrdinalNum + 2 * g.maxNumOfDifferentChirps)
+    regs[0], regs[2], regs[3], regs[4], regs[5] = 1, frame_num, inter, len(order), start
+    for c, segs in enumerate(chirps):
+        regs[6 + c] = len(segs)
+    for d, (o, r) in enumerate(zip(order, repeats)):
+        regs[6 + g.maxChirpOrdinalNum + d] = r
+        regs[6 + g.maxChirpOrdinalNum + g.maxNumOfDifferentChirps + d] = o
+    ram = [0] * (g.maxChirpOrdinalNum * g.maxNumOfSegments)
+    for c, segs in enumerate(chirps):
+        for i, sg in enumerate(segs):
+            ram[c * g.maxNumOfSegments + i] = oracle.plfg_ram_word(*sg, output_width=g.outputWidthInt, samples_width=g.maxNumOfSamplesWidth)
+    cp = _c_params(p.fftParams, p.magParams, p.cfarParams, p.plfgParams, p.ncoParams)
+    closed = np.zeros(total, np.uint32); running = np.zeros(total, np.uint32); table = np.zeros(total, np.uint32); plfg = np.zeros(total, np.int32)
+    err = C.create_string_buffer(512)
+    rc = emu.rsp_emu_generate(C.byref(cp), _u32(regs).ctypes.data_as(C.c_void_p), len(regs), _u32(ram).ctypes.data_as(C.c_void_p), len(ram),
+                              _u32(mult).ctypes.data_as(C.c_void_p), C.c_uint64(total), closed.ctypes.data_as(C.c_void_p),
+                              running.ctypes.data_as(C.c_void_p), table.ctypes.data_as(C.c_void_p), plfg.ctypes.data_as(C.c_void_p), err, 512)
+    return rc, err.value.decode(), closed, running, table, plfg
+
+
+def emu_generator_check(emu, oracle, p, chirps, order, repeats, start, frame_num, inter, want_plfg, mult=(0, 0), what=None):
+    total = len(want_plfg)
+    rc, msg, closed, running, table, plfg = emu_generate(emu, p, oracle, chirps, order, repeats, start, frame_num, inter, total, mult)
+    assert rc == 0, (msg, what)
+    assert (plfg == want_plfg).all(), what
+    n = p.ncoParams
+    want, _ = oracle.nco_words(want_plfg, n.tableSize, n.tableWidth, n.phaseWidth, n.phaseAccEnable, use_multiplier=n.useMultiplier,
+                               enable_multiplying=bool(mult[0]), multiplying_factor=mult[1], rounding_mode=n.roundingMode, rasterized=n.rasterizedMode)
+    assert (closed == want).all() and (running == want).all(), what
+    if n.phaseWidth <= 12 and not n.useMultiplier:
+        assert (table == want).all(), what      # the fused kernel's beats
+    if frame_num:                               # the schedule ends after frameNum frames: one sample more is refused
+        assert emu_generate(emu, p, oracle, chirps, order, repeats, start, frame_num, inter, total + 1, mult)[0] == _abi.RSP_EINVAL, what
+
+
 @pytest.mark.parametrize("nco_kw,plfg_kw", [(dict(), dict()), (dict(phaseAccEnable=False), dict()), (dict(phaseWidth=14, tableSize=1024), dict()),
                                             (dict(phaseWidth=12, tableSize=256, tableWidth=12), dict(outputWidthInt=12, outputWidthFrac=4)),
                                             (dict(useMultiplier=True, roundingMode="Convergent"), dict()),
@@ -228,37 +266,27 @@ def test_emu_generator(emu, oracle, nco_kw, plfg_kw, frame_num, inter):
         setattr(p.ncoParams, k, v)
     for k, v in plfg_kw.items():
         setattr(p.plfgParams, k, v)
-    g = p.plfgParams
     chirps = [[(3, 200, True, False), (5, 120, False, False)], [(1, 255, True, False), (0, 40, False, True), (2, 180, False, False)],
               [(7, 1, True, False)], [(11, 90, False, False), (11, 90, True, False), (4, 33, True, False)]]
     order, repeats, start = [2, 0, 1, 3, 0], [2, 1, 3, 1, 2], 37
-    op = oracle_plfg(oracle, p, start, chirps, order, repeats, frame_num, inter)
     frame_len = 2 * 2 + 320 + 3 * 475 + 213 + 2 * 320
     total = frame_num * frame_len + (frame_num - 1) * max(inter - 1, 0) if frame_num else 3 * frame_len + 100
-    regs = [0] * (6 + g.maxChirpOrdinalNum + 2 * g.maxNumOfDifferentChirps)
-    regs[0], regs[2], regs[3], regs[4], regs[5] = 1, frame_num, inter, len(order), start
-    for c, segs in enumerate(chirps):
-        regs[6 + c] = len(segs)
-    for d, (o, r) in enumerate(zip(order, repeats)):
-        regs[6 + g.maxChirpOrdinalNum + d] = r
-        regs[6 + g.maxChirpOrdinalNum + g.maxNumOfDifferentChirps + d] = o
-    ram = [0] * (g.maxChirpOrdinalNum * g.maxNumOfSegments)
-    for c, segs in enumerate(chirps):
-        for i, sg in enumerate(segs):
-            ram[c * g.maxNumOfSegments + i] = oracle.plfg_ram_word(*sg, output_width=g.outputWidthInt, samples_width=g.maxNumOfSamplesWidth)
-    mult = (1, 0x3000) if nco_kw.get("useMultiplier") else (0, 0)
-    cp = _c_params(p.fftParams, p.magParams, p.cfarParams, p.plfgParams, p.ncoParams)
-    closed = np.zeros(total, np.uint32); running = np.zeros(total, np.uint32); table = np.zeros(total, np.uint32); plfg = np.zeros(total, np.int32)
-    err = C.create_string_buffer(512)
-    rc = emu.rsp_emu_generate(C.byref(cp), _u32(regs).ctypes.data_as(C.c_void_p), len(regs), _u32(ram).ctypes.data_as(C.c_void_p), len(ram),
-                              _u32(mult).ctypes.data_as(C.c_void_p), C.c_uint64(total), closed.ctypes.data_as(C.c_void_p),
-                              running.ctypes.data_as(C.c_void_p), table.ctypes.data_as(C.c_void_p), plfg.ctypes.data_as(C.c_void_p), err, 512)
-    assert rc == 0, err.value.decode()
-    want_plfg = op.run(total)
-    assert len(want_plfg) == total and (plfg == want_plfg).all()
-    n = p.ncoParams
-    want, _ = oracle.nco_words(want_plfg, n.tableSize, n.tableWidth, n.phaseWidth, n.phaseAccEnable, use_multiplier=n.useMultiplier,
-                               enable_multiplying=bool(mult[0]), multiplying_factor=mult[1], rounding_mode=n.roundingMode, rasterized=n.rasterizedMode)
-    assert (closed == want).all() and (running == want).all()
-    if n.phaseWidth <= 12 and not n.useMultiplier:
-        assert (table == want).all()      # the fused kernel's beats
+    want_plfg = oracle_plfg(oracle, p, start, chirps, order, repeats, frame_num, inter).run(total)
+    assert len(want_plfg) == total
+    emu_generator_check(emu, oracle, p, chirps, order, repeats, start, frame_num, inter, want_plfg, mult=(1, 0x3000) if nco_kw.get("useMultiplier") else (0, 0))
+
+
+def test_emu_generator_randomised_programmes(emu, oracle):
+    """200 seeded random PLFG programmes (tests/util.py:random_plfg_programme) through the planner and the three device forms of the generator on the
+    CPU, against the oracle PLFG / NCO; the same programmes run on the GPU in tests/test_gpu_round2.py"""
+    from tests.util import random_plfg_programme
+    rng = np.random.default_rng(int(os.environ.get("RSP_FUZZ_SEED", "4242")))
+    for trial in range(int(os.environ.get("RSP_FUZZ_TRIALS", "200"))):
+        nco_kw, chirps, order, repeats, frame_num, inter, start, n_endless = random_plfg_programme(rng)
+        p = R.rsp_chain_vanilla_app_params()
+        for k, v in nco_kw.items():
+            setattr(p.ncoParams, k, v)
+        what = (trial, nco_kw, chirps, order, repeats, frame_num, inter, start)
+        want_plfg = oracle_plfg(oracle, p, start, chirps, order, repeats, frame_num, inter).run(n_endless if not frame_num else 1 << 18)
+        assert 0 < len(want_plfg) < 1 << 18, what
+        emu_generator_check(emu, oracle, p, chirps, order, repeats, start, frame_num, inter, want_plfg, what=what)

@@ -1043,3 +1043,54 @@ def test_randomised_fp32_configurations_against_the_fp64_dataflow(cuda, oracle):
             sure &= nb
         assert (pk[sure] == want_pk[sure]).all(), (trial, variant, dict(log_n=log_n, W=W, G=G, gws=gws, mode=mode, lin=lin, pg=pg))
     assert fast >= n_trials // 4, fast
+
+
+def test_randomised_generator_programmes_against_the_oracle(cuda, oracle):
+    """32 seeded random PLFG programmes (tests/util.py:random_plfg_programme: 1-4 chirp types of 1-4 segments with random slopes, lengths, directions
+    and resets, random chirp order and repeats, finite and endless frame counts, pauses 0 ... 63, starting points) through random NCO flavours, written
+    through the register bus: PLFG words and NCO beats bit-exact from both generator kernels, the schedule's end refused one sample later, and the
+    chain fed by the generator equal to the chain fed the oracle's beats.  The registers keep their Chisel widths (PLFGDspBlockMem.scala:49-53:
+    segmentNums log2Ceil(maxNumOfSegments) = 2 bits, differentChirpsNum 3 bits), so 4 segments / 8 different chirps wrap to 0 as in the RTL: the
+    oracle is given the wrapped values."""
+    import os
+    from tests.util import random_plfg_programme
+    n_trials, seed = int(os.environ.get("RSP_FUZZ_TRIALS", "32")), int(os.environ.get("RSP_FUZZ_SEED", "4242"))
+    rng = np.random.default_rng(seed)
+    regs = dict(fftWin=1024, thresholdScaler=4, logOrLinearMode=1, divSum=5, peakGrouping=0, cfarMode=0, windowCells=32, guardCells=4)
+    for trial in range(n_trials):
+        nco_kw, chirps, order, repeats, frame_num, inter, start, n_endless = random_plfg_programme(rng)
+        p = R.rsp_chain_vanilla_app_params()
+        for k, v in nco_kw.items():
+            setattr(p.ncoParams, k, v)
+        what = (trial, nco_kw, chirps, order, repeats, frame_num, inter, start)
+        op = oracle_plfg(oracle, p, start, chirps, order, repeats, frame_num, inter)
+        op.segment_nums = [len(s) & 3 for s in chirps]
+        op.different_chirps_num = len(order) & 7
+        want_plfg = op.run(n_endless if not frame_num else 1 << 18)
+        total = len(want_plfg)
+        assert total > 0 and (frame_num == 0 or total < 1 << 18), what
+        n_rows = min(total // 1024, 4)
+        with R.RspChainVanilla(p) as ch:
+            configure(ch, 10, 2, regs)
+            write_plfg(ch, p, oracle, start, chirps, order, repeats, frame_num, inter)
+            d_nco = cuda.zeros(total, dtype=cuda.int32, device="cuda")
+            d_plfg = cuda.zeros(total, dtype=cuda.int32, device="cuda")
+            d_tab = cuda.zeros(total, dtype=cuda.int32, device="cuda")
+            ch.generate(total, d_nco, d_plfg)       # generator_kernel (closed form)
+            ch.generate(total, d_tab, None)         # generator_table_kernel
+            if n_rows:
+                d_out = cuda.zeros((n_rows, 1024), dtype=cuda.int32, device="cuda")
+                ch.run_from_generator(n_rows, 1, out=d_out)
+            cuda.cuda.synchronize()
+            if frame_num:
+                with pytest.raises(R.RspError):
+                    ch.generate(total + 1, cuda.zeros(total + 1, dtype=cuda.int32, device="cuda"), None)
+        got_plfg, got_nco, got_tab = d_plfg.cpu().numpy(), from_dev_u32(d_nco), from_dev_u32(d_tab)
+        n = p.ncoParams                                 # (to_c has set the rasterized phase width by now)
+        want_nco, _ = oracle.nco_words(want_plfg, n.tableSize, n.tableWidth, n.phaseWidth, n.phaseAccEnable, rasterized=n.rasterizedMode)
+        assert (got_plfg == want_plfg).all(), (what, np.argwhere(got_plfg != want_plfg)[:3].ravel())
+        assert (got_nco == want_nco).all(), (what, np.argwhere(got_nco != want_nco)[:3].ravel())
+        assert (got_tab == want_nco).all(), (what, np.argwhere(got_tab != want_nco)[:3].ravel())
+        if n_rows:
+            fft, mag, cfar = oracle_cfgs(oracle, p, 10, 2, regs)
+            assert (from_dev_u32(d_out) == oracle.chain_fixed_words(fft, mag, cfar, want_nco[:n_rows * 1024].reshape(n_rows, 1024))).all(), what
