@@ -1416,13 +1416,15 @@ static rsp_status launch_fast_inst_lp(const LaunchCtx &c, const FastArgs &fa_in,
 }
 template <int S, int CMODE, bool LINEAR, int EJ>
 static rsp_status launch_fast_inst(const LaunchCtx &c, const FastArgs &fa, bool pg, cudaStream_t st, const char **err) {
-  if (fa.tw3 != nullptr) {   // binPoint >= 2 (never together with peak grouping: fast_chain_supported); its CFAR phase is the binary-point one
-    if constexpr (S == 14) return launch_fast_inst_lp<S, 5, CMODE, LINEAR, EJ, false, true, true>(c, fa, st, err);
-    else return launch_fast_inst_lp<S, 4, CMODE, LINEAR, EJ, false, true, true>(c, fa, st, err);
+  constexpr int LPV = S == 14 ? 5 : 4;
+  if (fa.tw3 != nullptr) {   // binPoint >= 2; its CFAR phase is the binary-point one.  Peak grouping is an instantiation of its own (as a run-time flag
+                             // it cost the applications' configuration 6.5 %)
+    if (pg) return launch_fast_inst_lp<S, LPV, CMODE, LINEAR, EJ, true, true, true>(c, fa, st, err);
+    return launch_fast_inst_lp<S, LPV, CMODE, LINEAR, EJ, false, true, true>(c, fa, st, err);
   }
   if (fa.bpc) {   // binPoint 0 in the transform, binary points in the CFAR (RspChainVanillaSpec: input 0, threshold 3, scaler 6)
-    if constexpr (S == 14) return launch_fast_inst_lp<S, 5, CMODE, LINEAR, EJ, false, false, true>(c, fa, st, err);
-    else return launch_fast_inst_lp<S, 4, CMODE, LINEAR, EJ, false, false, true>(c, fa, st, err);
+    if (pg) return launch_fast_inst_lp<S, LPV, CMODE, LINEAR, EJ, true, false, true>(c, fa, st, err);
+    return launch_fast_inst_lp<S, LPV, CMODE, LINEAR, EJ, false, false, true>(c, fa, st, err);
   }
   if (pg) {   // (one geometry per size: the peak-grouping kernels are the registers' other setting, not a tuning target)
     if constexpr (S == 14) return launch_fast_inst_lp<S, 5, CMODE, LINEAR, EJ, true>(c, fa, st, err);
@@ -1673,9 +1675,7 @@ bool fast_chain_supported(const Plan &pl, const FxArgs &a) {
   if (a.core == CORE_OS) return pl.S >= 10 && fast_os_supported(a);
   if (a.core != CORE_MEM || a.in_w != 16 || a.send_cut) return false;
   const bool bpc = tw3 || a.in_bp != 0 || a.sc_bp != 0 || a.thr_bp != 0;   // binary points in the CFAR: its own instantiation
-  // (peak grouping together with binary points stays on the run-time-parameter kernel: as a run-time flag in the binary-point kernels it cost the
-  // applications' own configuration 6.5 %, 197 -> 184 Gsamples/s, and as instantiations a third more kernels to build)
-  if (bpc && (a.peak_grouping || a.cfar_trim != TRIM_FLOOR || !fast_cfar_bp(a, nullptr))) return false;
+  if (bpc && (a.cfar_trim != TRIM_FLOOR || !fast_cfar_bp(a, nullptr))) return false;   // (peak grouping with binary points: its own instantiations)
   if (a.out == nullptr && a.det_list == nullptr) return false;
   if (a.thr_w < 1 || a.thr_w > 32 || a.G < 1 || a.W < 1 || a.div_sum < 0 || a.div_sum > 30) return false;
   const int ej = fast_edge_iters(pl.S, a.W, a.G);

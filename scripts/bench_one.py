@@ -17,11 +17,11 @@ elif key == "c2":
     B.run_case("C2 x 256 frames", B.fixed_params(1024, 64, 4), 10, ca(1024, 16, 4, 4), 65536, 1)
 elif key == "c5":
     B.run_case("C5 fixed one frame", B.fixed_params(16384, 64, 8), 14, ca(16384, 64, 8, 6), 32768, 8)
-elif key in ("app12", "app12_14"):   # FftMagCfarChainVanillaApp / RxFftMagCfarTxChainApp: binPoint 12 (src/main/scala/FftMagCfarChain.scala:76-120)
+elif key in ("app12", "app12_14", "app12pg"):   # FftMagCfarChainVanillaApp / RxFftMagCfarTxChainApp: binPoint 12 (src/main/scala/FftMagCfarChain.scala:76-120)
     import rsp_chains_b200 as R
     p = R.fft_mag_cfar_chain_vanilla_app_params()
-    if key == "app12":
-        B.run_case("FftMagCfarChainVanillaApp (binPoint 12) x 256 frames of 256 chirps", p, 10, dict(fftWin=1024, thresholdScaler=int(3.5 * 4096), logOrLinearMode=1, divSum=6, peakGrouping=0, cfarMode=0, windowCells=64, guardCells=4), 65536, 1)
+    if key in ("app12", "app12pg"):
+        B.run_case("FftMagCfarChainVanillaApp (binPoint 12) x 256 frames of 256 chirps", p, 10, dict(fftWin=1024, thresholdScaler=int(3.5 * 4096), logOrLinearMode=1, divSum=6, peakGrouping=int(key == "app12pg"), cfarMode=0, windowCells=64, guardCells=4), 65536, 1)
     else:
         p.fftParams.numPoints = 16384; p.cfarParams.fftSize = 16384
         p.fftParams.keepMSBorLSB = [True] * 14; p.fftParams.expandLogic = [0] * 14

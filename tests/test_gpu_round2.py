@@ -1094,3 +1094,47 @@ def test_randomised_generator_programmes_against_the_oracle(cuda, oracle):
         if n_rows:
             fft, mag, cfar = oracle_cfgs(oracle, p, 10, 2, regs)
             assert (from_dev_u32(d_out) == oracle.chain_fixed_words(fft, mag, cfar, want_nco[:n_rows * 1024].reshape(n_rows, 1024))).all(), what
+
+
+@pytest.mark.parametrize("log_n,bp,bps,W,G,gws,mode,lin", [(10, 12, None, 64, 4, 4, 0, 1),      # FftMagCfarChainVanillaApp's types with the testers' peakGrouping = 1
+                                                            (10, 12, None, 32, 2, 4, 1, 0),      # guardCells below the generator's: the left neighbour reads 0
+                                                            (12, 14, None, 16, 1, 1, 2, 1), (14, 12, None, 64, 8, 8, 0, 1), (13, 2, None, 32, 3, 8, 1, 1),
+                                                            (10, 0, (0, 3, 6), 32, 4, 4, 0, 1),  # RspChainVanillaSpec's CFAR types behind a binPoint-0 transform
+                                                            (14, 0, (0, 3, 6), 64, 4, 8, 2, 0), (11, 0, (4, 5, 2), 32, 4, 4, 1, 1),
+                                                            (8, 12, None, 16, 2, 2, 0, 1)])       # below 1024 points
+def test_fast_kernel_peak_grouping_with_binary_points(cuda, oracle, log_n, bp, bps, W, G, gws, mode, lin):
+    """peakGrouping = 1 together with binary points (in the transform, in the CFAR, or both) on the specialised kernel's <PG, TW3 / BPC> instantiations:
+    beats and detection list bit-exact, fewer peaks than without grouping, quiet / full-scale / corner rows"""
+    n = 1 << log_n
+    rows = 6 if log_n <= 12 else 3
+    beats = np.concatenate([synth.chirps_fixed(rows - 3, n, seed=260 + log_n, noise=2.0 ** -4), synth.random_beats(2, n, seed=270 + log_n),
+                            np.full((1, n), 0x80008000, dtype=np.uint32)])
+    p = fixed_params(n, 64, gws, bp=bp)
+    if bps is None:
+        p.cfarParams.protoScaler = FixedPoint(16, bp)
+        sb = bp
+    else:
+        p.cfarParams.protoIn, p.cfarParams.protoThreshold, p.cfarParams.protoScaler = FixedPoint(16, bps[0]), FixedPoint(16, bps[1]), FixedPoint(16, bps[2])
+        sb = bps[2]
+    regs = dict(fftWin=n, thresholdScaler=int(3.25 * (1 << sb)) if lin else int(0.01 * (1 << sb)) + 1, logOrLinearMode=lin, divSum=int(np.log2(W)),
+                peakGrouping=1, cfarMode=mode, windowCells=W, guardCells=G)
+    fft, mag, cfar = oracle_cfgs(oracle, p, log_n, 2, regs)
+    want = oracle.chain_fixed_words(fft, mag, cfar, beats)
+    fft0, mag0, cfar0 = oracle_cfgs(oracle, p, log_n, 2, dict(regs, peakGrouping=0))
+    _, _, peak0 = decode_cfar_words(oracle.chain_fixed_words(fft0, mag0, cfar0, beats), n)
+    with R.FftMagCfarChainVanilla(p) as ch:
+        configure(ch, log_n, 2, regs)
+        assert ch.variant == f"chain_fixed_fast<{log_n}>", ch.variant
+        d_in = to_dev(cuda, beats)
+        d_out = cuda.zeros_like(d_in)
+        det_list = cuda.zeros((rows * n, 4), dtype=cuda.int32, device="cuda")
+        det_count = cuda.zeros(1, dtype=cuda.int32, device="cuda")
+        ch.run(d_in, rows, 1, out=d_out, det_list=det_list, det_count=det_count)
+        cuda.cuda.synchronize()
+        got = from_dev_u32(d_out)
+        k = int(det_count.item())
+        dets = det_list[:k].cpu().numpy()
+    assert (got == want).all(), f"{int((got != want).sum())} beats differ, first at {np.argwhere(got != want)[:3].tolist()}"
+    thr, bins, peak = decode_cfar_words(want, n)
+    assert k == int(peak.sum()) and 0 < k <= int(peak0.sum())
+    assert {(int(d[0]), int(d[1])): int(d[2]) & 0xFFFF for d in dets} == {(r, b): int(thr[r, b]) for r, b in np.argwhere(peak == 1)}
