@@ -1138,3 +1138,50 @@ def test_fast_kernel_peak_grouping_with_binary_points(cuda, oracle, log_n, bp, b
     thr, bins, peak = decode_cfar_words(want, n)
     assert k == int(peak.sum()) and 0 < k <= int(peak0.sum())
     assert {(int(d[0]), int(d[1])): int(d[2]) & 0xFFFF for d in dets} == {(r, b): int(thr[r, b]) for r, b in np.argwhere(peak == 1)}
+
+
+def test_handles_on_two_streams_and_no_device_memory_left_behind(cuda, oracle):
+    """two handles with different configurations interleaved on two streams (each call asynchronous on the stream it is given), results bit-exact; then
+    150 handles created, used (chain, generator with its scratch, host-buffer run with its staging) and destroyed: the device's free memory returns to
+    where it was (rsp_destroy frees tables, scratch and staging)"""
+    n_a, n_b, rows = 1024, 4096, 64
+    beats_a, beats_b = synth.chirps_fixed(rows, n_a, seed=301, noise=2.0 ** -4), synth.chirps_fixed(rows, n_b, seed=302, noise=2.0 ** -4)
+    p_a, p_b = fixed_params(n_a, 64, 4), fixed_params(n_b, 64, 4, ctype=GOSCFARType)
+    regs_a = dict(fftWin=n_a, thresholdScaler=4, logOrLinearMode=1, divSum=4, peakGrouping=0, cfarMode=0, windowCells=16, guardCells=4)
+    regs_b = dict(fftWin=n_b, thresholdScaler=2, logOrLinearMode=1, peakGrouping=0, cfarMode=0, windowCells=64, guardCells=4, indexLagg=48, indexLead=48)
+    want_a = oracle.chain_fixed_words(*oracle_cfgs(oracle, p_a, 10, 2, regs_a), beats_a)
+    want_b = oracle.chain_fixed_words(*oracle_cfgs(oracle, p_b, 12, 2, regs_b), beats_b)
+    s_a, s_b = cuda.cuda.Stream(), cuda.cuda.Stream()
+    with R.FftMagCfarChainVanilla(p_a) as ch_a, R.FftMagCfarChainVanilla(p_b) as ch_b:
+        configure(ch_a, 10, 2, regs_a); configure(ch_b, 12, 2, regs_b)
+        d_a, d_b = to_dev(cuda, beats_a), to_dev(cuda, beats_b)
+        outs_a, outs_b = [cuda.zeros_like(d_a) for _ in range(8)], [cuda.zeros_like(d_b) for _ in range(8)]
+        cuda.cuda.synchronize()
+        for i in range(8):
+            ch_a.run(d_a, rows, 1, out=outs_a[i], stream=s_a)
+            ch_b.run(d_b, rows, 1, out=outs_b[i], stream=s_b)
+        s_a.synchronize(); s_b.synchronize()
+        for i in range(8):
+            assert (from_dev_u32(outs_a[i]) == want_a).all() and (from_dev_u32(outs_b[i]) == want_b).all(), i
+    del d_a, d_b, outs_a, outs_b
+
+    def one_handle(i):
+        p = R.rsp_chain_vanilla_app_params()
+        with R.RspChainVanilla(p) as ch:
+            configure(ch, 10, 2, regs_a)
+            write_plfg(ch, p, oracle, 37, CHIRPS, [2, 0, 1, 3, 0], [2, 1, 3, 1, 2], 0, 5)
+            ch.run_from_generator(8 + i % 5, 1, out=scratch_out[:8 + i % 5])
+            ch.run(scratch_in, 16, 1, out=scratch_out)
+            if i % 10 == 0:
+                ch.run_host(beats_a[:16], 16, 1)
+            cuda.cuda.synchronize()
+    scratch_in, scratch_out = to_dev(cuda, beats_a[:16]), cuda.zeros((16, n_a), dtype=cuda.int32, device="cuda")
+    for i in range(10):      # warm-up: kernel attributes, the allocator's pools
+        one_handle(i)
+    cuda.cuda.synchronize()
+    free0 = cuda.cuda.mem_get_info()[0]
+    for i in range(150):
+        one_handle(i)
+    cuda.cuda.synchronize()
+    free1 = cuda.cuda.mem_get_info()[0]
+    assert free0 - free1 < (4 << 20), (free0, free1)     # (cudaMalloc works in 2 MiB pages)
