@@ -1185,3 +1185,48 @@ def test_handles_on_two_streams_and_no_device_memory_left_behind(cuda, oracle):
     cuda.cuda.synchronize()
     free1 = cuda.cuda.mem_get_info()[0]
     assert free0 - free1 < (4 << 20), (free0, free1)     # (cudaMalloc works in 2 MiB pages)
+
+
+def test_handles_from_four_host_threads(cuda, oracle):
+    """four host threads, each with its own handle, stream and configuration (ctypes releases the GIL during the calls), 40 calls each: every result
+    bit-exact -- the library's process-wide state (per-variant launch configuration, environment knobs, last-error text) is safe to share"""
+    import threading
+    cases = [(10, CACFARType, dict(thresholdScaler=4, logOrLinearMode=1, divSum=4, cfarMode=0, windowCells=16, guardCells=4)),
+             (12, GOSCFARType, dict(thresholdScaler=2, logOrLinearMode=1, cfarMode=0, windowCells=64, guardCells=4, indexLagg=48, indexLead=48)),
+             (14, CACFARType, dict(thresholdScaler=4, logOrLinearMode=1, divSum=6, cfarMode=1, windowCells=64, guardCells=8)),
+             (8, CACFARType, dict(thresholdScaler=3, logOrLinearMode=1, divSum=4, cfarMode=2, windowCells=16, guardCells=2))]
+    jobs = []
+    for i, (log_n, ctype, r) in enumerate(cases):
+        n, rows = 1 << log_n, 12
+        p = fixed_params(n, 64, 8 if log_n == 14 else 4, ctype=ctype)
+        regs = dict(fftWin=n, peakGrouping=0, **r)
+        beats = synth.chirps_fixed(rows, n, seed=400 + i, noise=2.0 ** -4)
+        jobs.append((p, log_n, regs, beats, oracle.chain_fixed_words(*oracle_cfgs(oracle, p, log_n, 2, regs), beats)))
+    errors = []
+
+    def worker(p, log_n, regs, beats, want):
+        try:
+            cuda.cuda.set_device(0)
+            s = cuda.cuda.Stream()
+            with cuda.cuda.stream(s), R.FftMagCfarChainVanilla(p) as ch:
+                configure(ch, log_n, 2, regs)
+                d_in = to_dev(cuda, beats)
+                outs = [cuda.zeros_like(d_in) for _ in range(4)]
+                for it in range(40):
+                    ch.run(d_in, beats.shape[0], 1, out=outs[it % 4], stream=s)
+                    if it % 4 == 3:
+                        s.synchronize()
+                        for o in outs:
+                            if not (from_dev_u32(o) == want).all():
+                                errors.append((log_n, it, "beats differ"))
+                                return
+                            o.zero_()
+        except Exception as e:      # noqa: BLE001 -- reported by the main thread
+            errors.append((log_n, repr(e)))
+
+    threads = [threading.Thread(target=worker, args=j) for j in jobs]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    assert not errors, errors
