@@ -53,7 +53,7 @@ template <int MODE>
 bool dispatch_fixed(int S, const FxArgs &a) {
   switch (S) {
 #define EMU_CASE(s) case s: chain_fixed_rows<s, MODE>(a); return true;
-    EMU_CASE(1) EMU_CASE(2) EMU_CASE(3) EMU_CASE(4) EMU_CASE(5) EMU_CASE(6) EMU_CASE(8) EMU_CASE(10)
+    EMU_CASE(1) EMU_CASE(2) EMU_CASE(3) EMU_CASE(4) EMU_CASE(5) EMU_CASE(6) EMU_CASE(7) EMU_CASE(8) EMU_CASE(9) EMU_CASE(10)
 #undef EMU_CASE
   default: return false;
   }

@@ -290,3 +290,30 @@ def test_emu_generator_randomised_programmes(emu, oracle):
         want_plfg = oracle_plfg(oracle, p, start, chirps, order, repeats, frame_num, inter).run(n_endless if not frame_num else 1 << 18)
         assert 0 < len(want_plfg) < 1 << 18, what
         emu_generator_check(emu, oracle, p, chirps, order, repeats, start, frame_num, inter, want_plfg, what=what)
+
+
+def test_emu_randomised_run_time_parameter_chain(emu, oracle):
+    """150 seeded random configurations of the run-time-parameter kernel's whole parameter space on the CPU (tests/util.py:random_generic_configuration:
+    sizes 8 ... 512 and run-time sizes, binPoint 0 ... 14, all trim types, 3 / 4 multipliers, radix 2 / 2^2, DIF / DIT, keep-LSB stages, IFFT through
+    the register, every magnitude mode, the four CFAR cores with CASH, sendCut, peak grouping, linear / log): planner + device code bit-exact against
+    the oracle, or refused; the same generator runs on the GPU (tests/test_gpu_round2.py)"""
+    from tests.util import random_generic_configuration
+    rng = np.random.default_rng(int(os.environ.get("RSP_FUZZ_SEED", "777")))
+    ran = refused = 0
+    for trial in range(int(os.environ.get("RSP_FUZZ_TRIALS", "150"))):
+        c = random_generic_configuration(rng, trial, fft_dir_reg=True)
+        if c is None:
+            continue
+        p, log_n, sel, regs, beats, fft_dir, what = c
+        try:
+            got, _, _, _ = emu_fixed(emu, p, log_n, sel, regs, beats, fft_dir=fft_dir)
+        except RuntimeError as e:
+            assert "rc=1:" in str(e) or "rc=2:" in str(e), (what, str(e))      # RSP_EINVAL / RSP_EUNSUPPORTED with a message
+            refused += 1
+            continue
+        p.fftParams.fftDir = bool(fft_dir)      # (the oracle takes the direction the register selected)
+        fft, mag, cfar = oracle_cfgs(oracle, p, log_n, sel, regs)
+        want = oracle.chain_fixed_words(fft, mag, cfar, beats)
+        assert (got == want).all(), (what, int((got != want).sum()))
+        ran += 1
+    assert ran >= 60 and refused <= ran // 10, (ran, refused)

@@ -1230,3 +1230,37 @@ def test_handles_from_four_host_threads(cuda, oracle):
     for t in threads:
         t.join()
     assert not errors, errors
+
+
+def test_randomised_whole_parameter_space_against_the_oracle(cuda, oracle):
+    """60 seeded random configurations over the fixed-point chain's whole parameter space (tests/util.py:random_generic_configuration: sizes 8 ... 4096 and
+    run-time sizes, binPoint 0 ... 14, all trim types, 3 / 4 multipliers, radix 2 / 2^2, DIF / DIT, keep-LSB stages, IFFT, every magnitude mode, the four
+    CFAR cores with CASH, sendCut, peak grouping, linear / log) -- mostly the run-time-parameter kernel: bit-exact against the oracle, or refused"""
+    import os
+    from tests.util import random_generic_configuration
+    rng = np.random.default_rng(int(os.environ.get("RSP_FUZZ_SEED", "31337")))
+    ran = refused = 0
+    variants = set()
+    for trial in range(int(os.environ.get("RSP_FUZZ_TRIALS", "60"))):
+        c = random_generic_configuration(rng, trial, fft_dir_reg=False, max_log=12)
+        if c is None:
+            continue
+        p, log_n, sel, regs, beats, fft_dir, what = c
+        try:
+            with R.FftMagCfarChainVanilla(p) as ch:
+                configure(ch, log_n, sel, regs)
+                variants.add(ch.variant.split("<")[0])
+                d_in = to_dev(cuda, beats)
+                d_out = cuda.zeros_like(d_in)
+                ch.run(d_in, beats.shape[0], 1, out=d_out)
+                cuda.cuda.synchronize()
+                got = from_dev_u32(d_out)
+        except R.RspError as e:
+            assert e.status in (R._abi.RSP_EINVAL, R._abi.RSP_EUNSUPPORTED), (what, str(e))
+            refused += 1
+            continue
+        fft, mag, cfar = oracle_cfgs(oracle, p, log_n, sel, regs)
+        want = oracle.chain_fixed_words(fft, mag, cfar, beats)
+        assert (got == want).all(), (what, int((got != want).sum()), np.argwhere(got != want)[:3].tolist())
+        ran += 1
+    assert ran >= 30 and refused <= max(2, ran // 10), (ran, refused, variants)
