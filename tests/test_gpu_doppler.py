@@ -32,12 +32,46 @@ def _frame(n_rx, m, n, seed):
 @pytest.mark.parametrize("cfar_axis", ["doppler", "range"])
 @pytest.mark.parametrize("n_rx,m,n,sel", [(4, 64, 256, 2), (2, 128, 1024, 2), (1, 32, 64, 1), (8, 256, 128, 3)])
 def test_range_doppler_chain_equals_the_composed_oracle(cuda, oracle, n_rx, m, n, sel, cfar_axis):
-    log_n, log_m = n.bit_length() - 1, m.bit_length() - 1
     W, G = (8, 2) if min(n, m) <= 64 else (16, 2)
     pr, pd = chain_params(n, 0, W=W, G=G), chain_params(m, 0, W=W, G=G)
-    nc, log_c = (m, log_m) if cfar_axis == "doppler" else (n, log_n)
+    nc = m if cfar_axis == "doppler" else n
     regs = dict(fftWin=nc, thresholdScaler=5, logOrLinearMode=1, divSum=int(np.log2(W)), peakGrouping=0, cfarMode=0, windowCells=W, guardCells=G)
-    frame = _frame(n_rx, m, n, seed=n + m)
+    got = _check_frame(cuda, oracle, pr, pd, n_rx, m, n, sel, cfar_axis, regs, _frame(n_rx, m, n, seed=n + m))
+    if sel == 2:     # both targets are found: range bins n/8 and n/4, Doppler bins m/8 and 3m/4
+        peak = (got & 1).astype(bool)
+        peak = peak if cfar_axis == "doppler" else peak.T
+        assert peak[n // 8, m // 8] and peak[n // 4, (3 * m) // 4]
+
+
+def test_randomised_range_doppler_frames(cuda, oracle):
+    """16 seeded random frames: 1 ... 8 RX, 8 ... 512 chirps, 64 ... 2048 samples, binPoint 0 / 12, CA / GOS / combined-window OS along either axis,
+    the three magnitudes, linear / log -- each stage and the result equal to the composed oracle blocks"""
+    import os
+    from rsp_chains_b200.params import CACFARType, GOSCFARType, OSGoldenCFARType
+    rng = np.random.default_rng(int(os.environ.get("RSP_FUZZ_SEED", "555")))
+    for trial in range(int(os.environ.get("RSP_FUZZ_TRIALS", "16"))):
+        n_rx = 1 << int(rng.integers(0, 4))
+        m, n = 1 << int(rng.integers(3, 10)), 1 << int(rng.integers(6, 12))
+        cfar_axis = "doppler" if rng.random() < 0.5 else "range"
+        nc = m if cfar_axis == "doppler" else n
+        bp = int(rng.choice([0, 12]))
+        ctype = [CACFARType, GOSCFARType, OSGoldenCFARType][int(rng.integers(0, 3))]
+        W = 1 << int(rng.integers(1, max(2, min(5, int(np.log2(nc)) - 2))))
+        G = int(rng.integers(1, 3))
+        if nc <= 2 * W + 2 * G + 1:
+            continue
+        sel = int(rng.integers(1, 4))      # (0 is the bypass: nothing to combine, refused)
+        lin = int(rng.integers(0, 2)) if sel != 3 else 0
+        pr, pd = chain_params(n, bp, cfar_type=ctype, W=max(W, 4), G=G), chain_params(m, bp, cfar_type=ctype, W=max(W, 4), G=G)
+        regs = dict(fftWin=nc, thresholdScaler=int(4 * (1 << bp)) if lin else int(rng.integers(0, 30)), logOrLinearMode=lin, divSum=int(np.log2(W)),
+                    peakGrouping=0, cfarMode=int(rng.integers(0, 3)), windowCells=W, guardCells=G, indexLagg=int(rng.integers(1, W + 1)),
+                    indexLead=int(rng.integers(1, W + 1)))
+        _check_frame(cuda, oracle, pr, pd, n_rx, m, n, sel, cfar_axis, regs, _frame(n_rx, m, n, seed=700 + trial),
+                     what=(trial, dict(n_rx=n_rx, m=m, n=n, axis=cfar_axis, bp=bp, ctype=ctype, W=W, G=G, sel=sel, lin=lin)))
+
+
+def _check_frame(cuda, oracle, pr, pd, n_rx, m, n, sel, cfar_axis, regs, frame, what=None):
+    log_n, log_m = n.bit_length() - 1, m.bit_length() - 1
     # the oracle's blocks, composed
     fr, _, cr = oracle_cfgs(oracle, pr, log_n, sel, regs if cfar_axis == "range" else dict(regs, fftWin=n))
     fd, md, cd = oracle_cfgs(oracle, pd, log_m, sel, regs if cfar_axis == "doppler" else dict(regs, fftWin=m))
@@ -54,10 +88,10 @@ def test_range_doppler_chain_equals_the_composed_oracle(cuda, oracle, n_rx, m, n
         d_in = to_dev(cuda, frame.reshape(n_rx * m, n)).view(n_rx, m, n)
         st = rd.stages(d_in)
         cuda.cuda.synchronize()
-        assert (from_dev_u32(st["range_fft"]).reshape(n_rx, m, n) == want_range).all()
-        assert (from_dev_u32(st["turned"]).reshape(n_rx, n, m) == turned).all()
-        assert (from_dev_u32(st["doppler_fft"]).reshape(n_rx, n, m) == want_dopp).all()
-        assert (from_dev_u32(st["combined"]).reshape(n, m) == want_comb).all()
+        assert (from_dev_u32(st["range_fft"]).reshape(n_rx, m, n) == want_range).all(), what
+        assert (from_dev_u32(st["turned"]).reshape(n_rx, n, m) == turned).all(), what
+        assert (from_dev_u32(st["doppler_fft"]).reshape(n_rx, n, m) == want_dopp).all(), what
+        assert (from_dev_u32(st["combined"]).reshape(n, m) == want_comb).all(), what
         rows, cols = (n, m) if cfar_axis == "doppler" else (m, n)
         d_out = cuda.empty((rows, cols), dtype=cuda.int32, device="cuda")
         launches = rd.kernel_launches
@@ -65,11 +99,8 @@ def test_range_doppler_chain_equals_the_composed_oracle(cuda, oracle, n_rx, m, n
         cuda.cuda.synchronize()
         assert rd.kernel_launches - launches == (5 if cfar_axis == "doppler" else 6)
         got = from_dev_u32(d_out)
-    assert (got == want).all()
-    if sel == 2:     # both targets are found: range bins n/8 and n/4, Doppler bins m/8 and 3m/4
-        peak = (got & 1).astype(bool)
-        peak = peak if cfar_axis == "doppler" else peak.T
-        assert peak[n // 8, m // 8] and peak[n // 4, (3 * m) // 4]
+    assert (got == want).all(), what
+    return got
 
 
 @pytest.mark.parametrize("dtype,rows,cols,batch", [("int16", 100, 37, 3), ("int32", 64, 64, 1), ("int32", 33, 1000, 2), ("int64", 17, 130, 5),
