@@ -317,3 +317,25 @@ def test_emu_randomised_run_time_parameter_chain(emu, oracle):
         assert (got == want).all(), (what, int((got != want).sum()))
         ran += 1
     assert ran >= 60 and refused <= ran // 10, (ran, refused)
+
+
+def test_emu_randomised_fp32_cores(emu, oracle):
+    """40 seeded random configurations of the DspReal flavour on the CPU (tests/util.py:random_fp32_configuration: the four CFAR cores -- Mem, Lis / GOS,
+    ASR / CASH, combined-window OS -- window, guard, modes, ordered-statistic indices, linear / log, peak grouping, 64 / 256 / 1024 points): thresholds
+    within 1e-4 of the fp64 dataflow, decided detections identical; the same generator runs on the GPU (tests/test_gpu_round2.py)"""
+    from tests.util import check_fp32_against_f64, random_fp32_configuration
+    rng = np.random.default_rng(int(os.environ.get("RSP_FUZZ_SEED", "888")))
+    for trial in range(int(os.environ.get("RSP_FUZZ_TRIALS", "40"))):
+        c = random_fp32_configuration(rng, trial, sizes=(6, 8, 10))
+        if c is None:
+            continue
+        p, log_n, regs, scaler, x32, what = c
+        n, rows = 1 << log_n, x32.shape[0]
+        cp = _c_params(p.fftParams, p.magParams, p.cfarParams)
+        thr = np.zeros((rows, n), np.float32); mask = np.zeros((rows, n // 32), np.uint32)
+        err = C.create_string_buffer(512)
+        rc = emu.rsp_emu_run_f32(C.byref(cp), _u32([log_n, 1, 0, 0]).ctypes.data_as(C.c_void_p), _u32([2]).ctypes.data_as(C.c_void_p),
+                                 cfar_reg_words(p, regs).ctypes.data_as(C.c_void_p), C.c_float(scaler), STAGE_FFT, STAGE_CFAR, x32.ctypes.data_as(C.c_void_p),
+                                 C.c_uint32(rows), thr.ctypes.data_as(C.c_void_p), mask.ctypes.data_as(C.c_void_p), err, 512)
+        assert rc == 0, (err.value.decode(), what)
+        check_fp32_against_f64(oracle, what, log_n, regs, scaler, x32, thr, unpack_mask(mask, n))

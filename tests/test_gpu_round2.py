@@ -1264,3 +1264,22 @@ def test_randomised_whole_parameter_space_against_the_oracle(cuda, oracle):
         assert (got == want).all(), (what, int((got != want).sum()), np.argwhere(got != want)[:3].tolist())
         ran += 1
     assert ran >= 30 and refused <= max(2, ran // 10), (ran, refused, variants)
+
+
+def test_randomised_fp32_cores_against_the_fp64_dataflow(cuda, oracle):
+    """30 seeded random configurations of the DspReal flavour over the four CFAR cores (tests/util.py:random_fp32_configuration: Mem, Lis / GOS, ASR / CASH,
+    combined-window OS; window, guard, modes, ordered-statistic indices, linear / log, peak grouping; 64 ... 4096 points): thresholds within 1e-4 of the
+    fp64 dataflow, decided detections identical"""
+    import os
+    from tests.util import check_fp32_against_f64, random_fp32_configuration
+    rng = np.random.default_rng(int(os.environ.get("RSP_FUZZ_SEED", "888")))
+    variants = set()
+    for trial in range(int(os.environ.get("RSP_FUZZ_TRIALS", "30"))):
+        c = random_fp32_configuration(rng, trial, sizes=(6, 8, 10, 11, 12))
+        if c is None:
+            continue
+        p, log_n, regs, scaler, x32, what = c
+        thr, pk, variant = run_f32(cuda, p, log_n, 2, regs, scaler, x32)
+        variants.add(variant.split("<")[0])
+        check_fp32_against_f64(oracle, what, log_n, regs, scaler, x32, thr, pk, tol=REL_TOL)
+    assert "chain_f32" in variants, variants

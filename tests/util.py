@@ -101,3 +101,53 @@ def random_generic_configuration(rng, trial, fft_dir_reg=True, max_log=9):
     what = (trial, dict(npts=npts, n=n, radix=radix, dit=dit, bp=bp, trim=trim, use4=use4, keep=keep, ctype=ctype, cash=cash, W=W, G=G, gen=(gen_w, gen_g),
                         sel=sel, lin=lin, pg=pg, send_cut=send_cut, fft_dir=fft_dir), regs)
     return p, log_n, sel, regs, beats, fft_dir, what
+
+
+def random_fp32_configuration(rng, trial, sizes=(6, 8, 10)):
+    """one random configuration of the DspReal flavour over the four CFAR cores: (params, log_n, cfar registers, scaler, float32 beats [rows, n, 2],
+    description) or None when the draw has no valid window.  Shared by the CPU (emulated) and GPU randomised tests."""
+    from rsp_chains_b200 import synth
+    from rsp_chains_b200.params import (CACFARType, CFARParams, FFTParams, FftMagCfarVanillaParameters, GOSCFARType, MAGParams, OSGoldenCFARType)
+    core = ["mem", "gos", "cash", "os"][int(rng.integers(0, 4))]
+    log_n = int(rng.choice(list(sizes)))
+    n = 1 << log_n
+    W = 16 if core == "cash" else (1 << int(rng.integers(2, 5)) if core == "mem" else int(rng.integers(4, 17)))
+    G = int(rng.integers(1, 4))
+    lin = int(rng.integers(0, 2))
+    kl, kr = int(rng.integers(1, W + 1)), int(rng.integers(1, W + 1))
+    pg = int(rng.random() < 0.3) if core != "os" else 0
+    mode = 3 if core == "cash" else int(rng.integers(0, 3))
+    scaler = float(np.float32(rng.uniform(2.0, 5.0) if lin else rng.uniform(0.0, 2e-4)))
+    noise = 2.0 ** -int(rng.integers(3, 7))
+    if n <= 2 * W + 2 * G + 1:
+        return None
+    ctype = {"mem": CACFARType, "gos": GOSCFARType, "cash": CACFARType, "os": OSGoldenCFARType}[core]
+    p = FftMagCfarVanillaParameters(fftParams=FFTParams.DSPReal(numPoints=n, useBitReverse=True, runTime=True), magParams=MAGParams.fixed(),
+                                    cfarParams=CFARParams(leadLaggWindowSize=16, guardWindowSize=G, fftSize=n, CFARAlgorithm=ctype, sendCut=False,
+                                                          includeCASH=core == "cash", minSubWindowSize=4 if core == "cash" else None))
+    regs = dict(fftWin=n, logOrLinearMode=lin, divSum=2 if core == "cash" else int(np.log2(W)), peakGrouping=pg, cfarMode=mode, windowCells=W, guardCells=G,
+                indexLagg=kl, indexLead=kr, subWindowSize=4)
+    xc = synth.chirps_complex(3, n, seed=900 + trial, noise=noise)
+    x32 = np.ascontiguousarray(np.stack([xc.real, xc.imag], axis=-1).astype(np.float32))
+    return p, log_n, regs, scaler, x32, (trial, core, dict(log_n=log_n, W=W, G=G, lin=lin, pg=pg, kl=kl, kr=kr, scaler=scaler), regs)
+
+
+def check_fp32_against_f64(O, what, log_n, regs, scaler, x32, thr, pk, tol=1e-4):
+    """thresholds within tol (relative) of the fp64 dataflow; detections identical wherever the decision is not within 10 tol of a tie"""
+    from oracle.glue import f64_chain
+    core, W, G = what[1], regs["windowCells"], regs["guardCells"]
+    kw = {"mem": {}, "gos": dict(core=O.CORE_LIS, index_lagg=regs["indexLagg"], index_lead=regs["indexLead"]), "cash": dict(core=O.CORE_ASR, sub_cells=4),
+          "os": dict(core=O.CORE_OS)}[core]
+    xq = x32[..., 0].astype(np.float64) + 1j * x32[..., 1].astype(np.float64)
+    mag, want_thr, want_pk = f64_chain(O, xq, log_n, 2, regs, float(scaler), W, G, **kw)
+    # denominator: the threshold itself, floored at 1e-3 of the largest threshold and at 1e-2 of the row's largest magnitude -- the fp32 transform's own
+    # rounding noise is about eps * log2(N) * peak = 1e-6 of the row's peak, whatever the bin holds, so a threshold far below the peak (a small ordered
+    # statistic of the noise floor next to a strong target) cannot be held to 1e-4 of its own value in fp32
+    floor = np.maximum(1e-3 * np.abs(want_thr).max(), 1e-2 * np.abs(mag).max(axis=1, keepdims=True))
+    rel = np.abs(thr - want_thr) / np.maximum(np.abs(want_thr), floor)
+    assert rel.max() < tol, (what, float(rel.max()))
+    sure = np.abs(mag - want_thr) / np.maximum(np.abs(want_thr), floor) > 10 * tol
+    if regs.get("peakGrouping"):
+        nb = np.minimum(np.abs(mag - np.roll(mag, -1, axis=1)), np.abs(mag - np.roll(mag, -G, axis=1))) / np.maximum(np.abs(mag), floor) > 10 * tol
+        sure &= nb
+    assert (pk[sure] == want_pk[sure]).all(), what
