@@ -1283,3 +1283,55 @@ def test_randomised_fp32_cores_against_the_fp64_dataflow(cuda, oracle):
         variants.add(variant.split("<")[0])
         check_fp32_against_f64(oracle, what, log_n, regs, scaler, x32, thr, pk, tol=REL_TOL)
     assert "chain_f32" in variants, variants
+
+
+def test_randomised_wide_fft_blocks(cuda, oracle):
+    """30 seeded random configurations of the FFT block with wide beats (fft_wide_kernel): 16 ... 4096 points and run-time sizes, 17 ... 32-bit data,
+    9 ... 32-bit twiddles, any binary point, random grow stages and keep-LSB stages, every trim type, 3 / 4 multipliers, natural and bit-reversed output;
+    beats and the overflow status bit-exact against the oracle, or refused"""
+    import os
+    from tests.util import TRIM_TYPES
+    rng = np.random.default_rng(int(os.environ.get("RSP_FUZZ_SEED", "1234")))
+    ran = refused = 0
+    for trial in range(int(os.environ.get("RSP_FUZZ_TRIALS", "30"))):
+        s = int(rng.integers(4, 13))
+        n = 1 << s
+        dw = int(rng.integers(17, 33)) if rng.random() < 0.8 else 16
+        grow = [int(rng.random() < 0.35) for _ in range(s)] if (dw == 16 or rng.random() < 0.5) else [0] * s
+        if dw == 16 and not any(grow):
+            grow[int(rng.integers(0, s))] = 1           # (16 bits without grow is the 32-bit-beat kernels' configuration)
+        if dw + sum(grow) > 32 + 0 and dw > 16:
+            grow = [0] * s if dw + sum(grow) > 40 else grow
+        tw = int(rng.integers(9, min(32, dw + 8) + 1))
+        bp = int(rng.integers(0, dw - 1))
+        keep = [bool(rng.random() < 0.85) for _ in range(s)]
+        run_time = bool(rng.random() < 0.3)
+        log_n = s - 2 * int(rng.integers(0, (s - 2) // 2 + 1)) if run_time else s
+        kw = dict(trimType=str(rng.choice(TRIM_TYPES)), use4Muls=bool(rng.integers(0, 2)), useBitReverse=bool(rng.random() < 0.7), runTime=run_time)
+        what = (trial, dict(n=n, log_n=log_n, dw=dw, bp=bp, tw=tw, grow=grow, keep=keep, **kw))
+        m, rows = 1 << log_n, 3
+        re = rng.integers(-(1 << (dw - 1)), 1 << (dw - 1), (rows, m)); im = rng.integers(-(1 << (dw - 1)), 1 << (dw - 1), (rows, m))
+        re[1] >>= 3; im[1] >>= 3
+        beats = pack_beats64(re, im, dw)
+        try:
+            p = wide_params(n, dw, bp, tw, grow, keep, overflowReg=True, **kw)
+            with R.FftMagCfarChainVanilla(p) as ch:
+                if run_time:
+                    ch.memWriteWord(p.fftAddress.base, log_n)
+                k = ch.fft_out_beat_bytes // 8
+                d_in = cuda.from_numpy(beats.view(np.int64)).cuda()
+                d_out = cuda.zeros((rows, m, k), dtype=cuda.int64, device="cuda")
+                ch.fft(d_in, rows, d_out)
+                got = d_out.cpu().numpy().view(np.uint64)
+                ovf = ch.fft_overflow_flags()
+        except R.RspError as e:
+            assert e.status in (R._abi.RSP_EINVAL, R._abi.RSP_EUNSUPPORTED), (what, str(e))
+            refused += 1
+            continue
+        fft, _, _ = oracle_cfgs(oracle, p, log_n, 2, dict(fftWin=max(m, 64)))
+        want, want_ovf = oracle.fft_fixed_words64(fft, beats)
+        assert (got.reshape(want.shape) == want).all(), (what, np.argwhere(got.reshape(want.shape) != want)[:3].tolist())
+        assert ovf == want_ovf << (s - log_n), (what, hex(ovf), hex(want_ovf))
+        ran += 1
+    print(f"wide FFT: {ran} ran, {refused} refused")
+    assert ran >= 12 and refused <= ran, (ran, refused)
