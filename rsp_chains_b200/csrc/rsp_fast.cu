@@ -1087,6 +1087,19 @@ template <int S> struct OGeo {
   static_assert(NZ + (N / 16 + NZM + 1) / 2 <= FGeo<S>::XB, "the plane masks fit the exchange buffer behind the planes");
 };
 
+// Peak grouping on the core that reads its neighbours from the guard registers of both sides (CFARCoreWithLis.scala:191-192): a peak must also exceed x[n + 1] (read only when guardCells equals the generator's
+// guardWindowSize, else 0) and x[n - 1]; with guardCells = 0 both neighbours read 0.  X: the chirp's magnitudes (mhx layout).
+template <int S>
+__device__ __forceinline__ int lis_peak_grouping(const FastArgs &a, const short *X, int n, int cut, int pk) {
+  constexpr int N = 1 << S;
+  int left = 0, right = 0;
+  if (a.G != 0) {
+    if (a.pg_full > 0 && n + 1 < N) left = X[mhx<S>(n + 1)];
+    if (n >= 1) right = X[mhx<S>(n - 1)];
+  }
+  return (pk != 0 && cut > left && cut > right) ? 1 : 0;
+}
+
 // 16 x 16 bit-matrix transpose in 8 registers (word k = rows 2k | 2k+1 << 16): block swaps of size 8, 4, 2, 1.  In: row r = the 16-bit
 // value of bin r; out: row c = bit c of the 16 bins (bin r at bit r).  ~100 instructions per 16 bins, against 4 per bin and plane for
 // warp ballots (tests/test_kernel_layout.py holds the same algorithm in Python).
@@ -1258,7 +1271,7 @@ __global__ void __launch_bounds__(FGeo<S>::THREADS, 1024 / FGeo<S>::THREADS) cha
         int thr = ga.linear ? sar(t * a.scaler, a.thr_sh) : t * a.t_mul + a.sc_pre;   // (binary points at run time, see the GOS kernel)
         thr = both ? thr : 0;                         // the golden pads the edges with 0 (linear and log)
         const int cut = X[mhx<S>(n)];
-        const int pk = (both && (cut * a.ncut_mul + thr) < 0) ? 1 : 0;
+        const int pk = (both && (cut * a.ncut_mul + thr) < 0) ? 1 : 0;   // (no peak grouping in the cfarOS golden: refused by the host)
         thr = sar(thr, a.out_sh);
         ow[j] = ((uint32_t)thr & a.thr_mask) * (uint32_t)a.out_mul + (uint32_t)(n << 1) + (uint32_t)pk;
         if (pk && a.det_list != nullptr && active) {
@@ -1283,7 +1296,8 @@ __global__ void __launch_bounds__(FGeo<S>::THREADS, 1024 / FGeo<S>::THREADS) cha
 // cells starting at s is one radix selection per window start over NWD = ceil(W / 32) mask words (W <= 128), independent of k and -- per
 // mask word -- of W; the thresholds then read K[n + G + 1] and K[n - G - W] as in chain_fixed_fast_gos_kernel.  TWO: indexLagg and
 // indexLead differ, two selections.  No restriction on the cells' range (the bias makes them unsigned) or on W being a multiple of 8.
-template <int S, int NWD, bool TW3>
+// PG: peak grouping (the registers' other setting) as an instantiation of its own, so the default one is what it was.
+template <int S, int NWD, bool TW3, bool PG = false>
 __global__ void __launch_bounds__(FGeo<S>::THREADS, (NWD >= 3 ? 512 : 1024) / FGeo<S>::THREADS >= 1 ? (NWD >= 3 ? 512 : 1024) / FGeo<S>::THREADS : 1)
 chain_fixed_fast_gosb_kernel(const FastArgs a, const GosArgs ga) {
   using Gm = FGeo<S>;
@@ -1353,7 +1367,8 @@ chain_fixed_fast_gosb_kernel(const FastArgs a, const GosArgs ga) {
       // (the binary-point form of fast_cfar_bin at run time: without binary points the shifts are 0, t_mul 1, ncut_mul -1, sc_pre = scaler)
       const int thr = ga.linear ? sar(t * a.scaler, a.thr_sh) : t * a.t_mul + a.sc_pre;
       const int cut = X[mhx<S>(n)];
-      const int pk = (cut * a.ncut_mul + thr) < 0 ? 1 : 0;
+      int pk = (cut * a.ncut_mul + thr) < 0 ? 1 : 0;
+      if (PG) pk = lis_peak_grouping<S>(a, X, n, cut, pk);
       const int tf = sar(thr, a.out_sh);
       if (a.out != nullptr) gout[n] = ((uint32_t)tf & a.thr_mask) * (uint32_t)a.out_mul + (uint32_t)(n << 1) + (uint32_t)pk;
       if (pk && a.det_list != nullptr && active) {
@@ -1463,13 +1478,13 @@ static rsp_status launch_fast_gos(const LaunchCtx &c, const FastArgs &fa, const 
   return RSP_OK;
 }
 
-template <int S, int NWD, bool TW3>
+template <int S, int NWD, bool TW3, bool PG = false>
 static rsp_status launch_fast_gosb_inst(const LaunchCtx &c, const FastArgs &fa, const GosArgs &ga, cudaStream_t st, const char **err) {
   using Gm = FGeo<S>;
   static int occ_dev[64] = {0};
   int &occ = occ_dev[c.device & 63];
   const size_t smem = (size_t)Gm::CPC * (Gm::ROW + OGeo<S>::KW) * sizeof(uint32_t);
-  auto kernel = chain_fixed_fast_gosb_kernel<S, NWD, TW3>;
+  auto kernel = chain_fixed_fast_gosb_kernel<S, NWD, TW3, PG>;
   if (!occ) { const rsp_status s = launch_cfg(kernel, smem, Gm::THREADS, &occ, err); if (s != RSP_OK) return s; }
   const unsigned groups = (fa.n_rows + Gm::CPC - 1) / Gm::CPC;
   const unsigned grid = std::max(1u, std::min(groups, (unsigned)(c.sm_count * occ)));
@@ -1481,6 +1496,16 @@ template <int S>
 static rsp_status launch_fast_gosb(const LaunchCtx &c, const FastArgs &fa, const GosArgs &ga, cudaStream_t st, const char **err) {
   const int nwd = (fa.W + 31) / 32;
   const bool tw3 = fa.tw3 != nullptr;
+  if (fa.pg_full >= 0) switch (nwd * 2 + (tw3 ? 1 : 0)) {
+    case 2: return launch_fast_gosb_inst<S, 1, false, true>(c, fa, ga, st, err);
+    case 3: return launch_fast_gosb_inst<S, 1, true, true>(c, fa, ga, st, err);
+    case 4: return launch_fast_gosb_inst<S, 2, false, true>(c, fa, ga, st, err);
+    case 5: return launch_fast_gosb_inst<S, 2, true, true>(c, fa, ga, st, err);
+    case 6: return launch_fast_gosb_inst<S, 3, false, true>(c, fa, ga, st, err);
+    case 7: return launch_fast_gosb_inst<S, 3, true, true>(c, fa, ga, st, err);
+    case 8: return launch_fast_gosb_inst<S, 4, false, true>(c, fa, ga, st, err);
+    default: return launch_fast_gosb_inst<S, 4, true, true>(c, fa, ga, st, err);
+  }
   switch (nwd * 2 + (tw3 ? 1 : 0)) {
     case 2: return launch_fast_gosb_inst<S, 1, false>(c, fa, ga, st, err);
     case 3: return launch_fast_gosb_inst<S, 1, true>(c, fa, ga, st, err);
@@ -1547,7 +1572,7 @@ rsp_status RSP_CAT(launch_fast_size_, RSP_FAST_S)(int core, int cmode, bool line
   (void)ga; (void)ej;
   return launch_fast_modes<S, 8>(cmode, linear, fa.pg_full >= 0, ctx, fa, st, err);
 #else
-  if (core == CORE_LIS) return (gos_use_bitplanes(fa.W) || fa.tw3 != nullptr || fa.bpc || fa.cfar_only) ? launch_fast_gosb<S>(ctx, fa, ga, st, err) : launch_fast_gos<S>(ctx, fa, ga, st, err);
+  if (core == CORE_LIS) return (gos_use_bitplanes(fa.W) || fa.tw3 != nullptr || fa.bpc || fa.cfar_only || fa.pg_full >= 0) ? launch_fast_gosb<S>(ctx, fa, ga, st, err) : launch_fast_gos<S>(ctx, fa, ga, st, err);
   if (core == CORE_OS) return launch_fast_os<S>(ctx, fa, ga, st, err);
 #endif
 #if RSP_FAST_S == 10
@@ -1645,7 +1670,7 @@ static bool fast_bps_ok(const FxArgs &a) {   // binary points in the CFAR operan
 }
 static bool fast_gos_supported(const FxArgs &a) {
   if (a.core != CORE_LIS || a.cfar_algorithm != 1) return false;
-  if (a.in_w != 16 || !fast_bps_ok(a) || a.send_cut || a.peak_grouping) return false;
+  if (a.in_w != 16 || !fast_bps_ok(a) || a.send_cut) return false;   // (peak grouping: the <PG> instantiations)
   if (a.thr_w < 1 || a.thr_w > 32 || a.G < 0 || a.W < 1 || a.W > 128) return false;   // (W not a multiple of 8: bit planes only)
   if (a.idx_lagg < 1 || a.idx_lagg > a.W || a.idx_lead < 1 || a.idx_lead > a.W) return false;
   return a.out != nullptr && a.binw + 1 <= 31;

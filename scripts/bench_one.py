@@ -56,9 +56,9 @@ elif key == "c2pg":
 elif key == "c4os":
     os_regs = dict(fftWin=4096, thresholdScaler=2, logOrLinearMode=1, peakGrouping=0, cfarMode=0, windowCells=64, guardCells=4, indexLagg=48, indexLead=48)
     B.run_case("C4 GOS", B.fixed_params(4096, 64, 4, GOSCFARType), 12, os_regs, 1024, 1)
-elif key == "c4os16":
-    os_regs = dict(fftWin=4096, thresholdScaler=2, logOrLinearMode=1, peakGrouping=0, cfarMode=0, windowCells=64, guardCells=4, indexLagg=48, indexLead=48)
-    B.run_case("C4 x 16 GOS", B.fixed_params(4096, 64, 4, GOSCFARType), 12, os_regs, 16384, 1)
+elif key in ("c4os16", "c4os16pg"):
+    os_regs = dict(fftWin=4096, thresholdScaler=2, logOrLinearMode=1, peakGrouping=int(key == "c4os16pg"), cfarMode=0, windowCells=64, guardCells=4, indexLagg=48, indexLead=48)
+    B.run_case("C4 x 16 GOS" + (", peakGrouping = 1" if key == "c4os16pg" else ""), B.fixed_params(4096, 64, 4, GOSCFARType), 12, os_regs, 16384, 1)
 elif key in ("c4os16d", "c4osbd"):      # the same on full-range random beats: every plane is populated everywhere (worst case of the bit-plane selection)
     from rsp_chains_b200 import synth
     from rsp_chains_b200.params import OSGoldenCFARType

@@ -1335,3 +1335,44 @@ def test_randomised_wide_fft_blocks(cuda, oracle):
         ran += 1
     print(f"wide FFT: {ran} ran, {refused} refused")
     assert ran >= 12 and refused <= ran, (ran, refused)
+
+
+@pytest.mark.parametrize("ctype,log_n,bp,W,G,gws,kl,kr,lin", [("gos", 12, 0, 64, 4, 4, 48, 48, 1),      # C4 reading (A) with the testers' peakGrouping = 1
+                                                               ("gos", 10, 0, 16, 2, 4, 12, 5, 0),      # guardCells below the generator's: x[n + 1] reads 0
+                                                               ("gos", 14, 12, 100, 3, 3, 77, 77, 1), ("gos", 11, 0, 24, 1, 1, 1, 24, 1),
+                                                               ("gos", 13, 14, 40, 2, 2, 30, 9, 0)])
+def test_bit_plane_kernels_peak_grouping(cuda, oracle, ctype, log_n, bp, W, G, gws, kl, kr, lin):
+    """peakGrouping = 1 on the GOS bit-plane kernel (the cfarOS golden has no peak grouping: refused; neighbours x[n + 1] and x[n - 1] from the guard registers, CFARCoreWithLis.scala:191-192): the chain
+    and the CFAR block alone on stored profiles, bit-exact on the specialised variant, fewer peaks than without grouping, the detection list"""
+    n = 1 << log_n
+    rows = 6 if log_n <= 12 else 3
+    beats = np.concatenate([synth.chirps_fixed(rows - 2, n, seed=280 + log_n, noise=2.0 ** -4), synth.random_beats(2, n, seed=290 + log_n)])
+    p = fixed_params(n, 128 if W > 64 else 64, gws, bp=bp, ctype=GOSCFARType if ctype == "gos" else R.OSGoldenCFARType)
+    p.cfarParams.protoScaler = FixedPoint(16, bp)
+    regs = dict(fftWin=n, thresholdScaler=int(2.5 * (1 << bp)) if lin else max(1, int(0.002 * (1 << bp))), logOrLinearMode=lin, peakGrouping=1, cfarMode=0, windowCells=W,
+                guardCells=G, indexLagg=kl, indexLead=kr)
+    fft, mag, cfar = oracle_cfgs(oracle, p, log_n, 2, regs)
+    want, _, want_mag = oracle.chain_fixed_words(fft, mag, cfar, beats, want_stages=True)
+    _, _, peak0 = decode_cfar_words(oracle.chain_fixed_words(*oracle_cfgs(oracle, p, log_n, 2, dict(regs, peakGrouping=0)), beats), n)
+    name = f"chain_fixed_fast_gos<{log_n}>" if ctype == "gos" else f"chain_fixed_fast_os<{log_n}>"
+    with R.FftMagCfarChainVanilla(p) as ch:
+        configure(ch, log_n, 2, regs)
+        assert ch.variant == name, ch.variant
+        d_in = to_dev(cuda, beats)
+        d_out = cuda.zeros_like(d_in)
+        det_list = cuda.zeros((rows * n, 4), dtype=cuda.int32, device="cuda")
+        det_count = cuda.zeros(1, dtype=cuda.int32, device="cuda")
+        ch.run(d_in, rows, 1, out=d_out, det_list=det_list, det_count=det_count)
+        d_out2 = cuda.zeros_like(d_in)
+        launches = ch.kernel_launches
+        ch.cfar(to_dev(cuda, np.ascontiguousarray(want_mag).astype(np.uint32)), rows, out=d_out2)      # the CFAR block alone on the oracle's magnitudes
+        cuda.cuda.synchronize()
+        assert ch.kernel_launches == launches + 1
+        got, got2 = from_dev_u32(d_out), from_dev_u32(d_out2)
+        k = int(det_count.item())
+        dets = det_list[:k].cpu().numpy()
+    assert (got == want).all(), f"{int((got != want).sum())} beats differ, first at {np.argwhere(got != want)[:3].tolist()}"
+    assert (got2 == want).all(), f"CFAR alone: {int((got2 != want).sum())} beats differ, first at {np.argwhere(got2 != want)[:3].tolist()}"
+    thr, bins, peak = decode_cfar_words(want, n)
+    assert k == int(peak.sum()) and 0 < k <= int(peak0.sum())
+    assert set((int(d[0]), int(d[1])) for d in dets) == set(map(tuple, np.argwhere(peak == 1).tolist()))
