@@ -970,7 +970,7 @@ extern "C" const char *rsp_variant_name(rsp_chain *c) {
     if (plan_fixed(c->p, c->r, c->t, STAGE_FFT, STAGE_CFAR, a, pl, err) != RSP_OK) { c->variant = "invalid: " + err; return c->variant.c_str(); }
     a.out = reinterpret_cast<uint32_t *>(c);   // any non-null output: the name is that of the full chain with output beats requested
     bind_fixed(c, a);
-    const char *m = pl.mode == MODE_FAST ? "fast" : (pl.mode == MODE_FAST3 ? "fast3" : (a.radix2 ? (a.dit ? "radix2-dit" : "radix2-dif") : (a.dit ? "radix22-dit" : "generic")));
+    const char *m = pl.mode == MODE_FAST ? "fast" : (pl.mode == MODE_FAST3 ? "fast3" : pl.mode == MODE_FASTC ? "fast-convergent" : pl.mode == MODE_FAST3C ? "fast3-convergent" : (a.radix2 ? (a.dit ? "radix2-dit" : "radix2-dif") : (a.dit ? "radix22-dit" : "generic")));
     if (fast_chain_supported(pl, a)) std::snprintf(buf, sizeof(buf), a.core == CORE_LIS ? "chain_fixed_fast_gos<%d>" : (a.core == CORE_OS ? "chain_fixed_fast_os<%d>" : "chain_fixed_fast<%d>"), pl.S);
     else std::snprintf(buf, sizeof(buf), "chain_fixed<%d,%s>", pl.S, m);
   } else {

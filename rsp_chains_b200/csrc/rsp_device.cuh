@@ -35,8 +35,11 @@ enum { STAGE_FFT = 0, STAGE_MAG = 1, STAGE_CFAR = 2 };
 enum { MODE_GENERIC = 0,   // every parameter read at run time
        MODE_FAST = 1,      // 16-bit data, RoundHalfUp, scale every stage, forward, product trimmed once (binPoint <= 1)
        MODE_FAST3 = 2,     // as FAST but 3-multiplier product with per-product trim (binPoint >= 2, use4Muls = false)
-       MODE_RADIX2 = 3 };  // sdfRadix "2" (SDFChainRadix2.scala), DIF or DIT; every parameter read at run time like GENERIC
+       MODE_RADIX2 = 3,    // sdfRadix "2" (SDFChainRadix2.scala), DIF or DIT; every parameter read at run time like GENERIC
+       MODE_FASTC = 4,     // as FAST with trimType = Convergent (what the reference's SQNR specs elaborate), rounding folded at compile time
+       MODE_FAST3C = 5 };  // as FAST3 with trimType = Convergent
 constexpr bool mode_is_generic(int m) { return m == MODE_GENERIC || m == MODE_RADIX2; }
+constexpr bool mode_is_convergent(int m) { return m == MODE_FASTC || m == MODE_FAST3C; }
 
 struct Detection { uint32_t chirp, bin; int32_t threshold, cut; };
 
@@ -136,6 +139,13 @@ template <typename I> RSP_HD I trim_rt(I v, int shift, int mode) {
   }
 }
 
+// Convergent (round half to even) with the shift known to be >= 1: the compile-time form of trim_rt's TRIM_CONVERGENT case
+RSP_HD int trim_conv(int v, int shift) {
+  const int half = 1 << (shift - 1), q = v >> shift, r = v & ((1 << shift) - 1);
+  return q + ((r > half || (r == half && (q & 1))) ? 1 : 0);
+}
+RSP_HD int trim_conv1(int v) { return (v >> 1) + ((v & (v >> 1)) & 1); }   // shift 1: the remainder is the half exactly when v is odd
+
 // ------------------------------------------------------------------------------------------------ geometry
 constexpr int fx_n_passes(int S) { return S <= 4 ? 1 : ((S % 4 == 0) ? S / 4 : S / 4 + 1); }
 constexpr int fx_pass_size(int S, int k) {
@@ -168,7 +178,10 @@ template <int MODE> RSP_HD bool butterfly(const FxArgs &a, int scale, int &ar, i
     const int lim = 1 << (a.data_width - 1);
     ov = sr >= lim || si >= lim || dr >= lim || di >= lim;
   }
-  if (!mode_is_generic(MODE)) {
+  if (mode_is_convergent(MODE)) {
+    ar = trim_conv1(sr); ai = trim_conv1(si);
+    cr = wrap16(trim_conv1(dr)); ci = wrap16(trim_conv1(di));
+  } else if (!mode_is_generic(MODE)) {
     // RoundHalfUp div2: (v + 1) >> 1.  The sum cannot leave 16 bits; the difference can (+32768) and wraps.
     ar = (sr + 1) >> 1; ai = (si + 1) >> 1;
     cr = wrap16((dr + 1) >> 1); ci = wrap16((di + 1) >> 1);
@@ -201,6 +214,19 @@ template <int MODE> RSP_HD void cmul(const FxArgs &a, int &xr, int &xi, uint32_t
     const int sh = a.tw_bp, half = 1 << (sh - 1);
     xr = wrap16((ar * br - ai * bi + half) >> sh);
     xi = wrap16((ar * bi + ai * br + half) >> sh);
+  } else if (MODE == MODE_FASTC) {
+    const int sh = a.tw_bp;
+    xr = wrap16(trim_conv(ar * br - ai * bi, sh));
+    xi = wrap16(trim_conv(ar * bi + ai * br, sh));
+  } else if (MODE == MODE_FAST3C) {
+    const int bp_a = a.bp, bp_b = a.tw_bp;
+    const int ctx_bp = (bp_a > bp_b ? bp_a : bp_b) + 1;
+    const int s1 = bp_a + bp_b - ctx_bp, s2 = ctx_bp - bp_a;
+    const int k1 = trim_conv(ar * (br + bi), s1);
+    const int k2 = trim_conv((ar + ai) * bi, s1);
+    const int k3 = trim_conv((ai - ar) * br, s1);
+    xr = wrap16(trim_conv(k1 - k2, s2));
+    xi = wrap16(trim_conv(k1 + k3, s2));
   } else if (MODE == MODE_FAST3) {
     const int bp_a = a.bp, bp_b = a.tw_bp;
     const int ctx_bp = (bp_a > bp_b ? bp_a : bp_b) + 1;

@@ -422,14 +422,17 @@ inline rsp_status plan_fixed(const rsp_chain_params &p, const Regs &r, const Tab
   // kernel variant
   const int bp_a = a.bp, bp_b = a.tw_bp;
   const int s1 = bp_a + bp_b - ((bp_a > bp_b ? bp_a : bp_b) + 1);
-  const bool common = f.dataWidth == 16 && f.trimType == RSP_TRIM_ROUND_HALF_UP && a.keep_mask == smask && a.fft_dir == 1 &&
-                      p.mag.dataWidth == 16;
+  const bool shape = f.dataWidth == 16 && a.keep_mask == smask && a.fft_dir == 1 && p.mag.dataWidth == 16;
+  const bool common = shape && f.trimType == RSP_TRIM_ROUND_HALF_UP;
+  const bool common_c = shape && f.trimType == RSP_TRIM_CONVERGENT;   // (RSP_TRIM_CONVERGENT also stands for RoundHalfToEven)
   pl.mode = MODE_GENERIC;
   a.ovf_shift = a.dit ? 0 : Smax - S;    // physical stage of this transform's stage 0 (a run-time size uses the last S stages in DIF)
   if (a.radix2 || a.dit) { pl.mode = MODE_RADIX2; return RSP_OK; }   // run-time-parameter kernel with the radix-2 stage structure
   if (f.overflowReg && first_stage == STAGE_FFT) return RSP_OK;      // the overflow status is computed by the run-time-parameter kernels
   if (common && s1 <= 0) pl.mode = MODE_FAST;
   else if (common && s1 >= 1 && !f.use4Muls) pl.mode = MODE_FAST3;
+  else if (common_c && s1 <= 0) pl.mode = MODE_FASTC;
+  else if (common_c && s1 >= 1 && !f.use4Muls) pl.mode = MODE_FAST3C;
   return RSP_OK;
 }
 

@@ -1,12 +1,13 @@
 // rsp_inst.cu -- instantiates one slice of the templated chain kernels.  Compiled once per RSP_UNIT (see Makefile):
-//   0/1 generic fixed, 2/3 fast fixed, 4/5 fast3 fixed, 8/9 radix-2 fixed (low / high transform sizes); 6/7 fp32 (low / high).
+//   0/1 generic fixed, 2/3 fast fixed, 4/5 fast3 fixed, 8/9 radix-2 fixed, 10/11 fast Convergent, 12/13 fast3 Convergent (low / high transform sizes);
+//   6/7 fp32 (low / high).
 #include <algorithm>
 
 #include "rsp_kernels.cuh"
 #include "rsp_launch.hpp"
 
 #ifndef RSP_UNIT
-#error "compile with -DRSP_UNIT=0..9"
+#error "compile with -DRSP_UNIT=0..13"
 #endif
 
 namespace rsp {
@@ -33,6 +34,10 @@ static rsp_status launch_fixed_sm(const LaunchCtx &c, const FxArgs &a, cudaStrea
 #define RSP_MODE_OF_UNIT MODE_FAST
 #elif RSP_UNIT / 2 == 4
 #define RSP_MODE_OF_UNIT MODE_RADIX2
+#elif RSP_UNIT / 2 == 5
+#define RSP_MODE_OF_UNIT MODE_FASTC
+#elif RSP_UNIT / 2 == 6
+#define RSP_MODE_OF_UNIT MODE_FAST3C
 #else
 #define RSP_MODE_OF_UNIT MODE_FAST3
 #endif

@@ -22,5 +22,10 @@ p = B.fixed_params(1024, 64, 4); p.cfarParams.includeCASH = True; p.cfarParams.m
 case("CASH (ASR core), cfarMode 3", p, dict(base, cfarMode=3, divSum=2))
 p = B.fixed_params(1024, 64, 4); p.fftParams.trimType = "Convergent"
 case("CA, Convergent rounding", p, base)
+import rsp_chains_b200 as R
+p = R.fft_mag_cfar_chain_vanilla_app_params(); p.fftParams.trimType = "Convergent"
+case("FftMagCfarChainVanillaApp (binPoint 12), Convergent", p, dict(base, thresholdScaler=int(3.5 * 4096), divSum=6, windowCells=64))
+p = B.fixed_params(1024, 64, 4); p.fftParams.trimType = "RoundDown"
+case("CA, RoundDown (any other trim type)", p, base)
 p = B.fixed_params(1024, 64, 4); p.cfarParams.sendCut = True
 case("CA, sendCut", p, base)

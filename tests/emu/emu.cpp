@@ -142,6 +142,8 @@ int rsp_emu_run_fixed(const rsp_chain_params *p, const uint32_t *fft_regs, const
   switch (pl.mode) {
   case MODE_FAST: ok = dispatch_fixed<MODE_FAST>(pl.S, a); break;
   case MODE_FAST3: ok = dispatch_fixed<MODE_FAST3>(pl.S, a); break;
+  case MODE_FASTC: ok = dispatch_fixed<MODE_FASTC>(pl.S, a); break;
+  case MODE_FAST3C: ok = dispatch_fixed<MODE_FAST3C>(pl.S, a); break;
   case MODE_RADIX2: ok = dispatch_fixed<MODE_RADIX2>(pl.S, a); break;
   default: ok = dispatch_fixed<MODE_GENERIC>(pl.S, a); break;
   }

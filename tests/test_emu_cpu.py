@@ -339,3 +339,20 @@ def test_emu_randomised_fp32_cores(emu, oracle):
                                  C.c_uint32(rows), thr.ctypes.data_as(C.c_void_p), mask.ctypes.data_as(C.c_void_p), err, 512)
         assert rc == 0, (err.value.decode(), what)
         check_fp32_against_f64(oracle, what, log_n, regs, scaler, x32, thr, unpack_mask(mask, n))
+
+
+@pytest.mark.parametrize("bp,log_n,mode_want", [(0, 10, 4), (1, 8, 4), (2, 6, 5), (12, 10, 5), (14, 8, 5), (15, 5, 5)])
+def test_emu_convergent_modes(emu, oracle, bp, log_n, mode_want):
+    """trimType = Convergent (the reference's SQNR specs: Radix22SQNRSpec) on the compile-time modes FASTC / FAST3C of the run-time-parameter kernel:
+    full-range random beats (every tie and wrap), bit-exact against the oracle, chain and FFT block alone"""
+    n = 1 << log_n
+    p = chain_params(n, bp, "Convergent", W=max(2, min(16, n // 8)), G=1)
+    W = p.cfarParams.leadLaggWindowSize
+    regs = dict(fftWin=n, thresholdScaler=int(3.0 * (1 << bp)), logOrLinearMode=1, divSum=max(0, W.bit_length() - 1), peakGrouping=0, cfarMode=0, windowCells=W, guardCells=1)
+    beats = np.concatenate([synth.random_beats(6, n, seed=40 + log_n), synth.chirps_fixed(3, n, seed=41 + log_n), np.full((1, n), 0x80008000, dtype=np.uint32)])
+    fft, mag, cfar = oracle_cfgs(oracle, p, log_n, 2, regs)
+    got, _, kmode, _ = emu_fixed(emu, p, log_n, 2, regs, beats)
+    assert kmode == mode_want, kmode
+    assert (got == oracle.chain_fixed_words(fft, mag, cfar, beats)).all()
+    got, _, kmode, _ = emu_fixed(emu, p, log_n, 2, regs, beats, last=STAGE_FFT)
+    assert kmode == mode_want and (got == oracle.fft_fixed_words(fft, beats)).all()

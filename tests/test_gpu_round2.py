@@ -1376,3 +1376,32 @@ def test_bit_plane_kernels_peak_grouping(cuda, oracle, ctype, log_n, bp, W, G, g
     thr, bins, peak = decode_cfar_words(want, n)
     assert k == int(peak.sum()) and 0 < k <= int(peak0.sum())
     assert set((int(d[0]), int(d[1])) for d in dets) == set(map(tuple, np.argwhere(peak == 1).tolist()))
+
+
+@pytest.mark.parametrize("log_n,bp", [(10, 0), (14, 0), (12, 1), (6, 0), (10, 12), (14, 14), (11, 2), (13, 15), (8, 12)])
+def test_convergent_rounding_on_the_compile_time_modes(cuda, oracle, log_n, bp):
+    """trimType = Convergent (what the reference's SQNR specs elaborate, Radix22SQNRSpec.scala) on the run-time-parameter kernel's compile-time modes
+    <fast-convergent> / <fast3-convergent> (before: the <generic> mode, 7 Gsamples/s): chain and FFT block alone bit-exact on full-range random
+    beats (every tie, every wrap), chirps and the -32768 corners"""
+    n = 1 << log_n
+    rows = 7 if log_n <= 12 else 4
+    beats = np.concatenate([synth.random_beats(rows - 3, n, seed=310 + log_n), synth.chirps_fixed(2, n, seed=320 + log_n, noise=2.0 ** -4),
+                            np.full((1, n), 0x80008000, dtype=np.uint32)])
+    W, G = (16, 2) if n >= 128 else (4, 1)
+    p = fixed_params(n, 64 if n >= 256 else 4, G, bp=bp)
+    p.fftParams.trimType = "Convergent"
+    p.cfarParams.protoScaler = FixedPoint(16, bp)
+    regs = dict(fftWin=n, thresholdScaler=int(3.0 * (1 << bp)), logOrLinearMode=1, divSum=int(np.log2(W)), peakGrouping=0, cfarMode=0, windowCells=W, guardCells=G)
+    fft, mag, cfar = oracle_cfgs(oracle, p, log_n, 2, regs)
+    want, want_fft, _ = oracle.chain_fixed_words(fft, mag, cfar, beats, want_stages=True)
+    with R.FftMagCfarChainVanilla(p) as ch:
+        configure(ch, log_n, 2, regs)
+        assert ch.variant == f"chain_fixed<{log_n},{'fast-convergent' if bp <= 1 else 'fast3-convergent'}>", ch.variant
+        d_in = to_dev(cuda, beats)
+        d_out, d_fft = cuda.zeros_like(d_in), cuda.zeros_like(d_in)
+        ch.run(d_in, rows, 1, out=d_out)
+        ch.fft(d_in, rows, d_fft)
+        cuda.cuda.synchronize()
+        got, got_fft = from_dev_u32(d_out), from_dev_u32(d_fft)
+    assert (got_fft == want_fft).all(), f"FFT: {int((got_fft != want_fft).sum())} beats differ"
+    assert (got == want).all(), f"{int((got != want).sum())} beats differ, first at {np.argwhere(got != want)[:3].tolist()}"
