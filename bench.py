@@ -102,7 +102,17 @@ class ClockSampler:
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
     def __init__(self, index):
-        self.index, self.rows, self.proc = index, [], None
+        self.index, self.rows, self.proc, self.mark_at = index, [], None, 0
+
+    def wait_first(self, timeout=8.0):
+        """nvidia-smi needs 0.1 - 0.5 s to come up (longer on an 8-GPU box): wait for its first line so that the timed region is sampled from its start"""
+        t0 = time.perf_counter()
+        while self.proc is not None and not self.rows and time.perf_counter() - t0 < timeout:
+            time.sleep(0.01)
+
+    def mark(self):
+        """the timed region starts here: earlier rows (start-up, warm-up) are not counted"""
+        self.mark_at = len(self.rows)
 
     def start(self):
         try:
@@ -122,7 +132,7 @@ class ClockSampler:
         time.sleep(0.15)
         self.proc.terminate()
         sm, mx, reasons = [], None, set()
-        for r in self.rows:
+        for r in self.rows[self.mark_at:]:
             try:
                 sm.append(float(r[0])); mx = float(r[1])
             except Exception:
@@ -464,12 +474,15 @@ def main():
         return float(t.item())
 
     n_chirps = CHIRPS_PER_FRAME * FRAMES_PER_GPU
-    for _ in range(warmup):
-        ch.run(d_in, n_chirps, N_RX, out=d_out)
-    barrier()
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
+        sampler.wait_first()
+    barrier()
+    for _ in range(warmup):
+        ch.run(d_in, n_chirps, N_RX, out=d_out)
+    barrier()
+    sampler.mark()
     launches0 = ch.kernel_launches
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
     ev[0].record(stream)
